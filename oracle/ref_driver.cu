@@ -1,0 +1,268 @@
+// TEST/BASELINE INFRASTRUCTURE — not part of the product, never linked into libtcnn_b200.so.
+//
+// A small harness (our own code) over the UNMODIFIED reference's public C++ API
+// (/root/reference/include/tiny-cuda-nn/config.h:53 create_from_config, trainer.h:163 training_step,
+// object.h:147 inference).  Built by oracle/build_ref.sh into oracle/_ref/ref_driver; runs only on the GPU box.
+//
+//   ref_driver dump  <cfg.json> <n_in> <n_out> <B> <input.f32> <target.f32> <outdir> [params.f32]
+//       golden vectors for one batch: init params, per-level (scale,res,hashmap_size), grid indices computed by
+//       the reference's own __device__ grid_index/pos_fract, encoded features, network output, loss, param grads,
+//       params after one Adam step.
+//   ref_driver curve <cfg.json> <n_in> <n_out> <B> <n_steps> <seed> <outdir>
+//       loss after every step on pcg32-generated batches with the analytic target below.
+//   ref_driver bench <cfg.json> <n_in> <n_out> <B> <steps> <warmup>
+//       one JSON line: training / inference ms per step (CUDA events), device-resident inputs and
+//       host-buffer (H2D inside the timed region) variants.
+#include <tiny-cuda-nn/common_device.h>
+#include <tiny-cuda-nn/config.h>
+#include <tiny-cuda-nn/random.h>
+
+#include <chrono>
+#include <cstdio>
+#include <fstream>
+#include <iostream>
+#include <string>
+#include <vector>
+
+using namespace tcnn;
+using precision_t = network_precision_t;
+
+static std::vector<char> read_file(const std::string& p) {
+	std::ifstream f(p, std::ios::binary);
+	if (!f) { throw std::runtime_error("cannot open " + p); }
+	return std::vector<char>((std::istreambuf_iterator<char>(f)), std::istreambuf_iterator<char>());
+}
+
+template <typename T>
+static void write_dev(const std::string& path, const T* dev, size_t n) {
+	std::vector<T> h(n);
+	CUDA_CHECK_THROW(cudaMemcpy(h.data(), dev, n * sizeof(T), cudaMemcpyDeviceToHost));
+	std::ofstream f(path, std::ios::binary);
+	f.write((const char*)h.data(), n * sizeof(T));
+}
+
+template <typename T>
+static void write_host(const std::string& path, const std::vector<T>& h) {
+	std::ofstream f(path, std::ios::binary);
+	f.write((const char*)h.data(), h.size() * sizeof(T));
+}
+
+// Analytic training target shared with tests/bench of the product (tiny-cuda-nn_b200/tinycudann/synthetic.py).
+__global__ void synth_target(uint32_t n, uint32_t n_in, uint32_t n_out, const float* __restrict__ x, float* __restrict__ t) {
+	const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
+	if (i >= n) return;
+	float s = 0.0f;
+	for (uint32_t d = 0; d < n_in; ++d) s += x[i * n_in + d] * (1.0f + 0.5f * (float)d);
+	for (uint32_t c = 0; c < n_out; ++c) t[i * n_out + c] = 0.5f + 0.5f * sinf(6.2831853f * (float)(c + 1) * s);
+}
+
+// Indices as the reference's own device functions compute them (common_device.h:690-718, 825-868).
+template <uint32_t D>
+__global__ void dump_indices(uint32_t n, uint32_t n_levels, const uint32_t* __restrict__ hashmap_sizes, uint32_t base_resolution,
+	float log2_per_level_scale, const float* __restrict__ x, uint32_t* __restrict__ idx_out, float* __restrict__ scale_out, uint32_t* __restrict__ res_out) {
+	const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
+	const uint32_t level = blockIdx.y;
+	if (i >= n) return;
+	const float scale = grid_scale(level, log2_per_level_scale, base_resolution);
+	const uint32_t resolution = grid_resolution(scale);
+	if (i == 0) { scale_out[level] = scale; res_out[level] = resolution; }
+	float pos[D];
+	uvec<D> pos_grid;
+	for (uint32_t d = 0; d < D; ++d) pos_fract(x[i * D + d], &pos[d], &pos_grid[d], scale, identity_fun);
+	for (uint32_t c = 0; c < (1u << D); ++c) {
+		uvec<D> p;
+		for (uint32_t d = 0; d < D; ++d) p[d] = pos_grid[d] + ((c >> d) & 1u);
+		idx_out[((size_t)level * n + i) * (1u << D) + c] = grid_index<D, HashType::CoherentPrime>(GridType::Hash, hashmap_sizes[level], resolution, p);
+	}
+}
+
+static json load_cfg(const std::string& path) {
+	auto raw = read_file(path);
+	return json::parse(std::string(raw.begin(), raw.end()));
+}
+
+struct LevelTable { std::vector<uint32_t> offsets, sizes; };
+
+// Per-level entry counts as the reference's constructor derives them (encodings/grid.h:692-716),
+// evaluated with the reference's own host-callable grid_scale/grid_resolution.
+static LevelTable level_table(const json& enc, uint32_t n_in) {
+	const uint32_t L = enc.value("n_levels", 16u), log2T = enc.value("log2_hashmap_size", 19u), base = enc.value("base_resolution", 16u);
+	const float pls = enc.value("per_level_scale", 2.0f);
+	LevelTable t; uint32_t off = 0;
+	for (uint32_t l = 0; l < L; ++l) {
+		const uint32_t res = grid_resolution(grid_scale(l, std::log2(pls), base));
+		const uint32_t max_params = std::numeric_limits<uint32_t>::max() / 2;
+		uint32_t n = std::pow((float)res, (float)n_in) > (float)max_params ? max_params : powi(res, n_in);
+		n = std::min(next_multiple(n, 8u), 1u << log2T);
+		t.offsets.push_back(off); t.sizes.push_back(n); off += n;
+	}
+	t.offsets.push_back(off);
+	return t;
+}
+
+static int mode_dump(int argc, char** argv) {
+	if (argc < 9) { std::cerr << "dump: bad args\n"; return 2; }
+	json cfg = load_cfg(argv[2]);
+	const uint32_t n_in = std::stoul(argv[3]), n_out = std::stoul(argv[4]), B = std::stoul(argv[5]);
+	const std::string out = argv[8];
+	auto in_raw = read_file(argv[6]); auto tg_raw = read_file(argv[7]);
+	if (in_raw.size() != (size_t)B * n_in * 4 || tg_raw.size() != (size_t)B * n_out * 4) { std::cerr << "dump: size mismatch\n"; return 2; }
+
+	cudaStream_t stream; CUDA_CHECK_THROW(cudaStreamCreate(&stream));
+	auto model = create_from_config(n_in, n_out, cfg);
+	const size_t P = model.trainer->n_params();
+	write_dev(out + "/params_init.f32", model.trainer->params_full_precision(), P);
+	if (argc >= 10) {
+		auto p = read_file(argv[9]);
+		if (p.size() != P * 4) { std::cerr << "dump: params size mismatch\n"; return 2; }
+		model.trainer->set_params_full_precision((const float*)p.data(), P, false);
+	}
+	write_dev(out + "/params_used.f16", (const uint16_t*)model.trainer->params(), P);
+
+	GPUMatrix<float> input(n_in, B), target(n_out, B);
+	CUDA_CHECK_THROW(cudaMemcpy(input.data(), in_raw.data(), in_raw.size(), cudaMemcpyHostToDevice));
+	CUDA_CHECK_THROW(cudaMemcpy(target.data(), tg_raw.data(), tg_raw.size(), cudaMemcpyHostToDevice));
+
+	// indices / scales through the reference's device functions
+	json enc = cfg.value("encoding", json::object());
+	LevelTable lt = level_table(enc, n_in);
+	const uint32_t L = (uint32_t)lt.sizes.size();
+	const uint32_t F = enc.value("n_features_per_level", 2u);
+	if ((size_t)lt.offsets.back() * F != model.network->encoding()->n_params()) { std::cerr << "dump: level table disagrees with encoding->n_params()\n"; return 3; }
+	GPUMemory<uint32_t> d_sizes(L), d_idx((size_t)L * B * (1u << n_in)), d_res(L); GPUMemory<float> d_scale(L);
+	d_sizes.copy_from_host(lt.sizes);
+	const dim3 blocks{div_round_up(B, 256u), L, 1};
+	const float l2s = std::log2(enc.value("per_level_scale", 2.0f));
+	const uint32_t base = enc.value("base_resolution", 16u);
+	if (n_in == 2) dump_indices<2><<<blocks, 256, 0, stream>>>(B, L, d_sizes.data(), base, l2s, input.data(), d_idx.data(), d_scale.data(), d_res.data());
+	else if (n_in == 3) dump_indices<3><<<blocks, 256, 0, stream>>>(B, L, d_sizes.data(), base, l2s, input.data(), d_idx.data(), d_scale.data(), d_res.data());
+	else { std::cerr << "dump: n_in must be 2 or 3\n"; return 2; }
+	CUDA_CHECK_THROW(cudaStreamSynchronize(stream));
+	write_dev(out + "/indices.u32", d_idx.data(), d_idx.size());
+	write_dev(out + "/level_scale.f32", d_scale.data(), L);
+	write_dev(out + "/level_res.u32", d_res.data(), L);
+	write_host(out + "/level_size.u32", lt.sizes);
+
+	// encoded features (SoA [E x B], padded width) and network output
+	auto encoding = model.network->encoding();
+	GPUMatrixDynamic<precision_t> encoded(encoding->padded_output_width(), B, encoding->preferred_output_layout());
+	encoding->inference_mixed_precision(stream, input, encoded, false);
+	CUDA_CHECK_THROW(cudaStreamSynchronize(stream));
+	write_dev(out + "/encoded_soa.f16", (const uint16_t*)encoded.data(), (size_t)encoding->padded_output_width() * B);
+
+	GPUMatrix<float> prediction(n_out, B);
+	model.network->inference(stream, input, prediction);
+	CUDA_CHECK_THROW(cudaStreamSynchronize(stream));
+	write_dev(out + "/output.f32", prediction.data(), (size_t)n_out * B);
+
+	// one training step without the optimizer: loss + loss-scaled fp16 gradients
+	auto ctx = model.trainer->training_step(stream, input, target, nullptr, false);
+	const float loss = model.trainer->loss(stream, *ctx);
+	write_dev(out + "/grads.f16", (const uint16_t*)model.trainer->param_gradients(), P);
+	write_dev(out + "/output_padded.f16", (const uint16_t*)ctx->output.data(), (size_t)model.network->padded_output_width() * B);
+	write_dev(out + "/dL_doutput.f16", (const uint16_t*)ctx->dL_doutput.data(), (size_t)model.network->padded_output_width() * B);
+	// then the optimizer step on those gradients
+	model.trainer->optimizer_step(stream, default_loss_scale<precision_t>());
+	CUDA_CHECK_THROW(cudaStreamSynchronize(stream));
+	write_dev(out + "/params_after.f32", model.trainer->params_full_precision(), P);
+	std::ofstream(out + "/meta.json") << json{{"loss", loss}, {"n_params", P}, {"n_params_encoding", encoding->n_params()},
+		{"padded_output_width", model.network->padded_output_width()}, {"encoded_width", encoding->padded_output_width()},
+		{"B", B}, {"n_in", n_in}, {"n_out", n_out}, {"hyperparams", model.network->hyperparams()}}.dump(1);
+	std::cout << "dump ok loss=" << loss << " P=" << P << std::endl;
+	return 0;
+}
+
+static int mode_curve(int argc, char** argv) {
+	if (argc < 9) { std::cerr << "curve: bad args\n"; return 2; }
+	json cfg = load_cfg(argv[2]);
+	const uint32_t n_in = std::stoul(argv[3]), n_out = std::stoul(argv[4]), B = std::stoul(argv[5]), n_steps = std::stoul(argv[6]);
+	const uint64_t seed = std::stoull(argv[7]);
+	const std::string out = argv[8];
+	cudaStream_t stream; CUDA_CHECK_THROW(cudaStreamCreate(&stream));
+	auto model = create_from_config(n_in, n_out, cfg);
+	default_rng_t rng{seed};
+	GPUMatrix<float> input(n_in, B), target(n_out, B);
+	std::vector<float> losses(n_steps);
+	for (uint32_t i = 0; i < n_steps; ++i) {
+		generate_random_uniform<float>(stream, rng, (size_t)B * n_in, input.data());
+		synth_target<<<div_round_up(B, 256u), 256, 0, stream>>>(B, n_in, n_out, input.data(), target.data());
+		auto ctx = model.trainer->training_step(stream, input, target);
+		losses[i] = model.trainer->loss(stream, *ctx);
+	}
+	write_host(out + "/losses.f32", losses);
+	write_dev(out + "/params_final.f32", model.trainer->params_full_precision(), model.trainer->n_params());
+	std::cout << "curve ok first=" << losses.front() << " last=" << losses.back() << std::endl;
+	return 0;
+}
+
+static float time_loop(cudaStream_t stream, uint32_t steps, const std::function<void()>& body) {
+	cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+	CUDA_CHECK_THROW(cudaStreamSynchronize(stream));
+	cudaEventRecord(e0, stream);
+	for (uint32_t i = 0; i < steps; ++i) body();
+	cudaEventRecord(e1, stream);
+	CUDA_CHECK_THROW(cudaEventSynchronize(e1));
+	float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+	return ms / (float)steps;
+}
+
+static int mode_bench(int argc, char** argv) {
+	if (argc < 8) { std::cerr << "bench: bad args\n"; return 2; }
+	json cfg = load_cfg(argv[2]);
+	const uint32_t n_in = std::stoul(argv[3]), n_out = std::stoul(argv[4]), B = std::stoul(argv[5]);
+	const uint32_t steps = std::stoul(argv[6]), warmup = std::stoul(argv[7]);
+	cudaStream_t stream; CUDA_CHECK_THROW(cudaStreamCreate(&stream));
+	auto model = create_from_config(n_in, n_out, cfg);
+	default_rng_t rng{1337};
+	// several distinct resident batches so that consecutive steps do not see the same coordinates
+	const uint32_t n_batches = 4;
+	std::vector<GPUMatrix<float>> inputs, targets;
+	for (uint32_t b = 0; b < n_batches; ++b) {
+		inputs.emplace_back(n_in, B); targets.emplace_back(n_out, B);
+		generate_random_uniform<float>(stream, rng, (size_t)B * n_in, inputs[b].data());
+		synth_target<<<div_round_up(B, 256u), 256, 0, stream>>>(B, n_in, n_out, inputs[b].data(), targets[b].data());
+	}
+	GPUMatrix<float> prediction(n_out, B);
+	float *h_in, *h_tg, *h_loss;
+	CUDA_CHECK_THROW(cudaMallocHost(&h_in, (size_t)B * n_in * 4)); CUDA_CHECK_THROW(cudaMallocHost(&h_tg, (size_t)B * n_out * 4));
+	CUDA_CHECK_THROW(cudaMallocHost(&h_loss, 4));
+	CUDA_CHECK_THROW(cudaMemcpy(h_in, inputs[0].data(), (size_t)B * n_in * 4, cudaMemcpyDeviceToHost));
+	CUDA_CHECK_THROW(cudaMemcpy(h_tg, targets[0].data(), (size_t)B * n_out * 4, cudaMemcpyDeviceToHost));
+
+	uint32_t it = 0;
+	auto train = [&]() { model.trainer->training_step(stream, inputs[it % n_batches], targets[it % n_batches]); ++it; };
+	auto train_e2e = [&]() {
+		CUDA_CHECK_THROW(cudaMemcpyAsync(inputs[0].data(), h_in, (size_t)B * n_in * 4, cudaMemcpyHostToDevice, stream));
+		CUDA_CHECK_THROW(cudaMemcpyAsync(targets[0].data(), h_tg, (size_t)B * n_out * 4, cudaMemcpyHostToDevice, stream));
+		auto ctx = model.trainer->training_step(stream, inputs[0], targets[0]);
+		*h_loss = model.trainer->loss(stream, *ctx);
+	};
+	auto infer = [&]() { model.network->inference(stream, inputs[it % n_batches], prediction); ++it; };
+	for (uint32_t i = 0; i < warmup; ++i) train();
+	const float train_ms = time_loop(stream, steps, train);
+	for (uint32_t i = 0; i < warmup; ++i) train_e2e();
+	const float train_e2e_ms = time_loop(stream, steps, train_e2e);
+	for (uint32_t i = 0; i < warmup; ++i) infer();
+	const float infer_ms = time_loop(stream, steps, infer);
+	std::cout << json{{"impl", "reference-cuda-sm100"}, {"B", B}, {"steps", steps}, {"warmup", warmup},
+		{"train_ms_per_step", train_ms}, {"train_samples_per_s", (double)B / (train_ms * 1e-3)},
+		{"train_e2e_ms_per_step", train_e2e_ms}, {"train_e2e_samples_per_s", (double)B / (train_e2e_ms * 1e-3)},
+		{"inference_ms_per_step", infer_ms}, {"inference_samples_per_s", (double)B / (infer_ms * 1e-3)},
+		{"last_loss", *h_loss}, {"n_params", model.trainer->n_params()}}.dump() << std::endl;
+	return 0;
+}
+
+int main(int argc, char** argv) {
+	try {
+		if (argc < 2) { std::cerr << "usage: ref_driver dump|curve|bench ...\n"; return 2; }
+		const std::string mode = argv[1];
+		if (mode == "dump") return mode_dump(argc, argv);
+		if (mode == "curve") return mode_curve(argc, argv);
+		if (mode == "bench") return mode_bench(argc, argv);
+		std::cerr << "unknown mode " << mode << "\n";
+		return 2;
+	} catch (const std::exception& e) {
+		std::cerr << "ref_driver: exception: " << e.what() << std::endl;
+		return 1;
+	}
+}
