@@ -1,0 +1,460 @@
+"""CPU oracle for the HashGrid -> FullyFusedMLP -> L2 -> Adam hot path.  TEST INFRASTRUCTURE ONLY.
+
+This file is a numpy restatement of the reference's algorithm (leejaeyong7/tiny-cuda-nn, a fork of
+NVlabs/tiny-cuda-nn v1.7).  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+--impl reference legs may import it, and only as the checker.  The product (tiny-cuda-nn_b200/) never
+imports it and has no CPU fallback.
+
+Parity pinning: the reference ships NO golden vectors / known-answer tests for this path,
+and it has no CPU path, so it cannot run in the authoring container.  The oracle is pinned against dumps
+of the reference's own CUDA build (oracle/_ref/ref_driver, built by oracle/build_ref.sh from the
+unmodified sources) taken on a B200 and committed under tests/golden/ (see tests/golden/README.md and
+tests/golden/make_golden.sh).  Until those fixtures exist the status is "parity unpinned".
+
+Every function cites the reference file:line (relative to /root/reference) it restates.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass, field
+
+import numpy as np
+
+U32 = np.uint32
+F32 = np.float32
+F16 = np.float16
+
+# include/tiny-cuda-nn/common_device.h:650-654 (coherent_prime_hash factors)
+COHERENT_PRIMES = np.array([1, 2654435761, 805459861, 3674653429, 2097192037, 1434869437, 2165219737], dtype=np.uint64)
+
+BATCH_SIZE_GRANULARITY = 256  # include/tiny-cuda-nn/common.h:235
+LOSS_SCALE = 128.0            # include/tiny-cuda-nn/common.h:229-233 (default_loss_scale<__half>)
+
+
+def next_multiple(v: int, m: int) -> int:
+    return (v + m - 1) // m * m
+
+
+# --------------------------------------------------------------------------------------------------
+# pcg32 (dependencies/pcg32/pcg32.h:42-110,145-170: O'Neill's PCG-XSH-RR 64/32)
+# --------------------------------------------------------------------------------------------------
+PCG32_MULT = 0x5851F42D4C957F2D
+M64 = (1 << 64) - 1
+
+
+class Pcg32:
+    def __init__(self, initstate: int = 0x853C49E6748FEA9B, initseq: int | None = None):
+        if initseq is None and initstate == 0x853C49E6748FEA9B:
+            # default ctor: fixed state/stream (pcg32.h:43)
+            self.state = 0x853C49E6748FEA9B
+            self.inc = 0xDA3E39CB94B95BDB
+            return
+        self.seed(initstate, 1 if initseq is None else initseq)
+
+    def seed(self, initstate: int, initseq: int = 1):
+        # pcg32.h:54-60
+        self.state = 0
+        self.inc = ((initseq << 1) | 1) & M64
+        self.next_uint()
+        self.state = (self.state + initstate) & M64
+        self.next_uint()
+
+    def next_uint(self) -> int:
+        # pcg32.h:63-69
+        old = self.state
+        self.state = (old * PCG32_MULT + self.inc) & M64
+        xorshifted = (((old >> 18) ^ old) >> 27) & 0xFFFFFFFF
+        rot = old >> 59
+        return ((xorshifted >> rot) | (xorshifted << ((-rot) & 31))) & 0xFFFFFFFF
+
+    def advance(self, delta: int):
+        # pcg32.h:145-168 (Brown's arbitrary-stride jump)
+        cur_mult, cur_plus, acc_mult, acc_plus = PCG32_MULT, self.inc, 1, 0
+        delta &= M64
+        while delta > 0:
+            if delta & 1:
+                acc_mult = (acc_mult * cur_mult) & M64
+                acc_plus = (acc_plus * cur_mult + cur_plus) & M64
+            cur_plus = ((cur_mult + 1) * cur_plus) & M64
+            cur_mult = (cur_mult * cur_mult) & M64
+            delta >>= 1
+        self.state = (acc_mult * self.state + acc_plus) & M64
+
+    def copy(self) -> "Pcg32":
+        r = Pcg32.__new__(Pcg32)
+        r.state, r.inc = self.state, self.inc
+        return r
+
+
+def _pcg_output(old: np.ndarray) -> np.ndarray:
+    xorshifted = (((old >> np.uint64(18)) ^ old) >> np.uint64(27)).astype(np.uint32)
+    rot = (old >> np.uint64(59)).astype(np.uint32)
+    return (xorshifted >> rot) | (xorshifted << ((~rot + U32(1)) & U32(31)))
+
+
+def _uint_to_float01(u: np.ndarray) -> np.ndarray:
+    # pcg32.h:101-110 next_float: [1,2) mantissa trick
+    return ((u >> U32(9)) | U32(0x3F800000)).view(np.float32) - F32(1.0)
+
+
+def pcg32_stream(rng: Pcg32, n: int) -> np.ndarray:
+    """n consecutive next_uint() outputs, vectorised (LCG states via repeated doubling); advances rng."""
+    if n == 0:
+        return np.zeros(0, np.uint32)
+    with np.errstate(over="ignore"):
+        states = np.empty(n, dtype=np.uint64)
+        states[0] = np.uint64(rng.state)
+        mult, plus, filled = np.uint64(PCG32_MULT), np.uint64(rng.inc), 1
+        while filled < n:
+            m = min(filled, n - filled)
+            states[filled:filled + m] = states[:m] * mult + plus
+            plus = (mult + np.uint64(1)) * plus
+            mult = mult * mult
+            filled += m
+        out = _pcg_output(states)
+    rng.advance(n)
+    return out
+
+
+def seed_seq_first(seed: int) -> int:
+    """First 32-bit word of std::seed_seq{seed}.generate(2 words) (trainer.h:52-55; ISO C++ [rand.util.seedseq])."""
+    n, s = 2, 1
+    v = [seed & 0xFFFFFFFF]
+    b = [0x8B8B8B8B] * n
+    t = 0  # n < 7
+    p = (n - t) // 2
+    q = p + t
+    m = max(s + 1, n)
+    M32 = 0xFFFFFFFF
+
+    def T(x):
+        return x ^ (x >> 27)
+
+    for k in range(m):
+        r1 = (1664525 * T(b[k % n] ^ b[(k + p) % n] ^ b[(k - 1) % n])) & M32
+        if k == 0:
+            r2 = r1 + s
+        elif k <= s:
+            r2 = r1 + (k % n) + v[k - 1]
+        else:
+            r2 = r1 + (k % n)
+        r2 &= M32
+        b[(k + p) % n] = (b[(k + p) % n] + r1) & M32
+        b[(k + q) % n] = (b[(k + q) % n] + r2) & M32
+        b[k % n] = r2
+    for k in range(m, m + n):
+        r3 = (1566083941 * T((b[k % n] + b[(k + p) % n] + b[(k - 1) % n]) & M32)) & M32
+        r4 = (r3 - (k % n)) & M32
+        b[(k + p) % n] ^= r3
+        b[(k + q) % n] ^= r4
+        b[k % n] = r4
+    return b[0]
+
+
+# --------------------------------------------------------------------------------------------------
+# Grid encoding
+# --------------------------------------------------------------------------------------------------
+def grid_scale(level: int, log2_per_level_scale: float, base_resolution: int) -> np.float32:
+    # common_device.h:709-714  exp2f(level * log2_per_level_scale) * base_resolution - 1.0f   (all fp32)
+    e = F32(F32(level) * F32(log2_per_level_scale))
+    return F32(F32(np.exp2(e, dtype=np.float32) * F32(base_resolution)) - F32(1.0))
+
+
+def grid_resolution(scale: np.float32) -> int:
+    # common_device.h:716-718
+    return int(np.ceil(F32(scale))) + 1
+
+
+@dataclass
+class GridConfig:
+    """encodings/grid.h:1143-1208 JSON keys and defaults (HashGrid, CoherentPrime hash, Linear interpolation)."""
+    n_dims: int
+    n_levels: int = 16
+    n_features_per_level: int = 2
+    log2_hashmap_size: int = 19
+    base_resolution: int = 16
+    per_level_scale: float = 2.0
+    # optional per-level (scale, resolution) table dumped from the device (CUDA exp2f vs libm)
+    scales: np.ndarray | None = None
+    offsets: np.ndarray = field(init=False)
+    resolutions: np.ndarray = field(init=False)
+
+    def __post_init__(self):
+        # grid.h:692-716 offset table (host-side, std::log2(float) then the host grid_scale)
+        log2s = F32(np.log2(F32(self.per_level_scale)))
+        self.log2_per_level_scale = log2s
+        if self.scales is None:
+            self.scales = np.array([grid_scale(l, log2s, self.base_resolution) for l in range(self.n_levels)], dtype=np.float32)
+        self.resolutions = np.array([grid_resolution(s) for s in self.scales], dtype=np.uint32)
+        offs, off = [], 0
+        max_params = 0xFFFFFFFF // 2
+        for l in range(self.n_levels):
+            res = int(self.resolutions[l])
+            dense = max_params if float(F32(res) ** F32(self.n_dims)) > float(F32(max_params)) else (res ** self.n_dims) & 0xFFFFFFFF
+            n = next_multiple(dense, 8)
+            n = min(n, 1 << self.log2_hashmap_size)
+            offs.append(off)
+            off += n
+        offs.append(off)
+        self.offsets = np.array(offs, dtype=np.uint32)
+
+    @property
+    def n_features(self) -> int:
+        return self.n_levels * self.n_features_per_level
+
+    @property
+    def n_params(self) -> int:
+        return int(self.offsets[-1]) * self.n_features_per_level
+
+    def level_size(self, l: int) -> int:
+        return int(self.offsets[l + 1]) - int(self.offsets[l])
+
+
+def pos_fract(x: np.ndarray, scale: np.float32):
+    """common_device.h:857-868: pos = fmaf(scale, x, 0.5f); cell = (uint32)(int)floorf(pos); frac = pos - floorf(pos)."""
+    # fmaf = single rounding of the exact scale*x+0.5; float64 holds the exact product of two fp32 and the sum's
+    # rounding to fp32 from float64 is a double rounding only in measure-zero ties we accept here.
+    p = (np.float64(scale) * x.astype(np.float64) + 0.5).astype(np.float32)
+    fl = np.floor(p)
+    cell = (fl.astype(np.int64) & 0xFFFFFFFF).astype(np.uint32)  # (uint32_t)(int)floorf: two's complement wrap
+    frac = (p - fl).astype(np.float32)
+    return frac, cell
+
+
+def grid_index(pos_grid: np.ndarray, hashmap_size: int, resolution: int) -> np.ndarray:
+    """common_device.h:690-707 for GridType::Hash + CoherentPrime, including the uint32 stride wrap.
+
+    pos_grid: uint32 [..., D] -> uint32 [...]."""
+    D = pos_grid.shape[-1]
+    stride = 1
+    index = np.zeros(pos_grid.shape[:-1], dtype=np.uint64)
+    for d in range(D):
+        if not (stride <= hashmap_size):
+            break
+        index = (index + pos_grid[..., d].astype(np.uint64) * np.uint64(stride)) & np.uint64(0xFFFFFFFF)
+        stride = (stride * resolution) & 0xFFFFFFFF
+    if hashmap_size < stride:
+        h = np.zeros(pos_grid.shape[:-1], dtype=np.uint64)
+        for d in range(D):
+            h ^= (pos_grid[..., d].astype(np.uint64) * COHERENT_PRIMES[d]) & np.uint64(0xFFFFFFFF)
+        index = h
+    return (index % np.uint64(hashmap_size)).astype(np.uint32)
+
+
+def grid_corners(cfg: GridConfig, x: np.ndarray, level: int):
+    """Per-level corner indices (entry units, relative to the level) and fp32 weights.
+
+    grid.h:94-163: corner idx bit d selects +1 in dim d; weight = prod(dim) of (1-frac) or frac, in fp32,
+    multiplied in dim order starting from 1.0f.   x: fp32 [B, D] -> (uint32 [B, 2^D], fp32 [B, 2^D])."""
+    D = cfg.n_dims
+    frac, cell = pos_fract(x, cfg.scales[level])
+    B = x.shape[0]
+    idx = np.empty((B, 1 << D), dtype=np.uint32)
+    w = np.empty((B, 1 << D), dtype=np.float32)
+    hs, res = cfg.level_size(level), int(cfg.resolutions[level])
+    for c in range(1 << D):
+        weight = np.ones(B, dtype=np.float32)
+        pg = np.empty((B, D), dtype=np.uint32)
+        for d in range(D):
+            if (c >> d) & 1:
+                weight = (weight * frac[:, d]).astype(np.float32)
+                pg[:, d] = cell[:, d] + U32(1)
+            else:
+                weight = (weight * (F32(1) - frac[:, d])).astype(np.float32)
+                pg[:, d] = cell[:, d]
+        idx[:, c] = grid_index(pg, hs, res)
+        w[:, c] = weight
+    return idx, w
+
+
+def grid_forward(cfg: GridConfig, x: np.ndarray, table: np.ndarray) -> np.ndarray:
+    """kernel_grid, grid.h:48-169.  table: fp16 [n_params]; returns fp16 [B, L*F] (sample-major).
+
+    Interpolation in fp16: result = __hfma2((half)weight, value, result) per corner (grid.h:146-163, vec.h:370-375):
+    one rounding per fma, emulated as float64 fma -> fp16."""
+    B, F = x.shape[0], cfg.n_features_per_level
+    out = np.zeros((B, cfg.n_features), dtype=np.float16)
+    t = table.astype(np.float16).reshape(-1, F)
+    for l in range(cfg.n_levels):
+        idx, w = grid_corners(cfg, x, l)
+        base = int(cfg.offsets[l])
+        res = np.zeros((B, F), dtype=np.float16)
+        for c in range(idx.shape[1]):
+            val = t[base + idx[:, c].astype(np.int64)]
+            wh = w[:, c].astype(np.float16)
+            res = (wh.astype(np.float64)[:, None] * val.astype(np.float64) + res.astype(np.float64)).astype(np.float16)
+        out[:, l * F:(l + 1) * F] = res
+    return out
+
+
+def grid_backward(cfg: GridConfig, x: np.ndarray, dy: np.ndarray) -> np.ndarray:
+    """kernel_grid_backward, grid.h:214-320.  dy: fp16 [B, L*F] -> float64 [n_params] (exact sum of the fp16
+    products (half)weight * grad; the reference accumulates them with fp16 red atomics in arbitrary order, so
+    comparisons are tolerance-based)."""
+    F = cfg.n_features_per_level
+    g = np.zeros((int(cfg.offsets[-1]), F), dtype=np.float64)
+    for l in range(cfg.n_levels):
+        idx, w = grid_corners(cfg, x, l)
+        base = int(cfg.offsets[l])
+        gl = dy[:, l * F:(l + 1) * F].astype(np.float16)
+        for c in range(idx.shape[1]):
+            wh = w[:, c].astype(np.float16)
+            prod = (wh.astype(np.float32)[:, None] * gl.astype(np.float32)).astype(np.float16)  # __hmul2, one rounding
+            np.add.at(g, base + idx[:, c].astype(np.int64), prod.astype(np.float64))
+    return g.reshape(-1)
+
+
+# --------------------------------------------------------------------------------------------------
+# FullyFusedMLP (src/fully_fused_mlp.cu:635-678 weight layout, :499-557 forward, :150-259/:735-836 backward)
+# --------------------------------------------------------------------------------------------------
+@dataclass
+class MlpConfig:
+    """src/network.cu:107-113 defaults; weights are row-major [out, in], concatenated:
+    [W x in_pad], (H-1) x [W x W], [out_pad16 x W]  (fully_fused_mlp.cu:654-671)."""
+    n_input: int            # padded encoding width (multiple of 16)
+    n_output: int
+    n_neurons: int = 64
+    n_hidden_layers: int = 2
+    activation: str = "ReLU"
+    output_activation: str = "None"
+
+    @property
+    def padded_output(self) -> int:
+        return next_multiple(self.n_output, 16)
+
+    def shapes(self):
+        W = self.n_neurons
+        return [(W, self.n_input)] + [(W, W)] * (self.n_hidden_layers - 1) + [(self.padded_output, W)]
+
+    @property
+    def n_params(self) -> int:
+        return sum(a * b for a, b in self.shapes())
+
+    def split(self, params: np.ndarray):
+        out, pos = [], 0
+        for a, b in self.shapes():
+            out.append(params[pos:pos + a * b].reshape(a, b))
+            pos += a * b
+        return out
+
+
+def mlp_forward(cfg: MlpConfig, params: np.ndarray, x: np.ndarray, acc=np.float32):
+    """x: fp16 [B, n_input] -> (output fp16 [B, out_pad], list of post-activation hidden fp16 [B, W]).
+
+    Storage fp16 after every layer like the reference (fully_fused_mlp.cu:47-129); `acc` is the accumulator type:
+    the reference accumulates in fp16 wmma fragments, the B200 kernels in fp32 TMEM (BASELINE tolerance 1e-2)."""
+    assert cfg.activation == "ReLU" and cfg.output_activation == "None"
+    ws = cfg.split(params.astype(np.float16))
+    h = x.astype(np.float16)
+    hidden = []
+    for w in ws[:-1]:
+        z = h.astype(acc) @ w.astype(acc).T
+        h = np.maximum(z, 0).astype(np.float16)
+        hidden.append(h)
+    y = (h.astype(acc) @ ws[-1].astype(acc).T).astype(np.float16)
+    return y, hidden
+
+
+def mlp_backward(cfg: MlpConfig, params: np.ndarray, x: np.ndarray, hidden, dy: np.ndarray, acc=np.float32):
+    """dy: fp16 [B, out_pad] (loss-scaled) -> (dparams float64 [n_params] exact-ish, dx fp16 [B, n_input]).
+
+    Chain (fully_fused_mlp.cu:150-259): g = (W_next^T dy) * relu'(h) with the mask taken from the stored
+    post-activation (common_device.h:243-248), rounded to fp16 at every layer; weight gradients dW = g^T h_prev
+    over the batch (fully_fused_mlp.cu:783-829)."""
+    ws = cfg.split(params.astype(np.float16))
+    grads = [None] * len(ws)
+    g = dy.astype(np.float16)
+    for k in range(len(ws) - 1, -1, -1):
+        inp = hidden[k - 1] if k > 0 else x.astype(np.float16)
+        grads[k] = g.astype(np.float64).T @ inp.astype(np.float64)
+        z = g.astype(acc) @ ws[k].astype(acc)
+        if k > 0:
+            z = z * (hidden[k - 1] > 0)
+        g = z.astype(np.float16)
+    return np.concatenate([gr.reshape(-1) for gr in grads]), g
+
+
+# --------------------------------------------------------------------------------------------------
+# Losses (losses/l2.h:40-75, losses/relative_l2.h:40-75)
+# --------------------------------------------------------------------------------------------------
+def loss_l2(pred: np.ndarray, target: np.ndarray, n_out: int, loss_scale: float = LOSS_SCALE, relative: bool = False):
+    """pred fp16 [B, out_pad], target fp32 [B, n_out] -> (mean loss float, dL/dpred fp16 [B, out_pad])."""
+    B, stride = pred.shape
+    n_total = F32(B * n_out)
+    p = pred[:, :n_out].astype(np.float32)
+    diff = (p - target.astype(np.float32)).astype(np.float32)
+    denom = (p * p + F32(0.01)).astype(np.float32) if relative else np.ones_like(p)
+    values = (diff * diff / denom / n_total).astype(np.float32)
+    grad = (F32(2) * diff / denom).astype(np.float32)
+    g = np.zeros((B, stride), dtype=np.float16)
+    g[:, :n_out] = (F32(loss_scale) * grad / n_total).astype(np.float16)
+    return float(values.astype(np.float64).sum()), g
+
+
+# --------------------------------------------------------------------------------------------------
+# Adam (optimizers/adam.h:47-119; hyper-parameter defaults :312-326)
+# --------------------------------------------------------------------------------------------------
+@dataclass
+class AdamConfig:
+    learning_rate: float = 1e-3
+    beta1: float = 0.9
+    beta2: float = 0.999
+    epsilon: float = 1e-8
+    l2_reg: float = 1e-8
+    relative_decay: float = 0.0
+    absolute_decay: float = 0.0
+    adabound: bool = False
+
+
+def adam_step(cfg: AdamConfig, n_matrix: int, master: np.ndarray, grads_h: np.ndarray, m: np.ndarray, v: np.ndarray,
+              steps: np.ndarray, loss_scale: float = LOSS_SCALE):
+    """In-place Adam on fp32 master weights; returns the fp16 copy.  Non-matrix (grid) params with gradient == 0 are
+    skipped entirely and every parameter keeps its own step counter (adam.h:75-91,103-105)."""
+    n = master.shape[0]
+    grad = (grads_h.astype(np.float32) / F32(loss_scale)).astype(np.float32)
+    is_mat = np.arange(n) < n_matrix
+    active = is_mat | (grad != 0)
+    grad = np.where(is_mat, (grad + F32(cfg.l2_reg) * master).astype(np.float32), grad)
+    b1, b2 = F32(cfg.beta1), F32(cfg.beta2)
+    m_new = (b1 * m + (F32(1) - b1) * grad).astype(np.float32)
+    v_new = (b2 * v + (F32(1) - b2) * (grad * grad).astype(np.float32)).astype(np.float32)
+    t = (steps + active.astype(np.uint32)).astype(np.uint32)
+    tf = np.maximum(t, 1).astype(np.float32)
+    lr = (F32(cfg.learning_rate) * np.sqrt(F32(1) - np.power(b2, tf, dtype=np.float32)) / (F32(1) - np.power(b1, tf, dtype=np.float32))).astype(np.float32)
+    lo, hi = (F32(0.0), F32(np.finfo(np.float32).max))
+    eff = np.minimum(np.maximum(lr / (np.sqrt(v_new) + F32(cfg.epsilon)), lo), hi).astype(np.float32)
+    decayed = master  # weight_decay with zero relative/absolute decay is the identity (common_device.h:870-873)
+    new_w = (decayed - eff * m_new).astype(np.float32)
+    master[:] = np.where(active, new_w, master)
+    m[:] = np.where(active, m_new, m)
+    v[:] = np.where(active, v_new, v)
+    steps[:] = t
+    return master.astype(np.float16)
+
+
+# --------------------------------------------------------------------------------------------------
+# Parameter initialisation (trainer.h:50-87; network_with_input_encoding.h:124-130; fully_fused_mlp.cu:866-891;
+# gpu_matrix.h:284-299 xavier on the host; grid.h:1059-1062 + random.h:39-71 uniform(-1e-4,1e-4) on the device)
+# --------------------------------------------------------------------------------------------------
+def init_params(mlp: MlpConfig, grid: GridConfig | None, seed: int = 1337, trainer_seeding: bool = True) -> np.ndarray:
+    """fp32 [P_mlp + P_grid], MLP first.  trainer_seeding=True reproduces Trainer (seed_seq -> pcg32);
+    False reproduces cpp::Module::initialize_params (pcg32{seed} directly, src/cpp_api.cu:124-127)."""
+    rng = Pcg32(seed_seq_first(seed)) if trainer_seeding else Pcg32(seed)
+    parts = []
+    for (rows, cols) in mlp.shapes():
+        scale = F32(np.sqrt(F32(6.0) / F32(cols + rows)))
+        u = _uint_to_float01(pcg32_stream(rng, rows * cols))
+        parts.append((u * F32(2.0) * scale - scale).astype(np.float32))
+    if grid is not None:
+        n = grid.n_params
+        # generate_random_kernel: thread i advances by 4i and writes element i + n_threads*j with its j-th draw,
+        # n_threads = 128 * ceil(ceil(n/4)/128)   (random.h:39-63, common_host.h n_blocks_linear / N_THREADS_LINEAR=128)
+        n_threads = next_multiple((n + 3) // 4, 128)
+        draws = _uint_to_float01(pcg32_stream(rng.copy(), 4 * n_threads)).reshape(n_threads, 4)
+        flat = draws.T.reshape(-1)[:n]  # element idx = i + n_threads*j  <- draws[i, j]
+        rng.advance(n)
+        lo, hi = F32(-1e-4), F32(1e-4)
+        # the device lambda `val * (upper - lower) + lower` is contracted to one fmaf by nvcc (default -fmad=true)
+        rangef = F32(hi - lo)
+        parts.append((flat.astype(np.float64) * np.float64(rangef) + np.float64(lo)).astype(np.float32))
+    return np.concatenate(parts)
