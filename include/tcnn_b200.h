@@ -1,0 +1,124 @@
+/* tcnn_b200.h — C ABI of libtcnn_b200.so: the B200-native (sm_100a) HashGrid -> FullyFusedMLP hot path.
+ *
+ * This is the drop-in boundary.  Every entry point replaces a specific piece of the reference
+ * (leejaeyong7/tiny-cuda-nn; paths relative to the reference root) and is what the reference-side bindings
+ * (C++ facade include/tiny-cuda-nn/*.h in this repo, bindings/torch via ctypes) call.
+ *
+ * Conventions:
+ *   - plain C types only: opaque plan handle, caller-owned DEVICE pointers, explicit sizes, a cudaStream_t passed as void*;
+ *   - every function returns 0 on success, non-zero on error; tcnn_b200_last_error() returns the thread-local message
+ *     (the C++/Python facades turn it into std::runtime_error / RuntimeError like common_host.h:71-110);
+ *   - nothing synchronises the stream, nothing allocates device memory behind the caller's back (the caller passes a
+ *     workspace of tcnn_b200_workspace_bytes()); one plan is used from one host thread at a time;
+ *   - batch sizes must be multiples of 256 (BATCH_SIZE_GRANULARITY, include/tiny-cuda-nn/common.h:235; object.h:130);
+ *   - layouts: input x is [B][n_input_dims] fp32 (== GPUMatrix<float, CM> [D x B]); network output is [B][16] fp16
+ *     (== CM [16 x B], src/cpp_api.cu:76); params are fp16 [n_params] = [MLP weights | grid tables]
+ *     (network_with_input_encoding.h:115-130); param gradients fp16, same layout, loss-scaled.
+ *   - there is NO CPU fallback: every compute entry point fails if no sm_100 device is present.
+ */
+#ifndef TCNN_B200_H
+#define TCNN_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct tcnn_b200_plan tcnn_b200_plan;
+
+/* Hyper-parameters resolved from the JSON config (defaults as in the reference: encodings/grid.h:1145-1200,
+ * src/network.cu:107-113, optimizers/adam.h:312-326, src/loss.cu:86). */
+typedef struct tcnn_b200_info {
+	uint32_t n_input_dims;        /* D */
+	uint32_t n_output_dims;       /* O (unpadded) */
+	uint32_t padded_output_width; /* 16 */
+	uint32_t n_levels, n_features_per_level, log2_hashmap_size, base_resolution;
+	float per_level_scale;
+	uint32_t encoded_width;       /* L*F padded to a multiple of 16 = MLP input width */
+	uint32_t n_neurons, n_hidden_layers;
+	uint64_t n_params;            /* P = n_params_mlp + n_params_grid */
+	uint64_t n_params_mlp;        /* "matrix" weights (come first) */
+	uint64_t n_params_grid;
+	int loss_type;                /* 0 = L2, 1 = RelativeL2 */
+	float learning_rate, beta1, beta2, epsilon, l2_reg, relative_decay, absolute_decay;
+	uint32_t level_offset[33];    /* entry offsets per level (GridOffsetTable, grid_interface.h:84-88) */
+	float level_scale[32];        /* grid_scale per level, evaluated with CUDA exp2f when a device is present */
+	uint32_t level_resolution[32];
+} tcnn_b200_info;
+
+/* Error text of the last failing call on this thread. */
+const char* tcnn_b200_last_error(void);
+/* Library/ABI version, and the SM architecture the kernels were compiled for ("sm_100a"). */
+uint32_t tcnn_b200_abi_version(void);
+const char* tcnn_b200_arch(void);
+/* batch_size_granularity() of cpp_api.h (256). */
+uint32_t tcnn_b200_batch_size_granularity(void);
+
+/* create_from_config / create_network_with_input_encoding (config.h:53-63, src/cpp_api.cu:147-149).
+ * json_utf8 = {"encoding": {...}, "network": {...}, "loss": {...}?, "optimizer": {...}?}. */
+int tcnn_b200_plan_create(const char* json_utf8, uint32_t n_input_dims, uint32_t n_output_dims, tcnn_b200_plan** plan);
+void tcnn_b200_plan_destroy(tcnn_b200_plan* plan);
+int tcnn_b200_plan_info(const tcnn_b200_plan* plan, tcnn_b200_info* info);
+/* Trainer::update_hyperparams (trainer.h:213-216): JSON object with optimizer keys (learning_rate, beta1, ...). */
+int tcnn_b200_plan_update_optimizer(tcnn_b200_plan* plan, const char* json_utf8);
+
+/* Scratch device memory one call on a batch of B needs (any entry point below; max over them). */
+size_t tcnn_b200_workspace_bytes(const tcnn_b200_plan* plan, uint32_t batch_size);
+
+/* Trainer::initialize_params (trainer.h:68-87) when trainer_seeding != 0 (std::seed_seq{seed} -> pcg32), or
+ * cpp::Module::initialize_params (src/cpp_api.cu:124-127) when 0 (pcg32{seed}).  Writes fp32 [n_params]. */
+int tcnn_b200_init_params(const tcnn_b200_plan* plan, void* stream, uint64_t seed, int trainer_seeding, float* params_fp32);
+/* fp32 -> fp16 copy of the parameters (trainer.h:83-85). */
+int tcnn_b200_cast_params(void* stream, uint64_t n, const float* params_fp32, void* params_fp16);
+
+/* GridEncoding forward, kernel_grid (encodings/grid.h:48-212, 732-807).  encoded: fp16 [B][encoded_width]. */
+int tcnn_b200_encode_forward(const tcnn_b200_plan* plan, void* stream, uint32_t batch_size, const float* x, const void* grid_params_fp16, void* encoded_fp16);
+/* kernel_grid_backward (grid.h:214-320, 809-900).  Adds into grid_grads_fp16 [n_params_grid]; zero_first != 0
+ * clears it first (the reference's cudaMemsetAsync, grid.h:857-859). */
+int tcnn_b200_encode_backward(const tcnn_b200_plan* plan, void* stream, uint32_t batch_size, const float* x, const void* dL_dencoded_fp16, void* grid_grads_fp16, int zero_first);
+/* Parity probe: entry index of every interpolation corner, uint32 [n_levels][B][2^D], computed by the same device
+ * functions as the two kernels above (grid_index, common_device.h:690-707). */
+int tcnn_b200_grid_indices(const tcnn_b200_plan* plan, void* stream, uint32_t batch_size, const float* x, uint32_t* indices);
+
+/* FullyFusedMLP::inference_mixed_precision_impl (src/fully_fused_mlp.cu:680-705).  in: fp16 [B][encoded_width];
+ * out: fp16 [B][16]. */
+int tcnn_b200_mlp_forward(const tcnn_b200_plan* plan, void* stream, uint32_t batch_size, const void* input_fp16, const void* mlp_params_fp16, void* output_fp16);
+/* FullyFusedMLP::backward_impl (src/fully_fused_mlp.cu:735-836).  The forward activations are recomputed on chip from
+ * `input` instead of being re-read from HBM.  dL_dparams (fp16 [n_params_mlp], overwritten) and dL_dinput
+ * (fp16 [B][encoded_width]) may each be NULL. */
+int tcnn_b200_mlp_backward(const tcnn_b200_plan* plan, void* stream, uint32_t batch_size, const void* input_fp16, const void* mlp_params_fp16,
+                           const void* dL_doutput_fp16, void* dL_dparams_fp16, void* dL_dinput_fp16, void* workspace);
+
+/* cpp::Module::inference (src/cpp_api.cu:72-82) / Network::inference (object.h:147-176): encoding + MLP.
+ * output_fp16 [B][16] and/or output_fp32 [B][n_output_dims] (either may be NULL). */
+int tcnn_b200_inference(const tcnn_b200_plan* plan, void* stream, uint32_t batch_size, const float* x, const void* params_fp16,
+                        void* output_fp16, float* output_fp32, void* workspace);
+/* cpp::Module::forward (src/cpp_api.cu:84-94): like inference, and leaves what backward needs in the workspace
+ * (the encoded batch), which therefore plays the role of the reference's Context. */
+int tcnn_b200_forward(const tcnn_b200_plan* plan, void* stream, uint32_t batch_size, const float* x, const void* params_fp16, void* output_fp16, void* workspace);
+/* cpp::Module::backward (src/cpp_api.cu:96-109), GradientMode::Overwrite.  dL_dparams fp16 [n_params] may be NULL.
+ * dL_dinput (fp32 [B][D]) is not implemented in this round: passing non-NULL is an error. */
+int tcnn_b200_backward(const tcnn_b200_plan* plan, void* stream, uint32_t batch_size, const float* x, const void* params_fp16,
+                       const void* dL_doutput_fp16, void* dL_dparams_fp16, float* dL_dinput, void* workspace);
+
+/* Trainer::training_step minus the optimizer (trainer.h:163-184): forward, loss (losses/l2.h, relative_l2.h),
+ * backward.  target fp32 [B][n_output_dims]; grads fp16 [n_params]: the MLP part is overwritten, the grid part is
+ * accumulated into (zero_grid_grads != 0 clears it first; tcnn_b200_adam_step re-zeroes it for the next step).
+ * loss_out: device float receiving the mean loss (Trainer::loss, trainer.h:205-207) or NULL;
+ * output_fp16: [B][16] or NULL. */
+int tcnn_b200_training_fwd_bwd(const tcnn_b200_plan* plan, void* stream, uint32_t batch_size, const float* x, const float* target,
+                               const void* params_fp16, void* grads_fp16, float loss_scale, int zero_grid_grads,
+                               float* loss_out, void* output_fp16, void* workspace);
+
+/* AdamOptimizer::step (optimizers/adam.h:150-188) over [MLP | grid] parameters.  grad_divisor = loss_scale *
+ * world_size.  adam_step_count is the optimizer's global step after this update (only used by adabound). */
+int tcnn_b200_adam_step(const tcnn_b200_plan* plan, void* stream, float grad_divisor, uint32_t adam_step_count,
+                        float* params_fp32, void* params_fp16, void* grads_fp16, float* first_moments, float* second_moments,
+                        uint32_t* param_steps, int zero_grid_grads);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TCNN_B200_H */

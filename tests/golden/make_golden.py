@@ -1,0 +1,77 @@
+"""Generate the golden fixtures from the REFERENCE's own CUDA build (oracle/_ref/ref_driver, built by
+oracle/build_ref.sh from the unmodified reference sources).  Runs on a GPU box only:
+
+    python tests/golden/make_golden.py gpurun_out/golden
+
+For each config it feeds the seeded synthetic batch of tests/common.synth_inputs to `ref_driver dump`, which runs the
+reference's create_from_config / inference / training_step / optimizer_step and its own __device__ grid_index, and packs
+the results into <name>.npz small enough to commit (large arrays are stored sparsely or as strided samples + sums).
+The committed copies live next to this script; tests/test_golden*.py read them."""
+import json
+import os
+import subprocess
+import sys
+import tempfile
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+from tests import common  # noqa: E402
+
+REF = os.path.join(ROOT, "oracle", "_ref", "ref_driver")
+CASES = [  # name, config, n_in, n_out, B
+    ("cfg1_2d_T19", common.CONFIG_1, 2, 3, 1024),
+    ("shipped_2d_T15", common.CONFIG_SHIPPED, 2, 3, 1024),
+    ("nerf_3d_T19", common.CONFIG_NERF, 3, 4, 1024),
+    ("f4_3d_T14", common.CONFIG_F4, 3, 3, 512),
+]
+SAMPLE_STRIDE = 997
+
+
+def main(outdir):
+    os.makedirs(outdir, exist_ok=True)
+    for name, cfg, n_in, n_out, B in CASES:
+        x, t = common.synth_inputs(B, n_in, n_out, seed=1)
+        with tempfile.TemporaryDirectory() as d:
+            x.tofile(os.path.join(d, "x.f32")); t.tofile(os.path.join(d, "t.f32"))
+            with open(os.path.join(d, "cfg.json"), "w") as f:
+                json.dump(cfg, f)
+            r = subprocess.run([REF, "dump", os.path.join(d, "cfg.json"), str(n_in), str(n_out), str(B), os.path.join(d, "x.f32"),
+                                os.path.join(d, "t.f32"), d], capture_output=True, text=True, timeout=600)
+            print(name, r.returncode, r.stdout.strip(), r.stderr.strip()[-400:], flush=True)
+            if r.returncode != 0:
+                continue
+            meta = json.load(open(os.path.join(d, "meta.json")))
+            rd = lambda fn, dt: np.fromfile(os.path.join(d, fn), dtype=dt)  # noqa: E731
+            P, E = meta["n_params"], meta["encoded_width"]
+            P_grid = meta["n_params_encoding"]; P_mlp = P - P_grid
+            params_init = rd("params_init.f32", np.float32)
+            grads = rd("grads.f16", np.float16)
+            after = rd("params_after.f32", np.float32)
+            gg = grads[P_mlp:]
+            nz = np.flatnonzero(gg.view(np.uint16) & 0x7FFF).astype(np.uint32)
+            sample = np.arange(0, P, SAMPLE_STRIDE, dtype=np.int64)
+            moved = np.flatnonzero(after != params_init).astype(np.uint32)
+            L = len(rd("level_res.u32", np.uint32))
+            np.savez_compressed(
+                os.path.join(outdir, name + ".npz"),
+                config=json.dumps(cfg), n_in=n_in, n_out=n_out, B=B, seed=1, loss=np.float32(meta["loss"]),
+                n_params=P, n_params_mlp=P_mlp,
+                level_scale=rd("level_scale.f32", np.float32), level_res=rd("level_res.u32", np.uint32), level_size=rd("level_size.u32", np.uint32),
+                indices=rd("indices.u32", np.uint32).reshape(L, B, 1 << n_in),
+                encoded_soa=rd("encoded_soa.f16", np.float16).reshape(E, B),
+                output=rd("output.f32", np.float32).reshape(B, n_out),
+                output_padded=rd("output_padded.f16", np.float16).reshape(B, meta["padded_output_width"]),
+                dL_doutput=rd("dL_doutput.f16", np.float16).reshape(B, meta["padded_output_width"]),
+                params_init_mlp=params_init[:P_mlp], params_init_sample=params_init[sample],
+                params_init_sum=np.float64(params_init.astype(np.float64).sum()), params_init_sumsq=np.float64((params_init.astype(np.float64) ** 2).sum()),
+                grads_mlp=grads[:P_mlp], grads_grid_nz_idx=nz, grads_grid_nz_val=gg[nz],
+                params_after_mlp=after[:P_mlp], params_after_moved_idx=moved[:: max(1, len(moved) // 20000)],
+                params_after_moved_val=after[moved[:: max(1, len(moved) // 20000)]], n_moved=len(moved),
+            )
+            print(name, "saved", os.path.getsize(os.path.join(outdir, name + ".npz")), "bytes", flush=True)
+
+
+if __name__ == "__main__":
+    main(sys.argv[1] if len(sys.argv) > 1 else os.path.join(ROOT, "gpurun_out", "golden"))

@@ -1,0 +1,243 @@
+// Multiresolution hash-grid encoding for sm_100a: forward gather, backward scatter, index dump.
+//
+// Behaviour follows the reference's kernel_grid / kernel_grid_backward (include/tiny-cuda-nn/encodings/grid.h:48-320)
+// and its index math (include/tiny-cuda-nn/common_device.h:631-718, 825-868); the kernels themselves are new:
+//   * one thread owns (sample, 16-byte chunk of the encoded row) = 8/F consecutive levels, so all 2^D * 8/F gathers of
+//     the chunk are in flight together and the result is one 16-byte store into the sample-major [B x E_pad] fp16 matrix
+//     that the MLP kernel consumes as its K-major A operand (the reference writes SoA and re-reads it with wmma loads);
+//   * per-level constants (scale, resolution, strides with the uint32 wrap of grid_index, hashed-or-not) are resolved
+//     once on the host and passed by value.
+#pragma once
+#include "ptx.cuh"
+
+namespace b200 {
+
+constexpr int MAX_LEVELS = 32;
+constexpr int MAX_DIMS = 4;
+
+struct GridLevel {
+	float scale;            // exp2f(level * log2(per_level_scale)) * base_resolution - 1   (device-evaluated, see grid_scale_kernel)
+	uint32_t resolution;    // (uint32_t)ceilf(scale) + 1
+	uint32_t size;          // entries in this level (hashmap_size of grid_index)
+	uint32_t offset;        // first entry of this level
+	uint32_t stride[MAX_DIMS]; // dense strides incl. uint32 wrap; 0 for dims the reference loop never reaches
+	uint32_t n_dense_dims;  // number of loop iterations of grid_index executed
+	uint32_t hashed;        // 1 if (Hash grid && size < final stride)
+};
+
+struct GridParams {
+	uint32_t n_levels;
+	uint32_t n_features;     // n_levels * F
+	uint32_t padded_width;   // encoded row width in halfs (multiple of 16)
+	GridLevel level[MAX_LEVELS];
+};
+
+// common_device.h:709-714, evaluated on the device with CUDA's exp2f exactly like the reference kernels do.
+__device__ __forceinline__ float grid_scale_dev(uint32_t level, float log2_per_level_scale, uint32_t base_resolution) {
+	return exp2f(level * log2_per_level_scale) * base_resolution - 1.0f;
+}
+__global__ void grid_scale_kernel(uint32_t n_levels, float log2_per_level_scale, uint32_t base_resolution, float* __restrict__ scales) {
+	const uint32_t l = threadIdx.x;
+	if (l < n_levels) scales[l] = grid_scale_dev(l, log2_per_level_scale, base_resolution);
+}
+
+// common_device.h:857-868 (identity interpolation function = Linear)
+__device__ __forceinline__ void pos_fract_dev(float x, float scale, float& frac, uint32_t& cell) {
+	const float p = fmaf(scale, x, 0.5f);
+	const float f = floorf(p);
+	cell = (uint32_t)(int)f;
+	frac = p - f;
+}
+
+// common_device.h:690-707 with the level-constant part hoisted (strides, hashed flag); primes :650-654.
+template <int D>
+__device__ __forceinline__ uint32_t grid_index_dev(const GridLevel& lv, const uint32_t (&pg)[D]) {
+	constexpr uint32_t primes[7] = {1u, 2654435761u, 805459861u, 3674653429u, 2097192037u, 1434869437u, 2165219737u};
+	uint32_t index;
+	if (lv.hashed) {
+		index = 0;
+#pragma unroll
+		for (int d = 0; d < D; ++d) index ^= pg[d] * primes[d];
+	} else {
+		index = 0;
+#pragma unroll
+		for (int d = 0; d < D; ++d) index += pg[d] * lv.stride[d]; // stride[d] == 0 for skipped dims
+	}
+	// size is a power of two for every hashed level (2^log2_hashmap_size); dense levels need the real modulo
+	return (lv.size & (lv.size - 1)) == 0 ? (index & (lv.size - 1)) : (index % lv.size);
+}
+
+template <int F> struct FeatVec;
+template <> struct FeatVec<1> { using type = __half; };
+template <> struct FeatVec<2> { using type = __half2; };
+template <> struct FeatVec<4> { using type = uint2; };
+template <> struct FeatVec<8> { using type = uint4; };
+
+template <int D>
+__device__ __forceinline__ void load_position(const float* __restrict__ x, size_t i, float (&p)[D]) {
+	if constexpr (D == 2) {
+		const float2 v = __ldg(reinterpret_cast<const float2*>(x) + i);
+		p[0] = v.x; p[1] = v.y;
+	} else if constexpr (D == 4) {
+		const float4 v = __ldg(reinterpret_cast<const float4*>(x) + i);
+		p[0] = v.x; p[1] = v.y; p[2] = v.z; p[3] = v.w;
+	} else {
+#pragma unroll
+		for (int d = 0; d < D; ++d) p[d] = __ldg(x + i * D + d);
+	}
+}
+
+// Encode the levels of one 16-byte chunk for one sample.  Returns 8 halfs packed in a uint4.
+template <int D, int F>
+__device__ __forceinline__ uint4 encode_chunk(const GridParams& gp, const __half* __restrict__ grid, const float (&x)[D], uint32_t chunk) {
+	constexpr int LEVELS_PER_CHUNK = 8 / F;
+	constexpr int NC = 1 << D;
+	union { uint4 v; __half2 h2[4]; } out;
+	out.v = make_uint4(0, 0, 0, 0);
+#pragma unroll
+	for (int s = 0; s < LEVELS_PER_CHUNK; ++s) {
+		const uint32_t level = chunk * LEVELS_PER_CHUNK + s;
+		if (level >= gp.n_levels) break; // padding columns stay zero (grid.h:749-759 pads with zeros too)
+		const GridLevel& lv = gp.level[level];
+		float frac[D]; uint32_t cell[D];
+#pragma unroll
+		for (int d = 0; d < D; ++d) pos_fract_dev(x[d], lv.scale, frac[d], cell[d]);
+		const __half* table = grid + (size_t)lv.offset * F;
+		// issue every gather of the level before the fp16 fma chain (grid.h:146-163 order: corner 0..2^D-1)
+		uint32_t idx[NC]; float w[NC];
+#pragma unroll
+		for (int c = 0; c < NC; ++c) {
+			float weight = 1.0f; uint32_t pg[D];
+#pragma unroll
+			for (int d = 0; d < D; ++d) {
+				if ((c & (1 << d)) == 0) { weight *= 1.0f - frac[d]; pg[d] = cell[d]; }
+				else { weight *= frac[d]; pg[d] = cell[d] + 1u; }
+			}
+			idx[c] = grid_index_dev<D>(lv, pg);
+			w[c] = weight;
+		}
+		if constexpr (F == 2) {
+			__half2 val[NC];
+#pragma unroll
+			for (int c = 0; c < NC; ++c) val[c] = __ldg(reinterpret_cast<const __half2*>(table) + idx[c]);
+			__half2 r = __floats2half2_rn(0.f, 0.f);
+#pragma unroll
+			for (int c = 0; c < NC; ++c) r = __hfma2(__half2half2(__float2half(w[c])), val[c], r);
+			out.h2[s] = r;
+		} else if constexpr (F == 4) {
+			uint2 val[NC];
+#pragma unroll
+			for (int c = 0; c < NC; ++c) val[c] = __ldg(reinterpret_cast<const uint2*>(table) + idx[c]);
+			__half2 r0 = __floats2half2_rn(0.f, 0.f), r1 = r0;
+#pragma unroll
+			for (int c = 0; c < NC; ++c) {
+				const __half2 wh = __half2half2(__float2half(w[c]));
+				r0 = __hfma2(wh, *reinterpret_cast<__half2*>(&val[c].x), r0);
+				r1 = __hfma2(wh, *reinterpret_cast<__half2*>(&val[c].y), r1);
+			}
+			out.h2[2 * s] = r0; out.h2[2 * s + 1] = r1;
+		} else if constexpr (F == 8) {
+			uint4 val[NC];
+#pragma unroll
+			for (int c = 0; c < NC; ++c) val[c] = __ldg(reinterpret_cast<const uint4*>(table) + idx[c]);
+			__half2 r[4];
+#pragma unroll
+			for (int k = 0; k < 4; ++k) r[k] = __floats2half2_rn(0.f, 0.f);
+#pragma unroll
+			for (int c = 0; c < NC; ++c) {
+				const __half2 wh = __half2half2(__float2half(w[c]));
+				const __half2* v = reinterpret_cast<const __half2*>(&val[c]);
+#pragma unroll
+				for (int k = 0; k < 4; ++k) r[k] = __hfma2(wh, v[k], r[k]);
+			}
+#pragma unroll
+			for (int k = 0; k < 4; ++k) out.h2[k] = r[k];
+		} else { // F == 1: scalar __hfma (vec.h:210-212)
+			__half r = __float2half(0.f);
+#pragma unroll
+			for (int c = 0; c < NC; ++c) r = __hfma(__float2half(w[c]), table[idx[c]], r);
+			reinterpret_cast<__half*>(&out.v)[s] = r;
+		}
+	}
+	return out.v;
+}
+
+// grid = {ceil(B/256), E_pad/8}; chunk-major block order keeps one group of levels hot in L2 at a time.
+template <int D, int F>
+__global__ void __launch_bounds__(256) grid_forward_kernel(const __grid_constant__ GridParams gp, uint32_t B,
+	const float* __restrict__ x, const __half* __restrict__ grid, __half* __restrict__ encoded) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= B) return;
+	const uint32_t chunk = blockIdx.y;
+	float p[D];
+	load_position<D>(x, i, p);
+	const uint4 v = encode_chunk<D, F>(gp, grid, p, chunk);
+	*reinterpret_cast<uint4*>(encoded + (size_t)i * gp.padded_width + chunk * 8) = v;
+}
+
+// Scatter dL/d(encoded) [B x E_pad] (fp16, loss-scaled) into the fp16 grid gradient with f16x2 reductions.
+// Same arithmetic as grid.h:248-318: product (half)weight * grad rounded to fp16, then red.add.noftz.f16x2.
+template <int D, int F>
+__global__ void __launch_bounds__(256) grid_backward_kernel(const __grid_constant__ GridParams gp, uint32_t B,
+	const float* __restrict__ x, const __half* __restrict__ dL_denc, __half* __restrict__ grid_grad) {
+	static_assert(F == 2 || F == 4 || F == 8, "fp16 gradient scatter needs F >= 2 (grid.h:655-666)");
+	constexpr int LEVELS_PER_CHUNK = 8 / F;
+	constexpr int NC = 1 << D;
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= B) return;
+	const uint32_t chunk = blockIdx.y;
+	float p[D];
+	load_position<D>(x, i, p);
+	union { uint4 v; __half2 h2[4]; } g;
+	g.v = __ldg(reinterpret_cast<const uint4*>(dL_denc + (size_t)i * gp.padded_width + chunk * 8));
+#pragma unroll
+	for (int s = 0; s < LEVELS_PER_CHUNK; ++s) {
+		const uint32_t level = chunk * LEVELS_PER_CHUNK + s;
+		if (level >= gp.n_levels) break;
+		const GridLevel& lv = gp.level[level];
+		float frac[D]; uint32_t cell[D];
+#pragma unroll
+		for (int d = 0; d < D; ++d) pos_fract_dev(p[d], lv.scale, frac[d], cell[d]);
+		__half* gtable = grid_grad + (size_t)lv.offset * F;
+#pragma unroll
+		for (int c = 0; c < NC; ++c) {
+			float weight = 1.0f; uint32_t pg[D];
+#pragma unroll
+			for (int d = 0; d < D; ++d) {
+				if ((c & (1 << d)) == 0) { weight *= 1.0f - frac[d]; pg[d] = cell[d]; }
+				else { weight *= frac[d]; pg[d] = cell[d] + 1u; }
+			}
+			const uint32_t idx = grid_index_dev<D>(lv, pg);
+			const __half2 wh = __half2half2(__float2half(weight));
+#pragma unroll
+			for (int k = 0; k < F / 2; ++k) {
+				red_add_h2(gtable + (size_t)idx * F + 2 * k, __hmul2(wh, g.h2[s * (F / 2) + k]));
+			}
+		}
+	}
+}
+
+// Parity helper: the per-corner entry indices exactly as the encode/scatter kernels compute them.
+// out[(level * B + i) * 2^D + corner]   (same layout as oracle/ref_driver.cu dump_indices)
+template <int D>
+__global__ void grid_indices_kernel(const __grid_constant__ GridParams gp, uint32_t B, const float* __restrict__ x, uint32_t* __restrict__ out) {
+	constexpr int NC = 1 << D;
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= B) return;
+	const uint32_t level = blockIdx.y;
+	const GridLevel& lv = gp.level[level];
+	float p[D];
+	load_position<D>(x, i, p);
+	float frac[D]; uint32_t cell[D];
+#pragma unroll
+	for (int d = 0; d < D; ++d) pos_fract_dev(p[d], lv.scale, frac[d], cell[d]);
+#pragma unroll
+	for (int c = 0; c < NC; ++c) {
+		uint32_t pg[D];
+#pragma unroll
+		for (int d = 0; d < D; ++d) pg[d] = cell[d] + ((c >> d) & 1u);
+		out[((size_t)level * B + i) * NC + c] = grid_index_dev<D>(lv, pg);
+	}
+}
+
+} // namespace b200

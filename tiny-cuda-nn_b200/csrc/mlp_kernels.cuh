@@ -1,0 +1,439 @@
+// Fully fused MLP (width 64) for sm_100a on tcgen05 tensor cores.
+//
+// What it computes is the reference's FullyFusedMLP (src/fully_fused_mlp.cu:47-259, 499-557, 735-836): ReLU hidden
+// layers, linear output padded to 16, fp16 storage; plus (MODE_TRAIN) the L2 / RelativeL2 loss (losses/l2.h:40-75,
+// losses/relative_l2.h:40-75) and the weight gradients the reference obtains from CUTLASS split-K GEMMs
+// (include/tiny-cuda-nn/cutlass_matmul.h:437-479) and dL/d(input) (cutlass_matmul.h:351-408).
+//
+// How it is built is new (not wmma/CUTLASS): one persistent CTA of 128 threads owns 128-sample tiles.
+//   * every operand tile lives in shared memory exactly once, as rows of 128 bytes with the 128-byte swizzle:
+//     activation / gradient tiles [128 samples][64 halfs], weight tiles [out][in].  The same bytes serve as the
+//     K-major A operand of the forward / dgrad MMAs and as MN-major operands of the weight-gradient MMAs
+//     (where the batch is the K dimension), so nothing is ever transposed or stored twice;
+//   * accumulators live in TMEM: one 64-column block for the layer chain, and one 64-column block per weight matrix
+//     whose tcgen05.mma accumulate across ALL tiles of the CTA (split-K over the batch without any HBM traffic);
+//     they are flushed once per CTA as fp32 partials and reduced by mlp_finalize_kernel (deterministic);
+//   * thread t owns sample row t of the tile: tcgen05.ld gives it the whole fp32 row, it applies ReLU / the ReLU mask
+//     (kept as 64-bit register masks, the reference re-reads the stored activations) / the loss, and writes the fp16
+//     row back to shared memory for the next MMA.  No activation ever goes to HBM (the reference moves ~0.5 GB/step).
+#pragma once
+#include "ptx.cuh"
+
+namespace b200 {
+
+constexpr int MLP_W = 64;          // hidden width handled by this kernel
+constexpr int MLP_TILE = 128;      // samples per tile = UMMA M
+constexpr int MLP_OUT = 16;        // padded output width (fully_fused_mlp.cu:544: fused last layer only for <=16 outputs)
+constexpr int TILE_BYTES = MLP_TILE * 128;
+constexpr int MLP_MAX_HIDDEN = 4;
+
+enum MlpMode : int { MODE_INFER = 0, MODE_TRAIN = 1, MODE_BACKWARD = 2 };
+enum LossType : int { LOSS_L2 = 0, LOSS_RELATIVE_L2 = 1 };
+
+struct MlpArgs {
+	uint32_t n_tiles;              // B / 128
+	uint32_t in_width;             // E_pad: 16, 32, 48 or 64
+	uint32_t n_hidden;             // hidden layers H >= 1 (hidden matmuls = H-1)
+	uint32_t n_out;                // real output dims (<= 16)
+	const __half* input;           // [B][in_width]
+	const __half* params;          // [64 x in], (H-1) x [64 x 64], [16 x 64]   row-major (fully_fused_mlp.cu:654-671)
+	__half* output;                // [B][16]  (nullable in TRAIN)
+	float* output_f32;             // [B][n_out] (INFER only, nullable): fused trim_and_cast (object.h:174-175)
+	const float* target;           // [B][n_out] fp32 (TRAIN)
+	const __half* dL_doutput;      // [B][16] (BACKWARD)
+	__half* dL_dinput;             // [B][in_width] (nullable)
+	float* dW_partials;            // [gridDim.x][n_mlp_params] fp32 (TRAIN/BACKWARD, nullable => no weight gradients)
+	float* loss_partials;          // [gridDim.x] (TRAIN)
+	uint32_t n_mlp_params;
+	int loss_type;
+	float loss_scale;
+	float inv_n_total;             // 1 / (B * n_out)  (losses/l2.h:62-64: n_total = n_elements / stride * dims)
+	float n_total;
+};
+
+// byte offset of 16-byte chunk `c` of row `r` inside a 128-byte-swizzled tile
+__device__ __forceinline__ uint32_t sw128(uint32_t r, uint32_t c) { return r * 128u + ((c ^ (r & 7u)) << 4); }
+
+__host__ __device__ constexpr uint32_t mlp_smem_bytes(int n_hidden, int in_width, bool train) {
+	// [ACT 0..H][G0][G1 (train)] [W_in 8K][W_inT E x 128 B][W_hid (H-1) x 8K][W_out 2K][barrier etc.]
+	// The weight region (>= 8K + 2K + 2K..8K + ...) directly follows the tiles, so "tile + 16 KB" (the second, unused
+	// 64-row atom of an M = 128 MN-major operand) is always mapped shared memory.
+	return 1024u /*align slack*/ + (uint32_t)(n_hidden + 1 + (train ? 2 : 0)) * TILE_BYTES + 8192u + (uint32_t)in_width * 128u
+		+ (uint32_t)(n_hidden - 1) * 8192u + 2048u + 256u + (n_hidden == 1 && in_width < 48 ? 4096u : 0u);
+}
+__host__ __device__ constexpr uint32_t mlp_tmem_cols(int n_hidden, bool train) {
+	const uint32_t need = train ? 64u * (uint32_t)(n_hidden + 2) : 64u; // chain + dW_in + (H-1) dW_hid + dW_out
+	return need <= 64 ? 64 : need <= 128 ? 128 : need <= 256 ? 256 : 512;
+}
+
+template <int MODE, int H_>
+__global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArgs a) {
+	constexpr bool TRAIN = MODE != MODE_INFER;
+	extern __shared__ uint8_t smem_raw[];
+	uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+	const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+	constexpr uint32_t H = H_;
+	const uint32_t E = a.in_width;
+
+	// ---- shared memory carve-up -------------------------------------------------------------------
+	uint8_t* act = smem;                                        // ACT[0..H], ACT[0] = input tile
+	uint8_t* gbuf = act + (H + 1) * TILE_BYTES;                 // G[0], G[1]
+	uint8_t* w_in = gbuf + (TRAIN ? 2 : 0) * TILE_BYTES;        // [64 out][128 B], in < E valid
+	uint8_t* w_inT = w_in + 8192;                               // [E in][128 B = 64 out]   (K-major B operand of dX = G * W_in)
+	uint8_t* w_hid = w_inT + E * 128;                            // (H-1) x [64 out][128 B]
+	uint8_t* w_out = w_hid + (H - 1) * 8192;                    // [16 out][128 B]
+	uint8_t* tail = w_out + 2048;
+	uint64_t* bar = reinterpret_cast<uint64_t*>(tail);
+	uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tail + 16);
+	float* red_buf = reinterpret_cast<float*>(tail + 32);       // 4 floats
+
+	// ---- one-time setup ---------------------------------------------------------------------------
+	constexpr uint32_t tmem_cols = mlp_tmem_cols((int)H, TRAIN);
+	if (warp == 0) tmem_alloc(tmem_slot, tmem_cols);
+	if (tid == 32) { mbar_init(bar, 1); mbar_fence_init(); }
+
+	// weights: global row-major -> swizzled tiles (16-byte chunks, coalesced reads)
+	{
+		const __half* p = a.params;
+		const uint32_t cpr_in = E / 8; // chunks per row of W_in
+		for (uint32_t q = tid; q < 64 * cpr_in; q += 128) {
+			const uint32_t r = q / cpr_in, c = q % cpr_in;
+			*reinterpret_cast<uint4*>(w_in + sw128(r, c)) = __ldg(reinterpret_cast<const uint4*>(p + r * E) + c);
+		}
+		for (uint32_t q = tid; q < 64 * E; q += 128) { // transposed copy, element-wise (once per CTA)
+			const uint32_t o = q / E, i = q % E;
+			*reinterpret_cast<__half*>(w_inT + sw128(i, o >> 3) + (o & 7) * 2) = p[o * E + i];
+		}
+		p += 64 * E;
+		for (uint32_t l = 0; l + 1 < H; ++l) {
+			for (uint32_t q = tid; q < 64 * 8; q += 128) {
+				const uint32_t r = q >> 3, c = q & 7;
+				*reinterpret_cast<uint4*>(w_hid + l * 8192 + sw128(r, c)) = __ldg(reinterpret_cast<const uint4*>(p + r * 64) + c);
+			}
+			p += 64 * 64;
+		}
+		for (uint32_t q = tid; q < 16 * 8; q += 128) {
+			const uint32_t r = q >> 3, c = q & 7;
+			*reinterpret_cast<uint4*>(w_out + sw128(r, c)) = __ldg(reinterpret_cast<const uint4*>(p + r * 64) + c);
+		}
+	}
+	fence_proxy_async_smem();
+	tc_fence_before();
+	__syncthreads();
+	tc_fence_after();
+	const uint32_t tmem = *tmem_slot;
+	const uint32_t t_acc = tmem;                 // chain accumulator, 64 columns
+	const uint32_t t_dw_in = tmem + 64;          // D[in][out]   (transposed)
+	const uint32_t t_dw_hid = tmem + 128;        // D[out][in], 64 columns per hidden matmul
+	const uint32_t t_dw_out = tmem + 128 + 64 * (H - 1); // D[out(16 valid)][in]
+	const uint32_t lane_off = (warp * 32) << 16; // this warp's TMEM lane window
+
+	// descriptors (constant parts)
+	constexpr uint32_t SBO = 1024, LBO_K = 16, LBO_MN = TILE_BYTES;
+	const uint32_t act_addr = smem_u32(act), g_addr = smem_u32(gbuf);
+	const uint32_t idesc_fwd64 = make_idesc_f16(128, 64, 0, 0);
+	const uint32_t idesc_fwd16 = make_idesc_f16(128, 16, 0, 0);
+	const uint32_t idesc_dgrad = make_idesc_f16(128, 64, 0, 1);   // A K-major, B = weight tile viewed MN-major
+	const uint32_t idesc_dx = make_idesc_f16(128, E, 0, 0);       // B = W_inT K-major
+	const uint32_t idesc_dw = make_idesc_f16(128, 64, 1, 1);      // both operands MN-major, K = 128 samples
+
+	uint32_t phase = 0;
+	uint32_t first_tile = 1;
+	float loss_acc = 0.f;
+	const uint32_t row = tid;
+
+	for (uint32_t tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+		const size_t sample0 = (size_t)tile * MLP_TILE;
+		// ---- input tile -> ACT[0] ------------------------------------------------------------------
+		{
+			const uint32_t cpr = E / 8;
+			const uint4* src = reinterpret_cast<const uint4*>(a.input + sample0 * E);
+			for (uint32_t q = tid; q < MLP_TILE * cpr; q += 128) {
+				const uint32_t r = q / cpr, c = q % cpr;
+				*reinterpret_cast<uint4*>(act + sw128(r, c)) = __ldg(src + q);
+			}
+		}
+		fence_proxy_async_smem();
+		tc_fence_before();
+		__syncthreads();
+
+		uint64_t relu_mask[H];
+		// ---- forward hidden layers -----------------------------------------------------------------
+#pragma unroll
+		for (uint32_t k = 0; k < H; ++k) {
+			if (tid == 0) {
+				tc_fence_after();
+				const uint32_t ksteps = (k == 0 ? E : 64u) / 16;
+				const uint32_t a_addr = act_addr + k * TILE_BYTES;
+				const uint32_t b_addr = k == 0 ? smem_u32(w_in) : smem_u32(w_hid) + (k - 1) * 8192;
+				for (uint32_t s = 0; s < ksteps; ++s)
+					umma_f16(t_acc, make_desc_sw128(a_addr + s * 32, LBO_K, SBO), make_desc_sw128(b_addr + s * 32, LBO_K, SBO), idesc_fwd64, s > 0);
+				umma_commit(bar);
+			}
+			mbar_wait(bar, phase); phase ^= 1;
+			tc_fence_after();
+			uint64_t mask = 0;
+			uint8_t* dst = act + (k + 1) * TILE_BYTES;
+#pragma unroll
+			for (int half_i = 0; half_i < 2; ++half_i) {
+				uint32_t v[32];
+				tmem_ld32(t_acc + lane_off + half_i * 32, v);
+				tmem_ld_wait();
+#pragma unroll
+				for (int c = 0; c < 4; ++c) {
+					uint32_t pk[4];
+#pragma unroll
+					for (int j = 0; j < 4; ++j) {
+						float x0 = __uint_as_float(v[c * 8 + 2 * j]), x1 = __uint_as_float(v[c * 8 + 2 * j + 1]);
+						x0 = fmaxf(x0, 0.f); x1 = fmaxf(x1, 0.f);
+						pk[j] = pack_h2(x0, x1);
+						// ReLU' from the stored (fp16) post-activation > 0, like common_device.h:243-248
+						if (pk[j] & 0x00007FFFu) mask |= 1ull << (half_i * 32 + c * 8 + 2 * j);
+						if (pk[j] & 0x7FFF0000u) mask |= 1ull << (half_i * 32 + c * 8 + 2 * j + 1);
+					}
+					*reinterpret_cast<uint4*>(dst + sw128(row, half_i * 4 + c)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+				}
+			}
+			relu_mask[k] = mask;
+			fence_proxy_async_smem();
+			tc_fence_before();
+			__syncthreads();
+		}
+		// ---- output layer --------------------------------------------------------------------------
+		if (tid == 0) {
+			tc_fence_after();
+			const uint32_t a_addr = act_addr + H * TILE_BYTES, b_addr = smem_u32(w_out);
+			for (uint32_t s = 0; s < 4; ++s)
+				umma_f16(t_acc, make_desc_sw128(a_addr + s * 32, LBO_K, SBO), make_desc_sw128(b_addr + s * 32, LBO_K, SBO), idesc_fwd16, s > 0);
+			umma_commit(bar);
+		}
+		mbar_wait(bar, phase); phase ^= 1;
+		tc_fence_after();
+		{
+			uint32_t v[16];
+			tmem_ld16(t_acc + lane_off, v);
+			tmem_ld_wait();
+			uint32_t yk[8];
+#pragma unroll
+			for (int j = 0; j < 8; ++j) yk[j] = pack_h2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
+			const size_t s = sample0 + row;
+			if (MODE != MODE_BACKWARD && a.output) {
+				uint4* o = reinterpret_cast<uint4*>(a.output + s * MLP_OUT);
+				o[0] = make_uint4(yk[0], yk[1], yk[2], yk[3]);
+				o[1] = make_uint4(yk[4], yk[5], yk[6], yk[7]);
+			}
+			if (MODE == MODE_INFER && a.output_f32) {
+				const __half* yh = reinterpret_cast<const __half*>(yk);
+				for (uint32_t j = 0; j < a.n_out; ++j) a.output_f32[s * a.n_out + j] = __half2float(yh[j]);
+			}
+			if (MODE == MODE_TRAIN) {
+				// loss on the fp16 prediction (the reference's network output is fp16), gradients as fp16 * loss_scale
+				const __half* yh = reinterpret_cast<const __half*>(yk);
+				__half dy[16];
+#pragma unroll
+				for (int j = 0; j < 16; ++j) {
+					float g = 0.f;
+					if ((uint32_t)j < a.n_out) {
+						const float pred = __half2float(yh[j]);
+						const float diff = pred - __ldg(a.target + s * a.n_out + j);
+						if (a.loss_type == LOSS_RELATIVE_L2) {
+							const float denom = pred * pred + 0.01f;
+							loss_acc += diff * diff / denom / a.n_total;
+							g = 2.f * diff / denom;
+						} else {
+							loss_acc += diff * diff / a.n_total;
+							g = 2.f * diff;
+						}
+						g = a.loss_scale * g / a.n_total;
+					}
+					dy[j] = __float2half(g);
+				}
+				const uint4* d4 = reinterpret_cast<const uint4*>(dy);
+				*reinterpret_cast<uint4*>(gbuf + sw128(row, 0)) = d4[0];
+				*reinterpret_cast<uint4*>(gbuf + sw128(row, 1)) = d4[1];
+			}
+			if (MODE == MODE_BACKWARD) {
+				const uint4* d4 = reinterpret_cast<const uint4*>(a.dL_doutput + s * MLP_OUT);
+				*reinterpret_cast<uint4*>(gbuf + sw128(row, 0)) = __ldg(d4);
+				*reinterpret_cast<uint4*>(gbuf + sw128(row, 1)) = __ldg(d4 + 1);
+			}
+		}
+		if constexpr (TRAIN) {
+			fence_proxy_async_smem();
+			tc_fence_before();
+			__syncthreads();
+			const bool want_dw = a.dW_partials != nullptr;
+			uint32_t gcur = 0; // G[gcur] holds the gradient w.r.t. the pre-activation feeding weight matrix `k+1`
+			// ---- backward through output matmul and hidden matmuls: k = H .. 1 ------------------------
+#pragma unroll
+			for (uint32_t k = H; k >= 1; --k) {
+				// weight matrix index k: k == H -> W_out (K = 16 outputs), else W_hid[k-1] (K = 64)
+				if (tid == 0) {
+					tc_fence_after();
+					const uint32_t ga = g_addr + gcur * TILE_BYTES;
+					const uint32_t ksteps = (k == H) ? 1u : 4u;
+					const uint32_t wb = (k == H) ? smem_u32(w_out) : smem_u32(w_hid) + (k - 1) * 8192;
+					// dA_k[128 x 64] = G[128 x K] * W[K x 64]:  B = weight tile viewed MN-major (N = in, K = out rows)
+					for (uint32_t s = 0; s < ksteps; ++s)
+						umma_f16(t_acc, make_desc_sw128(ga + s * 32, LBO_K, SBO), make_desc_sw128(wb + s * 2048, LBO_MN, SBO), idesc_dgrad, s > 0);
+					if (want_dw) {
+						// dW[out][in] += G^T[out x 128] * ACT_k[128 x in]; batch is K: both tiles viewed MN-major
+						const uint32_t td = (k == H) ? t_dw_out : t_dw_hid + (k - 1) * 64;
+						const uint32_t ab = act_addr + k * TILE_BYTES;
+						for (uint32_t s = 0; s < 8; ++s)
+							umma_f16(td, make_desc_sw128(ga + s * 2048, LBO_MN, SBO), make_desc_sw128(ab + s * 2048, LBO_MN, SBO), idesc_dw, (!first_tile) || s > 0);
+					}
+					umma_commit(bar);
+				}
+				mbar_wait(bar, phase); phase ^= 1;
+				tc_fence_after();
+				const uint64_t mask = relu_mask[k - 1];
+				uint8_t* dst = gbuf + (gcur ^ 1) * TILE_BYTES;
+#pragma unroll
+				for (int half_i = 0; half_i < 2; ++half_i) {
+					uint32_t v[32];
+					tmem_ld32(t_acc + lane_off + half_i * 32, v);
+					tmem_ld_wait();
+#pragma unroll
+					for (int c = 0; c < 4; ++c) {
+						uint32_t pk[4];
+#pragma unroll
+						for (int j = 0; j < 4; ++j) {
+							const int col = half_i * 32 + c * 8 + 2 * j;
+							const float x0 = ((mask >> col) & 1ull) ? __uint_as_float(v[c * 8 + 2 * j]) : 0.f;
+							const float x1 = ((mask >> (col + 1)) & 1ull) ? __uint_as_float(v[c * 8 + 2 * j + 1]) : 0.f;
+							pk[j] = pack_h2(x0, x1);
+						}
+						*reinterpret_cast<uint4*>(dst + sw128(row, half_i * 4 + c)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+					}
+				}
+				gcur ^= 1;
+				fence_proxy_async_smem();
+				tc_fence_before();
+				__syncthreads();
+			}
+			// ---- input matmul: dW_in (transposed accumulator) and dL/d(input) ---------------------------
+			const bool want_dx = a.dL_dinput != nullptr;
+			if (want_dw || want_dx) {
+				if (tid == 0) {
+					tc_fence_after();
+					const uint32_t ga = g_addr + gcur * TILE_BYTES;
+					if (want_dx)
+						for (uint32_t s = 0; s < 4; ++s)
+							umma_f16(t_acc, make_desc_sw128(ga + s * 32, LBO_K, SBO), make_desc_sw128(smem_u32(w_inT) + s * 32, LBO_K, SBO), idesc_dx, s > 0);
+					if (want_dw)
+						for (uint32_t s = 0; s < 8; ++s) // D[in][out] += X^T[in x 128] * G[128 x out]
+							umma_f16(t_dw_in, make_desc_sw128(act_addr + s * 2048, LBO_MN, SBO), make_desc_sw128(ga + s * 2048, LBO_MN, SBO), idesc_dw, (!first_tile) || s > 0);
+					umma_commit(bar);
+				}
+				mbar_wait(bar, phase); phase ^= 1;
+				tc_fence_after();
+				if (want_dx) {
+					__half* dst = a.dL_dinput + (sample0 + row) * E;
+					for (uint32_t c0 = 0; c0 < E; c0 += 16) {
+						uint32_t v[16];
+						tmem_ld16(t_acc + lane_off + c0, v);
+						tmem_ld_wait();
+						uint32_t pk[8];
+#pragma unroll
+						for (int j = 0; j < 8; ++j) pk[j] = pack_h2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
+						reinterpret_cast<uint4*>(dst + c0)[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+						reinterpret_cast<uint4*>(dst + c0)[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+					}
+				}
+				tc_fence_before();
+				__syncthreads();
+			}
+			first_tile = 0;
+		} else {
+			tc_fence_before();
+			__syncthreads();
+		}
+	}
+
+	// ---- per-CTA flush: weight-gradient partials and loss partial ---------------------------------------
+	if constexpr (TRAIN) {
+		tc_fence_after();
+		if (a.dW_partials != nullptr) {
+			float* out = a.dW_partials + (size_t)blockIdx.x * a.n_mlp_params;
+			const bool have = !first_tile; // CTA processed at least one tile
+			if (warp < 2) {
+				const uint32_t r = warp * 32 + lane; // accumulator row 0..63
+				// dW_in: D[in = r][out = j]  ->  grads[out * E + in]
+#pragma unroll
+				for (int half_i = 0; half_i < 2; ++half_i) {
+					uint32_t v[32];
+					if (have) { tmem_ld32(t_dw_in + lane_off + half_i * 32, v); tmem_ld_wait(); }
+					if (r < E) {
+#pragma unroll
+						for (int j = 0; j < 32; ++j) out[(half_i * 32 + j) * E + r] = have ? __uint_as_float(v[j]) : 0.f;
+					}
+				}
+				float* o = out + 64 * E;
+				for (uint32_t l = 0; l + 1 < H; ++l) {
+#pragma unroll
+					for (int half_i = 0; half_i < 2; ++half_i) {
+						uint32_t v[32];
+						if (have) { tmem_ld32(t_dw_hid + l * 64 + lane_off + half_i * 32, v); tmem_ld_wait(); }
+						float4* o4 = reinterpret_cast<float4*>(o + r * 64 + half_i * 32);
+#pragma unroll
+						for (int j = 0; j < 8; ++j)
+							o4[j] = have ? make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3])) : make_float4(0, 0, 0, 0);
+					}
+					o += 64 * 64;
+				}
+				if (warp == 0) {
+#pragma unroll
+					for (int half_i = 0; half_i < 2; ++half_i) {
+						uint32_t v[32];
+						if (have) { tmem_ld32(t_dw_out + lane_off + half_i * 32, v); tmem_ld_wait(); }
+						if (r < 16) {
+							float4* o4 = reinterpret_cast<float4*>(o + r * 64 + half_i * 32);
+#pragma unroll
+							for (int j = 0; j < 8; ++j)
+								o4[j] = have ? make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3])) : make_float4(0, 0, 0, 0);
+						}
+					}
+				}
+			}
+		}
+		if (MODE == MODE_TRAIN && a.loss_partials != nullptr) {
+			float s = loss_acc;
+#pragma unroll
+			for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xFFFFFFFFu, s, o);
+			if (lane == 0) red_buf[warp] = s;
+			__syncthreads();
+			if (tid == 0) a.loss_partials[blockIdx.x] = red_buf[0] + red_buf[1] + red_buf[2] + red_buf[3];
+		}
+	}
+	tc_fence_before();
+	__syncthreads();
+	if (warp == 0) tmem_dealloc(tmem, tmem_cols);
+}
+
+// Sum the per-CTA fp32 partials -> fp16 weight gradients (layout of the reference's gradient matrices) and the loss.
+__global__ void mlp_finalize_kernel(uint32_t n_params, uint32_t n_parts, const float* __restrict__ partials, __half* __restrict__ grads,
+	const float* __restrict__ loss_partials, float* __restrict__ loss_out) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n_params && grads) {
+		float s = 0.f;
+		for (uint32_t p = 0; p < n_parts; ++p) s += partials[(size_t)p * n_params + i];
+		grads[i] = __float2half(s);
+	}
+	if (blockIdx.x == 0 && loss_partials && loss_out) {
+		__shared__ float sh[32];
+		float s = 0.f;
+		for (uint32_t p = threadIdx.x; p < n_parts; p += blockDim.x) s += loss_partials[p];
+#pragma unroll
+		for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xFFFFFFFFu, s, o);
+		if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = s;
+		__syncthreads();
+		if (threadIdx.x == 0) {
+			float t = 0.f;
+			for (uint32_t w = 0; w < blockDim.x / 32; ++w) t += sh[w];
+			*loss_out = t;
+		}
+	}
+}
+
+} // namespace b200

@@ -1,0 +1,139 @@
+// Fused Adam + fp32 master weights, and the reference-compatible parameter initialisation, for sm_100a.
+//
+// Semantics follow the reference's adam_step (include/tiny-cuda-nn/optimizers/adam.h:47-119): unscale by loss_scale,
+// L2 regularisation on matrix (MLP) weights only, skip of hash-grid entries whose gradient is exactly zero, a
+// per-parameter step counter for the bias correction, AdaBound clamp, fp32 master + fp16 copy.  New here:
+// 4 parameters per thread with 8/16-byte accesses, entries whose four gradients are all zero touch nothing but the
+// 8 gradient bytes, the gradient is re-zeroed in the same pass (the reference spends a cudaMemsetAsync over the whole
+// grid gradient every step, encodings/grid.h:857-859), and the 1/world_size of data-parallel training is folded in.
+#pragma once
+#include "ptx.cuh"
+
+namespace b200 {
+
+struct AdamArgs {
+	uint32_t n;                   // total parameters
+	uint32_t n_matrix;            // leading MLP weights (L2 reg, never skipped)
+	float loss_scale;             // gradient divisor: loss_scale * world_size
+	float learning_rate, beta1, beta2, epsilon, l2_reg;
+	float relative_decay, absolute_decay;
+	float lower_lr_bound, upper_lr_bound;
+	float weight_clip;
+	float non_matrix_lr_factor;
+	int zero_grads;               // re-zero the non-matrix gradients after consuming them
+	float* master;
+	__half* params;
+	__half* grads;
+	float* m;
+	float* v;
+	uint32_t* steps;
+};
+
+__device__ __forceinline__ bool adam_one(const AdamArgs& a, uint32_t i, float g_half, float& w, float& m, float& v, uint32_t& step) {
+	float gradient = g_half / a.loss_scale;
+	const bool is_matrix = i < a.n_matrix;
+	if (!is_matrix && gradient == 0.f) return false;
+	if (is_matrix) gradient += a.l2_reg * w;
+	const float gradient_sq = gradient * gradient;
+	m = a.beta1 * m + (1 - a.beta1) * gradient;
+	v = a.beta2 * v + (1 - a.beta2) * gradient_sq;
+	float lr = a.learning_rate;
+	if (!is_matrix) lr *= a.non_matrix_lr_factor;
+	step += 1;
+	lr *= sqrtf(1 - powf(a.beta2, (float)step)) / (1 - powf(a.beta1, (float)step));
+	const float eff = fminf(fmaxf(lr / (sqrtf(v) + a.epsilon), a.lower_lr_bound), a.upper_lr_bound);
+	// weight_decay(relative * lr, absolute * lr, w)   (common_device.h:870-873)
+	const float decayed = (1 - a.relative_decay * lr) * w - copysignf(a.absolute_decay * lr, w);
+	float nw = decayed - eff * m;
+	if (a.weight_clip != 0.f) nw = fminf(fmaxf(nw, -a.weight_clip), a.weight_clip);
+	w = nw;
+	return true;
+}
+
+__global__ void __launch_bounds__(256) adam_kernel(const __grid_constant__ AdamArgs a) {
+	const uint32_t i0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+	if (i0 >= a.n) return;
+	if (i0 + 4 <= a.n) {
+		union { uint2 u; __half h[4]; } g;
+		g.u = *reinterpret_cast<const uint2*>(a.grads + i0);
+		const bool any_nonzero = ((g.u.x | g.u.y) & 0x7FFF7FFFu) != 0;
+		if (i0 >= a.n_matrix && !any_nonzero) return; // nothing to do for four untouched grid entries
+		float4 w = *reinterpret_cast<float4*>(a.master + i0);
+		float4 m = *reinterpret_cast<float4*>(a.m + i0);
+		float4 v = *reinterpret_cast<float4*>(a.v + i0);
+		uint4 s = *reinterpret_cast<uint4*>(a.steps + i0);
+		adam_one(a, i0 + 0, __half2float(g.h[0]), w.x, m.x, v.x, s.x);
+		adam_one(a, i0 + 1, __half2float(g.h[1]), w.y, m.y, v.y, s.y);
+		adam_one(a, i0 + 2, __half2float(g.h[2]), w.z, m.z, v.z, s.z);
+		adam_one(a, i0 + 3, __half2float(g.h[3]), w.w, m.w, v.w, s.w);
+		*reinterpret_cast<float4*>(a.master + i0) = w;
+		*reinterpret_cast<float4*>(a.m + i0) = m;
+		*reinterpret_cast<float4*>(a.v + i0) = v;
+		*reinterpret_cast<uint4*>(a.steps + i0) = s;
+		uint2 ph;
+		ph.x = pack_h2(w.x, w.y); ph.y = pack_h2(w.z, w.w);
+		*reinterpret_cast<uint2*>(a.params + i0) = ph;
+		if (a.zero_grads && i0 >= a.n_matrix) *reinterpret_cast<uint2*>(a.grads + i0) = make_uint2(0, 0);
+	} else {
+		for (uint32_t i = i0; i < a.n; ++i) {
+			float w = a.master[i], m = a.m[i], v = a.v[i];
+			uint32_t s = a.steps[i];
+			if (adam_one(a, i, __half2float(a.grads[i]), w, m, v, s)) {
+				a.master[i] = w; a.m[i] = m; a.v[i] = v; a.steps[i] = s; a.params[i] = __float2half(w);
+			}
+			if (a.zero_grads && i >= a.n_matrix) a.grads[i] = __float2half(0.f);
+		}
+	}
+}
+
+// ---- parameter initialisation ---------------------------------------------------------------------
+// pcg32 (PCG-XSH-RR 64/32) with O(log n) jump-ahead, as vendored by the reference (dependencies/pcg32/pcg32.h).
+struct Pcg32Dev {
+	uint64_t state, inc;
+	__device__ void advance(uint64_t delta) {
+		uint64_t cur_mult = 0x5851f42d4c957f2dULL, cur_plus = inc, acc_mult = 1u, acc_plus = 0u;
+		while (delta > 0) {
+			if (delta & 1) { acc_mult *= cur_mult; acc_plus = acc_plus * cur_mult + cur_plus; }
+			cur_plus = (cur_mult + 1) * cur_plus;
+			cur_mult *= cur_mult;
+			delta >>= 1;
+		}
+		state = acc_mult * state + acc_plus;
+	}
+	__device__ uint32_t next_uint() {
+		const uint64_t old = state;
+		state = old * 0x5851f42d4c957f2dULL + inc;
+		const uint32_t xorshifted = (uint32_t)(((old >> 18u) ^ old) >> 27u);
+		const uint32_t rot = (uint32_t)(old >> 59u);
+		return (xorshifted >> rot) | (xorshifted << ((~rot + 1u) & 31));
+	}
+	__device__ float next_float() { return __uint_as_float((next_uint() >> 9) | 0x3f800000u) - 1.0f; }
+};
+
+// Xavier-uniform rows of one weight matrix; the reference does this on the host (gpu_matrix.h:284-299:
+// next_float() * 2.0f * scale - scale, separate roundings), element e uses the e-th draw after `base`.
+__global__ void init_xavier_kernel(uint32_t n, uint64_t state, uint64_t inc, uint64_t base, float scale, float* __restrict__ out) {
+	const uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
+	if (e >= n) return;
+	Pcg32Dev rng{state, inc};
+	rng.advance(base + e);
+	out[e] = __fsub_rn(__fmul_rn(__fmul_rn(rng.next_float(), 2.0f), scale), scale);
+}
+
+// Uniform(lower, upper) with the element -> draw mapping of the reference's generate_random_kernel
+// (include/tiny-cuda-nn/random.h:39-63): thread i jumps ahead 4 i and writes element i + n_threads * j with draw j.
+__global__ void init_uniform_kernel(uint32_t n, uint32_t n_threads, uint64_t state, uint64_t inc, uint64_t base, float lower, float upper, float* __restrict__ out) {
+	const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+	if (idx >= n) return;
+	const uint32_t i = idx % n_threads, j = idx / n_threads;
+	Pcg32Dev rng{state, inc};
+	rng.advance(base + (uint64_t)i * 4 + j);
+	out[idx] = rng.next_float() * (upper - lower) + lower;
+}
+
+__global__ void cast_f32_to_f16_kernel(size_t n, const float* __restrict__ in, __half* __restrict__ out) {
+	const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n) out[i] = __float2half(in[i]);
+}
+
+} // namespace b200

@@ -1,0 +1,545 @@
+// libtcnn_b200.so — host side of the C ABI declared in include/tcnn_b200.h.
+// Resolves the tcnn JSON config into a plan (level table, MLP shape, loss, Adam hyper-parameters) and launches the
+// sm_100a kernels of grid_kernels.cuh / mlp_kernels.cuh / optim_kernels.cuh.  No CPU compute path exists here.
+#include "../../include/tcnn_b200.h"
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <limits>
+#include <memory>
+#include <random>
+#include <string>
+
+#include "grid_kernels.cuh"
+#include "json_mini.h"
+#include "mlp_kernels.cuh"
+#include "optim_kernels.cuh"
+
+using namespace b200;
+
+static thread_local std::string g_last_error;
+
+#define API_BEGIN try {
+#define API_END                                                                                   \
+	return 0;                                                                                     \
+	}                                                                                             \
+	catch (const std::exception& e) { g_last_error = e.what(); return 1; }                        \
+	catch (...) { g_last_error = "unknown error"; return 1; }
+
+#define FAIL(msg) throw std::runtime_error(std::string(__FILE__) + ":" + std::to_string(__LINE__) + " " + (msg))
+#define CHECK(cond, msg) do { if (!(cond)) FAIL(std::string(msg) + " (" #cond ")"); } while (0)
+#define CUDA_OK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) FAIL(std::string(#call " failed: ") + cudaGetErrorString(e_)); } while (0)
+
+struct tcnn_b200_plan {
+	tcnn_b200_info info{};
+	GridParams grid{};
+	float log2_per_level_scale = 1.f;
+	bool device_scales = false;     // level scales were evaluated by the device (CUDA exp2f) rather than libm
+	int n_sms = 148;
+	// Adam extras
+	float non_matrix_lr_factor = 1.f, weight_clip = 0.f;
+	bool adabound = false;
+};
+
+static uint32_t next_multiple_u32(uint32_t v, uint32_t m) { return (v + m - 1) / m * m; }
+
+// Per-level constants of grid_index (common_device.h:690-707) for a given (scale, size): strides with uint32 wrap.
+static void fill_level(GridLevel& lv, float scale, uint32_t size, uint32_t offset, uint32_t n_dims) {
+	lv.scale = scale;
+	lv.resolution = (uint32_t)std::ceil(scale) + 1; // grid_resolution, common_device.h:716-718
+	lv.size = size;
+	lv.offset = offset;
+	uint32_t stride = 1, d = 0;
+	for (uint32_t k = 0; k < (uint32_t)MAX_DIMS; ++k) lv.stride[k] = 0;
+	for (; d < n_dims && stride <= size; ++d) {
+		lv.stride[d] = stride;
+		stride *= lv.resolution; // uint32 wrap on purpose
+	}
+	lv.n_dense_dims = d;
+	lv.hashed = size < stride ? 1u : 0u;
+}
+
+static void build_levels(tcnn_b200_plan* p, const float* scales) {
+	const tcnn_b200_info& in = p->info;
+	for (uint32_t l = 0; l < in.n_levels; ++l) {
+		fill_level(p->grid.level[l], scales[l], in.level_offset[l + 1] - in.level_offset[l], in.level_offset[l], in.n_input_dims);
+		p->info.level_scale[l] = scales[l];
+		p->info.level_resolution[l] = p->grid.level[l].resolution;
+	}
+}
+
+// The reference evaluates grid_scale inside its kernels with CUDA's exp2f; do the same so indices are bit-identical
+// even for non-power-of-two per_level_scale.  Falls back to libm only when no device is present (CPU-side tests).
+static void try_device_scales(tcnn_b200_plan* p) {
+	int n_dev = 0;
+	if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev == 0) { cudaGetLastError(); return; }
+	int dev = 0;
+	if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); return; }
+	cudaDeviceGetAttribute(&p->n_sms, cudaDevAttrMultiProcessorCount, dev);
+	float* d_scales = nullptr;
+	if (cudaMalloc(&d_scales, sizeof(float) * MAX_LEVELS) != cudaSuccess) { cudaGetLastError(); return; }
+	grid_scale_kernel<<<1, MAX_LEVELS>>>(p->info.n_levels, p->log2_per_level_scale, p->info.base_resolution, d_scales);
+	float h[MAX_LEVELS];
+	const cudaError_t e = cudaMemcpy(h, d_scales, sizeof(float) * p->info.n_levels, cudaMemcpyDeviceToHost);
+	cudaFree(d_scales);
+	if (e != cudaSuccess) { cudaGetLastError(); return; }
+	build_levels(p, h);
+	p->device_scales = true;
+}
+
+static void parse_optimizer(tcnn_b200_plan* p, const jsonmini::Value& o) {
+	tcnn_b200_info& in = p->info;
+	if (o.contains("otype")) {
+		const std::string t = jsonmini::lower(o.string("otype", "adam"));
+		CHECK(t == "adam", "optimizer otype '" + t + "' is outside the hot path (only Adam, optimizers/adam.h)");
+	}
+	// update_hyperparams, optimizers/adam.h:210-258
+	in.learning_rate = (float)o.number("learning_rate", in.learning_rate);
+	in.beta1 = (float)o.number("beta1", in.beta1);
+	in.beta2 = (float)o.number("beta2", in.beta2);
+	in.epsilon = (float)o.number("epsilon", in.epsilon);
+	in.l2_reg = (float)o.number("l2_reg", in.l2_reg);
+	in.relative_decay = (float)o.number("relative_decay", in.relative_decay);
+	in.absolute_decay = (float)o.number("absolute_decay", in.absolute_decay);
+	p->adabound = o.boolean("adabound", p->adabound);
+	p->weight_clip = (float)o.number("clipping_magnitude", p->weight_clip);
+	p->non_matrix_lr_factor = (float)o.number("non_matrix_learning_rate_factor", p->non_matrix_lr_factor);
+}
+
+// ---- plan ------------------------------------------------------------------------------------------
+extern "C" const char* tcnn_b200_last_error(void) { return g_last_error.c_str(); }
+extern "C" uint32_t tcnn_b200_abi_version(void) { return 1; }
+extern "C" const char* tcnn_b200_arch(void) { return "sm_100a"; }
+extern "C" uint32_t tcnn_b200_batch_size_granularity(void) { return 256; }
+
+extern "C" int tcnn_b200_plan_create(const char* json_utf8, uint32_t n_input_dims, uint32_t n_output_dims, tcnn_b200_plan** out) {
+	API_BEGIN
+	CHECK(json_utf8 && out, "null argument");
+	const jsonmini::Value cfg = jsonmini::parse(json_utf8);
+	const jsonmini::Value enc = cfg.object("encoding"), net = cfg.object("network"), loss = cfg.object("loss"), opt = cfg.object("optimizer");
+	std::unique_ptr<tcnn_b200_plan> p(new tcnn_b200_plan());
+	tcnn_b200_info& in = p->info;
+	in.n_input_dims = n_input_dims;
+	in.n_output_dims = n_output_dims;
+
+	// --- encoding: create_grid_encoding (encodings/grid.h:1143-1208) ---
+	const std::string etype = jsonmini::lower(enc.string("otype", "Grid"));
+	CHECK(etype == "hashgrid" || etype == "grid", "encoding otype '" + etype + "' is outside the hot path (HashGrid only; SURVEY.md section 8)");
+	CHECK(jsonmini::lower(enc.string("type", "Hash")) == "hash", "only grid type 'Hash' is implemented");
+	CHECK(jsonmini::lower(enc.string("hash", "CoherentPrime")) == "coherentprime", "only hash 'CoherentPrime' is implemented");
+	CHECK(jsonmini::lower(enc.string("interpolation", "Linear")) == "linear", "only interpolation 'Linear' is implemented");
+	CHECK(!enc.boolean("stochastic_interpolation", false), "stochastic_interpolation is not implemented");
+	in.n_features_per_level = (uint32_t)enc.number("n_features_per_level", 2);
+	CHECK(in.n_features_per_level == 2 || in.n_features_per_level == 4 || in.n_features_per_level == 8,
+		"GridEncoding: n_features_per_level must be 2, 4 or 8 on this path (1 needs the fp32 gradient variant)");
+	uint32_t n_features;
+	if (enc.contains("n_features") || enc.contains("n_grid_features")) {
+		CHECK(!enc.contains("n_levels"), "GridEncoding: may not specify n_features and n_levels simultaneously (one determines the other)");
+		n_features = (uint32_t)enc.number(enc.contains("n_features") ? "n_features" : "n_grid_features", 0);
+	} else {
+		n_features = in.n_features_per_level * (uint32_t)enc.number("n_levels", 16);
+	}
+	CHECK(n_features % in.n_features_per_level == 0, "GridEncoding: n_features must be a multiple of n_features_per_level");
+	in.n_levels = n_features / in.n_features_per_level;
+	CHECK(in.n_levels >= 1 && in.n_levels <= (uint32_t)MAX_LEVELS, "GridEncoding: n_levels must be in [1, 32] here");
+	in.log2_hashmap_size = (uint32_t)enc.number("log2_hashmap_size", 19);
+	CHECK(in.log2_hashmap_size >= 3 && in.log2_hashmap_size <= 28, "log2_hashmap_size out of range");
+	in.base_resolution = (uint32_t)enc.number("base_resolution", 16);
+	in.per_level_scale = (float)enc.number("per_level_scale", 2.0);
+	CHECK(n_input_dims >= 2 && n_input_dims <= 4, "GridEncoding: number of input dims must be 2, 3 or 4");
+	in.encoded_width = next_multiple_u32(n_features, 16); // set_alignment(16) for FullyFusedMLP, network_with_input_encoding.h:47
+	p->log2_per_level_scale = std::log2(in.per_level_scale);
+
+	// offset table on the host, as the reference's constructor does (grid.h:692-716)
+	float host_scales[MAX_LEVELS];
+	uint32_t offset = 0;
+	for (uint32_t l = 0; l < in.n_levels; ++l) {
+		host_scales[l] = exp2f(l * p->log2_per_level_scale) * in.base_resolution - 1.0f;
+		const uint32_t resolution = (uint32_t)std::ceil(host_scales[l]) + 1;
+		const uint32_t max_params = std::numeric_limits<uint32_t>::max() / 2;
+		uint32_t n = max_params;
+		if (!(std::pow((float)resolution, (float)n_input_dims) > (float)max_params)) {
+			n = 1;
+			for (uint32_t d = 0; d < n_input_dims; ++d) n *= resolution;
+		}
+		n = next_multiple_u32(n, 8u);
+		n = std::min(n, 1u << in.log2_hashmap_size);
+		in.level_offset[l] = offset;
+		offset += n;
+	}
+	in.level_offset[in.n_levels] = offset;
+	in.n_params_grid = (uint64_t)offset * in.n_features_per_level;
+	p->grid.n_levels = in.n_levels;
+	p->grid.n_features = n_features;
+	p->grid.padded_width = in.encoded_width;
+	build_levels(p.get(), host_scales);
+	try_device_scales(p.get());
+
+	// --- network: create_network (src/network.cu:97-140), FullyFusedMLP ctor (src/fully_fused_mlp.cu:635-678) ---
+	const std::string ntype = jsonmini::lower(net.string("otype", "FullyFusedMLP"));
+	CHECK(ntype == "fullyfusedmlp" || ntype == "megakernelmlp", "network otype '" + ntype + "' is outside the hot path (FullyFusedMLP only)");
+	in.n_neurons = (uint32_t)net.number("n_neurons", 128);
+	in.n_hidden_layers = (uint32_t)net.number("n_hidden_layers", 5);
+	CHECK(in.n_neurons == 64, "FullyFusedMLP: this build implements n_neurons = 64 (16/32/128 are listed as next in DESIGN.md)");
+	CHECK(in.n_hidden_layers >= 1 && in.n_hidden_layers <= (uint32_t)MLP_MAX_HIDDEN, "FullyFusedMLP: n_hidden_layers must be in [1, 4] here");
+	CHECK(jsonmini::lower(net.string("activation", "ReLU")) == "relu", "only activation 'ReLU' is implemented");
+	CHECK(jsonmini::lower(net.string("output_activation", "None")) == "none", "only output_activation 'None' is implemented");
+	CHECK(n_output_dims >= 1 && n_output_dims <= 16, "n_output_dims must be in [1, 16] (fused last layer, fully_fused_mlp.cu:544)");
+	CHECK(in.encoded_width <= 64, "encoded width above 64 is not implemented");
+	in.padded_output_width = 16;
+	in.n_params_mlp = (uint64_t)in.n_neurons * in.encoded_width + (uint64_t)(in.n_hidden_layers - 1) * in.n_neurons * in.n_neurons + (uint64_t)16 * in.n_neurons;
+	in.n_params = in.n_params_mlp + in.n_params_grid;
+	CHECK(in.n_params < (1ull << 32), "more than 2^32 parameters");
+
+	// --- loss: create_loss (src/loss.cu:53-93; default RelativeL2) ---
+	const std::string ltype = jsonmini::lower(loss.string("otype", "RelativeL2"));
+	if (ltype == "l2") in.loss_type = LOSS_L2;
+	else if (ltype == "relativel2") in.loss_type = LOSS_RELATIVE_L2;
+	else FAIL("loss otype '" + ltype + "' is outside the hot path (L2, RelativeL2)");
+
+	// --- optimizer: Adam defaults (optimizers/adam.h:312-326) ---
+	in.learning_rate = 1e-3f; in.beta1 = 0.9f; in.beta2 = 0.999f; in.epsilon = 1e-8f; in.l2_reg = 1e-8f;
+	in.relative_decay = 0.f; in.absolute_decay = 0.f;
+	parse_optimizer(p.get(), opt);
+
+	*out = p.release();
+	API_END
+}
+
+extern "C" void tcnn_b200_plan_destroy(tcnn_b200_plan* plan) { delete plan; }
+
+extern "C" int tcnn_b200_plan_info(const tcnn_b200_plan* plan, tcnn_b200_info* info) {
+	API_BEGIN
+	CHECK(plan && info, "null argument");
+	*info = plan->info;
+	API_END
+}
+
+extern "C" int tcnn_b200_plan_update_optimizer(tcnn_b200_plan* plan, const char* json_utf8) {
+	API_BEGIN
+	CHECK(plan && json_utf8, "null argument");
+	parse_optimizer(plan, jsonmini::parse(json_utf8));
+	API_END
+}
+
+// workspace layout: [encoded B x E fp16][dL_dencoded B x E fp16][dW partials n_ctas x P_mlp fp32][loss partials n_ctas fp32]
+struct Workspace {
+	__half* encoded; __half* dL_denc; float* dw_partials; float* loss_partials;
+};
+static uint32_t mlp_grid_size(const tcnn_b200_plan* p, uint32_t n_tiles, bool train) {
+	const uint32_t per_sm = train ? 2u : 3u;
+	return std::max(1u, std::min(n_tiles, (uint32_t)p->n_sms * per_sm));
+}
+static size_t align256(size_t v) { return (v + 255) / 256 * 256; }
+static Workspace carve(const tcnn_b200_plan* p, uint32_t B, void* ws) {
+	Workspace w;
+	uint8_t* b = (uint8_t*)ws;
+	const size_t act = align256((size_t)B * p->info.encoded_width * 2);
+	const uint32_t max_ctas = (uint32_t)p->n_sms * 3;
+	w.encoded = (__half*)b; b += act;
+	w.dL_denc = (__half*)b; b += act;
+	w.dw_partials = (float*)b; b += align256((size_t)max_ctas * p->info.n_params_mlp * 4);
+	w.loss_partials = (float*)b;
+	return w;
+}
+extern "C" size_t tcnn_b200_workspace_bytes(const tcnn_b200_plan* plan, uint32_t B) {
+	if (!plan) return 0;
+	const size_t act = align256((size_t)B * plan->info.encoded_width * 2);
+	const uint32_t max_ctas = (uint32_t)plan->n_sms * 3;
+	return 2 * act + align256((size_t)max_ctas * plan->info.n_params_mlp * 4) + align256((size_t)max_ctas * 4) + 256;
+}
+
+static void check_batch(uint32_t B) {
+	CHECK(B > 0 && B % 256 == 0, "batch size must be a multiple of 256 (BATCH_SIZE_GRANULARITY, common.h:235), got " + std::to_string(B));
+}
+static void require_device(const tcnn_b200_plan* p) {
+	CHECK(p, "null plan");
+	if (!p->device_scales) {
+		try_device_scales(const_cast<tcnn_b200_plan*>(p));
+		CHECK(p->device_scales, "no CUDA device: libtcnn_b200 has no CPU path");
+	}
+}
+static void launch_check(const char* what) {
+	const cudaError_t e = cudaGetLastError();
+	if (e != cudaSuccess) FAIL(std::string(what) + " launch failed: " + cudaGetErrorString(e));
+}
+
+// ---- init -------------------------------------------------------------------------------------------
+extern "C" int tcnn_b200_init_params(const tcnn_b200_plan* plan, void* stream_, uint64_t seed, int trainer_seeding, float* params_fp32) {
+	API_BEGIN
+	require_device(plan);
+	CHECK(params_fp32, "null params");
+	cudaStream_t stream = (cudaStream_t)stream_;
+	const tcnn_b200_info& in = plan->info;
+	uint64_t initstate = seed;
+	if (trainer_seeding) { // trainer.h:52-55
+		std::seed_seq seq{(uint32_t)seed};
+		uint32_t seeds[2];
+		seq.generate(seeds, seeds + 2);
+		initstate = seeds[0];
+	}
+	// pcg32::seed(initstate, 1)  (pcg32.h:54-60)
+	const uint64_t mult = 0x5851f42d4c957f2dULL;
+	uint64_t state = 0, inc = (1ull << 1) | 1ull;
+	state = state * mult + inc;
+	state += initstate;
+	state = state * mult + inc;
+	uint64_t base = 0;
+	float* dst = params_fp32;
+	const uint32_t W = in.n_neurons;
+	const uint32_t n_mats = in.n_hidden_layers + 1;
+	for (uint32_t k = 0; k < n_mats; ++k) {
+		const uint32_t rows = (k + 1 == n_mats) ? in.padded_output_width : W;
+		const uint32_t cols = (k == 0) ? in.encoded_width : W;
+		const uint32_t n = rows * cols;
+		const float scale = std::sqrt(6.0f / (float)(cols + rows)); // gpu_matrix.h:289 (fan_in = cols, fan_out = rows)
+		init_xavier_kernel<<<(n + 255) / 256, 256, 0, stream>>>(n, state, inc, base, scale, dst);
+		launch_check("init_xavier_kernel");
+		base += n; dst += n;
+	}
+	const uint32_t ng = (uint32_t)in.n_params_grid;
+	const uint32_t n_threads = next_multiple_u32((ng + 3) / 4, 128); // random.h:58-63 + n_blocks_linear (128 threads)
+	init_uniform_kernel<<<(ng + 255) / 256, 256, 0, stream>>>(ng, n_threads, state, inc, base, -1e-4f, 1e-4f, dst);
+	launch_check("init_uniform_kernel");
+	API_END
+}
+
+extern "C" int tcnn_b200_cast_params(void* stream_, uint64_t n, const float* params_fp32, void* params_fp16) {
+	API_BEGIN
+	CHECK(params_fp32 && params_fp16, "null argument");
+	cast_f32_to_f16_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream_>>>(n, params_fp32, (__half*)params_fp16);
+	launch_check("cast_f32_to_f16_kernel");
+	API_END
+}
+
+// ---- grid encoding ------------------------------------------------------------------------------------
+template <template <int, int> class K> struct GridDispatch;
+
+#define GRID_DISPATCH(KERNEL, plan, grid_dim, stream, ...)                                                        \
+	do {                                                                                                          \
+		const uint32_t D_ = (plan)->info.n_input_dims, F_ = (plan)->info.n_features_per_level;                   \
+		if (D_ == 2 && F_ == 2) KERNEL<2, 2><<<grid_dim, 256, 0, stream>>>(__VA_ARGS__);                          \
+		else if (D_ == 2 && F_ == 4) KERNEL<2, 4><<<grid_dim, 256, 0, stream>>>(__VA_ARGS__);                     \
+		else if (D_ == 2 && F_ == 8) KERNEL<2, 8><<<grid_dim, 256, 0, stream>>>(__VA_ARGS__);                     \
+		else if (D_ == 3 && F_ == 2) KERNEL<3, 2><<<grid_dim, 256, 0, stream>>>(__VA_ARGS__);                     \
+		else if (D_ == 3 && F_ == 4) KERNEL<3, 4><<<grid_dim, 256, 0, stream>>>(__VA_ARGS__);                     \
+		else if (D_ == 3 && F_ == 8) KERNEL<3, 8><<<grid_dim, 256, 0, stream>>>(__VA_ARGS__);                     \
+		else if (D_ == 4 && F_ == 2) KERNEL<4, 2><<<grid_dim, 256, 0, stream>>>(__VA_ARGS__);                     \
+		else if (D_ == 4 && F_ == 4) KERNEL<4, 4><<<grid_dim, 256, 0, stream>>>(__VA_ARGS__);                     \
+		else FAIL("unsupported (n_input_dims, n_features_per_level)");                                            \
+	} while (0)
+
+static void encode_forward(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t B, const float* x, const __half* grid, __half* encoded) {
+	const dim3 g((B + 255) / 256, plan->info.encoded_width / 8, 1);
+	GRID_DISPATCH(grid_forward_kernel, plan, g, stream, plan->grid, B, x, grid, encoded);
+	launch_check("grid_forward_kernel");
+}
+static void encode_backward(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t B, const float* x, const __half* dL_denc, __half* grid_grads, int zero_first) {
+	if (zero_first) CUDA_OK(cudaMemsetAsync(grid_grads, 0, plan->info.n_params_grid * 2, stream));
+	const uint32_t n_chunks = (plan->grid.n_features + 7) / 8; // padding chunks carry no gradient
+	const dim3 g((B + 255) / 256, n_chunks, 1);
+	GRID_DISPATCH(grid_backward_kernel, plan, g, stream, plan->grid, B, x, dL_denc, grid_grads);
+	launch_check("grid_backward_kernel");
+}
+
+extern "C" int tcnn_b200_encode_forward(const tcnn_b200_plan* plan, void* stream, uint32_t B, const float* x, const void* grid_params, void* encoded) {
+	API_BEGIN
+	require_device(plan); check_batch(B);
+	CHECK(x && grid_params && encoded, "null argument");
+	encode_forward(plan, (cudaStream_t)stream, B, x, (const __half*)grid_params, (__half*)encoded);
+	API_END
+}
+extern "C" int tcnn_b200_encode_backward(const tcnn_b200_plan* plan, void* stream, uint32_t B, const float* x, const void* dL_denc, void* grid_grads, int zero_first) {
+	API_BEGIN
+	require_device(plan); check_batch(B);
+	CHECK(x && dL_denc && grid_grads, "null argument");
+	encode_backward(plan, (cudaStream_t)stream, B, x, (const __half*)dL_denc, (__half*)grid_grads, zero_first);
+	API_END
+}
+extern "C" int tcnn_b200_grid_indices(const tcnn_b200_plan* plan, void* stream, uint32_t B, const float* x, uint32_t* indices) {
+	API_BEGIN
+	require_device(plan);
+	CHECK(x && indices && B > 0, "bad argument");
+	const dim3 g((B + 255) / 256, plan->info.n_levels, 1);
+	const uint32_t D = plan->info.n_input_dims;
+	if (D == 2) grid_indices_kernel<2><<<g, 256, 0, (cudaStream_t)stream>>>(plan->grid, B, x, indices);
+	else if (D == 3) grid_indices_kernel<3><<<g, 256, 0, (cudaStream_t)stream>>>(plan->grid, B, x, indices);
+	else grid_indices_kernel<4><<<g, 256, 0, (cudaStream_t)stream>>>(plan->grid, B, x, indices);
+	launch_check("grid_indices_kernel");
+	API_END
+}
+
+// ---- MLP ----------------------------------------------------------------------------------------------
+template <int MODE, int H>
+static void launch_mlp_h(const tcnn_b200_plan* plan, cudaStream_t stream, const MlpArgs& a, uint32_t grid) {
+	constexpr bool train = MODE != MODE_INFER;
+	const uint32_t smem = mlp_smem_bytes(H, (int)a.in_width, train);
+	static thread_local uint32_t configured = 0;
+	if (configured < smem) {
+		CUDA_OK(cudaFuncSetAttribute(mlp_kernel<MODE, H>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		configured = smem;
+	}
+	mlp_kernel<MODE, H><<<grid, 128, smem, stream>>>(a);
+	launch_check("mlp_kernel");
+}
+template <int MODE>
+static void launch_mlp(const tcnn_b200_plan* plan, cudaStream_t stream, const MlpArgs& a, uint32_t grid) {
+	switch (a.n_hidden) {
+		case 1: launch_mlp_h<MODE, 1>(plan, stream, a, grid); break;
+		case 2: launch_mlp_h<MODE, 2>(plan, stream, a, grid); break;
+		case 3: launch_mlp_h<MODE, 3>(plan, stream, a, grid); break;
+		case 4: launch_mlp_h<MODE, 4>(plan, stream, a, grid); break;
+		default: FAIL("n_hidden_layers out of range");
+	}
+}
+
+static MlpArgs base_mlp_args(const tcnn_b200_plan* plan, uint32_t B, const __half* input, const __half* params) {
+	MlpArgs a{};
+	a.n_tiles = B / MLP_TILE;
+	a.in_width = plan->info.encoded_width;
+	a.n_hidden = plan->info.n_hidden_layers;
+	a.n_out = plan->info.n_output_dims;
+	a.input = input;
+	a.params = params;
+	a.n_mlp_params = (uint32_t)plan->info.n_params_mlp;
+	a.loss_type = plan->info.loss_type;
+	a.n_total = (float)((uint64_t)B * plan->info.n_output_dims);
+	a.loss_scale = 128.f;
+	return a;
+}
+
+static void mlp_infer(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t B, const __half* input, const __half* params, __half* out_h, float* out_f) {
+	MlpArgs a = base_mlp_args(plan, B, input, params);
+	a.output = out_h;
+	a.output_f32 = out_f;
+	launch_mlp<MODE_INFER>(plan, stream, a, mlp_grid_size(plan, a.n_tiles, false));
+}
+
+static void mlp_finalize(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t n_parts, const Workspace& w, __half* grads, float* loss_out, bool with_loss) {
+	const uint32_t n = (uint32_t)plan->info.n_params_mlp;
+	mlp_finalize_kernel<<<(n + 255) / 256, 256, 0, stream>>>(n, n_parts, w.dw_partials, grads, with_loss ? w.loss_partials : nullptr, loss_out);
+	launch_check("mlp_finalize_kernel");
+}
+
+extern "C" int tcnn_b200_mlp_forward(const tcnn_b200_plan* plan, void* stream, uint32_t B, const void* input, const void* params, void* output) {
+	API_BEGIN
+	require_device(plan); check_batch(B);
+	CHECK(input && params && output, "null argument");
+	mlp_infer(plan, (cudaStream_t)stream, B, (const __half*)input, (const __half*)params, (__half*)output, nullptr);
+	API_END
+}
+
+extern "C" int tcnn_b200_mlp_backward(const tcnn_b200_plan* plan, void* stream_, uint32_t B, const void* input, const void* params,
+	const void* dL_doutput, void* dL_dparams, void* dL_dinput, void* workspace) {
+	API_BEGIN
+	require_device(plan); check_batch(B);
+	CHECK(input && params && dL_doutput, "null argument");
+	CHECK(!dL_dparams || workspace, "workspace required for weight gradients");
+	cudaStream_t stream = (cudaStream_t)stream_;
+	Workspace w{};
+	if (workspace) w = carve(plan, B, workspace);
+	MlpArgs a = base_mlp_args(plan, B, (const __half*)input, (const __half*)params);
+	a.dL_doutput = (const __half*)dL_doutput;
+	a.dL_dinput = (__half*)dL_dinput;
+	a.dW_partials = dL_dparams ? w.dw_partials : nullptr;
+	const uint32_t grid = mlp_grid_size(plan, a.n_tiles, true);
+	launch_mlp<MODE_BACKWARD>(plan, stream, a, grid);
+	if (dL_dparams) mlp_finalize(plan, stream, grid, w, (__half*)dL_dparams, nullptr, false);
+	API_END
+}
+
+// ---- encoding + MLP -------------------------------------------------------------------------------------
+extern "C" int tcnn_b200_inference(const tcnn_b200_plan* plan, void* stream_, uint32_t B, const float* x, const void* params,
+	void* output_fp16, float* output_fp32, void* workspace) {
+	API_BEGIN
+	require_device(plan); check_batch(B);
+	CHECK(x && params && workspace && (output_fp16 || output_fp32), "null argument");
+	cudaStream_t stream = (cudaStream_t)stream_;
+	const Workspace w = carve(plan, B, workspace);
+	const __half* p = (const __half*)params;
+	encode_forward(plan, stream, B, x, p + plan->info.n_params_mlp, w.encoded);
+	mlp_infer(plan, stream, B, w.encoded, p, (__half*)output_fp16, output_fp32);
+	API_END
+}
+
+extern "C" int tcnn_b200_forward(const tcnn_b200_plan* plan, void* stream, uint32_t B, const float* x, const void* params, void* output_fp16, void* workspace) {
+	return tcnn_b200_inference(plan, stream, B, x, params, output_fp16, nullptr, workspace);
+}
+
+extern "C" int tcnn_b200_backward(const tcnn_b200_plan* plan, void* stream_, uint32_t B, const float* x, const void* params,
+	const void* dL_doutput, void* dL_dparams, float* dL_dinput, void* workspace) {
+	API_BEGIN
+	require_device(plan); check_batch(B);
+	CHECK(x && params && dL_doutput && workspace, "null argument");
+	CHECK(dL_dinput == nullptr, "dL_dinput (kernel_grid_backward_input, grid.h:322-349) is not implemented in this round");
+	if (!dL_dparams) return 0;
+	cudaStream_t stream = (cudaStream_t)stream_;
+	const Workspace w = carve(plan, B, workspace);
+	const __half* p = (const __half*)params;
+	__half* g = (__half*)dL_dparams;
+	MlpArgs a = base_mlp_args(plan, B, w.encoded, p); // w.encoded was left by tcnn_b200_forward (the Context)
+	a.dL_doutput = (const __half*)dL_doutput;
+	a.dL_dinput = w.dL_denc;
+	a.dW_partials = w.dw_partials;
+	const uint32_t grid = mlp_grid_size(plan, a.n_tiles, true);
+	launch_mlp<MODE_BACKWARD>(plan, stream, a, grid);
+	mlp_finalize(plan, stream, grid, w, g, nullptr, false);
+	encode_backward(plan, stream, B, x, w.dL_denc, g + plan->info.n_params_mlp, /*zero_first=*/1);
+	API_END
+}
+
+extern "C" int tcnn_b200_training_fwd_bwd(const tcnn_b200_plan* plan, void* stream_, uint32_t B, const float* x, const float* target,
+	const void* params, void* grads, float loss_scale, int zero_grid_grads, float* loss_out, void* output_fp16, void* workspace) {
+	API_BEGIN
+	require_device(plan); check_batch(B);
+	CHECK(x && target && params && grads && workspace, "null argument");
+	cudaStream_t stream = (cudaStream_t)stream_;
+	const Workspace w = carve(plan, B, workspace);
+	const __half* p = (const __half*)params;
+	__half* g = (__half*)grads;
+	encode_forward(plan, stream, B, x, p + plan->info.n_params_mlp, w.encoded);
+	MlpArgs a = base_mlp_args(plan, B, w.encoded, p);
+	a.target = target;
+	a.output = (__half*)output_fp16;
+	a.dL_dinput = w.dL_denc;
+	a.dW_partials = w.dw_partials;
+	a.loss_partials = w.loss_partials;
+	a.loss_scale = loss_scale;
+	const uint32_t grid = mlp_grid_size(plan, a.n_tiles, true);
+	launch_mlp<MODE_TRAIN>(plan, stream, a, grid);
+	mlp_finalize(plan, stream, grid, w, g, loss_out, loss_out != nullptr);
+	encode_backward(plan, stream, B, x, w.dL_denc, g + plan->info.n_params_mlp, zero_grid_grads);
+	API_END
+}
+
+// ---- optimizer --------------------------------------------------------------------------------------------
+extern "C" int tcnn_b200_adam_step(const tcnn_b200_plan* plan, void* stream, float grad_divisor, uint32_t adam_step_count,
+	float* params_fp32, void* params_fp16, void* grads_fp16, float* first_moments, float* second_moments, uint32_t* param_steps, int zero_grid_grads) {
+	API_BEGIN
+	require_device(plan);
+	CHECK(params_fp32 && params_fp16 && grads_fp16 && first_moments && second_moments && param_steps, "null argument");
+	const tcnn_b200_info& in = plan->info;
+	AdamArgs a{};
+	a.n = (uint32_t)in.n_params;
+	a.n_matrix = (uint32_t)in.n_params_mlp;
+	a.loss_scale = grad_divisor;
+	a.learning_rate = in.learning_rate; a.beta1 = in.beta1; a.beta2 = in.beta2; a.epsilon = in.epsilon; a.l2_reg = in.l2_reg;
+	a.relative_decay = in.relative_decay; a.absolute_decay = in.absolute_decay;
+	a.lower_lr_bound = 0.f; a.upper_lr_bound = std::numeric_limits<float>::max();
+	if (plan->adabound) { // optimizers/adam.h:156-160
+		a.lower_lr_bound = 0.1f - 0.1f / ((1 - in.beta2) * (float)adam_step_count + 1);
+		a.upper_lr_bound = 0.1f + 0.1f / ((1 - in.beta2) * (float)adam_step_count);
+	}
+	a.weight_clip = plan->weight_clip;
+	a.non_matrix_lr_factor = plan->non_matrix_lr_factor;
+	a.zero_grads = zero_grid_grads;
+	a.master = params_fp32; a.params = (__half*)params_fp16; a.grads = (__half*)grads_fp16;
+	a.m = first_moments; a.v = second_moments; a.steps = param_steps;
+	const uint32_t n_threads = (a.n + 3) / 4;
+	adam_kernel<<<(n_threads + 255) / 256, 256, 0, (cudaStream_t)stream>>>(a);
+	launch_check("adam_kernel");
+	API_END
+}

@@ -1,0 +1,173 @@
+"""PyTorch module surface of the reference's bindings (bindings/torch/tinycudann/modules.py:162-329), on top of
+libtcnn_b200.so.  Same constructor arguments, same `.params` / `.n_output_dims` / `.dtype` / `.loss_scale`
+attributes, same batch padding to 256 and output slicing (modules.py:176-192), same loss-scaling convention in the
+autograd function (modules.py:91-130).  PyTorch is used for device memory and streams only; all compute goes
+through the C ABI."""
+from __future__ import annotations
+
+import json
+import warnings
+
+import torch
+
+from . import _lib
+from ._lib import check, ptr
+
+
+def _stream_ptr():
+    return _lib.C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class NativeModule:
+    """Plays the role of the pybind11 `Module` (bindings/torch/tinycudann/bindings.cpp:60-262) over a C-ABI plan."""
+
+    def __init__(self, n_input_dims: int, n_output_dims: int, config: dict):
+        self.lib = _lib.lib()
+        self.config = config
+        handle = _lib.C.c_void_p()
+        check(self.lib.tcnn_b200_plan_create(json.dumps(config).encode(), n_input_dims, n_output_dims, _lib.C.byref(handle)))
+        self.handle = handle
+        self.info = _lib.Info()
+        check(self.lib.tcnn_b200_plan_info(self.handle, _lib.C.byref(self.info)))
+        self._ws = {}
+
+    def __del__(self):
+        try:
+            if getattr(self, "handle", None):
+                self.lib.tcnn_b200_plan_destroy(self.handle)
+                self.handle = None
+        except Exception:
+            pass
+
+    def refresh_info(self):
+        check(self.lib.tcnn_b200_plan_info(self.handle, _lib.C.byref(self.info)))
+
+    # --- queries (cpp_api.h:100-115) ---
+    def n_params(self) -> int:
+        return int(self.info.n_params)
+
+    def n_output_dims(self) -> int:
+        return int(self.info.padded_output_width)
+
+    def hyperparams(self) -> dict:
+        return self.config
+
+    def workspace(self, batch_size: int, device, fresh: bool = False) -> torch.Tensor:
+        n = int(self.lib.tcnn_b200_workspace_bytes(self.handle, batch_size))
+        if fresh:
+            return torch.empty(n, dtype=torch.uint8, device=device)
+        key = (batch_size, str(device))
+        if key not in self._ws:
+            self._ws[key] = torch.empty(n, dtype=torch.uint8, device=device)
+        return self._ws[key]
+
+    def initial_params(self, seed: int, device="cuda", trainer_seeding: bool = False) -> torch.Tensor:
+        p = torch.empty(self.n_params(), dtype=torch.float32, device=device)
+        check(self.lib.tcnn_b200_init_params(self.handle, _stream_ptr(), seed, 1 if trainer_seeding else 0, ptr(p)))
+        return p
+
+    # --- compute ---
+    def fwd(self, x: torch.Tensor, params: torch.Tensor, need_ctx: bool):
+        B = x.shape[0]
+        out = torch.empty(B, self.n_output_dims(), dtype=torch.half, device=x.device)
+        if need_ctx:
+            ws = self.workspace(B, x.device, fresh=True)  # owned by the autograd context, like the reference's Context
+            check(self.lib.tcnn_b200_forward(self.handle, _stream_ptr(), B, ptr(x), ptr(params), ptr(out), ptr(ws)))
+            return ws, out
+        ws = self.workspace(B, x.device)
+        check(self.lib.tcnn_b200_inference(self.handle, _stream_ptr(), B, ptr(x), ptr(params), ptr(out), None, ptr(ws)))
+        return None, out
+
+    def bwd(self, ws, x, params, doutput, want_params_grad: bool):
+        B = x.shape[0]
+        if not want_params_grad:
+            return None
+        g = torch.empty(self.n_params(), dtype=torch.half, device=x.device)
+        check(self.lib.tcnn_b200_backward(self.handle, _stream_ptr(), B, ptr(x), ptr(params), ptr(doutput), ptr(g), None, ptr(ws)))
+        return g
+
+
+class _module_function(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, native, x, params, loss_scale):
+        ctx.set_materialize_grads(False)
+        need_ctx = torch.is_grad_enabled() and (params.requires_grad or x.requires_grad)
+        ws, output = native.fwd(x, params, need_ctx)
+        ctx.save_for_backward(x, params)
+        ctx.native, ctx.ws, ctx.loss_scale = native, ws, loss_scale
+        return output
+
+    @staticmethod
+    def backward(ctx, doutput):
+        if doutput is None:
+            return None, None, None, None
+        x, params = ctx.saved_tensors
+        if ctx.needs_input_grad[1]:
+            raise RuntimeError("dL/dinput of the grid encoding (kernel_grid_backward_input) is not implemented in tcnn_b200 yet")
+        with torch.no_grad():
+            scaled = (doutput.to(torch.float) * ctx.loss_scale).to(torch.half).contiguous()
+            g = ctx.native.bwd(ctx.ws, x, params, scaled, ctx.needs_input_grad[2])
+            g = None if g is None else g / ctx.loss_scale
+        return None, None, g, None
+
+
+class Module(torch.nn.Module):
+    def __init__(self, seed=1337):
+        super().__init__()
+        self.native_tcnn_module = self._native_tcnn_module()
+        self.dtype = torch.half
+        self.seed = seed
+        initial_params = self.native_tcnn_module.initial_params(seed)
+        self.params = torch.nn.Parameter(initial_params, requires_grad=True)
+        self.loss_scale = 128.0  # default_loss_scale(Fp16), cpp_api.h / common.h:229-233
+
+    def forward(self, x):
+        if not x.is_cuda:
+            warnings.warn("input must be a CUDA tensor, but isn't. This indicates suboptimal performance.")
+            x = x.cuda()
+        batch_size = x.shape[0]
+        g = int(_lib.lib().tcnn_b200_batch_size_granularity())
+        padded = (batch_size + g - 1) // g * g
+        x_padded = x if batch_size == padded else torch.nn.functional.pad(x, [0, 0, 0, padded - batch_size])
+        output = _module_function.apply(
+            self.native_tcnn_module,
+            x_padded.to(torch.float).contiguous(),
+            self.params.to(torch.half).contiguous(),
+            self.loss_scale,
+        )
+        return output[:batch_size, : self.n_output_dims]
+
+    def __getstate__(self):
+        state = self.__dict__.copy()
+        del state["native_tcnn_module"]
+        return state
+
+    def __setstate__(self, state):
+        self.__dict__.update(state)
+        self.native_tcnn_module = self._native_tcnn_module()
+
+    def extra_repr(self):
+        return f"n_input_dims={self.n_input_dims}, n_output_dims={self.n_output_dims}, seed={self.seed}, dtype={self.dtype}, hyperparams={self.native_tcnn_module.hyperparams()}"
+
+
+class NetworkWithInputEncoding(Module):
+    """Input encoding followed by a neural network (modules.py:209-247 of the reference).  Supported here:
+    HashGrid encoding + FullyFusedMLP (64 neurons, ReLU, linear output)."""
+
+    def __init__(self, n_input_dims, n_output_dims, encoding_config, network_config, seed=1337):
+        self.n_input_dims = n_input_dims
+        self.n_output_dims = n_output_dims
+        self.encoding_config = encoding_config
+        self.network_config = network_config
+        super().__init__(seed=seed)
+
+    def _native_tcnn_module(self):
+        return NativeModule(self.n_input_dims, self.n_output_dims, {"encoding": self.encoding_config, "network": self.network_config})
+
+
+def free_temporary_memory():
+    """tcnn.free_temporary_memory (modules.py:77-81): the C ABI owns no temporaries; workspaces are torch tensors."""
+    import gc
+
+    gc.collect()
+    torch.cuda.empty_cache()

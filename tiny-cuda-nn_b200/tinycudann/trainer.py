@@ -1,0 +1,117 @@
+"""Python mirror of the reference's C++ training facade for the hot path:
+`create_from_config` (include/tiny-cuda-nn/config.h:46-63) and `Trainer` (include/tiny-cuda-nn/trainer.h:47-361).
+
+The trainer owns the parameter buffer in the reference's layout (one allocation: fp32 master | fp16 params |
+fp16 gradients, trainer.h:75,322-336; MLP weights first, grid tables second), the Adam state
+(optimizers/adam.h:128-148), and drives the C-ABI kernels.  Data-parallel training (one process per GPU) adds exactly
+one collective per step: an all-reduce of the fp16 gradient buffer, with 1/world_size folded into the Adam kernel.
+"""
+from __future__ import annotations
+
+import json
+from dataclasses import dataclass
+
+import torch
+
+from . import _lib
+from ._lib import check, ptr
+from .modules import NativeModule, _stream_ptr
+
+LOSS_SCALE = 128.0  # default_loss_scale<__half>(), common.h:229-233; trainer.h:174
+
+
+class Trainer:
+    def __init__(self, native: NativeModule, seed: int = 1337, device="cuda", process_group=None):
+        self.native = native
+        self.lib = native.lib
+        self.device = torch.device(device)
+        self.info = native.info
+        P = int(self.info.n_params)
+        self.n_params = P
+        # trainer.h:75: [fp32 master (4P) | fp16 params (2P) | fp16 grads (2P)]
+        self.params_buffer = torch.zeros(8 * P, dtype=torch.uint8, device=self.device)
+        self.params_full_precision = self.params_buffer[: 4 * P].view(torch.float32)
+        self.params = self.params_buffer[4 * P : 6 * P].view(torch.half)
+        self.param_gradients = self.params_buffer[6 * P : 8 * P].view(torch.half)
+        # AdamOptimizer::allocate (adam.h:128-148)
+        self.first_moments = torch.zeros(P, dtype=torch.float32, device=self.device)
+        self.second_moments = torch.zeros(P, dtype=torch.float32, device=self.device)
+        self.param_steps = torch.zeros(P, dtype=torch.int32, device=self.device)
+        self.current_step = 0
+        self.loss_value = torch.zeros(1, dtype=torch.float32, device=self.device)
+        self._grid_grads_clean = True  # grid gradient region is all zero (after init / after an optimizer step)
+        self.process_group = process_group
+        self.world_size = 1
+        if process_group is not None or (torch.distributed.is_available() and torch.distributed.is_initialized()):
+            self.world_size = torch.distributed.get_world_size(process_group)
+        self.initialize_params(seed)
+
+    # trainer.h:68-87
+    def initialize_params(self, seed: int = 1337):
+        with torch.cuda.device(self.device):
+            check(self.lib.tcnn_b200_init_params(self.native.handle, _stream_ptr(), seed, 1, ptr(self.params_full_precision)))
+            check(self.lib.tcnn_b200_cast_params(_stream_ptr(), self.n_params, ptr(self.params_full_precision), ptr(self.params)))
+            self.param_gradients.zero_()
+            self.first_moments.zero_(); self.second_moments.zero_(); self.param_steps.zero_()
+            self.current_step = 0
+            self._grid_grads_clean = True
+            torch.cuda.synchronize(self.device)
+
+    def set_params_full_precision(self, params_fp32: torch.Tensor):
+        self.params_full_precision.copy_(params_fp32.to(self.device, torch.float32))
+        check(self.lib.tcnn_b200_cast_params(_stream_ptr(), self.n_params, ptr(self.params_full_precision), ptr(self.params)))
+
+    # trainer.h:163-190.  input [B, D] fp32, target [B, O] fp32 (== GPUMatrix CM [D x B] / [O x B]).
+    def training_step(self, input: torch.Tensor, target: torch.Tensor, run_optimizer: bool = True, output: torch.Tensor | None = None):
+        B = input.shape[0]
+        ws = self.native.workspace(B, self.device)
+        check(self.lib.tcnn_b200_training_fwd_bwd(
+            self.native.handle, _stream_ptr(), B, ptr(input), ptr(target), ptr(self.params), ptr(self.param_gradients),
+            LOSS_SCALE, 0 if self._grid_grads_clean else 1, ptr(self.loss_value), ptr(output), ptr(ws)))
+        self._grid_grads_clean = False
+        if self.world_size > 1:
+            torch.distributed.all_reduce(self.param_gradients, group=self.process_group)
+            torch.distributed.all_reduce(self.loss_value, group=self.process_group)
+        if run_optimizer:
+            self.optimizer_step(LOSS_SCALE)
+        return self
+
+    # trainer.h:155-157 + adam.h:150-188
+    def optimizer_step(self, loss_scale: float = LOSS_SCALE):
+        self.current_step += 1
+        check(self.lib.tcnn_b200_adam_step(
+            self.native.handle, _stream_ptr(), loss_scale * self.world_size, self.current_step,
+            ptr(self.params_full_precision), ptr(self.params), ptr(self.param_gradients),
+            ptr(self.first_moments), ptr(self.second_moments), ptr(self.param_steps), 1))
+        self._grid_grads_clean = True
+
+    # trainer.h:205-207 (synchronises, like the reference's reduce_sum + D2H)
+    def loss(self) -> float:
+        return float(self.loss_value.item()) / self.world_size
+
+    def update_hyperparams(self, params: dict):
+        check(self.lib.tcnn_b200_plan_update_optimizer(self.native.handle, json.dumps(params).encode()))
+        self.native.refresh_info()
+
+    # Network::inference (object.h:147-176): fp32 [B, O] output
+    def inference(self, input: torch.Tensor, output: torch.Tensor | None = None) -> torch.Tensor:
+        B = input.shape[0]
+        if output is None:
+            output = torch.empty(B, int(self.info.n_output_dims), dtype=torch.float32, device=self.device)
+        ws = self.native.workspace(B, self.device)
+        check(self.lib.tcnn_b200_inference(self.native.handle, _stream_ptr(), B, ptr(input), ptr(self.params), None, ptr(output), ptr(ws)))
+        return output
+
+
+@dataclass
+class TrainableModel:
+    """config.h:46-51: {loss, optimizer, network, trainer}; loss and optimizer live inside the plan here."""
+    network: NativeModule
+    trainer: Trainer
+
+
+def create_from_config(n_input_dims: int, n_output_dims: int, config: dict, seed: int = 1337, device="cuda", process_group=None) -> TrainableModel:
+    """config.h:53-63.  config = {"loss": {...}, "optimizer": {...}, "encoding": {...}, "network": {...}}."""
+    with torch.cuda.device(device):
+        native = NativeModule(n_input_dims, n_output_dims, config)
+        return TrainableModel(network=native, trainer=Trainer(native, seed=seed, device=device, process_group=process_group))
