@@ -76,8 +76,9 @@ int tcnn_b200_cast_params(void* stream, uint64_t n, const float* params_fp32, vo
 /* GridEncoding forward, kernel_grid (encodings/grid.h:48-212, 732-807).  encoded: fp16 [B][encoded_width]. */
 int tcnn_b200_encode_forward(const tcnn_b200_plan* plan, void* stream, uint32_t batch_size, const float* x, const void* grid_params_fp16, void* encoded_fp16);
 /* kernel_grid_backward (grid.h:214-320, 809-900).  Adds into grid_grads_fp16 [n_params_grid]; zero_first != 0
- * clears it first (the reference's cudaMemsetAsync, grid.h:857-859). */
-int tcnn_b200_encode_backward(const tcnn_b200_plan* plan, void* stream, uint32_t batch_size, const float* x, const void* dL_dencoded_fp16, void* grid_grads_fp16, int zero_first);
+ * clears it first (the reference's cudaMemsetAsync, grid.h:857-859).  workspace may be NULL (then the coarse levels
+ * are scattered without the contention-avoiding private copies). */
+int tcnn_b200_encode_backward(const tcnn_b200_plan* plan, void* stream, uint32_t batch_size, const float* x, const void* dL_dencoded_fp16, void* grid_grads_fp16, int zero_first, void* workspace);
 /* Parity probe: entry index of every interpolation corner, uint32 [n_levels][B][2^D], computed by the same device
  * functions as the two kernels above (grid_index, common_device.h:690-707). */
 int tcnn_b200_grid_indices(const tcnn_b200_plan* plan, void* stream, uint32_t batch_size, const float* x, uint32_t* indices);
@@ -117,6 +118,12 @@ int tcnn_b200_training_fwd_bwd(const tcnn_b200_plan* plan, void* stream, uint32_
 int tcnn_b200_adam_step(const tcnn_b200_plan* plan, void* stream, float grad_divisor, uint32_t adam_step_count,
                         float* params_fp32, void* params_fp16, void* grads_fp16, float* first_moments, float* second_moments,
                         uint32_t* param_steps, int zero_grid_grads);
+
+/* Per-kernel device timing for bench.py's roofline line (no reference counterpart): when enabled, every kernel launch
+ * of this plan is bracketed by CUDA events on its launch stream.  profile_read synchronises them and returns the summed
+ * milliseconds and launch counts for kind 0..4 = grid forward, MLP, MLP finalize, grid backward (+memset), Adam. */
+int tcnn_b200_profile_enable(tcnn_b200_plan* plan, int enable);
+int tcnn_b200_profile_read(tcnn_b200_plan* plan, float* ms_sum, uint32_t* count, uint32_t n_kinds);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,122 @@
+"""CPU: the C-ABI library loads, exports every symbol include/tcnn_b200.h declares, resolves configs exactly like the
+reference's factories, reports errors through tcnn_b200_last_error, and refuses to compute without a GPU."""
+import ctypes as C
+import json
+import os
+import re
+
+import numpy as np
+import pytest
+
+from tests import common
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    import __graft_entry__ as ge
+    ge.build_library()
+    from tinycudann import _lib
+    return _lib.lib()
+
+
+def _plan(lib, cfg, n_in, n_out):
+    from tinycudann import _lib
+    h = C.c_void_p()
+    rc = lib.tcnn_b200_plan_create(json.dumps(cfg).encode(), n_in, n_out, C.byref(h))
+    return rc, h
+
+
+def test_exports_every_declared_symbol(lib):
+    from tinycudann import _lib
+    header = open(os.path.join(ROOT, "include", "tcnn_b200.h")).read()
+    declared = sorted(set(re.findall(r"\b(tcnn_b200_[a-z0-9_]+)\s*\(", header)))
+    assert len(declared) >= 20
+    for name in declared:
+        assert hasattr(lib, name), f"{name} declared in tcnn_b200.h but not exported"
+    assert set(declared) == set(_lib.exported_symbols()), "ctypes binding out of sync with the header"
+    assert lib.tcnn_b200_arch() == b"sm_100a"
+    assert lib.tcnn_b200_batch_size_granularity() == 256
+
+
+@pytest.mark.parametrize("cfg,n_in,n_out,n_grid", [
+    (common.CONFIG_1, 2, 3, 11184640),
+    (common.CONFIG_SHIPPED, 2, 3, 708368),
+    (common.CONFIG_NERF, 3, 4, 12196240),
+])
+def test_plan_sizes_match_reference_tables(lib, cfg, n_in, n_out, n_grid):
+    from tinycudann import _lib
+    rc, h = _plan(lib, cfg, n_in, n_out)
+    assert rc == 0, lib.tcnn_b200_last_error()
+    info = _lib.Info()
+    assert lib.tcnn_b200_plan_info(h, C.byref(info)) == 0
+    assert info.n_params_grid == n_grid
+    assert info.n_params_mlp == 64 * 32 + 64 * 64 + 16 * 64
+    assert info.encoded_width == 32 and info.padded_output_width == 16
+    g, m = common.oracle_configs(cfg, n_in, n_out)
+    assert np.array_equal(np.array(info.level_offset[:17], dtype=np.uint32), g.offsets)
+    assert lib.tcnn_b200_workspace_bytes(h, 1 << 18) > 2 * (1 << 18) * 32 * 2
+    lib.tcnn_b200_plan_destroy(h)
+
+
+def test_defaults_and_case_insensitive_otype(lib):
+    from tinycudann import _lib
+    cfg = {"encoding": {"otype": "hashgrid"}, "network": {"otype": "FULLYFUSEDMLP", "n_neurons": 64, "n_hidden_layers": 2}}
+    rc, h = _plan(lib, cfg, 3, 1)
+    assert rc == 0, lib.tcnn_b200_last_error()
+    info = _lib.Info()
+    lib.tcnn_b200_plan_info(h, C.byref(info))
+    assert (info.n_levels, info.n_features_per_level, info.log2_hashmap_size, info.base_resolution) == (16, 2, 19, 16)
+    assert info.per_level_scale == 2.0 and info.loss_type == 1  # default loss is RelativeL2 (src/loss.cu:86)
+    assert abs(info.learning_rate - 1e-3) < 1e-9 and abs(info.beta2 - 0.999) < 1e-7 and abs(info.epsilon - 1e-8) < 1e-12
+    assert lib.tcnn_b200_plan_update_optimizer(h, json.dumps({"learning_rate": 0.01, "beta2": 0.99}).encode()) == 0
+    lib.tcnn_b200_plan_info(h, C.byref(info))
+    assert abs(info.learning_rate - 0.01) < 1e-8 and abs(info.beta2 - 0.99) < 1e-7
+    lib.tcnn_b200_plan_destroy(h)
+
+
+@pytest.mark.parametrize("patch,msg", [
+    ({"encoding": {"otype": "Frequency"}}, "outside the hot path"),
+    ({"network": {"otype": "CutlassMLP"}}, "outside the hot path"),
+    ({"network": {"otype": "FullyFusedMLP", "n_neurons": 48}}, "n_neurons"),
+    ({"encoding": {"otype": "HashGrid", "n_levels": 4, "n_features": 8}}, "simultaneously"),
+    ({"loss": {"otype": "CrossEntropy"}}, "outside the hot path"),
+    ({"optimizer": {"otype": "Shampoo"}}, "outside the hot path"),
+])
+def test_error_reporting(lib, patch, msg):
+    cfg = json.loads(json.dumps(common.CONFIG_1))
+    cfg.update(patch)
+    rc, _ = _plan(lib, cfg, 2, 3)
+    assert rc != 0
+    assert msg in lib.tcnn_b200_last_error().decode()
+
+
+def test_malformed_json(lib):
+    h = C.c_void_p()
+    assert lib.tcnn_b200_plan_create(b'{"encoding": {', 2, 3, C.byref(h)) != 0
+    assert b"json" in lib.tcnn_b200_last_error()
+
+
+def test_no_cpu_fallback(lib):
+    """Without a CUDA device every compute entry point must fail loudly (the product has no CPU path)."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present; covered by the gpu tests")
+    rc, h = _plan(lib, common.CONFIG_1, 2, 3)
+    assert rc == 0
+    buf = (C.c_float * 1024)()
+    rc = lib.tcnn_b200_encode_forward(h, None, 256, buf, buf, buf)
+    assert rc != 0 and b"no CUDA device" in lib.tcnn_b200_last_error()
+    rc = lib.tcnn_b200_adam_step(h, None, 128.0, 1, buf, buf, buf, buf, buf, buf, 1)
+    assert rc != 0
+    lib.tcnn_b200_plan_destroy(h)
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, "tiny-cuda-nn_b200")
+    for d, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(d, f), errors="ignore").read()
+                assert not re.search(r"^\s*(from|import)\s+oracle|#include\s+[\"<][^\n]*oracle", src, re.M), f

@@ -1,0 +1,342 @@
+"""GPU parity tests (run with -m gpu on a B200): every kernel through the C ABI against the CPU oracle on seeded
+inputs, and against the golden dumps of the reference's own CUDA build (tests/golden/*.npz).
+
+Tolerances (BASELINE.json north_star): grid/hash indices bit-exact; encoded features <= 1e-3 relative; MLP outputs
+and parameter gradients <= 1e-2 relative L2 (the reference accumulates in fp16, we in fp32).  Grid-table gradients are
+compared at 8e-2 against the reference because a handful of ReLU-mask flips between fp16- and fp32-accumulated
+activations dominate their difference (DESIGN.md "Parity"); against the oracle (same accumulation) they match to 2e-3."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+from oracle import tcnn_oracle as O  # noqa: E402
+from tests import common  # noqa: E402
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+CASES = {
+    "cfg1_2d_T19": (common.CONFIG_1, 2, 3),
+    "shipped_2d_T15": (common.CONFIG_SHIPPED, 2, 3),
+    "nerf_3d_T19": (common.CONFIG_NERF, 3, 4),
+    "f4_3d_T14": (common.CONFIG_F4, 3, 3),
+}
+
+
+@pytest.fixture(scope="module")
+def dev():
+    if not torch.cuda.is_available():
+        pytest.fail("no CUDA device: the gpu-marked tests need a B200 (there is no CPU fallback)")
+    return torch.device("cuda:0")
+
+
+def S():
+    from tinycudann import _lib
+    return _lib.C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class Ctx:
+    def __init__(self, name, dev):
+        import tinycudann as tcnn
+        self.cfg, self.n_in, self.n_out = CASES[name]
+        self.native = tcnn.NativeModule(self.n_in, self.n_out, self.cfg)
+        self.info = self.native.info
+        self.lib = self.native.lib
+        scales = np.array(self.info.level_scale[: self.info.n_levels], dtype=np.float32)
+        self.g, self.m = common.oracle_configs(self.cfg, self.n_in, self.n_out, scales=scales)
+        self.golden = np.load(os.path.join(GOLDEN, name + ".npz"))
+        self.dev = dev
+
+
+@pytest.fixture(scope="module", params=sorted(CASES))
+def ctx(request, dev):
+    return Ctx(request.param, dev)
+
+
+def test_level_table_matches_reference(ctx):
+    z = ctx.golden
+    L = ctx.info.n_levels
+    assert np.array_equal(np.array(ctx.info.level_scale[:L], dtype=np.float32), z["level_scale"])  # CUDA exp2f on both sides
+    assert np.array_equal(np.array(ctx.info.level_resolution[:L], dtype=np.uint32), z["level_res"])
+    assert np.array_equal(np.diff(np.array(ctx.info.level_offset[: L + 1], dtype=np.int64)), z["level_size"])
+    assert ctx.info.n_params == int(z["n_params"])
+
+
+def test_init_params_bit_exact(ctx):
+    from tinycudann._lib import check, ptr
+    p = ctx.native.initial_params(1337, ctx.dev, trainer_seeding=True).cpu().numpy()
+    z = ctx.golden
+    assert np.array_equal(p[: ctx.m.n_params], z["params_init_mlp"])
+    assert np.array_equal(p[::997], z["params_init_sample"])
+    assert np.array_equal(p, O.init_params(ctx.m, ctx.g, 1337, True))
+
+
+def test_grid_indices_bit_exact(ctx):
+    from tinycudann._lib import check, ptr
+    z = ctx.golden
+    B = int(z["B"])
+    x_np, _ = common.synth_inputs(B, ctx.n_in, ctx.n_out, seed=1)
+    x = torch.from_numpy(x_np).to(ctx.dev)
+    L, NC = ctx.info.n_levels, 1 << ctx.n_in
+    out = torch.empty(L * B * NC, dtype=torch.int32, device=ctx.dev)
+    check(ctx.lib.tcnn_b200_grid_indices(ctx.native.handle, S(), B, ptr(x), ptr(out)))
+    got = out.cpu().numpy().view(np.uint32).reshape(L, B, NC)
+    assert np.array_equal(got, z["indices"])  # reference's own __device__ grid_index
+    for l in range(L):
+        assert np.array_equal(got[l], O.grid_corners(ctx.g, x_np, l)[0])
+
+
+def test_edge_coordinates_indices(ctx):
+    """Negative, >= 1 and exactly-integer coordinates: (uint32)(int)floorf wrap and dense-level wraparound."""
+    from tinycudann._lib import check, ptr
+    rng = np.random.default_rng(3)
+    x_np = rng.uniform(-1.5, 2.5, (256, ctx.n_in)).astype(np.float32)
+    x_np[:8] = 0.0; x_np[8:16] = 1.0; x_np[16:24] = -0.0; x_np[24:32] = 0.5; x_np[32:40] = np.float32(1.0) - np.float32(2 ** -24)
+    x = torch.from_numpy(x_np).to(ctx.dev)
+    L, NC = ctx.info.n_levels, 1 << ctx.n_in
+    out = torch.empty(L * 256 * NC, dtype=torch.int32, device=ctx.dev)
+    check(ctx.lib.tcnn_b200_grid_indices(ctx.native.handle, S(), 256, ptr(x), ptr(out)))
+    got = out.cpu().numpy().view(np.uint32).reshape(L, 256, NC)
+    for l in range(L):
+        assert np.array_equal(got[l], O.grid_corners(ctx.g, x_np, l)[0]), f"level {l}"
+
+
+def test_encode_forward(ctx):
+    from tinycudann._lib import check, ptr
+    z = ctx.golden
+    B = int(z["B"])
+    x_np, _ = common.synth_inputs(B, ctx.n_in, ctx.n_out, seed=1)
+    p16 = O.init_params(ctx.m, ctx.g, 1337, True).astype(np.float16)
+    x = torch.from_numpy(x_np).to(ctx.dev)
+    table = torch.from_numpy(p16[ctx.m.n_params:]).to(ctx.dev)
+    enc = torch.empty(B, ctx.info.encoded_width, dtype=torch.half, device=ctx.dev)
+    check(ctx.lib.tcnn_b200_encode_forward(ctx.native.handle, S(), B, ptr(x), ptr(table), ptr(enc)))
+    got = enc.cpu().numpy()
+    nf = ctx.g.n_features
+    ref = z["encoded_soa"].T  # reference output is SoA [E x B]
+    assert np.array_equal(got[:, :nf].view(np.uint16), ref[:, :nf].view(np.uint16)), "encoded features differ from the reference build"
+    assert not got[:, nf:].any()
+    assert np.array_equal(got[:, :nf].view(np.uint16), O.grid_forward(ctx.g, x_np, p16[ctx.m.n_params:]).view(np.uint16))
+
+
+def _random_case(ctx, B, seed):
+    rng = np.random.default_rng(seed)
+    x_np, t_np = common.synth_inputs(B, ctx.n_in, ctx.n_out, seed=seed)
+    p32 = O.init_params(ctx.m, ctx.g, 1337, True)
+    p32[ctx.m.n_params:] = rng.uniform(-0.5, 0.5, ctx.g.n_params).astype(np.float32)  # well-conditioned features
+    return x_np, t_np, p32.astype(np.float16), rng
+
+
+def test_mlp_forward_backward_vs_oracle(ctx):
+    from tinycudann._lib import check, ptr
+    B = 512
+    x_np, _, p16_np, rng = _random_case(ctx, B, 11)
+    enc_np = np.zeros((B, ctx.m.n_input), np.float16)
+    enc_np[:, : ctx.g.n_features] = O.grid_forward(ctx.g, x_np, p16_np[ctx.m.n_params:])
+    enc, p16 = torch.from_numpy(enc_np).to(ctx.dev), torch.from_numpy(p16_np).to(ctx.dev)
+    out = torch.empty(B, 16, dtype=torch.half, device=ctx.dev)
+    check(ctx.lib.tcnn_b200_mlp_forward(ctx.native.handle, S(), B, ptr(enc), ptr(p16), ptr(out)))
+    y, hidden = O.mlp_forward(ctx.m, p16_np[: ctx.m.n_params], enc_np)
+    assert common.rel_l2(out.cpu().numpy(), y) < 1e-3
+    dy_np = (rng.standard_normal((B, 16)) * 0.1).astype(np.float16)
+    dy_np[:, ctx.n_out:] = 0
+    dy = torch.from_numpy(dy_np).to(ctx.dev)
+    ws = ctx.native.workspace(B, ctx.dev)
+    gp = torch.empty(ctx.m.n_params, dtype=torch.half, device=ctx.dev)
+    dx = torch.empty(B, ctx.info.encoded_width, dtype=torch.half, device=ctx.dev)
+    check(ctx.lib.tcnn_b200_mlp_backward(ctx.native.handle, S(), B, ptr(enc), ptr(p16), ptr(dy), ptr(gp), ptr(dx), ptr(ws)))
+    dW, dx_ref = O.mlp_backward(ctx.m, p16_np[: ctx.m.n_params], enc_np, hidden, dy_np)
+    assert common.rel_l2(dx.cpu().numpy(), dx_ref) < 2e-3
+    got = gp.cpu().numpy().astype(np.float64)
+    pos = 0
+    for (r, c) in ctx.m.shapes():
+        assert common.rel_l2(got[pos:pos + r * c], dW[pos:pos + r * c]) < 2e-3, f"dW {r}x{c}"
+        pos += r * c
+
+
+@pytest.mark.parametrize("B", [1024, 1 << 14])
+def test_training_step_vs_oracle(ctx, B):
+    """B = 2^14 switches the coarse levels to the replicated scatter path."""
+    from tinycudann._lib import check, ptr
+    x_np, t_np, p16_np, _ = _random_case(ctx, B, 5)
+    x, t, p16 = (torch.from_numpy(a).to(ctx.dev) for a in (x_np, t_np, p16_np))
+    ws = ctx.native.workspace(B, ctx.dev)
+    grads = torch.zeros(ctx.info.n_params, dtype=torch.half, device=ctx.dev)
+    loss = torch.zeros(1, dtype=torch.float32, device=ctx.dev)
+    out = torch.empty(B, 16, dtype=torch.half, device=ctx.dev)
+    check(ctx.lib.tcnn_b200_training_fwd_bwd(ctx.native.handle, S(), B, ptr(x), ptr(t), ptr(p16), ptr(grads), 128.0, 1, ptr(loss), ptr(out), ptr(ws)))
+    enc = np.zeros((B, ctx.m.n_input), np.float16)
+    enc[:, : ctx.g.n_features] = O.grid_forward(ctx.g, x_np, p16_np[ctx.m.n_params:])
+    y, hidden = O.mlp_forward(ctx.m, p16_np[: ctx.m.n_params], enc)
+    lv, dy = O.loss_l2(y, t_np, ctx.n_out, relative=(ctx.info.loss_type == 1))
+    dW, dx = O.mlp_backward(ctx.m, p16_np[: ctx.m.n_params], enc, hidden, dy)
+    gg = O.grid_backward(ctx.g, x_np, dx[:, : ctx.g.n_features])
+    got = grads.cpu().numpy().astype(np.float64)
+    assert abs(loss.item() - lv) <= 1e-4 * abs(lv)
+    assert common.rel_l2(out.cpu().numpy(), y) < 1e-3
+    assert common.rel_l2(got[: ctx.m.n_params], dW) < 2e-3
+    assert common.rel_l2(got[ctx.m.n_params:], gg) < 3e-3
+    assert np.array_equal(got[ctx.m.n_params:] != 0, gg != 0) or np.count_nonzero((got[ctx.m.n_params:] != 0) != (gg != 0)) < 1e-4 * gg.size
+
+
+def test_training_step_and_adam_vs_reference_golden(ctx):
+    """Same parameters (bit-exact init), same batch as the reference dump: loss, output, gradients, one Adam step."""
+    import tinycudann as tcnn
+    z = ctx.golden
+    B = int(z["B"])
+    model = tcnn.create_from_config(ctx.n_in, ctx.n_out, ctx.cfg, seed=1337, device=ctx.dev)
+    tr = model.trainer
+    x_np, t_np = common.synth_inputs(B, ctx.n_in, ctx.n_out, seed=1)
+    x, t = torch.from_numpy(x_np).to(ctx.dev), torch.from_numpy(t_np).to(ctx.dev)
+    pred = tr.inference(x).cpu().numpy()
+    assert common.rel_l2(pred, z["output"]) < 1e-2
+    out = torch.empty(B, 16, dtype=torch.half, device=ctx.dev)
+    tr.training_step(x, t, run_optimizer=False, output=out)
+    assert abs(tr.loss() - float(z["loss"])) <= 2e-3 * abs(float(z["loss"]))
+    assert common.rel_l2(out.cpu().numpy(), z["output_padded"]) < 1e-2
+    n_mlp = int(z["n_params_mlp"])
+    grads = tr.param_gradients.cpu().numpy()
+    assert common.rel_l2(grads[:n_mlp], z["grads_mlp"]) < 1e-2
+    nz = z["grads_grid_nz_idx"].astype(np.int64)
+    gg = grads[n_mlp:]
+    assert common.rel_l2(gg[nz], z["grads_grid_nz_val"]) < 8e-2
+    ours_nz = np.flatnonzero(gg.view(np.uint16) & 0x7FFF)
+    assert len(np.setxor1d(ours_nz, nz)) <= 2e-3 * len(nz) + 4  # same set of touched entries (up to fp16 underflow)
+    before = tr.params_full_precision.cpu().numpy()
+    tr.optimizer_step()
+    after = tr.params_full_precision.cpu().numpy()
+    # first Adam step moves every touched parameter by ~lr * sign(g): compare the update vectors
+    assert common.rel_l2(after[:n_mlp] - before[:n_mlp], z["params_after_mlp"] - z["params_init_mlp"]) < 5e-2
+    mi = z["params_after_moved_idx"].astype(np.int64)
+    assert common.rel_l2(after[mi] - before[mi], z["params_after_moved_val"] - before[mi]) < 8e-2
+    moved = np.count_nonzero(after != before)
+    assert abs(moved - int(z["n_moved"])) <= 2e-3 * int(z["n_moved"]) + 4
+
+
+def test_adam_vs_oracle(ctx):
+    from tinycudann._lib import check, ptr
+    P, n_mat = int(ctx.info.n_params), ctx.m.n_params
+    rng = np.random.default_rng(2)
+    master_np = O.init_params(ctx.m, ctx.g, 1337, True)
+    g_np = (rng.standard_normal(P) * 0.05).astype(np.float16)
+    g_np[n_mat:][rng.random(P - n_mat) < 0.6] = 0  # untouched hash entries must be skipped
+    o = ctx.cfg["optimizer"]
+    ac = O.AdamConfig(o.get("learning_rate", 1e-3), o.get("beta1", 0.9), o.get("beta2", 0.999), o.get("epsilon", 1e-8), o.get("l2_reg", 1e-8))
+    master = torch.from_numpy(master_np.copy()).to(ctx.dev)
+    params = torch.zeros(P, dtype=torch.half, device=ctx.dev)
+    m1 = torch.zeros(P, device=ctx.dev); v1 = torch.zeros(P, device=ctx.dev); st = torch.zeros(P, dtype=torch.int32, device=ctx.dev)
+    mm, m0, v0, s0 = master_np.copy(), np.zeros(P, np.float32), np.zeros(P, np.float32), np.zeros(P, np.uint32)
+    for step in (1, 2, 3):
+        grads = torch.from_numpy(g_np).to(ctx.dev)
+        check(ctx.lib.tcnn_b200_adam_step(ctx.native.handle, S(), 128.0, step, ptr(master), ptr(params), ptr(grads), ptr(m1), ptr(v1), ptr(st), 1))
+        O.adam_step(ac, n_mat, mm, g_np, m0, v0, s0)
+        assert not grads[n_mat:].any().item()  # grid gradients re-zeroed for the next step
+        if step == 2:  # entries touched from now on lag the global step -> per-parameter bias correction path
+            g_np = g_np.copy(); g_np[n_mat:][::3] = np.float16(0.01)
+    got = master.cpu().numpy()
+    assert np.array_equal(st.cpu().numpy().view(np.uint32), s0)
+    assert common.rel_l2(got - master_np, mm - master_np) < 1e-4
+    assert np.array_equal(params.cpu().numpy()[s0 > 0].view(np.uint16), got.astype(np.float16)[s0 > 0].view(np.uint16))
+    untouched = s0 == 0
+    assert np.array_equal(got[untouched], master_np[untouched])  # bit-identical where the gradient was zero
+
+
+def test_module_surface_forward_backward(dev):
+    """tcnn.NetworkWithInputEncoding: batch padding to 256, output slicing, autograd with loss scaling."""
+    import tinycudann as tcnn
+    cfg = common.CONFIG_SHIPPED
+    net = tcnn.NetworkWithInputEncoding(2, 3, cfg["encoding"], cfg["network"], seed=1337).to(dev)
+    assert net.params.dtype == torch.float32 and net.params.shape[0] == net.native_tcnn_module.n_params()
+    B = 1000  # not a multiple of 256
+    x_np, t_np = common.synth_inputs(B, 2, 3, seed=9)
+    x, t = torch.from_numpy(x_np).to(dev), torch.from_numpy(t_np).to(dev)
+    with torch.no_grad():
+        y_inf = net(x)
+    assert y_inf.shape == (B, 3) and y_inf.dtype == torch.half
+    y = net(x)
+    assert torch.equal(y, y_inf)
+    loss = ((y.float() - t) ** 2).mean()
+    loss.backward()
+    grad = net.params.grad.cpu().numpy().astype(np.float64)
+    # oracle on the padded batch (padding rows are zeros and receive zero gradient)
+    g, m = common.oracle_configs(cfg, 2, 3, scales=np.array(net.native_tcnn_module.info.level_scale[:16], dtype=np.float32))
+    p16 = net.params.detach().cpu().numpy().astype(np.float16)
+    xp = np.zeros((1024, 2), np.float32); xp[:B] = x_np
+    enc = O.grid_forward(g, xp, p16[m.n_params:])
+    yo, hidden = O.mlp_forward(m, p16[: m.n_params], enc)
+    assert common.rel_l2(y.detach().cpu().numpy(), yo[:B, :3]) < 1e-3
+    dy = np.zeros((1024, 16), np.float32)
+    dy[:B, :3] = 2 * (yo[:B, :3].astype(np.float32) - t_np) / (B * 3)
+    dy16 = (dy * 128.0).astype(np.float16)
+    dW, dx = O.mlp_backward(m, p16[: m.n_params], enc, hidden, dy16)
+    gg = O.grid_backward(g, xp, dx)
+    ref = np.concatenate([dW, gg]) / 128.0
+    assert common.rel_l2(grad[: m.n_params], ref[: m.n_params]) < 5e-3
+    assert common.rel_l2(grad[m.n_params:], ref[m.n_params:]) < 5e-3
+    # two forwards before one backward (context lifetime, scripts/test_toch_bindings.py:25-50 of the reference)
+    net.zero_grad()
+    y1 = net(x); y2 = net(x)
+    (y1.float().sum() + y2.float().sum()).backward()
+    assert torch.isfinite(net.params.grad).all()
+
+
+def test_trainer_converges_and_matches_reference_order_of_magnitude(dev):
+    import tinycudann as tcnn
+    model = tcnn.create_from_config(2, 3, common.CONFIG_1, seed=1337, device=dev)
+    tr = model.trainer
+    B = 1 << 14
+    losses = []
+    for i in range(300):
+        x_np, t_np = common.synth_inputs(B, 2, 3, seed=100 + i % 8)
+        tr.training_step(torch.from_numpy(x_np).to(dev), torch.from_numpy(t_np).to(dev))
+        if i % 50 == 0 or i == 299:
+            losses.append(tr.loss())
+    assert losses[-1] < 0.05 * losses[0], losses
+
+
+def test_batch_size_must_be_multiple_of_256(dev):
+    import tinycudann as tcnn
+    model = tcnn.create_from_config(2, 3, common.CONFIG_1, seed=1, device=dev)
+    x = torch.rand(300, 2, device=dev); t = torch.rand(300, 3, device=dev)
+    with pytest.raises(RuntimeError, match="multiple of 256"):
+        model.trainer.training_step(x, t)
+
+
+def test_full_size_properties(dev):
+    """BASELINE batch (2^18), too large for the numpy oracle: size-independent properties instead."""
+    import tinycudann as tcnn
+    from tinycudann._lib import check, ptr
+    native = tcnn.NativeModule(2, 3, common.CONFIG_1)
+    info, lib = native.info, native.lib
+    B = 1 << 18
+    gen = torch.Generator(device=dev); gen.manual_seed(5)
+    x = torch.rand(B, 2, device=dev, generator=gen)
+    P, n_mlp = int(info.n_params), int(info.n_params_mlp)
+    p16 = ((torch.rand(P, device=dev, generator=gen) - 0.5) * 0.5).half()
+    ws = native.workspace(B, dev)
+    # (1) inference is independent of where a sample sits in the batch / of the batch size
+    out_full = torch.empty(B, 16, dtype=torch.half, device=dev)
+    check(lib.tcnn_b200_inference(native.handle, S(), B, ptr(x), ptr(p16), ptr(out_full), None, ptr(ws)))
+    sub = x[B // 2: B // 2 + 1024].contiguous()
+    out_sub = torch.empty(1024, 16, dtype=torch.half, device=dev)
+    check(lib.tcnn_b200_inference(native.handle, S(), 1024, ptr(sub), ptr(p16), ptr(out_sub), None, ptr(native.workspace(1024, dev))))
+    assert torch.equal(out_full[B // 2: B // 2 + 1024], out_sub)
+    # (2) scatter checksum: interpolation weights sum to 1, so per (level, feature) the table gradient sums to the
+    #     column sum of dL/d(encoded)  (up to fp16 rounding of the products and of the accumulation)
+    E = info.encoded_width
+    dy = (torch.randn(B, E, device=dev, generator=gen) * 0.05).half()
+    grads = torch.zeros(int(info.n_params_grid), dtype=torch.half, device=dev)
+    check(lib.tcnn_b200_encode_backward(native.handle, S(), B, ptr(x), ptr(dy), ptr(grads), 1, ptr(ws)))
+    col = dy.float().sum(0).cpu().numpy()
+    colabs = dy.float().abs().sum(0).cpu().numpy()
+    for l in range(info.n_levels):
+        seg = grads[2 * info.level_offset[l]: 2 * info.level_offset[l + 1]].float().view(-1, 2).sum(0).cpu().numpy()
+        assert np.all(np.abs(seg - col[2 * l: 2 * l + 2]) < 2e-3 * colabs[2 * l: 2 * l + 2] + 1e-2), f"level {l}: {seg} vs {col[2*l:2*l+2]}"
+    # (3) linearity of the scatter: backward(2 dy) == 2 backward(dy) exactly in fp16 (power-of-two scaling), where
+    #     the accumulation order is fixed, i.e. on entries touched once; compare checksums instead
+    grads2 = torch.zeros_like(grads)
+    check(lib.tcnn_b200_encode_backward(native.handle, S(), B, ptr(x), ptr((dy.float() * 2).half()), ptr(grads2), 1, ptr(ws)))
+    assert abs(grads2.float().sum().item() - 2 * grads.float().sum().item()) < 1e-3 * grads.float().abs().sum().item()

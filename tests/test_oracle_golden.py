@@ -1,0 +1,85 @@
+"""CPU: pins the numpy oracle to the reference.  The fixtures in tests/golden/ are dumps of the reference's own CUDA
+build (oracle/_ref/ref_driver over the unmodified sources) on a B200, made by tests/golden/make_golden.py."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from oracle import tcnn_oracle as O
+from tests import common
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+NAMES = ["cfg1_2d_T19", "shipped_2d_T15", "nerf_3d_T19", "f4_3d_T14"]
+
+
+@pytest.fixture(scope="module", params=NAMES)
+def case(request):
+    z = np.load(os.path.join(GOLDEN, request.param + ".npz"))
+    cfg = json.loads(str(z["config"]))
+    n_in, n_out, B = int(z["n_in"]), int(z["n_out"]), int(z["B"])
+    g, m = common.oracle_configs(cfg, n_in, n_out, scales=z["level_scale"])
+    x, t = common.synth_inputs(B, n_in, n_out, seed=int(z["seed"]))
+    p = O.init_params(m, g, 1337, True)
+    return dict(z=z, cfg=cfg, g=g, m=m, x=x, t=t, p=p, n_out=n_out, B=B)
+
+
+def test_level_table(case):
+    z, g = case["z"], case["g"]
+    assert np.array_equal(g.resolutions, z["level_res"])
+    assert np.array_equal(np.diff(g.offsets.astype(np.int64)), z["level_size"])
+    assert g.n_params + case["m"].n_params == int(z["n_params"])
+
+
+def test_param_init_bit_exact(case):
+    z, p, m = case["z"], case["p"], case["m"]
+    assert np.array_equal(p[: m.n_params], z["params_init_mlp"])
+    assert np.array_equal(p[::997], z["params_init_sample"])
+    assert p.astype(np.float64).sum() == float(z["params_init_sum"])
+    assert (p.astype(np.float64) ** 2).sum() == float(z["params_init_sumsq"])
+
+
+def test_indices_bit_exact(case):
+    z, g, x = case["z"], case["g"], case["x"]
+    for l in range(g.n_levels):
+        idx, _ = O.grid_corners(g, x, l)
+        assert np.array_equal(idx, z["indices"][l]), f"level {l}"
+
+
+def test_encoded_features_bit_exact(case):
+    z, g, m = case["z"], case["g"], case["m"]
+    enc = O.grid_forward(g, case["x"], case["p"].astype(np.float16)[m.n_params:])
+    ref = z["encoded_soa"].T[:, : g.n_features]
+    assert np.array_equal(enc.view(np.uint16), ref.view(np.uint16))
+
+
+def test_mlp_loss_gradients_within_tolerance(case):
+    z, g, m, n_out, B = case["z"], case["g"], case["m"], case["n_out"], case["B"]
+    p16 = case["p"].astype(np.float16)
+    enc = np.zeros((B, m.n_input), np.float16)
+    enc[:, : g.n_features] = O.grid_forward(g, case["x"], p16[m.n_params:])
+    y, hidden = O.mlp_forward(m, p16[: m.n_params], enc)
+    assert common.rel_l2(y, z["output_padded"]) < 1e-2  # reference accumulates in fp16
+    assert common.rel_l2(y[:, :n_out].astype(np.float32), z["output"]) < 1e-2
+    relative = case["cfg"]["loss"]["otype"] == "RelativeL2"
+    # loss + gradient restatement checked on the reference's own prediction: must agree to fp32 rounding
+    lv, dy = O.loss_l2(z["output_padded"], case["t"], n_out, relative=relative)
+    assert abs(lv - float(z["loss"])) < 1e-5 * abs(lv)
+    assert common.rel_l2(dy, z["dL_doutput"]) < 1e-6
+    dW, dx = O.mlp_backward(m, p16[: m.n_params], enc, hidden, O.loss_l2(y, case["t"], n_out, relative=relative)[1])
+    assert common.rel_l2(dW, z["grads_mlp"]) < 1e-2
+    gg = O.grid_backward(g, case["x"], dx[:, : g.n_features])
+    nz = z["grads_grid_nz_idx"].astype(np.int64)
+    assert common.rel_l2(gg[nz], z["grads_grid_nz_val"]) < 8e-2  # ReLU-mask flips (fp16 vs fp32 accumulate), see DESIGN.md
+    assert abs(np.count_nonzero(gg) - len(nz)) <= 2e-3 * len(nz) + 4
+
+
+def test_adam_first_step(case):
+    z, m = case["z"], case["m"]
+    o = case["cfg"]["optimizer"]
+    ac = O.AdamConfig(o.get("learning_rate", 1e-3), o.get("beta1", 0.9), o.get("beta2", 0.999), o.get("epsilon", 1e-8), o.get("l2_reg", 1e-8))
+    n = m.n_params
+    master = case["p"][:n].copy()
+    mm, vv, ss = np.zeros(n, np.float32), np.zeros(n, np.float32), np.zeros(n, np.uint32)
+    O.adam_step(ac, n, master, z["grads_mlp"], mm, vv, ss)  # the reference's own gradients -> its own update
+    assert np.max(np.abs(master - z["params_after_mlp"])) < 2e-7 + 1e-5 * ac.learning_rate

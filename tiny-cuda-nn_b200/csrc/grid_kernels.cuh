@@ -23,12 +23,16 @@ struct GridLevel {
 	uint32_t stride[MAX_DIMS]; // dense strides incl. uint32 wrap; 0 for dims the reference loop never reaches
 	uint32_t n_dense_dims;  // number of loop iterations of grid_index executed
 	uint32_t hashed;        // 1 if (Hash grid && size < final stride)
+	uint32_t replicated;    // backward: scatter into one of n_replicas private copies (coarse, heavily contended levels)
+	uint32_t rep_offset;    // first entry of this level inside one replica
 };
 
 struct GridParams {
 	uint32_t n_levels;
 	uint32_t n_features;     // n_levels * F
 	uint32_t padded_width;   // encoded row width in halfs (multiple of 16)
+	uint32_t n_replicas;     // power of two
+	uint32_t rep_entries;    // entries per replica (sum of the replicated levels' sizes)
 	GridLevel level[MAX_LEVELS];
 };
 
@@ -179,7 +183,7 @@ __global__ void __launch_bounds__(256) grid_forward_kernel(const __grid_constant
 // Same arithmetic as grid.h:248-318: product (half)weight * grad rounded to fp16, then red.add.noftz.f16x2.
 template <int D, int F>
 __global__ void __launch_bounds__(256) grid_backward_kernel(const __grid_constant__ GridParams gp, uint32_t B,
-	const float* __restrict__ x, const __half* __restrict__ dL_denc, __half* __restrict__ grid_grad) {
+	const float* __restrict__ x, const __half* __restrict__ dL_denc, __half* __restrict__ grid_grad, __half* __restrict__ replicas) {
 	static_assert(F == 2 || F == 4 || F == 8, "fp16 gradient scatter needs F >= 2 (grid.h:655-666)");
 	constexpr int LEVELS_PER_CHUNK = 8 / F;
 	constexpr int NC = 1 << D;
@@ -198,7 +202,11 @@ __global__ void __launch_bounds__(256) grid_backward_kernel(const __grid_constan
 		float frac[D]; uint32_t cell[D];
 #pragma unroll
 		for (int d = 0; d < D; ++d) pos_fract_dev(p[d], lv.scale, frac[d], cell[d]);
-		__half* gtable = grid_grad + (size_t)lv.offset * F;
+		// Same-address f16x2 reductions serialise in L2 (~80 ns each, measured: 2-D level 0 alone took 244 us at B = 2^18);
+		// coarse levels therefore scatter into one of n_replicas copies chosen per block and are summed afterwards.
+		__half* gtable = lv.replicated
+			? replicas + ((size_t)(blockIdx.x & (gp.n_replicas - 1)) * gp.rep_entries + lv.rep_offset) * F
+			: grid_grad + (size_t)lv.offset * F;
 #pragma unroll
 		for (int c = 0; c < NC; ++c) {
 			float weight = 1.0f; uint32_t pg[D];
@@ -213,6 +221,29 @@ __global__ void __launch_bounds__(256) grid_backward_kernel(const __grid_constan
 			for (int k = 0; k < F / 2; ++k) {
 				red_add_h2(gtable + (size_t)idx * F + 2 * k, __hmul2(wh, g.h2[s * (F / 2) + k]));
 			}
+		}
+	}
+}
+
+// grid_grad[level entries] += sum over replicas (fp32 accumulate, one rounding), for the replicated levels.
+__global__ void grid_replica_reduce_kernel(const __grid_constant__ GridParams gp, uint32_t F, const __half* __restrict__ replicas, __half* __restrict__ grid_grad) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; // half2 index inside one replica
+	const uint32_t pairs = gp.rep_entries * F / 2;
+	if (i >= pairs) return;
+	float2 acc = make_float2(0.f, 0.f);
+	for (uint32_t r = 0; r < gp.n_replicas; ++r) {
+		const float2 v = __half22float2(reinterpret_cast<const __half2*>(replicas)[(size_t)r * pairs + i]);
+		acc.x += v.x; acc.y += v.y;
+	}
+	// locate the level this entry belongs to (a handful of coarse levels)
+	const uint32_t entry = (i * 2) / F;
+	for (uint32_t l = 0; l < gp.n_levels; ++l) {
+		const GridLevel& lv = gp.level[l];
+		if (lv.replicated && entry >= lv.rep_offset && entry < lv.rep_offset + lv.size) {
+			__half2* dst = reinterpret_cast<__half2*>(grid_grad + (size_t)lv.offset * F) + (i - lv.rep_offset * F / 2);
+			const float2 old = __half22float2(*dst);
+			*dst = __floats2half2_rn(old.x + acc.x, old.y + acc.y);
+			return;
 		}
 	}
 }

@@ -412,25 +412,35 @@ __global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArg
 }
 
 // Sum the per-CTA fp32 partials -> fp16 weight gradients (layout of the reference's gradient matrices) and the loss.
-__global__ void mlp_finalize_kernel(uint32_t n_params, uint32_t n_parts, const float* __restrict__ partials, __half* __restrict__ grads,
+// Block = 32 parameters x 8 slices of the partial list (coalesced 128-byte rows), tree-reduced in shared memory.
+__global__ void __launch_bounds__(256) mlp_finalize_kernel(uint32_t n_params, uint32_t n_parts, const float* __restrict__ partials, __half* __restrict__ grads,
 	const float* __restrict__ loss_partials, float* __restrict__ loss_out) {
-	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	__shared__ float sh[8][33];
+	const uint32_t px = threadIdx.x & 31, sl = threadIdx.x >> 5;
+	const uint32_t i = blockIdx.x * 32 + px;
+	float s = 0.f;
 	if (i < n_params && grads) {
-		float s = 0.f;
-		for (uint32_t p = 0; p < n_parts; ++p) s += partials[(size_t)p * n_params + i];
-		grads[i] = __float2half(s);
+		for (uint32_t p = sl; p < n_parts; p += 8) s += partials[(size_t)p * n_params + i];
+	}
+	sh[sl][px] = s;
+	__syncthreads();
+	if (sl == 0 && i < n_params && grads) {
+		float t = 0.f;
+#pragma unroll
+		for (int k = 0; k < 8; ++k) t += sh[k][px];
+		grads[i] = __float2half(t);
 	}
 	if (blockIdx.x == 0 && loss_partials && loss_out) {
-		__shared__ float sh[32];
-		float s = 0.f;
-		for (uint32_t p = threadIdx.x; p < n_parts; p += blockDim.x) s += loss_partials[p];
+		__syncthreads();
+		float l = 0.f;
+		for (uint32_t p = threadIdx.x; p < n_parts; p += blockDim.x) l += loss_partials[p];
 #pragma unroll
-		for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xFFFFFFFFu, s, o);
-		if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = s;
+		for (int o = 16; o > 0; o >>= 1) l += __shfl_xor_sync(0xFFFFFFFFu, l, o);
+		if (px == 0) sh[sl][0] = l;
 		__syncthreads();
 		if (threadIdx.x == 0) {
 			float t = 0.f;
-			for (uint32_t w = 0; w < blockDim.x / 32; ++w) t += sh[w];
+			for (int w = 0; w < 8; ++w) t += sh[w][0];
 			*loss_out = t;
 		}
 	}

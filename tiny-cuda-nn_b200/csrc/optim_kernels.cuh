@@ -20,6 +20,10 @@ struct AdamArgs {
 	float lower_lr_bound, upper_lr_bound;
 	float weight_clip;
 	float non_matrix_lr_factor;
+	float inv_loss_scale;         // 1 / loss_scale if that is exact (power of two), else 0 => divide
+	float log2_beta1, log2_beta2; // for beta^t = exp2f(t * log2(beta)) on parameters whose step lags the global step
+	uint32_t global_step;         // step count of parameters updated every step (after this update)
+	float global_correction;      // sqrtf(1 - beta2^t) / (1 - beta1^t) at t = global_step
 	int zero_grads;               // re-zero the non-matrix gradients after consuming them
 	float* master;
 	__half* params;
@@ -30,7 +34,7 @@ struct AdamArgs {
 };
 
 __device__ __forceinline__ bool adam_one(const AdamArgs& a, uint32_t i, float g_half, float& w, float& m, float& v, uint32_t& step) {
-	float gradient = g_half / a.loss_scale;
+	float gradient = a.inv_loss_scale != 0.f ? g_half * a.inv_loss_scale : g_half / a.loss_scale;
 	const bool is_matrix = i < a.n_matrix;
 	if (!is_matrix && gradient == 0.f) return false;
 	if (is_matrix) gradient += a.l2_reg * w;
@@ -40,7 +44,10 @@ __device__ __forceinline__ bool adam_one(const AdamArgs& a, uint32_t i, float g_
 	float lr = a.learning_rate;
 	if (!is_matrix) lr *= a.non_matrix_lr_factor;
 	step += 1;
-	lr *= sqrtf(1 - powf(a.beta2, (float)step)) / (1 - powf(a.beta1, (float)step));
+	// adam.h:103-105: lr *= sqrtf(1 - powf(beta2, t)) / (1 - powf(beta1, t)).  Two powf per parameter made this kernel
+	// SM-bound (ncu r01a: 85 % SM, 39 % DRAM); parameters in step with the optimizer use the host-evaluated factor.
+	if (step == a.global_step) lr *= a.global_correction;
+	else lr *= sqrtf(1 - exp2f((float)step * a.log2_beta2)) / (1 - exp2f((float)step * a.log2_beta1));
 	const float eff = fminf(fmaxf(lr / (sqrtf(v) + a.epsilon), a.lower_lr_bound), a.upper_lr_bound);
 	// weight_decay(relative * lr, absolute * lr, w)   (common_device.h:870-873)
 	const float decayed = (1 - a.relative_decay * lr) * w - copysignf(a.absolute_decay * lr, w);

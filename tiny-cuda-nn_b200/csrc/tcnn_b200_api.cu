@@ -12,6 +12,7 @@
 #include <memory>
 #include <random>
 #include <string>
+#include <vector>
 
 #include "grid_kernels.cuh"
 #include "json_mini.h"
@@ -42,6 +43,25 @@ struct tcnn_b200_plan {
 	// Adam extras
 	float non_matrix_lr_factor = 1.f, weight_clip = 0.f;
 	bool adabound = false;
+	// optional per-kernel timing (tcnn_b200_profile_*): CUDA events recorded around every launch on the launch stream
+	bool profiling = false;
+	struct Span { int kind; cudaEvent_t e0, e1; };
+	std::vector<Span> spans;
+};
+
+enum ProfileKind { PK_GRID_FWD = 0, PK_MLP = 1, PK_FINALIZE = 2, PK_GRID_BWD = 3, PK_ADAM = 4, PK_COUNT = 5 };
+
+struct ProfileScope {
+	tcnn_b200_plan* p; cudaStream_t s; cudaEvent_t e1{};
+	ProfileScope(const tcnn_b200_plan* plan, cudaStream_t stream, int kind) : p(const_cast<tcnn_b200_plan*>(plan)), s(stream) {
+		if (!p->profiling) { p = nullptr; return; }
+		tcnn_b200_plan::Span sp; sp.kind = kind;
+		cudaEventCreate(&sp.e0); cudaEventCreate(&sp.e1);
+		cudaEventRecord(sp.e0, s);
+		e1 = sp.e1;
+		p->spans.push_back(sp);
+	}
+	~ProfileScope() { if (p) cudaEventRecord(e1, s); }
 };
 
 static uint32_t next_multiple_u32(uint32_t v, uint32_t m) { return (v + m - 1) / m * m; }
@@ -60,6 +80,31 @@ static void fill_level(GridLevel& lv, float scale, uint32_t size, uint32_t offse
 	}
 	lv.n_dense_dims = d;
 	lv.hashed = size < stride ? 1u : 0u;
+	lv.replicated = 0; lv.rep_offset = 0;
+}
+
+constexpr uint32_t N_REPLICAS = 32;          // private copies of the contended coarse gradient levels
+constexpr uint32_t REPLICATE_MAX_ENTRIES = 8192; // levels up to this many entries are replicated ...
+constexpr uint32_t REPLICATE_MIN_BATCH = 1u << 14; // ... when the batch is large enough for contention to matter
+
+// GridParams for the backward launch: marks the replicated levels (if a replica buffer is available).
+static GridParams backward_params(const tcnn_b200_plan* p, uint32_t B, bool have_replicas) {
+	GridParams gp = p->grid;
+	gp.n_replicas = N_REPLICAS; gp.rep_entries = 0;
+	if (!have_replicas || B < REPLICATE_MIN_BATCH) return gp;
+	for (uint32_t l = 0; l < gp.n_levels; ++l) {
+		if (gp.level[l].size <= REPLICATE_MAX_ENTRIES) {
+			gp.level[l].replicated = 1;
+			gp.level[l].rep_offset = gp.rep_entries;
+			gp.rep_entries += gp.level[l].size;
+		}
+	}
+	return gp;
+}
+static size_t replica_bytes(const tcnn_b200_plan* p) {
+	size_t entries = 0;
+	for (uint32_t l = 0; l < p->grid.n_levels; ++l) if (p->grid.level[l].size <= REPLICATE_MAX_ENTRIES) entries += p->grid.level[l].size;
+	return entries * p->info.n_features_per_level * 2 * N_REPLICAS;
 }
 
 static void build_levels(tcnn_b200_plan* p, const float* scales) {
@@ -227,7 +272,7 @@ extern "C" int tcnn_b200_plan_update_optimizer(tcnn_b200_plan* plan, const char*
 
 // workspace layout: [encoded B x E fp16][dL_dencoded B x E fp16][dW partials n_ctas x P_mlp fp32][loss partials n_ctas fp32]
 struct Workspace {
-	__half* encoded; __half* dL_denc; float* dw_partials; float* loss_partials;
+	__half* encoded; __half* dL_denc; float* dw_partials; float* loss_partials; __half* replicas;
 };
 static uint32_t mlp_grid_size(const tcnn_b200_plan* p, uint32_t n_tiles, bool train) {
 	const uint32_t per_sm = train ? 2u : 3u;
@@ -242,14 +287,15 @@ static Workspace carve(const tcnn_b200_plan* p, uint32_t B, void* ws) {
 	w.encoded = (__half*)b; b += act;
 	w.dL_denc = (__half*)b; b += act;
 	w.dw_partials = (float*)b; b += align256((size_t)max_ctas * p->info.n_params_mlp * 4);
-	w.loss_partials = (float*)b;
+	w.loss_partials = (float*)b; b += align256((size_t)max_ctas * 4);
+	w.replicas = (__half*)b;
 	return w;
 }
 extern "C" size_t tcnn_b200_workspace_bytes(const tcnn_b200_plan* plan, uint32_t B) {
 	if (!plan) return 0;
 	const size_t act = align256((size_t)B * plan->info.encoded_width * 2);
 	const uint32_t max_ctas = (uint32_t)plan->n_sms * 3;
-	return 2 * act + align256((size_t)max_ctas * plan->info.n_params_mlp * 4) + align256((size_t)max_ctas * 4) + 256;
+	return 2 * act + align256((size_t)max_ctas * plan->info.n_params_mlp * 4) + align256((size_t)max_ctas * 4) + align256(replica_bytes(plan)) + 256;
 }
 
 static void check_batch(uint32_t B) {
@@ -316,8 +362,6 @@ extern "C" int tcnn_b200_cast_params(void* stream_, uint64_t n, const float* par
 }
 
 // ---- grid encoding ------------------------------------------------------------------------------------
-template <template <int, int> class K> struct GridDispatch;
-
 #define GRID_DISPATCH(KERNEL, plan, grid_dim, stream, ...)                                                        \
 	do {                                                                                                          \
 		const uint32_t D_ = (plan)->info.n_input_dims, F_ = (plan)->info.n_features_per_level;                   \
@@ -333,16 +377,26 @@ template <template <int, int> class K> struct GridDispatch;
 	} while (0)
 
 static void encode_forward(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t B, const float* x, const __half* grid, __half* encoded) {
+	ProfileScope prof(plan, stream, PK_GRID_FWD);
 	const dim3 g((B + 255) / 256, plan->info.encoded_width / 8, 1);
 	GRID_DISPATCH(grid_forward_kernel, plan, g, stream, plan->grid, B, x, grid, encoded);
 	launch_check("grid_forward_kernel");
 }
-static void encode_backward(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t B, const float* x, const __half* dL_denc, __half* grid_grads, int zero_first) {
+static void encode_backward(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t B, const float* x, const __half* dL_denc, __half* grid_grads, int zero_first, __half* replicas) {
+	ProfileScope prof(plan, stream, PK_GRID_BWD);
 	if (zero_first) CUDA_OK(cudaMemsetAsync(grid_grads, 0, plan->info.n_params_grid * 2, stream));
+	const GridParams gp = backward_params(plan, B, replicas != nullptr);
+	const uint32_t F = plan->info.n_features_per_level;
+	if (gp.rep_entries) CUDA_OK(cudaMemsetAsync(replicas, 0, (size_t)gp.rep_entries * F * 2 * gp.n_replicas, stream));
 	const uint32_t n_chunks = (plan->grid.n_features + 7) / 8; // padding chunks carry no gradient
 	const dim3 g((B + 255) / 256, n_chunks, 1);
-	GRID_DISPATCH(grid_backward_kernel, plan, g, stream, plan->grid, B, x, dL_denc, grid_grads);
+	GRID_DISPATCH(grid_backward_kernel, plan, g, stream, gp, B, x, dL_denc, grid_grads, replicas);
 	launch_check("grid_backward_kernel");
+	if (gp.rep_entries) {
+		const uint32_t pairs = gp.rep_entries * F / 2;
+		grid_replica_reduce_kernel<<<(pairs + 255) / 256, 256, 0, stream>>>(gp, F, replicas, grid_grads);
+		launch_check("grid_replica_reduce_kernel");
+	}
 }
 
 extern "C" int tcnn_b200_encode_forward(const tcnn_b200_plan* plan, void* stream, uint32_t B, const float* x, const void* grid_params, void* encoded) {
@@ -352,11 +406,11 @@ extern "C" int tcnn_b200_encode_forward(const tcnn_b200_plan* plan, void* stream
 	encode_forward(plan, (cudaStream_t)stream, B, x, (const __half*)grid_params, (__half*)encoded);
 	API_END
 }
-extern "C" int tcnn_b200_encode_backward(const tcnn_b200_plan* plan, void* stream, uint32_t B, const float* x, const void* dL_denc, void* grid_grads, int zero_first) {
+extern "C" int tcnn_b200_encode_backward(const tcnn_b200_plan* plan, void* stream, uint32_t B, const float* x, const void* dL_denc, void* grid_grads, int zero_first, void* workspace) {
 	API_BEGIN
 	require_device(plan); check_batch(B);
 	CHECK(x && dL_denc && grid_grads, "null argument");
-	encode_backward(plan, (cudaStream_t)stream, B, x, (const __half*)dL_denc, (__half*)grid_grads, zero_first);
+	encode_backward(plan, (cudaStream_t)stream, B, x, (const __half*)dL_denc, (__half*)grid_grads, zero_first, workspace ? carve(plan, B, workspace).replicas : nullptr);
 	API_END
 }
 extern "C" int tcnn_b200_grid_indices(const tcnn_b200_plan* plan, void* stream, uint32_t B, const float* x, uint32_t* indices) {
@@ -382,6 +436,7 @@ static void launch_mlp_h(const tcnn_b200_plan* plan, cudaStream_t stream, const 
 		CUDA_OK(cudaFuncSetAttribute(mlp_kernel<MODE, H>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
 		configured = smem;
 	}
+	ProfileScope prof(plan, stream, PK_MLP);
 	mlp_kernel<MODE, H><<<grid, 128, smem, stream>>>(a);
 	launch_check("mlp_kernel");
 }
@@ -419,8 +474,9 @@ static void mlp_infer(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t 
 }
 
 static void mlp_finalize(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t n_parts, const Workspace& w, __half* grads, float* loss_out, bool with_loss) {
+	ProfileScope prof(plan, stream, PK_FINALIZE);
 	const uint32_t n = (uint32_t)plan->info.n_params_mlp;
-	mlp_finalize_kernel<<<(n + 255) / 256, 256, 0, stream>>>(n, n_parts, w.dw_partials, grads, with_loss ? w.loss_partials : nullptr, loss_out);
+	mlp_finalize_kernel<<<(n + 31) / 32, 256, 0, stream>>>(n, n_parts, w.dw_partials, grads, with_loss ? w.loss_partials : nullptr, loss_out);
 	launch_check("mlp_finalize_kernel");
 }
 
@@ -487,7 +543,7 @@ extern "C" int tcnn_b200_backward(const tcnn_b200_plan* plan, void* stream_, uin
 	const uint32_t grid = mlp_grid_size(plan, a.n_tiles, true);
 	launch_mlp<MODE_BACKWARD>(plan, stream, a, grid);
 	mlp_finalize(plan, stream, grid, w, g, nullptr, false);
-	encode_backward(plan, stream, B, x, w.dL_denc, g + plan->info.n_params_mlp, /*zero_first=*/1);
+	encode_backward(plan, stream, B, x, w.dL_denc, g + plan->info.n_params_mlp, /*zero_first=*/1, w.replicas);
 	API_END
 }
 
@@ -511,7 +567,7 @@ extern "C" int tcnn_b200_training_fwd_bwd(const tcnn_b200_plan* plan, void* stre
 	const uint32_t grid = mlp_grid_size(plan, a.n_tiles, true);
 	launch_mlp<MODE_TRAIN>(plan, stream, a, grid);
 	mlp_finalize(plan, stream, grid, w, g, loss_out, loss_out != nullptr);
-	encode_backward(plan, stream, B, x, w.dL_denc, g + plan->info.n_params_mlp, zero_grid_grads);
+	encode_backward(plan, stream, B, x, w.dL_denc, g + plan->info.n_params_mlp, zero_grid_grads, w.replicas);
 	API_END
 }
 
@@ -536,10 +592,42 @@ extern "C" int tcnn_b200_adam_step(const tcnn_b200_plan* plan, void* stream, flo
 	a.weight_clip = plan->weight_clip;
 	a.non_matrix_lr_factor = plan->non_matrix_lr_factor;
 	a.zero_grads = zero_grid_grads;
+	{
+		int e = 0;
+		const float mant = std::frexp(grad_divisor, &e);
+		a.inv_loss_scale = (mant == 0.5f) ? 1.0f / grad_divisor : 0.f; // exact only for powers of two
+		a.log2_beta1 = std::log2(in.beta1); a.log2_beta2 = std::log2(in.beta2);
+		a.global_step = adam_step_count;
+		a.global_correction = std::sqrt(1 - std::pow(in.beta2, (float)adam_step_count)) / (1 - std::pow(in.beta1, (float)adam_step_count));
+	}
 	a.master = params_fp32; a.params = (__half*)params_fp16; a.grads = (__half*)grads_fp16;
 	a.m = first_moments; a.v = second_moments; a.steps = param_steps;
+	ProfileScope prof(plan, (cudaStream_t)stream, PK_ADAM);
 	const uint32_t n_threads = (a.n + 3) / 4;
 	adam_kernel<<<(n_threads + 255) / 256, 256, 0, (cudaStream_t)stream>>>(a);
 	launch_check("adam_kernel");
+	API_END
+}
+
+// ---- per-kernel timing --------------------------------------------------------------------------------------
+extern "C" int tcnn_b200_profile_enable(tcnn_b200_plan* plan, int enable) {
+	API_BEGIN
+	CHECK(plan, "null plan");
+	plan->profiling = enable != 0;
+	API_END
+}
+// Synchronises the recorded events; ms_sum[k] / count[k] for k = grid_fwd, mlp, finalize, grid_bwd, adam; clears the log.
+extern "C" int tcnn_b200_profile_read(tcnn_b200_plan* plan, float* ms_sum, uint32_t* count, uint32_t n_kinds) {
+	API_BEGIN
+	CHECK(plan && ms_sum && count && n_kinds >= (uint32_t)PK_COUNT, "bad argument");
+	for (uint32_t k = 0; k < n_kinds; ++k) { ms_sum[k] = 0.f; count[k] = 0; }
+	for (auto& sp : plan->spans) {
+		CUDA_OK(cudaEventSynchronize(sp.e1));
+		float ms = 0.f;
+		CUDA_OK(cudaEventElapsedTime(&ms, sp.e0, sp.e1));
+		ms_sum[sp.kind] += ms; count[sp.kind] += 1;
+		cudaEventDestroy(sp.e0); cudaEventDestroy(sp.e1);
+	}
+	plan->spans.clear();
 	API_END
 }

@@ -56,7 +56,7 @@ _SIGNATURES = {
     "tcnn_b200_init_params": (C.c_int, [_P, _P, C.c_uint64, C.c_int, _P]),
     "tcnn_b200_cast_params": (C.c_int, [_P, C.c_uint64, _P, _P]),
     "tcnn_b200_encode_forward": (C.c_int, [_P, _P, C.c_uint32, _P, _P, _P]),
-    "tcnn_b200_encode_backward": (C.c_int, [_P, _P, C.c_uint32, _P, _P, _P, C.c_int]),
+    "tcnn_b200_encode_backward": (C.c_int, [_P, _P, C.c_uint32, _P, _P, _P, C.c_int, _P]),
     "tcnn_b200_grid_indices": (C.c_int, [_P, _P, C.c_uint32, _P, _P]),
     "tcnn_b200_mlp_forward": (C.c_int, [_P, _P, C.c_uint32, _P, _P, _P]),
     "tcnn_b200_mlp_backward": (C.c_int, [_P, _P, C.c_uint32, _P, _P, _P, _P, _P, _P]),
@@ -65,6 +65,8 @@ _SIGNATURES = {
     "tcnn_b200_backward": (C.c_int, [_P, _P, C.c_uint32, _P, _P, _P, _P, _P, _P]),
     "tcnn_b200_training_fwd_bwd": (C.c_int, [_P, _P, C.c_uint32, _P, _P, _P, _P, C.c_float, C.c_int, _P, _P, _P]),
     "tcnn_b200_adam_step": (C.c_int, [_P, _P, C.c_float, C.c_uint32, _P, _P, _P, _P, _P, _P, C.c_int]),
+    "tcnn_b200_profile_enable": (C.c_int, [_P, C.c_int]),
+    "tcnn_b200_profile_read": (C.c_int, [_P, C.POINTER(C.c_float), C.POINTER(C.c_uint32), C.c_uint32]),
 }
 
 _lib = None

@@ -71,7 +71,6 @@ class Trainer:
         self._grid_grads_clean = False
         if self.world_size > 1:
             torch.distributed.all_reduce(self.param_gradients, group=self.process_group)
-            torch.distributed.all_reduce(self.loss_value, group=self.process_group)
         if run_optimizer:
             self.optimizer_step(LOSS_SCALE)
         return self
@@ -87,7 +86,11 @@ class Trainer:
 
     # trainer.h:205-207 (synchronises, like the reference's reduce_sum + D2H)
     def loss(self) -> float:
-        return float(self.loss_value.item()) / self.world_size
+        if self.world_size > 1:  # mean over the global batch; collective: call on every rank
+            v = self.loss_value.clone()
+            torch.distributed.all_reduce(v, group=self.process_group)
+            return float(v.item()) / self.world_size
+        return float(self.loss_value.item())
 
     def update_hyperparams(self, params: dict):
         check(self.lib.tcnn_b200_plan_update_optimizer(self.native.handle, json.dumps(params).encode()))
