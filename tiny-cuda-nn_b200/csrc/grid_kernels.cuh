@@ -231,9 +231,12 @@ __global__ void grid_replica_reduce_kernel(const __grid_constant__ GridParams gp
 	const uint32_t pairs = gp.rep_entries * F / 2;
 	if (i >= pairs) return;
 	float2 acc = make_float2(0.f, 0.f);
-	for (uint32_t r = 0; r < gp.n_replicas; ++r) {
-		const float2 v = __half22float2(reinterpret_cast<const __half2*>(replicas)[(size_t)r * pairs + i]);
-		acc.x += v.x; acc.y += v.y;
+	for (uint32_t r0 = 0; r0 < gp.n_replicas; r0 += 8) { // 8 independent loads in flight (n_replicas is a multiple of 8)
+		__half2 v[8];
+#pragma unroll
+		for (uint32_t k = 0; k < 8; ++k) v[k] = reinterpret_cast<const __half2*>(replicas)[(size_t)(r0 + k) * pairs + i];
+#pragma unroll
+		for (uint32_t k = 0; k < 8; ++k) { const float2 f = __half22float2(v[k]); acc.x += f.x; acc.y += f.y; }
 	}
 	// locate the level this entry belongs to (a handful of coarse levels)
 	const uint32_t entry = (i * 2) / F;

@@ -21,6 +21,13 @@
 
 namespace b200 {
 
+// Development aid (tests/dev/mlp_timing.cu): per-stage clock64 stamps of CTA 0 / thread 0.
+#ifdef MLP_STAGE_CLOCKS
+#define STAGE_CLOCK(args) do { if (blockIdx.x == 0 && threadIdx.x == 0 && (args).debug_clock && dbg_n < 256) (args).debug_clock[dbg_n++] = clock64(); } while (0)
+#else
+#define STAGE_CLOCK(args) do { } while (0)
+#endif
+
 constexpr int MLP_W = 64;          // hidden width handled by this kernel
 constexpr int MLP_TILE = 128;      // samples per tile = UMMA M
 constexpr int MLP_OUT = 16;        // padded output width (fully_fused_mlp.cu:544: fused last layer only for <=16 outputs)
@@ -49,6 +56,7 @@ struct MlpArgs {
 	float loss_scale;
 	float inv_n_total;             // 1 / (B * n_out)  (losses/l2.h:62-64: n_total = n_elements / stride * dims)
 	float n_total;
+	long long* debug_clock;        // MLP_STAGE_CLOCKS builds only
 };
 
 // byte offset of 16-byte chunk `c` of row `r` inside a 128-byte-swizzled tile
@@ -139,25 +147,49 @@ __global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArg
 
 	uint32_t phase = 0;
 	uint32_t first_tile = 1;
+	[[maybe_unused]] uint32_t dbg_n = 0;
+	STAGE_CLOCK(a); // 0: setup done
 	float loss_acc = 0.f;
 	const uint32_t row = tid;
+
+	// input tile prefetch: 128 rows x cpr 16-byte chunks, chunk q = tid + 128 j (coalesced), held in registers one tile ahead
+	const uint32_t cpr = E / 8;
+	uint4 xr[8];
+	auto load_x = [&](uint32_t tile) {
+		const uint4* src = reinterpret_cast<const uint4*>(a.input + (size_t)tile * MLP_TILE * E);
+#pragma unroll
+		for (uint32_t j = 0; j < 8; ++j) if (j < cpr) xr[j] = __ldg(src + tid + 128 * j);
+	};
+	if (blockIdx.x < a.n_tiles) load_x(blockIdx.x);
 
 	for (uint32_t tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
 		const size_t sample0 = (size_t)tile * MLP_TILE;
 		// ---- input tile -> ACT[0] ------------------------------------------------------------------
-		{
-			const uint32_t cpr = E / 8;
-			const uint4* src = reinterpret_cast<const uint4*>(a.input + sample0 * E);
-			for (uint32_t q = tid; q < MLP_TILE * cpr; q += 128) {
-				const uint32_t r = q / cpr, c = q % cpr;
-				*reinterpret_cast<uint4*>(act + sw128(r, c)) = __ldg(src + q);
+#pragma unroll
+		for (uint32_t j = 0; j < 8; ++j) {
+			if (j < cpr) {
+				const uint32_t q = tid + 128 * j, r = q / cpr, c = q % cpr;
+				sts128(act_addr + sw128(r, c), xr[j]);
 			}
 		}
+		STAGE_CLOCK(a); // E: epilogue math + sts issued
 		fence_proxy_async_smem();
 		tc_fence_before();
 		__syncthreads();
+		STAGE_CLOCK(a); // S: fenced + synced
+		if (tile + gridDim.x < a.n_tiles) load_x(tile + gridDim.x); // in flight during the whole chain of this tile
+		// per-row side inputs, requested now and consumed after the forward chain
+		float tgt[4] = {0.f, 0.f, 0.f, 0.f};
+		uint4 dy_in[2];
+		if (MODE == MODE_TRAIN) {
+#pragma unroll
+			for (uint32_t j = 0; j < 4; ++j) if (j < a.n_out) tgt[j] = __ldg(a.target + (sample0 + row) * a.n_out + j);
+		}
+		if (MODE == MODE_BACKWARD) {
+			const uint4* d4 = reinterpret_cast<const uint4*>(a.dL_doutput + (sample0 + row) * MLP_OUT);
+			dy_in[0] = __ldg(d4); dy_in[1] = __ldg(d4 + 1);
+		}
 
-		uint64_t relu_mask[H];
 		// ---- forward hidden layers -----------------------------------------------------------------
 #pragma unroll
 		for (uint32_t k = 0; k < H; ++k) {
@@ -171,33 +203,32 @@ __global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArg
 				umma_commit(bar);
 			}
 			mbar_wait(bar, phase); phase ^= 1;
+			STAGE_CLOCK(a); // W: MMA complete
 			tc_fence_after();
-			uint64_t mask = 0;
-			uint8_t* dst = act + (k + 1) * TILE_BYTES;
+			const uint32_t dst = act_addr + (k + 1) * TILE_BYTES;
+			uint32_t v0[32], v1[32];
+			tmem_ld32(t_acc + lane_off, v0);
+			tmem_ld32(t_acc + lane_off + 32, v1);
+			tmem_ld_wait();
 #pragma unroll
-			for (int half_i = 0; half_i < 2; ++half_i) {
-				uint32_t v[32];
-				tmem_ld32(t_acc + lane_off + half_i * 32, v);
-				tmem_ld_wait();
+			for (int c = 0; c < 4; ++c) {
+				uint32_t pk[4];
 #pragma unroll
-				for (int c = 0; c < 4; ++c) {
-					uint32_t pk[4];
-#pragma unroll
-					for (int j = 0; j < 4; ++j) {
-						float x0 = __uint_as_float(v[c * 8 + 2 * j]), x1 = __uint_as_float(v[c * 8 + 2 * j + 1]);
-						x0 = fmaxf(x0, 0.f); x1 = fmaxf(x1, 0.f);
-						pk[j] = pack_h2(x0, x1);
-						// ReLU' from the stored (fp16) post-activation > 0, like common_device.h:243-248
-						if (pk[j] & 0x00007FFFu) mask |= 1ull << (half_i * 32 + c * 8 + 2 * j);
-						if (pk[j] & 0x7FFF0000u) mask |= 1ull << (half_i * 32 + c * 8 + 2 * j + 1);
-					}
-					*reinterpret_cast<uint4*>(dst + sw128(row, half_i * 4 + c)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-				}
+				for (int j = 0; j < 4; ++j) pk[j] = h2_relu(pack_h2(__uint_as_float(v0[c * 8 + 2 * j]), __uint_as_float(v0[c * 8 + 2 * j + 1])));
+				sts128(dst + sw128(row, c), pk[0], pk[1], pk[2], pk[3]);
 			}
-			relu_mask[k] = mask;
+#pragma unroll
+			for (int c = 0; c < 4; ++c) {
+				uint32_t pk[4];
+#pragma unroll
+				for (int j = 0; j < 4; ++j) pk[j] = h2_relu(pack_h2(__uint_as_float(v1[c * 8 + 2 * j]), __uint_as_float(v1[c * 8 + 2 * j + 1])));
+				sts128(dst + sw128(row, 4 + c), pk[0], pk[1], pk[2], pk[3]);
+			}
+			STAGE_CLOCK(a); // E: epilogue math + sts issued
 			fence_proxy_async_smem();
 			tc_fence_before();
 			__syncthreads();
+			STAGE_CLOCK(a); // S: fenced + synced
 		}
 		// ---- output layer --------------------------------------------------------------------------
 		if (tid == 0) {
@@ -208,6 +239,7 @@ __global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArg
 			umma_commit(bar);
 		}
 		mbar_wait(bar, phase); phase ^= 1;
+		STAGE_CLOCK(a); // W: MMA complete
 		tc_fence_after();
 		{
 			uint32_t v[16];
@@ -235,7 +267,7 @@ __global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArg
 					float g = 0.f;
 					if ((uint32_t)j < a.n_out) {
 						const float pred = __half2float(yh[j]);
-						const float diff = pred - __ldg(a.target + s * a.n_out + j);
+						const float diff = pred - (j < 4 ? tgt[j < 4 ? j : 0] : __ldg(a.target + s * a.n_out + j));
 						if (a.loss_type == LOSS_RELATIVE_L2) {
 							const float denom = pred * pred + 0.01f;
 							loss_acc += diff * diff / denom / a.n_total;
@@ -249,19 +281,20 @@ __global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArg
 					dy[j] = __float2half(g);
 				}
 				const uint4* d4 = reinterpret_cast<const uint4*>(dy);
-				*reinterpret_cast<uint4*>(gbuf + sw128(row, 0)) = d4[0];
-				*reinterpret_cast<uint4*>(gbuf + sw128(row, 1)) = d4[1];
+				sts128(g_addr + sw128(row, 0), d4[0]);
+				sts128(g_addr + sw128(row, 1), d4[1]);
 			}
 			if (MODE == MODE_BACKWARD) {
-				const uint4* d4 = reinterpret_cast<const uint4*>(a.dL_doutput + s * MLP_OUT);
-				*reinterpret_cast<uint4*>(gbuf + sw128(row, 0)) = __ldg(d4);
-				*reinterpret_cast<uint4*>(gbuf + sw128(row, 1)) = __ldg(d4 + 1);
+				sts128(g_addr + sw128(row, 0), dy_in[0]);
+				sts128(g_addr + sw128(row, 1), dy_in[1]);
 			}
 		}
 		if constexpr (TRAIN) {
+			STAGE_CLOCK(a); // E: epilogue math + sts issued
 			fence_proxy_async_smem();
 			tc_fence_before();
 			__syncthreads();
+			STAGE_CLOCK(a); // S: fenced + synced
 			const bool want_dw = a.dW_partials != nullptr;
 			uint32_t gcur = 0; // G[gcur] holds the gradient w.r.t. the pre-activation feeding weight matrix `k+1`
 			// ---- backward through output matmul and hidden matmuls: k = H .. 1 ------------------------
@@ -286,31 +319,39 @@ __global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArg
 					umma_commit(bar);
 				}
 				mbar_wait(bar, phase); phase ^= 1;
+				STAGE_CLOCK(a); // W: MMA complete
 				tc_fence_after();
-				const uint64_t mask = relu_mask[k - 1];
-				uint8_t* dst = gbuf + (gcur ^ 1) * TILE_BYTES;
+				// ReLU' from this row's stored post-activation ACT[k] (fp16 > 0), applied to the packed fp16 gradient
+				const uint32_t dst = g_addr + (gcur ^ 1) * TILE_BYTES;
+				const uint32_t asrc = act_addr + k * TILE_BYTES;
+				uint32_t v0[32], v1[32];
+				tmem_ld32(t_acc + lane_off, v0);
+				tmem_ld32(t_acc + lane_off + 32, v1);
+				tmem_ld_wait();
 #pragma unroll
-				for (int half_i = 0; half_i < 2; ++half_i) {
-					uint32_t v[32];
-					tmem_ld32(t_acc + lane_off + half_i * 32, v);
-					tmem_ld_wait();
+				for (int c = 0; c < 4; ++c) {
+					const uint4 av = lds128(asrc + sw128(row, c));
+					const uint32_t aw[4] = {av.x, av.y, av.z, av.w};
+					uint32_t pk[4];
 #pragma unroll
-					for (int c = 0; c < 4; ++c) {
-						uint32_t pk[4];
+					for (int j = 0; j < 4; ++j) pk[j] = h2_mask_mul(pack_h2(__uint_as_float(v0[c * 8 + 2 * j]), __uint_as_float(v0[c * 8 + 2 * j + 1])), aw[j]);
+					sts128(dst + sw128(row, c), pk[0], pk[1], pk[2], pk[3]);
+				}
 #pragma unroll
-						for (int j = 0; j < 4; ++j) {
-							const int col = half_i * 32 + c * 8 + 2 * j;
-							const float x0 = ((mask >> col) & 1ull) ? __uint_as_float(v[c * 8 + 2 * j]) : 0.f;
-							const float x1 = ((mask >> (col + 1)) & 1ull) ? __uint_as_float(v[c * 8 + 2 * j + 1]) : 0.f;
-							pk[j] = pack_h2(x0, x1);
-						}
-						*reinterpret_cast<uint4*>(dst + sw128(row, half_i * 4 + c)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-					}
+				for (int c = 0; c < 4; ++c) {
+					const uint4 av = lds128(asrc + sw128(row, 4 + c));
+					const uint32_t aw[4] = {av.x, av.y, av.z, av.w};
+					uint32_t pk[4];
+#pragma unroll
+					for (int j = 0; j < 4; ++j) pk[j] = h2_mask_mul(pack_h2(__uint_as_float(v1[c * 8 + 2 * j]), __uint_as_float(v1[c * 8 + 2 * j + 1])), aw[j]);
+					sts128(dst + sw128(row, 4 + c), pk[0], pk[1], pk[2], pk[3]);
 				}
 				gcur ^= 1;
+				STAGE_CLOCK(a); // E: epilogue math + sts issued
 				fence_proxy_async_smem();
 				tc_fence_before();
 				__syncthreads();
+				STAGE_CLOCK(a); // S: fenced + synced
 			}
 			// ---- input matmul: dW_in (transposed accumulator) and dL/d(input) ---------------------------
 			const bool want_dx = a.dL_dinput != nullptr;
@@ -327,6 +368,7 @@ __global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArg
 					umma_commit(bar);
 				}
 				mbar_wait(bar, phase); phase ^= 1;
+				STAGE_CLOCK(a); // W: MMA complete
 				tc_fence_after();
 				if (want_dx) {
 					__half* dst = a.dL_dinput + (sample0 + row) * E;

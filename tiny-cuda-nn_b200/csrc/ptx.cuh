@@ -107,6 +107,30 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+// ---- shared memory by 32-bit address (explicit .shared space: STS/LDS instead of generic ST/LD) ----
+__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+	asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ void sts128(uint32_t addr, uint4 v) { sts128(addr, v.x, v.y, v.z, v.w); }
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+	uint4 v;
+	asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+	return v;
+}
+// packed fp16x2 helpers on raw 32-bit registers
+__device__ __forceinline__ uint32_t h2_relu(uint32_t x) {
+	const __half2 z = __floats2half2_rn(0.f, 0.f);
+	__half2 r = __hmax2(*reinterpret_cast<__half2*>(&x), z);
+	return *reinterpret_cast<uint32_t*>(&r);
+}
+// g * (a > 0 ? 1 : 0) per half: ReLU backward from the stored post-activation (common_device.h:243-248)
+__device__ __forceinline__ uint32_t h2_mask_mul(uint32_t g, uint32_t act) {
+	const __half2 z = __floats2half2_rn(0.f, 0.f);
+	__half2 m = __hgt2(*reinterpret_cast<__half2*>(&act), z); // 1.0 / 0.0
+	__half2 r = __hmul2(*reinterpret_cast<__half2*>(&g), m);
+	return *reinterpret_cast<uint32_t*>(&r);
+}
+
 // ---- misc ----------------------------------------------------------------------------------------
 // fp16x2 reduction into global memory without return value (the op the reference scatter uses, vec.h:326-333)
 __device__ __forceinline__ void red_add_h2(__half* addr, __half2 v) {

@@ -283,7 +283,7 @@ static Workspace carve(const tcnn_b200_plan* p, uint32_t B, void* ws) {
 	Workspace w;
 	uint8_t* b = (uint8_t*)ws;
 	const size_t act = align256((size_t)B * p->info.encoded_width * 2);
-	const uint32_t max_ctas = (uint32_t)p->n_sms * 3;
+	const uint32_t max_ctas = (uint32_t)p->n_sms * 4;
 	w.encoded = (__half*)b; b += act;
 	w.dL_denc = (__half*)b; b += act;
 	w.dw_partials = (float*)b; b += align256((size_t)max_ctas * p->info.n_params_mlp * 4);
@@ -294,7 +294,7 @@ static Workspace carve(const tcnn_b200_plan* p, uint32_t B, void* ws) {
 extern "C" size_t tcnn_b200_workspace_bytes(const tcnn_b200_plan* plan, uint32_t B) {
 	if (!plan) return 0;
 	const size_t act = align256((size_t)B * plan->info.encoded_width * 2);
-	const uint32_t max_ctas = (uint32_t)plan->n_sms * 3;
+	const uint32_t max_ctas = (uint32_t)plan->n_sms * 4;
 	return 2 * act + align256((size_t)max_ctas * plan->info.n_params_mlp * 4) + align256((size_t)max_ctas * 4) + align256(replica_bytes(plan)) + 256;
 }
 
@@ -362,17 +362,23 @@ extern "C" int tcnn_b200_cast_params(void* stream_, uint64_t n, const float* par
 }
 
 // ---- grid encoding ------------------------------------------------------------------------------------
+// NOTE (measured, r01): the gather kernel depends on a large L1 (adjacent corners and the coarse levels hit in L1);
+// forcing the max-shared carve-out so that it could co-reside with the MLP kernel doubled its time (48 -> 102 us).
+#define GRID_LAUNCH(KERNEL, DD, FF, grid_dim, stream, ...)                                                        \
+	do {                                                                                                          \
+		KERNEL<DD, FF><<<grid_dim, 256, 0, stream>>>(__VA_ARGS__);                                                \
+	} while (0)
 #define GRID_DISPATCH(KERNEL, plan, grid_dim, stream, ...)                                                        \
 	do {                                                                                                          \
 		const uint32_t D_ = (plan)->info.n_input_dims, F_ = (plan)->info.n_features_per_level;                   \
-		if (D_ == 2 && F_ == 2) KERNEL<2, 2><<<grid_dim, 256, 0, stream>>>(__VA_ARGS__);                          \
-		else if (D_ == 2 && F_ == 4) KERNEL<2, 4><<<grid_dim, 256, 0, stream>>>(__VA_ARGS__);                     \
-		else if (D_ == 2 && F_ == 8) KERNEL<2, 8><<<grid_dim, 256, 0, stream>>>(__VA_ARGS__);                     \
-		else if (D_ == 3 && F_ == 2) KERNEL<3, 2><<<grid_dim, 256, 0, stream>>>(__VA_ARGS__);                     \
-		else if (D_ == 3 && F_ == 4) KERNEL<3, 4><<<grid_dim, 256, 0, stream>>>(__VA_ARGS__);                     \
-		else if (D_ == 3 && F_ == 8) KERNEL<3, 8><<<grid_dim, 256, 0, stream>>>(__VA_ARGS__);                     \
-		else if (D_ == 4 && F_ == 2) KERNEL<4, 2><<<grid_dim, 256, 0, stream>>>(__VA_ARGS__);                     \
-		else if (D_ == 4 && F_ == 4) KERNEL<4, 4><<<grid_dim, 256, 0, stream>>>(__VA_ARGS__);                     \
+		if (D_ == 2 && F_ == 2) GRID_LAUNCH(KERNEL, 2, 2, grid_dim, stream, __VA_ARGS__);                  \
+		else if (D_ == 2 && F_ == 4) GRID_LAUNCH(KERNEL, 2, 4, grid_dim, stream, __VA_ARGS__);             \
+		else if (D_ == 2 && F_ == 8) GRID_LAUNCH(KERNEL, 2, 8, grid_dim, stream, __VA_ARGS__);             \
+		else if (D_ == 3 && F_ == 2) GRID_LAUNCH(KERNEL, 3, 2, grid_dim, stream, __VA_ARGS__);             \
+		else if (D_ == 3 && F_ == 4) GRID_LAUNCH(KERNEL, 3, 4, grid_dim, stream, __VA_ARGS__);             \
+		else if (D_ == 3 && F_ == 8) GRID_LAUNCH(KERNEL, 3, 8, grid_dim, stream, __VA_ARGS__);             \
+		else if (D_ == 4 && F_ == 2) GRID_LAUNCH(KERNEL, 4, 2, grid_dim, stream, __VA_ARGS__);             \
+		else if (D_ == 4 && F_ == 4) GRID_LAUNCH(KERNEL, 4, 4, grid_dim, stream, __VA_ARGS__);             \
 		else FAIL("unsupported (n_input_dims, n_features_per_level)");                                            \
 	} while (0)
 
@@ -382,21 +388,32 @@ static void encode_forward(const tcnn_b200_plan* plan, cudaStream_t stream, uint
 	GRID_DISPATCH(grid_forward_kernel, plan, g, stream, plan->grid, B, x, grid, encoded);
 	launch_check("grid_forward_kernel");
 }
-static void encode_backward(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t B, const float* x, const __half* dL_denc, __half* grid_grads, int zero_first, __half* replicas) {
+// backward in three pieces so that several batch chunks can scatter concurrently between one prepare and one finish
+static void backward_prepare(const tcnn_b200_plan* plan, cudaStream_t stream, const GridParams& gp, __half* grid_grads, int zero_first, __half* replicas) {
 	ProfileScope prof(plan, stream, PK_GRID_BWD);
 	if (zero_first) CUDA_OK(cudaMemsetAsync(grid_grads, 0, plan->info.n_params_grid * 2, stream));
-	const GridParams gp = backward_params(plan, B, replicas != nullptr);
-	const uint32_t F = plan->info.n_features_per_level;
-	if (gp.rep_entries) CUDA_OK(cudaMemsetAsync(replicas, 0, (size_t)gp.rep_entries * F * 2 * gp.n_replicas, stream));
+	if (gp.rep_entries) CUDA_OK(cudaMemsetAsync(replicas, 0, (size_t)gp.rep_entries * plan->info.n_features_per_level * 2 * gp.n_replicas, stream));
+}
+static void backward_scatter(const tcnn_b200_plan* plan, cudaStream_t stream, const GridParams& gp, uint32_t B, const float* x, const __half* dL_denc, __half* grid_grads, __half* replicas) {
+	ProfileScope prof(plan, stream, PK_GRID_BWD);
 	const uint32_t n_chunks = (plan->grid.n_features + 7) / 8; // padding chunks carry no gradient
 	const dim3 g((B + 255) / 256, n_chunks, 1);
 	GRID_DISPATCH(grid_backward_kernel, plan, g, stream, gp, B, x, dL_denc, grid_grads, replicas);
 	launch_check("grid_backward_kernel");
-	if (gp.rep_entries) {
-		const uint32_t pairs = gp.rep_entries * F / 2;
-		grid_replica_reduce_kernel<<<(pairs + 255) / 256, 256, 0, stream>>>(gp, F, replicas, grid_grads);
-		launch_check("grid_replica_reduce_kernel");
-	}
+}
+static void backward_finish(const tcnn_b200_plan* plan, cudaStream_t stream, const GridParams& gp, __half* grid_grads, __half* replicas) {
+	if (!gp.rep_entries) return;
+	ProfileScope prof(plan, stream, PK_GRID_BWD);
+	const uint32_t F = plan->info.n_features_per_level;
+	const uint32_t pairs = gp.rep_entries * F / 2;
+	grid_replica_reduce_kernel<<<(pairs + 63) / 64, 64, 0, stream>>>(gp, F, replicas, grid_grads);
+	launch_check("grid_replica_reduce_kernel");
+}
+static void encode_backward(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t B, const float* x, const __half* dL_denc, __half* grid_grads, int zero_first, __half* replicas) {
+	const GridParams gp = backward_params(plan, B, replicas != nullptr);
+	backward_prepare(plan, stream, gp, grid_grads, zero_first, replicas);
+	backward_scatter(plan, stream, gp, B, x, dL_denc, grid_grads, replicas);
+	backward_finish(plan, stream, gp, grid_grads, replicas);
 }
 
 extern "C" int tcnn_b200_encode_forward(const tcnn_b200_plan* plan, void* stream, uint32_t B, const float* x, const void* grid_params, void* encoded) {
@@ -552,11 +569,20 @@ extern "C" int tcnn_b200_training_fwd_bwd(const tcnn_b200_plan* plan, void* stre
 	API_BEGIN
 	require_device(plan); check_batch(B);
 	CHECK(x && target && params && grads && workspace, "null argument");
-	cudaStream_t stream = (cudaStream_t)stream_;
+	cudaStream_t main = (cudaStream_t)stream_;
 	const Workspace w = carve(plan, B, workspace);
+	const tcnn_b200_info& in = plan->info;
 	const __half* p = (const __half*)params;
 	__half* g = (__half*)grads;
-	encode_forward(plan, stream, B, x, p + plan->info.n_params_mlp, w.encoded);
+	__half* gg = g + in.n_params_mlp;
+	const GridParams gp = backward_params(plan, B, true);
+
+	// One stream, back to back.  A two-chunk pipeline over a high-priority stream (MLP of chunk k overlapping the gather of
+	// chunk k+1 / scatter of chunk k-1) was measured and dropped (r01): the MLP CTAs need the max-shared carve-out and
+	// cannot become resident next to gather blocks running with the max-L1 carve-out, and giving the gather kernel the
+	// shared carve-out doubles its time.
+	const uint32_t n_chunks = 1;
+	uint32_t part_off[1] = {0}, part_cnt[1] = {mlp_grid_size(plan, B / MLP_TILE, true)};
 	MlpArgs a = base_mlp_args(plan, B, w.encoded, p);
 	a.target = target;
 	a.output = (__half*)output_fp16;
@@ -564,10 +590,12 @@ extern "C" int tcnn_b200_training_fwd_bwd(const tcnn_b200_plan* plan, void* stre
 	a.dW_partials = w.dw_partials;
 	a.loss_partials = w.loss_partials;
 	a.loss_scale = loss_scale;
-	const uint32_t grid = mlp_grid_size(plan, a.n_tiles, true);
-	launch_mlp<MODE_TRAIN>(plan, stream, a, grid);
-	mlp_finalize(plan, stream, grid, w, g, loss_out, loss_out != nullptr);
-	encode_backward(plan, stream, B, x, w.dL_denc, g + plan->info.n_params_mlp, zero_grid_grads, w.replicas);
+	backward_prepare(plan, main, gp, gg, zero_grid_grads, w.replicas);
+	encode_forward(plan, main, B, x, p + in.n_params_mlp, w.encoded);
+	launch_mlp<MODE_TRAIN>(plan, main, a, part_cnt[0]);
+	backward_scatter(plan, main, gp, B, x, w.dL_denc, gg, w.replicas);
+	mlp_finalize(plan, main, part_off[n_chunks - 1] + part_cnt[n_chunks - 1], w, g, loss_out, loss_out != nullptr);
+	backward_finish(plan, main, gp, gg, w.replicas);
 	API_END
 }
 

@@ -89,9 +89,8 @@ class NativeModule:
 
 class _module_function(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, native, x, params, loss_scale):
+    def forward(ctx, native, x, params, loss_scale, need_ctx):
         ctx.set_materialize_grads(False)
-        need_ctx = torch.is_grad_enabled() and (params.requires_grad or x.requires_grad)
         ws, output = native.fwd(x, params, need_ctx)
         ctx.save_for_backward(x, params)
         ctx.native, ctx.ws, ctx.loss_scale = native, ws, loss_scale
@@ -100,7 +99,7 @@ class _module_function(torch.autograd.Function):
     @staticmethod
     def backward(ctx, doutput):
         if doutput is None:
-            return None, None, None, None
+            return None, None, None, None, None
         x, params = ctx.saved_tensors
         if ctx.needs_input_grad[1]:
             raise RuntimeError("dL/dinput of the grid encoding (kernel_grid_backward_input) is not implemented in tcnn_b200 yet")
@@ -108,7 +107,7 @@ class _module_function(torch.autograd.Function):
             scaled = (doutput.to(torch.float) * ctx.loss_scale).to(torch.half).contiguous()
             g = ctx.native.bwd(ctx.ws, x, params, scaled, ctx.needs_input_grad[2])
             g = None if g is None else g / ctx.loss_scale
-        return None, None, g, None
+        return None, None, g, None, None
 
 
 class Module(torch.nn.Module):
@@ -134,6 +133,7 @@ class Module(torch.nn.Module):
             x_padded.to(torch.float).contiguous(),
             self.params.to(torch.half).contiguous(),
             self.loss_scale,
+            torch.is_grad_enabled() and (self.params.requires_grad or x.requires_grad),  # grad mode is off inside Function.forward
         )
         return output[:batch_size, : self.n_output_dims]
 
