@@ -119,6 +119,16 @@ int tcnn_b200_adam_step(const tcnn_b200_plan* plan, void* stream, float grad_div
                         float* params_fp32, void* params_fp16, void* grads_fp16, float* first_moments, float* second_moments,
                         uint32_t* param_steps, int zero_grid_grads);
 
+/* Trainer::training_step with run_optimizer = true (trainer.h:163-190) as ONE call for a single GPU: the work of
+ * tcnn_b200_training_fwd_bwd followed by tcnn_b200_adam_step, scheduled so that the Adam update of a finished group of
+ * grid levels overlaps the gradient scatter of the next group (internal second stream, joined before returning to the
+ * caller's stream; capturable into a CUDA graph).  The grid part of grads_fp16 must be zero on entry and is zero again
+ * on exit.  Data-parallel training uses the two separate calls with the gradient all-reduce in between. */
+int tcnn_b200_training_step(const tcnn_b200_plan* plan, void* stream, uint32_t batch_size, const float* x, const float* target,
+                            float loss_scale, uint32_t adam_step_count, float* params_fp32, void* params_fp16, void* grads_fp16,
+                            float* first_moments, float* second_moments, uint32_t* param_steps, float* loss_out, void* output_fp16,
+                            void* workspace);
+
 /* Per-kernel device timing for bench.py's roofline line (no reference counterpart): when enabled, every kernel launch
  * of this plan is bracketed by CUDA events on its launch stream.  profile_read synchronises them and returns the summed
  * milliseconds and launch counts for kind 0..4 = grid forward, MLP, MLP finalize, grid backward (+memset), Adam. */

@@ -297,6 +297,25 @@ def test_trainer_converges_and_matches_reference_order_of_magnitude(dev):
     assert losses[-1] < 0.05 * losses[0], losses
 
 
+def test_fused_step_equals_separate_calls(dev):
+    """tcnn_b200_training_step (Adam overlapped with the scatter on a second stream) == fwd_bwd followed by adam_step."""
+    import tinycudann as tcnn
+    a = tcnn.create_from_config(2, 3, common.CONFIG_1, seed=1337, device=dev).trainer
+    b = tcnn.create_from_config(2, 3, common.CONFIG_1, seed=1337, device=dev).trainer
+    b.use_fused_step = False
+    B = 1 << 16
+    for i in range(3):
+        x_np, t_np = common.synth_inputs(B, 2, 3, seed=40 + i)
+        x, t = torch.from_numpy(x_np).to(dev), torch.from_numpy(t_np).to(dev)
+        a.training_step(x, t); b.training_step(x, t)
+        assert abs(a.loss() - b.loss()) <= 1e-5 * abs(b.loss())
+    pa, pb = a.params_full_precision.cpu().numpy(), b.params_full_precision.cpu().numpy()
+    p0 = O.init_params(*reversed(common.oracle_configs(common.CONFIG_1, 2, 3)), 1337, True)
+    assert common.rel_l2(pa - p0, pb - p0) < 2e-2  # fp16 atomics order differs run to run
+    assert np.array_equal(a.param_steps.cpu().numpy(), b.param_steps.cpu().numpy()) or np.mean(a.param_steps.cpu().numpy() != b.param_steps.cpu().numpy()) < 1e-3
+    assert not a.param_gradients[int(a.info.n_params_mlp):].any().item()
+
+
 def test_batch_size_must_be_multiple_of_256(dev):
     import tinycudann as tcnn
     model = tcnn.create_from_config(2, 3, common.CONFIG_1, seed=1, device=dev)

@@ -121,9 +121,19 @@ __device__ __forceinline__ uint4 encode_chunk(const GridParams& gp, const __half
 			w[c] = weight;
 		}
 		if constexpr (F == 2) {
+			// Corners c and c+1 differ in dim 0 only.  For even cells their entries are the two halves of one aligned 8-byte
+			// slot on every level (dense: index and index+1; coherent-prime hash: prime[0] = 1 so the indices differ in bit
+			// 0 only), so one 8-byte load serves both; otherwise the second corner gets its own (predicated) load.
 			__half2 val[NC];
 #pragma unroll
-			for (int c = 0; c < NC; ++c) val[c] = __ldg(reinterpret_cast<const __half2*>(table) + idx[c]);
+			for (int c = 0; c < NC; c += 2) {
+				const bool paired = ((idx[c] ^ idx[c + 1]) == 1u);
+				const uint2 a = __ldg(reinterpret_cast<const uint2*>(table) + (idx[c] >> 1));
+				uint32_t own = (idx[c] & 1u) ? a.y : a.x, other = (idx[c] & 1u) ? a.x : a.y;
+				if (!paired) other = __ldg(reinterpret_cast<const uint32_t*>(table) + idx[c + 1]);
+				val[c] = *reinterpret_cast<__half2*>(&own);
+				val[c + 1] = *reinterpret_cast<__half2*>(&other);
+			}
 			__half2 r = __floats2half2_rn(0.f, 0.f);
 #pragma unroll
 			for (int c = 0; c < NC; ++c) r = __hfma2(__half2half2(__float2half(w[c])), val[c], r);
@@ -131,7 +141,13 @@ __device__ __forceinline__ uint4 encode_chunk(const GridParams& gp, const __half
 		} else if constexpr (F == 4) {
 			uint2 val[NC];
 #pragma unroll
-			for (int c = 0; c < NC; ++c) val[c] = __ldg(reinterpret_cast<const uint2*>(table) + idx[c]);
+			for (int c = 0; c < NC; c += 2) { // same pairing with 16-byte slots
+				const bool paired = ((idx[c] ^ idx[c + 1]) == 1u);
+				const uint4 a = __ldg(reinterpret_cast<const uint4*>(table) + (idx[c] >> 1));
+				val[c] = (idx[c] & 1u) ? make_uint2(a.z, a.w) : make_uint2(a.x, a.y);
+				val[c + 1] = (idx[c] & 1u) ? make_uint2(a.x, a.y) : make_uint2(a.z, a.w);
+				if (!paired) val[c + 1] = __ldg(reinterpret_cast<const uint2*>(table) + idx[c + 1]);
+			}
 			__half2 r0 = __floats2half2_rn(0.f, 0.f), r1 = r0;
 #pragma unroll
 			for (int c = 0; c < NC; ++c) {
@@ -183,13 +199,13 @@ __global__ void __launch_bounds__(256) grid_forward_kernel(const __grid_constant
 // Same arithmetic as grid.h:248-318: product (half)weight * grad rounded to fp16, then red.add.noftz.f16x2.
 template <int D, int F>
 __global__ void __launch_bounds__(256) grid_backward_kernel(const __grid_constant__ GridParams gp, uint32_t B,
-	const float* __restrict__ x, const __half* __restrict__ dL_denc, __half* __restrict__ grid_grad, __half* __restrict__ replicas) {
+	const float* __restrict__ x, const __half* __restrict__ dL_denc, __half* __restrict__ grid_grad, __half* __restrict__ replicas, uint32_t chunk_begin) {
 	static_assert(F == 2 || F == 4 || F == 8, "fp16 gradient scatter needs F >= 2 (grid.h:655-666)");
 	constexpr int LEVELS_PER_CHUNK = 8 / F;
 	constexpr int NC = 1 << D;
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= B) return;
-	const uint32_t chunk = blockIdx.y;
+	const uint32_t chunk = chunk_begin + blockIdx.y;
 	float p[D];
 	load_position<D>(x, i, p);
 	union { uint4 v; __half2 h2[4]; } g;
@@ -207,6 +223,7 @@ __global__ void __launch_bounds__(256) grid_backward_kernel(const __grid_constan
 		__half* gtable = lv.replicated
 			? replicas + ((size_t)(blockIdx.x & (gp.n_replicas - 1)) * gp.rep_entries + lv.rep_offset) * F
 			: grid_grad + (size_t)lv.offset * F;
+		uint32_t idx[NC]; __half2 wh[NC];
 #pragma unroll
 		for (int c = 0; c < NC; ++c) {
 			float weight = 1.0f; uint32_t pg[D];
@@ -215,12 +232,36 @@ __global__ void __launch_bounds__(256) grid_backward_kernel(const __grid_constan
 				if ((c & (1 << d)) == 0) { weight *= 1.0f - frac[d]; pg[d] = cell[d]; }
 				else { weight *= frac[d]; pg[d] = cell[d] + 1u; }
 			}
-			const uint32_t idx = grid_index_dev<D>(lv, pg);
-			const __half2 wh = __half2half2(__float2half(weight));
+			idx[c] = grid_index_dev<D>(lv, pg);
+			wh[c] = __half2half2(__float2half(weight));
+		}
+		// One vector reduction covers the aligned slot {idx & ~1, idx | 1} (see the forward kernel): for even cells it carries
+		// both dim-0 neighbours, for odd cells the other half adds +0 and the neighbour gets its own (predicated) reduction.
+		// 1.5 L2 reduction ops per corner pair instead of 2 (the scatter is bound by L2 atomic throughput).
+		if constexpr (F == 2) {
 #pragma unroll
-			for (int k = 0; k < F / 2; ++k) {
-				red_add_h2(gtable + (size_t)idx * F + 2 * k, __hmul2(wh, g.h2[s * (F / 2) + k]));
+			for (int c = 0; c < NC; c += 2) {
+				const uint32_t v0 = h2_bits(__hmul2(wh[c], g.h2[s])), v1 = h2_bits(__hmul2(wh[c + 1], g.h2[s]));
+				const bool paired = ((idx[c] ^ idx[c + 1]) == 1u), odd = (idx[c] & 1u) != 0;
+				const uint32_t nb = paired ? v1 : 0u;
+				red_add_h2x2(gtable + (size_t)(idx[c] & ~1u) * 2, odd ? nb : v0, odd ? v0 : nb);
+				if (!paired) red_add_h2(gtable + (size_t)idx[c + 1] * 2, *reinterpret_cast<const __half2*>(&v1));
 			}
+		} else if constexpr (F == 4) {
+#pragma unroll
+			for (int c = 0; c < NC; c += 2) {
+				const uint32_t a0 = h2_bits(__hmul2(wh[c], g.h2[2 * s])), a1 = h2_bits(__hmul2(wh[c], g.h2[2 * s + 1]));
+				const uint32_t b0 = h2_bits(__hmul2(wh[c + 1], g.h2[2 * s])), b1 = h2_bits(__hmul2(wh[c + 1], g.h2[2 * s + 1]));
+				const bool paired = ((idx[c] ^ idx[c + 1]) == 1u), odd = (idx[c] & 1u) != 0;
+				const uint32_t n0 = paired ? b0 : 0u, n1 = paired ? b1 : 0u;
+				red_add_h2x4(gtable + (size_t)(idx[c] & ~1u) * 4, odd ? n0 : a0, odd ? n1 : a1, odd ? a0 : n0, odd ? a1 : n1);
+				if (!paired) red_add_h2x2(gtable + (size_t)idx[c + 1] * 4, b0, b1);
+			}
+		} else { // F == 8: one 16-byte reduction per corner
+#pragma unroll
+			for (int c = 0; c < NC; ++c)
+				red_add_h2x4(gtable + (size_t)idx[c] * 8, h2_bits(__hmul2(wh[c], g.h2[0])), h2_bits(__hmul2(wh[c], g.h2[1])),
+					h2_bits(__hmul2(wh[c], g.h2[2])), h2_bits(__hmul2(wh[c], g.h2[3])));
 		}
 	}
 }

@@ -92,13 +92,14 @@ __global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArg
 	uint8_t* w_out = w_hid + (H - 1) * 8192;                    // [16 out][128 B]
 	uint8_t* tail = w_out + 2048;
 	uint64_t* bar = reinterpret_cast<uint64_t*>(tail);
+	uint64_t* bar2 = reinterpret_cast<uint64_t*>(tail + 8); // completion of the weight-gradient MMAs of a tile's last stage
 	uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tail + 16);
 	float* red_buf = reinterpret_cast<float*>(tail + 32);       // 4 floats
 
 	// ---- one-time setup ---------------------------------------------------------------------------
 	constexpr uint32_t tmem_cols = mlp_tmem_cols((int)H, TRAIN);
 	if (warp == 0) tmem_alloc(tmem_slot, tmem_cols);
-	if (tid == 32) { mbar_init(bar, 1); mbar_fence_init(); }
+	if (tid == 32) { mbar_init(bar, 1); mbar_init(bar2, 1); mbar_fence_init(); }
 
 	// weights: global row-major -> swizzled tiles (16-byte chunks, coalesced reads)
 	{
@@ -145,7 +146,8 @@ __global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArg
 	const uint32_t idesc_dx = make_idesc_f16(128, E, 0, 0);       // B = W_inT K-major
 	const uint32_t idesc_dw = make_idesc_f16(128, 64, 1, 1);      // both operands MN-major, K = 128 samples
 
-	uint32_t phase = 0;
+	uint32_t phase = 0, phase2 = 0;
+	bool pending2 = false; // a commit on bar2 has not been waited for yet
 	uint32_t first_tile = 1;
 	[[maybe_unused]] uint32_t dbg_n = 0;
 	STAGE_CLOCK(a); // 0: setup done
@@ -158,13 +160,14 @@ __global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArg
 	auto load_x = [&](uint32_t tile) {
 		const uint4* src = reinterpret_cast<const uint4*>(a.input + (size_t)tile * MLP_TILE * E);
 #pragma unroll
-		for (uint32_t j = 0; j < 8; ++j) if (j < cpr) xr[j] = __ldg(src + tid + 128 * j);
+		for (uint32_t j = 0; j < 8; ++j) if (j < cpr) xr[j] = ldg128_here(src + tid + 128 * j);
 	};
 	if (blockIdx.x < a.n_tiles) load_x(blockIdx.x);
 
 	for (uint32_t tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
 		const size_t sample0 = (size_t)tile * MLP_TILE;
 		// ---- input tile -> ACT[0] ------------------------------------------------------------------
+		if (pending2) { mbar_wait(bar2, phase2); phase2 ^= 1; pending2 = false; } // previous tile's dW_in MMA still reads ACT[0]
 #pragma unroll
 		for (uint32_t j = 0; j < 8; ++j) {
 			if (j < cpr) {
@@ -183,11 +186,11 @@ __global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArg
 		uint4 dy_in[2];
 		if (MODE == MODE_TRAIN) {
 #pragma unroll
-			for (uint32_t j = 0; j < 4; ++j) if (j < a.n_out) tgt[j] = __ldg(a.target + (sample0 + row) * a.n_out + j);
+			for (uint32_t j = 0; j < 4; ++j) if (j < a.n_out) tgt[j] = ldg_f32_here(a.target + (sample0 + row) * a.n_out + j);
 		}
 		if (MODE == MODE_BACKWARD) {
 			const uint4* d4 = reinterpret_cast<const uint4*>(a.dL_doutput + (sample0 + row) * MLP_OUT);
-			dy_in[0] = __ldg(d4); dy_in[1] = __ldg(d4 + 1);
+			dy_in[0] = ldg128_here(d4); dy_in[1] = ldg128_here(d4 + 1);
 		}
 
 		// ---- forward hidden layers -----------------------------------------------------------------
@@ -259,30 +262,31 @@ __global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArg
 				for (uint32_t j = 0; j < a.n_out; ++j) a.output_f32[s * a.n_out + j] = __half2float(yh[j]);
 			}
 			if (MODE == MODE_TRAIN) {
-				// loss on the fp16 prediction (the reference's network output is fp16), gradients as fp16 * loss_scale
+				// loss on the fp16 prediction (the reference's network output is fp16), gradients as fp16 * loss_scale.
+				// Same operation order as losses/l2.h:62-74 / relative_l2.h:62-75.
 				const __half* yh = reinterpret_cast<const __half*>(yk);
-				__half dy[16];
+				const bool relative = a.loss_type == LOSS_RELATIVE_L2;
+				auto loss_elem = [&](float pred, float target) -> float {
+					const float diff = pred - target;
+					float value = diff * diff, grad = 2.f * diff;
+					if (relative) { const float denom = pred * pred + 0.01f; value = value / denom; grad = grad / denom; }
+					loss_acc += value / a.n_total;
+					return a.loss_scale * grad / a.n_total;
+				};
+				float g4[4];
 #pragma unroll
-				for (int j = 0; j < 16; ++j) {
-					float g = 0.f;
-					if ((uint32_t)j < a.n_out) {
-						const float pred = __half2float(yh[j]);
-						const float diff = pred - (j < 4 ? tgt[j < 4 ? j : 0] : __ldg(a.target + s * a.n_out + j));
-						if (a.loss_type == LOSS_RELATIVE_L2) {
-							const float denom = pred * pred + 0.01f;
-							loss_acc += diff * diff / denom / a.n_total;
-							g = 2.f * diff / denom;
-						} else {
-							loss_acc += diff * diff / a.n_total;
-							g = 2.f * diff;
-						}
-						g = a.loss_scale * g / a.n_total;
+				for (uint32_t j = 0; j < 4; ++j) g4[j] = (j < a.n_out) ? loss_elem(__half2float(yh[j]), tgt[j]) : 0.f;
+				uint32_t dyk[8] = {pack_h2(g4[0], g4[1]), pack_h2(g4[2], g4[3]), 0u, 0u, 0u, 0u, 0u, 0u};
+				if (a.n_out > 4) { // rare: more than 4 outputs (targets not prefetched); statically indexed to stay in registers
+#pragma unroll
+					for (uint32_t j = 4; j < 16; j += 2) {
+						const float ga = (j < a.n_out) ? loss_elem(__half2float(yh[j]), __ldg(a.target + s * a.n_out + j)) : 0.f;
+						const float gb = (j + 1 < a.n_out) ? loss_elem(__half2float(yh[j + 1]), __ldg(a.target + s * a.n_out + j + 1)) : 0.f;
+						dyk[j / 2] = pack_h2(ga, gb);
 					}
-					dy[j] = __float2half(g);
 				}
-				const uint4* d4 = reinterpret_cast<const uint4*>(dy);
-				sts128(g_addr + sw128(row, 0), d4[0]);
-				sts128(g_addr + sw128(row, 1), d4[1]);
+				sts128(g_addr + sw128(row, 0), dyk[0], dyk[1], dyk[2], dyk[3]);
+				sts128(g_addr + sw128(row, 1), dyk[4], dyk[5], dyk[6], dyk[7]);
 			}
 			if (MODE == MODE_BACKWARD) {
 				sts128(g_addr + sw128(row, 0), dy_in[0]);
@@ -309,14 +313,15 @@ __global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArg
 					// dA_k[128 x 64] = G[128 x K] * W[K x 64]:  B = weight tile viewed MN-major (N = in, K = out rows)
 					for (uint32_t s = 0; s < ksteps; ++s)
 						umma_f16(t_acc, make_desc_sw128(ga + s * 32, LBO_K, SBO), make_desc_sw128(wb + s * 2048, LBO_MN, SBO), idesc_dgrad, s > 0);
+					umma_commit(bar); // the epilogue only needs dA_k ...
 					if (want_dw) {
-						// dW[out][in] += G^T[out x 128] * ACT_k[128 x in]; batch is K: both tiles viewed MN-major
+						// ... dW[out][in] += G^T[out x 128] * ACT_k[128 x in] (batch is K: both tiles viewed MN-major) runs under
+						// that epilogue; the tensor pipe executes in issue order, so the next stage's commit also covers it.
 						const uint32_t td = (k == H) ? t_dw_out : t_dw_hid + (k - 1) * 64;
 						const uint32_t ab = act_addr + k * TILE_BYTES;
 						for (uint32_t s = 0; s < 8; ++s)
 							umma_f16(td, make_desc_sw128(ga + s * 2048, LBO_MN, SBO), make_desc_sw128(ab + s * 2048, LBO_MN, SBO), idesc_dw, (!first_tile) || s > 0);
 					}
-					umma_commit(bar);
 				}
 				mbar_wait(bar, phase); phase ^= 1;
 				STAGE_CLOCK(a); // W: MMA complete
@@ -327,24 +332,21 @@ __global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArg
 				uint32_t v0[32], v1[32];
 				tmem_ld32(t_acc + lane_off, v0);
 				tmem_ld32(t_acc + lane_off + 32, v1);
+				uint4 av[8];
+#pragma unroll
+				for (int c = 0; c < 8; ++c) av[c] = lds128(asrc + sw128(row, c)); // all in flight under the TMEM load
 				tmem_ld_wait();
 #pragma unroll
-				for (int c = 0; c < 4; ++c) {
-					const uint4 av = lds128(asrc + sw128(row, c));
-					const uint32_t aw[4] = {av.x, av.y, av.z, av.w};
+				for (int c = 0; c < 8; ++c) {
+					const uint32_t aw[4] = {av[c].x, av[c].y, av[c].z, av[c].w};
 					uint32_t pk[4];
 #pragma unroll
-					for (int j = 0; j < 4; ++j) pk[j] = h2_mask_mul(pack_h2(__uint_as_float(v0[c * 8 + 2 * j]), __uint_as_float(v0[c * 8 + 2 * j + 1])), aw[j]);
+					for (int j = 0; j < 4; ++j) {
+						const int e = (c & 3) * 8 + 2 * j;
+						const float f0 = __uint_as_float(c < 4 ? v0[e] : v1[e]), f1 = __uint_as_float(c < 4 ? v0[e + 1] : v1[e + 1]);
+						pk[j] = h2_mask_mul(pack_h2(f0, f1), aw[j]);
+					}
 					sts128(dst + sw128(row, c), pk[0], pk[1], pk[2], pk[3]);
-				}
-#pragma unroll
-				for (int c = 0; c < 4; ++c) {
-					const uint4 av = lds128(asrc + sw128(row, 4 + c));
-					const uint32_t aw[4] = {av.x, av.y, av.z, av.w};
-					uint32_t pk[4];
-#pragma unroll
-					for (int j = 0; j < 4; ++j) pk[j] = h2_mask_mul(pack_h2(__uint_as_float(v1[c * 8 + 2 * j]), __uint_as_float(v1[c * 8 + 2 * j + 1])), aw[j]);
-					sts128(dst + sw128(row, 4 + c), pk[0], pk[1], pk[2], pk[3]);
 				}
 				gcur ^= 1;
 				STAGE_CLOCK(a); // E: epilogue math + sts issued
@@ -362,11 +364,13 @@ __global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArg
 					if (want_dx)
 						for (uint32_t s = 0; s < 4; ++s)
 							umma_f16(t_acc, make_desc_sw128(ga + s * 32, LBO_K, SBO), make_desc_sw128(smem_u32(w_inT) + s * 32, LBO_K, SBO), idesc_dx, s > 0);
-					if (want_dw)
-						for (uint32_t s = 0; s < 8; ++s) // D[in][out] += X^T[in x 128] * G[128 x out]
-							umma_f16(t_dw_in, make_desc_sw128(act_addr + s * 2048, LBO_MN, SBO), make_desc_sw128(ga + s * 2048, LBO_MN, SBO), idesc_dw, (!first_tile) || s > 0);
 					umma_commit(bar);
+					if (want_dw)
+						for (uint32_t s = 0; s < 8; ++s) // D[in][out] += X^T[in x 128] * G[128 x out], under the dX epilogue
+							umma_f16(t_dw_in, make_desc_sw128(act_addr + s * 2048, LBO_MN, SBO), make_desc_sw128(ga + s * 2048, LBO_MN, SBO), idesc_dw, (!first_tile) || s > 0);
+					umma_commit(bar2); // waited for before ACT[0] / the accumulators are touched again
 				}
+				pending2 = true;
 				mbar_wait(bar, phase); phase ^= 1;
 				STAGE_CLOCK(a); // W: MMA complete
 				tc_fence_after();
@@ -395,6 +399,7 @@ __global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArg
 
 	// ---- per-CTA flush: weight-gradient partials and loss partial ---------------------------------------
 	if constexpr (TRAIN) {
+		if (pending2) { mbar_wait(bar2, phase2); phase2 ^= 1; pending2 = false; }
 		tc_fence_after();
 		if (a.dW_partials != nullptr) {
 			float* out = a.dW_partials + (size_t)blockIdx.x * a.n_mlp_params;

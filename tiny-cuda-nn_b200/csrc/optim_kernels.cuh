@@ -12,7 +12,8 @@
 namespace b200 {
 
 struct AdamArgs {
-	uint32_t n;                   // total parameters
+	uint32_t n;                   // end of the parameter range handled by this launch
+	uint32_t begin;               // start of the range (multiple of 4)
 	uint32_t n_matrix;            // leading MLP weights (L2 reg, never skipped)
 	float loss_scale;             // gradient divisor: loss_scale * world_size
 	float learning_rate, beta1, beta2, epsilon, l2_reg;
@@ -58,7 +59,7 @@ __device__ __forceinline__ bool adam_one(const AdamArgs& a, uint32_t i, float g_
 }
 
 __global__ void __launch_bounds__(256) adam_kernel(const __grid_constant__ AdamArgs a) {
-	const uint32_t i0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+	const uint32_t i0 = a.begin + (blockIdx.x * blockDim.x + threadIdx.x) * 4;
 	if (i0 >= a.n) return;
 	if (i0 + 4 <= a.n) {
 		union { uint2 u; __half h[4]; } g;

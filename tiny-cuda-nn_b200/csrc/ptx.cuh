@@ -131,11 +131,32 @@ __device__ __forceinline__ uint32_t h2_mask_mul(uint32_t g, uint32_t act) {
 	return *reinterpret_cast<uint32_t*>(&r);
 }
 
+// Loads whose position in the instruction stream matters (software prefetch): ld.global.nc may otherwise be sunk to its
+// first use by the compiler, which re-exposes the latency the prefetch was meant to hide.
+__device__ __forceinline__ uint4 ldg128_here(const void* p) {
+	uint4 v;
+	asm volatile("ld.global.nc.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+	return v;
+}
+__device__ __forceinline__ float ldg_f32_here(const float* p) {
+	float v;
+	asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(v) : "l"(p));
+	return v;
+}
+
 // ---- misc ----------------------------------------------------------------------------------------
 // fp16x2 reduction into global memory without return value (the op the reference scatter uses, vec.h:326-333)
 __device__ __forceinline__ void red_add_h2(__half* addr, __half2 v) {
 	asm volatile("red.relaxed.gpu.global.add.noftz.f16x2 [%0], %1;" ::"l"(addr), "r"(*reinterpret_cast<uint32_t*>(&v)) : "memory");
 }
+// 8- and 16-byte vector forms (SASS: REDG.E.ADD.F16x4 / F16x8), address aligned to the vector size
+__device__ __forceinline__ void red_add_h2x2(__half* addr, uint32_t a, uint32_t b) {
+	asm volatile("red.relaxed.gpu.global.add.noftz.v2.f16x2 [%0], {%1, %2};" ::"l"(addr), "r"(a), "r"(b) : "memory");
+}
+__device__ __forceinline__ void red_add_h2x4(__half* addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+	asm volatile("red.relaxed.gpu.global.add.noftz.v4.f16x2 [%0], {%1, %2, %3, %4};" ::"l"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ uint32_t h2_bits(__half2 v) { return *reinterpret_cast<uint32_t*>(&v); }
 __device__ __forceinline__ uint32_t pack_h2(float a, float b) {
 	__half2 h = __floats2half2_rn(a, b);
 	return *reinterpret_cast<uint32_t*>(&h);

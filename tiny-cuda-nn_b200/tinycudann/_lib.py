@@ -65,6 +65,7 @@ _SIGNATURES = {
     "tcnn_b200_backward": (C.c_int, [_P, _P, C.c_uint32, _P, _P, _P, _P, _P, _P]),
     "tcnn_b200_training_fwd_bwd": (C.c_int, [_P, _P, C.c_uint32, _P, _P, _P, _P, C.c_float, C.c_int, _P, _P, _P]),
     "tcnn_b200_adam_step": (C.c_int, [_P, _P, C.c_float, C.c_uint32, _P, _P, _P, _P, _P, _P, C.c_int]),
+    "tcnn_b200_training_step": (C.c_int, [_P, _P, C.c_uint32, _P, _P, C.c_float, C.c_uint32, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "tcnn_b200_profile_enable": (C.c_int, [_P, C.c_int]),
     "tcnn_b200_profile_read": (C.c_int, [_P, C.POINTER(C.c_float), C.POINTER(C.c_uint32), C.c_uint32]),
 }

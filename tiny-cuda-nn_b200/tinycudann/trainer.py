@@ -40,6 +40,7 @@ class Trainer:
         self.current_step = 0
         self.loss_value = torch.zeros(1, dtype=torch.float32, device=self.device)
         self._grid_grads_clean = True  # grid gradient region is all zero (after init / after an optimizer step)
+        self.use_fused_step = True     # single GPU: tcnn_b200_training_step (Adam overlapped with the scatter)
         self.process_group = process_group
         self.world_size = 1
         if process_group is not None or (torch.distributed.is_available() and torch.distributed.is_initialized()):
@@ -65,6 +66,14 @@ class Trainer:
     def training_step(self, input: torch.Tensor, target: torch.Tensor, run_optimizer: bool = True, output: torch.Tensor | None = None):
         B = input.shape[0]
         ws = self.native.workspace(B, self.device)
+        if run_optimizer and self.use_fused_step and self.world_size == 1 and self._grid_grads_clean:
+            # single GPU: one fused call, Adam of finished level groups overlaps the remaining gradient scatter
+            self.current_step += 1
+            check(self.lib.tcnn_b200_training_step(
+                self.native.handle, _stream_ptr(), B, ptr(input), ptr(target), LOSS_SCALE, self.current_step,
+                ptr(self.params_full_precision), ptr(self.params), ptr(self.param_gradients), ptr(self.first_moments),
+                ptr(self.second_moments), ptr(self.param_steps), ptr(self.loss_value), ptr(output), ptr(ws)))
+            return self
         check(self.lib.tcnn_b200_training_fwd_bwd(
             self.native.handle, _stream_ptr(), B, ptr(input), ptr(target), ptr(self.params), ptr(self.param_gradients),
             LOSS_SCALE, 0 if self._grid_grads_clean else 1, ptr(self.loss_value), ptr(output), ptr(ws)))
