@@ -17,13 +17,14 @@ int main() {
 	cudaMemset(target, 0, (size_t)B * 3 * 4); cudaMemset(clk, 0, 256 * 8);
 	MlpArgs a{}; a.n_tiles = B / 128; a.in_width = E; a.n_hidden = H; a.n_out = 3; a.input = in; a.params = params; a.target = target;
 	a.dL_dinput = dx; a.dW_partials = dw; a.loss_partials = lp; a.n_mlp_params = P; a.loss_type = 0; a.loss_scale = 128.f; a.n_total = B * 3.f; a.debug_clock = clk;
+	GridParams gp{};
 	const uint32_t smem = mlp_smem_bytes(H, E, true);
 	cudaFuncSetAttribute(mlp_kernel<MODE_TRAIN, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
 	for (int grid : {296, 148}) {
 		cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
-		for (int i = 0; i < 3; ++i) mlp_kernel<MODE_TRAIN, 2><<<grid, 128, smem>>>(a);
+		for (int i = 0; i < 3; ++i) mlp_kernel<MODE_TRAIN, 2><<<grid, 128, smem>>>(a, gp);
 		cudaEventRecord(e0);
-		for (int i = 0; i < 10; ++i) mlp_kernel<MODE_TRAIN, 2><<<grid, 128, smem>>>(a);
+		for (int i = 0; i < 10; ++i) mlp_kernel<MODE_TRAIN, 2><<<grid, 128, smem>>>(a, gp);
 		cudaEventRecord(e1); cudaEventSynchronize(e1);
 		float ms; cudaEventElapsedTime(&ms, e0, e1);
 		printf("grid %d: %.1f us per launch (%s)\n", grid, ms * 100.f, cudaGetErrorString(cudaGetLastError()));

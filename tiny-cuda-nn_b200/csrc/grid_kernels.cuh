@@ -195,21 +195,17 @@ __global__ void __launch_bounds__(256) grid_forward_kernel(const __grid_constant
 	*reinterpret_cast<uint4*>(encoded + (size_t)i * gp.padded_width + chunk * 8) = v;
 }
 
-// Scatter dL/d(encoded) [B x E_pad] (fp16, loss-scaled) into the fp16 grid gradient with f16x2 reductions.
+// Scatter one sample's 8-half chunk of dL/d(encoded) (fp16, loss-scaled) into the fp16 grid gradient.
 // Same arithmetic as grid.h:248-318: product (half)weight * grad rounded to fp16, then red.add.noftz.f16x2.
+// Shared by grid_backward_kernel and the fused MLP training kernel (mlp_kernels.cuh).
 template <int D, int F>
-__global__ void __launch_bounds__(256) grid_backward_kernel(const __grid_constant__ GridParams gp, uint32_t B,
-	const float* __restrict__ x, const __half* __restrict__ dL_denc, __half* __restrict__ grid_grad, __half* __restrict__ replicas, uint32_t chunk_begin) {
+__device__ __forceinline__ void scatter_chunk(const GridParams& gp, const float (&p)[D], uint4 gv, uint32_t chunk,
+	__half* __restrict__ grid_grad, __half* __restrict__ replicas, uint32_t replica_id) {
 	static_assert(F == 2 || F == 4 || F == 8, "fp16 gradient scatter needs F >= 2 (grid.h:655-666)");
 	constexpr int LEVELS_PER_CHUNK = 8 / F;
 	constexpr int NC = 1 << D;
-	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-	if (i >= B) return;
-	const uint32_t chunk = chunk_begin + blockIdx.y;
-	float p[D];
-	load_position<D>(x, i, p);
 	union { uint4 v; __half2 h2[4]; } g;
-	g.v = __ldg(reinterpret_cast<const uint4*>(dL_denc + (size_t)i * gp.padded_width + chunk * 8));
+	g.v = gv;
 #pragma unroll
 	for (int s = 0; s < LEVELS_PER_CHUNK; ++s) {
 		const uint32_t level = chunk * LEVELS_PER_CHUNK + s;
@@ -221,7 +217,7 @@ __global__ void __launch_bounds__(256) grid_backward_kernel(const __grid_constan
 		// Same-address f16x2 reductions serialise in L2 (~80 ns each, measured: 2-D level 0 alone took 244 us at B = 2^18);
 		// coarse levels therefore scatter into one of n_replicas copies chosen per block and are summed afterwards.
 		__half* gtable = lv.replicated
-			? replicas + ((size_t)(blockIdx.x & (gp.n_replicas - 1)) * gp.rep_entries + lv.rep_offset) * F
+			? replicas + ((size_t)replica_id * gp.rep_entries + lv.rep_offset) * F
 			: grid_grad + (size_t)lv.offset * F;
 		uint32_t idx[NC]; __half2 wh[NC];
 #pragma unroll
@@ -264,6 +260,18 @@ __global__ void __launch_bounds__(256) grid_backward_kernel(const __grid_constan
 					h2_bits(__hmul2(wh[c], g.h2[2])), h2_bits(__hmul2(wh[c], g.h2[3])));
 		}
 	}
+}
+
+template <int D, int F>
+__global__ void __launch_bounds__(256) grid_backward_kernel(const __grid_constant__ GridParams gp, uint32_t B,
+	const float* __restrict__ x, const __half* __restrict__ dL_denc, __half* __restrict__ grid_grad, __half* __restrict__ replicas, uint32_t chunk_begin) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= B) return;
+	const uint32_t chunk = chunk_begin + blockIdx.y;
+	float p[D];
+	load_position<D>(x, i, p);
+	const uint4 gv = __ldg(reinterpret_cast<const uint4*>(dL_denc + (size_t)i * gp.padded_width + chunk * 8));
+	scatter_chunk<D, F>(gp, p, gv, chunk, grid_grad, replicas, blockIdx.x & (gp.n_replicas - 1));
 }
 
 // grid_grad[level entries] += sum over replicas (fp32 accumulate, one rounding), for the replicated levels.

@@ -17,6 +17,7 @@
 //     (kept as 64-bit register masks, the reference re-reads the stored activations) / the loss, and writes the fp16
 //     row back to shared memory for the next MMA.  No activation ever goes to HBM (the reference moves ~0.5 GB/step).
 #pragma once
+#include "grid_kernels.cuh"
 #include "ptx.cuh"
 
 namespace b200 {
@@ -56,6 +57,10 @@ struct MlpArgs {
 	float loss_scale;
 	float inv_n_total;             // 1 / (B * n_out)  (losses/l2.h:62-64: n_total = n_elements / stride * dims)
 	float n_total;
+	// fused gradient scatter (kernel template FD > 0): dL/d(encoded) never leaves the SM, each row's thread scatters it
+	const float* positions;        // [B][D] fp32
+	__half* grid_grad;             // [n_params_grid]
+	__half* replicas;              // private copies of the replicated coarse levels (grid_kernels.cuh)
 	long long* debug_clock;        // MLP_STAGE_CLOCKS builds only
 };
 
@@ -74,9 +79,11 @@ __host__ __device__ constexpr uint32_t mlp_tmem_cols(int n_hidden, bool train) {
 	return need <= 64 ? 64 : need <= 128 ? 128 : need <= 256 ? 256 : 512;
 }
 
-template <int MODE, int H_>
-__global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArgs a) {
+template <int MODE, int H_, int FD = 0, int FF = 2>
+__global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArgs a, const __grid_constant__ GridParams gp) {
 	constexpr bool TRAIN = MODE != MODE_INFER;
+	constexpr bool FUSE_SCATTER = FD > 0;
+	static_assert(!FUSE_SCATTER || TRAIN, "the fused scatter belongs to the backward pass");
 	extern __shared__ uint8_t smem_raw[];
 	uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
 	const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -184,6 +191,11 @@ __global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArg
 		// per-row side inputs, requested now and consumed after the forward chain
 		float tgt[4] = {0.f, 0.f, 0.f, 0.f};
 		uint4 dy_in[2];
+		float pos[FUSE_SCATTER ? FD : 1];
+		if constexpr (FUSE_SCATTER) {
+#pragma unroll
+			for (int d = 0; d < FD; ++d) pos[d] = ldg_f32_here(a.positions + (sample0 + row) * FD + d);
+		}
 		if (MODE == MODE_TRAIN) {
 #pragma unroll
 			for (uint32_t j = 0; j < 4; ++j) if (j < a.n_out) tgt[j] = ldg_f32_here(a.target + (sample0 + row) * a.n_out + j);
@@ -356,7 +368,7 @@ __global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArg
 				STAGE_CLOCK(a); // S: fenced + synced
 			}
 			// ---- input matmul: dW_in (transposed accumulator) and dL/d(input) ---------------------------
-			const bool want_dx = a.dL_dinput != nullptr;
+			const bool want_dx = a.dL_dinput != nullptr || FUSE_SCATTER;
 			if (want_dw || want_dx) {
 				if (tid == 0) {
 					tc_fence_after();
@@ -375,7 +387,7 @@ __global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArg
 				STAGE_CLOCK(a); // W: MMA complete
 				tc_fence_after();
 				if (want_dx) {
-					__half* dst = a.dL_dinput + (sample0 + row) * E;
+					__half* dst = a.dL_dinput ? a.dL_dinput + (sample0 + row) * E : nullptr;
 					for (uint32_t c0 = 0; c0 < E; c0 += 16) {
 						uint32_t v[16];
 						tmem_ld16(t_acc + lane_off + c0, v);
@@ -383,8 +395,17 @@ __global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArg
 						uint32_t pk[8];
 #pragma unroll
 						for (int j = 0; j < 8; ++j) pk[j] = pack_h2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
-						reinterpret_cast<uint4*>(dst + c0)[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-						reinterpret_cast<uint4*>(dst + c0)[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+						if (dst) {
+							reinterpret_cast<uint4*>(dst + c0)[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+							reinterpret_cast<uint4*>(dst + c0)[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+						}
+						if constexpr (FUSE_SCATTER) {
+							// this row's dL/d(encoded) goes straight into the hash-table gradient: fire-and-forget reductions that
+							// overlap the weight-gradient MMA still running and the other CTA's MMA chain
+							const uint32_t rep = blockIdx.x & (gp.n_replicas - 1);
+							scatter_chunk<FD, FF>(gp, pos, make_uint4(pk[0], pk[1], pk[2], pk[3]), c0 / 8, a.grid_grad, a.replicas, rep);
+							scatter_chunk<FD, FF>(gp, pos, make_uint4(pk[4], pk[5], pk[6], pk[7]), c0 / 8 + 1, a.grid_grad, a.replicas, rep);
+						}
 					}
 				}
 				tc_fence_before();

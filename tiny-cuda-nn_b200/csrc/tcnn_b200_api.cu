@@ -16,7 +16,7 @@
 
 #include "grid_kernels.cuh"
 #include "json_mini.h"
-#include "mlp_kernels.cuh"
+#include "mlp_kernels.cuh"  // includes grid_kernels.cuh (fused scatter)
 #include "optim_kernels.cuh"
 
 using namespace b200;
@@ -464,26 +464,49 @@ extern "C" int tcnn_b200_grid_indices(const tcnn_b200_plan* plan, void* stream, 
 }
 
 // ---- MLP ----------------------------------------------------------------------------------------------
-template <int MODE, int H>
-static void launch_mlp_h(const tcnn_b200_plan* plan, cudaStream_t stream, const MlpArgs& a, uint32_t grid) {
+template <int MODE, int H, int FD = 0, int FF = 2>
+static void launch_mlp_h(const tcnn_b200_plan* plan, cudaStream_t stream, const MlpArgs& a, uint32_t grid, const GridParams& gp) {
 	constexpr bool train = MODE != MODE_INFER;
 	const uint32_t smem = mlp_smem_bytes(H, (int)a.in_width, train);
 	static thread_local uint32_t configured = 0;
 	if (configured < smem) {
-		CUDA_OK(cudaFuncSetAttribute(mlp_kernel<MODE, H>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		CUDA_OK(cudaFuncSetAttribute(mlp_kernel<MODE, H, FD, FF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
 		configured = smem;
 	}
 	ProfileScope prof(plan, stream, PK_MLP);
-	mlp_kernel<MODE, H><<<grid, 128, smem, stream>>>(a);
+	mlp_kernel<MODE, H, FD, FF><<<grid, 128, smem, stream>>>(a, gp);
 	launch_check("mlp_kernel");
 }
 template <int MODE>
 static void launch_mlp(const tcnn_b200_plan* plan, cudaStream_t stream, const MlpArgs& a, uint32_t grid) {
 	switch (a.n_hidden) {
-		case 1: launch_mlp_h<MODE, 1>(plan, stream, a, grid); break;
-		case 2: launch_mlp_h<MODE, 2>(plan, stream, a, grid); break;
-		case 3: launch_mlp_h<MODE, 3>(plan, stream, a, grid); break;
-		case 4: launch_mlp_h<MODE, 4>(plan, stream, a, grid); break;
+		case 1: launch_mlp_h<MODE, 1>(plan, stream, a, grid, plan->grid); break;
+		case 2: launch_mlp_h<MODE, 2>(plan, stream, a, grid, plan->grid); break;
+		case 3: launch_mlp_h<MODE, 3>(plan, stream, a, grid, plan->grid); break;
+		case 4: launch_mlp_h<MODE, 4>(plan, stream, a, grid, plan->grid); break;
+		default: FAIL("n_hidden_layers out of range");
+	}
+}
+// Training kernel with the hash-table gradient scatter fused into its last stage; instantiated for the common shapes.
+static bool fused_scatter_available(const tcnn_b200_plan* plan) {
+	const uint32_t D = plan->info.n_input_dims, F = plan->info.n_features_per_level;
+	return (D == 2 || D == 3) && (F == 2 || F == 4);
+}
+template <int H>
+static void launch_mlp_train_fused_h(const tcnn_b200_plan* plan, cudaStream_t stream, const MlpArgs& a, uint32_t grid, const GridParams& gp) {
+	const uint32_t D = plan->info.n_input_dims, F = plan->info.n_features_per_level;
+	if (D == 2 && F == 2) launch_mlp_h<MODE_TRAIN, H, 2, 2>(plan, stream, a, grid, gp);
+	else if (D == 3 && F == 2) launch_mlp_h<MODE_TRAIN, H, 3, 2>(plan, stream, a, grid, gp);
+	else if (D == 2 && F == 4) launch_mlp_h<MODE_TRAIN, H, 2, 4>(plan, stream, a, grid, gp);
+	else if (D == 3 && F == 4) launch_mlp_h<MODE_TRAIN, H, 3, 4>(plan, stream, a, grid, gp);
+	else FAIL("no fused-scatter kernel for this (n_input_dims, n_features_per_level)");
+}
+static void launch_mlp_train_fused(const tcnn_b200_plan* plan, cudaStream_t stream, const MlpArgs& a, uint32_t grid, const GridParams& gp) {
+	switch (a.n_hidden) {
+		case 1: launch_mlp_train_fused_h<1>(plan, stream, a, grid, gp); break;
+		case 2: launch_mlp_train_fused_h<2>(plan, stream, a, grid, gp); break;
+		case 3: launch_mlp_train_fused_h<3>(plan, stream, a, grid, gp); break;
+		case 4: launch_mlp_train_fused_h<4>(plan, stream, a, grid, gp); break;
 		default: FAIL("n_hidden_layers out of range");
 	}
 }
@@ -612,8 +635,13 @@ extern "C" int tcnn_b200_training_fwd_bwd(const tcnn_b200_plan* plan, void* stre
 	a.loss_scale = loss_scale;
 	backward_prepare(plan, main, gp, gg, zero_grid_grads, w.replicas);
 	encode_forward(plan, main, B, x, p + in.n_params_mlp, w.encoded);
-	launch_mlp<MODE_TRAIN>(plan, main, a, part_cnt[0]);
-	backward_scatter(plan, main, gp, B, x, w.dL_denc, gg, w.replicas);
+	if (fused_scatter_available(plan)) {
+		a.dL_dinput = nullptr; a.positions = x; a.grid_grad = gg; a.replicas = w.replicas;
+		launch_mlp_train_fused(plan, main, a, part_cnt[0], gp);
+	} else {
+		launch_mlp<MODE_TRAIN>(plan, main, a, part_cnt[0]);
+		backward_scatter(plan, main, gp, B, x, w.dL_denc, gg, w.replicas);
+	}
 	mlp_finalize(plan, main, part_off[n_chunks - 1] + part_cnt[n_chunks - 1], w, g, loss_out, loss_out != nullptr);
 	backward_finish(plan, main, gp, gg, w.replicas);
 	API_END
@@ -693,6 +721,21 @@ extern "C" int tcnn_b200_training_step(const tcnn_b200_plan* plan, void* stream_
 
 	backward_prepare(plan, main, gp, gg, /*zero_first=*/0, w.replicas);
 	encode_forward(plan, main, B, x, p + in.n_params_mlp, w.encoded);
+	if (fused_scatter_available(plan)) {
+		// gather -> [MLP forward, loss, backward, weight gradients, hash-table scatter] -> Adam.  The small dW reduction runs on
+		// the second stream under the Adam pass over the grid tables; the MLP weights are updated after the join.
+		a.dL_dinput = nullptr; a.positions = x; a.grid_grad = gg; a.replicas = w.replicas;
+		launch_mlp_train_fused(plan, main, a, mlp_grid, gp);
+		CUDA_OK(cudaEventRecord(ev[0], main));
+		CUDA_OK(cudaStreamWaitEvent(aux, ev[0], 0));
+		mlp_finalize(plan, aux, mlp_grid, w, g, loss_out, loss_out != nullptr);
+		CUDA_OK(cudaEventRecord(ev[1], aux));
+		backward_finish(plan, main, gp, gg, w.replicas);
+		adam_launch(plan, main, loss_scale, adam_step_count, ab, 1, (uint32_t)in.n_params_mlp, (uint32_t)in.n_params);
+		CUDA_OK(cudaStreamWaitEvent(main, ev[1], 0)); // join
+		adam_launch(plan, main, loss_scale, adam_step_count, ab, 1, 0u, (uint32_t)in.n_params_mlp);
+		return 0;
+	}
 	launch_mlp<MODE_TRAIN>(plan, main, a, mlp_grid);
 	CUDA_OK(cudaEventRecord(ev[0], main));
 	CUDA_OK(cudaStreamWaitEvent(aux, ev[0], 0));

@@ -16,6 +16,7 @@ import torch
 from . import _lib
 from ._lib import check, ptr
 from .modules import NativeModule, _stream_ptr
+from .parallel import allreduce_gradients, grad_divisor
 
 LOSS_SCALE = 128.0  # default_loss_scale<__half>(), common.h:229-233; trainer.h:174
 
@@ -79,7 +80,8 @@ class Trainer:
             LOSS_SCALE, 0 if self._grid_grads_clean else 1, ptr(self.loss_value), ptr(output), ptr(ws)))
         self._grid_grads_clean = False
         if self.world_size > 1:
-            torch.distributed.all_reduce(self.param_gradients, group=self.process_group)
+            for h in allreduce_gradients(self.param_gradients, self.process_group):
+                h.wait()  # stream-ordered for NCCL: makes the current stream wait, the host does not block
         if run_optimizer:
             self.optimizer_step(LOSS_SCALE)
         return self
@@ -88,7 +90,7 @@ class Trainer:
     def optimizer_step(self, loss_scale: float = LOSS_SCALE):
         self.current_step += 1
         check(self.lib.tcnn_b200_adam_step(
-            self.native.handle, _stream_ptr(), loss_scale * self.world_size, self.current_step,
+            self.native.handle, _stream_ptr(), grad_divisor(loss_scale, self.world_size), self.current_step,
             ptr(self.params_full_precision), ptr(self.params), ptr(self.param_gradients),
             ptr(self.first_moments), ptr(self.second_moments), ptr(self.param_steps), 1))
         self._grid_grads_clean = True
