@@ -169,6 +169,13 @@ def run_reference(args, cfg):
     print(json.dumps(line), flush=True)
 
 
+DP_NOTE = {
+    "peer": "one fused kernel per step: NVSwitch multimem.ld_reduce of this rank's gradient shard -> Adam on the shard -> multimem.st of the new fp16 parameters to all ranks, both barriers in-kernel",
+    "peer-p2p": "one fused kernel per step: peer loads of this rank's gradient shard from all ranks -> Adam on the shard -> peer stores of the new fp16 parameters, both barriers in-kernel",
+    "allreduce": "fp16 NCCL all-reduce of the 22.4 MB gradient buffer per step, replicated Adam",
+}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -177,6 +184,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--e2e-steps", type=int, default=300)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--force-dp", action="store_true", help="N = 1: run the data-parallel step on a one-rank group")
+    ap.add_argument("--dp-mode", default="peer", choices=["peer", "peer-p2p", "allreduce"],
+                    help="N > 1: fused reduce-scatter+Adam+all-gather kernel over NVSwitch multicast (peer) or plain peer loads/stores (peer-p2p), or NCCL all-reduce + replicated Adam (allreduce)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
 
@@ -199,8 +209,10 @@ def main():
     torch.cuda.set_device(dev)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
+    elif args.force_dp:  # development aid: the data-parallel step on a one-rank group (ncu can profile it)
+        dist.init_process_group("nccl", init_method="tcp://127.0.0.1:29533", rank=0, world_size=1, device_id=dev)
 
-    model = tcnn.create_from_config(N_IN, N_OUT, cfg, seed=1337, device=dev)
+    model = tcnn.create_from_config(N_IN, N_OUT, cfg, seed=1337, device=dev, **({} if world == 1 and not args.force_dp else {"dp_mode": args.dp_mode.split("-")[0], "use_multicast": args.dp_mode != "peer-p2p"}))
     tr = model.trainer
     info = tr.info
     lib = tr.lib
@@ -307,7 +319,7 @@ def main():
             "data": "synthetic",
             "config": {"workload": WORKLOAD, "batch_per_gpu": BATCH, "global_batch": BATCH * world, "parallelism": f"dp{world}",
                        "l2": "no flush: one step streams ~0.45 GB of parameter/optimizer state (> 126 MB L2) and cycles 4 distinct resident batches",
-                       "grad_allreduce": "fp16 NCCL all-reduce of the 22.4 MB gradient buffer per step" if world > 1 else "none"},
+                       "gradient_exchange": DP_NOTE.get(args.dp_mode, args.dp_mode) if world > 1 else "none"},
             "clocks": clk.summary(),
             "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": BATCH * 4 * (N_IN + N_OUT), "d2h_bytes_per_step": 4,
                     "ms_per_step": e2e_ms, "steps": e2e_steps, "how": "pinned host batch -> H2D on a copy stream (double-buffered, overlaps the previous step) -> training_step -> async 4-byte loss D2H; one host sync at the end"},

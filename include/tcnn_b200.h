@@ -119,6 +119,35 @@ int tcnn_b200_adam_step(const tcnn_b200_plan* plan, void* stream, float grad_div
                         float* params_fp32, void* params_fp16, void* grads_fp16, float* first_moments, float* second_moments,
                         uint32_t* param_steps, int zero_grid_grads);
 
+/* tcnn_b200_adam_step restricted to parameters [param_begin, param_end) (param_begin a multiple of 4). */
+int tcnn_b200_adam_step_range(const tcnn_b200_plan* plan, void* stream, float grad_divisor, uint32_t adam_step_count,
+                              float* params_fp32, void* params_fp16, void* grads_fp16, float* first_moments, float* second_moments,
+                              uint32_t* param_steps, int zero_grid_grads, uint64_t param_begin, uint64_t param_end);
+
+/* Data-parallel training step over NVLink peer memory (no reference counterpart).  The fp16 parameter and gradient
+ * buffers of all ranks (one process per GPU, at most 8 = one NVSwitch domain) are symmetric allocations mapped into every
+ * process (e.g. torch.distributed._symmetric_memory); peer_*[r] is rank r's buffer as seen from the calling process.
+ * After the local forward/backward, ONE kernel sums the gradient shard [param_begin, param_end) of this rank over all
+ * ranks, applies Adam to it and stores the new fp16 parameters into every rank; both inter-GPU barriers are inside that
+ * kernel (flag blocks of tcnn_b200_dp_flag_bytes() zeroed bytes per rank; `epoch` = 1, 2, 3, ... on every rank).  With
+ * the multicast mappings set, reduction and broadcast go through the NVSwitch (multimem.ld_reduce / multimem.st).
+ * fp32 master weights, Adam moments and step counters are passed for the rank's OWN shard only (element 0 = parameter
+ * param_begin of tcnn_b200_dp_shard).  Grid gradients must be zero on entry and are zero on return. */
+typedef struct tcnn_b200_dp_comm {
+  uint32_t rank, world_size, epoch, reserved;
+  void* peer_grads[8];
+  void* peer_params[8];
+  void* peer_flags[8];
+  void* grads_multicast;  /* or NULL: peer loads */
+  void* params_multicast; /* or NULL: peer stores */
+} tcnn_b200_dp_comm;
+int tcnn_b200_dp_shard(const tcnn_b200_plan* plan, uint32_t rank, uint32_t world_size, uint64_t* param_begin, uint64_t* param_end);
+uint32_t tcnn_b200_dp_flag_bytes(void);
+int tcnn_b200_training_step_dp(const tcnn_b200_plan* plan, void* stream, uint32_t batch_size, const float* x, const float* target,
+                               float loss_scale, uint32_t adam_step_count, float* params_fp32_shard, float* first_moments_shard,
+                               float* second_moments_shard, uint32_t* param_steps_shard, float* loss_out, void* output_fp16,
+                               void* workspace, const tcnn_b200_dp_comm* comm);
+
 /* Trainer::training_step with run_optimizer = true (trainer.h:163-190) as ONE call for a single GPU: the work of
  * tcnn_b200_training_fwd_bwd followed by tcnn_b200_adam_step, scheduled so that the Adam update of a finished group of
  * grid levels overlaps the gradient scatter of the next group (internal second stream, joined before returning to the

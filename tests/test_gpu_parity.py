@@ -316,6 +316,63 @@ def test_fused_step_equals_separate_calls(dev):
     assert not a.param_gradients[int(a.info.n_params_mlp):].any().item()
 
 
+def _steps_agree(a, b, cfg, n_in, n_out, dev, B=1 << 16, step_a=None):
+    for i in range(3):
+        x_np, t_np = common.synth_inputs(B, n_in, n_out, seed=40 + i)
+        x, t = torch.from_numpy(x_np).to(dev), torch.from_numpy(t_np).to(dev)
+        (step_a or a.training_step)(x, t); b.training_step(x, t)
+        assert abs(a.loss() - b.loss()) <= 1e-5 * abs(b.loss())
+    pa, pb = a.params_full_precision.cpu().numpy(), b.params_full_precision.cpu().numpy()
+    p0 = O.init_params(*reversed(common.oracle_configs(cfg, n_in, n_out)), 1337, True)
+    assert common.rel_l2(pa - p0, pb - p0) < 2e-2
+    assert np.mean(a.param_steps.cpu().numpy() != b.param_steps.cpu().numpy()) < 1e-3
+    assert not a.param_gradients[int(a.info.n_params_mlp):].any().item()
+
+
+def test_unfused_level_group_step_equals_separate_calls(dev):
+    """F = 8 has no fused MLP+scatter kernel: tcnn_b200_training_step then scatters level group by level group with Adam
+    of each finished group on a second stream (replicated coarse levels reduced per group)."""
+    import tinycudann as tcnn
+    cfg = json.loads(json.dumps(common.CONFIG_F4))
+    cfg["encoding"].update(n_features_per_level=8, n_levels=4)
+    a = tcnn.create_from_config(3, 3, cfg, seed=1337, device=dev).trainer
+    b = tcnn.create_from_config(3, 3, cfg, seed=1337, device=dev).trainer
+    b.use_fused_step = False
+    _steps_agree(a, b, cfg, 3, 3, dev)
+
+
+def test_peer_memory_step_on_one_rank_equals_separate_calls(dev):
+    """tcnn_b200_training_step_dp with a one-rank group (symmetric memory, both in-kernel barriers, sharded Adam over the
+    whole parameter range) == fwd_bwd followed by adam_step.  tests/dp_peer_check.py is the same check on 2+ GPUs."""
+    import tinycudann as tcnn
+    import torch.distributed as dist
+    own = not dist.is_initialized()
+    if own:
+        dist.init_process_group("nccl", init_method="tcp://127.0.0.1:29617", rank=0, world_size=1, device_id=dev)
+    try:
+        for mc in (False, True):
+            a = tcnn.create_from_config(2, 3, common.CONFIG_1, seed=1337, device=dev, dp_mode="peer", use_multicast=mc).trainer
+            b = tcnn.create_from_config(2, 3, common.CONFIG_1, seed=1337, device=dev, dp_mode="allreduce").trainer
+            b.use_fused_step = False
+            assert a.peer_memory.shard == (0, a.n_params)
+            _steps_agree(a, b, common.CONFIG_1, 2, 3, dev)
+    finally:
+        if own:
+            dist.destroy_process_group()
+
+
+def test_peer_memory_step_on_all_gpus(dev):
+    """2+ GPUs: peer-memory data parallelism against the NCCL all-reduce path (tests/dp_peer_check.py under torchrun)."""
+    import subprocess, sys
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("one GPU: the multi-rank peer-memory check needs at least two")
+    n = 2 if n < 4 else (4 if n < 8 else 8)
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr", "127.0.0.1",
+                        "--master-port", "29618", os.path.join(os.path.dirname(__file__), "dp_peer_check.py")], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "dp_peer_check ok" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+
+
 def test_batch_size_must_be_multiple_of_256(dev):
     import tinycudann as tcnn
     model = tcnn.create_from_config(2, 3, common.CONFIG_1, seed=1, device=dev)

@@ -275,10 +275,12 @@ __global__ void __launch_bounds__(256) grid_backward_kernel(const __grid_constan
 }
 
 // grid_grad[level entries] += sum over replicas (fp32 accumulate, one rounding), for the replicated levels.
-__global__ void grid_replica_reduce_kernel(const __grid_constant__ GridParams gp, uint32_t F, const __half* __restrict__ replicas, __half* __restrict__ grid_grad) {
-	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; // half2 index inside one replica
+// Covers the half2 range [pair_begin, pair_end) of one replica (= the replicated levels of one level group).
+__global__ void grid_replica_reduce_kernel(const __grid_constant__ GridParams gp, uint32_t F, const __half* __restrict__ replicas, __half* __restrict__ grid_grad,
+	uint32_t pair_begin, uint32_t pair_end) {
+	const uint32_t i = pair_begin + blockIdx.x * blockDim.x + threadIdx.x; // half2 index inside one replica
 	const uint32_t pairs = gp.rep_entries * F / 2;
-	if (i >= pairs) return;
+	if (i >= pair_end) return;
 	float2 acc = make_float2(0.f, 0.f);
 	for (uint32_t r0 = 0; r0 < gp.n_replicas; r0 += 8) { // 8 independent loads in flight (n_replicas is a multiple of 8)
 		__half2 v[8];

@@ -94,6 +94,115 @@ __global__ void __launch_bounds__(256) adam_kernel(const __grid_constant__ AdamA
 	}
 }
 
+// ---- data-parallel optimizer step over NVLink peer memory -----------------------------------------------
+// One kernel = reduce-scatter of the fp16 gradients + Adam on this rank's shard of the parameters + all-gather of the
+// updated fp16 parameters, with both inter-GPU barriers inside.  Gradient and fp16 parameter buffers are symmetric
+// allocations mapped into every rank; fp32 master weights, moments and step counters exist only for the rank's own
+// shard (ZeRO-1 style), so the optimizer's HBM traffic per GPU shrinks with the number of ranks.
+//   entry:  every rank announces "my gradients are complete" in each peer's flag block and waits for all peers
+//   body :  thread = 4 parameters: sum the 8-byte gradient slices of all ranks (peer loads, or ONE multimem.ld_reduce
+//           through the NVSwitch), Adam, 8-byte store of the new fp16 parameters into all ranks (peer stores, or ONE
+//           multimem.st)
+//   exit :  the last CTA announces "my parameter writes are visible" and waits for the same from all peers, so that
+//           when the kernel retires every rank may read its parameters and re-zero its gradients.
+// The waits are on other GPUs' kernels, never on CTAs of this launch, and give up after DP_TIMEOUT_NS (trap).
+constexpr uint32_t DP_MAX_RANKS = 8;
+constexpr uint32_t DP_FLAG_GRADS = 0, DP_FLAG_PARAMS = 8, DP_FLAG_COUNTER = 16, DP_FLAG_WORDS = 32;
+constexpr uint64_t DP_TIMEOUT_NS = 10ull * 1000 * 1000 * 1000;
+struct DpComm {
+	uint32_t rank, world, epoch, use_multicast;
+	__half* peer_grads[DP_MAX_RANKS];
+	__half* peer_params[DP_MAX_RANKS];
+	uint32_t* peer_flags[DP_MAX_RANKS];
+	__half* grads_mc;
+	__half* params_mc;
+};
+
+// signal = release store, wait = acquire polling with back-off (hundreds of CTAs poll the same line), both system scope
+__device__ __forceinline__ void dp_signal(uint32_t* flag, uint32_t epoch) { st_release_sys(flag, epoch); }
+__device__ __forceinline__ void dp_wait_flag(const uint32_t* flag, uint32_t epoch) {
+	if ((int32_t)(ld_acquire_sys(flag) - epoch) >= 0) return;
+	const uint64_t t0 = globaltimer_ns();
+	while ((int32_t)(ld_acquire_sys(flag) - epoch) < 0) {
+		__nanosleep(100);
+		if (globaltimer_ns() - t0 > DP_TIMEOUT_NS) { printf("tcnn_b200: data-parallel barrier timed out (a peer rank is gone)\n"); __trap(); }
+	}
+}
+
+// Persistent: a few CTAs per SM walk the shard in rows of 256 groups (group = 4 consecutive parameters = one 8-byte
+// gradient slice per rank), so the flag poll at entry and the system fence at exit are paid once per CTA, not once per
+// 2048 parameters (r01d: 1.6x slower than the plain Adam kernel when they were).  MAXW = compiled bound of the world size.
+template <bool MC, int MAXW>
+__global__ void __launch_bounds__(256) dp_adam_kernel(const __grid_constant__ AdamArgs a, const __grid_constant__ DpComm c) {
+	uint32_t* my_flags = c.peer_flags[c.rank];
+#ifdef DP_STAMPS
+	if (blockIdx.x == 0 && threadIdx.x == 0) reinterpret_cast<uint64_t*>(my_flags)[12] = globaltimer_ns();
+#endif
+	// the scatter before this kernel is complete (stream order): thread r of the first CTA tells rank r
+	if (blockIdx.x == 0 && threadIdx.x < c.world) dp_signal(c.peer_flags[threadIdx.x] + DP_FLAG_GRADS + c.rank, c.epoch);
+	if (threadIdx.x < c.world) dp_wait_flag(my_flags + DP_FLAG_GRADS + threadIdx.x, c.epoch);
+	__syncthreads();
+#ifdef DP_STAMPS
+	if (blockIdx.x == 0 && threadIdx.x == 0) reinterpret_cast<uint64_t*>(my_flags)[13] = globaltimer_ns();
+#endif
+
+#pragma unroll 1
+	for (uint32_t i0 = a.begin + (blockIdx.x * 256 + threadIdx.x) * 4; i0 < a.n; i0 += gridDim.x * (256 * 4)) {
+		float2 g01 = make_float2(0.f, 0.f), g23 = make_float2(0.f, 0.f);
+		if (MC) {
+			const uint2 r = multimem_ld_reduce_h2x2(c.grads_mc + i0);
+			g01 = __half22float2(*reinterpret_cast<const __half2*>(&r.x));
+			g23 = __half22float2(*reinterpret_cast<const __half2*>(&r.y));
+		} else {
+			uint2 raw[MAXW];
+#pragma unroll
+			for (int r = 0; r < MAXW; ++r) if (r < (int)c.world) raw[r] = ld_sys_v2(c.peer_grads[r] + i0); // all in flight at once
+#pragma unroll
+			for (int r = 0; r < MAXW; ++r) if (r < (int)c.world) { // fixed rank order, fp32 accumulation
+				const float2 lo = __half22float2(*reinterpret_cast<const __half2*>(&raw[r].x)), hi = __half22float2(*reinterpret_cast<const __half2*>(&raw[r].y));
+				g01.x += lo.x; g01.y += lo.y; g23.x += hi.x; g23.y += hi.y;
+			}
+		}
+		const bool any_nonzero = g01.x != 0.f || g01.y != 0.f || g23.x != 0.f || g23.y != 0.f;
+		if (i0 >= a.n_matrix && !any_nonzero) continue;
+		float4 w = *reinterpret_cast<float4*>(a.master + i0);
+		float4 m = *reinterpret_cast<float4*>(a.m + i0);
+		float4 v = *reinterpret_cast<float4*>(a.v + i0);
+		uint4 s = *reinterpret_cast<uint4*>(a.steps + i0);
+		adam_one(a, i0 + 0, g01.x, w.x, m.x, v.x, s.x);
+		adam_one(a, i0 + 1, g01.y, w.y, m.y, v.y, s.y);
+		adam_one(a, i0 + 2, g23.x, w.z, m.z, v.z, s.z);
+		adam_one(a, i0 + 3, g23.y, w.w, m.w, v.w, s.w);
+		*reinterpret_cast<float4*>(a.master + i0) = w;
+		*reinterpret_cast<float4*>(a.m + i0) = m;
+		*reinterpret_cast<float4*>(a.v + i0) = v;
+		*reinterpret_cast<uint4*>(a.steps + i0) = s;
+		const uint2 ph = make_uint2(pack_h2(w.x, w.y), pack_h2(w.z, w.w));
+		if (MC) multimem_st_v2(c.params_mc + i0, ph);
+		else {
+#pragma unroll
+			for (int r = 0; r < MAXW; ++r) if (r < (int)c.world) st_sys_v2(c.peer_params[r] + i0, ph);
+		}
+	}
+	// exit: count the CTA as done (its peer stores are ordered before the increment by barrier + release); the last CTA
+	// tells every rank and waits for every rank, thread r taking rank r
+	__shared__ uint32_t is_last;
+	__syncthreads();
+	if (threadIdx.x == 0) is_last = atom_inc_acq_rel_gpu(my_flags + DP_FLAG_COUNTER, gridDim.x - 1) == gridDim.x - 1; // wraps to 0 for the next launch
+	__syncthreads();
+	if (is_last && threadIdx.x < c.world) {
+#ifdef DP_STAMPS
+		if (threadIdx.x == 0) reinterpret_cast<uint64_t*>(my_flags)[14] = globaltimer_ns();
+#endif
+		dp_signal(c.peer_flags[threadIdx.x] + DP_FLAG_PARAMS + c.rank, c.epoch);
+		dp_wait_flag(my_flags + DP_FLAG_PARAMS + threadIdx.x, c.epoch);
+	}
+#ifdef DP_STAMPS
+	__syncthreads();
+	if (is_last && threadIdx.x == 0) reinterpret_cast<uint64_t*>(my_flags)[15] = globaltimer_ns();
+#endif
+}
+
 // ---- parameter initialisation ---------------------------------------------------------------------
 // pcg32 (PCG-XSH-RR 64/32) with O(log n) jump-ahead, as vendored by the reference (dependencies/pcg32/pcg32.h).
 struct Pcg32Dev {

@@ -162,4 +162,69 @@ __device__ __forceinline__ uint32_t pack_h2(float a, float b) {
 	return *reinterpret_cast<uint32_t*>(&h);
 }
 
+// ---- peer memory over NVLink / NVSwitch ---------------------------------------------------------------
+// System-scope accesses for buffers that other GPUs read and write (symmetric allocations mapped into every rank).
+__device__ __forceinline__ uint4 ld_sys_v4(const void* addr) {
+	uint4 v;
+	asm volatile("ld.relaxed.sys.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(addr) : "memory");
+	return v;
+}
+__device__ __forceinline__ void st_sys_v4(void* addr, uint4 v) {
+	asm volatile("st.relaxed.sys.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ uint2 ld_sys_v2(const void* addr) {
+	uint2 v;
+	asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(addr) : "memory");
+	return v;
+}
+__device__ __forceinline__ void st_sys_v2(void* addr, uint2 v) {
+	asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(addr), "r"(v.x), "r"(v.y) : "memory");
+}
+__device__ __forceinline__ void st_relaxed_sys(uint32_t* addr, uint32_t v) {
+	asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* addr) {
+	uint32_t v;
+	asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(addr) : "memory");
+	return v;
+}
+__device__ __forceinline__ void fence_acq_rel_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
+// counter += 1 with wrap to 0 after `wrap`; release/acquire at GPU scope (orders the CTA's earlier stores before it)
+__device__ __forceinline__ uint32_t atom_inc_acq_rel_gpu(uint32_t* addr, uint32_t wrap) {
+	uint32_t old;
+	asm volatile("atom.acq_rel.gpu.global.inc.u32 %0, [%1], %2;" : "=r"(old) : "l"(addr), "r"(wrap) : "memory");
+	return old;
+}
+__device__ __forceinline__ void st_release_sys(uint32_t* addr, uint32_t v) {
+	asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* addr) {
+	uint32_t v;
+	asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(addr) : "memory");
+	return v;
+}
+__device__ __forceinline__ uint64_t globaltimer_ns() {
+	uint64_t t;
+	asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+	return t;
+}
+// NVSwitch multicast (NVLS): one load returns the sum over every rank's copy, one store lands in every rank's copy.
+__device__ __forceinline__ uint4 multimem_ld_reduce_h2x4(const void* mc_addr) {
+	uint4 v;
+	asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.f16x2 {%0, %1, %2, %3}, [%4];"
+		: "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(mc_addr) : "memory");
+	return v;
+}
+__device__ __forceinline__ uint2 multimem_ld_reduce_h2x2(const void* mc_addr) {
+	uint2 v;
+	asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v2.f16x2 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(mc_addr) : "memory");
+	return v;
+}
+__device__ __forceinline__ void multimem_st_v2(void* mc_addr, uint2 v) {
+	asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1, %2};" ::"l"(mc_addr), "r"(v.x), "r"(v.y) : "memory");
+}
+__device__ __forceinline__ void multimem_st_v4(void* mc_addr, uint4 v) {
+	asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc_addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
 } // namespace b200

@@ -421,12 +421,23 @@ static void backward_scatter(const tcnn_b200_plan* plan, cudaStream_t stream, co
 	GRID_DISPATCH(grid_backward_kernel, plan, g, stream, gp, B, x, dL_denc, grid_grads, replicas, chunk_begin);
 	launch_check("grid_backward_kernel");
 }
-static void backward_finish(const tcnn_b200_plan* plan, cudaStream_t stream, const GridParams& gp, __half* grid_grads, __half* replicas) {
+// Adds the replica sums of the replicated levels among the encoding chunks [chunk_begin, chunk_end) to the gradient buffer.
+static void backward_finish(const tcnn_b200_plan* plan, cudaStream_t stream, const GridParams& gp, __half* grid_grads, __half* replicas,
+	uint32_t chunk_begin = 0, uint32_t chunk_end = 0xFFFFFFFFu) {
 	if (!gp.rep_entries) return;
+	const uint32_t F = plan->info.n_features_per_level, lpc = 8 / F;
+	const uint32_t level_begin = std::min(chunk_begin * lpc, gp.n_levels);
+	const uint32_t level_end = chunk_end > gp.n_levels ? gp.n_levels : std::min(chunk_end * lpc, gp.n_levels);
+	uint32_t entry_begin = 0xFFFFFFFFu, entry_end = 0;
+	for (uint32_t l = level_begin; l < level_end; ++l) {
+		if (!gp.level[l].replicated) continue;
+		entry_begin = std::min(entry_begin, gp.level[l].rep_offset);
+		entry_end = std::max(entry_end, gp.level[l].rep_offset + gp.level[l].size);
+	}
+	if (entry_begin >= entry_end) return;
 	ProfileScope prof(plan, stream, PK_GRID_BWD);
-	const uint32_t F = plan->info.n_features_per_level;
-	const uint32_t pairs = gp.rep_entries * F / 2;
-	grid_replica_reduce_kernel<<<(pairs + 63) / 64, 64, 0, stream>>>(gp, F, replicas, grid_grads);
+	const uint32_t pair_begin = entry_begin * F / 2, pair_end = entry_end * F / 2;
+	grid_replica_reduce_kernel<<<(pair_end - pair_begin + 63) / 64, 64, 0, stream>>>(gp, F, replicas, grid_grads, pair_begin, pair_end);
 	launch_check("grid_replica_reduce_kernel");
 }
 static void encode_backward(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t B, const float* x, const __half* dL_denc, __half* grid_grads, int zero_first, __half* replicas) {
@@ -649,13 +660,12 @@ extern "C" int tcnn_b200_training_fwd_bwd(const tcnn_b200_plan* plan, void* stre
 
 // ---- optimizer --------------------------------------------------------------------------------------------
 struct AdamBuffers { float* master; __half* params; __half* grads; float* m; float* v; uint32_t* steps; };
-static void adam_launch(const tcnn_b200_plan* plan, cudaStream_t stream, float grad_divisor, uint32_t adam_step_count, const AdamBuffers& b,
+static AdamArgs adam_args(const tcnn_b200_plan* plan, float grad_divisor, uint32_t adam_step_count, const AdamBuffers& b,
 	int zero_grid_grads, uint32_t begin, uint32_t end) {
 	const tcnn_b200_info& in = plan->info;
 	AdamArgs a{};
 	a.n = std::min<uint32_t>(end, (uint32_t)in.n_params);
 	a.begin = begin;
-	if (a.begin >= a.n) return;
 	a.n_matrix = (uint32_t)in.n_params_mlp;
 	a.loss_scale = grad_divisor;
 	a.learning_rate = in.learning_rate; a.beta1 = in.beta1; a.beta2 = in.beta2; a.epsilon = in.epsilon; a.l2_reg = in.l2_reg;
@@ -675,6 +685,12 @@ static void adam_launch(const tcnn_b200_plan* plan, cudaStream_t stream, float g
 	a.global_step = adam_step_count;
 	a.global_correction = std::sqrt(1 - std::pow(in.beta2, (float)adam_step_count)) / (1 - std::pow(in.beta1, (float)adam_step_count));
 	a.master = b.master; a.params = b.params; a.grads = b.grads; a.m = b.m; a.v = b.v; a.steps = b.steps;
+	return a;
+}
+static void adam_launch(const tcnn_b200_plan* plan, cudaStream_t stream, float grad_divisor, uint32_t adam_step_count, const AdamBuffers& b,
+	int zero_grid_grads, uint32_t begin, uint32_t end) {
+	const AdamArgs a = adam_args(plan, grad_divisor, adam_step_count, b, zero_grid_grads, begin, end);
+	if (a.begin >= a.n) return;
 	ProfileScope prof(plan, stream, PK_ADAM);
 	const uint32_t n_threads = (a.n - a.begin + 3) / 4;
 	adam_kernel<<<(n_threads + 255) / 256, 256, 0, stream>>>(a);
@@ -688,6 +704,18 @@ extern "C" int tcnn_b200_adam_step(const tcnn_b200_plan* plan, void* stream, flo
 	CHECK(params_fp32 && params_fp16 && grads_fp16 && first_moments && second_moments && param_steps, "null argument");
 	adam_launch(plan, (cudaStream_t)stream, grad_divisor, adam_step_count,
 		AdamBuffers{params_fp32, (__half*)params_fp16, (__half*)grads_fp16, first_moments, second_moments, param_steps}, zero_grid_grads, 0, (uint32_t)plan->info.n_params);
+	API_END
+}
+
+extern "C" int tcnn_b200_adam_step_range(const tcnn_b200_plan* plan, void* stream, float grad_divisor, uint32_t adam_step_count,
+	float* params_fp32, void* params_fp16, void* grads_fp16, float* first_moments, float* second_moments, uint32_t* param_steps, int zero_grid_grads,
+	uint64_t param_begin, uint64_t param_end) {
+	API_BEGIN
+	require_device(plan);
+	CHECK(params_fp32 && params_fp16 && grads_fp16 && first_moments && second_moments && param_steps, "null argument");
+	CHECK(param_begin % 4 == 0 && param_begin <= param_end && param_end <= plan->info.n_params, "bad parameter range");
+	adam_launch(plan, (cudaStream_t)stream, grad_divisor, adam_step_count,
+		AdamBuffers{params_fp32, (__half*)params_fp16, (__half*)grads_fp16, first_moments, second_moments, param_steps}, zero_grid_grads, (uint32_t)param_begin, (uint32_t)param_end);
 	API_END
 }
 
@@ -750,7 +778,7 @@ extern "C" int tcnn_b200_training_step(const tcnn_b200_plan* plan, void* stream_
 		const uint32_t group_begin = group_end - (group_end + remaining_groups - 1) / remaining_groups;
 		backward_scatter(plan, main, gp, B, x, w.dL_denc, gg, w.replicas, group_begin, group_end);
 		const bool last = group_begin == 0;
-		if (last) backward_finish(plan, main, gp, gg, w.replicas); // replicated coarse levels live in the first chunks
+		backward_finish(plan, main, gp, gg, w.replicas, group_begin, group_end); // replica sums of this group's coarse levels
 		CUDA_OK(cudaEventRecord(ev[1 + gi], main));
 		CUDA_OK(cudaStreamWaitEvent(aux, ev[1 + gi], 0));
 		const uint32_t lvl_begin = std::min(group_begin * levels_per_chunk, in.n_levels), lvl_end = std::min(group_end * levels_per_chunk, in.n_levels);
@@ -760,6 +788,100 @@ extern "C" int tcnn_b200_training_step(const tcnn_b200_plan* plan, void* stream_
 	}
 	CUDA_OK(cudaEventRecord(ev[6], aux));
 	CUDA_OK(cudaStreamWaitEvent(main, ev[6], 0)); // join
+	API_END
+}
+
+// ---- data parallel: sharded optimizer over peer memory ---------------------------------------------------------
+static void dp_shard(const tcnn_b200_plan* plan, uint32_t rank, uint32_t world, uint64_t* begin, uint64_t* end) {
+	const uint64_t n = plan->info.n_params;
+	const uint64_t per = ((n + world - 1) / world + 1023) / 1024 * 1024;
+	*begin = std::min<uint64_t>((uint64_t)rank * per, n);
+	*end = std::min<uint64_t>(*begin + per, n);
+}
+extern "C" int tcnn_b200_dp_shard(const tcnn_b200_plan* plan, uint32_t rank, uint32_t world_size, uint64_t* param_begin, uint64_t* param_end) {
+	API_BEGIN
+	CHECK(plan && param_begin && param_end && world_size >= 1 && world_size <= DP_MAX_RANKS && rank < world_size, "bad argument");
+	dp_shard(plan, rank, world_size, param_begin, param_end);
+	API_END
+}
+extern "C" uint32_t tcnn_b200_dp_flag_bytes(void) { return DP_FLAG_WORDS * 4; }
+
+extern "C" int tcnn_b200_training_step_dp(const tcnn_b200_plan* plan, void* stream_, uint32_t B, const float* x, const float* target,
+	float loss_scale, uint32_t adam_step_count, float* params_fp32_shard, float* first_moments_shard, float* second_moments_shard,
+	uint32_t* param_steps_shard, float* loss_out, void* output_fp16, void* workspace, const tcnn_b200_dp_comm* comm) {
+	API_BEGIN
+	require_device(plan); check_batch(B);
+	CHECK(x && target && params_fp32_shard && first_moments_shard && second_moments_shard && param_steps_shard && workspace && comm, "null argument");
+	CHECK(comm->world_size >= 1 && comm->world_size <= DP_MAX_RANKS && comm->rank < comm->world_size, "bad rank / world size (at most 8 ranks: one NVSwitch domain)");
+	CHECK(comm->epoch >= 1, "epoch starts at 1 and grows by one per call");
+	const tcnn_b200_info& in = plan->info;
+	CHECK(in.n_params % 4 == 0, "parameter count must be a multiple of 4");
+	DpComm c{};
+	c.rank = comm->rank; c.world = comm->world_size; c.epoch = comm->epoch;
+	for (uint32_t r = 0; r < c.world; ++r) {
+		CHECK(comm->peer_grads[r] && comm->peer_params[r] && comm->peer_flags[r], "null peer buffer");
+		c.peer_grads[r] = (__half*)comm->peer_grads[r]; c.peer_params[r] = (__half*)comm->peer_params[r]; c.peer_flags[r] = (uint32_t*)comm->peer_flags[r];
+	}
+	c.use_multicast = comm->grads_multicast && comm->params_multicast;
+#ifdef DP_STAMPS
+	c.use_multicast |= comm->reserved;
+#endif
+	c.grads_mc = (__half*)comm->grads_multicast; c.params_mc = (__half*)comm->params_multicast;
+
+	ensure_aux(plan);
+	cudaStream_t main = (cudaStream_t)stream_, aux = plan->aux;
+	const cudaEvent_t* ev = plan->ev;
+	const Workspace w = carve(plan, B, workspace);
+	const __half* p = c.peer_params[c.rank];
+	__half* g = c.peer_grads[c.rank];
+	__half* gg = g + in.n_params_mlp;
+	const GridParams gp = backward_params(plan, B, true);
+	MlpArgs a = base_mlp_args(plan, B, w.encoded, p);
+	a.target = target; a.output = (__half*)output_fp16; a.dL_dinput = w.dL_denc;
+	a.dW_partials = w.dw_partials; a.loss_partials = w.loss_partials; a.loss_scale = loss_scale;
+	const uint32_t mlp_grid = mlp_grid_size(plan, B / MLP_TILE, true);
+
+	// local part: identical to the single-GPU step up to the complete local gradient (grid gradients are zero on entry)
+	backward_prepare(plan, main, gp, gg, /*zero_first=*/0, w.replicas);
+	encode_forward(plan, main, B, x, p + in.n_params_mlp, w.encoded);
+	if (fused_scatter_available(plan)) {
+		a.dL_dinput = nullptr; a.positions = x; a.grid_grad = gg; a.replicas = w.replicas;
+		launch_mlp_train_fused(plan, main, a, mlp_grid, gp);
+		CUDA_OK(cudaEventRecord(ev[0], main));
+		CUDA_OK(cudaStreamWaitEvent(aux, ev[0], 0));
+		mlp_finalize(plan, aux, mlp_grid, w, g, loss_out, loss_out != nullptr); // beside the replica reduction
+		CUDA_OK(cudaEventRecord(ev[1], aux));
+		backward_finish(plan, main, gp, gg, w.replicas);
+		CUDA_OK(cudaStreamWaitEvent(main, ev[1], 0));
+	} else {
+		launch_mlp<MODE_TRAIN>(plan, main, a, mlp_grid);
+		mlp_finalize(plan, main, mlp_grid, w, g, loss_out, loss_out != nullptr);
+		backward_scatter(plan, main, gp, B, x, w.dL_denc, gg, w.replicas);
+		backward_finish(plan, main, gp, gg, w.replicas);
+	}
+	// exchange + optimizer: one kernel (optim_kernels.cuh, dp_adam_kernel)
+	uint64_t sb = 0, se = 0;
+	dp_shard(plan, c.rank, c.world, &sb, &se);
+#ifdef DP_STAMPS
+	if (const char* fw = getenv("DP_FAKE_WORLD")) dp_shard(plan, (uint32_t)atoi(getenv("DP_FAKE_RANK")), (uint32_t)atoi(fw), &sb, &se);
+#endif
+	AdamArgs ad = adam_args(plan, loss_scale * (float)c.world, adam_step_count,
+		AdamBuffers{params_fp32_shard - sb, nullptr, nullptr, first_moments_shard - sb, second_moments_shard - sb, param_steps_shard - sb}, 0, (uint32_t)sb, (uint32_t)se);
+	{
+		ProfileScope prof(plan, main, PK_ADAM);
+		const uint32_t n_groups = (uint32_t)((se - sb + 3) / 4);
+		const uint32_t maxw = c.world <= 2 ? 2 : c.world <= 4 ? 4 : 8;
+		// persistent: as many CTAs as are resident at once walk the shard; an empty shard still takes part in both barriers
+		using DpKernel = void (*)(const AdamArgs, const DpComm);
+		const DpKernel kernel = (c.use_multicast & 1) ? dp_adam_kernel<true, 8> : maxw == 2 ? dp_adam_kernel<false, 2> : maxw == 4 ? dp_adam_kernel<false, 4> : dp_adam_kernel<false, 8>;
+		int per_sm = 0;
+		CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, 256, 0));
+		const uint32_t blocks = std::max(1u, std::min((n_groups + 255) / 256, (uint32_t)plan->n_sms * (uint32_t)std::max(per_sm, 1)));
+		kernel<<<blocks, 256, 0, main>>>(ad, c);
+		launch_check("dp_adam_kernel");
+		// every rank has consumed this rank's gradients once the kernel has retired
+		CUDA_OK(cudaMemsetAsync(gg, 0, in.n_params_grid * 2, main));
+	}
 	API_END
 }
 

@@ -42,6 +42,17 @@ class Info(C.Structure):
 
 
 _P = C.c_void_p
+
+
+class DpComm(C.Structure):
+    """tcnn_b200_dp_comm (include/tcnn_b200.h)."""
+    _fields_ = [
+        ("rank", C.c_uint32), ("world_size", C.c_uint32), ("epoch", C.c_uint32), ("reserved", C.c_uint32),
+        ("peer_grads", C.c_void_p * 8), ("peer_params", C.c_void_p * 8), ("peer_flags", C.c_void_p * 8),
+        ("grads_multicast", C.c_void_p), ("params_multicast", C.c_void_p),
+    ]
+
+
 _SIGNATURES = {
     # name: (restype, argtypes)
     "tcnn_b200_last_error": (C.c_char_p, []),
@@ -65,6 +76,10 @@ _SIGNATURES = {
     "tcnn_b200_backward": (C.c_int, [_P, _P, C.c_uint32, _P, _P, _P, _P, _P, _P]),
     "tcnn_b200_training_fwd_bwd": (C.c_int, [_P, _P, C.c_uint32, _P, _P, _P, _P, C.c_float, C.c_int, _P, _P, _P]),
     "tcnn_b200_adam_step": (C.c_int, [_P, _P, C.c_float, C.c_uint32, _P, _P, _P, _P, _P, _P, C.c_int]),
+    "tcnn_b200_adam_step_range": (C.c_int, [_P, _P, C.c_float, C.c_uint32, _P, _P, _P, _P, _P, _P, C.c_int, C.c_uint64, C.c_uint64]),
+    "tcnn_b200_dp_shard": (C.c_int, [_P, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
+    "tcnn_b200_dp_flag_bytes": (C.c_uint32, []),
+    "tcnn_b200_training_step_dp": (C.c_int, [_P, _P, C.c_uint32, _P, _P, C.c_float, C.c_uint32, _P, _P, _P, _P, _P, _P, _P, C.POINTER(DpComm)]),
     "tcnn_b200_training_step": (C.c_int, [_P, _P, C.c_uint32, _P, _P, C.c_float, C.c_uint32, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "tcnn_b200_profile_enable": (C.c_int, [_P, C.c_int]),
     "tcnn_b200_profile_read": (C.c_int, [_P, C.POINTER(C.c_float), C.POINTER(C.c_uint32), C.c_uint32]),

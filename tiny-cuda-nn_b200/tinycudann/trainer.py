@@ -4,7 +4,9 @@
 The trainer owns the parameter buffer in the reference's layout (one allocation: fp32 master | fp16 params |
 fp16 gradients, trainer.h:75,322-336; MLP weights first, grid tables second), the Adam state
 (optimizers/adam.h:128-148), and drives the C-ABI kernels.  Data-parallel training (one process per GPU) adds exactly
-one collective per step: an all-reduce of the fp16 gradient buffer, with 1/world_size folded into the Adam kernel.
+one exchange per step: by default a fused reduce-scatter + Adam + all-gather kernel over NVLink peer memory
+(dp_mode="peer", tcnn_b200_training_step_dp), else an NCCL all-reduce of the fp16 gradient buffer (dp_mode="allreduce"),
+with 1/world_size folded into the Adam kernel either way.
 """
 from __future__ import annotations
 
@@ -16,13 +18,13 @@ import torch
 from . import _lib
 from ._lib import check, ptr
 from .modules import NativeModule, _stream_ptr
-from .parallel import allreduce_gradients, grad_divisor
+from .parallel import PeerMemory, allreduce_gradients, grad_divisor
 
 LOSS_SCALE = 128.0  # default_loss_scale<__half>(), common.h:229-233; trainer.h:174
 
 
 class Trainer:
-    def __init__(self, native: NativeModule, seed: int = 1337, device="cuda", process_group=None):
+    def __init__(self, native: NativeModule, seed: int = 1337, device="cuda", process_group=None, dp_mode: str | None = None, use_multicast: bool = True):
         self.native = native
         self.lib = native.lib
         self.device = torch.device(device)
@@ -30,10 +32,23 @@ class Trainer:
         P = int(self.info.n_params)
         self.n_params = P
         # trainer.h:75: [fp32 master (4P) | fp16 params (2P) | fp16 grads (2P)]
-        self.params_buffer = torch.zeros(8 * P, dtype=torch.uint8, device=self.device)
-        self.params_full_precision = self.params_buffer[: 4 * P].view(torch.float32)
-        self.params = self.params_buffer[4 * P : 6 * P].view(torch.half)
-        self.param_gradients = self.params_buffer[6 * P : 8 * P].view(torch.half)
+        self.process_group = process_group
+        self.world_size = 1
+        if process_group is not None or (torch.distributed.is_available() and torch.distributed.is_initialized()):
+            self.world_size = torch.distributed.get_world_size(process_group)
+        self.peer_memory = None
+        if dp_mode is None:
+            dp_mode = "peer" if (self.world_size > 1 and self.device.type == "cuda" and torch.distributed.get_backend(process_group) == "nccl") else "allreduce"
+        if dp_mode == "peer":
+            # fp16 parameters and gradients live in symmetric memory that every rank maps (parallel.PeerMemory)
+            self.peer_memory = PeerMemory(native, self.device, process_group, use_multicast=use_multicast)
+            self.params_full_precision = torch.zeros(P, dtype=torch.float32, device=self.device)
+            self.params, self.param_gradients = self.peer_memory.params, self.peer_memory.grads
+        else:
+            self.params_buffer = torch.zeros(8 * P, dtype=torch.uint8, device=self.device)
+            self.params_full_precision = self.params_buffer[: 4 * P].view(torch.float32)
+            self.params = self.params_buffer[4 * P : 6 * P].view(torch.half)
+            self.param_gradients = self.params_buffer[6 * P : 8 * P].view(torch.half)
         # AdamOptimizer::allocate (adam.h:128-148)
         self.first_moments = torch.zeros(P, dtype=torch.float32, device=self.device)
         self.second_moments = torch.zeros(P, dtype=torch.float32, device=self.device)
@@ -42,10 +57,6 @@ class Trainer:
         self.loss_value = torch.zeros(1, dtype=torch.float32, device=self.device)
         self._grid_grads_clean = True  # grid gradient region is all zero (after init / after an optimizer step)
         self.use_fused_step = True     # single GPU: tcnn_b200_training_step (Adam overlapped with the scatter)
-        self.process_group = process_group
-        self.world_size = 1
-        if process_group is not None or (torch.distributed.is_available() and torch.distributed.is_initialized()):
-            self.world_size = torch.distributed.get_world_size(process_group)
         self.initialize_params(seed)
 
     # trainer.h:68-87
@@ -67,6 +78,11 @@ class Trainer:
     def training_step(self, input: torch.Tensor, target: torch.Tensor, run_optimizer: bool = True, output: torch.Tensor | None = None):
         B = input.shape[0]
         ws = self.native.workspace(B, self.device)
+        if self.peer_memory is not None and run_optimizer:
+            if not self._grid_grads_clean:
+                self.param_gradients[int(self.info.n_params_mlp):].zero_()
+                self._grid_grads_clean = True
+            return self._peer_step(input, target, output, ws)
         if run_optimizer and self.use_fused_step and self.world_size == 1 and self._grid_grads_clean:
             # single GPU: one fused call, Adam of finished level groups overlaps the remaining gradient scatter
             self.current_step += 1
@@ -79,15 +95,43 @@ class Trainer:
             self.native.handle, _stream_ptr(), B, ptr(input), ptr(target), ptr(self.params), ptr(self.param_gradients),
             LOSS_SCALE, 0 if self._grid_grads_clean else 1, ptr(self.loss_value), ptr(output), ptr(ws)))
         self._grid_grads_clean = False
-        if self.world_size > 1:
+        if self.world_size > 1 and self.peer_memory is None:
             for h in allreduce_gradients(self.param_gradients, self.process_group):
                 h.wait()  # stream-ordered for NCCL: makes the current stream wait, the host does not block
         if run_optimizer:
             self.optimizer_step(LOSS_SCALE)
         return self
 
+    def _peer_step(self, input, target, output, ws):
+        """Data-parallel step over NVLink peer memory: local forward/backward, then ONE kernel that sums this rank's shard
+        of the gradients over all ranks, applies Adam to it and stores the new fp16 parameters into every rank
+        (tcnn_b200_training_step_dp).  Master weights and Adam state are live only inside the rank's own shard."""
+        B = input.shape[0]
+        self.current_step += 1
+        pm = self.peer_memory
+        pm.comm.epoch += 1
+        b, e = pm.shard
+        check(self.lib.tcnn_b200_training_step_dp(
+            self.native.handle, _stream_ptr(), B, ptr(input), ptr(target), LOSS_SCALE, self.current_step,
+            ptr(self.params_full_precision[b:e]), ptr(self.first_moments[b:e]), ptr(self.second_moments[b:e]),
+            ptr(self.param_steps[b:e]), ptr(self.loss_value), ptr(output), ptr(ws), _lib.C.byref(pm.comm)))
+        return self
+
+    def gather_params_full_precision(self) -> torch.Tensor:
+        """fp32 master weights of all shards (collective; in peer-memory mode each rank only updates its own shard)."""
+        if self.peer_memory is None:
+            return self.params_full_precision.clone()
+        full = self.params_full_precision.clone()
+        for r in range(self.world_size):
+            b, e = self.peer_memory.shard_of(r)
+            if e > b:
+                torch.distributed.broadcast(full[b:e], src=torch.distributed.get_global_rank(self.process_group, r) if self.process_group else r, group=self.process_group)
+        return full
+
     # trainer.h:155-157 + adam.h:150-188
     def optimizer_step(self, loss_scale: float = LOSS_SCALE):
+        if self.peer_memory is not None:
+            raise RuntimeError("dp_mode='peer' shards the optimizer state: use training_step(run_optimizer=True), or dp_mode='allreduce'")
         self.current_step += 1
         check(self.lib.tcnn_b200_adam_step(
             self.native.handle, _stream_ptr(), grad_divisor(loss_scale, self.world_size), self.current_step,
@@ -124,8 +168,8 @@ class TrainableModel:
     trainer: Trainer
 
 
-def create_from_config(n_input_dims: int, n_output_dims: int, config: dict, seed: int = 1337, device="cuda", process_group=None) -> TrainableModel:
+def create_from_config(n_input_dims: int, n_output_dims: int, config: dict, seed: int = 1337, device="cuda", process_group=None, **trainer_kwargs) -> TrainableModel:
     """config.h:53-63.  config = {"loss": {...}, "optimizer": {...}, "encoding": {...}, "network": {...}}."""
     with torch.cuda.device(device):
         native = NativeModule(n_input_dims, n_output_dims, config)
-        return TrainableModel(network=native, trainer=Trainer(native, seed=seed, device=device, process_group=process_group))
+        return TrainableModel(network=native, trainer=Trainer(native, seed=seed, device=device, process_group=process_group, **trainer_kwargs))
