@@ -170,7 +170,8 @@ def run_reference(args, cfg):
 
 
 DP_NOTE = {
-    "peer": "one fused kernel per step: NVSwitch multimem.ld_reduce of this rank's gradient shard -> Adam on the shard -> multimem.st of the new fp16 parameters to all ranks, both barriers in-kernel",
+    "peer": "one fused kernel per step: sum of this rank's gradient shard over all ranks (NVSwitch multimem.ld_reduce; plain peer loads at 2 GPUs) -> Adam on the shard -> new fp16 parameters to all ranks (multimem.st / peer stores), both barriers in-kernel",
+    "peer-mc": "one fused kernel per step: NVSwitch multimem.ld_reduce of this rank's gradient shard -> Adam on the shard -> multimem.st of the new fp16 parameters to all ranks, both barriers in-kernel",
     "peer-p2p": "one fused kernel per step: peer loads of this rank's gradient shard from all ranks -> Adam on the shard -> peer stores of the new fp16 parameters, both barriers in-kernel",
     "allreduce": "fp16 NCCL all-reduce of the 22.4 MB gradient buffer per step, replicated Adam",
 }
@@ -185,7 +186,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=300)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--force-dp", action="store_true", help="N = 1: run the data-parallel step on a one-rank group")
-    ap.add_argument("--dp-mode", default="peer", choices=["peer", "peer-p2p", "allreduce"],
+    ap.add_argument("--dp-mode", default="peer", choices=["peer", "peer-p2p", "peer-mc", "allreduce"],
                     help="N > 1: fused reduce-scatter+Adam+all-gather kernel over NVSwitch multicast (peer) or plain peer loads/stores (peer-p2p), or NCCL all-reduce + replicated Adam (allreduce)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
@@ -212,7 +213,7 @@ def main():
     elif args.force_dp:  # development aid: the data-parallel step on a one-rank group (ncu can profile it)
         dist.init_process_group("nccl", init_method="tcp://127.0.0.1:29533", rank=0, world_size=1, device_id=dev)
 
-    model = tcnn.create_from_config(N_IN, N_OUT, cfg, seed=1337, device=dev, **({} if world == 1 and not args.force_dp else {"dp_mode": args.dp_mode.split("-")[0], "use_multicast": args.dp_mode != "peer-p2p"}))
+    model = tcnn.create_from_config(N_IN, N_OUT, cfg, seed=1337, device=dev, **({} if world == 1 and not args.force_dp else {"dp_mode": args.dp_mode.split("-")[0], "use_multicast": {"peer": None, "peer-p2p": False, "peer-mc": True}.get(args.dp_mode)}))
     tr = model.trainer
     info = tr.info
     lib = tr.lib

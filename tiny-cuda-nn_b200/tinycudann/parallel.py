@@ -47,7 +47,7 @@ class PeerMemory:
     same sizes from torch's symmetric-memory allocator, the rendezvous maps all ranks' buffers (and, on NVSwitch systems,
     a multicast alias) into each process, and the pointers go into a tcnn_b200_dp_comm."""
 
-    def __init__(self, native, device, group=None, use_multicast: bool = True):
+    def __init__(self, native, device, group=None, use_multicast: bool | None = None):
         import torch.distributed._symmetric_memory as symm
 
         from . import _lib
@@ -77,6 +77,10 @@ class PeerMemory:
         c.rank, c.world_size, c.epoch = self.rank, self.world, 0
         for r in range(self.world):
             c.peer_params[r], c.peer_grads[r], c.peer_flags[r] = pp[r], gp[r], fp[r]
+        if use_multicast is None:
+            # measured (profiles/r01d_bench_n*): 2 ranks 0.235 ms/step with peer loads vs 0.247 through the switch;
+            # 4 ranks 0.240 vs 0.235; 8 ranks 0.248 vs 0.237
+            use_multicast = self.world > 2
         self.multicast = bool(use_multicast and pmc and gmc)
         if self.multicast:
             c.params_multicast, c.grads_multicast = pmc, gmc

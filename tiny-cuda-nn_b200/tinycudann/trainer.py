@@ -24,7 +24,7 @@ LOSS_SCALE = 128.0  # default_loss_scale<__half>(), common.h:229-233; trainer.h:
 
 
 class Trainer:
-    def __init__(self, native: NativeModule, seed: int = 1337, device="cuda", process_group=None, dp_mode: str | None = None, use_multicast: bool = True):
+    def __init__(self, native: NativeModule, seed: int = 1337, device="cuda", process_group=None, dp_mode: str | None = None, use_multicast: bool | None = None):
         self.native = native
         self.lib = native.lib
         self.device = torch.device(device)
