@@ -1,0 +1,53 @@
+/* tcnn::cpp::Module — the raw-pointer API the PyTorch extension of the reference is written against
+ * (include/tiny-cuda-nn/cpp_api.h:86-115, src/cpp_api.cu:62-165), over the tcnn_b200 C ABI.  All pointers are device
+ * pointers owned by the caller: input [B][D] fp32, output [B][16] fp16, params / dL_dparams [n_params] fp16. */
+#pragma once
+#include "trainer.h"
+
+namespace tcnn { namespace cpp {
+
+enum class Precision { Fp32, Fp16 };
+inline uint32_t batch_size_granularity() { return tcnn_b200_batch_size_granularity(); }
+inline float default_loss_scale(Precision p) { return p == Precision::Fp16 ? 128.0f : 1.0f; }
+inline Precision preferred_precision() { return Precision::Fp16; }
+
+struct Context { GPUMemory<char> saved; }; /* what backward needs: the encoded batch */
+
+class Module {
+public:
+	Module(uint32_t n_input_dims, uint32_t n_output_dims, const std::string& encoding_json, const std::string& network_json)
+	: m_network("{\"encoding\": " + encoding_json + ", \"network\": " + network_json + "}", n_input_dims, n_output_dims) {}
+
+	void inference(cudaStream_t stream, uint32_t n_elements, const float* input, void* output, void* params) {
+		TCNN_B200_CHECK_THROW(tcnn_b200_inference(m_network.plan(), stream, n_elements, input, params, output, nullptr, m_network.workspace(n_elements)));
+	}
+	Context forward(cudaStream_t stream, uint32_t n_elements, const float* input, void* output, void* params, bool prepare_input_gradients) {
+		if (prepare_input_gradients) throw std::runtime_error("tcnn_b200: dL_dinput of the grid encoding is not implemented yet");
+		Context ctx;
+		ctx.saved.resize(tcnn_b200_workspace_bytes(m_network.plan(), n_elements));
+		TCNN_B200_CHECK_THROW(tcnn_b200_forward(m_network.plan(), stream, n_elements, input, params, output, ctx.saved.data()));
+		return ctx;
+	}
+	void backward(cudaStream_t stream, const Context& ctx, uint32_t n_elements, float* dL_dinput, const void* dL_doutput, void* dL_dparams,
+		const float* input, const void* /*output*/, const void* params) {
+		TCNN_B200_CHECK_THROW(tcnn_b200_backward(m_network.plan(), stream, n_elements, input, params, dL_doutput, dL_dparams, dL_dinput, ctx.saved.data()));
+	}
+	void initialize_params(size_t seed, float* params_full_precision) {
+		TCNN_B200_CHECK_THROW(tcnn_b200_init_params(m_network.plan(), nullptr, seed, 0, params_full_precision));
+	}
+	uint32_t n_input_dims() const { return m_network.input_width(); }
+	uint32_t n_output_dims() const { return m_network.padded_output_width(); } /* padded, as in the reference */
+	size_t n_params() const { return m_network.n_params(); }
+	Precision param_precision() const { return Precision::Fp16; }
+	Precision output_precision() const { return Precision::Fp16; }
+	std::string name() const { return "NetworkWithInputEncoding"; }
+
+private:
+	Network m_network;
+};
+
+inline Module* create_network_with_input_encoding(uint32_t n_input_dims, uint32_t n_output_dims, const std::string& encoding_json, const std::string& network_json) {
+	return new Module(n_input_dims, n_output_dims, encoding_json, network_json);
+}
+
+}} // namespace tcnn::cpp

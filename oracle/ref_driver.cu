@@ -186,6 +186,11 @@ static int mode_curve(int argc, char** argv) {
 	for (uint32_t i = 0; i < n_steps; ++i) {
 		generate_random_uniform<float>(stream, rng, (size_t)B * n_in, input.data());
 		synth_target<<<div_round_up(B, 256u), 256, 0, stream>>>(B, n_in, n_out, input.data(), target.data());
+		if (i == 0 || i + 1 == n_steps) { // pins the batch generator of the parity test (pcg32 stream position per step)
+			CUDA_CHECK_THROW(cudaStreamSynchronize(stream));
+			write_dev(out + (i == 0 ? "/x_first.f32" : "/x_last.f32"), input.data(), (size_t)B * n_in);
+			write_dev(out + (i == 0 ? "/t_first.f32" : "/t_last.f32"), target.data(), (size_t)B * n_out);
+		}
 		auto ctx = model.trainer->training_step(stream, input, target);
 		losses[i] = model.trainer->loss(stream, *ctx);
 	}

@@ -338,6 +338,19 @@ class MlpConfig:
         return out
 
 
+def matmul_acc(a: np.ndarray, b: np.ndarray, acc=np.float32) -> np.ndarray:
+    """a [M, K] @ b [K, N] for fp16 operands.  acc = np.float32 / np.float64: one accumulation, the caller rounds.
+    acc = "hmma16": the accumulator is rounded to fp16 after every 16-deep MMA step, which is how tensor-core fp16
+    accumulation (the reference's wmma fragments, fully_fused_mlp.cu:47-129) behaves; numpy's own fp16 matmul does NOT do
+    this (it accumulates in fp32 and rounds once)."""
+    if acc != "hmma16":
+        return a.astype(acc) @ b.astype(acc)
+    out = np.zeros((a.shape[0], b.shape[1]), np.float16)
+    for k0 in range(0, a.shape[1], 16):
+        out = (out.astype(np.float32) + a[:, k0:k0 + 16].astype(np.float32) @ b[k0:k0 + 16].astype(np.float32)).astype(np.float16)
+    return out
+
+
 def mlp_forward(cfg: MlpConfig, params: np.ndarray, x: np.ndarray, acc=np.float32):
     """x: fp16 [B, n_input] -> (output fp16 [B, out_pad], list of post-activation hidden fp16 [B, W]).
 
@@ -348,10 +361,10 @@ def mlp_forward(cfg: MlpConfig, params: np.ndarray, x: np.ndarray, acc=np.float3
     h = x.astype(np.float16)
     hidden = []
     for w in ws[:-1]:
-        z = h.astype(acc) @ w.astype(acc).T
+        z = matmul_acc(h, w.T, acc)
         h = np.maximum(z, 0).astype(np.float16)
         hidden.append(h)
-    y = (h.astype(acc) @ ws[-1].astype(acc).T).astype(np.float16)
+    y = matmul_acc(h, ws[-1].T, acc).astype(np.float16)
     return y, hidden
 
 
@@ -367,7 +380,7 @@ def mlp_backward(cfg: MlpConfig, params: np.ndarray, x: np.ndarray, hidden, dy: 
     for k in range(len(ws) - 1, -1, -1):
         inp = hidden[k - 1] if k > 0 else x.astype(np.float16)
         grads[k] = g.astype(np.float64).T @ inp.astype(np.float64)
-        z = g.astype(acc) @ ws[k].astype(acc)
+        z = matmul_acc(g, ws[k], acc)
         if k > 0:
             z = z * (hidden[k - 1] > 0)
         g = z.astype(np.float16)
@@ -436,6 +449,29 @@ def adam_step(cfg: AdamConfig, n_matrix: int, master: np.ndarray, grads_h: np.nd
 # Parameter initialisation (trainer.h:50-87; network_with_input_encoding.h:124-130; fully_fused_mlp.cu:866-891;
 # gpu_matrix.h:284-299 xavier on the host; grid.h:1059-1062 + random.h:39-71 uniform(-1e-4,1e-4) on the device)
 # --------------------------------------------------------------------------------------------------
+def random_uniform(rng: Pcg32, n: int) -> np.ndarray:
+    """generate_random_uniform<float>(stream, rng, n, out) with lower = 0, upper = 1 (random.h:39-71): thread i of
+    n_threads = 128 * ceil(ceil(n/4)/128) advances the generator by 4 i and writes element i + n_threads * j with its j-th
+    draw; afterwards the host generator is advanced by n.  Used by samples/benchmarks to draw training batches."""
+    n_threads = next_multiple((n + 3) // 4, 128)
+    draws = _uint_to_float01(pcg32_stream(rng.copy(), 4 * n_threads)).reshape(n_threads, 4)
+    flat = draws.T.reshape(-1)[:n].copy()  # val * (1 - 0) + 0 is exact
+    rng.advance(n)
+    return flat
+
+
+def synth_target(x: np.ndarray, n_out: int) -> np.ndarray:
+    """The analytic training target of oracle/ref_driver.cu (synth_target kernel): fp32 throughout."""
+    n, n_in = x.shape
+    s = np.zeros(n, np.float32)
+    for d in range(n_in):
+        s = (s + x[:, d] * F32(1.0 + 0.5 * d)).astype(np.float32)
+    t = np.empty((n, n_out), np.float32)
+    for c in range(n_out):
+        t[:, c] = F32(0.5) + F32(0.5) * np.sin((F32(6.2831853) * F32(c + 1) * s).astype(np.float32), dtype=np.float32)
+    return t
+
+
 def init_params(mlp: MlpConfig, grid: GridConfig | None, seed: int = 1337, trainer_seeding: bool = True) -> np.ndarray:
     """fp32 [P_mlp + P_grid], MLP first (SURVEY F4).  trainer_seeding=True reproduces Trainer (seed_seq -> pcg32);
     False reproduces cpp::Module::initialize_params (pcg32{seed} directly, src/cpp_api.cu:124-127)."""

@@ -27,10 +27,38 @@ CASES = [  # name, config, n_in, n_out, B
     ("f4_3d_T14", common.CONFIG_F4, 3, 3, 512),
 ]
 SAMPLE_STRIDE = 997
+CURVES = [  # name, config, n_in, n_out, B, steps, seed
+    ("curve_cfg1_2d_T19", common.CONFIG_1, 2, 3, 1 << 16, 1000, 42),
+    ("curve_nerf_3d_T19", common.CONFIG_NERF, 3, 4, 1 << 16, 1000, 43),
+]
+
+
+def curves(outdir):
+    """1000 training steps of the reference (`ref_driver curve`): batches drawn with the reference's own pcg32
+    generate_random_uniform, analytic target; the loss of every step + first/last batch (pins the batch generator)."""
+    for name, cfg, n_in, n_out, B, steps, seed in CURVES:
+        with tempfile.TemporaryDirectory() as d:
+            with open(os.path.join(d, "cfg.json"), "w") as f:
+                json.dump(cfg, f)
+            r = subprocess.run([REF, "curve", os.path.join(d, "cfg.json"), str(n_in), str(n_out), str(B), str(steps), str(seed), d],
+                               capture_output=True, text=True, timeout=900)
+            print(name, r.returncode, r.stdout.strip(), r.stderr.strip()[-400:], flush=True)
+            if r.returncode != 0:
+                continue
+            rd = lambda fn: np.fromfile(os.path.join(d, fn), dtype=np.float32)  # noqa: E731
+            k = 4096
+            np.savez_compressed(
+                os.path.join(outdir, name + ".npz"), config=json.dumps(cfg), n_in=n_in, n_out=n_out, B=B, steps=steps, seed=seed,
+                losses=rd("losses.f32"), x_first=rd("x_first.f32").reshape(B, n_in)[:k], x_last=rd("x_last.f32").reshape(B, n_in)[-k:],
+                t_first=rd("t_first.f32").reshape(B, n_out)[:k], t_last=rd("t_last.f32").reshape(B, n_out)[-k:])
+            print(name, "saved", os.path.getsize(os.path.join(outdir, name + ".npz")), "bytes", flush=True)
 
 
 def main(outdir):
     os.makedirs(outdir, exist_ok=True)
+    curves(outdir)
+    if os.environ.get("GOLDEN_CURVES_ONLY"):
+        return
     for name, cfg, n_in, n_out, B in CASES:
         x, t = common.synth_inputs(B, n_in, n_out, seed=1)
         with tempfile.TemporaryDirectory() as d:

@@ -120,3 +120,14 @@ def test_product_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 src = open(os.path.join(d, f), errors="ignore").read()
                 assert not re.search(r"^\s*(from|import)\s+oracle|#include\s+[\"<][^\n]*oracle", src, re.M), f
+
+
+def test_cpp_facade_compiles_and_builds_a_plan_without_gpu():
+    """include/tiny-cuda-nn/*.h (create_from_config / Trainer / Network / GPUMatrix / cpp::Module over the C ABI) compile
+    with plain g++; without a device the sample host can still build the plan and report the reference's sizes."""
+    import subprocess
+    import __graft_entry__ as ge
+    exe = ge.build_cpp_facade_sample()
+    r = subprocess.run([exe, "--no-gpu"], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "n_params=11191808 padded_output_width=16" in r.stdout

@@ -373,6 +373,49 @@ def test_peer_memory_step_on_all_gpus(dev):
     assert r.returncode == 0 and "dp_peer_check ok" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
 
 
+@pytest.mark.parametrize("name", ["curve_cfg1_2d_T19", "curve_nerf_3d_T19"])
+def test_loss_curve_vs_reference(dev, name):
+    """north_star: training loss after 1000 steps within 2 % of the reference.  Same initial parameters (bit-exact init),
+    same batches (the reference's pcg32 generate_random_uniform stream, restated in the oracle and pinned by the first
+    and last batch of the reference run), same analytic target; golden = loss of every step of `ref_driver curve`."""
+    import tinycudann as tcnn
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    cfg = json.loads(str(g["config"]))
+    B, n_in, n_out, steps, seed = (int(g[k]) for k in ("B", "n_in", "n_out", "steps", "seed"))
+    ref = g["losses"].astype(np.float64)
+    tr = tcnn.create_from_config(n_in, n_out, cfg, seed=1337, device=dev).trainer
+    rng = O.Pcg32(seed)
+    losses = torch.zeros(steps, dtype=torch.float32, device=dev)
+    for i in range(steps):
+        x_np = O.random_uniform(rng, B * n_in).reshape(B, n_in)
+        if i == 0:
+            assert np.array_equal(x_np[: len(g["x_first"])], g["x_first"])
+        x = torch.from_numpy(x_np).to(dev)
+        t = torch.from_numpy(O.synth_target(x_np, n_out)).to(dev)
+        tr.training_step(x, t)
+        losses[i] = tr.loss_value[0]
+    assert np.array_equal(x_np[-len(g["x_last"]):], g["x_last"])
+    ours = losses.cpu().numpy().astype(np.float64)
+    assert abs(ours[0] - ref[0]) <= 1e-3 * ref[0], (ours[0], ref[0])          # same parameters, same batch
+    for lo, hi in ((0, 10), (10, 50), (50, 100), (100, 200), (200, 500), (500, 950)):
+        a, b = ours[lo:hi].mean(), ref[lo:hi].mean()
+        assert abs(a - b) <= 0.10 * b, f"steps {lo}-{hi}: {a} vs reference {b}"    # trajectory stays on the reference's curve
+    a, b = ours[-50:].mean(), ref[-50:].mean()
+    print(f"{name}: final loss (mean of last 50 steps) {a:.4e}, reference {b:.4e}, ratio {a / b:.4f}")
+    assert abs(a - b) <= 0.02 * b, f"loss after {steps} steps {a} vs reference {b}"
+
+
+def test_cpp_facade_host_trains(dev):
+    """tests/cpp/facade_train.cpp: create_from_config -> Trainer::training_step x300 -> Trainer::loss -> Network::inference
+    through the C++ facade headers; exit code 0 = loss fell 20x, inference matches the training loss, bad batch size throws."""
+    import subprocess
+    import __graft_entry__ as ge
+    exe = ge.build_cpp_facade_sample()
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "inference mse" in r.stdout
+
+
 def test_batch_size_must_be_multiple_of_256(dev):
     import tinycudann as tcnn
     model = tcnn.create_from_config(2, 3, common.CONFIG_1, seed=1, device=dev)

@@ -83,3 +83,21 @@ def test_adam_first_step(case):
     mm, vv, ss = np.zeros(n, np.float32), np.zeros(n, np.float32), np.zeros(n, np.uint32)
     O.adam_step(ac, n, master, z["grads_mlp"], mm, vv, ss)  # the reference's own gradients -> its own update
     assert np.max(np.abs(master - z["params_after_mlp"])) < 2e-7 + 1e-5 * ac.learning_rate
+
+
+@pytest.mark.parametrize("name", ["curve_cfg1_2d_T19", "curve_nerf_3d_T19"])
+def test_batch_generator_matches_reference_run(name):
+    """random_uniform / synth_target restate generate_random_uniform (random.h:39-71) and the driver's target kernel:
+    the first and the 1000th batch of the reference's loss-curve run are reproduced bit for bit (targets to 1 ulp of sinf)."""
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    B, n_in, n_out, steps, seed = (int(g[k]) for k in ("B", "n_in", "n_out", "steps", "seed"))
+    rng = O.Pcg32(seed)
+    x0 = O.random_uniform(rng, B * n_in).reshape(B, n_in)
+    rng.advance(B * n_in * (steps - 2))
+    xl = O.random_uniform(rng, B * n_in).reshape(B, n_in)
+    k = len(g["x_first"])
+    assert np.array_equal(x0[:k], g["x_first"]) and np.array_equal(xl[-k:], g["x_last"])
+    assert np.abs(O.synth_target(x0[:k], n_out) - g["t_first"]).max() < 1e-5
+    assert np.abs(O.synth_target(xl[-k:], n_out) - g["t_last"]).max() < 1e-5
+    losses = g["losses"]
+    assert losses.shape == (steps,) and losses[-50:].mean() < 1e-3 * losses[0]
