@@ -368,7 +368,7 @@ def mlp_forward(cfg: MlpConfig, params: np.ndarray, x: np.ndarray, acc=np.float3
     return y, hidden
 
 
-def mlp_backward(cfg: MlpConfig, params: np.ndarray, x: np.ndarray, hidden, dy: np.ndarray, acc=np.float32):
+def mlp_backward(cfg: MlpConfig, params: np.ndarray, x: np.ndarray, hidden, dy: np.ndarray, acc=np.float32, dw_acc=np.float64):
     """dy: fp16 [B, out_pad] (loss-scaled) -> (dparams float64 [n_params] exact-ish, dx fp16 [B, n_input]).
 
     Chain (fully_fused_mlp.cu:150-259): g = (W_next^T dy) * relu'(h) with the mask taken from the stored
@@ -379,7 +379,7 @@ def mlp_backward(cfg: MlpConfig, params: np.ndarray, x: np.ndarray, hidden, dy: 
     g = dy.astype(np.float16)
     for k in range(len(ws) - 1, -1, -1):
         inp = hidden[k - 1] if k > 0 else x.astype(np.float16)
-        grads[k] = g.astype(np.float64).T @ inp.astype(np.float64)
+        grads[k] = matmul_acc(np.ascontiguousarray(g.T), inp, dw_acc).astype(np.float64)
         z = matmul_acc(g, ws[k], acc)
         if k > 0:
             z = z * (hidden[k - 1] > 0)

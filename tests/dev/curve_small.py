@@ -27,6 +27,7 @@ if mode == "gpu":
         np.save(os.path.join(out, f"ours{rep}.npy"), losses.cpu().numpy())
 else:
     acc = "hmma16" if mode.startswith("oracle16") else np.float32
+    steps = 220
     g, m = common.oracle_configs(cfg, n_in, n_out)
     p32 = O.init_params(m, g, 1337, True)
     ad = O.AdamConfig()
@@ -39,7 +40,7 @@ else:
         enc = O.grid_forward(g, x, p16[m.n_params:])
         y, hidden = O.mlp_forward(m, p16[:m.n_params], enc, acc)
         lv, dy = O.loss_l2(y, t, n_out)
-        dW, dx = O.mlp_backward(m, p16[:m.n_params], enc, hidden, dy, acc)
+        dW, dx = O.mlp_backward(m, p16[:m.n_params], enc, hidden, dy, acc, "hmma16" if "dw16" in mode else np.float64)
         gg = O.grid_backward(g, x, dx)
         grads = np.concatenate([dW, gg]).astype(np.float16)
         O.adam_step(ad, m.n_params, p32, grads, mm, vv, st)

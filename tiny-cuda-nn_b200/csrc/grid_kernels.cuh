@@ -198,6 +198,9 @@ __global__ void __launch_bounds__(256) grid_forward_kernel(const __grid_constant
 // Scatter one sample's 8-half chunk of dL/d(encoded) (fp16, loss-scaled) into the fp16 grid gradient.
 // Same arithmetic as grid.h:248-318: product (half)weight * grad rounded to fp16, then red.add.noftz.f16x2.
 // Shared by grid_backward_kernel and the fused MLP training kernel (mlp_kernels.cuh).
+#ifndef TCNN_B200_SCATTER_QUAD
+#define TCNN_B200_SCATTER_QUAD 1
+#endif
 template <int D, int F>
 __device__ __forceinline__ void scatter_chunk(const GridParams& gp, const float (&p)[D], uint4 gv, uint32_t chunk,
 	__half* __restrict__ grid_grad, __half* __restrict__ replicas, uint32_t replica_id) {
@@ -238,10 +241,20 @@ __device__ __forceinline__ void scatter_chunk(const GridParams& gp, const float 
 #pragma unroll
 			for (int c = 0; c < NC; c += 2) {
 				const uint32_t v0 = h2_bits(__hmul2(wh[c], g.h2[s])), v1 = h2_bits(__hmul2(wh[c + 1], g.h2[s]));
+#if TCNN_B200_SCATTER_QUAD
+				// 16-byte slot {idx & ~3 .. idx | 3}: holds the dim-0 neighbour unless idx % 4 == 3 -> 1.25 reductions per pair
+				const uint32_t l0 = idx[c] & 3u, l1 = idx[c + 1] & 3u;
+				const bool together = ((idx[c] ^ idx[c + 1]) & ~3u) == 0u && l0 != l1;
+				const uint32_t q0 = l0 == 0 ? v0 : (together && l1 == 0 ? v1 : 0u), q1 = l0 == 1 ? v0 : (together && l1 == 1 ? v1 : 0u);
+				const uint32_t q2 = l0 == 2 ? v0 : (together && l1 == 2 ? v1 : 0u), q3 = l0 == 3 ? v0 : (together && l1 == 3 ? v1 : 0u);
+				red_add_h2x4(gtable + (size_t)(idx[c] & ~3u) * 2, q0, q1, q2, q3);
+				if (!together) red_add_h2(gtable + (size_t)idx[c + 1] * 2, *reinterpret_cast<const __half2*>(&v1));
+#else
 				const bool paired = ((idx[c] ^ idx[c + 1]) == 1u), odd = (idx[c] & 1u) != 0;
 				const uint32_t nb = paired ? v1 : 0u;
 				red_add_h2x2(gtable + (size_t)(idx[c] & ~1u) * 2, odd ? nb : v0, odd ? v0 : nb);
 				if (!paired) red_add_h2(gtable + (size_t)idx[c + 1] * 2, *reinterpret_cast<const __half2*>(&v1));
+#endif
 			}
 		} else if constexpr (F == 4) {
 #pragma unroll

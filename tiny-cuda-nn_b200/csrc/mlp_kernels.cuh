@@ -74,16 +74,33 @@ __host__ __device__ constexpr uint32_t mlp_smem_bytes(int n_hidden, int in_width
 	return 1024u /*align slack*/ + (uint32_t)(n_hidden + 1 + (train ? 2 : 0)) * TILE_BYTES + 8192u + (uint32_t)in_width * 128u
 		+ (uint32_t)(n_hidden - 1) * 8192u + 2048u + 256u + (n_hidden == 1 && in_width < 48 ? 4096u : 0u);
 }
+// extra shared memory of the warp-specialised fused kernel: the dL/d(encoded) hand-over slot
+__host__ __device__ constexpr uint32_t mlp_ws_slot_bytes(int in_width) { return 128u * (uint32_t)in_width * 2u; }
 __host__ __device__ constexpr uint32_t mlp_tmem_cols(int n_hidden, bool train) {
 	const uint32_t need = train ? 64u * (uint32_t)(n_hidden + 2) : 64u; // chain + dW_in + (H-1) dW_hid + dW_out
 	return need <= 64 ? 64 : need <= 128 ? 128 : need <= 256 ? 256 : 512;
 }
 
-template <int MODE, int H_, int FD = 0, int FF = 2>
-__global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArgs a, const __grid_constant__ GridParams gp) {
+// WS (warp-specialised scatter, fused kernels only): the CTA has a second warpgroup (threads 128..255) that does nothing
+// but the hash-table scatter.  The compute warpgroup hands each tile's dL/d(encoded) over through one shared-memory slot
+// (named barriers 2 = "slot full", 3 = "slot empty"), so the reductions of tile k run under the whole MMA chain of tile k+1
+// instead of after it; the compute warpgroup only waits if the scatter of tile k is still running when dX of tile k+1 is ready.
+#ifndef SCATTER_CHUNK_UNROLL
+#define SCATTER_CHUNK_UNROLL 1
+#endif
+#define CTA_SYNC() do { if constexpr (NSG > 0) named_bar_sync(1, 128); else __syncthreads(); } while (0)
+template <int MODE, int H_, int FD = 0, int FF = 2, int NSG = 0>
+__global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const __grid_constant__ MlpArgs a, const __grid_constant__ GridParams gp) {
 	constexpr bool TRAIN = MODE != MODE_INFER;
 	constexpr bool FUSE_SCATTER = FD > 0;
+	constexpr bool WS = NSG > 0;           // NSG scatter warpgroups behind the compute warpgroup
+	constexpr uint32_t NT = 128 + 128 * NSG;
+	// registers per thread: the launch gives 65536 / (2 CTAs x NT) to everybody; the scatter warpgroups hand back what
+	// they do not need and the compute warpgroup (128 registers of accumulator rows) takes it
+	constexpr uint32_t REG_LAUNCH = NSG == 0 ? 255 : (65536 / (2 * NT)) / 8 * 8, REG_COMPUTE = 128;
+	constexpr uint32_t REG_SCATTER = NSG == 0 ? 0 : ((NT * REG_LAUNCH - 128 * REG_COMPUTE) / (128 * NSG)) / 8 * 8;
 	static_assert(!FUSE_SCATTER || TRAIN, "the fused scatter belongs to the backward pass");
+	static_assert(!WS || FUSE_SCATTER, "warp specialisation is for the fused scatter");
 	extern __shared__ uint8_t smem_raw[];
 	uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
 	const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -102,6 +119,7 @@ __global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArg
 	uint64_t* bar2 = reinterpret_cast<uint64_t*>(tail + 8); // completion of the weight-gradient MMAs of a tile's last stage
 	uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tail + 16);
 	float* red_buf = reinterpret_cast<float*>(tail + 32);       // 4 floats
+	uint8_t* dx_slot = tail + 256 + ((H == 1 && E < 48) ? 4096 : 0); // WS: [128 rows][E halves], 16-byte chunks swizzled
 
 	// ---- one-time setup ---------------------------------------------------------------------------
 	constexpr uint32_t tmem_cols = mlp_tmem_cols((int)H, TRAIN);
@@ -112,23 +130,23 @@ __global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArg
 	{
 		const __half* p = a.params;
 		const uint32_t cpr_in = E / 8; // chunks per row of W_in
-		for (uint32_t q = tid; q < 64 * cpr_in; q += 128) {
+		for (uint32_t q = tid; q < 64 * cpr_in; q += NT) {
 			const uint32_t r = q / cpr_in, c = q % cpr_in;
 			*reinterpret_cast<uint4*>(w_in + sw128(r, c)) = __ldg(reinterpret_cast<const uint4*>(p + r * E) + c);
 		}
-		for (uint32_t q = tid; q < 64 * E; q += 128) { // transposed copy, element-wise (once per CTA)
+		for (uint32_t q = tid; q < 64 * E; q += NT) { // transposed copy, element-wise (once per CTA)
 			const uint32_t o = q / E, i = q % E;
 			*reinterpret_cast<__half*>(w_inT + sw128(i, o >> 3) + (o & 7) * 2) = p[o * E + i];
 		}
 		p += 64 * E;
 		for (uint32_t l = 0; l + 1 < H; ++l) {
-			for (uint32_t q = tid; q < 64 * 8; q += 128) {
+			for (uint32_t q = tid; q < 64 * 8; q += NT) {
 				const uint32_t r = q >> 3, c = q & 7;
 				*reinterpret_cast<uint4*>(w_hid + l * 8192 + sw128(r, c)) = __ldg(reinterpret_cast<const uint4*>(p + r * 64) + c);
 			}
 			p += 64 * 64;
 		}
-		for (uint32_t q = tid; q < 16 * 8; q += 128) {
+		for (uint32_t q = tid; q < 16 * 8; q += NT) {
 			const uint32_t r = q >> 3, c = q & 7;
 			*reinterpret_cast<uint4*>(w_out + sw128(r, c)) = __ldg(reinterpret_cast<const uint4*>(p + r * 64) + c);
 		}
@@ -153,6 +171,36 @@ __global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArg
 	const uint32_t idesc_dx = make_idesc_f16(128, E, 0, 0);       // B = W_inT K-major
 	const uint32_t idesc_dw = make_idesc_f16(128, 64, 1, 1);      // both operands MN-major, K = 128 samples
 
+	// ---- scatter warpgroups (WS) ---------------------------------------------------------------------
+	if constexpr (WS) {
+		if (tid >= 128) {
+			if constexpr (REG_SCATTER < REG_LAUNCH) setmaxnreg_dec<REG_SCATTER>();
+			const uint32_t srow = tid & 127, sgroup = (tid >> 7) - 1; // row of the tile, and which chunks of the row: j = sgroup (mod NSG)
+			const uint32_t cpr_s = E / 8, swz = (srow * cpr_s / 8) & (cpr_s - 1);
+			const uint32_t slot_row = smem_u32(dx_slot) + srow * E * 2;
+			const uint32_t rep = blockIdx.x & (gp.n_replicas - 1);
+			float nxt[FD];
+#pragma unroll
+			for (int d = 0; d < FD; ++d) nxt[d] = ldg_f32_here(a.positions + ((size_t)blockIdx.x * MLP_TILE + srow) * FD + d);
+			named_bar_arrive(3, NT); // the slot starts empty
+			for (uint32_t tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+				float pos[FD];
+#pragma unroll
+				for (int d = 0; d < FD; ++d) pos[d] = nxt[d];
+				if (tile + gridDim.x < a.n_tiles) {
+#pragma unroll
+					for (int d = 0; d < FD; ++d) nxt[d] = ldg_f32_here(a.positions + ((size_t)(tile + gridDim.x) * MLP_TILE + srow) * FD + d);
+				}
+				named_bar_sync(2, NT); // slot full: this tile's dL/d(encoded)
+#pragma unroll SCATTER_CHUNK_UNROLL
+				for (uint32_t j = sgroup; j < cpr_s; j += NSG) // (nearly) rolled: the level constants stay in the constant bank
+					scatter_chunk<FD, FF>(gp, pos, lds128(slot_row + ((j ^ swz) * 16)), j, a.grid_grad, a.replicas, rep);
+				named_bar_arrive(3, NT); // slot consumed: the compute warpgroup may refill it
+			}
+			return;
+		}
+		if constexpr (REG_COMPUTE > REG_LAUNCH) setmaxnreg_inc<REG_COMPUTE>();
+	}
 	uint32_t phase = 0, phase2 = 0;
 	bool pending2 = false; // a commit on bar2 has not been waited for yet
 	uint32_t first_tile = 1;
@@ -185,14 +233,14 @@ __global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArg
 		STAGE_CLOCK(a); // E: epilogue math + sts issued
 		fence_proxy_async_smem();
 		tc_fence_before();
-		__syncthreads();
+		CTA_SYNC();
 		STAGE_CLOCK(a); // S: fenced + synced
 		if (tile + gridDim.x < a.n_tiles) load_x(tile + gridDim.x); // in flight during the whole chain of this tile
 		// per-row side inputs, requested now and consumed after the forward chain
 		float tgt[4] = {0.f, 0.f, 0.f, 0.f};
 		uint4 dy_in[2];
-		float pos[FUSE_SCATTER ? FD : 1];
-		if constexpr (FUSE_SCATTER) {
+		[[maybe_unused]] float pos[FUSE_SCATTER ? FD : 1];
+		if constexpr (FUSE_SCATTER && !WS) {
 #pragma unroll
 			for (int d = 0; d < FD; ++d) pos[d] = ldg_f32_here(a.positions + (sample0 + row) * FD + d);
 		}
@@ -242,7 +290,7 @@ __global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArg
 			STAGE_CLOCK(a); // E: epilogue math + sts issued
 			fence_proxy_async_smem();
 			tc_fence_before();
-			__syncthreads();
+			CTA_SYNC();
 			STAGE_CLOCK(a); // S: fenced + synced
 		}
 		// ---- output layer --------------------------------------------------------------------------
@@ -309,7 +357,7 @@ __global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArg
 			STAGE_CLOCK(a); // E: epilogue math + sts issued
 			fence_proxy_async_smem();
 			tc_fence_before();
-			__syncthreads();
+			CTA_SYNC();
 			STAGE_CLOCK(a); // S: fenced + synced
 			const bool want_dw = a.dW_partials != nullptr;
 			uint32_t gcur = 0; // G[gcur] holds the gradient w.r.t. the pre-activation feeding weight matrix `k+1`
@@ -364,7 +412,7 @@ __global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArg
 				STAGE_CLOCK(a); // E: epilogue math + sts issued
 				fence_proxy_async_smem();
 				tc_fence_before();
-				__syncthreads();
+				CTA_SYNC();
 				STAGE_CLOCK(a); // S: fenced + synced
 			}
 			// ---- input matmul: dW_in (transposed accumulator) and dL/d(input) ---------------------------
@@ -399,7 +447,13 @@ __global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArg
 							reinterpret_cast<uint4*>(dst + c0)[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
 							reinterpret_cast<uint4*>(dst + c0)[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
 						}
-						if constexpr (FUSE_SCATTER) {
+						if constexpr (WS) {
+							// hand the row to the scatter warpgroup through the shared-memory slot
+							const uint32_t cpr_s = E / 8, swz = (row * cpr_s / 8) & (cpr_s - 1), slot_row = smem_u32(dx_slot) + row * E * 2;
+							if (c0 == 0) named_bar_sync(3, NT); // slot empty: the scatter warpgroup is done with the previous tile
+							sts128(slot_row + (((c0 / 8) ^ swz) * 16), make_uint4(pk[0], pk[1], pk[2], pk[3]));
+							sts128(slot_row + (((c0 / 8 + 1) ^ swz) * 16), make_uint4(pk[4], pk[5], pk[6], pk[7]));
+						} else if constexpr (FUSE_SCATTER) {
 							// this row's dL/d(encoded) goes straight into the hash-table gradient: fire-and-forget reductions that
 							// overlap the weight-gradient MMA still running and the other CTA's MMA chain
 							const uint32_t rep = blockIdx.x & (gp.n_replicas - 1);
@@ -407,14 +461,15 @@ __global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArg
 							scatter_chunk<FD, FF>(gp, pos, make_uint4(pk[4], pk[5], pk[6], pk[7]), c0 / 8 + 1, a.grid_grad, a.replicas, rep);
 						}
 					}
+					if constexpr (WS) named_bar_arrive(2, NT); // slot full
 				}
 				tc_fence_before();
-				__syncthreads();
+				CTA_SYNC();
 			}
 			first_tile = 0;
 		} else {
 			tc_fence_before();
-			__syncthreads();
+			CTA_SYNC();
 		}
 	}
 
@@ -470,12 +525,12 @@ __global__ void __launch_bounds__(128) mlp_kernel(const __grid_constant__ MlpArg
 #pragma unroll
 			for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xFFFFFFFFu, s, o);
 			if (lane == 0) red_buf[warp] = s;
-			__syncthreads();
+			CTA_SYNC();
 			if (tid == 0) a.loss_partials[blockIdx.x] = red_buf[0] + red_buf[1] + red_buf[2] + red_buf[3];
 		}
 	}
 	tc_fence_before();
-	__syncthreads();
+	CTA_SYNC();
 	if (warp == 0) tmem_dealloc(tmem, tmem_cols);
 }
 

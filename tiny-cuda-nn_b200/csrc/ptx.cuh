@@ -162,6 +162,14 @@ __device__ __forceinline__ uint32_t pack_h2(float a, float b) {
 	return *reinterpret_cast<uint32_t*>(&h);
 }
 
+// named barriers (producer/consumer hand-off between warpgroups of one CTA; id 0 is __syncthreads)
+__device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t n_threads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n_threads) : "memory"); }
+__device__ __forceinline__ void named_bar_arrive(uint32_t id, uint32_t n_threads) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n_threads) : "memory"); }
+
+// register re-balancing between warpgroups (all warps of the warpgroup execute it together)
+template <uint32_t N> __device__ __forceinline__ void setmaxnreg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
+template <uint32_t N> __device__ __forceinline__ void setmaxnreg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
+
 // ---- peer memory over NVLink / NVSwitch ---------------------------------------------------------------
 // System-scope accesses for buffers that other GPUs read and write (symmetric allocations mapped into every rank).
 __device__ __forceinline__ uint4 ld_sys_v4(const void* addr) {

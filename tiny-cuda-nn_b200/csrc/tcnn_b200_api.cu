@@ -43,6 +43,7 @@ struct tcnn_b200_plan {
 	// Adam extras
 	float non_matrix_lr_factor = 1.f, weight_clip = 0.f;
 	bool adabound = false;
+	bool no_warp_specialization = getenv("TCNN_B200_NO_WS") != nullptr; // development switch: fused kernel without the scatter warpgroup
 	// optional per-kernel timing (tcnn_b200_profile_*): CUDA events recorded around every launch on the launch stream
 	// fork/join for the fused training step: Adam on finished level groups overlaps the scatter of the next group
 	cudaStream_t aux = nullptr;
@@ -475,18 +476,33 @@ extern "C" int tcnn_b200_grid_indices(const tcnn_b200_plan* plan, void* stream, 
 }
 
 // ---- MLP ----------------------------------------------------------------------------------------------
+#ifndef TCNN_B200_SCATTER_WARPGROUPS
+#define TCNN_B200_SCATTER_WARPGROUPS 2
+#endif
+template <int MODE, int H, int FD = 0, int FF = 2, int NSG = 0>
+static void launch_mlp_k(const tcnn_b200_plan* plan, cudaStream_t stream, const MlpArgs& a, uint32_t grid, const GridParams& gp, uint32_t smem) {
+	static thread_local uint32_t configured = 0;
+	if (configured < smem) {
+		CUDA_OK(cudaFuncSetAttribute(mlp_kernel<MODE, H, FD, FF, NSG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		configured = smem;
+	}
+	ProfileScope prof(plan, stream, PK_MLP);
+	mlp_kernel<MODE, H, FD, FF, NSG><<<grid, 128 + 128 * NSG, smem, stream>>>(a, gp);
+	launch_check("mlp_kernel");
+}
 template <int MODE, int H, int FD = 0, int FF = 2>
 static void launch_mlp_h(const tcnn_b200_plan* plan, cudaStream_t stream, const MlpArgs& a, uint32_t grid, const GridParams& gp) {
 	constexpr bool train = MODE != MODE_INFER;
 	const uint32_t smem = mlp_smem_bytes(H, (int)a.in_width, train);
-	static thread_local uint32_t configured = 0;
-	if (configured < smem) {
-		CUDA_OK(cudaFuncSetAttribute(mlp_kernel<MODE, H, FD, FF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-		configured = smem;
+	if constexpr (FD > 0) {
+		// warp-specialised scatter (second warpgroup + hand-over slot) unless the slot would cost a resident CTA per SM
+		const uint32_t per_sm = 233472u, smem_ws = smem + mlp_ws_slot_bytes((int)a.in_width);
+		if (per_sm / (smem_ws + 1024u) >= std::min(2u, per_sm / (smem + 1024u)) && per_sm / (smem_ws + 1024u) >= 1u && !plan->no_warp_specialization) {
+			launch_mlp_k<MODE, H, FD, FF, TCNN_B200_SCATTER_WARPGROUPS>(plan, stream, a, grid, gp, smem_ws);
+			return;
+		}
 	}
-	ProfileScope prof(plan, stream, PK_MLP);
-	mlp_kernel<MODE, H, FD, FF><<<grid, 128, smem, stream>>>(a, gp);
-	launch_check("mlp_kernel");
+	launch_mlp_k<MODE, H, FD, FF, 0>(plan, stream, a, grid, gp, smem);
 }
 template <int MODE>
 static void launch_mlp(const tcnn_b200_plan* plan, cudaStream_t stream, const MlpArgs& a, uint32_t grid) {
