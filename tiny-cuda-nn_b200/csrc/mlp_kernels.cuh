@@ -88,6 +88,7 @@ __host__ __device__ constexpr uint32_t mlp_tmem_cols(int n_hidden, bool train) {
 #ifndef SCATTER_CHUNK_UNROLL
 #define SCATTER_CHUNK_UNROLL 1
 #endif
+constexpr int kScatterChunkUnroll = SCATTER_CHUNK_UNROLL;
 #define CTA_SYNC() do { if constexpr (NSG > 0) named_bar_sync(1, 128); else __syncthreads(); } while (0)
 template <int MODE, int H_, int FD = 0, int FF = 2, int NSG = 0>
 __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const __grid_constant__ MlpArgs a, const __grid_constant__ GridParams gp) {
@@ -192,7 +193,7 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 					for (int d = 0; d < FD; ++d) nxt[d] = ldg_f32_here(a.positions + ((size_t)(tile + gridDim.x) * MLP_TILE + srow) * FD + d);
 				}
 				named_bar_sync(2, NT); // slot full: this tile's dL/d(encoded)
-#pragma unroll SCATTER_CHUNK_UNROLL
+#pragma unroll kScatterChunkUnroll
 				for (uint32_t j = sgroup; j < cpr_s; j += NSG) // (nearly) rolled: the level constants stay in the constant bank
 					scatter_chunk<FD, FF>(gp, pos, lds128(slot_row + ((j ^ swz) * 16)), j, a.grid_grad, a.replicas, rep);
 				named_bar_arrive(3, NT); // slot consumed: the compute warpgroup may refill it
