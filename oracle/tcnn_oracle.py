@@ -287,7 +287,7 @@ def grid_forward(cfg: GridConfig, x: np.ndarray, table: np.ndarray) -> np.ndarra
     return out
 
 
-def grid_backward(cfg: GridConfig, x: np.ndarray, dy: np.ndarray) -> np.ndarray:
+def grid_backward(cfg: GridConfig, x: np.ndarray, dy: np.ndarray, sequential_fp16: bool = False) -> np.ndarray:
     """kernel_grid_backward, grid.h:214-320.  dy: fp16 [B, L*F] -> float64 [n_params] (exact sum of the fp16
     products (half)weight * grad; the reference accumulates them with fp16 red atomics in arbitrary order, so
     comparisons are tolerance-based)."""
@@ -297,10 +297,25 @@ def grid_backward(cfg: GridConfig, x: np.ndarray, dy: np.ndarray) -> np.ndarray:
         idx, w = grid_corners(cfg, x, l)
         base = int(cfg.offsets[l])
         gl = dy[:, l * F:(l + 1) * F].astype(np.float16)
+        contrib = []
         for c in range(idx.shape[1]):
             wh = w[:, c].astype(np.float16)
             prod = (wh.astype(np.float32)[:, None] * gl.astype(np.float32)).astype(np.float16)  # __hmul2, one rounding
-            np.add.at(g, base + idx[:, c].astype(np.int64), prod.astype(np.float64))
+            if not sequential_fp16:
+                np.add.at(g, base + idx[:, c].astype(np.int64), prod.astype(np.float64))
+            else:
+                contrib.append((idx[:, c].astype(np.int64), prod))
+        if sequential_fp16:
+            # what red.add.noftz.f16x2 does: the running sum is rounded to fp16 after EVERY addition (order: sample, corner)
+            rows = np.concatenate([cc[0] for cc in contrib]); vals = np.concatenate([cc[1] for cc in contrib])
+            order = np.argsort(rows, kind="stable"); rows, vals = rows[order], vals[order]
+            first = np.r_[True, rows[1:] != rows[:-1]]
+            start = np.flatnonzero(first); rank = np.arange(len(rows)) - np.repeat(start, np.diff(np.r_[start, len(rows)]))
+            acc = np.zeros((cfg.level_size(l), F), np.float16)
+            for r in range(int(rank.max()) + 1):
+                sel = rank == r
+                acc[rows[sel]] = (acc[rows[sel]].astype(np.float32) + vals[sel].astype(np.float32)).astype(np.float16)
+            g[base:base + cfg.level_size(l)] = acc.astype(np.float64)
     return g.reshape(-1)
 
 

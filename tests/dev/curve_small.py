@@ -41,7 +41,7 @@ else:
         y, hidden = O.mlp_forward(m, p16[:m.n_params], enc, acc)
         lv, dy = O.loss_l2(y, t, n_out)
         dW, dx = O.mlp_backward(m, p16[:m.n_params], enc, hidden, dy, acc, "hmma16" if "dw16" in mode else np.float64)
-        gg = O.grid_backward(g, x, dx)
+        gg = O.grid_backward(g, x, dx, sequential_fp16="seq16" in mode)
         grads = np.concatenate([dW, gg]).astype(np.float16)
         O.adam_step(ad, m.n_params, p32, grads, mm, vv, st)
         losses.append(lv)

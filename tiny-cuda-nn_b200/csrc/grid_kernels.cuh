@@ -91,6 +91,9 @@ __device__ __forceinline__ void load_position(const float* __restrict__ x, size_
 	}
 }
 
+#ifndef TCNN_B200_GATHER_QUAD
+#define TCNN_B200_GATHER_QUAD 1
+#endif
 // Encode the levels of one 16-byte chunk for one sample.  Returns 8 halfs packed in a uint4.
 template <int D, int F>
 __device__ __forceinline__ uint4 encode_chunk(const GridParams& gp, const __half* __restrict__ grid, const float (&x)[D], uint32_t chunk) {
@@ -127,12 +130,23 @@ __device__ __forceinline__ uint4 encode_chunk(const GridParams& gp, const __half
 			__half2 val[NC];
 #pragma unroll
 			for (int c = 0; c < NC; c += 2) {
+#if TCNN_B200_GATHER_QUAD
+				// the gather is bound by L1 tag lookups (one per lane and load): a 16-byte load of the aligned slot
+				// {idx & ~3 .. idx | 3} also brings the dim-0 neighbour unless idx % 4 == 3 -> 1.25 lookups per corner pair
+				const uint32_t l0 = idx[c] & 3u, l1 = idx[c + 1] & 3u;
+				const bool together = ((idx[c] ^ idx[c + 1]) & ~3u) == 0u;
+				const uint4 a = __ldg(reinterpret_cast<const uint4*>(table) + (idx[c] >> 2));
+				const uint32_t own = l0 == 0 ? a.x : l0 == 1 ? a.y : l0 == 2 ? a.z : a.w;
+				uint32_t other = l1 == 0 ? a.x : l1 == 1 ? a.y : l1 == 2 ? a.z : a.w;
+				if (!together) other = __ldg(reinterpret_cast<const uint32_t*>(table) + idx[c + 1]);
+#else
 				const bool paired = ((idx[c] ^ idx[c + 1]) == 1u);
 				const uint2 a = __ldg(reinterpret_cast<const uint2*>(table) + (idx[c] >> 1));
 				uint32_t own = (idx[c] & 1u) ? a.y : a.x, other = (idx[c] & 1u) ? a.x : a.y;
 				if (!paired) other = __ldg(reinterpret_cast<const uint32_t*>(table) + idx[c + 1]);
-				val[c] = *reinterpret_cast<__half2*>(&own);
-				val[c + 1] = *reinterpret_cast<__half2*>(&other);
+#endif
+				val[c] = *reinterpret_cast<const __half2*>(&own);
+				val[c + 1] = *reinterpret_cast<const __half2*>(&other);
 			}
 			__half2 r = __floats2half2_rn(0.f, 0.f);
 #pragma unroll

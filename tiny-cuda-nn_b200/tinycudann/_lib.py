@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libtcnn_b200.so")
+LIB_PATH = os.environ.get("TCNN_B200_LIB") or os.path.join(os.path.dirname(_HERE), "lib", "libtcnn_b200.so")  # env: A/B builds
 
 
 class Info(C.Structure):
