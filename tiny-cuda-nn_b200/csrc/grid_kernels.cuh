@@ -197,10 +197,16 @@ __device__ __forceinline__ uint4 encode_chunk(const GridParams& gp, const __half
 }
 
 // grid = {ceil(B/256), E_pad/8}; chunk-major block order keeps one group of levels hot in L2 at a time.
+// zero16 / n_zero16 (optional): 16-byte words this launch clears on the side (the gradient replicas of the coarse levels
+// for the backward pass that follows; saves a memset launch per training step).
 template <int D, int F>
 __global__ void __launch_bounds__(256) grid_forward_kernel(const __grid_constant__ GridParams gp, uint32_t B,
-	const float* __restrict__ x, const __half* __restrict__ grid, __half* __restrict__ encoded) {
+	const float* __restrict__ x, const __half* __restrict__ grid, __half* __restrict__ encoded, uint4* __restrict__ zero16, uint32_t n_zero16) {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (zero16 != nullptr) {
+		const uint32_t n_threads = gridDim.x * gridDim.y * blockDim.x;
+		for (uint32_t k = blockIdx.y * gridDim.x * blockDim.x + i; k < n_zero16; k += n_threads) zero16[k] = make_uint4(0, 0, 0, 0);
+	}
 	if (i >= B) return;
 	const uint32_t chunk = blockIdx.y;
 	float p[D];

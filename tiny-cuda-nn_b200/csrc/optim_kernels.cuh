@@ -94,6 +94,45 @@ __global__ void __launch_bounds__(256) adam_kernel(const __grid_constant__ AdamA
 	}
 }
 
+// Reduction of the per-CTA weight-gradient partials of the MLP kernel (see mlp_finalize_kernel) with the Adam update of the
+// MLP weights applied in the same pass: on one GPU the 7 K weights need no separate optimizer launch on the critical path.
+// The gradient is rounded to fp16 first (it is also stored), so the update equals adam_kernel on the stored gradient.
+__global__ void __launch_bounds__(256) mlp_finalize_adam_kernel(uint32_t n_params, uint32_t n_parts, const float* __restrict__ partials,
+	const float* __restrict__ loss_partials, float* __restrict__ loss_out, const __grid_constant__ AdamArgs a) {
+	__shared__ float sh[8][33];
+	const uint32_t px = threadIdx.x & 31, sl = threadIdx.x >> 5;
+	const uint32_t i = blockIdx.x * 32 + px;
+	float s = 0.f;
+	if (i < n_params) for (uint32_t p = sl; p < n_parts; p += 8) s += partials[(size_t)p * n_params + i];
+	sh[sl][px] = s;
+	__syncthreads();
+	if (sl == 0 && i < n_params) {
+		float t = 0.f;
+#pragma unroll
+		for (int k = 0; k < 8; ++k) t += sh[k][px];
+		const __half gh = __float2half(t);
+		a.grads[i] = gh;
+		float w = a.master[i], m = a.m[i], v = a.v[i];
+		uint32_t st = a.steps[i];
+		adam_one(a, i, __half2float(gh), w, m, v, st); // i < n_matrix: never skipped
+		a.master[i] = w; a.m[i] = m; a.v[i] = v; a.steps[i] = st; a.params[i] = __float2half(w);
+	}
+	if (blockIdx.x == 0 && loss_partials && loss_out) {
+		__syncthreads();
+		float l = 0.f;
+		for (uint32_t p = threadIdx.x; p < n_parts; p += blockDim.x) l += loss_partials[p];
+#pragma unroll
+		for (int o = 16; o > 0; o >>= 1) l += __shfl_xor_sync(0xFFFFFFFFu, l, o);
+		if ((threadIdx.x & 31) == 0) sh[0][threadIdx.x >> 5] = l;
+		__syncthreads();
+		if (threadIdx.x == 0) {
+			float t = 0.f;
+			for (int k = 0; k < 8; ++k) t += sh[0][k];
+			*loss_out = t;
+		}
+	}
+}
+
 // ---- data-parallel optimizer step over NVLink peer memory -----------------------------------------------
 // One kernel = reduce-scatter of the fp16 gradients + Adam on this rank's shard of the parameters + all-gather of the
 // updated fp16 parameters, with both inter-GPU barriers inside.  Gradient and fp16 parameter buffers are symmetric

@@ -400,13 +400,17 @@ extern "C" int tcnn_b200_cast_params(void* stream_, uint64_t n, const float* par
 		else FAIL("unsupported (n_input_dims, n_features_per_level)");                                            \
 	} while (0)
 
-static void encode_forward(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t B, const float* x, const __half* grid, __half* encoded) {
+static void encode_forward(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t B, const float* x, const __half* grid, __half* encoded,
+	void* zero_on_the_side = nullptr, size_t zero_bytes = 0) {
 	ProfileScope prof(plan, stream, PK_GRID_FWD);
 	const dim3 g((B + 255) / 256, plan->info.encoded_width / 8, 1);
-	GRID_DISPATCH(grid_forward_kernel, plan, g, stream, plan->grid, B, x, grid, encoded);
+	uint4* z16 = zero_bytes ? (uint4*)zero_on_the_side : nullptr;
+	const uint32_t nz16 = (uint32_t)(zero_bytes / 16);
+	GRID_DISPATCH(grid_forward_kernel, plan, g, stream, plan->grid, B, x, grid, encoded, z16, nz16);
 	launch_check("grid_forward_kernel");
 }
 // backward in three pieces so that several batch chunks can scatter concurrently between one prepare and one finish
+static size_t replica_bytes_of(const tcnn_b200_plan* plan, const GridParams& gp) { return (size_t)gp.rep_entries * plan->info.n_features_per_level * 2 * gp.n_replicas; }
 static void backward_prepare(const tcnn_b200_plan* plan, cudaStream_t stream, const GridParams& gp, __half* grid_grads, int zero_first, __half* replicas) {
 	ProfileScope prof(plan, stream, PK_GRID_BWD);
 	if (zero_first) CUDA_OK(cudaMemsetAsync(grid_grads, 0, plan->info.n_params_grid * 2, stream));
@@ -763,23 +767,29 @@ extern "C" int tcnn_b200_training_step(const tcnn_b200_plan* plan, void* stream_
 	a.dW_partials = w.dw_partials; a.loss_partials = w.loss_partials; a.loss_scale = loss_scale;
 	const uint32_t mlp_grid = mlp_grid_size(plan, B / MLP_TILE, true);
 
-	backward_prepare(plan, main, gp, gg, /*zero_first=*/0, w.replicas);
-	encode_forward(plan, main, B, x, p + in.n_params_mlp, w.encoded);
 	if (fused_scatter_available(plan)) {
-		// gather -> [MLP forward, loss, backward, weight gradients, hash-table scatter] -> Adam.  The small dW reduction runs on
-		// the second stream under the Adam pass over the grid tables; the MLP weights are updated after the join.
+		// gather (+ clears the gradient replicas) -> [MLP forward, loss, backward, weight gradients, hash-table scatter] ->
+		// replica reduction + Adam over the grid tables || on the second stream: weight-gradient reduction + Adam of the MLP weights
+		encode_forward(plan, main, B, x, p + in.n_params_mlp, w.encoded, w.replicas, replica_bytes_of(plan, gp));
 		a.dL_dinput = nullptr; a.positions = x; a.grid_grad = gg; a.replicas = w.replicas;
 		launch_mlp_train_fused(plan, main, a, mlp_grid, gp);
 		CUDA_OK(cudaEventRecord(ev[0], main));
 		CUDA_OK(cudaStreamWaitEvent(aux, ev[0], 0));
-		mlp_finalize(plan, aux, mlp_grid, w, g, loss_out, loss_out != nullptr);
+		{
+			ProfileScope prof(plan, aux, PK_FINALIZE);
+			const AdamArgs am = adam_args(plan, loss_scale, adam_step_count, ab, 1, 0u, (uint32_t)in.n_params_mlp);
+			mlp_finalize_adam_kernel<<<((uint32_t)in.n_params_mlp + 31) / 32, 256, 0, aux>>>((uint32_t)in.n_params_mlp, mlp_grid, w.dw_partials,
+				loss_out ? w.loss_partials : nullptr, loss_out, am);
+			launch_check("mlp_finalize_adam_kernel");
+		}
 		CUDA_OK(cudaEventRecord(ev[1], aux));
 		backward_finish(plan, main, gp, gg, w.replicas);
 		adam_launch(plan, main, loss_scale, adam_step_count, ab, 1, (uint32_t)in.n_params_mlp, (uint32_t)in.n_params);
 		CUDA_OK(cudaStreamWaitEvent(main, ev[1], 0)); // join
-		adam_launch(plan, main, loss_scale, adam_step_count, ab, 1, 0u, (uint32_t)in.n_params_mlp);
 		return 0;
 	}
+	backward_prepare(plan, main, gp, gg, /*zero_first=*/0, w.replicas);
+	encode_forward(plan, main, B, x, p + in.n_params_mlp, w.encoded);
 	launch_mlp<MODE_TRAIN>(plan, main, a, mlp_grid);
 	CUDA_OK(cudaEventRecord(ev[0], main));
 	CUDA_OK(cudaStreamWaitEvent(aux, ev[0], 0));
@@ -858,8 +868,7 @@ extern "C" int tcnn_b200_training_step_dp(const tcnn_b200_plan* plan, void* stre
 	const uint32_t mlp_grid = mlp_grid_size(plan, B / MLP_TILE, true);
 
 	// local part: identical to the single-GPU step up to the complete local gradient (grid gradients are zero on entry)
-	backward_prepare(plan, main, gp, gg, /*zero_first=*/0, w.replicas);
-	encode_forward(plan, main, B, x, p + in.n_params_mlp, w.encoded);
+	encode_forward(plan, main, B, x, p + in.n_params_mlp, w.encoded, w.replicas, replica_bytes_of(plan, gp)); // also clears the replicas
 	if (fused_scatter_available(plan)) {
 		a.dL_dinput = nullptr; a.positions = x; a.grid_grad = gg; a.replicas = w.replicas;
 		launch_mlp_train_fused(plan, main, a, mlp_grid, gp);
