@@ -57,7 +57,11 @@ const char* tcnn_b200_arch(void);
 uint32_t tcnn_b200_batch_size_granularity(void);
 
 /* create_from_config / create_network_with_input_encoding (config.h:53-63, src/cpp_api.cu:147-149).
- * json_utf8 = {"encoding": {...}, "network": {...}, "loss": {...}?, "optimizer": {...}?}. */
+ * json_utf8 = {"encoding": {...}, "network": {...}, "loss": {...}?, "optimizer": {...}?}.
+ * With "network" alone the plan is create_network (Identity encoding + network, src/cpp_api.cu:151-153); with "encoding"
+ * alone it is create_encoding (src/cpp_api.cu:156-165): inference/forward then write the encoded batch, fp16
+ * [B][next multiple of 8 of n_levels * n_features_per_level], and backward takes dL/d(encoded) of that shape.  The training
+ * entry points need both objects. */
 int tcnn_b200_plan_create(const char* json_utf8, uint32_t n_input_dims, uint32_t n_output_dims, tcnn_b200_plan** plan);
 void tcnn_b200_plan_destroy(tcnn_b200_plan* plan);
 int tcnn_b200_plan_info(const tcnn_b200_plan* plan, tcnn_b200_info* info);
@@ -100,7 +104,8 @@ int tcnn_b200_inference(const tcnn_b200_plan* plan, void* stream, uint32_t batch
  * (the encoded batch), which therefore plays the role of the reference's Context. */
 int tcnn_b200_forward(const tcnn_b200_plan* plan, void* stream, uint32_t batch_size, const float* x, const void* params_fp16, void* output_fp16, void* workspace);
 /* cpp::Module::backward (src/cpp_api.cu:96-109), GradientMode::Overwrite.  dL_dparams fp16 [n_params] may be NULL.
- * dL_dinput (fp32 [B][D]) is not implemented in this round: passing non-NULL is an error. */
+ * dL_dinput (fp32 [B][D]) is implemented for network-only plans (identity_backward, encodings/identity.h:68-83); through a
+ * grid encoding (kernel_grid_backward_input) it is not implemented in this round: passing non-NULL is then an error. */
 int tcnn_b200_backward(const tcnn_b200_plan* plan, void* stream, uint32_t batch_size, const float* x, const void* params_fp16,
                        const void* dL_doutput_fp16, void* dL_dparams_fp16, float* dL_dinput, void* workspace);
 

@@ -17,12 +17,14 @@ class Module {
 public:
 	Module(uint32_t n_input_dims, uint32_t n_output_dims, const std::string& encoding_json, const std::string& network_json)
 	: m_network("{\"encoding\": " + encoding_json + ", \"network\": " + network_json + "}", n_input_dims, n_output_dims) {}
+	/* one of the two objects alone: {"network": ...} = Identity encoding + network, {"encoding": ...} = grid encoding */
+	Module(uint32_t n_input_dims, uint32_t n_output_dims, const std::string& config_json) : m_network(config_json, n_input_dims, n_output_dims) {}
 
 	void inference(cudaStream_t stream, uint32_t n_elements, const float* input, void* output, void* params) {
 		TCNN_B200_CHECK_THROW(tcnn_b200_inference(m_network.plan(), stream, n_elements, input, params, output, nullptr, m_network.workspace(n_elements)));
 	}
 	Context forward(cudaStream_t stream, uint32_t n_elements, const float* input, void* output, void* params, bool prepare_input_gradients) {
-		if (prepare_input_gradients) throw std::runtime_error("tcnn_b200: dL_dinput of the grid encoding is not implemented yet");
+		if (prepare_input_gradients && m_network.info().n_levels != 0) throw std::runtime_error("tcnn_b200: dL_dinput of the grid encoding is not implemented yet");
 		Context ctx;
 		ctx.saved.resize(tcnn_b200_workspace_bytes(m_network.plan(), n_elements));
 		TCNN_B200_CHECK_THROW(tcnn_b200_forward(m_network.plan(), stream, n_elements, input, params, output, ctx.saved.data()));
@@ -48,6 +50,16 @@ private:
 
 inline Module* create_network_with_input_encoding(uint32_t n_input_dims, uint32_t n_output_dims, const std::string& encoding_json, const std::string& network_json) {
 	return new Module(n_input_dims, n_output_dims, encoding_json, network_json);
+}
+
+/* src/cpp_api.cu:151-153 */
+inline Module* create_network(uint32_t n_input_dims, uint32_t n_output_dims, const std::string& network_json) {
+	return new Module(n_input_dims, n_output_dims, "{\"network\": " + network_json + "}");
+}
+/* src/cpp_api.cu:156-165; fp16 only; n_output_dims() is the row width of the output (next multiple of 8 of L * F) */
+inline Module* create_encoding(uint32_t n_input_dims, const std::string& encoding_json, Precision requested_precision = Precision::Fp16) {
+	if (requested_precision != Precision::Fp16) throw std::runtime_error("tcnn_b200: encodings are implemented for fp16 precision only");
+	return new Module(n_input_dims, 0, "{\"encoding\": " + encoding_json + "}");
 }
 
 }} // namespace tcnn::cpp

@@ -283,6 +283,66 @@ def test_module_surface_forward_backward(dev):
     assert torch.isfinite(net.params.grad).all()
 
 
+def test_network_module_forward_backward_with_input_gradient(dev):
+    """tcnn.Network = Identity encoding (fp32 -> fp16, padded to 16 columns with ones) + FullyFusedMLP; parameters, output,
+    parameter gradients and dL/dinput against the oracle MLP."""
+    import tinycudann as tcnn
+    n_in, n_out, B = 5, 4, 700
+    netcfg = {"otype": "FullyFusedMLP", "activation": "ReLU", "output_activation": "None", "n_neurons": 64, "n_hidden_layers": 3}
+    net = tcnn.Network(n_in, n_out, netcfg, seed=11).to(dev)
+    m = O.MlpConfig(n_input=16, n_output=n_out, n_neurons=64, n_hidden_layers=3)
+    assert net.params.shape[0] == m.n_params
+    assert np.array_equal(net.params.detach().cpu().numpy(), O.init_params(m, None, 11, trainer_seeding=False))
+    rng = np.random.default_rng(3)
+    x_np = rng.standard_normal((B, n_in)).astype(np.float32)
+    t_np = rng.standard_normal((B, n_out)).astype(np.float32)
+    x = torch.from_numpy(x_np).to(dev).requires_grad_(True)
+    y = net(x)
+    assert y.shape == (B, n_out) and y.dtype == torch.half
+    (((y.float() - torch.from_numpy(t_np).to(dev)) ** 2).sum() / 16).backward()
+    p16 = net.params.detach().cpu().numpy().astype(np.float16)
+    xp = np.ones((768, 16), np.float32); xp[:, :n_in] = 0; xp[:B, :n_in] = x_np
+    yo, hidden = O.mlp_forward(m, p16, xp.astype(np.float16))
+    assert common.rel_l2(y.detach().cpu().numpy(), yo[:B, :n_out]) < 1e-3
+    dy = np.zeros((768, 16), np.float32)
+    dy[:B, :n_out] = 2 * (yo[:B, :n_out].astype(np.float32) - t_np) / 16
+    dW, dx = O.mlp_backward(m, p16, xp.astype(np.float16), hidden, (dy * 128.0).astype(np.float16))
+    assert common.rel_l2(net.params.grad.cpu().numpy(), dW / 128.0) < 5e-3
+    assert x.grad.shape == (B, n_in)
+    assert common.rel_l2(x.grad.cpu().numpy(), dx[:B, :n_in].astype(np.float32) / 128.0) < 5e-3
+
+
+def test_encoding_module_forward_backward(dev):
+    """tcnn.Encoding (HashGrid alone, unpadded n_output_dims = n_levels * n_features_per_level): table init, encoded features
+    (bit-exact) and table gradients against the oracle; dL/dinput is refused loudly."""
+    import tinycudann as tcnn
+    enc_cfg = {"otype": "HashGrid", "n_levels": 5, "n_features_per_level": 2, "log2_hashmap_size": 12, "base_resolution": 4, "per_level_scale": 1.7}
+    enc = tcnn.Encoding(3, enc_cfg, seed=5).to(dev)
+    assert enc.n_output_dims == 10 and enc.dtype == torch.half
+    info = enc.native_tcnn_module.info
+    g = O.GridConfig(3, 5, 2, 12, 4, 1.7, scales=np.array(info.level_scale[:5], dtype=np.float32))
+    assert enc.params.shape[0] == g.n_params
+    with torch.no_grad():
+        enc.params.mul_(3000.0)  # U(-1e-4, 1e-4) tables would make every product subnormal in fp16
+    B = 600
+    rng = np.random.default_rng(8)
+    x_np = rng.random((B, 3), dtype=np.float32)
+    x = torch.from_numpy(x_np).to(dev)
+    y = enc(x)
+    assert y.shape == (B, 10) and y.dtype == torch.half
+    p16 = enc.params.detach().cpu().numpy().astype(np.float16)
+    assert np.array_equal(y.detach().cpu().numpy(), O.grid_forward(g, x_np, p16)[:, :10])
+    w_np = rng.standard_normal((B, 10)).astype(np.float32)
+    (y.float() * torch.from_numpy(w_np).to(dev)).sum().backward()
+    dy = np.zeros((768, 10), np.float32); dy[:B] = w_np
+    xp = np.zeros((768, 3), np.float32); xp[:B] = x_np
+    gg = O.grid_backward(g, xp, (dy * 128.0).astype(np.float16)) / 128.0
+    assert common.rel_l2(enc.params.grad.cpu().numpy(), gg) < 5e-3
+    xr = x.clone().requires_grad_(True)
+    with pytest.raises(RuntimeError, match="not implemented"):
+        enc(xr).float().sum().backward()
+
+
 def test_trainer_converges_and_matches_reference_order_of_magnitude(dev):
     import tinycudann as tcnn
     model = tcnn.create_from_config(2, 3, common.CONFIG_1, seed=1337, device=dev)

@@ -335,6 +335,26 @@ __global__ void grid_replica_reduce_kernel(const __grid_constant__ GridParams gp
 	}
 }
 
+// Identity encoding in front of a stand-alone Network (encodings/identity.h:46-90, src/cpp_api.cu:151-153): fp32 [B][n_in] ->
+// fp16 [B][width], columns >= n_in are ONE (identity.h:63), so that the first layer can learn a bias through them.
+// Thread = sample x 8-column chunk.
+__global__ void __launch_bounds__(256) identity_encode_kernel(uint32_t B, uint32_t n_in, uint32_t width, const float* __restrict__ x, __half* __restrict__ out) {
+	const uint32_t cpr = width / 8, q = blockIdx.x * blockDim.x + threadIdx.x;
+	if (q >= B * cpr) return;
+	const uint32_t i = q / cpr, c0 = (q % cpr) * 8;
+	union { uint4 v; __half h[8]; } o;
+#pragma unroll
+	for (uint32_t k = 0; k < 8; ++k) o.h[k] = __float2half(c0 + k < n_in ? __ldg(x + (size_t)i * n_in + c0 + k) : 1.0f);
+	*reinterpret_cast<uint4*>(out + (size_t)i * width + c0) = o.v;
+}
+// identity_backward (identity.h:68-83): dL/dx = (float) dL/dy for the first n_in columns
+__global__ void __launch_bounds__(256) identity_backward_kernel(uint32_t B, uint32_t n_in, uint32_t width, const __half* __restrict__ dL_dy, float* __restrict__ dL_dx) {
+	const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
+	if (q >= B * n_in) return;
+	const uint32_t i = q / n_in, j = q % n_in;
+	dL_dx[q] = __half2float(dL_dy[(size_t)i * width + j]);
+}
+
 // Parity helper: the per-corner entry indices exactly as the encode/scatter kernels compute them.
 // out[(level * B + i) * 2^D + corner]   (same layout as oracle/ref_driver.cu dump_indices)
 template <int D>

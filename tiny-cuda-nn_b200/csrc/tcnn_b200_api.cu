@@ -43,6 +43,7 @@ struct tcnn_b200_plan {
 	// Adam extras
 	float non_matrix_lr_factor = 1.f, weight_clip = 0.f;
 	bool adabound = false;
+	int kind = 0;                   // PLAN_FULL: encoding + network; PLAN_NETWORK: Identity encoding + network; PLAN_ENCODING: grid encoding alone
 	bool no_warp_specialization = getenv("TCNN_B200_NO_WS") != nullptr; // development switch: fused kernel without the scatter warpgroup
 	// optional per-kernel timing (tcnn_b200_profile_*): CUDA events recorded around every launch on the launch stream
 	// fork/join for the fused training step: Adam on finished level groups overlaps the scatter of the next group
@@ -54,6 +55,7 @@ struct tcnn_b200_plan {
 	std::vector<Span> spans;
 };
 
+enum PlanKind { PLAN_FULL = 0, PLAN_NETWORK = 1, PLAN_ENCODING = 2 };
 enum ProfileKind { PK_GRID_FWD = 0, PK_MLP = 1, PK_FINALIZE = 2, PK_GRID_BWD = 3, PK_ADAM = 4, PK_COUNT = 5 };
 
 struct ProfileScope {
@@ -175,6 +177,13 @@ extern "C" int tcnn_b200_plan_create(const char* json_utf8, uint32_t n_input_dim
 	in.n_input_dims = n_input_dims;
 	in.n_output_dims = n_output_dims;
 
+	// Which reference object the config describes (src/cpp_api.cu:143-165): encoding + network = NetworkWithInputEncoding,
+	// network alone = create_network (Identity encoding in front), encoding alone = create_encoding (no padding to 16).
+	const bool has_encoding = cfg.contains("encoding"), has_network = cfg.contains("network");
+	CHECK(has_encoding || has_network, "config needs an \"encoding\" and/or a \"network\" object");
+	p->kind = has_encoding ? (has_network ? PLAN_FULL : PLAN_ENCODING) : PLAN_NETWORK;
+	uint32_t n_features = 0;
+	if (has_encoding) {
 	// --- encoding: create_grid_encoding (encodings/grid.h:1143-1208) ---
 	const std::string etype = jsonmini::lower(enc.string("otype", "Grid"));
 	CHECK(etype == "hashgrid" || etype == "grid", "encoding otype '" + etype + "' is outside the hot path (HashGrid only; SURVEY.md section 8)");
@@ -185,7 +194,6 @@ extern "C" int tcnn_b200_plan_create(const char* json_utf8, uint32_t n_input_dim
 	in.n_features_per_level = (uint32_t)enc.number("n_features_per_level", 2);
 	CHECK(in.n_features_per_level == 2 || in.n_features_per_level == 4 || in.n_features_per_level == 8,
 		"GridEncoding: n_features_per_level must be 2, 4 or 8 on this path (1 needs the fp32 gradient variant)");
-	uint32_t n_features;
 	if (enc.contains("n_features") || enc.contains("n_grid_features")) {
 		CHECK(!enc.contains("n_levels"), "GridEncoding: may not specify n_features and n_levels simultaneously (one determines the other)");
 		n_features = (uint32_t)enc.number(enc.contains("n_features") ? "n_features" : "n_grid_features", 0);
@@ -200,7 +208,9 @@ extern "C" int tcnn_b200_plan_create(const char* json_utf8, uint32_t n_input_dim
 	in.base_resolution = (uint32_t)enc.number("base_resolution", 16);
 	in.per_level_scale = (float)enc.number("per_level_scale", 2.0);
 	CHECK(n_input_dims >= 2 && n_input_dims <= 4, "GridEncoding: number of input dims must be 2, 3 or 4");
-	in.encoded_width = next_multiple_u32(n_features, 16); // set_alignment(16) for FullyFusedMLP, network_with_input_encoding.h:47
+	// set_alignment(16) in front of FullyFusedMLP (network_with_input_encoding.h:47); a stand-alone encoding is not padded by
+	// the reference (alignment 0, src/cpp_api.cu:156-165) - its rows are stored here at the next multiple of 8 columns
+	in.encoded_width = next_multiple_u32(n_features, has_network ? 16u : 8u);
 	p->log2_per_level_scale = std::log2(in.per_level_scale);
 
 	// offset table on the host, as the reference's constructor does (grid.h:692-716)
@@ -227,7 +237,14 @@ extern "C" int tcnn_b200_plan_create(const char* json_utf8, uint32_t n_input_dim
 	p->grid.padded_width = in.encoded_width;
 	build_levels(p.get(), host_scales);
 	try_device_scales(p.get());
+	} else {
+		// Identity encoding (encodings/identity.h:46-90): fp32 -> fp16 copy, padded to a multiple of 16 columns with ones
+		CHECK(n_input_dims >= 1 && n_input_dims <= 64, "Network: n_input_dims must be in [1, 64] here");
+		in.encoded_width = next_multiple_u32(n_input_dims, 16);
+		try_device_scales(p.get());
+	}
 
+	if (has_network) {
 	// --- network: create_network (src/network.cu:97-140), FullyFusedMLP ctor (src/fully_fused_mlp.cu:635-678) ---
 	const std::string ntype = jsonmini::lower(net.string("otype", "FullyFusedMLP"));
 	CHECK(ntype == "fullyfusedmlp" || ntype == "megakernelmlp", "network otype '" + ntype + "' is outside the hot path (FullyFusedMLP only)");
@@ -241,6 +258,11 @@ extern "C" int tcnn_b200_plan_create(const char* json_utf8, uint32_t n_input_dim
 	CHECK(in.encoded_width <= 64, "encoded width above 64 is not implemented");
 	in.padded_output_width = 16;
 	in.n_params_mlp = (uint64_t)in.n_neurons * in.encoded_width + (uint64_t)(in.n_hidden_layers - 1) * in.n_neurons * in.n_neurons + (uint64_t)16 * in.n_neurons;
+	} else {
+		in.n_output_dims = n_features;             // Encoding.n_output_dims (modules.py:272-275)
+		in.padded_output_width = in.encoded_width;
+		in.n_params_mlp = 0;
+	}
 	in.n_params = in.n_params_mlp + in.n_params_grid;
 	CHECK(in.n_params < (1ull << 32), "more than 2^32 parameters");
 
@@ -354,7 +376,7 @@ extern "C" int tcnn_b200_init_params(const tcnn_b200_plan* plan, void* stream_, 
 	uint64_t base = 0;
 	float* dst = params_fp32;
 	const uint32_t W = in.n_neurons;
-	const uint32_t n_mats = in.n_hidden_layers + 1;
+	const uint32_t n_mats = in.n_params_mlp ? in.n_hidden_layers + 1 : 0; // a stand-alone encoding draws its table first
 	for (uint32_t k = 0; k < n_mats; ++k) {
 		const uint32_t rows = (k + 1 == n_mats) ? in.padded_output_width : W;
 		const uint32_t cols = (k == 0) ? in.encoded_width : W;
@@ -366,8 +388,10 @@ extern "C" int tcnn_b200_init_params(const tcnn_b200_plan* plan, void* stream_, 
 	}
 	const uint32_t ng = (uint32_t)in.n_params_grid;
 	const uint32_t n_threads = next_multiple_u32((ng + 3) / 4, 128); // random.h:58-63 + n_blocks_linear (128 threads)
-	init_uniform_kernel<<<(ng + 255) / 256, 256, 0, stream>>>(ng, n_threads, state, inc, base, -1e-4f, 1e-4f, dst);
-	launch_check("init_uniform_kernel");
+	if (ng) {
+		init_uniform_kernel<<<(ng + 255) / 256, 256, 0, stream>>>(ng, n_threads, state, inc, base, -1e-4f, 1e-4f, dst);
+		launch_check("init_uniform_kernel");
+	}
 	API_END
 }
 
@@ -599,6 +623,15 @@ extern "C" int tcnn_b200_mlp_backward(const tcnn_b200_plan* plan, void* stream_,
 }
 
 // ---- encoding + MLP -------------------------------------------------------------------------------------
+// grid gather, or the Identity encoding of a stand-alone Network
+static void encode_any(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t B, const float* x, const __half* grid, __half* encoded) {
+	if (plan->kind != PLAN_NETWORK) { encode_forward(plan, stream, B, x, grid, encoded); return; }
+	ProfileScope prof(plan, stream, PK_GRID_FWD);
+	const uint32_t n = B * (plan->info.encoded_width / 8);
+	identity_encode_kernel<<<(n + 255) / 256, 256, 0, stream>>>(B, plan->info.n_input_dims, plan->info.encoded_width, x, encoded);
+	launch_check("identity_encode_kernel");
+}
+
 extern "C" int tcnn_b200_inference(const tcnn_b200_plan* plan, void* stream_, uint32_t B, const float* x, const void* params,
 	void* output_fp16, float* output_fp32, void* workspace) {
 	API_BEGIN
@@ -607,7 +640,12 @@ extern "C" int tcnn_b200_inference(const tcnn_b200_plan* plan, void* stream_, ui
 	cudaStream_t stream = (cudaStream_t)stream_;
 	const Workspace w = carve(plan, B, workspace);
 	const __half* p = (const __half*)params;
-	encode_forward(plan, stream, B, x, p + plan->info.n_params_mlp, w.encoded);
+	if (plan->kind == PLAN_ENCODING) { // tcnn.Encoding: output = the encoded batch, fp16 [B][encoded_width]
+		CHECK(output_fp16 && !output_fp32, "a stand-alone encoding writes fp16 [B][encoded_width]");
+		encode_forward(plan, stream, B, x, p, (__half*)output_fp16);
+		return 0;
+	}
+	encode_any(plan, stream, B, x, p + plan->info.n_params_mlp, w.encoded);
 	mlp_infer(plan, stream, B, w.encoded, p, (__half*)output_fp16, output_fp32);
 	API_END
 }
@@ -621,20 +659,32 @@ extern "C" int tcnn_b200_backward(const tcnn_b200_plan* plan, void* stream_, uin
 	API_BEGIN
 	require_device(plan); check_batch(B);
 	CHECK(x && params && dL_doutput && workspace, "null argument");
-	CHECK(dL_dinput == nullptr, "dL_dinput (kernel_grid_backward_input, grid.h:322-349) is not implemented in this round");
-	if (!dL_dparams) return 0;
+	CHECK(dL_dinput == nullptr || plan->kind == PLAN_NETWORK, "dL_dinput of the grid encoding (kernel_grid_backward_input, grid.h:322-349) is not implemented in this round");
+	if (!dL_dparams && !dL_dinput) return 0;
 	cudaStream_t stream = (cudaStream_t)stream_;
 	const Workspace w = carve(plan, B, workspace);
 	const __half* p = (const __half*)params;
 	__half* g = (__half*)dL_dparams;
+	if (plan->kind == PLAN_ENCODING) { // dL_doutput is dL/d(encoded), fp16 [B][encoded_width]
+		encode_backward(plan, stream, B, x, (const __half*)dL_doutput, g, /*zero_first=*/1, w.replicas);
+		return 0;
+	}
 	MlpArgs a = base_mlp_args(plan, B, w.encoded, p); // w.encoded was left by tcnn_b200_forward (the Context)
 	a.dL_doutput = (const __half*)dL_doutput;
 	a.dL_dinput = w.dL_denc;
-	a.dW_partials = w.dw_partials;
+	a.dW_partials = g ? w.dw_partials : nullptr;
 	const uint32_t grid = mlp_grid_size(plan, a.n_tiles, true);
 	launch_mlp<MODE_BACKWARD>(plan, stream, a, grid);
-	mlp_finalize(plan, stream, grid, w, g, nullptr, false);
-	encode_backward(plan, stream, B, x, w.dL_denc, g + plan->info.n_params_mlp, /*zero_first=*/1, w.replicas);
+	if (g) mlp_finalize(plan, stream, grid, w, g, nullptr, false);
+	if (plan->kind == PLAN_NETWORK) {
+		if (dL_dinput) {
+			const uint32_t n = B * plan->info.n_input_dims;
+			identity_backward_kernel<<<(n + 255) / 256, 256, 0, stream>>>(B, plan->info.n_input_dims, plan->info.encoded_width, w.dL_denc, dL_dinput);
+			launch_check("identity_backward_kernel");
+		}
+	} else if (g) {
+		encode_backward(plan, stream, B, x, w.dL_denc, g + plan->info.n_params_mlp, /*zero_first=*/1, w.replicas);
+	}
 	API_END
 }
 
@@ -642,6 +692,7 @@ extern "C" int tcnn_b200_training_fwd_bwd(const tcnn_b200_plan* plan, void* stre
 	const void* params, void* grads, float loss_scale, int zero_grid_grads, float* loss_out, void* output_fp16, void* workspace) {
 	API_BEGIN
 	require_device(plan); check_batch(B);
+	CHECK(plan->kind == PLAN_FULL, "training entry points need an encoding and a network");
 	CHECK(x && target && params && grads && workspace, "null argument");
 	cudaStream_t main = (cudaStream_t)stream_;
 	const Workspace w = carve(plan, B, workspace);
@@ -749,6 +800,7 @@ extern "C" int tcnn_b200_training_step(const tcnn_b200_plan* plan, void* stream_
 	uint32_t* param_steps, float* loss_out, void* output_fp16, void* workspace) {
 	API_BEGIN
 	require_device(plan); check_batch(B);
+	CHECK(plan->kind == PLAN_FULL, "training entry points need an encoding and a network");
 	CHECK(x && target && params_fp32 && params_fp16 && grads_fp16 && first_moments && second_moments && param_steps && workspace, "null argument");
 	ensure_aux(plan);
 	cudaStream_t main = (cudaStream_t)stream_, aux = plan->aux;
@@ -837,6 +889,7 @@ extern "C" int tcnn_b200_training_step_dp(const tcnn_b200_plan* plan, void* stre
 	uint32_t* param_steps_shard, float* loss_out, void* output_fp16, void* workspace, const tcnn_b200_dp_comm* comm) {
 	API_BEGIN
 	require_device(plan); check_batch(B);
+	CHECK(plan->kind == PLAN_FULL, "training entry points need an encoding and a network");
 	CHECK(x && target && params_fp32_shard && first_moments_shard && second_moments_shard && param_steps_shard && workspace && comm, "null argument");
 	CHECK(comm->world_size >= 1 && comm->world_size <= DP_MAX_RANKS && comm->rank < comm->world_size, "bad rank / world size (at most 8 ranks: one NVSwitch domain)");
 	CHECK(comm->epoch >= 1, "epoch starts at 1 and grows by one per call");

@@ -30,6 +30,7 @@ class NativeModule:
         self.info = _lib.Info()
         check(self.lib.tcnn_b200_plan_info(self.handle, _lib.C.byref(self.info)))
         self._ws = {}
+        self.has_input_gradient = "encoding" not in config  # Identity encoding in front of a stand-alone Network
 
     def __del__(self):
         try:
@@ -78,13 +79,14 @@ class NativeModule:
         check(self.lib.tcnn_b200_inference(self.handle, _stream_ptr(), B, ptr(x), ptr(params), ptr(out), None, ptr(ws)))
         return None, out
 
-    def bwd(self, ws, x, params, doutput, want_params_grad: bool):
+    def bwd(self, ws, x, params, doutput, want_params_grad: bool, want_input_grad: bool = False):
+        """-> (dL_dinput fp32 [B, n_input_dims] or None, dL_dparams fp16 [n_params] or None)"""
         B = x.shape[0]
-        if not want_params_grad:
-            return None
-        g = torch.empty(self.n_params(), dtype=torch.half, device=x.device)
-        check(self.lib.tcnn_b200_backward(self.handle, _stream_ptr(), B, ptr(x), ptr(params), ptr(doutput), ptr(g), None, ptr(ws)))
-        return g
+        g = torch.empty(self.n_params(), dtype=torch.half, device=x.device) if want_params_grad else None
+        dx = torch.empty(B, int(self.info.n_input_dims), dtype=torch.float32, device=x.device) if want_input_grad else None
+        if g is not None or dx is not None:
+            check(self.lib.tcnn_b200_backward(self.handle, _stream_ptr(), B, ptr(x), ptr(params), ptr(doutput), ptr(g), ptr(dx), ptr(ws)))
+        return dx, g
 
 
 class _module_function(torch.autograd.Function):
@@ -101,13 +103,14 @@ class _module_function(torch.autograd.Function):
         if doutput is None:
             return None, None, None, None, None
         x, params = ctx.saved_tensors
-        if ctx.needs_input_grad[1]:
+        if ctx.needs_input_grad[1] and not ctx.native.has_input_gradient:
             raise RuntimeError("dL/dinput of the grid encoding (kernel_grid_backward_input) is not implemented in tcnn_b200 yet")
         with torch.no_grad():
             scaled = (doutput.to(torch.float) * ctx.loss_scale).to(torch.half).contiguous()
-            g = ctx.native.bwd(ctx.ws, x, params, scaled, ctx.needs_input_grad[2])
+            dx, g = ctx.native.bwd(ctx.ws, x, params, scaled, ctx.needs_input_grad[2], ctx.needs_input_grad[1])
+            dx = None if dx is None else dx / ctx.loss_scale
             g = None if g is None else g / ctx.loss_scale
-        return None, None, g, None, None
+        return None, dx, g, None, None
 
 
 class Module(torch.nn.Module):
@@ -163,6 +166,39 @@ class NetworkWithInputEncoding(Module):
 
     def _native_tcnn_module(self):
         return NativeModule(self.n_input_dims, self.n_output_dims, {"encoding": self.encoding_config, "network": self.network_config})
+
+
+class Network(Module):
+    """Neural network (modules.py:251-283 of the reference; src/cpp_api.cu:151-153: Identity encoding + network).  Supported
+    here: FullyFusedMLP with 64 neurons, 1-4 hidden layers, ReLU, linear output, n_input_dims <= 64, n_output_dims <= 16.
+    Gradients w.r.t. the input are available (identity_backward)."""
+
+    def __init__(self, n_input_dims, n_output_dims, network_config, seed=1337):
+        self.n_input_dims = n_input_dims
+        self.n_output_dims = n_output_dims
+        self.network_config = network_config
+        super().__init__(seed=seed)
+
+    def _native_tcnn_module(self):
+        return NativeModule(self.n_input_dims, self.n_output_dims, {"network": self.network_config})
+
+
+class Encoding(Module):
+    """Input encoding (modules.py:285-329 of the reference; src/cpp_api.cu:156-165: no padding of the output).  Supported
+    here: HashGrid, fp16 output and parameters (dtype None or torch.half)."""
+
+    def __init__(self, n_input_dims, encoding_config, seed=1337, dtype=None):
+        self.n_input_dims = n_input_dims
+        self.encoding_config = encoding_config
+        if dtype not in (None, torch.float16):
+            if dtype == torch.float32:
+                raise ValueError("tcnn_b200: Encoding is implemented for fp16 precision only")
+            raise ValueError(f"Encoding only supports fp32 or fp16 precision, but got {dtype}")
+        super().__init__(seed=seed)
+        self.n_output_dims = int(self.native_tcnn_module.info.n_output_dims)
+
+    def _native_tcnn_module(self):
+        return NativeModule(self.n_input_dims, 0, {"encoding": self.encoding_config})
 
 
 def free_temporary_memory():
