@@ -104,8 +104,8 @@ int tcnn_b200_inference(const tcnn_b200_plan* plan, void* stream, uint32_t batch
  * (the encoded batch), which therefore plays the role of the reference's Context. */
 int tcnn_b200_forward(const tcnn_b200_plan* plan, void* stream, uint32_t batch_size, const float* x, const void* params_fp16, void* output_fp16, void* workspace);
 /* cpp::Module::backward (src/cpp_api.cu:96-109), GradientMode::Overwrite.  dL_dparams fp16 [n_params] may be NULL.
- * dL_dinput (fp32 [B][D]) is implemented for network-only plans (identity_backward, encodings/identity.h:68-83); through a
- * grid encoding (kernel_grid_backward_input) it is not implemented in this round: passing non-NULL is then an error. */
+ * dL_dinput (fp32 [B][D], may be NULL): identity_backward (encodings/identity.h:68-83) for network-only plans, otherwise
+ * kernel_grid_backward_input (grid.h:322-349) with dy/dx (grid.h:171-211) recomputed on the fly instead of stored. */
 int tcnn_b200_backward(const tcnn_b200_plan* plan, void* stream, uint32_t batch_size, const float* x, const void* params_fp16,
                        const void* dL_doutput_fp16, void* dL_dparams_fp16, float* dL_dinput, void* workspace);
 

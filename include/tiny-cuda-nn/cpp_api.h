@@ -24,7 +24,7 @@ public:
 		TCNN_B200_CHECK_THROW(tcnn_b200_inference(m_network.plan(), stream, n_elements, input, params, output, nullptr, m_network.workspace(n_elements)));
 	}
 	Context forward(cudaStream_t stream, uint32_t n_elements, const float* input, void* output, void* params, bool prepare_input_gradients) {
-		if (prepare_input_gradients && m_network.info().n_levels != 0) throw std::runtime_error("tcnn_b200: dL_dinput of the grid encoding is not implemented yet");
+		(void)prepare_input_gradients; /* nothing to prepare: dy/dx is recomputed in backward */
 		Context ctx;
 		ctx.saved.resize(tcnn_b200_workspace_bytes(m_network.plan(), n_elements));
 		TCNN_B200_CHECK_THROW(tcnn_b200_forward(m_network.plan(), stream, n_elements, input, params, output, ctx.saved.data()));

@@ -319,6 +319,41 @@ def grid_backward(cfg: GridConfig, x: np.ndarray, dy: np.ndarray, sequential_fp1
     return g.reshape(-1)
 
 
+def grid_backward_input(cfg: GridConfig, x: np.ndarray, table: np.ndarray, dy: np.ndarray) -> np.ndarray:
+    """dL/dx of the grid encoding: dy/dx as kernel_grid computes it when asked (grid.h:171-211: per level and feature,
+    sum over the 2^(D-1) corner pairs along the gradient dim of scale * prod(other weights) * (val_right - val_left), fp32)
+    contracted with dL/dy as kernel_grid_backward_input does (grid.h:322-349: k ascending).  x fp32 [B, D], table fp16,
+    dy fp16 [B, >= L*F] -> fp32 [B, D]."""
+    B, D = x.shape
+    F = cfg.n_features_per_level
+    t = table.astype(np.float16).reshape(-1, F)
+    result = np.zeros((B, D), np.float32)
+    for l in range(cfg.n_levels):
+        scale, res = F32(cfg.scales[l]), int(cfg.resolutions[l])
+        frac, cell = pos_fract(x, F32(scale))
+        size, base = cfg.level_size(l), int(cfg.offsets[l])
+        grads = np.zeros((B, F, D), np.float32)
+        for gd in range(D):
+            for idx in range(1 << (D - 1)):
+                weight = np.full(B, F32(scale), np.float32)
+                pg = np.empty((B, D), np.uint32)
+                for nd in range(D - 1):
+                    dim = nd + 1 if nd >= gd else nd
+                    if (idx & (1 << nd)) == 0:
+                        weight = (weight * (F32(1.0) - frac[:, dim])).astype(np.float32); pg[:, dim] = cell[:, dim]
+                    else:
+                        weight = (weight * frac[:, dim]).astype(np.float32); pg[:, dim] = cell[:, dim] + np.uint32(1)
+                pg[:, gd] = cell[:, gd]
+                vl = t[base + grid_index(pg, size, res).astype(np.int64)].astype(np.float32)
+                pg[:, gd] = cell[:, gd] + np.uint32(1)
+                vr = t[base + grid_index(pg, size, res).astype(np.int64)].astype(np.float32)
+                grads[:, :, gd] = (grads[:, :, gd] + weight[:, None] * (vr - vl)).astype(np.float32)
+        for f in range(F):
+            dl = dy[:, l * F + f].astype(np.float32)
+            result = (result + dl[:, None] * grads[:, f, :]).astype(np.float32)
+    return result
+
+
 # --------------------------------------------------------------------------------------------------
 # FullyFusedMLP (src/fully_fused_mlp.cu:635-678 weight layout, :499-557 forward, :150-259/:735-836 backward)
 # --------------------------------------------------------------------------------------------------

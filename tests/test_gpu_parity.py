@@ -276,6 +276,15 @@ def test_module_surface_forward_backward(dev):
     ref = np.concatenate([dW, gg]) / 128.0
     assert common.rel_l2(grad[: m.n_params], ref[: m.n_params]) < 5e-3
     assert common.rel_l2(grad[m.n_params:], ref[m.n_params:]) < 5e-3
+    # dL/dinput through MLP and grid (NeRF-style normals) against the oracle chain
+    xg = x.clone().requires_grad_(True)
+    net.zero_grad()
+    net(xg).float().sum().backward()
+    dy1 = np.zeros((1024, 16), np.float32); dy1[:B, :3] = 128.0
+    _, dx_enc = O.mlp_backward(m, p16[: m.n_params], enc, hidden, dy1.astype(np.float16))
+    dxo = O.grid_backward_input(g, xp, p16[m.n_params:], dx_enc)[:B] / 128.0
+    assert xg.grad.shape == (B, 2)
+    assert common.rel_l2(xg.grad.cpu().numpy(), dxo) < 5e-3
     # two forwards before one backward (context lifetime, scripts/test_toch_bindings.py:25-50 of the reference)
     net.zero_grad()
     y1 = net(x); y2 = net(x)
@@ -314,7 +323,7 @@ def test_network_module_forward_backward_with_input_gradient(dev):
 
 def test_encoding_module_forward_backward(dev):
     """tcnn.Encoding (HashGrid alone, unpadded n_output_dims = n_levels * n_features_per_level): table init, encoded features
-    (bit-exact) and table gradients against the oracle; dL/dinput is refused loudly."""
+    (bit-exact), table gradients and dL/dinput against the oracle."""
     import tinycudann as tcnn
     enc_cfg = {"otype": "HashGrid", "n_levels": 5, "n_features_per_level": 2, "log2_hashmap_size": 12, "base_resolution": 4, "per_level_scale": 1.7}
     enc = tcnn.Encoding(3, enc_cfg, seed=5).to(dev)
@@ -338,9 +347,12 @@ def test_encoding_module_forward_backward(dev):
     xp = np.zeros((768, 3), np.float32); xp[:B] = x_np
     gg = O.grid_backward(g, xp, (dy * 128.0).astype(np.float16)) / 128.0
     assert common.rel_l2(enc.params.grad.cpu().numpy(), gg) < 5e-3
+    # dL/dinput (kernel_grid_backward_input with dy/dx recomputed on the fly) against the oracle restatement
     xr = x.clone().requires_grad_(True)
-    with pytest.raises(RuntimeError, match="not implemented"):
-        enc(xr).float().sum().backward()
+    (enc(xr).float() * torch.from_numpy(w_np).to(dev)).sum().backward()
+    dxo = O.grid_backward_input(g, xp, p16, (dy * 128.0).astype(np.float16))[:B] / 128.0
+    assert xr.grad.shape == (B, 3)
+    assert common.rel_l2(xr.grad.cpu().numpy(), dxo) < 1e-5
 
 
 def test_trainer_converges_and_matches_reference_order_of_magnitude(dev):

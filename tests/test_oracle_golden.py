@@ -101,3 +101,39 @@ def test_batch_generator_matches_reference_run(name):
     assert np.abs(O.synth_target(xl[-k:], n_out) - g["t_last"]).max() < 1e-5
     losses = g["losses"]
     assert losses.shape == (steps,) and losses[-50:].mean() < 1e-3 * losses[0]
+
+
+def test_grid_input_gradient_restatement_matches_finite_differences():
+    """oracle.grid_backward_input (grid.h:171-211 + 322-349) against central differences of a float64 interpolation of the
+    same fp16 table; samples whose +-eps probes cross a cell boundary are excluded."""
+    g = O.GridConfig(3, 5, 2, 12, 4, 1.7)
+    rng = np.random.default_rng(0)
+    table = (rng.standard_normal(g.n_params) * 0.3).astype(np.float16)
+    x = (rng.random((256, 3)) * 0.9 + 0.05).astype(np.float32)
+    dy = rng.standard_normal((256, 10)).astype(np.float16)
+    dx = O.grid_backward_input(g, x, table, dy)
+
+    def f(xx):
+        tot = np.zeros(len(xx))
+        t = table.astype(np.float64).reshape(-1, 2)
+        for l in range(5):
+            idx, _ = O.grid_corners(g, xx.astype(np.float32), l)
+            p = np.float64(g.scales[l]) * xx + 0.5
+            fr = p - np.floor(p)
+            val = np.zeros((len(xx), 2))
+            for c in range(8):
+                wc = np.ones(len(xx))
+                for d in range(3):
+                    wc *= fr[:, d] if (c >> d) & 1 else 1 - fr[:, d]
+                val += wc[:, None] * t[int(g.offsets[l]) + idx[:, c].astype(np.int64)]
+            tot += (val * dy[:, 2 * l:2 * l + 2].astype(np.float64)).sum(1)
+        return tot
+
+    eps, num = 1e-4, np.zeros((256, 3))
+    for d in range(3):
+        xp, xm = x.astype(np.float64).copy(), x.astype(np.float64).copy()
+        xp[:, d] += eps; xm[:, d] -= eps
+        num[:, d] = (f(xp) - f(xm)) / (2 * eps)
+    ok = (np.abs(num - dx) < 1e-2 * np.abs(num).max()).all(1)
+    assert ok.mean() > 0.97
+    assert np.linalg.norm((num - dx)[ok]) / np.linalg.norm(num[ok]) < 1e-2

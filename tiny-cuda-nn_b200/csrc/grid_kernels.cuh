@@ -335,6 +335,66 @@ __global__ void grid_replica_reduce_kernel(const __grid_constant__ GridParams gp
 	}
 }
 
+// kernel_grid (dy_dx part, grid.h:171-211) + kernel_grid_backward_input (grid.h:322-349) in one pass: the reference stores
+// dy/dx (fp32, D x E values per sample = 256 B at cfg #1) in the forward pass and contracts it with dL/dy in the backward pass;
+// here the corner values are gathered again and contracted on the fly, nothing is stored.  Same fp32 arithmetic and
+// summation order: per level and feature, dy/dx[d] = sum over the 2^(D-1) corner pairs along d of
+// scale * prod_{other dims} w * (val_right - val_left); dL/dx[d] = sum_k dL/dy_k * dy_k/dx[d], k ascending.
+// Thread = sample.
+template <int D, int F>
+__global__ void __launch_bounds__(256) grid_backward_input_kernel(const __grid_constant__ GridParams gp, uint32_t B, const float* __restrict__ x,
+	const __half* __restrict__ grid, const __half* __restrict__ dL_denc, float* __restrict__ dL_dx) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= B) return;
+	float p[D];
+	load_position<D>(x, i, p);
+	float result[D];
+#pragma unroll
+	for (int d = 0; d < D; ++d) result[d] = 0.f;
+	for (uint32_t level = 0; level < gp.n_levels; ++level) {
+		const GridLevel& lv = gp.level[level];
+		const __half* table = grid + (size_t)lv.offset * F;
+		float frac[D]; uint32_t cell[D];
+#pragma unroll
+		for (int d = 0; d < D; ++d) pos_fract_dev(p[d], lv.scale, frac[d], cell[d]);
+		float dl[F];
+#pragma unroll
+		for (int f = 0; f < F; ++f) dl[f] = __half2float(dL_denc[(size_t)i * gp.padded_width + level * F + f]);
+		float grads[F][D];
+#pragma unroll
+		for (int f = 0; f < F; ++f)
+#pragma unroll
+			for (int d = 0; d < D; ++d) grads[f][d] = 0.f;
+#pragma unroll
+		for (int gd = 0; gd < D; ++gd) {
+#pragma unroll
+			for (int idx = 0; idx < (1 << (D - 1)); ++idx) {
+				float weight = lv.scale;
+				uint32_t pg[D];
+#pragma unroll
+				for (int nd = 0; nd < D - 1; ++nd) {
+					const int dim = nd >= gd ? nd + 1 : nd;
+					if ((idx & (1 << nd)) == 0) { weight *= 1.0f - frac[dim]; pg[dim] = cell[dim]; }
+					else { weight *= frac[dim]; pg[dim] = cell[dim] + 1u; }
+				}
+				pg[gd] = cell[gd];
+				const uint32_t il = grid_index_dev<D>(lv, pg);
+				pg[gd] = cell[gd] + 1u;
+				const uint32_t ir = grid_index_dev<D>(lv, pg);
+#pragma unroll
+				for (int f = 0; f < F; ++f)
+					grads[f][gd] += weight * (__half2float(table[(size_t)ir * F + f]) - __half2float(table[(size_t)il * F + f]));
+			}
+		}
+#pragma unroll
+		for (int f = 0; f < F; ++f)
+#pragma unroll
+			for (int d = 0; d < D; ++d) result[d] += dl[f] * grads[f][d];
+	}
+#pragma unroll
+	for (int d = 0; d < D; ++d) dL_dx[(size_t)i * D + d] = result[d];
+}
+
 // Identity encoding in front of a stand-alone Network (encodings/identity.h:46-90, src/cpp_api.cu:151-153): fp32 [B][n_in] ->
 // fp16 [B][width], columns >= n_in are ONE (identity.h:63), so that the first layer can learn a bias through them.
 // Thread = sample x 8-column chunk.

@@ -623,6 +623,13 @@ extern "C" int tcnn_b200_mlp_backward(const tcnn_b200_plan* plan, void* stream_,
 }
 
 // ---- encoding + MLP -------------------------------------------------------------------------------------
+static void encode_backward_input(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t B, const float* x, const __half* grid, const __half* dL_denc, float* dL_dx) {
+	ProfileScope prof(plan, stream, PK_GRID_BWD);
+	const dim3 g((B + 255) / 256, 1, 1);
+	GRID_DISPATCH(grid_backward_input_kernel, plan, g, stream, plan->grid, B, x, grid, dL_denc, dL_dx);
+	launch_check("grid_backward_input_kernel");
+}
+
 // grid gather, or the Identity encoding of a stand-alone Network
 static void encode_any(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t B, const float* x, const __half* grid, __half* encoded) {
 	if (plan->kind != PLAN_NETWORK) { encode_forward(plan, stream, B, x, grid, encoded); return; }
@@ -659,14 +666,14 @@ extern "C" int tcnn_b200_backward(const tcnn_b200_plan* plan, void* stream_, uin
 	API_BEGIN
 	require_device(plan); check_batch(B);
 	CHECK(x && params && dL_doutput && workspace, "null argument");
-	CHECK(dL_dinput == nullptr || plan->kind == PLAN_NETWORK, "dL_dinput of the grid encoding (kernel_grid_backward_input, grid.h:322-349) is not implemented in this round");
 	if (!dL_dparams && !dL_dinput) return 0;
 	cudaStream_t stream = (cudaStream_t)stream_;
 	const Workspace w = carve(plan, B, workspace);
 	const __half* p = (const __half*)params;
 	__half* g = (__half*)dL_dparams;
 	if (plan->kind == PLAN_ENCODING) { // dL_doutput is dL/d(encoded), fp16 [B][encoded_width]
-		encode_backward(plan, stream, B, x, (const __half*)dL_doutput, g, /*zero_first=*/1, w.replicas);
+		if (g) encode_backward(plan, stream, B, x, (const __half*)dL_doutput, g, /*zero_first=*/1, w.replicas);
+		if (dL_dinput) encode_backward_input(plan, stream, B, x, p, (const __half*)dL_doutput, dL_dinput);
 		return 0;
 	}
 	MlpArgs a = base_mlp_args(plan, B, w.encoded, p); // w.encoded was left by tcnn_b200_forward (the Context)
@@ -682,8 +689,9 @@ extern "C" int tcnn_b200_backward(const tcnn_b200_plan* plan, void* stream_, uin
 			identity_backward_kernel<<<(n + 255) / 256, 256, 0, stream>>>(B, plan->info.n_input_dims, plan->info.encoded_width, w.dL_denc, dL_dinput);
 			launch_check("identity_backward_kernel");
 		}
-	} else if (g) {
-		encode_backward(plan, stream, B, x, w.dL_denc, g + plan->info.n_params_mlp, /*zero_first=*/1, w.replicas);
+	} else {
+		if (g) encode_backward(plan, stream, B, x, w.dL_denc, g + plan->info.n_params_mlp, /*zero_first=*/1, w.replicas);
+		if (dL_dinput) encode_backward_input(plan, stream, B, x, p + plan->info.n_params_mlp, w.dL_denc, dL_dinput);
 	}
 	API_END
 }

@@ -30,7 +30,6 @@ class NativeModule:
         self.info = _lib.Info()
         check(self.lib.tcnn_b200_plan_info(self.handle, _lib.C.byref(self.info)))
         self._ws = {}
-        self.has_input_gradient = "encoding" not in config  # Identity encoding in front of a stand-alone Network
 
     def __del__(self):
         try:
@@ -103,8 +102,6 @@ class _module_function(torch.autograd.Function):
         if doutput is None:
             return None, None, None, None, None
         x, params = ctx.saved_tensors
-        if ctx.needs_input_grad[1] and not ctx.native.has_input_gradient:
-            raise RuntimeError("dL/dinput of the grid encoding (kernel_grid_backward_input) is not implemented in tcnn_b200 yet")
         with torch.no_grad():
             scaled = (doutput.to(torch.float) * ctx.loss_scale).to(torch.half).contiguous()
             dx, g = ctx.native.bwd(ctx.ws, x, params, scaled, ctx.needs_input_grad[2], ctx.needs_input_grad[1])
