@@ -131,3 +131,32 @@ def test_cpp_facade_compiles_and_builds_a_plan_without_gpu():
     r = subprocess.run([exe, "--no-gpu"], capture_output=True, text=True, timeout=60)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "n_params=11191808 padded_output_width=16" in r.stdout
+
+
+def test_snapshot_format_roundtrip_through_msgpack():
+    """checkpoint.pack/unpack = the reference's Trainer::serialize object (trainer.h:275-315, adam.h:278-299); through msgpack
+    (what hosts of the reference write with json::to_msgpack) and through nlohmann's text form of binary values."""
+    import msgpack
+    import numpy as np
+    from tinycudann import checkpoint
+    rng = np.random.default_rng(0)
+    p = rng.standard_normal(1000).astype(np.float16)
+    opt = {"current_step": 17, "base_learning_rate": 1e-2, "first_moments": rng.standard_normal(1000).astype(np.float32),
+           "second_moments": rng.random(1000).astype(np.float32), "param_steps": rng.integers(0, 17, 1000).astype(np.uint32)}
+    snap = checkpoint.pack(p, opt)
+    assert snap["params_type"] == "__half" and snap["n_params"] == 1000 and len(snap["params_binary"]) == 2000
+    back = msgpack.unpackb(msgpack.packb(snap, use_bin_type=True), raw=False)
+    p2, o2 = checkpoint.unpack(back)
+    assert p2.dtype == np.float16 and np.array_equal(p2, p)
+    assert o2["current_step"] == 17 and abs(o2["base_learning_rate"] - 1e-2) < 1e-12
+    for k in ("first_moments", "second_moments", "param_steps"):
+        assert np.array_equal(o2[k], opt[k])
+    # float snapshot, JSON-text binary form, missing param_steps (older snapshots: adam.h:290-295)
+    f32 = {"n_params": 4, "params_type": "float", "params_binary": {"bytes": list(np.arange(4, dtype=np.float32).tobytes()), "subtype": None},
+           "optimizer": {"current_step": 1, "base_learning_rate": 0.5, "first_moments_binary": np.zeros(4, np.float32).tobytes(),
+                         "second_moments_binary": np.ones(4, np.float32).tobytes()}}
+    p3, o3 = checkpoint.unpack(f32)
+    assert p3.dtype == np.float32 and np.array_equal(p3, np.arange(4, dtype=np.float32)) and not o3["param_steps"].any()
+    import pytest
+    with pytest.raises(RuntimeError, match="float of __half"):
+        checkpoint.unpack({"params_type": "double", "params_binary": b""})

@@ -491,6 +491,28 @@ def test_cpp_facade_host_trains(dev):
     assert "inference mse" in r.stdout
 
 
+def test_trainer_snapshot_resumes_identically(dev):
+    """Trainer.serialize(serialize_optimizer=True) -> msgpack -> Trainer.deserialize on a fresh trainer: same parameters and
+    optimizer state, and the next step gives the same loss as the uninterrupted run (trainer.h:275-315)."""
+    import msgpack
+    import tinycudann as tcnn
+    a = tcnn.create_from_config(2, 3, common.CONFIG_SHIPPED, seed=1337, device=dev).trainer
+    B = 1 << 12
+    batches = [tuple(torch.from_numpy(v).to(dev) for v in common.synth_inputs(B, 2, 3, seed=60 + i)) for i in range(6)]
+    for x, t in batches[:4]:
+        a.training_step(x, t)
+    blob = msgpack.packb(a.serialize(serialize_optimizer=True), use_bin_type=True)
+    b = tcnn.create_from_config(2, 3, common.CONFIG_SHIPPED, seed=7, device=dev).trainer
+    b.deserialize(msgpack.unpackb(blob, raw=False))
+    assert torch.equal(a.params, b.params) and torch.equal(a.first_moments, b.first_moments)
+    assert torch.equal(a.second_moments, b.second_moments) and torch.equal(a.param_steps, b.param_steps) and b.current_step == 4
+    # master weights of the restored trainer are the fp16 snapshot cast up (the reference stores the fp16 copy)
+    assert torch.equal(b.params_full_precision, a.params.float())
+    for x, t in batches[4:]:
+        a.training_step(x, t); b.training_step(x, t)
+        assert abs(a.loss() - b.loss()) <= 2e-3 * abs(a.loss())
+
+
 def test_batch_size_must_be_multiple_of_256(dev):
     import tinycudann as tcnn
     model = tcnn.create_from_config(2, 3, common.CONFIG_1, seed=1, device=dev)

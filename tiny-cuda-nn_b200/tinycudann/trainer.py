@@ -147,6 +147,37 @@ class Trainer:
             return float(v.item()) / self.world_size
         return float(self.loss_value.item())
 
+    # trainer.h:275-315 + adam.h:278-299: the reference's snapshot object (see checkpoint.py)
+    def serialize(self, serialize_optimizer: bool = False) -> dict:
+        from . import checkpoint
+        opt = None
+        if serialize_optimizer:
+            if self.peer_memory is not None:
+                raise RuntimeError("dp_mode='peer' shards the optimizer state over the ranks: serialize the parameters only, or use dp_mode='allreduce'")
+            opt = {"current_step": self.current_step, "base_learning_rate": float(self.info.learning_rate),
+                   "first_moments": self.first_moments.cpu().numpy(), "second_moments": self.second_moments.cpu().numpy(),
+                   "param_steps": self.param_steps.cpu().numpy().view("uint32")}
+        return checkpoint.pack(self.params.cpu().numpy(), opt)
+
+    def deserialize(self, data: dict):
+        from . import checkpoint
+        params, opt = checkpoint.unpack(data)
+        if params.size != self.n_params:
+            raise RuntimeError(f"Can't set params because CPU buffer has the wrong size: {params.size} != {self.n_params}")
+        # float snapshots set the master weights, __half snapshots set both copies from the fp16 values (trainer.h:290-305)
+        self.set_params_full_precision(torch.from_numpy(params.astype("float32")))
+        if opt is not None:
+            if self.peer_memory is not None:
+                raise RuntimeError("dp_mode='peer' shards the optimizer state over the ranks")
+            self.first_moments.copy_(torch.from_numpy(opt["first_moments"]))
+            self.second_moments.copy_(torch.from_numpy(opt["second_moments"]))
+            self.param_steps.copy_(torch.from_numpy(opt["param_steps"].view("int32")))
+            self.current_step = opt["current_step"]
+            self.update_hyperparams({"learning_rate": opt["base_learning_rate"]})
+        self.param_gradients.zero_()
+        self._grid_grads_clean = True
+        torch.cuda.synchronize(self.device)
+
     def update_hyperparams(self, params: dict):
         check(self.lib.tcnn_b200_plan_update_optimizer(self.native.handle, json.dumps(params).encode()))
         self.native.refresh_info()
