@@ -284,6 +284,13 @@ def main():
     value = BATCH * world / (ms_per_step * 1e-3)
     final_loss = tr.loss()
 
+    # Network::inference (object.h:147-176) on the same resident batches: fp32 [B][O] output, device time
+    inf_out = torch.empty(BATCH, N_OUT, dtype=torch.float32, device=dev)
+    for i in range(5):
+        tr.inference(batches[i % n_batches][0], inf_out)
+    inf_steps = min(args.steps, 500)
+    inf_ms = timed(inf_steps, lambda i: tr.inference(batches[i % n_batches][0], inf_out)) / inf_steps
+
     for ev in ev_free:
         ev.record(torch.cuda.current_stream())
     e2e_steps = min(args.e2e_steps, args.steps)
@@ -330,6 +337,8 @@ def main():
                          "kernel_ms_per_step_serial": kernel_ms, "launches_per_step": launches_per_step, "kernel_share": {k: v / max(sum(kernel_ms.values()), 1e-9) for k, v in kernel_ms.items()},
                          "step": {"algorithmic_bytes": a_train, "achieved": a_train / (ms_per_step * 1e-3) / 1e9, "frac": a_train / (ms_per_step * 1e-3) / 1e9 / hbm_peak}},
             "final_loss": final_loss,
+            "inference": {"value": BATCH * world / (inf_ms * 1e-3), "unit": "samples/s", "ms_per_batch": inf_ms,
+                          "what": "Network::inference, fp32 output, inputs resident, batch 2^18 per GPU"},
         }
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_port(cfg)
