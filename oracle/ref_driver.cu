@@ -17,6 +17,7 @@
 #include <tiny-cuda-nn/config.h>
 #include <tiny-cuda-nn/random.h>
 
+#include <cctype>
 #include <chrono>
 #include <cstdio>
 #include <fstream>
@@ -123,26 +124,31 @@ static int mode_dump(int argc, char** argv) {
 	CUDA_CHECK_THROW(cudaMemcpy(input.data(), in_raw.data(), in_raw.size(), cudaMemcpyHostToDevice));
 	CUDA_CHECK_THROW(cudaMemcpy(target.data(), tg_raw.data(), tg_raw.size(), cudaMemcpyHostToDevice));
 
-	// indices / scales through the reference's device functions
+	// indices / scales through the reference's device functions (grid encodings only; OneBlob / Identity have no table)
 	json enc = cfg.value("encoding", json::object());
-	LevelTable lt = level_table(enc, n_in);
-	const uint32_t L = (uint32_t)lt.sizes.size();
-	const uint32_t F = enc.value("n_features_per_level", 2u);
-	if ((size_t)lt.offsets.back() * F != model.network->encoding()->n_params()) { std::cerr << "dump: level table disagrees with encoding->n_params()\n"; return 3; }
-	GPUMemory<uint32_t> d_sizes(L), d_idx((size_t)L * B * (1u << n_in)), d_res(L); GPUMemory<float> d_scale(L);
-	d_sizes.copy_from_host(lt.sizes);
-	const dim3 blocks{div_round_up(B, 256u), L, 1};
-	const float l2s = std::log2(enc.value("per_level_scale", 2.0f));
-	const uint32_t base = enc.value("base_resolution", 16u);
-	if (n_in == 2) dump_indices<2><<<blocks, 256, 0, stream>>>(B, L, d_sizes.data(), base, l2s, input.data(), d_idx.data(), d_scale.data(), d_res.data());
-	else if (n_in == 3) dump_indices<3><<<blocks, 256, 0, stream>>>(B, L, d_sizes.data(), base, l2s, input.data(), d_idx.data(), d_scale.data(), d_res.data());
-	else { std::cerr << "dump: n_in must be 2 or 3\n"; return 2; }
-	CUDA_CHECK_THROW(cudaStreamSynchronize(stream));
-	write_dev(out + "/indices.u32", d_idx.data(), d_idx.size());
-	write_dev(out + "/level_scale.f32", d_scale.data(), L);
-	write_dev(out + "/level_res.u32", d_res.data(), L);
-	write_host(out + "/level_size.u32", lt.sizes);
+	std::string enc_otype = enc.value("otype", std::string("Identity"));
+	for (auto& c : enc_otype) c = (char)std::tolower(c);
+	const bool is_grid = enc_otype == "hashgrid" || enc_otype == "grid";
+	if (is_grid) {
+		LevelTable lt = level_table(enc, n_in);
+		const uint32_t L = (uint32_t)lt.sizes.size();
+		const uint32_t F = enc.value("n_features_per_level", 2u);
+		if ((size_t)lt.offsets.back() * F != model.network->encoding()->n_params()) { std::cerr << "dump: level table disagrees with encoding->n_params()\n"; return 3; }
+		GPUMemory<uint32_t> d_sizes(L), d_idx((size_t)L * B * (1u << n_in)), d_res(L); GPUMemory<float> d_scale(L);
+		d_sizes.copy_from_host(lt.sizes);
+		const dim3 blocks{div_round_up(B, 256u), L, 1};
+		const float l2s = std::log2(enc.value("per_level_scale", 2.0f));
+		const uint32_t base = enc.value("base_resolution", 16u);
+		if (n_in == 2) dump_indices<2><<<blocks, 256, 0, stream>>>(B, L, d_sizes.data(), base, l2s, input.data(), d_idx.data(), d_scale.data(), d_res.data());
+		else if (n_in == 3) dump_indices<3><<<blocks, 256, 0, stream>>>(B, L, d_sizes.data(), base, l2s, input.data(), d_idx.data(), d_scale.data(), d_res.data());
+		else { std::cerr << "dump: n_in must be 2 or 3\n"; return 2; }
+		CUDA_CHECK_THROW(cudaStreamSynchronize(stream));
+		write_dev(out + "/indices.u32", d_idx.data(), d_idx.size());
+		write_dev(out + "/level_scale.f32", d_scale.data(), L);
+		write_dev(out + "/level_res.u32", d_res.data(), L);
+		write_host(out + "/level_size.u32", lt.sizes);
 
+	}
 	// encoded features (SoA [E x B], padded width) and network output
 	auto encoding = model.network->encoding();
 	GPUMatrixDynamic<precision_t> encoded(encoding->padded_output_width(), B, encoding->preferred_output_layout());
@@ -167,7 +173,8 @@ static int mode_dump(int argc, char** argv) {
 	write_dev(out + "/params_after.f32", model.trainer->params_full_precision(), P);
 	std::ofstream(out + "/meta.json") << json{{"loss", loss}, {"n_params", P}, {"n_params_encoding", encoding->n_params()},
 		{"padded_output_width", model.network->padded_output_width()}, {"encoded_width", encoding->padded_output_width()},
-		{"B", B}, {"n_in", n_in}, {"n_out", n_out}, {"hyperparams", model.network->hyperparams()}}.dump(1);
+		{"B", B}, {"n_in", n_in}, {"n_out", n_out}, {"hyperparams", model.network->hyperparams()},
+		{"encoded_layout", encoding->preferred_output_layout() == AoS ? "AoS" : "SoA"}}.dump(1);
 	std::cout << "dump ok loss=" << loss << " P=" << P << std::endl;
 	return 0;
 }

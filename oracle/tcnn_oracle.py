@@ -544,3 +544,73 @@ def init_params(mlp: MlpConfig, grid: GridConfig | None, seed: int = 1337, train
         rangef = F32(hi - lo)
         parts.append((flat.astype(np.float64) * np.float64(rangef) + np.float64(lo)).astype(np.float32))
     return np.concatenate(parts)
+
+
+# --------------------------------------------------------------------------------------------------
+# OneBlob encoding (encodings/oneblob.h:47-160; quartic kernel common_device.h:905-920) - BASELINE config #2
+# --------------------------------------------------------------------------------------------------
+def quartic_cdf(x: np.ndarray, inv_radius: float) -> np.ndarray:
+    """common_device.h:915-920, fp32."""
+    u = (x.astype(np.float32) * F32(inv_radius)).astype(np.float32)
+    u2 = (u * u).astype(np.float32)
+    u4 = (u2 * u2).astype(np.float32)
+    poly = (F32(1.0) - F32(F32(2.0) / F32(3.0)) * u2 + F32(F32(1.0) / F32(5.0)) * u4).astype(np.float32)
+    v = (F32(15.0 / 16.0) * u * poly + F32(0.5)).astype(np.float32)
+    return np.maximum(F32(0.0), np.minimum(F32(1.0), v)).astype(np.float32)
+
+
+def quartic_pdf(x: np.ndarray, inv_radius: float) -> np.ndarray:
+    """quartic_cdf_deriv, common_device.h:905-913."""
+    u = (x.astype(np.float32) * F32(inv_radius)).astype(np.float32)
+    t = np.maximum(F32(1.0) - u * u, F32(0.0)).astype(np.float32)
+    return (F32(15.0 / 16.0) * t * t * F32(inv_radius)).astype(np.float32)
+
+
+def oneblob_shuffle_source(n_out: int, n_bins: int) -> np.ndarray:
+    """Column whose LEFT-edge CDF a column takes as its RIGHT-edge CDF (one_blob_subwarp_aligned, oneblob.h:47-70):
+    `__shfl_sync(0xffffffff, left_cdf, bin_index + 1, n_bins)` in a block of (n_out, ceil(128/n_out)) threads.
+    For n_bins <= 32 that is the next bin of the same dimension, wrapping inside the dimension.  For n_bins = 64 the
+    shuffle width exceeds the warp: the hardware then uses lane (bin + 1) mod 32 of the SAME warp (segment mask 0), so
+    bins 31 and 63 read bins 0 and 32 - the reference's actual output, which parity follows."""
+    j = np.arange(n_out)
+    b = j % n_bins
+    if n_bins <= 32:
+        return (j - b) + (b + 1) % n_bins
+    return (j & ~31) | ((b + 1) & 31)
+
+
+def oneblob_forward(x: np.ndarray, n_bins: int, width: int | None = None) -> np.ndarray:
+    """x fp32 [B, D] -> fp16 [B, width]; columns >= D * n_bins are 1 (oneblob.h:131-133).  AoS kernel (oneblob.h:84-96)."""
+    B, D = x.shape
+    n_out = D * n_bins
+    width = width or next_multiple(n_out, 16)
+    j = np.arange(n_out)
+    b = (j % n_bins).astype(np.float32)
+    xv = x.astype(np.float32)[:, j // n_bins]
+    lb = (b / F32(n_bins)).astype(np.float32)[None, :]  # scalbnf(bin, -log2 n_bins): exact
+    d = (lb - xv).astype(np.float32)
+    left = (quartic_cdf(d, n_bins) + quartic_cdf((d - F32(1.0)).astype(np.float32), n_bins)).astype(np.float32)
+    left = (left + quartic_cdf((d + F32(1.0)).astype(np.float32), n_bins)).astype(np.float32)
+    right = left[:, oneblob_shuffle_source(n_out, n_bins)].copy()
+    right[:, (j % n_bins) == n_bins - 1] += F32(1.0)
+    out = np.ones((B, width), np.float16)
+    out[:, :n_out] = (right - left).astype(np.float16)
+    return out
+
+
+def oneblob_backward_input(x: np.ndarray, n_bins: int, dy: np.ndarray) -> np.ndarray:
+    """dL/dx fp32 [B, D] from dL/dy fp16 [B, >= D * n_bins] (kernel_one_blob_backward, oneblob.h:105-141)."""
+    B, D = x.shape
+    xv = x.astype(np.float32)
+
+    def wrapped(boundary):
+        d = (F32(boundary) - xv).astype(np.float32)
+        return (quartic_pdf(d, n_bins) + quartic_pdf(d - F32(1.0), n_bins) + quartic_pdf(d + F32(1.0), n_bins)).astype(np.float32)
+
+    res = np.zeros((B, D), np.float32)
+    left = wrapped(0.0)
+    for k in range(n_bins):
+        right = wrapped((k + 1) / n_bins)
+        res += dy[:, np.arange(D) * n_bins + k].astype(np.float32) * (left - right)
+        left = right
+    return res

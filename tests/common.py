@@ -28,9 +28,42 @@ CONFIG_F4 = {  # F = 4, small table, 3 hidden layers: exercises the other templa
     "network": {"otype": "FullyFusedMLP", "activation": "ReLU", "output_activation": "None", "n_neurons": 64, "n_hidden_layers": 3},
 }
 
+CONFIG_ONEBLOB = {  # BASELINE.json configs[1]: data/config_oneblob.json of the reference (bench_ours.cu), 2-D input -> 128 features
+    "loss": {"otype": "RelativeL2"},
+    "optimizer": {"otype": "Adam", "learning_rate": 1e-2, "beta1": 0.9, "beta2": 0.99, "epsilon": 1e-8, "l2_reg": 1e-8},
+    "encoding": {"otype": "OneBlob", "n_bins": 64},
+    "network": {"otype": "FullyFusedMLP", "activation": "ReLU", "output_activation": "None", "n_neurons": 128, "n_hidden_layers": 5},
+}
+CONFIG_ONEBLOB16 = {  # OneBlob in front of the 64-neuron kernel (32 features)
+    "loss": {"otype": "L2"},
+    "optimizer": {"otype": "Adam", "learning_rate": 1e-3},
+    "encoding": {"otype": "OneBlob", "n_bins": 16},
+    "network": {"otype": "FullyFusedMLP", "activation": "ReLU", "output_activation": "None", "n_neurons": 64, "n_hidden_layers": 4},
+}
+CONFIG_WIDE_F4 = {  # BASELINE.json configs[3] with a table small enough for fixtures: 3-D, 16 x 4 features, 128 x 4
+    "loss": {"otype": "L2"},
+    "optimizer": {"otype": "Adam", "learning_rate": 1e-3},
+    "encoding": {"otype": "HashGrid", "n_levels": 16, "n_features_per_level": 4, "log2_hashmap_size": 14, "base_resolution": 16, "per_level_scale": 1.38},
+    "network": {"otype": "FullyFusedMLP", "activation": "ReLU", "output_activation": "None", "n_neurons": 128, "n_hidden_layers": 4},
+}
+CONFIG_WIDE_DP = {  # BASELINE.json configs[4] with a small table: 3-D, 16 x 2 features, 128 x 3
+    "loss": {"otype": "L2"},
+    "optimizer": {"otype": "Adam", "learning_rate": 1e-3},
+    "encoding": {"otype": "HashGrid", "n_levels": 16, "n_features_per_level": 2, "log2_hashmap_size": 15, "base_resolution": 16, "per_level_scale": 1.38},
+    "network": {"otype": "FullyFusedMLP", "activation": "ReLU", "output_activation": "None", "n_neurons": 128, "n_hidden_layers": 3},
+}
+
+
+def is_oneblob(cfg):
+    return cfg["encoding"].get("otype", "").lower() == "oneblob"
+
 
 def oracle_configs(cfg, n_in, n_out, scales=None):
     e = cfg["encoding"]
+    n = cfg["network"]
+    if is_oneblob(cfg):  # no table: g is None, the MLP input is the padded OneBlob width
+        m = O.MlpConfig(O.next_multiple(n_in * e.get("n_bins", 16), 16), n_out, n.get("n_neurons", 128), n.get("n_hidden_layers", 5))
+        return None, m
     g = O.GridConfig(n_in, e.get("n_levels", 16), e.get("n_features_per_level", 2), e.get("log2_hashmap_size", 19),
                      e.get("base_resolution", 16), e.get("per_level_scale", 2.0), scales=scales)
     n = cfg["network"]
@@ -50,3 +83,12 @@ def synth_inputs(B, n_in, n_out, seed=0):
 def rel_l2(a, b):
     a = np.asarray(a, dtype=np.float64); b = np.asarray(b, dtype=np.float64)
     return float(np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-30))
+
+
+def oracle_encode(cfg, g, m, x, table16):
+    """fp16 [B, m.n_input]: the encoded batch as the MLP sees it (grid features zero-padded, OneBlob one-padded)."""
+    if is_oneblob(cfg):
+        return O.oneblob_forward(x, cfg["encoding"].get("n_bins", 16), m.n_input)
+    enc = np.zeros((x.shape[0], m.n_input), np.float16)
+    enc[:, : g.n_features] = O.grid_forward(g, x, table16)
+    return enc

@@ -25,6 +25,11 @@ CASES = [  # name, config, n_in, n_out, B
     ("shipped_2d_T15", common.CONFIG_SHIPPED, 2, 3, 1024),
     ("nerf_3d_T19", common.CONFIG_NERF, 3, 4, 1024),
     ("f4_3d_T14", common.CONFIG_F4, 3, 3, 512),
+    # 128-neuron networks and the OneBlob encoding (BASELINE configs #2, #4, #5 at fixture-sized tables)
+    ("wide_dp_3d_T15", common.CONFIG_WIDE_DP, 3, 3, 512),
+    ("wide_f4_3d_T14", common.CONFIG_WIDE_F4, 3, 4, 512),
+    ("oneblob_2d_128x5", common.CONFIG_ONEBLOB, 2, 3, 1024),
+    ("oneblob16_2d_64x4", common.CONFIG_ONEBLOB16, 2, 3, 512),
 ]
 SAMPLE_STRIDE = 997
 CURVES = [  # name, config, n_in, n_out, B, steps, seed
@@ -56,10 +61,14 @@ def curves(outdir):
 
 def main(outdir):
     os.makedirs(outdir, exist_ok=True)
-    curves(outdir)
+    only = [n for n in os.environ.get("GOLDEN_ONLY", "").split(",") if n]  # restrict to these case names (no curves)
+    if not only:
+        curves(outdir)
     if os.environ.get("GOLDEN_CURVES_ONLY"):
         return
     for name, cfg, n_in, n_out, B in CASES:
+        if only and name not in only:
+            continue
         x, t = common.synth_inputs(B, n_in, n_out, seed=1)
         with tempfile.TemporaryDirectory() as d:
             x.tofile(os.path.join(d, "x.f32")); t.tofile(os.path.join(d, "t.f32"))
@@ -81,14 +90,18 @@ def main(outdir):
             nz = np.flatnonzero(gg.view(np.uint16) & 0x7FFF).astype(np.uint32)
             sample = np.arange(0, P, SAMPLE_STRIDE, dtype=np.int64)
             moved = np.flatnonzero(after != params_init).astype(np.uint32)
-            L = len(rd("level_res.u32", np.uint32))
+            grid = os.path.exists(os.path.join(d, "level_res.u32"))  # OneBlob has no level table / indices
+            L = len(rd("level_res.u32", np.uint32)) if grid else 0
+            enc_raw = rd("encoded_soa.f16", np.float16)
+            extra = dict(level_scale=rd("level_scale.f32", np.float32), level_res=rd("level_res.u32", np.uint32), level_size=rd("level_size.u32", np.uint32),
+                         indices=rd("indices.u32", np.uint32).reshape(L, B, 1 << n_in)) if grid else {}
+            # SoA dumps are [E x B]; an AoS encoding (OneBlob) is stored transposed so that `encoded_soa` always reads [E x B]
+            encoded_soa = enc_raw.reshape(E, B) if meta.get("encoded_layout", "SoA") == "SoA" else np.ascontiguousarray(enc_raw.reshape(B, E).T)
             np.savez_compressed(
                 os.path.join(outdir, name + ".npz"),
                 config=json.dumps(cfg), n_in=n_in, n_out=n_out, B=B, seed=1, loss=np.float32(meta["loss"]),
                 n_params=P, n_params_mlp=P_mlp,
-                level_scale=rd("level_scale.f32", np.float32), level_res=rd("level_res.u32", np.uint32), level_size=rd("level_size.u32", np.uint32),
-                indices=rd("indices.u32", np.uint32).reshape(L, B, 1 << n_in),
-                encoded_soa=rd("encoded_soa.f16", np.float16).reshape(E, B),
+                encoded_soa=encoded_soa, **extra,
                 output=rd("output.f32", np.float32).reshape(B, n_out),
                 output_padded=rd("output_padded.f16", np.float16).reshape(B, meta["padded_output_width"]),
                 dL_doutput=rd("dL_doutput.f16", np.float16).reshape(B, meta["padded_output_width"]),

@@ -62,6 +62,8 @@ struct MlpArgs {
 	__half* grid_grad;             // [n_params_grid]
 	__half* replicas;              // private copies of the replicated coarse levels (grid_kernels.cuh)
 	long long* debug_clock;        // MLP_STAGE_CLOCKS builds only
+	// 128-neuron path (mlp_wide_kernels.cuh; host side only): per-layer buffers in the caller's workspace
+	__half* wide_hidden; __half* wide_gtmp; __half* wide_dy;
 };
 
 // byte offset of 16-byte chunk `c` of row `r` inside a 128-byte-swizzled tile
@@ -538,7 +540,7 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 // Sum the per-CTA fp32 partials -> fp16 weight gradients (layout of the reference's gradient matrices) and the loss.
 // Block = 32 parameters x 8 slices of the partial list (coalesced 128-byte rows), tree-reduced in shared memory.
 __global__ void __launch_bounds__(256) mlp_finalize_kernel(uint32_t n_params, uint32_t n_parts, const float* __restrict__ partials, __half* __restrict__ grads,
-	const float* __restrict__ loss_partials, float* __restrict__ loss_out) {
+	const float* __restrict__ loss_partials, float* __restrict__ loss_out, uint32_t n_loss_parts) {
 	__shared__ float sh[8][33];
 	const uint32_t px = threadIdx.x & 31, sl = threadIdx.x >> 5;
 	const uint32_t i = blockIdx.x * 32 + px;
@@ -557,7 +559,7 @@ __global__ void __launch_bounds__(256) mlp_finalize_kernel(uint32_t n_params, ui
 	if (blockIdx.x == 0 && loss_partials && loss_out) {
 		__syncthreads();
 		float l = 0.f;
-		for (uint32_t p = threadIdx.x; p < n_parts; p += blockDim.x) l += loss_partials[p];
+		for (uint32_t p = threadIdx.x; p < n_loss_parts; p += blockDim.x) l += loss_partials[p];
 #pragma unroll
 		for (int o = 16; o > 0; o >>= 1) l += __shfl_xor_sync(0xFFFFFFFFu, l, o);
 		if (px == 0) sh[sl][0] = l;

@@ -1,0 +1,456 @@
+// Fully fused MLP, width 128, for sm_100a on tcgen05 tensor cores (BASELINE configs #2, #4, #5).
+//
+// Computes the reference's FullyFusedMLP<half, 128> (src/fully_fused_mlp.cu:47-259, 499-557, 735-836): ReLU hidden layers,
+// linear output padded to 16, fp16 storage, plus the L2 / RelativeL2 loss (losses/l2.h:40-75, relative_l2.h:40-75), the
+// weight gradients of the reference's split-K GEMMs (cutlass_matmul.h:437-479) and dL/d(input) (cutlass_matmul.h:351-408).
+//
+// At width 128 a tile's activations of all layers (32 KB each) plus all weight matrices (32 KB each) no longer fit one
+// SM's shared memory together, and the weight-gradient accumulators (128 TMEM columns per matrix) no longer fit TMEM, so the
+// training pass is three kernels with the activations / pre-activation gradients kept in HBM as the reference does:
+//   mlp_wide_forward_kernel   all weights resident in shared memory; one 128-sample tile per warpgroup, two warpgroups per
+//                             CTA working on independent tiles so that one's epilogue hides under the other's MMAs; the
+//                             activation tile is overwritten in place layer by layer; loss + dL/d(output) in the epilogue
+//   mlp_wide_backward_kernel  same structure for the dgrad chain; the ReLU mask is re-read from the stored activations
+//   mlp_wide_dw_kernel        split-K over the batch: CTA (split, matrix) accumulates G^T * ACT in TMEM over its tiles
+// Operand tiles are [128 rows][128 halfs] stored as TWO 128-byte-swizzled sub-tiles of [128][64 halfs] (16 KB apart): as a
+// K-major operand K-step s starts at sub-tile s/4, byte 32 (s%4); as an MN-major operand (weight tiles in the dgrad MMAs,
+// both operands of the weight-gradient MMAs) the sub-tiles are the two 64-wide M/N atoms, LBO = 16 KB.
+#pragma once
+#include "mlp_kernels.cuh"
+
+namespace b200 {
+
+constexpr int WIDE_W = 128;
+constexpr uint32_t SUB_BYTES = 16384;               // [128 rows][64 halfs]
+constexpr uint32_t WIDE_TILE_BYTES = 2 * SUB_BYTES;
+constexpr int WIDE_MAX_HIDDEN = 8;
+
+struct WideArgs {
+	uint32_t n_tiles;              // B / 128
+	uint32_t in_width;             // E_pad: multiple of 16, <= 128
+	uint32_t n_hidden;             // H >= 1
+	uint32_t n_out;                // real outputs (<= 16)
+	uint64_t batch;                // B = row count of every per-layer buffer
+	const __half* input;           // [B][E]
+	const __half* params;          // [128 x E], (H-1) x [128 x 128], [16 x 128] row-major (fully_fused_mlp.cu:654-671)
+	__half* output;                // [B][16] nullable
+	float* output_f32;             // [B][n_out] nullable (inference: fused trim_and_cast, object.h:174-175)
+	const float* target;           // [B][n_out]
+	const __half* dL_doutput;      // backward / dW: [B][16]
+	__half* dL_doutput_out;        // forward with loss: [B][16] written
+	__half* hidden;                // [H][B][128] post-activation outputs of matrices 0..H-1
+	__half* gtmp;                  // [H][B][128] gradients w.r.t. the pre-activations of matrices 0..H-1
+	__half* dL_dinput;             // [B][E] nullable
+	float* dW_partials;            // [n_splits][n_mlp_params]
+	float* loss_partials;          // one per forward warpgroup
+	uint32_t n_mlp_params, n_splits;
+	int loss_type;
+	float loss_scale, n_total;
+};
+
+__host__ __device__ constexpr uint32_t wide_in_sub(uint32_t E) { return (E + 63u) / 64u; }
+__host__ __device__ constexpr uint32_t wide_fwd_smem(uint32_t H, uint32_t E, uint32_t nwg) {
+	return 1024u + nwg * WIDE_TILE_BYTES + wide_in_sub(E) * SUB_BYTES + (H - 1) * WIDE_TILE_BYTES + 4096u + 256u;
+}
+__host__ __device__ constexpr uint32_t wide_bwd_smem(uint32_t H, uint32_t E, uint32_t nwg, bool want_dx) {
+	return 1024u + nwg * WIDE_TILE_BYTES + (want_dx ? wide_in_sub(E) * SUB_BYTES : 0u) + (H - 1) * WIDE_TILE_BYTES + 4096u + 256u;
+}
+constexpr uint32_t WIDE_DW_SMEM = 1024u + 2 * WIDE_TILE_BYTES + 256u;
+
+// global row-major [rows][cols] halfs -> K-major swizzled sub-tiles of [rows][64 halfs] (rows * 128 bytes each); columns
+// beyond `cols` up to the next multiple of 64 are zero-filled (they are read by the MN-major view of the input matrix)
+__device__ __forceinline__ void wide_stage_weights(uint8_t* dst, const __half* src, uint32_t rows, uint32_t cols, uint32_t tid, uint32_t nt) {
+	const uint32_t cpr = cols / 8, cprp = wide_in_sub(cols) * 8, sub_bytes = rows * 128;
+	for (uint32_t q = tid; q < rows * cprp; q += nt) {
+		const uint32_t r = q / cprp, c = q % cprp;
+		uint4 v = make_uint4(0, 0, 0, 0);
+		if (c < cpr) v = __ldg(reinterpret_cast<const uint4*>(src + (size_t)r * cols) + c);
+		*reinterpret_cast<uint4*>(dst + (c >> 3) * sub_bytes + sw128(r, c & 7)) = v;
+	}
+}
+
+template <int NWG> __device__ __forceinline__ void wide_wg_sync(uint32_t wg) {
+	if constexpr (NWG == 1) __syncthreads(); else named_bar_sync(1 + wg, 128);
+}
+
+// rows of `width` halfs (global, contiguous tile of 128 rows) -> swizzled tile; executed by 128 threads (index wt)
+__device__ __forceinline__ void wide_load_tile(uint32_t dst_addr, const __half* src, uint32_t width, uint32_t wt) {
+	const uint4* s4 = reinterpret_cast<const uint4*>(src);
+	const uint32_t cpr = width / 8;
+	for (uint32_t j0 = 0; j0 < cpr; j0 += 4) {
+		uint4 v[4];
+#pragma unroll
+		for (uint32_t u = 0; u < 4; ++u) if (j0 + u < cpr) v[u] = ldg128_here(s4 + wt + 128 * (j0 + u));
+#pragma unroll
+		for (uint32_t u = 0; u < 4; ++u) {
+			if (j0 + u < cpr) {
+				const uint32_t q = wt + 128 * (j0 + u), r = q / cpr, c = q % cpr;
+				sts128(dst_addr + (c >> 3) * SUB_BYTES + sw128(r, c & 7), v[u]);
+			}
+		}
+	}
+}
+
+// ---- forward (+ loss) ----------------------------------------------------------------------------------------
+// MODE_INFER: output only.  MODE_TRAIN: stores hidden activations, loss partials and dL/d(output).
+// MODE_BACKWARD: stores hidden activations only (forward recomputation in front of a caller-supplied dL/d(output)).
+template <int MODE, int NWG>
+__global__ void __launch_bounds__(128 * NWG, 1) mlp_wide_forward_kernel(const __grid_constant__ WideArgs a) {
+	constexpr bool STORE = MODE != MODE_INFER;
+	extern __shared__ uint8_t smem_raw[];
+	uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+	const uint32_t tid = threadIdx.x, wg = tid >> 7, wt = tid & 127, warp = wt >> 5, lane = tid & 31;
+	const uint32_t E = a.in_width, H = a.n_hidden, in_sub = wide_in_sub(E);
+	uint8_t* act = smem;                                    // NWG activation tiles, overwritten in place layer by layer
+	uint8_t* w_in = act + NWG * WIDE_TILE_BYTES;            // in_sub x [128 out][128 B]
+	uint8_t* w_hid = w_in + in_sub * SUB_BYTES;             // (H-1) x 2 x [128 out][128 B]
+	uint8_t* w_out = w_hid + (H - 1) * WIDE_TILE_BYTES;     // 2 x [16 out][128 B]
+	uint8_t* tail = w_out + 4096;
+	uint64_t* bars = reinterpret_cast<uint64_t*>(tail);     // one per warpgroup
+	uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tail + 32);
+	float* red_buf = reinterpret_cast<float*>(tail + 64);   // NWG x 4
+
+	constexpr uint32_t tmem_cols = 128 * NWG;
+	if (tid < 32) tmem_alloc(tmem_slot, tmem_cols);
+	if (tid == 32) {
+		for (int g = 0; g < NWG; ++g) mbar_init(bars + g, 1);
+		mbar_fence_init();
+	}
+	{
+		const __half* p = a.params;
+		wide_stage_weights(w_in, p, 128, E, tid, 128 * NWG);
+		p += 128 * E;
+		for (uint32_t l = 0; l + 1 < H; ++l) { wide_stage_weights(w_hid + l * WIDE_TILE_BYTES, p, 128, 128, tid, 128 * NWG); p += 128 * 128; }
+		wide_stage_weights(w_out, p, 16, 128, tid, 128 * NWG);
+	}
+	fence_proxy_async_smem();
+	tc_fence_before();
+	__syncthreads();
+	tc_fence_after();
+	const uint32_t t_acc = *tmem_slot + wg * 128;
+	const uint32_t lane_off = (warp * 32) << 16;
+	const uint32_t act_addr = smem_u32(act) + wg * WIDE_TILE_BYTES;
+	const uint32_t idesc_hid = make_idesc_f16(128, 128, 0, 0), idesc_out = make_idesc_f16(128, 16, 0, 0);
+	uint64_t* bar = bars + wg;
+	uint32_t phase = 0;
+	float loss_acc = 0.f;
+	const uint32_t row = wt;
+
+	for (uint32_t tile = blockIdx.x * NWG + wg; tile < a.n_tiles; tile += gridDim.x * NWG) {
+		const size_t sample0 = (size_t)tile * MLP_TILE;
+		wide_load_tile(act_addr, a.input + sample0 * E, E, wt);
+		float tgt[4] = {0.f, 0.f, 0.f, 0.f};
+		if (MODE == MODE_TRAIN) {
+#pragma unroll
+			for (uint32_t j = 0; j < 4; ++j) if (j < a.n_out) tgt[j] = ldg_f32_here(a.target + (sample0 + row) * a.n_out + j);
+		}
+		fence_proxy_async_smem();
+		tc_fence_before();
+		wide_wg_sync<NWG>(wg);
+
+		for (uint32_t k = 0; k < H; ++k) {
+			if (wt == 0) {
+				tc_fence_after();
+				const uint32_t ksteps = (k == 0 ? E : 128u) / 16;
+				const uint32_t b_addr = k == 0 ? smem_u32(w_in) : smem_u32(w_hid) + (k - 1) * WIDE_TILE_BYTES;
+				for (uint32_t s = 0; s < ksteps; ++s) {
+					const uint32_t off = (s >> 2) * SUB_BYTES + (s & 3) * 32;
+					umma_f16(t_acc, make_desc_sw128(act_addr + off, 16, 1024), make_desc_sw128(b_addr + off, 16, 1024), idesc_hid, s > 0);
+				}
+				umma_commit(bar);
+			}
+			mbar_wait(bar, phase); phase ^= 1;
+			tc_fence_after();
+			uint4* hdst = STORE ? reinterpret_cast<uint4*>(a.hidden + ((size_t)k * a.batch + sample0 + row) * WIDE_W) : nullptr;
+#pragma unroll
+			for (int cb = 0; cb < 4; ++cb) {
+				uint32_t v[32];
+				tmem_ld32(t_acc + lane_off + cb * 32, v);
+				tmem_ld_wait();
+#pragma unroll
+				for (int c = 0; c < 4; ++c) {
+					uint32_t pk[4];
+#pragma unroll
+					for (int j = 0; j < 4; ++j) pk[j] = h2_relu(pack_h2(__uint_as_float(v[c * 8 + 2 * j]), __uint_as_float(v[c * 8 + 2 * j + 1])));
+					sts128(act_addr + (cb >> 1) * SUB_BYTES + sw128(row, (cb & 1) * 4 + c), pk[0], pk[1], pk[2], pk[3]);
+					if (STORE) hdst[cb * 4 + c] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+				}
+			}
+			fence_proxy_async_smem();
+			tc_fence_before();
+			wide_wg_sync<NWG>(wg);
+		}
+		// ---- output layer (N = 16, K = 128) ----
+		if (wt == 0) {
+			tc_fence_after();
+			for (uint32_t s = 0; s < 8; ++s)
+				umma_f16(t_acc, make_desc_sw128(act_addr + (s >> 2) * SUB_BYTES + (s & 3) * 32, 16, 1024),
+					make_desc_sw128(smem_u32(w_out) + (s >> 2) * 2048 + (s & 3) * 32, 16, 1024), idesc_out, s > 0);
+			umma_commit(bar);
+		}
+		mbar_wait(bar, phase); phase ^= 1;
+		tc_fence_after();
+		{
+			uint32_t v[16];
+			tmem_ld16(t_acc + lane_off, v);
+			tmem_ld_wait();
+			uint32_t yk[8];
+#pragma unroll
+			for (int j = 0; j < 8; ++j) yk[j] = pack_h2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
+			const size_t s = sample0 + row;
+			if (MODE != MODE_BACKWARD && a.output) {
+				uint4* o = reinterpret_cast<uint4*>(a.output + s * MLP_OUT);
+				o[0] = make_uint4(yk[0], yk[1], yk[2], yk[3]);
+				o[1] = make_uint4(yk[4], yk[5], yk[6], yk[7]);
+			}
+			if (MODE == MODE_INFER && a.output_f32) {
+				const __half* yh = reinterpret_cast<const __half*>(yk);
+				for (uint32_t j = 0; j < a.n_out; ++j) a.output_f32[s * a.n_out + j] = __half2float(yh[j]);
+			}
+			if (MODE == MODE_TRAIN) {
+				// same operation order as losses/l2.h:62-74 / relative_l2.h:62-75 (see mlp_kernels.cuh)
+				const __half* yh = reinterpret_cast<const __half*>(yk);
+				const bool relative = a.loss_type == LOSS_RELATIVE_L2;
+				auto loss_elem = [&](float pred, float target) -> float {
+					const float diff = pred - target;
+					float value = diff * diff, grad = 2.f * diff;
+					if (relative) { const float denom = pred * pred + 0.01f; value = value / denom; grad = grad / denom; }
+					loss_acc += value / a.n_total;
+					return a.loss_scale * grad / a.n_total;
+				};
+				float g4[4];
+#pragma unroll
+				for (uint32_t j = 0; j < 4; ++j) g4[j] = (j < a.n_out) ? loss_elem(__half2float(yh[j]), tgt[j]) : 0.f;
+				uint32_t dyk[8] = {pack_h2(g4[0], g4[1]), pack_h2(g4[2], g4[3]), 0u, 0u, 0u, 0u, 0u, 0u};
+				if (a.n_out > 4) {
+#pragma unroll
+					for (uint32_t j = 4; j < 16; j += 2) {
+						const float ga = (j < a.n_out) ? loss_elem(__half2float(yh[j]), __ldg(a.target + s * a.n_out + j)) : 0.f;
+						const float gb = (j + 1 < a.n_out) ? loss_elem(__half2float(yh[j + 1]), __ldg(a.target + s * a.n_out + j + 1)) : 0.f;
+						dyk[j / 2] = pack_h2(ga, gb);
+					}
+				}
+				uint4* d = reinterpret_cast<uint4*>(a.dL_doutput_out + s * MLP_OUT);
+				d[0] = make_uint4(dyk[0], dyk[1], dyk[2], dyk[3]);
+				d[1] = make_uint4(dyk[4], dyk[5], dyk[6], dyk[7]);
+			}
+		}
+		tc_fence_before(); // the next tile's barrier orders these TMEM reads before its first MMA
+	}
+	if (MODE == MODE_TRAIN && a.loss_partials != nullptr) {
+		float s = loss_acc;
+#pragma unroll
+		for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xFFFFFFFFu, s, o);
+		if (lane == 0) red_buf[wg * 4 + warp] = s;
+		wide_wg_sync<NWG>(wg);
+		if (wt == 0) a.loss_partials[blockIdx.x * NWG + wg] = red_buf[wg * 4] + red_buf[wg * 4 + 1] + red_buf[wg * 4 + 2] + red_buf[wg * 4 + 3];
+	}
+	tc_fence_before();
+	__syncthreads();
+	if (tid < 32) tmem_dealloc(*tmem_slot, tmem_cols);
+}
+
+// ---- backward (dgrad chain) ----------------------------------------------------------------------------------
+// Matrices m = 0..H (0 = input, H = output); ACT_m = input of matrix m (ACT_0 = X, ACT_m = hidden[m-1]); G_m = gradient
+// w.r.t. the output of matrix m before its activation (G_H = dL/d(output)).  G_{m-1} = (G_m * W_m) (.) [ACT_m > 0]
+// (fully_fused_mlp.cu:150-259, ReLU' from the stored post-activation, common_device.h:243-248), written to gtmp[m-1] for
+// the weight-gradient kernel; finally dL/d(input) = G_0 * W_0.  The G tile is overwritten in place.
+template <int NWG>
+__global__ void __launch_bounds__(128 * NWG, 1) mlp_wide_backward_kernel(const __grid_constant__ WideArgs a) {
+	extern __shared__ uint8_t smem_raw[];
+	uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+	const uint32_t tid = threadIdx.x, wg = tid >> 7, wt = tid & 127, warp = wt >> 5;
+	const uint32_t E = a.in_width, H = a.n_hidden, in_sub = wide_in_sub(E);
+	const bool want_dx = a.dL_dinput != nullptr;
+	uint8_t* gt = smem;                                                 // NWG gradient tiles
+	uint8_t* w_in = gt + NWG * WIDE_TILE_BYTES;                         // only when dL/d(input) is wanted
+	uint8_t* w_hid = w_in + (want_dx ? in_sub * SUB_BYTES : 0u);
+	uint8_t* w_out = w_hid + (H - 1) * WIDE_TILE_BYTES;
+	uint8_t* tail = w_out + 4096;
+	uint64_t* bars = reinterpret_cast<uint64_t*>(tail);
+	uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tail + 32);
+
+	constexpr uint32_t tmem_cols = 128 * NWG;
+	if (tid < 32) tmem_alloc(tmem_slot, tmem_cols);
+	if (tid == 32) {
+		for (int g = 0; g < NWG; ++g) mbar_init(bars + g, 1);
+		mbar_fence_init();
+	}
+	{
+		const __half* p = a.params;
+		if (want_dx) wide_stage_weights(w_in, p, 128, E, tid, 128 * NWG);
+		p += 128 * E;
+		for (uint32_t l = 0; l + 1 < H; ++l) { wide_stage_weights(w_hid + l * WIDE_TILE_BYTES, p, 128, 128, tid, 128 * NWG); p += 128 * 128; }
+		wide_stage_weights(w_out, p, 16, 128, tid, 128 * NWG);
+	}
+	// columns 16.. of the gradient tile are read (as zeros) by nobody before they are written, except through the K = 16
+	// A operand of the output matrix, which only touches chunks 0 and 1: no clearing needed
+	fence_proxy_async_smem();
+	tc_fence_before();
+	__syncthreads();
+	tc_fence_after();
+	const uint32_t t_acc = *tmem_slot + wg * 128;
+	const uint32_t lane_off = (warp * 32) << 16;
+	const uint32_t g_addr = smem_u32(gt) + wg * WIDE_TILE_BYTES;
+	const uint32_t idesc_dgrad = make_idesc_f16(128, 128, 0, 1);         // A K-major, B = weight tile viewed MN-major
+	const uint32_t idesc_dx = make_idesc_f16(128, in_sub * 64, 0, 1);
+	uint64_t* bar = bars + wg;
+	uint32_t phase = 0;
+	const uint32_t row = wt;
+
+	for (uint32_t tile = blockIdx.x * NWG + wg; tile < a.n_tiles; tile += gridDim.x * NWG) {
+		const size_t sample0 = (size_t)tile * MLP_TILE;
+		{
+			const uint4* d4 = reinterpret_cast<const uint4*>(a.dL_doutput + (sample0 + row) * MLP_OUT);
+			const uint4 d0 = ldg128_here(d4), d1 = ldg128_here(d4 + 1);
+			sts128(g_addr + sw128(row, 0), d0);
+			sts128(g_addr + sw128(row, 1), d1);
+		}
+		fence_proxy_async_smem();
+		tc_fence_before();
+		wide_wg_sync<NWG>(wg);
+
+		for (uint32_t m = H; m >= 1; --m) {
+			if (wt == 0) {
+				tc_fence_after();
+				if (m == H) {
+					// Z[128 x 128 in] = dy[128 x 16] * W_out[16 x 128]: one K step; B atoms (64 inputs each) 2 KB apart
+					umma_f16(t_acc, make_desc_sw128(g_addr, 16, 1024), make_desc_sw128(smem_u32(w_out), 2048, 1024), idesc_dgrad, 0);
+				} else {
+					const uint32_t wb = smem_u32(w_hid) + (m - 1) * WIDE_TILE_BYTES;
+					for (uint32_t s = 0; s < 8; ++s) // K = 128 outputs of W_m, 16 rows (2 KB) per step; N atoms 16 KB apart
+						umma_f16(t_acc, make_desc_sw128(g_addr + (s >> 2) * SUB_BYTES + (s & 3) * 32, 16, 1024),
+							make_desc_sw128(wb + s * 2048, SUB_BYTES, 1024), idesc_dgrad, s > 0);
+				}
+				umma_commit(bar);
+			}
+			// ReLU mask source: this row of ACT_m = hidden[m-1]; requested now, in flight under the MMA
+			const uint4* hsrc = reinterpret_cast<const uint4*>(a.hidden + ((size_t)(m - 1) * a.batch + sample0 + row) * WIDE_W);
+			uint4 av[16];
+#pragma unroll
+			for (int c = 0; c < 16; ++c) av[c] = ldg128_here(hsrc + c);
+			mbar_wait(bar, phase); phase ^= 1;
+			tc_fence_after();
+			uint4* gdst = reinterpret_cast<uint4*>(a.gtmp + ((size_t)(m - 1) * a.batch + sample0 + row) * WIDE_W);
+#pragma unroll
+			for (int cb = 0; cb < 4; ++cb) {
+				uint32_t v[32];
+				tmem_ld32(t_acc + lane_off + cb * 32, v);
+				tmem_ld_wait();
+#pragma unroll
+				for (int c = 0; c < 4; ++c) {
+					const uint4 aw4 = av[cb * 4 + c];
+					const uint32_t aw[4] = {aw4.x, aw4.y, aw4.z, aw4.w};
+					uint32_t pk[4];
+#pragma unroll
+					for (int j = 0; j < 4; ++j) pk[j] = h2_mask_mul(pack_h2(__uint_as_float(v[c * 8 + 2 * j]), __uint_as_float(v[c * 8 + 2 * j + 1])), aw[j]);
+					sts128(g_addr + (cb >> 1) * SUB_BYTES + sw128(row, (cb & 1) * 4 + c), pk[0], pk[1], pk[2], pk[3]);
+					gdst[cb * 4 + c] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+				}
+			}
+			fence_proxy_async_smem();
+			tc_fence_before();
+			wide_wg_sync<NWG>(wg);
+		}
+		if (want_dx) {
+			if (wt == 0) {
+				tc_fence_after();
+				for (uint32_t s = 0; s < 8; ++s)
+					umma_f16(t_acc, make_desc_sw128(g_addr + (s >> 2) * SUB_BYTES + (s & 3) * 32, 16, 1024),
+						make_desc_sw128(smem_u32(w_in) + s * 2048, SUB_BYTES, 1024), idesc_dx, s > 0);
+				umma_commit(bar);
+			}
+			mbar_wait(bar, phase); phase ^= 1;
+			tc_fence_after();
+			__half* dst = a.dL_dinput + (sample0 + row) * E;
+			for (uint32_t c0 = 0; c0 < E; c0 += 16) {
+				uint32_t v[16];
+				tmem_ld16(t_acc + lane_off + c0, v);
+				tmem_ld_wait();
+				uint32_t pk[8];
+#pragma unroll
+				for (int j = 0; j < 8; ++j) pk[j] = pack_h2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
+				reinterpret_cast<uint4*>(dst + c0)[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+				reinterpret_cast<uint4*>(dst + c0)[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+			}
+		}
+		tc_fence_before();
+	}
+	tc_fence_before();
+	__syncthreads();
+	if (tid < 32) tmem_dealloc(*tmem_slot, tmem_cols);
+}
+
+// ---- weight gradients: split-K over the batch ------------------------------------------------------------------
+// CTA (split j, matrix m): D[out][in] = sum over its tiles of G_m^T[out x 128 samples] * ACT_m[128 samples x in], both
+// operands MN-major views of row-major [sample][feature] tiles; fp32 in TMEM across all tiles of the CTA, one flush at the
+// end into partials[j]; mlp_finalize(_adam)_kernel sums the splits (deterministic).  Replaces the reference's three
+// split-K CUTLASS GEMMs (fully_fused_mlp.cu:783-829).  Up to 3 CTAs per SM hide the global loads of one under the MMAs
+// of the others.
+__global__ void __launch_bounds__(128, 3) mlp_wide_dw_kernel(const __grid_constant__ WideArgs a) {
+	extern __shared__ uint8_t smem_raw[];
+	uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+	const uint32_t tid = threadIdx.x, warp = tid >> 5;
+	const uint32_t E = a.in_width, H = a.n_hidden, in_sub = wide_in_sub(E);
+	const uint32_t split = blockIdx.x, m = blockIdx.y;
+	uint8_t* a_tile = smem;
+	uint8_t* b_tile = smem + WIDE_TILE_BYTES;
+	uint8_t* tail = b_tile + WIDE_TILE_BYTES;
+	uint64_t* bar = reinterpret_cast<uint64_t*>(tail);
+	uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tail + 32);
+	if (warp == 0) tmem_alloc(tmem_slot, 128);
+	if (tid == 32) { mbar_init(bar, 1); mbar_fence_init(); }
+	for (uint32_t q = tid; q < 2 * WIDE_TILE_BYTES / 16; q += 128) reinterpret_cast<uint4*>(smem)[q] = make_uint4(0, 0, 0, 0);
+	fence_proxy_async_smem();
+	tc_fence_before();
+	__syncthreads();
+	tc_fence_after();
+	const uint32_t t_acc = *tmem_slot;
+	const uint32_t lane_off = (warp * 32) << 16;
+	const uint32_t aw = (m == H) ? (uint32_t)MLP_OUT : (uint32_t)WIDE_W;
+	const uint32_t bw = (m == 0) ? E : (uint32_t)WIDE_W;
+	const __half* asrc = (m == H) ? a.dL_doutput : a.gtmp + (size_t)m * a.batch * WIDE_W;
+	const __half* bsrc = (m == 0) ? a.input : a.hidden + (size_t)(m - 1) * a.batch * WIDE_W;
+	const uint32_t idesc = make_idesc_f16(128, (m == 0) ? in_sub * 64 : 128, 1, 1);
+	const uint32_t a_addr = smem_u32(a_tile), b_addr = smem_u32(b_tile);
+	uint32_t phase = 0;
+	bool pending = false, first = true;
+	for (uint32_t tile = split; tile < a.n_tiles; tile += a.n_splits) {
+		if (pending) { mbar_wait(bar, phase); phase ^= 1; pending = false; }
+		wide_load_tile(a_addr, asrc + (size_t)tile * MLP_TILE * aw, aw, tid);
+		wide_load_tile(b_addr, bsrc + (size_t)tile * MLP_TILE * bw, bw, tid);
+		fence_proxy_async_smem();
+		tc_fence_before();
+		__syncthreads();
+		if (tid == 0) {
+			tc_fence_after();
+			for (uint32_t s = 0; s < 8; ++s) // K = 128 samples, 16 rows (2 KB) per step
+				umma_f16(t_acc, make_desc_sw128(a_addr + s * 2048, SUB_BYTES, 1024), make_desc_sw128(b_addr + s * 2048, SUB_BYTES, 1024), idesc, (!first) || s > 0);
+			umma_commit(bar);
+		}
+		pending = true; first = false;
+	}
+	if (pending) { mbar_wait(bar, phase); phase ^= 1; }
+	tc_fence_after();
+	{
+		const uint32_t out_rows = (m == H) ? (uint32_t)MLP_OUT : (uint32_t)WIDE_W;
+		const uint32_t mat_off = (m == 0) ? 0u : 128u * E + (m - 1) * 128u * 128u;
+		float* out = a.dW_partials + (size_t)split * a.n_mlp_params + mat_off + (size_t)tid * bw;
+		for (uint32_t c0 = 0; c0 < bw; c0 += 16) {
+			uint32_t v[16];
+			tmem_ld16(t_acc + lane_off + c0, v);
+			tmem_ld_wait();
+			if (tid < out_rows) {
+#pragma unroll
+				for (int j = 0; j < 4; ++j)
+					reinterpret_cast<float4*>(out + c0)[j] = first ? make_float4(0, 0, 0, 0)
+						: make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
+			}
+		}
+	}
+	tc_fence_before();
+	__syncthreads();
+	if (warp == 0) tmem_dealloc(t_acc, 128);
+}
+
+} // namespace b200

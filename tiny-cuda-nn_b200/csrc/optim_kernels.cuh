@@ -98,7 +98,7 @@ __global__ void __launch_bounds__(256) adam_kernel(const __grid_constant__ AdamA
 // MLP weights applied in the same pass: on one GPU the 7 K weights need no separate optimizer launch on the critical path.
 // The gradient is rounded to fp16 first (it is also stored), so the update equals adam_kernel on the stored gradient.
 __global__ void __launch_bounds__(256) mlp_finalize_adam_kernel(uint32_t n_params, uint32_t n_parts, const float* __restrict__ partials,
-	const float* __restrict__ loss_partials, float* __restrict__ loss_out, const __grid_constant__ AdamArgs a) {
+	const float* __restrict__ loss_partials, float* __restrict__ loss_out, const __grid_constant__ AdamArgs a, uint32_t n_loss_parts) {
 	__shared__ float sh[8][33];
 	const uint32_t px = threadIdx.x & 31, sl = threadIdx.x >> 5;
 	const uint32_t i = blockIdx.x * 32 + px;
@@ -120,7 +120,7 @@ __global__ void __launch_bounds__(256) mlp_finalize_adam_kernel(uint32_t n_param
 	if (blockIdx.x == 0 && loss_partials && loss_out) {
 		__syncthreads();
 		float l = 0.f;
-		for (uint32_t p = threadIdx.x; p < n_parts; p += blockDim.x) l += loss_partials[p];
+		for (uint32_t p = threadIdx.x; p < n_loss_parts; p += blockDim.x) l += loss_partials[p];
 #pragma unroll
 		for (int o = 16; o > 0; o >>= 1) l += __shfl_xor_sync(0xFFFFFFFFu, l, o);
 		if ((threadIdx.x & 31) == 0) sh[0][threadIdx.x >> 5] = l;

@@ -17,6 +17,8 @@
 #include "grid_kernels.cuh"
 #include "json_mini.h"
 #include "mlp_kernels.cuh"  // includes grid_kernels.cuh (fused scatter)
+#include "mlp_wide_kernels.cuh"
+#include "oneblob_kernels.cuh"
 #include "optim_kernels.cuh"
 
 using namespace b200;
@@ -43,6 +45,8 @@ struct tcnn_b200_plan {
 	// Adam extras
 	float non_matrix_lr_factor = 1.f, weight_clip = 0.f;
 	bool adabound = false;
+	int enc_kind = 0;               // ENC_GRID / ENC_IDENTITY / ENC_ONEBLOB
+	uint32_t oneblob_log2_bins = 0;
 	int kind = 0;                   // PLAN_FULL: encoding + network; PLAN_NETWORK: Identity encoding + network; PLAN_ENCODING: grid encoding alone
 	bool no_warp_specialization = getenv("TCNN_B200_NO_WS") != nullptr; // development switch: fused kernel without the scatter warpgroup
 	// optional per-kernel timing (tcnn_b200_profile_*): CUDA events recorded around every launch on the launch stream
@@ -56,6 +60,7 @@ struct tcnn_b200_plan {
 };
 
 enum PlanKind { PLAN_FULL = 0, PLAN_NETWORK = 1, PLAN_ENCODING = 2 };
+enum EncKind { ENC_GRID = 0, ENC_IDENTITY = 1, ENC_ONEBLOB = 2 };
 enum ProfileKind { PK_GRID_FWD = 0, PK_MLP = 1, PK_FINALIZE = 2, PK_GRID_BWD = 3, PK_ADAM = 4, PK_COUNT = 5 };
 
 struct ProfileScope {
@@ -186,6 +191,20 @@ extern "C" int tcnn_b200_plan_create(const char* json_utf8, uint32_t n_input_dim
 	if (has_encoding) {
 	// --- encoding: create_grid_encoding (encodings/grid.h:1143-1208) ---
 	const std::string etype = jsonmini::lower(enc.string("otype", "Grid"));
+	if (etype == "oneblob") {
+		// OneBlobEncoding (encodings/oneblob.h:162-175; created by src/encoding.cu with n_bins default 16)
+		CHECK(has_network, "a stand-alone OneBlob encoding is outside the hot path (OneBlob feeds the fused MLP, config #2)");
+		const uint32_t n_bins = (uint32_t)enc.number("n_bins", 16);
+		CHECK(n_bins >= 2 && (n_bins & (n_bins - 1)) == 0, "Number of bins must be a power of 2");
+		CHECK(n_input_dims >= 1 && (uint64_t)n_input_dims * n_bins <= 128, "OneBlob: n_input_dims * n_bins must be <= 128 here");
+		p->enc_kind = ENC_ONEBLOB;
+		while ((1u << p->oneblob_log2_bins) < n_bins) ++p->oneblob_log2_bins;
+		n_features = n_input_dims * n_bins;
+		in.encoded_width = next_multiple_u32(n_features, 16u);
+		p->grid.n_features = n_features;
+		p->grid.padded_width = in.encoded_width;
+		try_device_scales(p.get());
+	} else {
 	CHECK(etype == "hashgrid" || etype == "grid", "encoding otype '" + etype + "' is outside the hot path (HashGrid only; SURVEY.md section 8)");
 	CHECK(jsonmini::lower(enc.string("type", "Hash")) == "hash", "only grid type 'Hash' is implemented");
 	CHECK(jsonmini::lower(enc.string("hash", "CoherentPrime")) == "coherentprime", "only hash 'CoherentPrime' is implemented");
@@ -237,7 +256,9 @@ extern "C" int tcnn_b200_plan_create(const char* json_utf8, uint32_t n_input_dim
 	p->grid.padded_width = in.encoded_width;
 	build_levels(p.get(), host_scales);
 	try_device_scales(p.get());
+	}
 	} else {
+		p->enc_kind = ENC_IDENTITY;
 		// Identity encoding (encodings/identity.h:46-90): fp32 -> fp16 copy, padded to a multiple of 16 columns with ones
 		CHECK(n_input_dims >= 1 && n_input_dims <= 64, "Network: n_input_dims must be in [1, 64] here");
 		in.encoded_width = next_multiple_u32(n_input_dims, 16);
@@ -250,12 +271,15 @@ extern "C" int tcnn_b200_plan_create(const char* json_utf8, uint32_t n_input_dim
 	CHECK(ntype == "fullyfusedmlp" || ntype == "megakernelmlp", "network otype '" + ntype + "' is outside the hot path (FullyFusedMLP only)");
 	in.n_neurons = (uint32_t)net.number("n_neurons", 128);
 	in.n_hidden_layers = (uint32_t)net.number("n_hidden_layers", 5);
-	CHECK(in.n_neurons == 64, "FullyFusedMLP: this build implements n_neurons = 64 (16/32/128 are listed as next in DESIGN.md)");
-	CHECK(in.n_hidden_layers >= 1 && in.n_hidden_layers <= (uint32_t)MLP_MAX_HIDDEN, "FullyFusedMLP: n_hidden_layers must be in [1, 4] here");
+	CHECK(in.n_neurons == 64 || in.n_neurons == 128, "FullyFusedMLP: this build implements n_neurons = 64 and 128 (16/32 are out of scope, DESIGN.md)");
+	if (in.n_neurons == 64) CHECK(in.n_hidden_layers >= 1 && in.n_hidden_layers <= (uint32_t)MLP_MAX_HIDDEN, "FullyFusedMLP: n_hidden_layers must be in [1, 4] at 64 neurons");
+	else CHECK(in.n_hidden_layers >= 1 && in.n_hidden_layers <= (uint32_t)WIDE_MAX_HIDDEN, "FullyFusedMLP: n_hidden_layers must be in [1, 8] at 128 neurons");
 	CHECK(jsonmini::lower(net.string("activation", "ReLU")) == "relu", "only activation 'ReLU' is implemented");
 	CHECK(jsonmini::lower(net.string("output_activation", "None")) == "none", "only output_activation 'None' is implemented");
 	CHECK(n_output_dims >= 1 && n_output_dims <= 16, "n_output_dims must be in [1, 16] (fused last layer, fully_fused_mlp.cu:544)");
-	CHECK(in.encoded_width <= 64, "encoded width above 64 is not implemented");
+	CHECK(in.encoded_width <= in.n_neurons, "encoded width above n_neurons is not implemented");
+	if (in.n_neurons == 128)
+		CHECK(wide_fwd_smem(in.n_hidden_layers, in.encoded_width, 1) <= 232448u, "FullyFusedMLP 128: the weight matrices of this many hidden layers do not fit shared memory");
 	in.padded_output_width = 16;
 	in.n_params_mlp = (uint64_t)in.n_neurons * in.encoded_width + (uint64_t)(in.n_hidden_layers - 1) * in.n_neurons * in.n_neurons + (uint64_t)16 * in.n_neurons;
 	} else {
@@ -313,10 +337,24 @@ extern "C" int tcnn_b200_plan_update_optimizer(tcnn_b200_plan* plan, const char*
 // workspace layout: [encoded B x E fp16][dL_dencoded B x E fp16][dW partials n_ctas x P_mlp fp32][loss partials n_ctas fp32]
 struct Workspace {
 	__half* encoded; __half* dL_denc; float* dw_partials; float* loss_partials; __half* replicas;
+	// 128-neuron path only: hidden activations and pre-activation gradients [H][B][128], dL/d(output) [B][16]
+	__half* wide_hidden; __half* wide_gtmp; __half* wide_dy;
 };
+static bool is_wide(const tcnn_b200_plan* p) { return p->info.n_neurons == 128; }
+// 64 neurons: CTAs of the persistent MLP kernel = number of weight-gradient / loss partials.
+// 128 neurons: number of batch splits of the weight-gradient kernel (one CTA per split and matrix, 3 resident per SM).
 static uint32_t mlp_grid_size(const tcnn_b200_plan* p, uint32_t n_tiles, bool train) {
+	if (is_wide(p) && train) return std::max(1u, std::min(n_tiles, (uint32_t)p->n_sms * 3u / (p->info.n_hidden_layers + 1)));
 	const uint32_t per_sm = train ? 2u : 3u;
 	return std::max(1u, std::min(n_tiles, (uint32_t)p->n_sms * per_sm));
+}
+// warpgroups (independent tiles) per CTA of the 128-neuron forward / backward kernels: two if shared memory allows
+static uint32_t wide_nwg_fwd(const tcnn_b200_plan* p) { return wide_fwd_smem(p->info.n_hidden_layers, p->info.encoded_width, 2) <= 232448u ? 2u : 1u; }
+static uint32_t wide_nwg_bwd(const tcnn_b200_plan* p, bool want_dx) { return wide_bwd_smem(p->info.n_hidden_layers, p->info.encoded_width, 2, want_dx) <= 232448u ? 2u : 1u; }
+static uint32_t wide_fwd_ctas(const tcnn_b200_plan* p, uint32_t n_tiles) { const uint32_t g = wide_nwg_fwd(p); return std::max(1u, std::min((n_tiles + g - 1) / g, (uint32_t)p->n_sms)); }
+// number of loss partials the training forward leaves (the 64-neuron kernel: one per CTA = per weight-gradient partial)
+static uint32_t mlp_loss_parts(const tcnn_b200_plan* p, uint32_t n_tiles, uint32_t n_parts) {
+	return is_wide(p) ? wide_fwd_ctas(p, n_tiles) * wide_nwg_fwd(p) : n_parts;
 }
 static size_t align256(size_t v) { return (v + 255) / 256 * 256; }
 static Workspace carve(const tcnn_b200_plan* p, uint32_t B, void* ws) {
@@ -328,14 +366,22 @@ static Workspace carve(const tcnn_b200_plan* p, uint32_t B, void* ws) {
 	w.dL_denc = (__half*)b; b += act;
 	w.dw_partials = (float*)b; b += align256((size_t)max_ctas * p->info.n_params_mlp * 4);
 	w.loss_partials = (float*)b; b += align256((size_t)max_ctas * 4);
-	w.replicas = (__half*)b;
+	w.replicas = (__half*)b; b += align256(replica_bytes(p));
+	w.wide_hidden = w.wide_gtmp = w.wide_dy = nullptr;
+	if (is_wide(p)) {
+		const size_t layer = align256((size_t)p->info.n_hidden_layers * B * WIDE_W * 2);
+		w.wide_hidden = (__half*)b; b += layer;
+		w.wide_gtmp = (__half*)b; b += layer;
+		w.wide_dy = (__half*)b;
+	}
 	return w;
 }
 extern "C" size_t tcnn_b200_workspace_bytes(const tcnn_b200_plan* plan, uint32_t B) {
 	if (!plan) return 0;
 	const size_t act = align256((size_t)B * plan->info.encoded_width * 2);
 	const uint32_t max_ctas = (uint32_t)plan->n_sms * 4;
-	return 2 * act + align256((size_t)max_ctas * plan->info.n_params_mlp * 4) + align256((size_t)max_ctas * 4) + align256(replica_bytes(plan)) + 256;
+	const size_t wide = is_wide(plan) ? 2 * align256((size_t)plan->info.n_hidden_layers * B * WIDE_W * 2) + align256((size_t)B * MLP_OUT * 2) : 0;
+	return 2 * act + align256((size_t)max_ctas * plan->info.n_params_mlp * 4) + align256((size_t)max_ctas * 4) + align256(replica_bytes(plan)) + wide + 256;
 }
 
 static void check_batch(uint32_t B) {
@@ -476,11 +522,12 @@ static void encode_backward(const tcnn_b200_plan* plan, cudaStream_t stream, uin
 	backward_finish(plan, stream, gp, grid_grads, replicas);
 }
 
+static void encode_any(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t B, const float* x, const __half* grid, __half* encoded);
 extern "C" int tcnn_b200_encode_forward(const tcnn_b200_plan* plan, void* stream, uint32_t B, const float* x, const void* grid_params, void* encoded) {
 	API_BEGIN
 	require_device(plan); check_batch(B);
-	CHECK(x && grid_params && encoded, "null argument");
-	encode_forward(plan, (cudaStream_t)stream, B, x, (const __half*)grid_params, (__half*)encoded);
+	CHECK(x && encoded && (grid_params || plan->enc_kind != ENC_GRID), "null argument");
+	encode_any(plan, (cudaStream_t)stream, B, x, (const __half*)grid_params, (__half*)encoded); // OneBlob / Identity: grid_params unused
 	API_END
 }
 extern "C" int tcnn_b200_encode_backward(const tcnn_b200_plan* plan, void* stream, uint32_t B, const float* x, const void* dL_denc, void* grid_grads, int zero_first, void* workspace) {
@@ -532,8 +579,53 @@ static void launch_mlp_h(const tcnn_b200_plan* plan, cudaStream_t stream, const 
 	}
 	launch_mlp_k<MODE, H, FD, FF, 0>(plan, stream, a, grid, gp, smem);
 }
+// ---- 128 neurons: forward (+ loss) -> dgrad chain -> split-K weight gradients (mlp_wide_kernels.cuh) ----
+template <typename K>
+static void wide_set_smem(K kernel, uint32_t smem) {
+	CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+}
+template <int MODE>
+static void launch_mlp_wide(const tcnn_b200_plan* plan, cudaStream_t stream, const MlpArgs& a, uint32_t n_splits) {
+	constexpr bool train = MODE != MODE_INFER;
+	const uint32_t H = a.n_hidden, E = a.in_width;
+	WideArgs w{};
+	w.n_tiles = a.n_tiles; w.in_width = E; w.n_hidden = H; w.n_out = a.n_out; w.batch = (uint64_t)a.n_tiles * MLP_TILE;
+	w.input = a.input; w.params = a.params; w.output = a.output; w.output_f32 = a.output_f32; w.target = a.target;
+	w.hidden = a.wide_hidden; w.gtmp = a.wide_gtmp; w.dL_dinput = a.dL_dinput;
+	w.dL_doutput = MODE == MODE_TRAIN ? a.wide_dy : a.dL_doutput; w.dL_doutput_out = a.wide_dy;
+	w.dW_partials = a.dW_partials; w.loss_partials = a.loss_partials; w.n_mlp_params = a.n_mlp_params; w.n_splits = n_splits;
+	w.loss_type = a.loss_type; w.loss_scale = a.loss_scale; w.n_total = a.n_total;
+	if (train) CHECK(w.hidden && w.gtmp && w.dL_doutput, "the 128-neuron training / backward pass needs the workspace");
+	{
+		ProfileScope prof(plan, stream, PK_MLP);
+		const uint32_t nwg = wide_nwg_fwd(plan), grid = wide_fwd_ctas(plan, a.n_tiles), smem = wide_fwd_smem(H, E, nwg);
+		if (nwg == 2) { wide_set_smem(mlp_wide_forward_kernel<MODE, 2>, smem); mlp_wide_forward_kernel<MODE, 2><<<grid, 256, smem, stream>>>(w); }
+		else { wide_set_smem(mlp_wide_forward_kernel<MODE, 1>, smem); mlp_wide_forward_kernel<MODE, 1><<<grid, 128, smem, stream>>>(w); }
+		launch_check("mlp_wide_forward_kernel");
+	}
+	if constexpr (train) {
+		const bool want_dx = a.dL_dinput != nullptr;
+		{
+			ProfileScope prof(plan, stream, PK_MLP);
+			const uint32_t nwg = wide_nwg_bwd(plan, want_dx), smem = wide_bwd_smem(H, E, nwg, want_dx);
+			const uint32_t grid = std::max(1u, std::min((a.n_tiles + nwg - 1) / nwg, (uint32_t)plan->n_sms));
+			if (nwg == 2) { wide_set_smem(mlp_wide_backward_kernel<2>, smem); mlp_wide_backward_kernel<2><<<grid, 256, smem, stream>>>(w); }
+			else { wide_set_smem(mlp_wide_backward_kernel<1>, smem); mlp_wide_backward_kernel<1><<<grid, 128, smem, stream>>>(w); }
+			launch_check("mlp_wide_backward_kernel");
+		}
+		if (a.dW_partials) {
+			ProfileScope prof(plan, stream, PK_MLP);
+			CHECK(n_splits >= 1 && n_splits <= a.n_tiles, "bad weight-gradient split count");
+			wide_set_smem(mlp_wide_dw_kernel, WIDE_DW_SMEM);
+			mlp_wide_dw_kernel<<<dim3(n_splits, H + 1, 1), 128, WIDE_DW_SMEM, stream>>>(w);
+			launch_check("mlp_wide_dw_kernel");
+		}
+	}
+}
+
 template <int MODE>
 static void launch_mlp(const tcnn_b200_plan* plan, cudaStream_t stream, const MlpArgs& a, uint32_t grid) {
+	if (is_wide(plan)) { launch_mlp_wide<MODE>(plan, stream, a, grid); return; }
 	switch (a.n_hidden) {
 		case 1: launch_mlp_h<MODE, 1>(plan, stream, a, grid, plan->grid); break;
 		case 2: launch_mlp_h<MODE, 2>(plan, stream, a, grid, plan->grid); break;
@@ -545,7 +637,7 @@ static void launch_mlp(const tcnn_b200_plan* plan, cudaStream_t stream, const Ml
 // Training kernel with the hash-table gradient scatter fused into its last stage; instantiated for the common shapes.
 static bool fused_scatter_available(const tcnn_b200_plan* plan) {
 	const uint32_t D = plan->info.n_input_dims, F = plan->info.n_features_per_level;
-	return (D == 2 || D == 3) && (F == 2 || F == 4);
+	return !is_wide(plan) && plan->enc_kind == ENC_GRID && (D == 2 || D == 3) && (F == 2 || F == 4);
 }
 template <int H>
 static void launch_mlp_train_fused_h(const tcnn_b200_plan* plan, cudaStream_t stream, const MlpArgs& a, uint32_t grid, const GridParams& gp) {
@@ -566,8 +658,9 @@ static void launch_mlp_train_fused(const tcnn_b200_plan* plan, cudaStream_t stre
 	}
 }
 
-static MlpArgs base_mlp_args(const tcnn_b200_plan* plan, uint32_t B, const __half* input, const __half* params) {
+static MlpArgs base_mlp_args(const tcnn_b200_plan* plan, uint32_t B, const __half* input, const __half* params, const Workspace* w = nullptr) {
 	MlpArgs a{};
+	if (w) { a.wide_hidden = w->wide_hidden; a.wide_gtmp = w->wide_gtmp; a.wide_dy = w->wide_dy; }
 	a.n_tiles = B / MLP_TILE;
 	a.in_width = plan->info.encoded_width;
 	a.n_hidden = plan->info.n_hidden_layers;
@@ -588,10 +681,11 @@ static void mlp_infer(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t 
 	launch_mlp<MODE_INFER>(plan, stream, a, mlp_grid_size(plan, a.n_tiles, false));
 }
 
-static void mlp_finalize(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t n_parts, const Workspace& w, __half* grads, float* loss_out, bool with_loss) {
+static void mlp_finalize(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t n_parts, const Workspace& w, __half* grads, float* loss_out, bool with_loss, uint32_t n_tiles = 0) {
 	ProfileScope prof(plan, stream, PK_FINALIZE);
 	const uint32_t n = (uint32_t)plan->info.n_params_mlp;
-	mlp_finalize_kernel<<<(n + 31) / 32, 256, 0, stream>>>(n, n_parts, w.dw_partials, grads, with_loss ? w.loss_partials : nullptr, loss_out);
+	mlp_finalize_kernel<<<(n + 31) / 32, 256, 0, stream>>>(n, n_parts, w.dw_partials, grads, with_loss ? w.loss_partials : nullptr, loss_out,
+		mlp_loss_parts(plan, n_tiles, n_parts));
 	launch_check("mlp_finalize_kernel");
 }
 
@@ -612,7 +706,7 @@ extern "C" int tcnn_b200_mlp_backward(const tcnn_b200_plan* plan, void* stream_,
 	cudaStream_t stream = (cudaStream_t)stream_;
 	Workspace w{};
 	if (workspace) w = carve(plan, B, workspace);
-	MlpArgs a = base_mlp_args(plan, B, (const __half*)input, (const __half*)params);
+	MlpArgs a = base_mlp_args(plan, B, (const __half*)input, (const __half*)params, workspace ? &w : nullptr);
 	a.dL_doutput = (const __half*)dL_doutput;
 	a.dL_dinput = (__half*)dL_dinput;
 	a.dW_partials = dL_dparams ? w.dw_partials : nullptr;
@@ -632,8 +726,15 @@ static void encode_backward_input(const tcnn_b200_plan* plan, cudaStream_t strea
 
 // grid gather, or the Identity encoding of a stand-alone Network
 static void encode_any(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t B, const float* x, const __half* grid, __half* encoded) {
-	if (plan->kind != PLAN_NETWORK) { encode_forward(plan, stream, B, x, grid, encoded); return; }
+	if (plan->enc_kind == ENC_GRID) { encode_forward(plan, stream, B, x, grid, encoded); return; }
 	ProfileScope prof(plan, stream, PK_GRID_FWD);
+	if (plan->enc_kind == ENC_ONEBLOB) {
+		const uint32_t n_out = plan->grid.n_features, rows = (128 + n_out - 1) / n_out; // the reference's block shape (oneblob.h:118-121)
+		oneblob_encode_kernel<<<(B + rows - 1) / rows, dim3(n_out, rows, 1), 0, stream>>>(B, plan->info.n_input_dims, plan->oneblob_log2_bins, n_out,
+			plan->info.encoded_width, x, encoded);
+		launch_check("oneblob_encode_kernel");
+		return;
+	}
 	const uint32_t n = B * (plan->info.encoded_width / 8);
 	identity_encode_kernel<<<(n + 255) / 256, 256, 0, stream>>>(B, plan->info.n_input_dims, plan->info.encoded_width, x, encoded);
 	launch_check("identity_encode_kernel");
@@ -676,18 +777,24 @@ extern "C" int tcnn_b200_backward(const tcnn_b200_plan* plan, void* stream_, uin
 		if (dL_dinput) encode_backward_input(plan, stream, B, x, p, (const __half*)dL_doutput, dL_dinput);
 		return 0;
 	}
-	MlpArgs a = base_mlp_args(plan, B, w.encoded, p); // w.encoded was left by tcnn_b200_forward (the Context)
+	MlpArgs a = base_mlp_args(plan, B, w.encoded, p, &w); // w.encoded was left by tcnn_b200_forward (the Context)
 	a.dL_doutput = (const __half*)dL_doutput;
 	a.dL_dinput = w.dL_denc;
 	a.dW_partials = g ? w.dw_partials : nullptr;
 	const uint32_t grid = mlp_grid_size(plan, a.n_tiles, true);
 	launch_mlp<MODE_BACKWARD>(plan, stream, a, grid);
 	if (g) mlp_finalize(plan, stream, grid, w, g, nullptr, false);
-	if (plan->kind == PLAN_NETWORK) {
+	if (plan->enc_kind == ENC_IDENTITY) {
 		if (dL_dinput) {
 			const uint32_t n = B * plan->info.n_input_dims;
 			identity_backward_kernel<<<(n + 255) / 256, 256, 0, stream>>>(B, plan->info.n_input_dims, plan->info.encoded_width, w.dL_denc, dL_dinput);
 			launch_check("identity_backward_kernel");
+		}
+	} else if (plan->enc_kind == ENC_ONEBLOB) {
+		if (dL_dinput) {
+			const uint32_t n = B * plan->info.n_input_dims;
+			oneblob_backward_input_kernel<<<(n + 255) / 256, 256, 0, stream>>>(B, plan->info.n_input_dims, plan->oneblob_log2_bins, plan->info.encoded_width, x, w.dL_denc, dL_dinput);
+			launch_check("oneblob_backward_input_kernel");
 		}
 	} else {
 		if (g) encode_backward(plan, stream, B, x, w.dL_denc, g + plan->info.n_params_mlp, /*zero_first=*/1, w.replicas);
@@ -716,13 +823,20 @@ extern "C" int tcnn_b200_training_fwd_bwd(const tcnn_b200_plan* plan, void* stre
 	// shared carve-out doubles its time.
 	const uint32_t n_chunks = 1;
 	uint32_t part_off[1] = {0}, part_cnt[1] = {mlp_grid_size(plan, B / MLP_TILE, true)};
-	MlpArgs a = base_mlp_args(plan, B, w.encoded, p);
+	MlpArgs a = base_mlp_args(plan, B, w.encoded, p, &w);
 	a.target = target;
 	a.output = (__half*)output_fp16;
 	a.dL_dinput = w.dL_denc;
 	a.dW_partials = w.dw_partials;
 	a.loss_partials = w.loss_partials;
 	a.loss_scale = loss_scale;
+	if (plan->enc_kind != ENC_GRID) { // parameter-free encoding (OneBlob): no table gradients, dL/d(encoded) is not needed
+		encode_any(plan, main, B, x, nullptr, w.encoded);
+		a.dL_dinput = nullptr;
+		launch_mlp<MODE_TRAIN>(plan, main, a, part_cnt[0]);
+		mlp_finalize(plan, main, part_cnt[0], w, g, loss_out, loss_out != nullptr, B / MLP_TILE);
+		return 0;
+	}
 	backward_prepare(plan, main, gp, gg, zero_grid_grads, w.replicas);
 	encode_forward(plan, main, B, x, p + in.n_params_mlp, w.encoded);
 	if (fused_scatter_available(plan)) {
@@ -732,7 +846,7 @@ extern "C" int tcnn_b200_training_fwd_bwd(const tcnn_b200_plan* plan, void* stre
 		launch_mlp<MODE_TRAIN>(plan, main, a, part_cnt[0]);
 		backward_scatter(plan, main, gp, B, x, w.dL_denc, gg, w.replicas);
 	}
-	mlp_finalize(plan, main, part_off[n_chunks - 1] + part_cnt[n_chunks - 1], w, g, loss_out, loss_out != nullptr);
+	mlp_finalize(plan, main, part_off[n_chunks - 1] + part_cnt[n_chunks - 1], w, g, loss_out, loss_out != nullptr, B / MLP_TILE);
 	backward_finish(plan, main, gp, gg, w.replicas);
 	API_END
 }
@@ -820,9 +934,9 @@ extern "C" int tcnn_b200_training_step(const tcnn_b200_plan* plan, void* stream_
 	__half* gg = g + in.n_params_mlp;
 	const AdamBuffers ab{params_fp32, (__half*)params_fp16, g, first_moments, second_moments, param_steps};
 	const GridParams gp = backward_params(plan, B, true);
-	const uint32_t F = in.n_features_per_level, levels_per_chunk = 8 / F;
+	const uint32_t F = in.n_features_per_level, levels_per_chunk = F ? 8 / F : 0;
 
-	MlpArgs a = base_mlp_args(plan, B, w.encoded, p);
+	MlpArgs a = base_mlp_args(plan, B, w.encoded, p, &w);
 	a.target = target; a.output = (__half*)output_fp16; a.dL_dinput = w.dL_denc;
 	a.dW_partials = w.dw_partials; a.loss_partials = w.loss_partials; a.loss_scale = loss_scale;
 	const uint32_t mlp_grid = mlp_grid_size(plan, B / MLP_TILE, true);
@@ -839,7 +953,7 @@ extern "C" int tcnn_b200_training_step(const tcnn_b200_plan* plan, void* stream_
 			ProfileScope prof(plan, aux, PK_FINALIZE);
 			const AdamArgs am = adam_args(plan, loss_scale, adam_step_count, ab, 1, 0u, (uint32_t)in.n_params_mlp);
 			mlp_finalize_adam_kernel<<<((uint32_t)in.n_params_mlp + 31) / 32, 256, 0, aux>>>((uint32_t)in.n_params_mlp, mlp_grid, w.dw_partials,
-				loss_out ? w.loss_partials : nullptr, loss_out, am);
+				loss_out ? w.loss_partials : nullptr, loss_out, am, mlp_grid);
 			launch_check("mlp_finalize_adam_kernel");
 		}
 		CUDA_OK(cudaEventRecord(ev[1], aux));
@@ -848,12 +962,23 @@ extern "C" int tcnn_b200_training_step(const tcnn_b200_plan* plan, void* stream_
 		CUDA_OK(cudaStreamWaitEvent(main, ev[1], 0)); // join
 		return 0;
 	}
+	if (plan->enc_kind != ENC_GRID) { // parameter-free encoding: encode -> MLP forward/backward -> weight-gradient reduction + Adam in one kernel
+		encode_any(plan, main, B, x, nullptr, w.encoded);
+		a.dL_dinput = nullptr;
+		launch_mlp<MODE_TRAIN>(plan, main, a, mlp_grid);
+		ProfileScope prof(plan, main, PK_FINALIZE);
+		const AdamArgs am = adam_args(plan, loss_scale, adam_step_count, ab, 1, 0u, (uint32_t)in.n_params_mlp);
+		mlp_finalize_adam_kernel<<<((uint32_t)in.n_params_mlp + 31) / 32, 256, 0, main>>>((uint32_t)in.n_params_mlp, mlp_grid, w.dw_partials,
+			loss_out ? w.loss_partials : nullptr, loss_out, am, mlp_loss_parts(plan, B / MLP_TILE, mlp_grid));
+		launch_check("mlp_finalize_adam_kernel");
+		return 0;
+	}
 	backward_prepare(plan, main, gp, gg, /*zero_first=*/0, w.replicas);
 	encode_forward(plan, main, B, x, p + in.n_params_mlp, w.encoded);
 	launch_mlp<MODE_TRAIN>(plan, main, a, mlp_grid);
 	CUDA_OK(cudaEventRecord(ev[0], main));
 	CUDA_OK(cudaStreamWaitEvent(aux, ev[0], 0));
-	mlp_finalize(plan, aux, mlp_grid, w, g, loss_out, loss_out != nullptr); // under the scatter
+	mlp_finalize(plan, aux, mlp_grid, w, g, loss_out, loss_out != nullptr, B / MLP_TILE); // under the scatter
 
 	// level groups: up to 4, finest first
 	const uint32_t n_chunks = n_grad_chunks(plan);
@@ -903,6 +1028,7 @@ extern "C" int tcnn_b200_training_step_dp(const tcnn_b200_plan* plan, void* stre
 	CHECK(comm->epoch >= 1, "epoch starts at 1 and grows by one per call");
 	const tcnn_b200_info& in = plan->info;
 	CHECK(in.n_params % 4 == 0, "parameter count must be a multiple of 4");
+	CHECK(plan->enc_kind == ENC_GRID, "the data-parallel step is built for the grid encoding (a parameter-free encoding has ~100 KB of gradients: all-reduce them)");
 	DpComm c{};
 	c.rank = comm->rank; c.world = comm->world_size; c.epoch = comm->epoch;
 	for (uint32_t r = 0; r < c.world; ++r) {
@@ -923,7 +1049,7 @@ extern "C" int tcnn_b200_training_step_dp(const tcnn_b200_plan* plan, void* stre
 	__half* g = c.peer_grads[c.rank];
 	__half* gg = g + in.n_params_mlp;
 	const GridParams gp = backward_params(plan, B, true);
-	MlpArgs a = base_mlp_args(plan, B, w.encoded, p);
+	MlpArgs a = base_mlp_args(plan, B, w.encoded, p, &w);
 	a.target = target; a.output = (__half*)output_fp16; a.dL_dinput = w.dL_denc;
 	a.dW_partials = w.dw_partials; a.loss_partials = w.loss_partials; a.loss_scale = loss_scale;
 	const uint32_t mlp_grid = mlp_grid_size(plan, B / MLP_TILE, true);
@@ -935,13 +1061,13 @@ extern "C" int tcnn_b200_training_step_dp(const tcnn_b200_plan* plan, void* stre
 		launch_mlp_train_fused(plan, main, a, mlp_grid, gp);
 		CUDA_OK(cudaEventRecord(ev[0], main));
 		CUDA_OK(cudaStreamWaitEvent(aux, ev[0], 0));
-		mlp_finalize(plan, aux, mlp_grid, w, g, loss_out, loss_out != nullptr); // beside the replica reduction
+		mlp_finalize(plan, aux, mlp_grid, w, g, loss_out, loss_out != nullptr, B / MLP_TILE); // beside the replica reduction
 		CUDA_OK(cudaEventRecord(ev[1], aux));
 		backward_finish(plan, main, gp, gg, w.replicas);
 		CUDA_OK(cudaStreamWaitEvent(main, ev[1], 0));
 	} else {
 		launch_mlp<MODE_TRAIN>(plan, main, a, mlp_grid);
-		mlp_finalize(plan, main, mlp_grid, w, g, loss_out, loss_out != nullptr);
+		mlp_finalize(plan, main, mlp_grid, w, g, loss_out, loss_out != nullptr, B / MLP_TILE);
 		backward_scatter(plan, main, gp, B, x, w.dL_denc, gg, w.replicas);
 		backward_finish(plan, main, gp, gg, w.replicas);
 	}
