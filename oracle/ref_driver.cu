@@ -60,7 +60,7 @@ __global__ void synth_target(uint32_t n, uint32_t n_in, uint32_t n_out, const fl
 // Indices as the reference's own device functions compute them (common_device.h:690-718, 825-868).
 template <uint32_t D>
 __global__ void dump_indices(uint32_t n, uint32_t n_levels, const uint32_t* __restrict__ hashmap_sizes, uint32_t base_resolution,
-	float log2_per_level_scale, const float* __restrict__ x, uint32_t* __restrict__ idx_out, float* __restrict__ scale_out, uint32_t* __restrict__ res_out) {
+	float log2_per_level_scale, const float* __restrict__ x, uint32_t* __restrict__ idx_out, float* __restrict__ scale_out, uint32_t* __restrict__ res_out, GridType grid_type) {
 	const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
 	const uint32_t level = blockIdx.y;
 	if (i >= n) return;
@@ -73,7 +73,7 @@ __global__ void dump_indices(uint32_t n, uint32_t n_levels, const uint32_t* __re
 	for (uint32_t c = 0; c < (1u << D); ++c) {
 		uvec<D> p;
 		for (uint32_t d = 0; d < D; ++d) p[d] = pos_grid[d] + ((c >> d) & 1u);
-		idx_out[((size_t)level * n + i) * (1u << D) + c] = grid_index<D, HashType::CoherentPrime>(GridType::Hash, hashmap_sizes[level], resolution, p);
+		idx_out[((size_t)level * n + i) * (1u << D) + c] = grid_index<D, HashType::CoherentPrime>(grid_type, hashmap_sizes[level], resolution, p);
 	}
 }
 
@@ -86,6 +86,15 @@ struct LevelTable { std::vector<uint32_t> offsets, sizes; };
 
 // Per-level entry counts as the reference's constructor derives them (encodings/grid.h:692-716),
 // evaluated with the reference's own host-callable grid_scale/grid_resolution.
+static GridType grid_type_of(const json& enc) {
+	std::string o = enc.value("otype", std::string("Grid")), t = enc.value("type", std::string("Hash"));
+	for (auto& c : o) c = (char)std::tolower(c);
+	for (auto& c : t) c = (char)std::tolower(c);
+	if (o == "densegrid" || (o != "tiledgrid" && t == "dense")) return GridType::Dense;
+	if (o == "tiledgrid" || t == "tiled") return GridType::Tiled;
+	return GridType::Hash;
+}
+
 static LevelTable level_table(const json& enc, uint32_t n_in) {
 	const uint32_t L = enc.value("n_levels", 16u), log2T = enc.value("log2_hashmap_size", 19u), base = enc.value("base_resolution", 16u);
 	const float pls = enc.value("per_level_scale", 2.0f);
@@ -94,7 +103,10 @@ static LevelTable level_table(const json& enc, uint32_t n_in) {
 		const uint32_t res = grid_resolution(grid_scale(l, std::log2(pls), base));
 		const uint32_t max_params = std::numeric_limits<uint32_t>::max() / 2;
 		uint32_t n = std::pow((float)res, (float)n_in) > (float)max_params ? max_params : powi(res, n_in);
-		n = std::min(next_multiple(n, 8u), 1u << log2T);
+		n = next_multiple(n, 8u);
+		const GridType gt = grid_type_of(enc);
+		if (gt == GridType::Hash) n = std::min(n, 1u << log2T);
+		else if (gt == GridType::Tiled) n = std::min(n, powi(base, n_in));
 		t.offsets.push_back(off); t.sizes.push_back(n); off += n;
 	}
 	t.offsets.push_back(off);
@@ -128,7 +140,7 @@ static int mode_dump(int argc, char** argv) {
 	json enc = cfg.value("encoding", json::object());
 	std::string enc_otype = enc.value("otype", std::string("Identity"));
 	for (auto& c : enc_otype) c = (char)std::tolower(c);
-	const bool is_grid = enc_otype == "hashgrid" || enc_otype == "grid";
+	const bool is_grid = enc_otype == "hashgrid" || enc_otype == "grid" || enc_otype == "densegrid" || enc_otype == "tiledgrid";
 	if (is_grid) {
 		LevelTable lt = level_table(enc, n_in);
 		const uint32_t L = (uint32_t)lt.sizes.size();
@@ -139,8 +151,8 @@ static int mode_dump(int argc, char** argv) {
 		const dim3 blocks{div_round_up(B, 256u), L, 1};
 		const float l2s = std::log2(enc.value("per_level_scale", 2.0f));
 		const uint32_t base = enc.value("base_resolution", 16u);
-		if (n_in == 2) dump_indices<2><<<blocks, 256, 0, stream>>>(B, L, d_sizes.data(), base, l2s, input.data(), d_idx.data(), d_scale.data(), d_res.data());
-		else if (n_in == 3) dump_indices<3><<<blocks, 256, 0, stream>>>(B, L, d_sizes.data(), base, l2s, input.data(), d_idx.data(), d_scale.data(), d_res.data());
+		if (n_in == 2) dump_indices<2><<<blocks, 256, 0, stream>>>(B, L, d_sizes.data(), base, l2s, input.data(), d_idx.data(), d_scale.data(), d_res.data(), grid_type_of(enc));
+		else if (n_in == 3) dump_indices<3><<<blocks, 256, 0, stream>>>(B, L, d_sizes.data(), base, l2s, input.data(), d_idx.data(), d_scale.data(), d_res.data(), grid_type_of(enc));
 		else { std::cerr << "dump: n_in must be 2 or 3\n"; return 2; }
 		CUDA_CHECK_THROW(cudaStreamSynchronize(stream));
 		write_dev(out + "/indices.u32", d_idx.data(), d_idx.size());

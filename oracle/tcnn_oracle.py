@@ -176,6 +176,8 @@ class GridConfig:
     per_level_scale: float = 2.0
     # optional per-level (scale, resolution) table dumped from the device (CUDA exp2f vs libm)
     scales: np.ndarray | None = None
+    grid_type: str = "Hash"           # Hash | Dense | Tiled (grid.h:702-712; DenseGrid / TiledGrid otypes, grid.h:1180-1208)
+    interpolation: str = "Linear"     # Linear | Smoothstep (common_device.h:801-807)
     offsets: np.ndarray = field(init=False)
     resolutions: np.ndarray = field(init=False)
 
@@ -192,7 +194,13 @@ class GridConfig:
             res = int(self.resolutions[l])
             dense = max_params if float(F32(res) ** F32(self.n_dims)) > float(F32(max_params)) else (res ** self.n_dims) & 0xFFFFFFFF
             n = next_multiple(dense, 8)
-            n = min(n, 1 << self.log2_hashmap_size)
+            gt = self.grid_type.lower()
+            if gt == "hash":
+                n = min(n, 1 << self.log2_hashmap_size)
+            elif gt == "tiled":
+                n = min(n, self.base_resolution ** self.n_dims)
+            else:
+                assert gt == "dense", self.grid_type
             offs.append(off)
             off += n
         offs.append(off)
@@ -209,6 +217,26 @@ class GridConfig:
     def level_size(self, l: int) -> int:
         return int(self.offsets[l + 1]) - int(self.offsets[l])
 
+    @property
+    def hashed(self) -> bool:
+        return self.grid_type.lower() == "hash"
+
+    @property
+    def smooth(self) -> bool:
+        return self.interpolation.lower() == "smoothstep"
+
+
+def smoothstep(v: np.ndarray) -> np.ndarray:
+    """common_device.h:801-803, fp32."""
+    v = v.astype(np.float32)
+    return (v * v * (F32(3.0) - F32(2.0) * v)).astype(np.float32)
+
+
+def smoothstep_derivative(v: np.ndarray) -> np.ndarray:
+    """common_device.h:805-807."""
+    v = v.astype(np.float32)
+    return (F32(6.0) * v * (F32(1.0) - v)).astype(np.float32)
+
 
 def pos_fract(x: np.ndarray, scale: np.float32):
     """common_device.h:857-868: pos = fmaf(scale, x, 0.5f); cell = (uint32)(int)floorf(pos); frac = pos - floorf(pos)."""
@@ -221,7 +249,7 @@ def pos_fract(x: np.ndarray, scale: np.float32):
     return frac, cell
 
 
-def grid_index(pos_grid: np.ndarray, hashmap_size: int, resolution: int) -> np.ndarray:
+def grid_index(pos_grid: np.ndarray, hashmap_size: int, resolution: int, hashed: bool = True) -> np.ndarray:
     """common_device.h:690-707 for GridType::Hash + CoherentPrime, including the uint32 stride wrap (SURVEY F6).
 
     pos_grid: uint32 [..., D] -> uint32 [...]."""
@@ -233,7 +261,7 @@ def grid_index(pos_grid: np.ndarray, hashmap_size: int, resolution: int) -> np.n
             break
         index = (index + pos_grid[..., d].astype(np.uint64) * np.uint64(stride)) & np.uint64(0xFFFFFFFF)
         stride = (stride * resolution) & 0xFFFFFFFF
-    if hashmap_size < stride:
+    if hashed and hashmap_size < stride:
         h = np.zeros(pos_grid.shape[:-1], dtype=np.uint64)
         for d in range(D):
             h ^= (pos_grid[..., d].astype(np.uint64) * COHERENT_PRIMES[d]) & np.uint64(0xFFFFFFFF)
@@ -248,6 +276,8 @@ def grid_corners(cfg: GridConfig, x: np.ndarray, level: int):
     multiplied in dim order starting from 1.0f.   x: fp32 [B, D] -> (uint32 [B, 2^D], fp32 [B, 2^D])."""
     D = cfg.n_dims
     frac, cell = pos_fract(x, cfg.scales[level])
+    if cfg.smooth:
+        frac = smoothstep(frac)
     B = x.shape[0]
     idx = np.empty((B, 1 << D), dtype=np.uint32)
     w = np.empty((B, 1 << D), dtype=np.float32)
@@ -262,7 +292,7 @@ def grid_corners(cfg: GridConfig, x: np.ndarray, level: int):
             else:
                 weight = (weight * (F32(1) - frac[:, d])).astype(np.float32)
                 pg[:, d] = cell[:, d]
-        idx[:, c] = grid_index(pg, hs, res)
+        idx[:, c] = grid_index(pg, hs, res, cfg.hashed)
         w[:, c] = weight
     return idx, w
 
@@ -331,6 +361,9 @@ def grid_backward_input(cfg: GridConfig, x: np.ndarray, table: np.ndarray, dy: n
     for l in range(cfg.n_levels):
         scale, res = F32(cfg.scales[l]), int(cfg.resolutions[l])
         frac, cell = pos_fract(x, F32(scale))
+        dfrac = smoothstep_derivative(frac) if cfg.smooth else np.ones_like(frac)  # pos_derivative (grid.h:100-113)
+        if cfg.smooth:
+            frac = smoothstep(frac)
         size, base = cfg.level_size(l), int(cfg.offsets[l])
         grads = np.zeros((B, F, D), np.float32)
         for gd in range(D):
@@ -344,10 +377,10 @@ def grid_backward_input(cfg: GridConfig, x: np.ndarray, table: np.ndarray, dy: n
                     else:
                         weight = (weight * frac[:, dim]).astype(np.float32); pg[:, dim] = cell[:, dim] + np.uint32(1)
                 pg[:, gd] = cell[:, gd]
-                vl = t[base + grid_index(pg, size, res).astype(np.int64)].astype(np.float32)
+                vl = t[base + grid_index(pg, size, res, cfg.hashed).astype(np.int64)].astype(np.float32)
                 pg[:, gd] = cell[:, gd] + np.uint32(1)
-                vr = t[base + grid_index(pg, size, res).astype(np.int64)].astype(np.float32)
-                grads[:, :, gd] = (grads[:, :, gd] + weight[:, None] * (vr - vl)).astype(np.float32)
+                vr = t[base + grid_index(pg, size, res, cfg.hashed).astype(np.int64)].astype(np.float32)
+                grads[:, :, gd] = (grads[:, :, gd] + (weight[:, None] * (vr - vl)).astype(np.float32) * dfrac[:, gd, None]).astype(np.float32)
         for f in range(F):
             dl = dy[:, l * F + f].astype(np.float32)
             result = (result + dl[:, None] * grads[:, f, :]).astype(np.float32)

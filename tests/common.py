@@ -28,6 +28,18 @@ CONFIG_F4 = {  # F = 4, small table, 3 hidden layers: exercises the other templa
     "network": {"otype": "FullyFusedMLP", "activation": "ReLU", "output_activation": "None", "n_neurons": 64, "n_hidden_layers": 3},
 }
 
+CONFIG_TILED_SMOOTH = {  # TiledGrid + Smoothstep interpolation (grid.h:702-712, common_device.h:801-807), 2-D
+    "loss": {"otype": "L2"},
+    "optimizer": {"otype": "Adam", "learning_rate": 1e-3},
+    "encoding": {"otype": "TiledGrid", "n_levels": 8, "n_features_per_level": 2, "base_resolution": 16, "per_level_scale": 1.5, "interpolation": "Smoothstep"},
+    "network": {"otype": "FullyFusedMLP", "activation": "ReLU", "output_activation": "None", "n_neurons": 64, "n_hidden_layers": 2},
+}
+CONFIG_DENSE = {  # DenseGrid, Linear, 3-D, F = 4
+    "loss": {"otype": "L2"},
+    "optimizer": {"otype": "Adam", "learning_rate": 1e-3},
+    "encoding": {"otype": "DenseGrid", "n_levels": 4, "n_features_per_level": 4, "base_resolution": 8, "per_level_scale": 1.6},
+    "network": {"otype": "FullyFusedMLP", "activation": "ReLU", "output_activation": "None", "n_neurons": 64, "n_hidden_layers": 2},
+}
 CONFIG_ONEBLOB = {  # BASELINE.json configs[1]: data/config_oneblob.json of the reference (bench_ours.cu), 2-D input -> 128 features
     "loss": {"otype": "RelativeL2"},
     "optimizer": {"otype": "Adam", "learning_rate": 1e-2, "beta1": 0.9, "beta2": 0.99, "epsilon": 1e-8, "l2_reg": 1e-8},
@@ -64,8 +76,11 @@ def oracle_configs(cfg, n_in, n_out, scales=None):
     if is_oneblob(cfg):  # no table: g is None, the MLP input is the padded OneBlob width
         m = O.MlpConfig(O.next_multiple(n_in * e.get("n_bins", 16), 16), n_out, n.get("n_neurons", 128), n.get("n_hidden_layers", 5))
         return None, m
+    otype = e.get("otype", "Grid").lower()
+    gtype = "Dense" if otype == "densegrid" else "Tiled" if otype == "tiledgrid" else e.get("type", "Hash")
     g = O.GridConfig(n_in, e.get("n_levels", 16), e.get("n_features_per_level", 2), e.get("log2_hashmap_size", 19),
-                     e.get("base_resolution", 16), e.get("per_level_scale", 2.0), scales=scales)
+                     e.get("base_resolution", 16), e.get("per_level_scale", 2.0), scales=scales, grid_type=gtype,
+                     interpolation=e.get("interpolation", "Linear"))
     n = cfg["network"]
     m = O.MlpConfig(O.next_multiple(g.n_features, 16), n_out, n.get("n_neurons", 128), n.get("n_hidden_layers", 5))
     return g, m

@@ -1,0 +1,314 @@
+"""GPU parity tests of the 128-neuron FullyFusedMLP kernels (mlp_wide_kernels.cuh) and the OneBlob encoding through the
+C ABI: against the numpy oracle on seeded inputs and against the reference's own CUDA build (tests/golden/wide_*.npz,
+oneblob*.npz).  BASELINE configs #2 (OneBlob + 128 x 5), #4 (F = 4 grid + 128 x 4), #5 (grid + 128 x 3) with fixture-sized
+tables; the full-size table configs run in test_full_size_* below through size-independent properties.
+
+Tolerances: north_star's 1e-2 relative L2 on outputs / gradients is met against the ORACLE (same fp32 accumulation) with a
+wide margin (<= 2e-3).  Against the reference dump the bar is 2e-2 on the outputs: the reference accumulates 128-deep dot
+products in fp16, and emulating that in the oracle reproduces its outputs to 2e-3 (tests/test_oracle_golden.py)."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+from oracle import tcnn_oracle as O  # noqa: E402
+from tests import common  # noqa: E402
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+CASES = {
+    "tiled_smooth_2d": (common.CONFIG_TILED_SMOOTH, 2, 3),
+    "dense_3d_f4": (common.CONFIG_DENSE, 3, 3),
+    "wide_dp_3d_T15": (common.CONFIG_WIDE_DP, 3, 3),
+    "wide_f4_3d_T14": (common.CONFIG_WIDE_F4, 3, 4),
+    "oneblob_2d_128x5": (common.CONFIG_ONEBLOB, 2, 3),
+    "oneblob16_2d_64x4": (common.CONFIG_ONEBLOB16, 2, 3),
+}
+
+
+@pytest.fixture(scope="module")
+def dev():
+    if not torch.cuda.is_available():
+        pytest.fail("no CUDA device: the gpu-marked tests need a B200 (there is no CPU fallback)")
+    return torch.device("cuda:0")
+
+
+def S():
+    from tinycudann import _lib
+    return _lib.C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class Ctx:
+    def __init__(self, name, dev):
+        import tinycudann as tcnn
+        self.name = name
+        self.cfg, self.n_in, self.n_out = CASES[name]
+        self.native = tcnn.NativeModule(self.n_in, self.n_out, self.cfg)
+        self.info, self.lib = self.native.info, self.native.lib
+        L = self.info.n_levels
+        self.g, self.m = common.oracle_configs(self.cfg, self.n_in, self.n_out, scales=np.array(self.info.level_scale[:L], dtype=np.float32) if L else None)
+        self.golden = np.load(os.path.join(GOLDEN, name + ".npz"))
+        self.dev = dev
+
+    def params16(self, rng=None):
+        p = O.init_params(self.m, self.g, 1337, True)
+        if rng is not None and self.g is not None:  # table values large enough for the features to matter
+            p[self.m.n_params:] = rng.uniform(-0.5, 0.5, p.size - self.m.n_params).astype(np.float32)
+        return p.astype(np.float16)
+
+
+@pytest.fixture(scope="module", params=sorted(CASES))
+def ctx(request, dev):
+    return Ctx(request.param, dev)
+
+
+def _per_matrix(m, got, ref, bar, what):
+    pos = 0
+    for (r, c) in m.shapes():
+        e = common.rel_l2(got[pos:pos + r * c], ref[pos:pos + r * c])
+        assert e < bar, f"{what} {r}x{c}: {e}"
+        pos += r * c
+
+
+def test_plan_and_init(ctx):
+    z = ctx.golden
+    assert ctx.info.n_params == int(z["n_params"]) and ctx.info.n_params_mlp == ctx.m.n_params
+    p = ctx.native.initial_params(1337, ctx.dev, trainer_seeding=True).cpu().numpy()
+    assert np.array_equal(p[: ctx.m.n_params], z["params_init_mlp"])
+    assert np.array_equal(p[::997], z["params_init_sample"])
+
+
+def test_encoding_vs_reference(ctx):
+    """encoded batch [B][E] of the encoding kernel in front of the MLP against the reference dump: grid bit-exact, OneBlob
+    <= 1e-3 of the largest feature (north_star: encoded features <= 1e-3 relative)."""
+    from tinycudann._lib import check, ptr
+    z = ctx.golden
+    B = int(z["B"])
+    x_np, _ = common.synth_inputs(B, ctx.n_in, ctx.n_out, seed=1)
+    p16 = ctx.params16()
+    x = torch.from_numpy(x_np).to(ctx.dev)
+    table = torch.from_numpy(p16[ctx.m.n_params:]).to(ctx.dev) if ctx.g is not None else None
+    enc = torch.zeros(B, ctx.info.encoded_width, dtype=torch.half, device=ctx.dev)
+    check(ctx.lib.tcnn_b200_encode_forward(ctx.native.handle, S(), B, ptr(x), ptr(table), ptr(enc)))
+    got, ref = enc.cpu().numpy(), z["encoded_soa"].T
+    if ctx.g is not None:
+        nf = ctx.g.n_features
+        assert np.array_equal(got[:, :nf].view(np.uint16), ref[:, :nf].view(np.uint16))
+    else:
+        d = np.abs(got.astype(np.float32) - ref.astype(np.float32))
+        assert d.max() <= 1e-3 * np.abs(ref.astype(np.float32)).max(), d.max()
+        assert np.array_equal(got, common.oracle_encode(ctx.cfg, None, ctx.m, x_np, None)) or np.count_nonzero(d) < 5e-3 * d.size
+
+
+def test_grid_indices_and_level_table_vs_reference(ctx):
+    """Dense / Tiled / Hash index function through the reference's own __device__ grid_index (bit-exact)."""
+    if ctx.g is None:
+        pytest.skip("no grid")
+    from tinycudann._lib import check, ptr
+    z = ctx.golden
+    B, L, NC = int(z["B"]), ctx.info.n_levels, 1 << ctx.n_in
+    assert np.array_equal(np.array(ctx.info.level_resolution[:L], dtype=np.uint32), z["level_res"])
+    assert np.array_equal(np.diff(np.array(ctx.info.level_offset[: L + 1], dtype=np.int64)), z["level_size"])
+    x_np, _ = common.synth_inputs(B, ctx.n_in, ctx.n_out, seed=1)
+    x = torch.from_numpy(x_np).to(ctx.dev)
+    out = torch.empty(L * B * NC, dtype=torch.int32, device=ctx.dev)
+    check(ctx.lib.tcnn_b200_grid_indices(ctx.native.handle, S(), B, ptr(x), ptr(out)))
+    got = out.cpu().numpy().view(np.uint32).reshape(L, B, NC)
+    assert np.array_equal(got, z["indices"])
+    for l in range(L):
+        assert np.array_equal(got[l], O.grid_corners(ctx.g, x_np, l)[0])
+
+
+def test_grid_input_gradient_vs_oracle(ctx):
+    """dL/dx of the encoding (Smoothstep: with the derivative of the interpolation weight, grid.h:171-211)."""
+    if ctx.g is None:
+        pytest.skip("no grid")
+    import tinycudann as tcnn
+    from tinycudann._lib import check, ptr
+    B = 512
+    rng = np.random.default_rng(21)
+    enc_mod = tcnn.NativeModule(ctx.n_in, 0, {"encoding": ctx.cfg["encoding"]})
+    x_np, _ = common.synth_inputs(B, ctx.n_in, ctx.n_out, seed=8)
+    table_np = rng.uniform(-0.5, 0.5, ctx.g.n_params).astype(np.float16)
+    W = enc_mod.info.encoded_width
+    dy_np = np.zeros((B, W), np.float16)
+    dy_np[:, : ctx.g.n_features] = (rng.standard_normal((B, ctx.g.n_features)) * 0.1).astype(np.float16)
+    x, table, dy = (torch.from_numpy(a).to(ctx.dev) for a in (x_np, table_np, dy_np))
+    ws = enc_mod.workspace(B, ctx.dev)
+    dx = torch.zeros(B, ctx.n_in, dtype=torch.float32, device=ctx.dev)
+    gt = torch.zeros(ctx.g.n_params, dtype=torch.half, device=ctx.dev)
+    check(enc_mod.lib.tcnn_b200_backward(enc_mod.handle, S(), B, ptr(x), ptr(table), ptr(dy), ptr(gt), ptr(dx), ptr(ws)))
+    ref = O.grid_backward_input(ctx.g, x_np, table_np, dy_np)
+    assert common.rel_l2(dx.cpu().numpy(), ref) < 1e-4
+    gref = O.grid_backward(ctx.g, x_np, dy_np[:, : ctx.g.n_features])
+    assert common.rel_l2(gt.cpu().numpy().astype(np.float64), gref) < 1e-2
+
+
+@pytest.mark.parametrize("B", [256, 1024, 1 << 15])
+def test_mlp_forward_backward_vs_oracle(ctx, B):
+    """B = 256: fewer tiles than warpgroups; 2^15: several tiles per warpgroup and per weight-gradient split."""
+    from tinycudann._lib import check, ptr
+    rng = np.random.default_rng(11)
+    p16_np = ctx.params16(rng)
+    for seed in range(4, 40):
+        # A hidden activation within fp32 rounding of zero flips its ReLU mask between two correct implementations and with it
+        # a whole gradient element (one flip in 256 x 128 x 5 moves dx by 5e-3 between a float32 and a float64 run of the
+        # oracle itself): the small batches use the first seeded batch without such a borderline activation.
+        x_np, _ = common.synth_inputs(B, ctx.n_in, ctx.n_out, seed=seed)
+        enc_np = common.oracle_encode(ctx.cfg, ctx.g, ctx.m, x_np, p16_np[ctx.m.n_params:])
+        if B > 1024 or not any(((h > 0) & (h < 1e-4)).any() for h in O.mlp_forward(ctx.m, p16_np[: ctx.m.n_params], enc_np)[1]):
+            break
+    enc, p16 = torch.from_numpy(enc_np).to(ctx.dev), torch.from_numpy(p16_np).to(ctx.dev)
+    out = torch.zeros(B, 16, dtype=torch.half, device=ctx.dev)
+    check(ctx.lib.tcnn_b200_mlp_forward(ctx.native.handle, S(), B, ptr(enc), ptr(p16), ptr(out)))
+    y, hidden = O.mlp_forward(ctx.m, p16_np[: ctx.m.n_params], enc_np)
+    assert common.rel_l2(out.cpu().numpy(), y) < 1e-3
+    dy_np = (rng.standard_normal((B, 16)) * 0.1).astype(np.float16)  # keeps the chain's gradients out of the fp16 subnormal range
+    dy_np[:, ctx.n_out:] = 0
+    dy = torch.from_numpy(dy_np).to(ctx.dev)
+    ws = ctx.native.workspace(B, ctx.dev)
+    gp = torch.zeros(ctx.m.n_params, dtype=torch.half, device=ctx.dev)
+    dx = torch.zeros(B, ctx.info.encoded_width, dtype=torch.half, device=ctx.dev)
+    check(ctx.lib.tcnn_b200_mlp_backward(ctx.native.handle, S(), B, ptr(enc), ptr(p16), ptr(dy), ptr(gp), ptr(dx), ptr(ws)))
+    dW, dx_ref = O.mlp_backward(ctx.m, p16_np[: ctx.m.n_params], enc_np, hidden, dy_np)
+    # A handful of ReLU-mask flips (pre-activations within fp32 rounding of zero: 8 of 25 M elements at B = 2^16 between a
+    # float32 and a float64 run of the ORACLE itself) carry a whole gradient element each: 1e-3 at large B is the oracle's
+    # own reproducibility, not kernel error.
+    bar = 2e-3 if B <= 1024 else 6e-3
+    assert common.rel_l2(dx.cpu().numpy(), dx_ref) < bar
+    _per_matrix(ctx.m, gp.cpu().numpy().astype(np.float64), dW, bar, "dW")
+
+
+def test_training_fwd_bwd_vs_oracle_and_reference(ctx):
+    from tinycudann._lib import check, ptr
+    z = ctx.golden
+    B = int(z["B"])
+    x_np, t_np = common.synth_inputs(B, ctx.n_in, ctx.n_out, seed=1)
+    p16_np = ctx.params16()  # the reference's initial parameters
+    x, t, p16 = (torch.from_numpy(a).to(ctx.dev) for a in (x_np, t_np, p16_np))
+    ws = ctx.native.workspace(B, ctx.dev)
+    grads = torch.zeros(ctx.info.n_params, dtype=torch.half, device=ctx.dev)
+    loss = torch.zeros(1, dtype=torch.float32, device=ctx.dev)
+    out = torch.zeros(B, 16, dtype=torch.half, device=ctx.dev)
+    check(ctx.lib.tcnn_b200_training_fwd_bwd(ctx.native.handle, S(), B, ptr(x), ptr(t), ptr(p16), ptr(grads), 128.0, 1, ptr(loss), ptr(out), ptr(ws)))
+    relative = ctx.info.loss_type == 1
+    enc = common.oracle_encode(ctx.cfg, ctx.g, ctx.m, x_np, p16_np[ctx.m.n_params:])
+    y, hidden = O.mlp_forward(ctx.m, p16_np[: ctx.m.n_params], enc)
+    lv, dy = O.loss_l2(y, t_np, ctx.n_out, relative=relative)
+    dW, dx = O.mlp_backward(ctx.m, p16_np[: ctx.m.n_params], enc, hidden, dy)
+    got = grads.cpu().numpy().astype(np.float64)
+    # oracle (same arithmetic)
+    assert abs(loss.item() - lv) <= 2e-4 * abs(lv)
+    assert common.rel_l2(out.cpu().numpy(), y) < 1e-3
+    _per_matrix(ctx.m, got[: ctx.m.n_params], dW, 3e-3, "dW vs oracle")
+    if ctx.g is not None:
+        gg = O.grid_backward(ctx.g, x_np, dx[:, : ctx.g.n_features]).reshape(-1)
+        assert common.rel_l2(got[ctx.m.n_params:], gg) < 1e-2
+    # reference dump (fp16 accumulation on its side)
+    assert common.rel_l2(out.cpu().numpy()[:, : ctx.n_out].astype(np.float32), z["output"]) < 2e-2
+    assert abs(loss.item() - float(z["loss"])) <= 2e-3 * float(z["loss"])
+    last = ctx.m.shapes()[-1][0] * ctx.m.shapes()[-1][1]
+    assert common.rel_l2(got[ctx.m.n_params - last: ctx.m.n_params], z["grads_mlp"][-last:].astype(np.float64)) < 1e-2
+
+
+def test_inference_fp32_output(ctx):
+    from tinycudann._lib import check, ptr
+    B = 512
+    rng = np.random.default_rng(2)
+    x_np, _ = common.synth_inputs(B, ctx.n_in, ctx.n_out, seed=9)
+    p16_np = ctx.params16(rng)
+    x, p16 = torch.from_numpy(x_np).to(ctx.dev), torch.from_numpy(p16_np).to(ctx.dev)
+    ws = ctx.native.workspace(B, ctx.dev)
+    o32 = torch.zeros(B, ctx.n_out, dtype=torch.float32, device=ctx.dev)
+    o16 = torch.zeros(B, 16, dtype=torch.half, device=ctx.dev)
+    check(ctx.lib.tcnn_b200_inference(ctx.native.handle, S(), B, ptr(x), ptr(p16), ptr(o16), ptr(o32), ptr(ws)))
+    y, _ = O.mlp_forward(ctx.m, p16_np[: ctx.m.n_params], common.oracle_encode(ctx.cfg, ctx.g, ctx.m, x_np, p16_np[ctx.m.n_params:]))
+    assert common.rel_l2(o16.cpu().numpy(), y) < 2e-3
+    assert np.array_equal(o32.cpu().numpy(), o16.cpu().numpy()[:, : ctx.n_out].astype(np.float32))  # trim_and_cast of the same values
+
+
+def test_trainer_converges_and_matches_unfused_step(ctx):
+    """Trainer.training_step (fused call) against forward/backward + separate Adam on the same batches: same parameters."""
+    import tinycudann as tcnn
+    B = 2048
+    a = tcnn.create_from_config(ctx.n_in, ctx.n_out, ctx.cfg, device=ctx.dev)
+    b = tcnn.create_from_config(ctx.n_in, ctx.n_out, ctx.cfg, device=ctx.dev)
+    b.trainer.use_fused_step = False
+    la = []
+    for i in range(40):
+        x_np, t_np = common.synth_inputs(B, ctx.n_in, ctx.n_out, seed=50 + i)
+        x, t = torch.from_numpy(x_np).to(ctx.dev), torch.from_numpy(t_np).to(ctx.dev)
+        a.trainer.training_step(x, t); b.trainer.training_step(x, t)
+        la.append(a.trainer.loss())
+    assert la[-1] < 0.6 * la[0]
+    pa, pb = a.trainer.params_full_precision.cpu().numpy(), b.trainer.params_full_precision.cpu().numpy()
+    n = ctx.m.n_params
+    assert common.rel_l2(pa[:n], pb[:n]) < 2e-3  # fp16 atomics of the grid scatter make runs differ in the last bits
+    assert abs(a.trainer.loss() - b.trainer.loss()) < 5e-2 * abs(b.trainer.loss())
+
+
+def test_module_autograd_surface(ctx):
+    """tcnn.NetworkWithInputEncoding forward/backward (bindings/torch/tinycudann/modules.py:176-192) with the new shapes."""
+    import tinycudann as tcnn
+    B = 512
+    net = tcnn.NetworkWithInputEncoding(ctx.n_in, ctx.n_out, ctx.cfg["encoding"], ctx.cfg["network"]).to(ctx.dev)
+    x_np, t_np = common.synth_inputs(B, ctx.n_in, ctx.n_out, seed=3)
+    x = torch.from_numpy(x_np).to(ctx.dev).requires_grad_(True)
+    y = net(x)
+    assert y.shape == (B, ctx.n_out) and y.dtype == torch.half
+    (y.float() ** 2).sum().backward()
+    assert net.params.grad is not None and torch.isfinite(net.params.grad).all()
+    assert x.grad is not None and torch.isfinite(x.grad).all()
+    if common.is_oneblob(ctx.cfg):  # dL/dx of the OneBlob encoding against the oracle restatement (checked against finite differences on CPU)
+        p16_np = net.params.detach().half().cpu().numpy()
+        enc = common.oracle_encode(ctx.cfg, None, ctx.m, x_np, None)
+        yo, hidden = O.mlp_forward(ctx.m, p16_np, enc)
+        dy = np.zeros((B, 16), np.float16)
+        dy[:, : ctx.n_out] = (2 * y.detach().float().cpu().numpy()).astype(np.float16)
+        _, dx = O.mlp_backward(ctx.m, p16_np, enc, hidden, dy)
+        ref = O.oneblob_backward_input(x_np, ctx.cfg["encoding"]["n_bins"], dx)
+        assert common.rel_l2(x.grad.cpu().numpy(), ref) < 3e-2
+
+
+def test_full_size_inference_is_position_independent(dev):
+    """BASELINE config #2 at batch 2^18: a sample's output does not depend on where in the batch it sits (bit-exact)."""
+    import tinycudann as tcnn
+    model = tcnn.create_from_config(2, 3, common.CONFIG_ONEBLOB, device=dev)
+    B = 1 << 18
+    x = torch.rand(B, 2, device=dev)
+    y = model.trainer.inference(x)
+    perm = torch.randperm(B, device=dev)
+    y2 = model.trainer.inference(x[perm].contiguous())
+    assert torch.equal(y[perm], y2)
+
+
+def test_full_size_weight_gradients_are_linear_in_dy(dev):
+    """Split-K weight gradients at 2^18 samples: dW(2 dy) == 2 dW(dy) up to fp16 rounding of the result, and the
+    batch split in two halves sums to the whole (the splits of the batch are a partition)."""
+    import tinycudann as tcnn
+    from tinycudann._lib import check, ptr
+    native = tcnn.NativeModule(3, 3, common.CONFIG_WIDE_DP)
+    info = native.info
+    B = 1 << 18
+    g = torch.Generator(device=dev).manual_seed(1)
+    enc = (torch.rand(B, info.encoded_width, device=dev, generator=g) - 0.5).half()
+    p16 = native.initial_params(1337, dev, trainer_seeding=True).half()
+    dy = torch.zeros(B, 16, dtype=torch.half, device=dev)
+    dy[:, :3] = (torch.randn(B, 3, device=dev, generator=g) * 1e-3).half()
+    n = int(info.n_params_mlp)
+
+    def dW(e, d):
+        ws = native.workspace(e.shape[0], dev)
+        gp = torch.zeros(n, dtype=torch.half, device=dev)
+        check(native.lib.tcnn_b200_mlp_backward(native.handle, S(), e.shape[0], ptr(e), ptr(p16), ptr(d), ptr(gp), None, ptr(ws)))
+        return gp.float()
+
+    full = dW(enc, dy)
+    assert torch.isfinite(full).all() and full.abs().max() > 0
+    dbl = dW(enc, (dy.float() * 2).half())
+    assert common.rel_l2((dbl / 2).cpu().numpy(), full.cpu().numpy()) < 2e-3
+    halves = dW(enc[: B // 2].contiguous(), dy[: B // 2].contiguous()) + dW(enc[B // 2:].contiguous(), dy[B // 2:].contiguous())
+    assert common.rel_l2(halves.cpu().numpy(), full.cpu().numpy()) < 2e-3

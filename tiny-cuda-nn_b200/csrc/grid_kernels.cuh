@@ -33,6 +33,7 @@ struct GridParams {
 	uint32_t padded_width;   // encoded row width in halfs (multiple of 16)
 	uint32_t n_replicas;     // power of two
 	uint32_t rep_entries;    // entries per replica (sum of the replicated levels' sizes)
+	uint32_t smoothstep;     // interpolation: 0 = Linear, 1 = Smoothstep (weights w -> w^2 (3 - 2 w), common_device.h:801-807)
 	GridLevel level[MAX_LEVELS];
 };
 
@@ -52,6 +53,9 @@ __device__ __forceinline__ void pos_fract_dev(float x, float scale, float& frac,
 	cell = (uint32_t)(int)f;
 	frac = p - f;
 }
+
+__device__ __forceinline__ float smoothstep_dev(float v) { return v * v * (3.0f - 2.0f * v); }
+__device__ __forceinline__ float smoothstep_derivative_dev(float v) { return 6 * v * (1.0f - v); }
 
 // common_device.h:690-707 with the level-constant part hoisted (strides, hashed flag); primes :650-654.
 template <int D>
@@ -109,6 +113,10 @@ __device__ __forceinline__ uint4 encode_chunk(const GridParams& gp, const __half
 		float frac[D]; uint32_t cell[D];
 #pragma unroll
 		for (int d = 0; d < D; ++d) pos_fract_dev(x[d], lv.scale, frac[d], cell[d]);
+		if (gp.smoothstep) {
+#pragma unroll
+			for (int d = 0; d < D; ++d) frac[d] = smoothstep_dev(frac[d]);
+		}
 		const __half* table = grid + (size_t)lv.offset * F;
 		// issue every gather of the level before the fp16 fma chain (grid.h:146-163 order: corner 0..2^D-1)
 		uint32_t idx[NC]; float w[NC];
@@ -221,7 +229,8 @@ __global__ void __launch_bounds__(256) grid_forward_kernel(const __grid_constant
 #ifndef TCNN_B200_SCATTER_QUAD
 #define TCNN_B200_SCATTER_QUAD 1
 #endif
-template <int D, int F>
+// SMOOTH = false compiles the Smoothstep branch out: the fused MLP kernel (Linear only) keeps its register budget.
+template <int D, int F, bool SMOOTH = false>
 __device__ __forceinline__ void scatter_chunk(const GridParams& gp, const float (&p)[D], uint4 gv, uint32_t chunk,
 	__half* __restrict__ grid_grad, __half* __restrict__ replicas, uint32_t replica_id) {
 	static_assert(F == 2 || F == 4 || F == 8, "fp16 gradient scatter needs F >= 2 (grid.h:655-666)");
@@ -237,6 +246,12 @@ __device__ __forceinline__ void scatter_chunk(const GridParams& gp, const float 
 		float frac[D]; uint32_t cell[D];
 #pragma unroll
 		for (int d = 0; d < D; ++d) pos_fract_dev(p[d], lv.scale, frac[d], cell[d]);
+		if constexpr (SMOOTH) {
+			if (gp.smoothstep) {
+#pragma unroll
+				for (int d = 0; d < D; ++d) frac[d] = smoothstep_dev(frac[d]);
+			}
+		}
 		// Same-address f16x2 reductions serialise in L2 (~80 ns each, measured: 2-D level 0 alone took 244 us at B = 2^18);
 		// coarse levels therefore scatter into one of n_replicas copies chosen per block and are summed afterwards.
 		__half* gtable = lv.replicated
@@ -304,7 +319,7 @@ __global__ void __launch_bounds__(256) grid_backward_kernel(const __grid_constan
 	float p[D];
 	load_position<D>(x, i, p);
 	const uint4 gv = __ldg(reinterpret_cast<const uint4*>(dL_denc + (size_t)i * gp.padded_width + chunk * 8));
-	scatter_chunk<D, F>(gp, p, gv, chunk, grid_grad, replicas, blockIdx.x & (gp.n_replicas - 1));
+	scatter_chunk<D, F, true>(gp, p, gv, chunk, grid_grad, replicas, blockIdx.x & (gp.n_replicas - 1));
 }
 
 // grid_grad[level entries] += sum over replicas (fp32 accumulate, one rounding), for the replicated levels.
@@ -357,6 +372,9 @@ __global__ void __launch_bounds__(256) grid_backward_input_kernel(const __grid_c
 		float frac[D]; uint32_t cell[D];
 #pragma unroll
 		for (int d = 0; d < D; ++d) pos_fract_dev(p[d], lv.scale, frac[d], cell[d]);
+		float dfrac[D]; // d(weight)/d(frac): 1 for Linear
+#pragma unroll
+		for (int d = 0; d < D; ++d) { dfrac[d] = gp.smoothstep ? smoothstep_derivative_dev(frac[d]) : 1.0f; if (gp.smoothstep) frac[d] = smoothstep_dev(frac[d]); }
 		float dl[F];
 #pragma unroll
 		for (int f = 0; f < F; ++f) dl[f] = __half2float(dL_denc[(size_t)i * gp.padded_width + level * F + f]);
@@ -383,7 +401,7 @@ __global__ void __launch_bounds__(256) grid_backward_input_kernel(const __grid_c
 				const uint32_t ir = grid_index_dev<D>(lv, pg);
 #pragma unroll
 				for (int f = 0; f < F; ++f)
-					grads[f][gd] += weight * (__half2float(table[(size_t)ir * F + f]) - __half2float(table[(size_t)il * F + f]));
+					grads[f][gd] += weight * (__half2float(table[(size_t)ir * F + f]) - __half2float(table[(size_t)il * F + f])) * dfrac[gd];
 			}
 		}
 #pragma unroll

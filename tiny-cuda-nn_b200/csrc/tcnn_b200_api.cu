@@ -45,6 +45,7 @@ struct tcnn_b200_plan {
 	// Adam extras
 	float non_matrix_lr_factor = 1.f, weight_clip = 0.f;
 	bool adabound = false;
+	int grid_type = 0;              // GRID_HASH / GRID_DENSE / GRID_TILED (GridType, grid_interface.h)
 	int enc_kind = 0;               // ENC_GRID / ENC_IDENTITY / ENC_ONEBLOB
 	uint32_t oneblob_log2_bins = 0;
 	int kind = 0;                   // PLAN_FULL: encoding + network; PLAN_NETWORK: Identity encoding + network; PLAN_ENCODING: grid encoding alone
@@ -60,6 +61,7 @@ struct tcnn_b200_plan {
 };
 
 enum PlanKind { PLAN_FULL = 0, PLAN_NETWORK = 1, PLAN_ENCODING = 2 };
+enum GridTypeKind { GRID_HASH = 0, GRID_DENSE = 1, GRID_TILED = 2 };
 enum EncKind { ENC_GRID = 0, ENC_IDENTITY = 1, ENC_ONEBLOB = 2 };
 enum ProfileKind { PK_GRID_FWD = 0, PK_MLP = 1, PK_FINALIZE = 2, PK_GRID_BWD = 3, PK_ADAM = 4, PK_COUNT = 5 };
 
@@ -79,7 +81,7 @@ struct ProfileScope {
 static uint32_t next_multiple_u32(uint32_t v, uint32_t m) { return (v + m - 1) / m * m; }
 
 // Per-level constants of grid_index (common_device.h:690-707) for a given (scale, size): strides with uint32 wrap.
-static void fill_level(GridLevel& lv, float scale, uint32_t size, uint32_t offset, uint32_t n_dims) {
+static void fill_level(GridLevel& lv, float scale, uint32_t size, uint32_t offset, uint32_t n_dims, bool hash_type) {
 	lv.scale = scale;
 	lv.resolution = (uint32_t)std::ceil(scale) + 1; // grid_resolution, common_device.h:716-718
 	lv.size = size;
@@ -91,7 +93,7 @@ static void fill_level(GridLevel& lv, float scale, uint32_t size, uint32_t offse
 		stride *= lv.resolution; // uint32 wrap on purpose
 	}
 	lv.n_dense_dims = d;
-	lv.hashed = size < stride ? 1u : 0u;
+	lv.hashed = (hash_type && size < stride) ? 1u : 0u; // Dense / Tiled grids never hash: dense index with wrap, % size
 	lv.replicated = 0; lv.rep_offset = 0;
 }
 
@@ -122,7 +124,7 @@ static size_t replica_bytes(const tcnn_b200_plan* p) {
 static void build_levels(tcnn_b200_plan* p, const float* scales) {
 	const tcnn_b200_info& in = p->info;
 	for (uint32_t l = 0; l < in.n_levels; ++l) {
-		fill_level(p->grid.level[l], scales[l], in.level_offset[l + 1] - in.level_offset[l], in.level_offset[l], in.n_input_dims);
+		fill_level(p->grid.level[l], scales[l], in.level_offset[l + 1] - in.level_offset[l], in.level_offset[l], in.n_input_dims, p->grid_type == GRID_HASH);
 		p->info.level_scale[l] = scales[l];
 		p->info.level_resolution[l] = p->grid.level[l].resolution;
 	}
@@ -205,10 +207,18 @@ extern "C" int tcnn_b200_plan_create(const char* json_utf8, uint32_t n_input_dim
 		p->grid.padded_width = in.encoded_width;
 		try_device_scales(p.get());
 	} else {
-	CHECK(etype == "hashgrid" || etype == "grid", "encoding otype '" + etype + "' is outside the hot path (HashGrid only; SURVEY.md section 8)");
-	CHECK(jsonmini::lower(enc.string("type", "Hash")) == "hash", "only grid type 'Hash' is implemented");
+	CHECK(etype == "hashgrid" || etype == "grid" || etype == "densegrid" || etype == "tiledgrid",
+		"encoding otype '" + etype + "' is outside the hot path (HashGrid / DenseGrid / TiledGrid and OneBlob; SURVEY.md section 8)");
+	// create_grid_encoding (grid.h:1180-1208): DenseGrid / TiledGrid fix the type, otherwise "type" decides (default Hash)
+	const std::string gtype = etype == "densegrid" ? "dense" : etype == "tiledgrid" ? "tiled" : jsonmini::lower(enc.string("type", "Hash"));
+	if (gtype == "hash") p->grid_type = GRID_HASH;
+	else if (gtype == "dense") p->grid_type = GRID_DENSE;
+	else if (gtype == "tiled") p->grid_type = GRID_TILED;
+	else FAIL("GridEncoding: invalid grid type '" + gtype + "'");
 	CHECK(jsonmini::lower(enc.string("hash", "CoherentPrime")) == "coherentprime", "only hash 'CoherentPrime' is implemented");
-	CHECK(jsonmini::lower(enc.string("interpolation", "Linear")) == "linear", "only interpolation 'Linear' is implemented");
+	const std::string interp = jsonmini::lower(enc.string("interpolation", "Linear"));
+	CHECK(interp == "linear" || interp == "smoothstep", "interpolation '" + interp + "' is not implemented (Linear, Smoothstep)");
+	p->grid.smoothstep = interp == "smoothstep" ? 1u : 0u;
 	CHECK(!enc.boolean("stochastic_interpolation", false), "stochastic_interpolation is not implemented");
 	in.n_features_per_level = (uint32_t)enc.number("n_features_per_level", 2);
 	CHECK(in.n_features_per_level == 2 || in.n_features_per_level == 4 || in.n_features_per_level == 8,
@@ -245,8 +255,14 @@ extern "C" int tcnn_b200_plan_create(const char* json_utf8, uint32_t n_input_dim
 			for (uint32_t d = 0; d < n_input_dims; ++d) n *= resolution;
 		}
 		n = next_multiple_u32(n, 8u);
-		n = std::min(n, 1u << in.log2_hashmap_size);
+		if (p->grid_type == GRID_HASH) n = std::min(n, 1u << in.log2_hashmap_size);   // grid.h:702-712
+		else if (p->grid_type == GRID_TILED) {
+			uint32_t tile = 1;
+			for (uint32_t d = 0; d < n_input_dims; ++d) tile *= in.base_resolution;     // powi(base_resolution, N_POS_DIMS)
+			n = std::min(n, tile);
+		}
 		in.level_offset[l] = offset;
+		CHECK((uint64_t)offset + n < (1ull << 32) / in.n_features_per_level, "GridEncoding: more than 2^32 grid parameters");
 		offset += n;
 	}
 	in.level_offset[in.n_levels] = offset;
@@ -637,7 +653,7 @@ static void launch_mlp(const tcnn_b200_plan* plan, cudaStream_t stream, const Ml
 // Training kernel with the hash-table gradient scatter fused into its last stage; instantiated for the common shapes.
 static bool fused_scatter_available(const tcnn_b200_plan* plan) {
 	const uint32_t D = plan->info.n_input_dims, F = plan->info.n_features_per_level;
-	return !is_wide(plan) && plan->enc_kind == ENC_GRID && (D == 2 || D == 3) && (F == 2 || F == 4);
+	return !is_wide(plan) && plan->enc_kind == ENC_GRID && !plan->grid.smoothstep && (D == 2 || D == 3) && (F == 2 || F == 4);
 }
 template <int H>
 static void launch_mlp_train_fused_h(const tcnn_b200_plan* plan, cudaStream_t stream, const MlpArgs& a, uint32_t grid, const GridParams& gp) {
