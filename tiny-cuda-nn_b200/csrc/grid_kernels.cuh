@@ -15,6 +15,15 @@ namespace b200 {
 constexpr int MAX_LEVELS = 32;
 constexpr int MAX_DIMS = 4;
 
+// Tile images (mlp_wide_kernels.cuh): the 128-neuron MLP reads its input as the byte image of its shared-memory tiles -
+// 128 samples x 64 columns per 16 KB sub-tile, rows of 128 bytes, 16-byte chunks XOR-swizzled by (row & 7) - so that a tile
+// moves with one TMA bulk copy.  Byte offset of 16-byte chunk c (8 halfs) of sample i, `subs` sub-tiles per tile:
+constexpr uint32_t SUB_BYTES = 16384;
+__host__ __device__ __forceinline__ size_t wide_image_chunk(size_t i, uint32_t c, uint32_t subs) {
+	const uint32_t r = (uint32_t)(i & 127);
+	return (i >> 7) * ((size_t)subs * SUB_BYTES) + (size_t)(c >> 3) * SUB_BYTES + r * 128u + (((c & 7u) ^ (r & 7u)) << 4);
+}
+
 struct GridLevel {
 	float scale;            // exp2f(level * log2(per_level_scale)) * base_resolution - 1   (device-evaluated, see grid_scale_kernel)
 	uint32_t resolution;    // (uint32_t)ceilf(scale) + 1
@@ -33,6 +42,7 @@ struct GridParams {
 	uint32_t padded_width;   // encoded row width in halfs (multiple of 16)
 	uint32_t n_replicas;     // power of two
 	uint32_t rep_entries;    // entries per replica (sum of the replicated levels' sizes)
+	uint32_t image_subs;     // 0: encoded rows [B][padded_width]; n > 0: tile images with n sub-tiles per tile (wide_image_chunk)
 	uint32_t smoothstep;     // interpolation: 0 = Linear, 1 = Smoothstep (weights w -> w^2 (3 - 2 w), common_device.h:801-807)
 	GridLevel level[MAX_LEVELS];
 };
@@ -220,7 +230,8 @@ __global__ void __launch_bounds__(256) grid_forward_kernel(const __grid_constant
 	float p[D];
 	load_position<D>(x, i, p);
 	const uint4 v = encode_chunk<D, F>(gp, grid, p, chunk);
-	*reinterpret_cast<uint4*>(encoded + (size_t)i * gp.padded_width + chunk * 8) = v;
+	const size_t off = gp.image_subs ? wide_image_chunk(i, chunk, gp.image_subs) : ((size_t)i * gp.padded_width + chunk * 8) * 2;
+	*reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(encoded) + off) = v;
 }
 
 // Scatter one sample's 8-half chunk of dL/d(encoded) (fp16, loss-scaled) into the fp16 grid gradient.
@@ -416,14 +427,16 @@ __global__ void __launch_bounds__(256) grid_backward_input_kernel(const __grid_c
 // Identity encoding in front of a stand-alone Network (encodings/identity.h:46-90, src/cpp_api.cu:151-153): fp32 [B][n_in] ->
 // fp16 [B][width], columns >= n_in are ONE (identity.h:63), so that the first layer can learn a bias through them.
 // Thread = sample x 8-column chunk.
-__global__ void __launch_bounds__(256) identity_encode_kernel(uint32_t B, uint32_t n_in, uint32_t width, const float* __restrict__ x, __half* __restrict__ out) {
+__global__ void __launch_bounds__(256) identity_encode_kernel(uint32_t B, uint32_t n_in, uint32_t width, const float* __restrict__ x, __half* __restrict__ out,
+	uint32_t image_subs = 0) {
 	const uint32_t cpr = width / 8, q = blockIdx.x * blockDim.x + threadIdx.x;
 	if (q >= B * cpr) return;
 	const uint32_t i = q / cpr, c0 = (q % cpr) * 8;
 	union { uint4 v; __half h[8]; } o;
 #pragma unroll
 	for (uint32_t k = 0; k < 8; ++k) o.h[k] = __float2half(c0 + k < n_in ? __ldg(x + (size_t)i * n_in + c0 + k) : 1.0f);
-	*reinterpret_cast<uint4*>(out + (size_t)i * width + c0) = o.v;
+	const size_t off = image_subs ? wide_image_chunk(i, c0 / 8, image_subs) : ((size_t)i * width + c0) * 2;
+	*reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(out) + off) = o.v;
 }
 // identity_backward (identity.h:68-83): dL/dx = (float) dL/dy for the first n_in columns
 __global__ void __launch_bounds__(256) identity_backward_kernel(uint32_t B, uint32_t n_in, uint32_t width, const __half* __restrict__ dL_dy, float* __restrict__ dL_dx) {

@@ -6,6 +6,8 @@
 #include <cuda_fp16.h>
 #include <stdint.h>
 
+#include "grid_kernels.cuh"
+
 namespace b200 {
 
 __device__ __forceinline__ float oneblob_quartic_cdf(float x, float inv_radius) {
@@ -20,26 +22,44 @@ __device__ __forceinline__ float oneblob_quartic_pdf(float x, float inv_radius) 
 	return (15.0f / 16.0f) * t * t * inv_radius;
 }
 
-// Block = (n_out, ceil(128 / n_out)) threads like the reference's launch (oneblob.h:118-121): thread (j, y) = encoded column
-// j of sample blockIdx.x * blockDim.y + y.  Every thread evaluates the wrapped CDF at the LEFT edge of its bin and takes the
-// right edge from the neighbouring lane with a sub-warp shuffle of width n_bins (oneblob.h:47-70) - kept exactly, including
-// what the shuffle does for n_bins = 64 (> warp size), because parity is against the reference's output, not its intent.
+// Block = (n_out, ceil(128 / n_out)) threads like the reference's launch (oneblob.h:118-121), so that a column sits in the
+// same lane as there: thread (j, y) = encoded column j of samples (blockIdx.x * ONEBLOB_ROUNDS + r) * blockDim.y + y.  Every
+// thread evaluates the wrapped CDF at the LEFT edge of its bin and takes the right edge from the neighbouring lane with a
+// sub-warp shuffle of width n_bins (oneblob.h:47-70) - kept exactly, including what the shuffle does for n_bins = 64
+// (> warp size), because parity is against the reference's output, not its intent.  Unlike the reference a block walks
+// ONEBLOB_ROUNDS samples per thread row (262144 one-sample blocks at batch 2^18 were launch-bound: 137 us).
+// image_subs > 0: the output is written as tile images for the 128-neuron MLP (grid_kernels.cuh wide_image_chunk).
+constexpr uint32_t ONEBLOB_ROUNDS = 8;
 __global__ void oneblob_encode_kernel(uint32_t B, uint32_t n_in, uint32_t log2_bins, uint32_t n_out, uint32_t width,
-	const float* __restrict__ x, __half* __restrict__ out) {
-	const uint32_t i = blockIdx.x * blockDim.y + threadIdx.y;
+	const float* __restrict__ x, __half* __restrict__ out, uint32_t image_subs) {
 	const uint32_t j = threadIdx.x;
-	if (i >= B) return;
 	const uint32_t n_bins = 1u << log2_bins;
-	const uint32_t bin = j & (n_bins - 1);
-	const float xv = x[(size_t)i * n_in + (j >> log2_bins)];
+	const uint32_t bin = j & (n_bins - 1), dim = j >> log2_bins;
 	const float inv_radius = (float)n_bins;
 	const float left_boundary = scalbnf((float)bin, -(int)log2_bins);
-	const float left_cdf = oneblob_quartic_cdf(left_boundary - xv, inv_radius) + oneblob_quartic_cdf(left_boundary - xv - 1.0f, inv_radius)
-		+ oneblob_quartic_cdf(left_boundary - xv + 1.0f, inv_radius);
-	float right_cdf = __shfl_sync(0xffffffffu, left_cdf, bin + 1, n_bins);
-	if (bin == n_bins - 1) right_cdf += 1.0f; // wrap-around: the last bin's right edge is the first bin's left edge + 1
-	out[(size_t)i * width + j] = __float2half(right_cdf - left_cdf);
-	if (j < width - n_out) out[(size_t)i * width + n_out + j] = __float2half(1.0f);
+	const uint32_t i0 = blockIdx.x * ONEBLOB_ROUNDS * blockDim.y + threadIdx.y;
+	float xv[ONEBLOB_ROUNDS];
+#pragma unroll
+	for (uint32_t r = 0; r < ONEBLOB_ROUNDS; ++r) {
+		const uint32_t i = i0 + r * blockDim.y;
+		xv[r] = i < B ? __ldg(x + (size_t)i * n_in + dim) : 0.0f;
+	}
+#pragma unroll
+	for (uint32_t r = 0; r < ONEBLOB_ROUNDS; ++r) {
+		const uint32_t i = i0 + r * blockDim.y;
+		const float d = left_boundary - xv[r];
+		const float left_cdf = oneblob_quartic_cdf(d, inv_radius) + oneblob_quartic_cdf(d - 1.0f, inv_radius) + oneblob_quartic_cdf(d + 1.0f, inv_radius);
+		float right_cdf = __shfl_sync(0xffffffffu, left_cdf, bin + 1, n_bins); // whole warps stay in the loop: no lane has exited
+		if (bin == n_bins - 1) right_cdf += 1.0f; // wrap-around: the last bin's right edge is the first bin's left edge + 1
+		if (i >= B) continue;
+		uint8_t* o = reinterpret_cast<uint8_t*>(out);
+		const size_t row = image_subs ? 0 : (size_t)i * width * 2;
+		auto at = [&](uint32_t col) -> __half* {
+			return reinterpret_cast<__half*>(o + (image_subs ? wide_image_chunk(i, col >> 3, image_subs) + (col & 7) * 2 : row + col * 2));
+		};
+		*at(j) = __float2half(right_cdf - left_cdf);
+		if (j < width - n_out) *at(n_out + j) = __float2half(1.0f);
+	}
 }
 
 // dL/dx (oneblob.h:105-141): sum over the bins of dL/dy * (pdf at the left edge - pdf at the right edge), wrapped

@@ -358,9 +358,9 @@ struct Workspace {
 };
 static bool is_wide(const tcnn_b200_plan* p) { return p->info.n_neurons == 128; }
 // 64 neurons: CTAs of the persistent MLP kernel = number of weight-gradient / loss partials.
-// 128 neurons: number of batch splits of the weight-gradient kernel (one CTA per split and matrix, 3 resident per SM).
+// 128 neurons: number of batch splits of the weight-gradient kernel (one CTA per split and matrix, one CTA per SM).
 static uint32_t mlp_grid_size(const tcnn_b200_plan* p, uint32_t n_tiles, bool train) {
-	if (is_wide(p) && train) return std::max(1u, std::min(n_tiles, (uint32_t)p->n_sms * 3u / (p->info.n_hidden_layers + 1)));
+	if (is_wide(p) && train) return std::max(1u, std::min(n_tiles, (uint32_t)p->n_sms / (p->info.n_hidden_layers + 1))); // one CTA per SM (192 KB ring)
 	const uint32_t per_sm = train ? 2u : 3u;
 	return std::max(1u, std::min(n_tiles, (uint32_t)p->n_sms * per_sm));
 }
@@ -373,10 +373,15 @@ static uint32_t mlp_loss_parts(const tcnn_b200_plan* p, uint32_t n_tiles, uint32
 	return is_wide(p) ? wide_fwd_ctas(p, n_tiles) * wide_nwg_fwd(p) : n_parts;
 }
 static size_t align256(size_t v) { return (v + 255) / 256 * 256; }
+// encoded batch: rows [B][E] for the 64-neuron kernel, tile images (whole 64-column sub-tiles) for the 128-neuron kernels
+static uint32_t image_subs(const tcnn_b200_plan* p) { return is_wide(p) ? wide_in_sub(p->info.encoded_width) : 0u; }
+static size_t encoded_bytes(const tcnn_b200_plan* p, uint32_t B) {
+	return align256((size_t)B * (is_wide(p) ? wide_in_sub(p->info.encoded_width) * 64u : p->info.encoded_width) * 2);
+}
 static Workspace carve(const tcnn_b200_plan* p, uint32_t B, void* ws) {
 	Workspace w;
 	uint8_t* b = (uint8_t*)ws;
-	const size_t act = align256((size_t)B * p->info.encoded_width * 2);
+	const size_t act = encoded_bytes(p, B);
 	const uint32_t max_ctas = (uint32_t)p->n_sms * 4;
 	w.encoded = (__half*)b; b += act;
 	w.dL_denc = (__half*)b; b += act;
@@ -394,7 +399,7 @@ static Workspace carve(const tcnn_b200_plan* p, uint32_t B, void* ws) {
 }
 extern "C" size_t tcnn_b200_workspace_bytes(const tcnn_b200_plan* plan, uint32_t B) {
 	if (!plan) return 0;
-	const size_t act = align256((size_t)B * plan->info.encoded_width * 2);
+	const size_t act = encoded_bytes(plan, B);
 	const uint32_t max_ctas = (uint32_t)plan->n_sms * 4;
 	const size_t wide = is_wide(plan) ? 2 * align256((size_t)plan->info.n_hidden_layers * B * WIDE_W * 2) + align256((size_t)B * MLP_OUT * 2) : 0;
 	return 2 * act + align256((size_t)max_ctas * plan->info.n_params_mlp * 4) + align256((size_t)max_ctas * 4) + align256(replica_bytes(plan)) + wide + 256;
@@ -487,12 +492,14 @@ extern "C" int tcnn_b200_cast_params(void* stream_, uint64_t n, const float* par
 	} while (0)
 
 static void encode_forward(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t B, const float* x, const __half* grid, __half* encoded,
-	void* zero_on_the_side = nullptr, size_t zero_bytes = 0) {
+	void* zero_on_the_side = nullptr, size_t zero_bytes = 0, bool image = false) {
 	ProfileScope prof(plan, stream, PK_GRID_FWD);
 	const dim3 g((B + 255) / 256, plan->info.encoded_width / 8, 1);
 	uint4* z16 = zero_bytes ? (uint4*)zero_on_the_side : nullptr;
 	const uint32_t nz16 = (uint32_t)(zero_bytes / 16);
-	GRID_DISPATCH(grid_forward_kernel, plan, g, stream, plan->grid, B, x, grid, encoded, z16, nz16);
+	GridParams gp = plan->grid;
+	gp.image_subs = image ? image_subs(plan) : 0u;
+	GRID_DISPATCH(grid_forward_kernel, plan, g, stream, gp, B, x, grid, encoded, z16, nz16);
 	launch_check("grid_forward_kernel");
 }
 // backward in three pieces so that several batch chunks can scatter concurrently between one prepare and one finish
@@ -538,12 +545,12 @@ static void encode_backward(const tcnn_b200_plan* plan, cudaStream_t stream, uin
 	backward_finish(plan, stream, gp, grid_grads, replicas);
 }
 
-static void encode_any(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t B, const float* x, const __half* grid, __half* encoded);
+static void encode_any(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t B, const float* x, const __half* grid, __half* encoded, bool image);
 extern "C" int tcnn_b200_encode_forward(const tcnn_b200_plan* plan, void* stream, uint32_t B, const float* x, const void* grid_params, void* encoded) {
 	API_BEGIN
 	require_device(plan); check_batch(B);
 	CHECK(x && encoded && (grid_params || plan->enc_kind != ENC_GRID), "null argument");
-	encode_any(plan, (cudaStream_t)stream, B, x, (const __half*)grid_params, (__half*)encoded); // OneBlob / Identity: grid_params unused
+	encode_any(plan, (cudaStream_t)stream, B, x, (const __half*)grid_params, (__half*)encoded, /*image=*/false); // OneBlob / Identity: grid_params unused
 	API_END
 }
 extern "C" int tcnn_b200_encode_backward(const tcnn_b200_plan* plan, void* stream, uint32_t B, const float* x, const void* dL_denc, void* grid_grads, int zero_first, void* workspace) {
@@ -705,10 +712,25 @@ static void mlp_finalize(const tcnn_b200_plan* plan, cudaStream_t stream, uint32
 	launch_check("mlp_finalize_kernel");
 }
 
+static void rows_to_image(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t B, const __half* rows, __half* image) {
+	const uint32_t n = B * (plan->info.encoded_width / 8);
+	wide_rowmajor_to_image_kernel<<<(n + 255) / 256, 256, 0, stream>>>(B, plan->info.encoded_width, rows, image);
+	launch_check("wide_rowmajor_to_image_kernel");
+}
+
 extern "C" int tcnn_b200_mlp_forward(const tcnn_b200_plan* plan, void* stream, uint32_t B, const void* input, const void* params, void* output) {
 	API_BEGIN
 	require_device(plan); check_batch(B);
 	CHECK(input && params && output, "null argument");
+	if (is_wide(plan)) { // the 128-neuron kernels read tile images: convert the caller's rows into a stream-ordered scratch buffer
+		cudaStream_t st = (cudaStream_t)stream;
+		void* img = nullptr;
+		CUDA_OK(cudaMallocAsync(&img, encoded_bytes(plan, B), st));
+		rows_to_image(plan, st, B, (const __half*)input, (__half*)img);
+		mlp_infer(plan, st, B, (const __half*)img, (const __half*)params, (__half*)output, nullptr);
+		CUDA_OK(cudaFreeAsync(img, st));
+		return 0;
+	}
 	mlp_infer(plan, (cudaStream_t)stream, B, (const __half*)input, (const __half*)params, (__half*)output, nullptr);
 	API_END
 }
@@ -723,6 +745,11 @@ extern "C" int tcnn_b200_mlp_backward(const tcnn_b200_plan* plan, void* stream_,
 	Workspace w{};
 	if (workspace) w = carve(plan, B, workspace);
 	MlpArgs a = base_mlp_args(plan, B, (const __half*)input, (const __half*)params, workspace ? &w : nullptr);
+	if (is_wide(plan)) {
+		CHECK(workspace, "the 128-neuron backward pass needs the workspace");
+		rows_to_image(plan, stream, B, (const __half*)input, w.encoded);
+		a.input = w.encoded;
+	}
 	a.dL_doutput = (const __half*)dL_doutput;
 	a.dL_dinput = (__half*)dL_dinput;
 	a.dW_partials = dL_dparams ? w.dw_partials : nullptr;
@@ -741,18 +768,21 @@ static void encode_backward_input(const tcnn_b200_plan* plan, cudaStream_t strea
 }
 
 // grid gather, or the Identity encoding of a stand-alone Network
-static void encode_any(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t B, const float* x, const __half* grid, __half* encoded) {
-	if (plan->enc_kind == ENC_GRID) { encode_forward(plan, stream, B, x, grid, encoded); return; }
+// `image`: write tile images for the 128-neuron MLP instead of rows (internal callers pass is_wide(plan))
+static void encode_any(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t B, const float* x, const __half* grid, __half* encoded, bool image) {
+	if (plan->enc_kind == ENC_GRID) { encode_forward(plan, stream, B, x, grid, encoded, nullptr, 0, image); return; }
+	const uint32_t subs = image ? image_subs(plan) : 0u;
 	ProfileScope prof(plan, stream, PK_GRID_FWD);
 	if (plan->enc_kind == ENC_ONEBLOB) {
 		const uint32_t n_out = plan->grid.n_features, rows = (128 + n_out - 1) / n_out; // the reference's block shape (oneblob.h:118-121)
-		oneblob_encode_kernel<<<(B + rows - 1) / rows, dim3(n_out, rows, 1), 0, stream>>>(B, plan->info.n_input_dims, plan->oneblob_log2_bins, n_out,
-			plan->info.encoded_width, x, encoded);
+		const uint32_t per_block = rows * ONEBLOB_ROUNDS;
+		oneblob_encode_kernel<<<(B + per_block - 1) / per_block, dim3(n_out, rows, 1), 0, stream>>>(B, plan->info.n_input_dims, plan->oneblob_log2_bins, n_out,
+			plan->info.encoded_width, x, encoded, subs);
 		launch_check("oneblob_encode_kernel");
 		return;
 	}
 	const uint32_t n = B * (plan->info.encoded_width / 8);
-	identity_encode_kernel<<<(n + 255) / 256, 256, 0, stream>>>(B, plan->info.n_input_dims, plan->info.encoded_width, x, encoded);
+	identity_encode_kernel<<<(n + 255) / 256, 256, 0, stream>>>(B, plan->info.n_input_dims, plan->info.encoded_width, x, encoded, subs);
 	launch_check("identity_encode_kernel");
 }
 
@@ -769,7 +799,7 @@ extern "C" int tcnn_b200_inference(const tcnn_b200_plan* plan, void* stream_, ui
 		encode_forward(plan, stream, B, x, p, (__half*)output_fp16);
 		return 0;
 	}
-	encode_any(plan, stream, B, x, p + plan->info.n_params_mlp, w.encoded);
+	encode_any(plan, stream, B, x, p + plan->info.n_params_mlp, w.encoded, is_wide(plan));
 	mlp_infer(plan, stream, B, w.encoded, p, (__half*)output_fp16, output_fp32);
 	API_END
 }
@@ -847,14 +877,14 @@ extern "C" int tcnn_b200_training_fwd_bwd(const tcnn_b200_plan* plan, void* stre
 	a.loss_partials = w.loss_partials;
 	a.loss_scale = loss_scale;
 	if (plan->enc_kind != ENC_GRID) { // parameter-free encoding (OneBlob): no table gradients, dL/d(encoded) is not needed
-		encode_any(plan, main, B, x, nullptr, w.encoded);
+		encode_any(plan, main, B, x, nullptr, w.encoded, is_wide(plan));
 		a.dL_dinput = nullptr;
 		launch_mlp<MODE_TRAIN>(plan, main, a, part_cnt[0]);
 		mlp_finalize(plan, main, part_cnt[0], w, g, loss_out, loss_out != nullptr, B / MLP_TILE);
 		return 0;
 	}
 	backward_prepare(plan, main, gp, gg, zero_grid_grads, w.replicas);
-	encode_forward(plan, main, B, x, p + in.n_params_mlp, w.encoded);
+	encode_forward(plan, main, B, x, p + in.n_params_mlp, w.encoded, nullptr, 0, is_wide(plan));
 	if (fused_scatter_available(plan)) {
 		a.dL_dinput = nullptr; a.positions = x; a.grid_grad = gg; a.replicas = w.replicas;
 		launch_mlp_train_fused(plan, main, a, part_cnt[0], gp);
@@ -979,7 +1009,7 @@ extern "C" int tcnn_b200_training_step(const tcnn_b200_plan* plan, void* stream_
 		return 0;
 	}
 	if (plan->enc_kind != ENC_GRID) { // parameter-free encoding: encode -> MLP forward/backward -> weight-gradient reduction + Adam in one kernel
-		encode_any(plan, main, B, x, nullptr, w.encoded);
+		encode_any(plan, main, B, x, nullptr, w.encoded, is_wide(plan));
 		a.dL_dinput = nullptr;
 		launch_mlp<MODE_TRAIN>(plan, main, a, mlp_grid);
 		ProfileScope prof(plan, main, PK_FINALIZE);
@@ -990,7 +1020,7 @@ extern "C" int tcnn_b200_training_step(const tcnn_b200_plan* plan, void* stream_
 		return 0;
 	}
 	backward_prepare(plan, main, gp, gg, /*zero_first=*/0, w.replicas);
-	encode_forward(plan, main, B, x, p + in.n_params_mlp, w.encoded);
+	encode_forward(plan, main, B, x, p + in.n_params_mlp, w.encoded, nullptr, 0, is_wide(plan));
 	launch_mlp<MODE_TRAIN>(plan, main, a, mlp_grid);
 	CUDA_OK(cudaEventRecord(ev[0], main));
 	CUDA_OK(cudaStreamWaitEvent(aux, ev[0], 0));
@@ -1071,7 +1101,7 @@ extern "C" int tcnn_b200_training_step_dp(const tcnn_b200_plan* plan, void* stre
 	const uint32_t mlp_grid = mlp_grid_size(plan, B / MLP_TILE, true);
 
 	// local part: identical to the single-GPU step up to the complete local gradient (grid gradients are zero on entry)
-	encode_forward(plan, main, B, x, p + in.n_params_mlp, w.encoded, w.replicas, replica_bytes_of(plan, gp)); // also clears the replicas
+	encode_forward(plan, main, B, x, p + in.n_params_mlp, w.encoded, w.replicas, replica_bytes_of(plan, gp), is_wide(plan)); // also clears the replicas
 	if (fused_scatter_available(plan)) {
 		a.dL_dinput = nullptr; a.positions = x; a.grid_grad = gg; a.replicas = w.replicas;
 		launch_mlp_train_fused(plan, main, a, mlp_grid, gp);
