@@ -25,6 +25,7 @@ def big(cfg, log2_T):
 
 CASES = {  # name: (config, n_in, n_out, B)
     "oneblob_128x5_b18": (common.CONFIG_ONEBLOB, 2, 3, 1 << 18),
+    "oneblob16_64x4_b18": (common.CONFIG_ONEBLOB16, 2, 3, 1 << 18),
     "oneblob_128x5_b20": (common.CONFIG_ONEBLOB, 2, 3, 1 << 20),
     "cfg4_T24_128x4_b20": (big(common.CONFIG_WIDE_F4, 24), 3, 4, 1 << 20),
     "cfg5_T22_128x3_b19": (big(common.CONFIG_WIDE_DP, 22), 3, 3, 1 << 19),
@@ -77,9 +78,15 @@ def reference(name, cfg, n_in, n_out, B, steps=30, warmup=5):
             print(json.dumps({"case": name, "impl": "reference", "error": (r.stderr or r.stdout)[-300:]}), flush=True)
 
 
+# the reference's own benchmark sweep (benchmarks/image/bench_ours.cu:188-331 with data/config_oneblob.json): batch 2^14 .. 2^21
+for _k in range(14, 22):
+    CASES[f"sweep_oneblob_128x5_b{_k}"] = (common.CONFIG_ONEBLOB, 2, 3, 1 << _k)
+
 if __name__ == "__main__":
+    if "--sweep" in sys.argv:
+        sys.argv += [n for n in CASES if n.startswith("sweep_")]
     no_ref = "--no-ref" in sys.argv
-    names = [a for a in sys.argv[1:] if not a.startswith("--")] or list(CASES)
+    names = [a for a in sys.argv[1:] if not a.startswith("--")] or [n for n in CASES if not n.startswith("sweep_")]
     for n in names:
         try:
             ours(n, *CASES[n])

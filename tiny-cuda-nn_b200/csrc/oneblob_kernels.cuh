@@ -10,8 +10,12 @@
 
 namespace b200 {
 
+// |u| >= 1.25: the polynomial is at least 2 % outside [0, 1] (1.023 at u = 1.25, monotone), far more than fp32 rounding can
+// move it, so the reference's clamp returns exactly 0 or 1 there: the early-out is bit-identical and lets whole warps skip
+// the polynomial (two of the three wrapped terms are saturated for almost every bin).  NaN takes the polynomial path.
 __device__ __forceinline__ float oneblob_quartic_cdf(float x, float inv_radius) {
 	const float u = x * inv_radius;
+	if (fabsf(u) >= 1.25f) return u > 0.0f ? 1.0f : 0.0f;
 	const float u2 = u * u;
 	const float u4 = u2 * u2;
 	return fmaxf(0.0f, fminf(1.0f, (15.0f / 16.0f) * u * (1.0f - (2.0f / 3.0f) * u2 + (1.0f / 5.0f) * u4) + 0.5f));
