@@ -421,6 +421,63 @@ class MlpConfig:
         return out
 
 
+K_ACT = F32(10.0)  # common_device.h:100
+
+
+def activation_forward(z16: np.ndarray, name: str) -> np.ndarray:
+    """warp_activation<__half> (common_device.h:102-160): fp16 pre-activation in, function in fp32, fp16 out."""
+    n = name.lower()
+    x = z16.astype(np.float16).astype(np.float32)
+    if n == "none":
+        return z16.astype(np.float16)
+    if n == "relu":
+        return np.maximum(z16.astype(np.float16), np.float16(0))
+    if n == "leakyrelu":  # half multiply by (half)1 or (half)0.01
+        return (x * np.where(x > 0, np.float16(1.0), np.float16(0.01)).astype(np.float32)).astype(np.float16)
+    with np.errstate(over="ignore"):
+        if n == "exponential":
+            r = np.exp(x, dtype=np.float32)
+        elif n == "sigmoid":
+            r = F32(1.0) / (F32(1.0) + np.exp(-x, dtype=np.float32))
+        elif n == "squareplus":
+            t = x * K_ACT
+            r = F32(0.5) * (t + np.sqrt(t * t + F32(4.0), dtype=np.float32)) / K_ACT
+        elif n == "softplus":
+            r = np.log(np.exp(x * K_ACT, dtype=np.float32) + F32(1.0), dtype=np.float32) / K_ACT
+        elif n == "tanh":
+            r = np.tanh(x, dtype=np.float32)
+        else:
+            raise ValueError(name)
+    return r.astype(np.float16)
+
+
+def activation_backward(g16: np.ndarray, y16: np.ndarray, name: str) -> np.ndarray:
+    """warp_activation_backward<__half> (common_device.h:240-293): fp16 gradient times an fp16 derivative factor that is
+    computed from the stored POST-activation y."""
+    n = name.lower()
+    y = y16.astype(np.float16).astype(np.float32)
+    if n == "none":
+        return g16.astype(np.float16)
+    if n == "relu":
+        d = (y > 0).astype(np.float16)
+    elif n == "leakyrelu":
+        d = np.where(y > 0, np.float16(1.0), np.float16(0.01)).astype(np.float16)
+    elif n == "exponential":
+        d = y16.astype(np.float16)
+    elif n == "sigmoid":  # (T)(y * (T)(1.0f - (float)y)): half * half
+        d = (y * (F32(1.0) - y).astype(np.float16).astype(np.float32)).astype(np.float16)
+    elif n == "squareplus":
+        t = y * K_ACT
+        d = (t * t / (t * t + F32(1.0))).astype(np.float16)
+    elif n == "softplus":
+        d = (F32(1.0) - np.exp(-y * K_ACT, dtype=np.float32)).astype(np.float16)
+    elif n == "tanh":
+        d = (F32(1.0) - y * y).astype(np.float16)
+    else:
+        raise ValueError(name)
+    return (g16.astype(np.float16).astype(np.float32) * d.astype(np.float32)).astype(np.float16)
+
+
 def matmul_acc(a: np.ndarray, b: np.ndarray, acc=np.float32) -> np.ndarray:
     """a [M, K] @ b [K, N] for fp16 operands.  acc = np.float32 / np.float64: one accumulation, the caller rounds.
     acc = "hmma16": the accumulator is rounded to fp16 after every 16-deep MMA step, which is how tensor-core fp16
@@ -439,19 +496,18 @@ def mlp_forward(cfg: MlpConfig, params: np.ndarray, x: np.ndarray, acc=np.float3
 
     Storage fp16 after every layer like the reference (fully_fused_mlp.cu:47-129); `acc` is the accumulator type:
     the reference accumulates in fp16 wmma fragments, the B200 kernels in fp32 TMEM (BASELINE tolerance 1e-2)."""
-    assert cfg.activation == "ReLU" and cfg.output_activation == "None"
     ws = cfg.split(params.astype(np.float16))
     h = x.astype(np.float16)
     hidden = []
     for w in ws[:-1]:
         z = matmul_acc(h, w.T, acc)
-        h = np.maximum(z, 0).astype(np.float16)
+        h = activation_forward(z.astype(np.float16), cfg.activation)
         hidden.append(h)
-    y = matmul_acc(h, ws[-1].T, acc).astype(np.float16)
+    y = activation_forward(matmul_acc(h, ws[-1].T, acc).astype(np.float16), cfg.output_activation)
     return y, hidden
 
 
-def mlp_backward(cfg: MlpConfig, params: np.ndarray, x: np.ndarray, hidden, dy: np.ndarray, acc=np.float32, dw_acc=np.float64):
+def mlp_backward(cfg: MlpConfig, params: np.ndarray, x: np.ndarray, hidden, dy: np.ndarray, acc=np.float32, dw_acc=np.float64, y=None):
     """dy: fp16 [B, out_pad] (loss-scaled) -> (dparams float64 [n_params] exact-ish, dx fp16 [B, n_input]).
 
     Chain (fully_fused_mlp.cu:150-259): g = (W_next^T dy) * relu'(h) with the mask taken from the stored
@@ -460,13 +516,17 @@ def mlp_backward(cfg: MlpConfig, params: np.ndarray, x: np.ndarray, hidden, dy: 
     ws = cfg.split(params.astype(np.float16))
     grads = [None] * len(ws)
     g = dy.astype(np.float16)
+    if cfg.output_activation.lower() != "none":
+        # activation_backward_output_gpu (fully_fused_mlp.cu:757-762): needs the activated network output y
+        assert y is not None, "mlp_backward needs the forward output when the network has an output activation"
+        g = activation_backward(g, y, cfg.output_activation)
     for k in range(len(ws) - 1, -1, -1):
         inp = hidden[k - 1] if k > 0 else x.astype(np.float16)
         grads[k] = matmul_acc(np.ascontiguousarray(g.T), inp, dw_acc).astype(np.float64)
         z = matmul_acc(g, ws[k], acc)
-        if k > 0:
-            z = z * (hidden[k - 1] > 0)
         g = z.astype(np.float16)
+        if k > 0:
+            g = activation_backward(g, hidden[k - 1], cfg.activation)
     return np.concatenate([gr.reshape(-1) for gr in grads]), g
 
 

@@ -40,6 +40,17 @@ CONFIG_DENSE = {  # DenseGrid, Linear, 3-D, F = 4
     "encoding": {"otype": "DenseGrid", "n_levels": 4, "n_features_per_level": 4, "base_resolution": 8, "per_level_scale": 1.6},
     "network": {"otype": "FullyFusedMLP", "activation": "ReLU", "output_activation": "None", "n_neurons": 64, "n_hidden_layers": 2},
 }
+def _net(n, h, act, out_act):
+    return {"otype": "FullyFusedMLP", "activation": act, "output_activation": out_act, "n_neurons": n, "n_hidden_layers": h}
+
+
+_GRID_SMALL_2D = {"otype": "HashGrid", "n_levels": 8, "n_features_per_level": 2, "log2_hashmap_size": 12, "base_resolution": 8, "per_level_scale": 1.5}
+_GRID_SMALL_3D = {"otype": "HashGrid", "n_levels": 8, "n_features_per_level": 4, "log2_hashmap_size": 12, "base_resolution": 8, "per_level_scale": 1.5}
+# hidden / output activations other than ReLU / None (common_device.h:100-304), on both MLP widths
+CONFIG_ACT_A = {"loss": {"otype": "L2"}, "optimizer": {"otype": "Adam"}, "encoding": _GRID_SMALL_2D, "network": _net(64, 3, "Sigmoid", "Exponential")}
+CONFIG_ACT_B = {"loss": {"otype": "RelativeL2"}, "optimizer": {"otype": "Adam"}, "encoding": {"otype": "OneBlob", "n_bins": 16}, "network": _net(128, 2, "Tanh", "Sigmoid")}
+CONFIG_ACT_C = {"loss": {"otype": "L2"}, "optimizer": {"otype": "Adam"}, "encoding": {"otype": "OneBlob", "n_bins": 16}, "network": _net(64, 2, "Squareplus", "Softplus")}
+CONFIG_ACT_D = {"loss": {"otype": "L2"}, "optimizer": {"otype": "Adam"}, "encoding": _GRID_SMALL_3D, "network": _net(128, 2, "LeakyReLU", "LeakyReLU")}
 CONFIG_ONEBLOB = {  # BASELINE.json configs[1]: data/config_oneblob.json of the reference (bench_ours.cu), 2-D input -> 128 features
     "loss": {"otype": "RelativeL2"},
     "optimizer": {"otype": "Adam", "learning_rate": 1e-2, "beta1": 0.9, "beta2": 0.99, "epsilon": 1e-8, "l2_reg": 1e-8},
@@ -74,7 +85,8 @@ def oracle_configs(cfg, n_in, n_out, scales=None):
     e = cfg["encoding"]
     n = cfg["network"]
     if is_oneblob(cfg):  # no table: g is None, the MLP input is the padded OneBlob width
-        m = O.MlpConfig(O.next_multiple(n_in * e.get("n_bins", 16), 16), n_out, n.get("n_neurons", 128), n.get("n_hidden_layers", 5))
+        m = O.MlpConfig(O.next_multiple(n_in * e.get("n_bins", 16), 16), n_out, n.get("n_neurons", 128), n.get("n_hidden_layers", 5),
+                        n.get("activation", "ReLU"), n.get("output_activation", "None"))
         return None, m
     otype = e.get("otype", "Grid").lower()
     gtype = "Dense" if otype == "densegrid" else "Tiled" if otype == "tiledgrid" else e.get("type", "Hash")
@@ -82,7 +94,8 @@ def oracle_configs(cfg, n_in, n_out, scales=None):
                      e.get("base_resolution", 16), e.get("per_level_scale", 2.0), scales=scales, grid_type=gtype,
                      interpolation=e.get("interpolation", "Linear"))
     n = cfg["network"]
-    m = O.MlpConfig(O.next_multiple(g.n_features, 16), n_out, n.get("n_neurons", 128), n.get("n_hidden_layers", 5))
+    m = O.MlpConfig(O.next_multiple(g.n_features, 16), n_out, n.get("n_neurons", 128), n.get("n_hidden_layers", 5),
+                    n.get("activation", "ReLU"), n.get("output_activation", "None"))
     return g, m
 
 

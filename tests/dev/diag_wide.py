@@ -66,7 +66,7 @@ def run(name, cfg, n_in, n_out, B):
     dx = torch.zeros(B, E, dtype=torch.half, device=dev)
     check(lib.tcnn_b200_mlp_backward(native.handle, S(), B, ptr(enc), ptr(p16), ptr(dy), ptr(gp), ptr(dx), ptr(ws)))
     torch.cuda.synchronize()
-    dW, dx_ref = O.mlp_backward(m, p16_np[: m.n_params], enc_np, hidden, dy_np)
+    dW, dx_ref = O.mlp_backward(m, p16_np[: m.n_params], enc_np, hidden, dy_np, y=y)
     print("mlp_backward dx rel", common.rel_l2(dx.cpu().numpy(), dx_ref), flush=True)
     print("mlp_backward dW ", per_matrix(m, gp.cpu().numpy().astype(np.float64), dW), flush=True)
 
@@ -82,7 +82,7 @@ def run(name, cfg, n_in, n_out, B):
     check(lib.tcnn_b200_training_fwd_bwd(native.handle, S(), B, ptr(x), ptr(t), ptr(p16), ptr(grads), 128.0, 1, ptr(loss), ptr(out), ptr(ws)))
     torch.cuda.synchronize()
     lv, dyl = O.loss_l2(y, t_np, n_out, relative=(info.loss_type == 1))
-    dW, dxl = O.mlp_backward(m, p16_np[: m.n_params], enc_np, hidden, dyl)
+    dW, dxl = O.mlp_backward(m, p16_np[: m.n_params], enc_np, hidden, dyl, y=y)
     got = grads.cpu().numpy().astype(np.float64)
     print("train loss", loss.item(), "oracle", lv, flush=True)
     print("train dW ", per_matrix(m, got[: m.n_params], dW), flush=True)
@@ -101,6 +101,10 @@ def run(name, cfg, n_in, n_out, B):
 
 
 CASES = [
+    ("act_a", common.CONFIG_ACT_A, 2, 3, 512),
+    ("act_b", common.CONFIG_ACT_B, 2, 3, 512),
+    ("act_c", common.CONFIG_ACT_C, 2, 3, 512),
+    ("act_d", common.CONFIG_ACT_D, 3, 3, 512),
     ("wide_dp_3d", common.CONFIG_WIDE_DP, 3, 3, 512),
     ("wide_f4_3d", common.CONFIG_WIDE_F4, 3, 4, 1024),
     ("oneblob_128x5", common.CONFIG_ONEBLOB, 2, 3, 1024),

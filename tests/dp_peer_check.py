@@ -20,11 +20,13 @@ def main():
     torch.cuda.set_device(dev)
     dist.init_process_group("nccl", device_id=dev)
     B, steps = 1 << 14, 4
-    ref = tcnn.create_from_config(2, 3, common.CONFIG_1, seed=1337, device=dev, dp_mode="allreduce").trainer
+    # DP_CHECK_CONFIG=wide_dp: BASELINE config #5's shape (3-D grid + 128 x 3 network, unfused scatter) instead of config #1
+    CFG, n_in, n_out = (common.CONFIG_WIDE_DP, 3, 3) if os.environ.get("DP_CHECK_CONFIG") == "wide_dp" else (common.CONFIG_1, 2, 3)
+    ref = tcnn.create_from_config(n_in, n_out, CFG, seed=1337, device=dev, dp_mode="allreduce").trainer
     p0 = ref.params_full_precision.clone()
     batches = []
     for i in range(steps):
-        x_np, t_np = common.synth_inputs(B * world, 2, 3, seed=70 + i)
+        x_np, t_np = common.synth_inputs(B * world, n_in, n_out, seed=70 + i)
         s, e = tcnn.shard_bounds(B * world, rank, world)
         batches.append((torch.from_numpy(x_np[s:e]).to(dev), torch.from_numpy(t_np[s:e]).to(dev)))
     for x, t in batches:
@@ -32,7 +34,7 @@ def main():
     ref_loss = ref.loss()
     d_ref = (ref.params_full_precision - p0).double()
     for mc in (False, True):
-        tr = tcnn.create_from_config(2, 3, common.CONFIG_1, seed=1337, device=dev, dp_mode="peer", use_multicast=mc).trainer
+        tr = tcnn.create_from_config(n_in, n_out, CFG, seed=1337, device=dev, dp_mode="peer", use_multicast=mc).trainer
         if mc and not tr.peer_memory.multicast:
             if rank == 0:
                 print("no multicast mapping on this box: NVSwitch variant skipped")

@@ -26,6 +26,11 @@ CASES = {
     "wide_f4_3d_T14": (common.CONFIG_WIDE_F4, 3, 4),
     "oneblob_2d_128x5": (common.CONFIG_ONEBLOB, 2, 3),
     "oneblob16_2d_64x4": (common.CONFIG_ONEBLOB16, 2, 3),
+    # hidden / output activations other than ReLU / None, both MLP widths
+    "act_a_sigmoid_exp_64": (common.CONFIG_ACT_A, 2, 3),
+    "act_b_tanh_sigmoid_128": (common.CONFIG_ACT_B, 2, 3),
+    "act_c_squareplus_softplus_64": (common.CONFIG_ACT_C, 2, 3),
+    "act_d_leaky_leaky_128": (common.CONFIG_ACT_D, 3, 3),
 }
 
 
@@ -159,7 +164,7 @@ def test_mlp_forward_backward_vs_oracle(ctx, B):
         # oracle itself): the small batches use the first seeded batch without such a borderline activation.
         x_np, _ = common.synth_inputs(B, ctx.n_in, ctx.n_out, seed=seed)
         enc_np = common.oracle_encode(ctx.cfg, ctx.g, ctx.m, x_np, p16_np[ctx.m.n_params:])
-        if B > 1024 or not any(((h > 0) & (h < 1e-4)).any() for h in O.mlp_forward(ctx.m, p16_np[: ctx.m.n_params], enc_np)[1]):
+        if B > 1024 or not any(((h != 0) & (np.abs(h.astype(np.float32)) < 1e-4)).any() for h in O.mlp_forward(ctx.m, p16_np[: ctx.m.n_params], enc_np)[1]):
             break
     enc, p16 = torch.from_numpy(enc_np).to(ctx.dev), torch.from_numpy(p16_np).to(ctx.dev)
     out = torch.zeros(B, 16, dtype=torch.half, device=ctx.dev)
@@ -173,7 +178,7 @@ def test_mlp_forward_backward_vs_oracle(ctx, B):
     gp = torch.zeros(ctx.m.n_params, dtype=torch.half, device=ctx.dev)
     dx = torch.zeros(B, ctx.info.encoded_width, dtype=torch.half, device=ctx.dev)
     check(ctx.lib.tcnn_b200_mlp_backward(ctx.native.handle, S(), B, ptr(enc), ptr(p16), ptr(dy), ptr(gp), ptr(dx), ptr(ws)))
-    dW, dx_ref = O.mlp_backward(ctx.m, p16_np[: ctx.m.n_params], enc_np, hidden, dy_np)
+    dW, dx_ref = O.mlp_backward(ctx.m, p16_np[: ctx.m.n_params], enc_np, hidden, dy_np, y=y)
     # A handful of ReLU-mask flips (pre-activations within fp32 rounding of zero: 8 of 25 M elements at B = 2^16 between a
     # float32 and a float64 run of the ORACLE itself) carry a whole gradient element each: 1e-3 at large B is the oracle's
     # own reproducibility, not kernel error.
@@ -198,7 +203,7 @@ def test_training_fwd_bwd_vs_oracle_and_reference(ctx):
     enc = common.oracle_encode(ctx.cfg, ctx.g, ctx.m, x_np, p16_np[ctx.m.n_params:])
     y, hidden = O.mlp_forward(ctx.m, p16_np[: ctx.m.n_params], enc)
     lv, dy = O.loss_l2(y, t_np, ctx.n_out, relative=relative)
-    dW, dx = O.mlp_backward(ctx.m, p16_np[: ctx.m.n_params], enc, hidden, dy)
+    dW, dx = O.mlp_backward(ctx.m, p16_np[: ctx.m.n_params], enc, hidden, dy, y=y)
     got = grads.cpu().numpy().astype(np.float64)
     # oracle (same arithmetic)
     assert abs(loss.item() - lv) <= 2e-4 * abs(lv)
@@ -274,7 +279,7 @@ def test_module_autograd_surface(ctx):
         yo, hidden = O.mlp_forward(ctx.m, p16_np, enc)
         dy = np.zeros((B, 16), np.float16)
         dy[:, : ctx.n_out] = (2 * y.detach().float().cpu().numpy()).astype(np.float16)
-        _, dx = O.mlp_backward(ctx.m, p16_np, enc, hidden, dy)
+        _, dx = O.mlp_backward(ctx.m, p16_np, enc, hidden, dy, y=yo)
         ref = O.oneblob_backward_input(x_np, ctx.cfg["encoding"]["n_bins"], dx)
         assert common.rel_l2(x.grad.cpu().numpy(), ref) < 3e-2
 

@@ -140,7 +140,8 @@ def test_grid_input_gradient_restatement_matches_finite_differences():
 
 
 # ---- 128-neuron networks and the OneBlob encoding (BASELINE configs #2, #4, #5) -----------------------------------
-WIDE_NAMES = ["wide_dp_3d_T15", "wide_f4_3d_T14", "oneblob_2d_128x5", "oneblob16_2d_64x4"]
+WIDE_NAMES = ["wide_dp_3d_T15", "wide_f4_3d_T14", "oneblob_2d_128x5", "oneblob16_2d_64x4",
+              "act_a_sigmoid_exp_64", "act_b_tanh_sigmoid_128", "act_c_squareplus_softplus_64", "act_d_leaky_leaky_128"]
 
 
 @pytest.fixture(scope="module", params=WIDE_NAMES)
@@ -193,7 +194,7 @@ def test_wide_mlp_vs_reference(wide_case):
     lv, dy = O.loss_l2(z["output_padded"], wide_case["t"], n_out, relative=relative)
     assert abs(lv - float(z["loss"])) < 1e-5 * abs(lv)
     assert common.rel_l2(dy, z["dL_doutput"]) < 1e-6
-    dW, _ = O.mlp_backward(m, p16[: m.n_params], enc, hidden, O.loss_l2(y, wide_case["t"], n_out, relative=relative)[1])
+    dW, _ = O.mlp_backward(m, p16[: m.n_params], enc, hidden, O.loss_l2(y, wide_case["t"], n_out, relative=relative)[1], y=y)
     # last matrices first: the closer to the input, the more fp16-accumulated layers of the reference lie in between
     pos = m.n_params
     bars = [5e-3, 1.5e-2, 3e-2, 5e-2, 5e-2, 5e-2]

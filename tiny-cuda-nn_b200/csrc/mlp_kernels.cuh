@@ -17,6 +17,7 @@
 //     (kept as 64-bit register masks, the reference re-reads the stored activations) / the loss, and writes the fp16
 //     row back to shared memory for the next MMA.  No activation ever goes to HBM (the reference moves ~0.5 GB/step).
 #pragma once
+#include "activation.cuh"
 #include "grid_kernels.cuh"
 #include "ptx.cuh"
 
@@ -61,6 +62,8 @@ struct MlpArgs {
 	const float* positions;        // [B][D] fp32
 	__half* grid_grad;             // [n_params_grid]
 	__half* replicas;              // private copies of the replicated coarse levels (grid_kernels.cuh)
+	int activation;                // hidden layers (Activation, activation.cuh); kernels instantiated with GEN = false assume ReLU
+	int output_activation;         // applied to the (padded) output; its derivative, from the activated output, to dL/d(output)
 	long long* debug_clock;        // MLP_STAGE_CLOCKS builds only
 	// 128-neuron path (mlp_wide_kernels.cuh; host side only): per-layer buffers in the caller's workspace
 	__half* wide_hidden; __half* wide_gtmp; __half* wide_dy;
@@ -92,7 +95,17 @@ __host__ __device__ constexpr uint32_t mlp_tmem_cols(int n_hidden, bool train) {
 #endif
 constexpr int kScatterChunkUnroll = SCATTER_CHUNK_UNROLL;
 #define CTA_SYNC() do { if constexpr (NSG > 0) named_bar_sync(1, 128); else __syncthreads(); } while (0)
-template <int MODE, int H_, int FD = 0, int FF = 2, int NSG = 0>
+// GEN: hidden activation taken from a.activation at run time (any of activation.cuh); false = ReLU compiled in (hot kernels)
+template <bool GEN> __device__ __forceinline__ uint32_t hidden_act_forward(uint32_t pre, int act) {
+	if constexpr (GEN) return act == ACT_RELU ? h2_relu(pre) : act_forward_h2(pre, act);
+	else return h2_relu(pre);
+}
+template <bool GEN> __device__ __forceinline__ uint32_t hidden_act_backward(uint32_t grad, uint32_t post, int act) {
+	if constexpr (GEN) return act == ACT_RELU ? h2_mask_mul(grad, post) : act_backward_h2(grad, post, act);
+	else return h2_mask_mul(grad, post);
+}
+
+template <int MODE, int H_, int FD = 0, int FF = 2, int NSG = 0, bool GEN = false>
 __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const __grid_constant__ MlpArgs a, const __grid_constant__ GridParams gp) {
 	constexpr bool TRAIN = MODE != MODE_INFER;
 	constexpr bool FUSE_SCATTER = FD > 0;
@@ -280,14 +293,14 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 			for (int c = 0; c < 4; ++c) {
 				uint32_t pk[4];
 #pragma unroll
-				for (int j = 0; j < 4; ++j) pk[j] = h2_relu(pack_h2(__uint_as_float(v0[c * 8 + 2 * j]), __uint_as_float(v0[c * 8 + 2 * j + 1])));
+				for (int j = 0; j < 4; ++j) pk[j] = hidden_act_forward<GEN>(pack_h2(__uint_as_float(v0[c * 8 + 2 * j]), __uint_as_float(v0[c * 8 + 2 * j + 1])), a.activation);
 				sts128(dst + sw128(row, c), pk[0], pk[1], pk[2], pk[3]);
 			}
 #pragma unroll
 			for (int c = 0; c < 4; ++c) {
 				uint32_t pk[4];
 #pragma unroll
-				for (int j = 0; j < 4; ++j) pk[j] = h2_relu(pack_h2(__uint_as_float(v1[c * 8 + 2 * j]), __uint_as_float(v1[c * 8 + 2 * j + 1])));
+				for (int j = 0; j < 4; ++j) pk[j] = hidden_act_forward<GEN>(pack_h2(__uint_as_float(v1[c * 8 + 2 * j]), __uint_as_float(v1[c * 8 + 2 * j + 1])), a.activation);
 				sts128(dst + sw128(row, 4 + c), pk[0], pk[1], pk[2], pk[3]);
 			}
 			STAGE_CLOCK(a); // E: epilogue math + sts issued
@@ -314,6 +327,10 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 			uint32_t yk[8];
 #pragma unroll
 			for (int j = 0; j < 8; ++j) yk[j] = pack_h2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
+			if (a.output_activation != ACT_NONE) { // on the fp16 pre-activation, all 16 padded columns like the reference
+#pragma unroll
+				for (int j = 0; j < 8; ++j) yk[j] = act_forward_h2(yk[j], a.output_activation);
+			}
 			const size_t s = sample0 + row;
 			if (MODE != MODE_BACKWARD && a.output) {
 				uint4* o = reinterpret_cast<uint4*>(a.output + s * MLP_OUT);
@@ -348,12 +365,21 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 						dyk[j / 2] = pack_h2(ga, gb);
 					}
 				}
+				if (a.output_activation != ACT_NONE) { // activation_backward_output_gpu (fully_fused_mlp.cu:757-762): derivative from the activated output
+#pragma unroll
+					for (int j = 0; j < 8; ++j) dyk[j] = act_backward_h2(dyk[j], yk[j], a.output_activation);
+				}
 				sts128(g_addr + sw128(row, 0), dyk[0], dyk[1], dyk[2], dyk[3]);
 				sts128(g_addr + sw128(row, 1), dyk[4], dyk[5], dyk[6], dyk[7]);
 			}
 			if (MODE == MODE_BACKWARD) {
-				sts128(g_addr + sw128(row, 0), dy_in[0]);
-				sts128(g_addr + sw128(row, 1), dy_in[1]);
+				uint32_t dq[8] = {dy_in[0].x, dy_in[0].y, dy_in[0].z, dy_in[0].w, dy_in[1].x, dy_in[1].y, dy_in[1].z, dy_in[1].w};
+				if (a.output_activation != ACT_NONE) {
+#pragma unroll
+					for (int j = 0; j < 8; ++j) dq[j] = act_backward_h2(dq[j], yk[j], a.output_activation);
+				}
+				sts128(g_addr + sw128(row, 0), dq[0], dq[1], dq[2], dq[3]);
+				sts128(g_addr + sw128(row, 1), dq[4], dq[5], dq[6], dq[7]);
 			}
 		}
 		if constexpr (TRAIN) {
@@ -407,7 +433,7 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 					for (int j = 0; j < 4; ++j) {
 						const int e = (c & 3) * 8 + 2 * j;
 						const float f0 = __uint_as_float(c < 4 ? v0[e] : v1[e]), f1 = __uint_as_float(c < 4 ? v0[e + 1] : v1[e + 1]);
-						pk[j] = h2_mask_mul(pack_h2(f0, f1), aw[j]);
+						pk[j] = hidden_act_backward<GEN>(pack_h2(f0, f1), aw[j], a.activation);
 					}
 					sts128(dst + sw128(row, c), pk[0], pk[1], pk[2], pk[3]);
 				}

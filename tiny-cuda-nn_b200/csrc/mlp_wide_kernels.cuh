@@ -55,6 +55,7 @@ struct WideArgs {
 	uint32_t n_mlp_params, n_splits;
 	int loss_type;
 	float loss_scale, n_total;
+	int activation, output_activation; // Activation (activation.cuh): hidden layers / output
 };
 
 __host__ __device__ constexpr uint32_t wide_in_sub(uint32_t E) { return (E + 63u) / 64u; }
@@ -208,7 +209,7 @@ __global__ void __launch_bounds__(128 * NWG, 1) mlp_wide_forward_kernel(const __
 				for (int c = 0; c < 4; ++c) {
 					uint32_t pk[4];
 #pragma unroll
-					for (int j = 0; j < 4; ++j) pk[j] = h2_relu(pack_h2(__uint_as_float(v[c * 8 + 2 * j]), __uint_as_float(v[c * 8 + 2 * j + 1])));
+					for (int j = 0; j < 4; ++j) pk[j] = hidden_act_forward<true>(pack_h2(__uint_as_float(v[c * 8 + 2 * j]), __uint_as_float(v[c * 8 + 2 * j + 1])), a.activation);
 					sts128(act_addr + (cb >> 1) * SUB_BYTES + sw128(row, (cb & 1) * 4 + c), pk[0], pk[1], pk[2], pk[3]);
 				}
 			}
@@ -243,7 +244,23 @@ __global__ void __launch_bounds__(128 * NWG, 1) mlp_wide_forward_kernel(const __
 			uint32_t yk[8];
 #pragma unroll
 			for (int j = 0; j < 8; ++j) yk[j] = pack_h2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
+			if (a.output_activation != ACT_NONE) {
+#pragma unroll
+				for (int j = 0; j < 8; ++j) yk[j] = act_forward_h2(yk[j], a.output_activation);
+			}
 			const size_t s = sample0 + row;
+			if (MODE == MODE_BACKWARD && a.output_activation != ACT_NONE) {
+				// forward recomputation in front of a caller-supplied dL/d(output): leave dL/d(output) * activation'(output) for
+				// the backward and weight-gradient kernels (activation_backward_output_gpu, fully_fused_mlp.cu:757-762)
+				const uint4* d4 = reinterpret_cast<const uint4*>(a.dL_doutput + s * MLP_OUT);
+				const uint4 d0 = __ldg(d4), d1 = __ldg(d4 + 1);
+				uint32_t dq[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+#pragma unroll
+				for (int j = 0; j < 8; ++j) dq[j] = act_backward_h2(dq[j], yk[j], a.output_activation);
+				uint4* d = reinterpret_cast<uint4*>(a.dL_doutput_out + s * MLP_OUT);
+				d[0] = make_uint4(dq[0], dq[1], dq[2], dq[3]);
+				d[1] = make_uint4(dq[4], dq[5], dq[6], dq[7]);
+			}
 			if (MODE != MODE_BACKWARD && a.output) {
 				uint4* o = reinterpret_cast<uint4*>(a.output + s * MLP_OUT);
 				o[0] = make_uint4(yk[0], yk[1], yk[2], yk[3]);
@@ -275,6 +292,10 @@ __global__ void __launch_bounds__(128 * NWG, 1) mlp_wide_forward_kernel(const __
 						const float gb = (j + 1 < a.n_out) ? loss_elem(__half2float(yh[j + 1]), __ldg(a.target + s * a.n_out + j + 1)) : 0.f;
 						dyk[j / 2] = pack_h2(ga, gb);
 					}
+				}
+				if (a.output_activation != ACT_NONE) {
+#pragma unroll
+					for (int j = 0; j < 8; ++j) dyk[j] = act_backward_h2(dyk[j], yk[j], a.output_activation);
 				}
 				uint4* d = reinterpret_cast<uint4*>(a.dL_doutput_out + s * MLP_OUT);
 				d[0] = make_uint4(dyk[0], dyk[1], dyk[2], dyk[3]);
@@ -396,7 +417,7 @@ __global__ void __launch_bounds__(128 * NWG, 1) mlp_wide_backward_kernel(const _
 					const uint32_t aw[4] = {aw4.x, aw4.y, aw4.z, aw4.w};
 					uint32_t pk[4];
 #pragma unroll
-					for (int j = 0; j < 4; ++j) pk[j] = h2_mask_mul(pack_h2(__uint_as_float(v[c * 8 + 2 * j]), __uint_as_float(v[c * 8 + 2 * j + 1])), aw[j]);
+					for (int j = 0; j < 4; ++j) pk[j] = hidden_act_backward<true>(pack_h2(__uint_as_float(v[c * 8 + 2 * j]), __uint_as_float(v[c * 8 + 2 * j + 1])), aw[j], a.activation);
 					sts128(g_addr + (cb >> 1) * SUB_BYTES + sw128(row, (cb & 1) * 4 + c), pk[0], pk[1], pk[2], pk[3]);
 				}
 			}

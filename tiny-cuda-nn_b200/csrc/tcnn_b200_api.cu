@@ -43,6 +43,7 @@ struct tcnn_b200_plan {
 	bool device_scales = false;     // level scales were evaluated by the device (CUDA exp2f) rather than libm
 	int n_sms = 148;
 	// Adam extras
+	int activation = ACT_RELU, output_activation = ACT_NONE; // network.activation / network.output_activation (activation.cuh)
 	float non_matrix_lr_factor = 1.f, weight_clip = 0.f;
 	bool adabound = false;
 	int grid_type = 0;              // GRID_HASH / GRID_DENSE / GRID_TILED (GridType, grid_interface.h)
@@ -147,6 +148,21 @@ static void try_device_scales(tcnn_b200_plan* p) {
 	if (e != cudaSuccess) { cudaGetLastError(); return; }
 	build_levels(p, h);
 	p->device_scales = true;
+}
+
+// string_to_activation (src/common_host.cu:74-100).  Sine has no backward in the reference's fused kernels
+// (common_device.h:262-266: "requires stored pre-activations, which we don't have") and is not offered.
+static int parse_activation(const std::string& name) {
+	const std::string n = jsonmini::lower(name);
+	if (n == "none") return ACT_NONE;
+	if (n == "relu") return ACT_RELU;
+	if (n == "leakyrelu") return ACT_LEAKY_RELU;
+	if (n == "exponential") return ACT_EXPONENTIAL;
+	if (n == "sigmoid") return ACT_SIGMOID;
+	if (n == "squareplus") return ACT_SQUAREPLUS;
+	if (n == "softplus") return ACT_SOFTPLUS;
+	if (n == "tanh") return ACT_TANH;
+	FAIL("Invalid activation name: " + name + " (None, ReLU, LeakyReLU, Exponential, Sigmoid, Squareplus, Softplus, Tanh)");
 }
 
 static void parse_optimizer(tcnn_b200_plan* p, const jsonmini::Value& o) {
@@ -290,8 +306,8 @@ extern "C" int tcnn_b200_plan_create(const char* json_utf8, uint32_t n_input_dim
 	CHECK(in.n_neurons == 64 || in.n_neurons == 128, "FullyFusedMLP: this build implements n_neurons = 64 and 128 (16/32 are out of scope, DESIGN.md)");
 	if (in.n_neurons == 64) CHECK(in.n_hidden_layers >= 1 && in.n_hidden_layers <= (uint32_t)MLP_MAX_HIDDEN, "FullyFusedMLP: n_hidden_layers must be in [1, 4] at 64 neurons");
 	else CHECK(in.n_hidden_layers >= 1 && in.n_hidden_layers <= (uint32_t)WIDE_MAX_HIDDEN, "FullyFusedMLP: n_hidden_layers must be in [1, 8] at 128 neurons");
-	CHECK(jsonmini::lower(net.string("activation", "ReLU")) == "relu", "only activation 'ReLU' is implemented");
-	CHECK(jsonmini::lower(net.string("output_activation", "None")) == "none", "only output_activation 'None' is implemented");
+	p->activation = parse_activation(net.string("activation", "ReLU"));               // defaults: src/network.cu:107-113
+	p->output_activation = parse_activation(net.string("output_activation", "None"));
 	CHECK(n_output_dims >= 1 && n_output_dims <= 16, "n_output_dims must be in [1, 16] (fused last layer, fully_fused_mlp.cu:544)");
 	CHECK(in.encoded_width <= in.n_neurons, "encoded width above n_neurons is not implemented");
 	if (in.n_neurons == 128)
@@ -577,15 +593,15 @@ extern "C" int tcnn_b200_grid_indices(const tcnn_b200_plan* plan, void* stream, 
 #ifndef TCNN_B200_SCATTER_WARPGROUPS
 #define TCNN_B200_SCATTER_WARPGROUPS 2
 #endif
-template <int MODE, int H, int FD = 0, int FF = 2, int NSG = 0>
+template <int MODE, int H, int FD = 0, int FF = 2, int NSG = 0, bool GEN = false>
 static void launch_mlp_k(const tcnn_b200_plan* plan, cudaStream_t stream, const MlpArgs& a, uint32_t grid, const GridParams& gp, uint32_t smem) {
 	static thread_local uint32_t configured = 0;
 	if (configured < smem) {
-		CUDA_OK(cudaFuncSetAttribute(mlp_kernel<MODE, H, FD, FF, NSG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		CUDA_OK(cudaFuncSetAttribute(mlp_kernel<MODE, H, FD, FF, NSG, GEN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
 		configured = smem;
 	}
 	ProfileScope prof(plan, stream, PK_MLP);
-	mlp_kernel<MODE, H, FD, FF, NSG><<<grid, 128 + 128 * NSG, smem, stream>>>(a, gp);
+	mlp_kernel<MODE, H, FD, FF, NSG, GEN><<<grid, 128 + 128 * NSG, smem, stream>>>(a, gp);
 	launch_check("mlp_kernel");
 }
 template <int MODE, int H, int FD = 0, int FF = 2>
@@ -599,6 +615,10 @@ static void launch_mlp_h(const tcnn_b200_plan* plan, cudaStream_t stream, const 
 			launch_mlp_k<MODE, H, FD, FF, TCNN_B200_SCATTER_WARPGROUPS>(plan, stream, a, grid, gp, smem_ws);
 			return;
 		}
+	}
+	if constexpr (FD == 0) {
+		// hidden activation other than ReLU: the kernel variant that reads it at run time (never the fused-scatter kernels)
+		if (a.activation != ACT_RELU) { launch_mlp_k<MODE, H, 0, 2, 0, true>(plan, stream, a, grid, gp, smem); return; }
 	}
 	launch_mlp_k<MODE, H, FD, FF, 0>(plan, stream, a, grid, gp, smem);
 }
@@ -616,6 +636,7 @@ static void launch_mlp_wide(const tcnn_b200_plan* plan, cudaStream_t stream, con
 	w.input = a.input; w.params = a.params; w.output = a.output; w.output_f32 = a.output_f32; w.target = a.target;
 	w.hidden = a.wide_hidden; w.gtmp = a.wide_gtmp; w.dL_dinput = a.dL_dinput;
 	w.dL_doutput = MODE == MODE_TRAIN ? a.wide_dy : a.dL_doutput; w.dL_doutput_out = a.wide_dy;
+	w.activation = a.activation; w.output_activation = a.output_activation;
 	w.dW_partials = a.dW_partials; w.loss_partials = a.loss_partials; w.n_mlp_params = a.n_mlp_params; w.n_splits = n_splits;
 	w.loss_type = a.loss_type; w.loss_scale = a.loss_scale; w.n_total = a.n_total;
 	if (train) CHECK(w.hidden && w.gtmp && w.dL_doutput, "the 128-neuron training / backward pass needs the workspace");
@@ -627,6 +648,7 @@ static void launch_mlp_wide(const tcnn_b200_plan* plan, cudaStream_t stream, con
 		launch_check("mlp_wide_forward_kernel");
 	}
 	if constexpr (train) {
+		if (MODE == MODE_BACKWARD && a.output_activation != ACT_NONE) w.dL_doutput = a.wide_dy; // written by the forward recomputation
 		const bool want_dx = a.dL_dinput != nullptr;
 		{
 			ProfileScope prof(plan, stream, PK_MLP);
@@ -660,7 +682,7 @@ static void launch_mlp(const tcnn_b200_plan* plan, cudaStream_t stream, const Ml
 // Training kernel with the hash-table gradient scatter fused into its last stage; instantiated for the common shapes.
 static bool fused_scatter_available(const tcnn_b200_plan* plan) {
 	const uint32_t D = plan->info.n_input_dims, F = plan->info.n_features_per_level;
-	return !is_wide(plan) && plan->enc_kind == ENC_GRID && !plan->grid.smoothstep && (D == 2 || D == 3) && (F == 2 || F == 4);
+	return !is_wide(plan) && plan->enc_kind == ENC_GRID && !plan->grid.smoothstep && plan->activation == ACT_RELU && (D == 2 || D == 3) && (F == 2 || F == 4);
 }
 template <int H>
 static void launch_mlp_train_fused_h(const tcnn_b200_plan* plan, cudaStream_t stream, const MlpArgs& a, uint32_t grid, const GridParams& gp) {
@@ -694,6 +716,7 @@ static MlpArgs base_mlp_args(const tcnn_b200_plan* plan, uint32_t B, const __hal
 	a.loss_type = plan->info.loss_type;
 	a.n_total = (float)((uint64_t)B * plan->info.n_output_dims);
 	a.loss_scale = 128.f;
+	a.activation = plan->activation; a.output_activation = plan->output_activation;
 	return a;
 }
 
