@@ -57,6 +57,12 @@ CONFIG_ONEBLOB = {  # BASELINE.json configs[1]: data/config_oneblob.json of the 
     "encoding": {"otype": "OneBlob", "n_bins": 64},
     "network": {"otype": "FullyFusedMLP", "activation": "ReLU", "output_activation": "None", "n_neurons": 128, "n_hidden_layers": 5},
 }
+CONFIG_ONEBLOB_64 = {  # the 64-neuron curve of the same benchmark (bench_ours.cu runs config_oneblob.json at 64 and 128 neurons): 128 -> 64 x 5
+    "loss": {"otype": "RelativeL2"},
+    "optimizer": {"otype": "Adam", "learning_rate": 1e-2, "beta1": 0.9, "beta2": 0.99, "epsilon": 1e-8, "l2_reg": 1e-8},
+    "encoding": {"otype": "OneBlob", "n_bins": 64},
+    "network": {"otype": "FullyFusedMLP", "activation": "ReLU", "output_activation": "None", "n_neurons": 64, "n_hidden_layers": 5},
+}
 CONFIG_ONEBLOB16 = {  # OneBlob in front of the 64-neuron kernel (32 features)
     "loss": {"otype": "L2"},
     "optimizer": {"otype": "Adam", "learning_rate": 1e-3},

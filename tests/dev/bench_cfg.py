@@ -26,6 +26,8 @@ def big(cfg, log2_T):
 CASES = {  # name: (config, n_in, n_out, B)
     "oneblob_128x5_b18": (common.CONFIG_ONEBLOB, 2, 3, 1 << 18),
     "oneblob16_64x4_b18": (common.CONFIG_ONEBLOB16, 2, 3, 1 << 18),
+    "oneblob_64x5_b18": (common.CONFIG_ONEBLOB_64, 2, 3, 1 << 18),
+    "oneblob_64x5_b20": (common.CONFIG_ONEBLOB_64, 2, 3, 1 << 20),
     "oneblob_128x5_b20": (common.CONFIG_ONEBLOB, 2, 3, 1 << 20),
     "cfg4_T24_128x4_b20": (big(common.CONFIG_WIDE_F4, 24), 3, 4, 1 << 20),
     "cfg5_T22_128x3_b19": (big(common.CONFIG_WIDE_DP, 22), 3, 3, 1 << 19),

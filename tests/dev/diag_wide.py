@@ -101,6 +101,8 @@ def run(name, cfg, n_in, n_out, B):
 
 
 CASES = [
+    ("oneblob_64x5", common.CONFIG_ONEBLOB_64, 2, 3, 1024),
+    ("oneblob_64x5_big", common.CONFIG_ONEBLOB_64, 2, 3, 1 << 16),
     ("act_a", common.CONFIG_ACT_A, 2, 3, 512),
     ("act_b", common.CONFIG_ACT_B, 2, 3, 512),
     ("act_c", common.CONFIG_ACT_C, 2, 3, 512),

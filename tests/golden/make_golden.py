@@ -30,6 +30,7 @@ CASES = [  # name, config, n_in, n_out, B
     ("wide_f4_3d_T14", common.CONFIG_WIDE_F4, 3, 4, 512),
     ("oneblob_2d_128x5", common.CONFIG_ONEBLOB, 2, 3, 1024),
     ("oneblob16_2d_64x4", common.CONFIG_ONEBLOB16, 2, 3, 512),
+    ("oneblob_2d_64x5", common.CONFIG_ONEBLOB_64, 2, 3, 512),
     # other grid types / interpolation
     ("tiled_smooth_2d", common.CONFIG_TILED_SMOOTH, 2, 3, 512),
     ("dense_3d_f4", common.CONFIG_DENSE, 3, 3, 512),

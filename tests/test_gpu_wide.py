@@ -26,6 +26,7 @@ CASES = {
     "wide_f4_3d_T14": (common.CONFIG_WIDE_F4, 3, 4),
     "oneblob_2d_128x5": (common.CONFIG_ONEBLOB, 2, 3),
     "oneblob16_2d_64x4": (common.CONFIG_ONEBLOB16, 2, 3),
+    "oneblob_2d_64x5": (common.CONFIG_ONEBLOB_64, 2, 3),  # 128 inputs in front of 64 neurons x 5 (mlp_kernel<..., WIN>)
     # hidden / output activations other than ReLU / None, both MLP widths
     "act_a_sigmoid_exp_64": (common.CONFIG_ACT_A, 2, 3),
     "act_b_tanh_sigmoid_128": (common.CONFIG_ACT_B, 2, 3),

@@ -140,7 +140,7 @@ def test_grid_input_gradient_restatement_matches_finite_differences():
 
 
 # ---- 128-neuron networks and the OneBlob encoding (BASELINE configs #2, #4, #5) -----------------------------------
-WIDE_NAMES = ["wide_dp_3d_T15", "wide_f4_3d_T14", "oneblob_2d_128x5", "oneblob16_2d_64x4",
+WIDE_NAMES = ["wide_dp_3d_T15", "wide_f4_3d_T14", "oneblob_2d_128x5", "oneblob16_2d_64x4", "oneblob_2d_64x5",
               "act_a_sigmoid_exp_64", "act_b_tanh_sigmoid_128", "act_c_squareplus_softplus_64", "act_d_leaky_leaky_128"]
 
 

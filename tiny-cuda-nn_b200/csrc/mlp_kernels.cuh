@@ -34,7 +34,7 @@ constexpr int MLP_W = 64;          // hidden width handled by this kernel
 constexpr int MLP_TILE = 128;      // samples per tile = UMMA M
 constexpr int MLP_OUT = 16;        // padded output width (fully_fused_mlp.cu:544: fused last layer only for <=16 outputs)
 constexpr int TILE_BYTES = MLP_TILE * 128;
-constexpr int MLP_MAX_HIDDEN = 4;
+constexpr int MLP_MAX_HIDDEN = 5;       // 4 in the fused-scatter kernels; 5 = data/config_oneblob.json with 64 neurons (bench_ours.cu)
 
 enum MlpMode : int { MODE_INFER = 0, MODE_TRAIN = 1, MODE_BACKWARD = 2 };
 enum LossType : int { LOSS_L2 = 0, LOSS_RELATIVE_L2 = 1 };
@@ -76,13 +76,15 @@ __host__ __device__ constexpr uint32_t mlp_smem_bytes(int n_hidden, int in_width
 	// [ACT 0..H][G0][G1 (train)] [W_in 8K][W_inT E x 128 B][W_hid (H-1) x 8K][W_out 2K][barrier etc.]
 	// The weight region (>= 8K + 2K + 2K..8K + ...) directly follows the tiles, so "tile + 16 KB" (the second, unused
 	// 64-row atom of an M = 128 MN-major operand) is always mapped shared memory.
-	return 1024u /*align slack*/ + (uint32_t)(n_hidden + 1 + (train ? 2 : 0)) * TILE_BYTES + 8192u + (uint32_t)in_width * 128u
-		+ (uint32_t)(n_hidden - 1) * 8192u + 2048u + 256u + (n_hidden == 1 && in_width < 48 ? 4096u : 0u);
+	// in_width > 64 (kernel template WIN): the input tile ACT[0] and W_in have a second 64-column sub-tile each.
+	return 1024u /*align slack*/ + (uint32_t)(n_hidden + 1 + (train ? 2 : 0) + (in_width > 64 ? 1 : 0)) * TILE_BYTES + (in_width > 64 ? 16384u : 8192u)
+		+ (uint32_t)in_width * 128u + (uint32_t)(n_hidden - 1) * 8192u + 2048u + 256u + (n_hidden == 1 && in_width < 48 ? 4096u : 0u);
 }
 // extra shared memory of the warp-specialised fused kernel: the dL/d(encoded) hand-over slot
 __host__ __device__ constexpr uint32_t mlp_ws_slot_bytes(int in_width) { return 128u * (uint32_t)in_width * 2u; }
-__host__ __device__ constexpr uint32_t mlp_tmem_cols(int n_hidden, bool train) {
-	const uint32_t need = train ? 64u * (uint32_t)(n_hidden + 2) : 64u; // chain + dW_in + (H-1) dW_hid + dW_out
+__host__ __device__ constexpr uint32_t mlp_tmem_cols(int n_hidden, bool train, bool wide_in = false) {
+	// chain (128 columns if dL/d(input) can be 128 wide) + dW_in + (H-1) dW_hid + dW_out
+	const uint32_t need = train ? 64u * (uint32_t)(n_hidden + 2) + (wide_in ? 64u : 0u) : 64u;
 	return need <= 64 ? 64 : need <= 128 ? 128 : need <= 256 ? 256 : 512;
 }
 
@@ -105,7 +107,9 @@ template <bool GEN> __device__ __forceinline__ uint32_t hidden_act_backward(uint
 	else return h2_mask_mul(grad, post);
 }
 
-template <int MODE, int H_, int FD = 0, int FF = 2, int NSG = 0, bool GEN = false>
+// WIN: the input may be wider than the network (64 < in_width <= 128: OneBlob 2 x 64 in front of 64 neurons, bench_ours.cu) -
+// the input tile, W_in and the dL/d(input) accumulator get a second 64-column half
+template <int MODE, int H_, int FD = 0, int FF = 2, int NSG = 0, bool GEN = false, bool WIN = false>
 __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const __grid_constant__ MlpArgs a, const __grid_constant__ GridParams gp) {
 	constexpr bool TRAIN = MODE != MODE_INFER;
 	constexpr bool FUSE_SCATTER = FD > 0;
@@ -125,9 +129,10 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 
 	// ---- shared memory carve-up -------------------------------------------------------------------
 	uint8_t* act = smem;                                        // ACT[0..H], ACT[0] = input tile
-	uint8_t* gbuf = act + (H + 1) * TILE_BYTES;                 // G[0], G[1]
-	uint8_t* w_in = gbuf + (TRAIN ? 2 : 0) * TILE_BYTES;        // [64 out][128 B], in < E valid
-	uint8_t* w_inT = w_in + 8192;                               // [E in][128 B = 64 out]   (K-major B operand of dX = G * W_in)
+	constexpr uint32_t ACT0_EXTRA = WIN ? TILE_BYTES : 0;       // ACT[0] = input tile: columns 64.. in a second sub-tile right behind the first
+	uint8_t* gbuf = act + ACT0_EXTRA + (H + 1) * TILE_BYTES;    // G[0], G[1]
+	uint8_t* w_in = gbuf + (TRAIN ? 2 : 0) * TILE_BYTES;        // [64 out][128 B] (x 2 sub-tiles if WIN), in < E valid
+	uint8_t* w_inT = w_in + (WIN ? 16384 : 8192);               // [E in][128 B = 64 out]   (K-major B operand of dX = G * W_in)
 	uint8_t* w_hid = w_inT + E * 128;                            // (H-1) x [64 out][128 B]
 	uint8_t* w_out = w_hid + (H - 1) * 8192;                    // [16 out][128 B]
 	uint8_t* tail = w_out + 2048;
@@ -138,7 +143,8 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 	uint8_t* dx_slot = tail + 256 + ((H == 1 && E < 48) ? 4096 : 0); // WS: [128 rows][E halves], 16-byte chunks swizzled
 
 	// ---- one-time setup ---------------------------------------------------------------------------
-	constexpr uint32_t tmem_cols = mlp_tmem_cols((int)H, TRAIN);
+	constexpr uint32_t tmem_cols = mlp_tmem_cols((int)H, TRAIN, WIN);
+	static_assert(!WIN || (FD == 0 && NSG == 0), "inputs wider than 64 only in the unfused kernels");
 	if (warp == 0) tmem_alloc(tmem_slot, tmem_cols);
 	if (tid == 32) { mbar_init(bar, 1); mbar_init(bar2, 1); mbar_fence_init(); }
 
@@ -148,7 +154,7 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 		const uint32_t cpr_in = E / 8; // chunks per row of W_in
 		for (uint32_t q = tid; q < 64 * cpr_in; q += NT) {
 			const uint32_t r = q / cpr_in, c = q % cpr_in;
-			*reinterpret_cast<uint4*>(w_in + sw128(r, c)) = __ldg(reinterpret_cast<const uint4*>(p + r * E) + c);
+			*reinterpret_cast<uint4*>(w_in + (c >> 3) * 8192 + sw128(r, c & 7)) = __ldg(reinterpret_cast<const uint4*>(p + r * E) + c);
 		}
 		for (uint32_t q = tid; q < 64 * E; q += NT) { // transposed copy, element-wise (once per CTA)
 			const uint32_t o = q / E, i = q % E;
@@ -172,10 +178,10 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 	__syncthreads();
 	tc_fence_after();
 	const uint32_t tmem = *tmem_slot;
-	const uint32_t t_acc = tmem;                 // chain accumulator, 64 columns
-	const uint32_t t_dw_in = tmem + 64;          // D[in][out]   (transposed)
-	const uint32_t t_dw_hid = tmem + 128;        // D[out][in], 64 columns per hidden matmul
-	const uint32_t t_dw_out = tmem + 128 + 64 * (H - 1); // D[out(16 valid)][in]
+	const uint32_t t_acc = tmem;                 // chain accumulator, 64 columns (128 if WIN: dL/d(input) is up to 128 wide)
+	const uint32_t t_dw_in = tmem + (WIN ? 128 : 64); // D[in][out]   (transposed)
+	const uint32_t t_dw_hid = t_dw_in + 64;      // D[out][in], 64 columns per hidden matmul
+	const uint32_t t_dw_out = t_dw_hid + 64 * (H - 1); // D[out(16 valid)][in]
 	const uint32_t lane_off = (warp * 32) << 16; // this warp's TMEM lane window
 
 	// descriptors (constant parts)
@@ -227,11 +233,13 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 
 	// input tile prefetch: 128 rows x cpr 16-byte chunks, chunk q = tid + 128 j (coalesced), held in registers one tile ahead
 	const uint32_t cpr = E / 8;
-	uint4 xr[8];
+	constexpr uint32_t XR = WIN ? 16 : 8;
+	uint4 xr[XR];
+	auto act_tile = [&](uint32_t k) { return act_addr + (k ? ACT0_EXTRA : 0u) + k * TILE_BYTES; };
 	auto load_x = [&](uint32_t tile) {
 		const uint4* src = reinterpret_cast<const uint4*>(a.input + (size_t)tile * MLP_TILE * E);
 #pragma unroll
-		for (uint32_t j = 0; j < 8; ++j) if (j < cpr) xr[j] = ldg128_here(src + tid + 128 * j);
+		for (uint32_t j = 0; j < XR; ++j) if (j < cpr) xr[j] = ldg128_here(src + tid + 128 * j);
 	};
 	if (blockIdx.x < a.n_tiles) load_x(blockIdx.x);
 
@@ -240,10 +248,10 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 		// ---- input tile -> ACT[0] ------------------------------------------------------------------
 		if (pending2) { mbar_wait(bar2, phase2); phase2 ^= 1; pending2 = false; } // previous tile's dW_in MMA still reads ACT[0]
 #pragma unroll
-		for (uint32_t j = 0; j < 8; ++j) {
+		for (uint32_t j = 0; j < XR; ++j) {
 			if (j < cpr) {
 				const uint32_t q = tid + 128 * j, r = q / cpr, c = q % cpr;
-				sts128(act_addr + sw128(r, c), xr[j]);
+				sts128(act_addr + (c >> 3) * TILE_BYTES + sw128(r, c & 7), xr[j]);
 			}
 		}
 		STAGE_CLOCK(a); // E: epilogue math + sts issued
@@ -275,16 +283,17 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 			if (tid == 0) {
 				tc_fence_after();
 				const uint32_t ksteps = (k == 0 ? E : 64u) / 16;
-				const uint32_t a_addr = act_addr + k * TILE_BYTES;
+				const uint32_t a_addr = act_tile(k);
 				const uint32_t b_addr = k == 0 ? smem_u32(w_in) : smem_u32(w_hid) + (k - 1) * 8192;
-				for (uint32_t s = 0; s < ksteps; ++s)
-					umma_f16(t_acc, make_desc_sw128(a_addr + s * 32, LBO_K, SBO), make_desc_sw128(b_addr + s * 32, LBO_K, SBO), idesc_fwd64, s > 0);
+				for (uint32_t s = 0; s < ksteps; ++s) // K steps 4.. (layer 0, WIN) live in the second sub-tiles of ACT[0] / W_in
+					umma_f16(t_acc, make_desc_sw128(a_addr + (s >> 2) * TILE_BYTES + (s & 3) * 32, LBO_K, SBO),
+						make_desc_sw128(b_addr + (s >> 2) * 8192 + (s & 3) * 32, LBO_K, SBO), idesc_fwd64, s > 0);
 				umma_commit(bar);
 			}
 			mbar_wait(bar, phase); phase ^= 1;
 			STAGE_CLOCK(a); // W: MMA complete
 			tc_fence_after();
-			const uint32_t dst = act_addr + (k + 1) * TILE_BYTES;
+			const uint32_t dst = act_tile(k + 1);
 			uint32_t v0[32], v1[32];
 			tmem_ld32(t_acc + lane_off, v0);
 			tmem_ld32(t_acc + lane_off + 32, v1);
@@ -312,7 +321,7 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 		// ---- output layer --------------------------------------------------------------------------
 		if (tid == 0) {
 			tc_fence_after();
-			const uint32_t a_addr = act_addr + H * TILE_BYTES, b_addr = smem_u32(w_out);
+			const uint32_t a_addr = act_tile(H), b_addr = smem_u32(w_out);
 			for (uint32_t s = 0; s < 4; ++s)
 				umma_f16(t_acc, make_desc_sw128(a_addr + s * 32, LBO_K, SBO), make_desc_sw128(b_addr + s * 32, LBO_K, SBO), idesc_fwd16, s > 0);
 			umma_commit(bar);
@@ -407,7 +416,7 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 						// ... dW[out][in] += G^T[out x 128] * ACT_k[128 x in] (batch is K: both tiles viewed MN-major) runs under
 						// that epilogue; the tensor pipe executes in issue order, so the next stage's commit also covers it.
 						const uint32_t td = (k == H) ? t_dw_out : t_dw_hid + (k - 1) * 64;
-						const uint32_t ab = act_addr + k * TILE_BYTES;
+						const uint32_t ab = act_tile(k);
 						for (uint32_t s = 0; s < 8; ++s)
 							umma_f16(td, make_desc_sw128(ga + s * 2048, LBO_MN, SBO), make_desc_sw128(ab + s * 2048, LBO_MN, SBO), idesc_dw, (!first_tile) || s > 0);
 					}
@@ -417,7 +426,7 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 				tc_fence_after();
 				// ReLU' from this row's stored post-activation ACT[k] (fp16 > 0), applied to the packed fp16 gradient
 				const uint32_t dst = g_addr + (gcur ^ 1) * TILE_BYTES;
-				const uint32_t asrc = act_addr + k * TILE_BYTES;
+				const uint32_t asrc = act_tile(k);
 				uint32_t v0[32], v1[32];
 				tmem_ld32(t_acc + lane_off, v0);
 				tmem_ld32(t_acc + lane_off + 32, v1);
@@ -509,6 +518,20 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 		if (a.dW_partials != nullptr) {
 			float* out = a.dW_partials + (size_t)blockIdx.x * a.n_mlp_params;
 			const bool have = !first_tile; // CTA processed at least one tile
+			if constexpr (WIN) {
+				if (warp >= 2) { // inputs 64..127 of dW_in: accumulator rows of warps 2 and 3
+					const uint32_t r = warp * 32 + lane;
+#pragma unroll
+					for (int half_i = 0; half_i < 2; ++half_i) {
+						uint32_t v[32];
+						if (have) { tmem_ld32(t_dw_in + lane_off + half_i * 32, v); tmem_ld_wait(); }
+						if (r < E) {
+#pragma unroll
+							for (int j = 0; j < 32; ++j) out[(half_i * 32 + j) * E + r] = have ? __uint_as_float(v[j]) : 0.f;
+						}
+					}
+				}
+			}
 			if (warp < 2) {
 				const uint32_t r = warp * 32 + lane; // accumulator row 0..63
 				// dW_in: D[in = r][out = j]  ->  grads[out * E + in]

@@ -304,12 +304,12 @@ extern "C" int tcnn_b200_plan_create(const char* json_utf8, uint32_t n_input_dim
 	in.n_neurons = (uint32_t)net.number("n_neurons", 128);
 	in.n_hidden_layers = (uint32_t)net.number("n_hidden_layers", 5);
 	CHECK(in.n_neurons == 64 || in.n_neurons == 128, "FullyFusedMLP: this build implements n_neurons = 64 and 128 (16/32 are out of scope, DESIGN.md)");
-	if (in.n_neurons == 64) CHECK(in.n_hidden_layers >= 1 && in.n_hidden_layers <= (uint32_t)MLP_MAX_HIDDEN, "FullyFusedMLP: n_hidden_layers must be in [1, 4] at 64 neurons");
+	if (in.n_neurons == 64) CHECK(in.n_hidden_layers >= 1 && in.n_hidden_layers <= (uint32_t)MLP_MAX_HIDDEN, "FullyFusedMLP: n_hidden_layers must be in [1, 5] at 64 neurons");
 	else CHECK(in.n_hidden_layers >= 1 && in.n_hidden_layers <= (uint32_t)WIDE_MAX_HIDDEN, "FullyFusedMLP: n_hidden_layers must be in [1, 8] at 128 neurons");
 	p->activation = parse_activation(net.string("activation", "ReLU"));               // defaults: src/network.cu:107-113
 	p->output_activation = parse_activation(net.string("output_activation", "None"));
 	CHECK(n_output_dims >= 1 && n_output_dims <= 16, "n_output_dims must be in [1, 16] (fused last layer, fully_fused_mlp.cu:544)");
-	CHECK(in.encoded_width <= in.n_neurons, "encoded width above n_neurons is not implemented");
+	CHECK(in.encoded_width <= 128, "encoded width above 128 is not implemented");
 	if (in.n_neurons == 128)
 		CHECK(wide_fwd_smem(in.n_hidden_layers, in.encoded_width, 1) <= 232448u, "FullyFusedMLP 128: the weight matrices of this many hidden layers do not fit shared memory");
 	in.padded_output_width = 16;
@@ -377,7 +377,10 @@ static bool is_wide(const tcnn_b200_plan* p) { return p->info.n_neurons == 128; 
 // 128 neurons: number of batch splits of the weight-gradient kernel (one CTA per split and matrix, one CTA per SM).
 static uint32_t mlp_grid_size(const tcnn_b200_plan* p, uint32_t n_tiles, bool train) {
 	if (is_wide(p) && train) return std::max(1u, std::min(n_tiles, (uint32_t)p->n_sms / (p->info.n_hidden_layers + 1))); // one CTA per SM (192 KB ring)
-	const uint32_t per_sm = train ? 2u : 3u;
+	// resident CTAs per SM of the 64-neuron kernel: 2 when training (100 KB, 256 TMEM columns each), 3 for inference; the
+	// 5-hidden-layer / wide-input shapes need 512 TMEM columns or > 113 KB: one
+	const bool big = p->info.n_hidden_layers > 4 || p->info.encoded_width > 64;
+	const uint32_t per_sm = train ? (big ? 1u : 2u) : (big ? 2u : 3u);
 	return std::max(1u, std::min(n_tiles, (uint32_t)p->n_sms * per_sm));
 }
 // warpgroups (independent tiles) per CTA of the 128-neuron forward / backward kernels: two if shared memory allows
@@ -593,15 +596,15 @@ extern "C" int tcnn_b200_grid_indices(const tcnn_b200_plan* plan, void* stream, 
 #ifndef TCNN_B200_SCATTER_WARPGROUPS
 #define TCNN_B200_SCATTER_WARPGROUPS 2
 #endif
-template <int MODE, int H, int FD = 0, int FF = 2, int NSG = 0, bool GEN = false>
+template <int MODE, int H, int FD = 0, int FF = 2, int NSG = 0, bool GEN = false, bool WIN = false>
 static void launch_mlp_k(const tcnn_b200_plan* plan, cudaStream_t stream, const MlpArgs& a, uint32_t grid, const GridParams& gp, uint32_t smem) {
 	static thread_local uint32_t configured = 0;
 	if (configured < smem) {
-		CUDA_OK(cudaFuncSetAttribute(mlp_kernel<MODE, H, FD, FF, NSG, GEN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		CUDA_OK(cudaFuncSetAttribute(mlp_kernel<MODE, H, FD, FF, NSG, GEN, WIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
 		configured = smem;
 	}
 	ProfileScope prof(plan, stream, PK_MLP);
-	mlp_kernel<MODE, H, FD, FF, NSG, GEN><<<grid, 128 + 128 * NSG, smem, stream>>>(a, gp);
+	mlp_kernel<MODE, H, FD, FF, NSG, GEN, WIN><<<grid, 128 + 128 * NSG, smem, stream>>>(a, gp);
 	launch_check("mlp_kernel");
 }
 template <int MODE, int H, int FD = 0, int FF = 2>
@@ -618,6 +621,8 @@ static void launch_mlp_h(const tcnn_b200_plan* plan, cudaStream_t stream, const 
 	}
 	if constexpr (FD == 0) {
 		// hidden activation other than ReLU: the kernel variant that reads it at run time (never the fused-scatter kernels)
+		// inputs wider than the network (64 < E <= 128): the variant with a two-sub-tile input (activation read at run time)
+		if (a.in_width > 64) { launch_mlp_k<MODE, H, 0, 2, 0, true, true>(plan, stream, a, grid, gp, smem); return; }
 		if (a.activation != ACT_RELU) { launch_mlp_k<MODE, H, 0, 2, 0, true>(plan, stream, a, grid, gp, smem); return; }
 	}
 	launch_mlp_k<MODE, H, FD, FF, 0>(plan, stream, a, grid, gp, smem);
@@ -676,13 +681,15 @@ static void launch_mlp(const tcnn_b200_plan* plan, cudaStream_t stream, const Ml
 		case 2: launch_mlp_h<MODE, 2>(plan, stream, a, grid, plan->grid); break;
 		case 3: launch_mlp_h<MODE, 3>(plan, stream, a, grid, plan->grid); break;
 		case 4: launch_mlp_h<MODE, 4>(plan, stream, a, grid, plan->grid); break;
+		case 5: launch_mlp_h<MODE, 5>(plan, stream, a, grid, plan->grid); break;
 		default: FAIL("n_hidden_layers out of range");
 	}
 }
 // Training kernel with the hash-table gradient scatter fused into its last stage; instantiated for the common shapes.
 static bool fused_scatter_available(const tcnn_b200_plan* plan) {
 	const uint32_t D = plan->info.n_input_dims, F = plan->info.n_features_per_level;
-	return !is_wide(plan) && plan->enc_kind == ENC_GRID && !plan->grid.smoothstep && plan->activation == ACT_RELU && (D == 2 || D == 3) && (F == 2 || F == 4);
+	return !is_wide(plan) && plan->enc_kind == ENC_GRID && !plan->grid.smoothstep && plan->activation == ACT_RELU && plan->info.n_hidden_layers <= 4
+		&& plan->info.encoded_width <= 64 && (D == 2 || D == 3) && (F == 2 || F == 4);
 }
 template <int H>
 static void launch_mlp_train_fused_h(const tcnn_b200_plan* plan, cudaStream_t stream, const MlpArgs& a, uint32_t grid, const GridParams& gp) {
