@@ -109,6 +109,17 @@ int tcnn_b200_forward(const tcnn_b200_plan* plan, void* stream, uint32_t batch_s
 int tcnn_b200_backward(const tcnn_b200_plan* plan, void* stream, uint32_t batch_size, const float* x, const void* params_fp16,
                        const void* dL_doutput_fp16, void* dL_dparams_fp16, float* dL_dinput, void* workspace);
 
+/* DifferentiableObject::backward_backward_input (object.h:208-240) for the stand-alone grid encoding
+ * (encodings/grid.h:351-650, 902-1026): the backward pass of dL/dx = sum_k dL/dy_k * dy_k/dx.  Given dL_ddLdinput
+ * (fp32 [B][D]) and the dL_doutput (fp16 [B][encoded_width]) of the first backward pass, writes any of
+ *   dL_ddLdoutput fp16 [B][encoded_width]  (kernel_grid_backward_input_backward_dLdoutput),
+ *   dL_dparams    fp16 [n_params], overwritten (kernel_grid_backward_input_backward_grid),
+ *   dL_dinput     fp32 [B][D]               (kernel_grid_backward_input_backward_input).
+ * Encoding-only plans; like the reference, the fused MLP has no second order. */
+int tcnn_b200_backward_backward_input(const tcnn_b200_plan* plan, void* stream, uint32_t batch_size, const float* x, const void* params_fp16,
+                                      const float* dL_ddLdinput, const void* dL_doutput_fp16, void* dL_ddLdoutput_fp16, void* dL_dparams_fp16,
+                                      float* dL_dinput, void* workspace);
+
 /* Trainer::training_step minus the optimizer (trainer.h:163-184): forward, loss (losses/l2.h, relative_l2.h),
  * backward.  target fp32 [B][n_output_dims]; grads fp16 [n_params]: the MLP part is overwritten, the grid part is
  * accumulated into (zero_grid_grads != 0 clears it first; tcnn_b200_adam_step re-zeroes it for the next step).

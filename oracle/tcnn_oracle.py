@@ -707,3 +707,138 @@ def oneblob_backward_input(x: np.ndarray, n_bins: int, dy: np.ndarray) -> np.nda
         res += dy[:, np.arange(D) * n_bins + k].astype(np.float32) * (left - right)
         left = right
     return res
+
+
+# --------------------------------------------------------------------------------------------------
+# Second order of the grid encoding (encodings/grid.h:351-650): the backward pass of dL/dx = sum_k dL/dy_k * dy_k/dx,
+# i.e. the gradients of  S = sum_{i,d} dL_ddLdx[i,d] * dL/dx[i,d]  with respect to dL/dy, the table and x.
+# Used by eikonal / SDF losses through tcnn.Encoding (bindings/torch/tinycudann/modules.py:120-160).
+# --------------------------------------------------------------------------------------------------
+def smoothstep_2nd_derivative(v: np.ndarray) -> np.ndarray:
+    """common_device.h:809-811."""
+    return (F32(6.0) - F32(12.0) * v.astype(np.float32)).astype(np.float32)
+
+
+def _level_frac(cfg: GridConfig, x: np.ndarray, l: int):
+    """(interpolation weight w, dw/dfrac, d2w/dfrac2, cell) of level l - pos_fract with three outputs, common_device.h:825-839."""
+    frac, cell = pos_fract(x, F32(cfg.scales[l]))
+    if cfg.smooth:
+        return smoothstep(frac), smoothstep_derivative(frac), smoothstep_2nd_derivative(frac), cell
+    return frac, np.ones_like(frac), np.zeros_like(frac), cell
+
+
+def grid_dy_dx(cfg: GridConfig, x: np.ndarray, table: np.ndarray) -> np.ndarray:
+    """dy_k/dx_d as kernel_grid stores it (grid.h:171-211): fp32 [B, L*F, D]."""
+    B, D = x.shape
+    F = cfg.n_features_per_level
+    t = table.astype(np.float16).reshape(-1, F)
+    out = np.zeros((B, cfg.n_features, D), np.float32)
+    for l in range(cfg.n_levels):
+        scale, res = F32(cfg.scales[l]), int(cfg.resolutions[l])
+        w, dw, _, cell = _level_frac(cfg, x, l)
+        size, base = cfg.level_size(l), int(cfg.offsets[l])
+        for gd in range(D):
+            for idx in range(1 << (D - 1)):
+                weight = np.full(B, scale, np.float32)
+                pg = np.empty((B, D), np.uint32)
+                for nd in range(D - 1):
+                    dim = nd + 1 if nd >= gd else nd
+                    if (idx & (1 << nd)) == 0:
+                        weight = (weight * (F32(1.0) - w[:, dim])).astype(np.float32); pg[:, dim] = cell[:, dim]
+                    else:
+                        weight = (weight * w[:, dim]).astype(np.float32); pg[:, dim] = cell[:, dim] + np.uint32(1)
+                pg[:, gd] = cell[:, gd]
+                vl = t[base + grid_index(pg, size, res, cfg.hashed).astype(np.int64)].astype(np.float32)
+                pg[:, gd] = cell[:, gd] + np.uint32(1)
+                vr = t[base + grid_index(pg, size, res, cfg.hashed).astype(np.int64)].astype(np.float32)
+                out[:, l * F:(l + 1) * F, gd] += (weight[:, None] * (vr - vl)).astype(np.float32) * dw[:, gd, None]
+    return out
+
+
+def grid_bwd_bwd_dLddLdy(cfg: GridConfig, x: np.ndarray, table: np.ndarray, dL_ddLdx: np.ndarray) -> np.ndarray:
+    """kernel_grid_backward_input_backward_dLdoutput (grid.h:624-650): fp16 [B, L*F], result_k = sum_d dy_k/dx_d * dL_ddLdx_d."""
+    dydx = grid_dy_dx(cfg, x, table)
+    return np.einsum("bkd,bd->bk", dydx.astype(np.float32), dL_ddLdx.astype(np.float32)).astype(np.float16)
+
+
+def grid_bwd_bwd_grid(cfg: GridConfig, x: np.ndarray, dy: np.ndarray, dL_ddLdx: np.ndarray) -> np.ndarray:
+    """kernel_grid_backward_input_backward_grid (grid.h:351-451): float64 [n_params]; per corner pair along grad_dim the table
+    entries receive -/+ (half)weight * dL/dy with weight = scale * dL_ddLdx[gd] * dw[gd] * prod(other interpolation weights)."""
+    B, D = x.shape
+    F = cfg.n_features_per_level
+    g = np.zeros((int(cfg.offsets[-1]), F), np.float64)
+    for l in range(cfg.n_levels):
+        scale, res = F32(cfg.scales[l]), int(cfg.resolutions[l])
+        w, dw, _, cell = _level_frac(cfg, x, l)
+        size, base = cfg.level_size(l), int(cfg.offsets[l])
+        gl = dy[:, l * F:(l + 1) * F].astype(np.float16).astype(np.float32)
+        for gd in range(D):
+            grad_in = (scale * dL_ddLdx[:, gd].astype(np.float32) * dw[:, gd]).astype(np.float32)
+            for idx in range(1 << (D - 1)):
+                weight = grad_in.copy()
+                pg = np.empty((B, D), np.uint32)
+                for nd in range(D - 1):
+                    dim = nd + 1 if nd >= gd else nd
+                    if (idx & (1 << nd)) == 0:
+                        weight = (weight * (F32(1.0) - w[:, dim])).astype(np.float32); pg[:, dim] = cell[:, dim]
+                    else:
+                        weight = (weight * w[:, dim]).astype(np.float32); pg[:, dim] = cell[:, dim] + np.uint32(1)
+                for side, sign in ((0, -1.0), (1, 1.0)):
+                    pg[:, gd] = cell[:, gd] + np.uint32(side)
+                    wh = (F32(sign) * weight).astype(np.float16).astype(np.float32)
+                    prod = (wh[:, None] * gl).astype(np.float16)  # (GRAD_T)weight * grad: half multiply
+                    np.add.at(g, base + grid_index(pg, size, res, cfg.hashed).astype(np.int64), prod.astype(np.float64))
+    return g.reshape(-1)
+
+
+def grid_bwd_bwd_input(cfg: GridConfig, x: np.ndarray, table: np.ndarray, dy: np.ndarray, dL_ddLdx: np.ndarray) -> np.ndarray:
+    """kernel_grid_backward_input_backward_input (grid.h:453-622): fp32 [B, D], the Hessian of the interpolation contracted with
+    dL/dy and dL_ddLdx - diagonal part (Smoothstep only: d2w/dfrac2) and the cross terms between grad_dim and the other dims."""
+    B, D = x.shape
+    F = cfg.n_features_per_level
+    t = table.astype(np.float16).reshape(-1, F).astype(np.float32)
+    out = np.zeros((B, D), np.float32)
+    v = dL_ddLdx.astype(np.float32)
+    for l in range(cfg.n_levels):
+        scale, res = F32(cfg.scales[l]), int(cfg.resolutions[l])
+        w, dw, d2w, cell = _level_frac(cfg, x, l)
+        size, base = cfg.level_size(l), int(cfg.offsets[l])
+        gl = dy[:, l * F:(l + 1) * F].astype(np.float16).astype(np.float32)
+
+        def calc(pg, weight):
+            vals = t[base + grid_index(pg, size, res, cfg.hashed).astype(np.int64)]
+            return ((vals * gl).sum(axis=1) * weight).astype(np.float32)
+
+        diag = (scale * scale * v * d2w).astype(np.float32)
+        other = (scale * scale * v * dw).astype(np.float32)
+        for gd in range(D):
+            acc = np.zeros(B, np.float32)
+            for idx in range(1 << (D - 1)):
+                if cfg.smooth:
+                    weight = diag[:, gd].copy()
+                    pg = np.empty((B, D), np.uint32)
+                    for nd in range(D - 1):
+                        dim = nd + 1 if nd >= gd else nd
+                        if (idx & (1 << nd)) == 0:
+                            weight = weight * (F32(1.0) - w[:, dim]); pg[:, dim] = cell[:, dim]
+                        else:
+                            weight = weight * w[:, dim]; pg[:, dim] = cell[:, dim] + np.uint32(1)
+                    pg[:, gd] = cell[:, gd]; acc += calc(pg, -weight)
+                    pg[:, gd] = cell[:, gd] + np.uint32(1); acc += calc(pg, weight)
+                for og in range(D - 1):
+                    rog = og + 1 if og >= gd else og  # the other gradient dim
+                    weight = (other[:, rog] * dw[:, gd]).astype(np.float32)
+                    pg = np.empty((B, D), np.uint32)
+                    for nd in range(D - 1):
+                        dim = nd + 1 if nd >= rog else nd
+                        if (idx & (1 << nd)) == 0:
+                            weight = weight * (F32(1.0) - w[:, dim]) if dim != gd else -weight
+                            pg[:, dim] = cell[:, dim]
+                        else:
+                            if dim != gd:
+                                weight = weight * w[:, dim]
+                            pg[:, dim] = cell[:, dim] + np.uint32(1)
+                    pg[:, rog] = cell[:, rog]; acc += calc(pg, -weight)
+                    pg[:, rog] = cell[:, rog] + np.uint32(1); acc += calc(pg, weight)
+            out[:, gd] += acc
+    return out

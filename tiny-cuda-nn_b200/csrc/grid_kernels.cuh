@@ -424,6 +424,165 @@ __global__ void __launch_bounds__(256) grid_backward_input_kernel(const __grid_c
 	for (int d = 0; d < D; ++d) dL_dx[(size_t)i * D + d] = result[d];
 }
 
+// ---- second order (encodings/grid.h:351-650) --------------------------------------------------------------------
+// The backward pass of dL/dx = sum_k dL/dy_k * dy_k/dx (grid_backward_input_kernel): given dL_ddLdx = d(loss)/d(dL/dx), the
+// gradients with respect to dL/dy, the table and x.  Needed when a loss contains the spatial gradient of the encoded field
+// (eikonal / SDF terms) and autograd differentiates through the first backward pass (modules.py:120-160 of the reference).
+__device__ __forceinline__ float smoothstep_2nd_derivative_dev(float v) { return 6.0f - 12.0f * v; }
+
+// Interpolation weight, its first and second derivative with respect to the fractional coordinate (common_device.h:825-839).
+template <int D>
+__device__ __forceinline__ void level_weights(const GridParams& gp, const GridLevel& lv, const float (&p)[D], float (&w)[D], float (&dw)[D], float (&d2w)[D], uint32_t (&cell)[D]) {
+#pragma unroll
+	for (int d = 0; d < D; ++d) {
+		float f;
+		pos_fract_dev(p[d], lv.scale, f, cell[d]);
+		w[d] = gp.smoothstep ? smoothstep_dev(f) : f;
+		dw[d] = gp.smoothstep ? smoothstep_derivative_dev(f) : 1.0f;
+		d2w[d] = gp.smoothstep ? smoothstep_2nd_derivative_dev(f) : 0.0f;
+	}
+}
+
+// kernel_grid_backward_input_backward_dLdoutput (grid.h:624-650) and kernel_grid_backward_input_backward_input
+// (grid.h:453-622) in one pass over the levels; thread = sample (no float atomics over levels / features as in the reference).
+//   dL_ddLdy[i][k] = sum_d dy_k/dx_d * dL_ddLdx[i][d]                    (fp16 [B][padded_width], nullable)
+//   dL_dx[i][d]    = Hessian of the interpolation contracted with dL/dy and dL_ddLdx: the diagonal part exists for
+//                    Smoothstep only (d2w), the cross terms couple grad_dim with every other dim (fp32 [B][D], nullable)
+template <int D, int F>
+__global__ void __launch_bounds__(256) grid_backward_backward_input_kernel(const __grid_constant__ GridParams gp, uint32_t B, const float* __restrict__ x,
+	const __half* __restrict__ grid, const __half* __restrict__ dL_denc, const float* __restrict__ dL_ddLdx, __half* __restrict__ dL_ddLdy, float* __restrict__ dL_dx) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= B) return;
+	float p[D], v[D], result[D];
+	load_position<D>(x, i, p);
+#pragma unroll
+	for (int d = 0; d < D; ++d) { v[d] = dL_ddLdx[(size_t)i * D + d]; result[d] = 0.f; }
+	for (uint32_t level = 0; level < gp.n_levels; ++level) {
+		const GridLevel& lv = gp.level[level];
+		const __half* table = grid + (size_t)lv.offset * F;
+		float w[D], dw[D], d2w[D]; uint32_t cell[D];
+		level_weights<D>(gp, lv, p, w, dw, d2w, cell);
+		float dl[F];
+#pragma unroll
+		for (int f = 0; f < F; ++f) dl[f] = dL_denc ? __half2float(dL_denc[(size_t)i * gp.padded_width + level * F + f]) : 0.f;
+		// sum_f table[index][f] * dL/dy[f] * weight   (calc_dLdx, grid.h:529-540)
+		auto contract = [&](const uint32_t (&pg)[D], float weight) {
+			const uint32_t index = grid_index_dev<D>(lv, pg);
+			float s = 0.f;
+#pragma unroll
+			for (int f = 0; f < F; ++f) s += __half2float(table[(size_t)index * F + f]) * dl[f] * weight;
+			return s;
+		};
+		float dydx[F][D];
+#pragma unroll
+		for (int f = 0; f < F; ++f)
+#pragma unroll
+			for (int d = 0; d < D; ++d) dydx[f][d] = 0.f;
+#pragma unroll
+		for (int gd = 0; gd < D; ++gd) {
+			float grad_out = 0.f;
+#pragma unroll
+			for (int idx = 0; idx < (1 << (D - 1)); ++idx) {
+				// first derivative along gd (dy/dx, grid.h:171-211) and the diagonal of the Hessian share corners and the weight
+				float weight = 1.0f; uint32_t pg[D];
+#pragma unroll
+				for (int nd = 0; nd < D - 1; ++nd) {
+					const int dim = nd >= gd ? nd + 1 : nd;
+					if ((idx & (1 << nd)) == 0) { weight *= 1.0f - w[dim]; pg[dim] = cell[dim]; }
+					else { weight *= w[dim]; pg[dim] = cell[dim] + 1u; }
+				}
+				if (dL_ddLdy) {
+					pg[gd] = cell[gd];
+					const uint32_t il = grid_index_dev<D>(lv, pg);
+					pg[gd] = cell[gd] + 1u;
+					const uint32_t ir = grid_index_dev<D>(lv, pg);
+#pragma unroll
+					for (int f = 0; f < F; ++f)
+						dydx[f][gd] += lv.scale * weight * (__half2float(table[(size_t)ir * F + f]) - __half2float(table[(size_t)il * F + f])) * dw[gd];
+				}
+				if (dL_dx) {
+					if (gp.smoothstep) {
+						const float wd = lv.scale * lv.scale * v[gd] * d2w[gd] * weight;
+						pg[gd] = cell[gd]; grad_out += contract(pg, -wd);
+						pg[gd] = cell[gd] + 1u; grad_out += contract(pg, wd);
+					}
+#pragma unroll
+					for (int og = 0; og < D - 1; ++og) {
+						const int rog = og >= gd ? og + 1 : og; // the other gradient dim
+						float wo = lv.scale * lv.scale * v[rog] * dw[rog] * dw[gd];
+						uint32_t pq[D];
+#pragma unroll
+						for (int nd = 0; nd < D - 1; ++nd) {
+							const int dim = nd >= rog ? nd + 1 : nd;
+							if ((idx & (1 << nd)) == 0) { if (dim != gd) wo *= 1.0f - w[dim]; else wo *= -1.0f; pq[dim] = cell[dim]; }
+							else { if (dim != gd) wo *= w[dim]; pq[dim] = cell[dim] + 1u; }
+						}
+						pq[rog] = cell[rog]; grad_out += contract(pq, -wo);
+						pq[rog] = cell[rog] + 1u; grad_out += contract(pq, wo);
+					}
+				}
+			}
+			result[gd] += grad_out;
+		}
+		if (dL_ddLdy) {
+#pragma unroll
+			for (int f = 0; f < F; ++f) {
+				float r = 0.f;
+#pragma unroll
+				for (int d = 0; d < D; ++d) r += dydx[f][d] * v[d];
+				dL_ddLdy[(size_t)i * gp.padded_width + level * F + f] = __float2half(r);
+			}
+		}
+	}
+	if (dL_ddLdy) for (uint32_t k = gp.n_features; k < gp.padded_width; ++k) dL_ddLdy[(size_t)i * gp.padded_width + k] = __float2half(0.f);
+	if (dL_dx) {
+#pragma unroll
+		for (int d = 0; d < D; ++d) dL_dx[(size_t)i * D + d] = result[d];
+	}
+}
+
+// kernel_grid_backward_input_backward_grid (grid.h:351-451): thread = sample x level; the two corners of every pair along
+// grad_dim receive -/+ (half)weight * dL/dy with weight = scale * dL_ddLdx[gd] * dw[gd] * prod(other interpolation weights).
+template <int D, int F>
+__global__ void __launch_bounds__(256) grid_backward_backward_grid_kernel(const __grid_constant__ GridParams gp, uint32_t B, const float* __restrict__ x,
+	const __half* __restrict__ dL_denc, const float* __restrict__ dL_ddLdx, __half* __restrict__ grid_grad) {
+	static_assert(F % 2 == 0, "fp16 gradient scatter needs F >= 2");
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= B) return;
+	const uint32_t level = blockIdx.y;
+	const GridLevel& lv = gp.level[level];
+	float p[D];
+	load_position<D>(x, i, p);
+	float w[D], dw[D], d2w[D]; uint32_t cell[D];
+	level_weights<D>(gp, lv, p, w, dw, d2w, cell);
+	__half2 g2[F / 2];
+#pragma unroll
+	for (int f = 0; f < F / 2; ++f) g2[f] = *reinterpret_cast<const __half2*>(dL_denc + (size_t)i * gp.padded_width + level * F + 2 * f);
+	__half* gt = grid_grad + (size_t)lv.offset * F;
+#pragma unroll
+	for (int gd = 0; gd < D; ++gd) {
+		const float grad_in = lv.scale * dL_ddLdx[(size_t)i * D + gd] * dw[gd];
+#pragma unroll
+		for (int idx = 0; idx < (1 << (D - 1)); ++idx) {
+			float weight = grad_in; uint32_t pg[D];
+#pragma unroll
+			for (int nd = 0; nd < D - 1; ++nd) {
+				const int dim = nd >= gd ? nd + 1 : nd;
+				if ((idx & (1 << nd)) == 0) { weight *= 1.0f - w[dim]; pg[dim] = cell[dim]; }
+				else { weight *= w[dim]; pg[dim] = cell[dim] + 1u; }
+			}
+#pragma unroll
+			for (int side = 0; side < 2; ++side) {
+				pg[gd] = cell[gd] + (uint32_t)side;
+				const __half2 wh = __float2half2_rn(side ? weight : -weight);
+				__half* dst = gt + (size_t)grid_index_dev<D>(lv, pg) * F;
+#pragma unroll
+				for (int f = 0; f < F / 2; ++f) red_add_h2(dst + 2 * f, __hmul2(wh, g2[f]));
+			}
+		}
+	}
+}
+
 // Identity encoding in front of a stand-alone Network (encodings/identity.h:46-90, src/cpp_api.cu:151-153): fp32 [B][n_in] ->
 // fp16 [B][width], columns >= n_in are ONE (identity.h:63), so that the first layer can learn a bias through them.
 // Thread = sample x 8-column chunk.

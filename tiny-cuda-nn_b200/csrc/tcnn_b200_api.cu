@@ -879,6 +879,33 @@ extern "C" int tcnn_b200_backward(const tcnn_b200_plan* plan, void* stream_, uin
 	API_END
 }
 
+// DifferentiableObject::backward_backward_input (object.h:208-240) of the grid encoding (grid.h:902-1026).
+extern "C" int tcnn_b200_backward_backward_input(const tcnn_b200_plan* plan, void* stream_, uint32_t B, const float* x, const void* params,
+	const float* dL_ddLdinput, const void* dL_doutput, void* dL_ddLdoutput, void* dL_dparams, float* dL_dinput, void* workspace) {
+	API_BEGIN
+	require_device(plan); check_batch(B);
+	CHECK(plan->kind == PLAN_ENCODING && plan->enc_kind == ENC_GRID,
+		"second-order gradients exist for the stand-alone grid encoding only (FullyFusedMLP has no backward_backward_input in the reference either)");
+	CHECK(x && params && dL_ddLdinput && dL_doutput, "null argument");
+	(void)workspace;
+	cudaStream_t stream = (cudaStream_t)stream_;
+	const dim3 g((B + 255) / 256, 1, 1);
+	if (dL_ddLdoutput || dL_dinput) {
+		ProfileScope prof(plan, stream, PK_GRID_BWD);
+		GRID_DISPATCH(grid_backward_backward_input_kernel, plan, g, stream, plan->grid, B, x, (const __half*)params, (const __half*)dL_doutput, dL_ddLdinput,
+			(__half*)dL_ddLdoutput, dL_dinput);
+		launch_check("grid_backward_backward_input_kernel");
+	}
+	if (dL_dparams) { // GradientMode::Overwrite
+		ProfileScope prof(plan, stream, PK_GRID_BWD);
+		CUDA_OK(cudaMemsetAsync(dL_dparams, 0, plan->info.n_params_grid * 2, stream));
+		const dim3 gl((B + 255) / 256, plan->info.n_levels, 1);
+		GRID_DISPATCH(grid_backward_backward_grid_kernel, plan, gl, stream, plan->grid, B, x, (const __half*)dL_doutput, dL_ddLdinput, (__half*)dL_dparams);
+		launch_check("grid_backward_backward_grid_kernel");
+	}
+	API_END
+}
+
 extern "C" int tcnn_b200_training_fwd_bwd(const tcnn_b200_plan* plan, void* stream_, uint32_t B, const float* x, const float* target,
 	const void* params, void* grads, float loss_scale, int zero_grid_grads, float* loss_out, void* output_fp16, void* workspace) {
 	API_BEGIN

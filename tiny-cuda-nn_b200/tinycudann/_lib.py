@@ -74,6 +74,7 @@ _SIGNATURES = {
     "tcnn_b200_inference": (C.c_int, [_P, _P, C.c_uint32, _P, _P, _P, _P, _P]),
     "tcnn_b200_forward": (C.c_int, [_P, _P, C.c_uint32, _P, _P, _P, _P]),
     "tcnn_b200_backward": (C.c_int, [_P, _P, C.c_uint32, _P, _P, _P, _P, _P, _P]),
+    "tcnn_b200_backward_backward_input": (C.c_int, [_P, _P, C.c_uint32, _P, _P, _P, _P, _P, _P, _P, _P]),
     "tcnn_b200_training_fwd_bwd": (C.c_int, [_P, _P, C.c_uint32, _P, _P, _P, _P, C.c_float, C.c_int, _P, _P, _P]),
     "tcnn_b200_adam_step": (C.c_int, [_P, _P, C.c_float, C.c_uint32, _P, _P, _P, _P, _P, _P, C.c_int]),
     "tcnn_b200_adam_step_range": (C.c_int, [_P, _P, C.c_float, C.c_uint32, _P, _P, _P, _P, _P, _P, C.c_int, C.c_uint64, C.c_uint64]),

@@ -88,6 +88,25 @@ class NativeModule:
         return dx, g
 
 
+    def bwd_bwd_input(self, x, params, dL_ddLdinput, doutput, want_doutput_grad=True, want_params_grad=True, want_input_grad=True):
+        """DifferentiableObject::backward_backward_input (object.h:208-240): -> (dL_ddLdoutput fp16 [B, width], dL_dparams fp16, dL_dinput fp32)."""
+        B = x.shape[0]
+        dd = torch.empty(B, self.n_output_dims(), dtype=torch.half, device=x.device) if want_doutput_grad else None
+        g = torch.empty(self.n_params(), dtype=torch.half, device=x.device) if want_params_grad else None
+        dx = torch.empty(B, int(self.info.n_input_dims), dtype=torch.float32, device=x.device) if want_input_grad else None
+        check(self.lib.tcnn_b200_backward_backward_input(self.handle, _stream_ptr(), B, ptr(x), ptr(params), ptr(dL_ddLdinput), ptr(doutput),
+                                                         ptr(dd), ptr(g), ptr(dx), None))
+        return dd, g, dx
+
+
+def _empty_like(t):
+    return torch.empty([], dtype=t.dtype, device=t.device)
+
+
+def _none_if_empty(t):
+    return None if t.dim() == 0 else t
+
+
 class _module_function(torch.autograd.Function):
     @staticmethod
     def forward(ctx, native, x, params, loss_scale, need_ctx):
@@ -102,12 +121,40 @@ class _module_function(torch.autograd.Function):
         if doutput is None:
             return None, None, None, None, None
         x, params = ctx.saved_tensors
+        # the backward pass is itself a differentiable function (second order of the grid encoding, modules.py:120-160 of the reference)
+        dx, g = _module_function_backward.apply(ctx, doutput, x, params)
+        return None, _none_if_empty(dx), _none_if_empty(g), None, None
+
+
+class _module_function_backward(torch.autograd.Function):
+    """dL/dinput and dL/dparams from dL/doutput.  Its own backward supports, like the reference, the gradients that flow through
+    dL/dinput: d(dL_dinput)/d(dL_doutput), d(dL_dinput)/d(params), d(dL_dinput)/d(input); nothing through dL/dparams."""
+
+    @staticmethod
+    def forward(ctx, fwd, doutput, x, params):
+        ctx.fwd = fwd
+        ctx.save_for_backward(x, params, doutput)
         with torch.no_grad():
-            scaled = (doutput.to(torch.float) * ctx.loss_scale).to(torch.half).contiguous()
-            dx, g = ctx.native.bwd(ctx.ws, x, params, scaled, ctx.needs_input_grad[2], ctx.needs_input_grad[1])
-            dx = None if dx is None else dx / ctx.loss_scale
-            g = None if g is None else g / ctx.loss_scale
-        return None, dx, g, None, None
+            scaled = (doutput.to(torch.float) * fwd.loss_scale).to(torch.half).contiguous()
+            dx, g = fwd.native.bwd(fwd.ws, x, params, scaled, fwd.needs_input_grad[2], fwd.needs_input_grad[1])
+            dx = _empty_like(x) if dx is None else dx / fwd.loss_scale
+            g = _empty_like(params) if g is None else g / fwd.loss_scale
+        return dx, g
+
+    @staticmethod
+    def backward(ctx, ddx, dg):
+        if ddx is None or ddx.dim() == 0:
+            return None, None, None, None
+        x, params, doutput = ctx.saved_tensors
+        fwd = ctx.fwd
+        with torch.no_grad():
+            scaled = (doutput.to(torch.float) * fwd.loss_scale).to(torch.half).contiguous()
+            d_doutput, d_params, d_x = fwd.native.bwd_bwd_input(x, params, ddx.to(torch.float).contiguous(), scaled,
+                                                                 ctx.needs_input_grad[1], ctx.needs_input_grad[3], ctx.needs_input_grad[2])
+            # d_doutput depends on ddx only; the other two on ddx * doutput, which carried the loss scale
+            d_params = None if d_params is None else d_params / fwd.loss_scale
+            d_x = None if d_x is None else d_x / fwd.loss_scale
+        return None, d_doutput, d_x, d_params
 
 
 class Module(torch.nn.Module):
