@@ -10,6 +10,9 @@
 //       params after one Adam step.
 //   ref_driver curve <cfg.json> <n_in> <n_out> <B> <n_steps> <seed> <outdir>
 //       loss after every step on pcg32-generated batches with the analytic target below.
+//   ref_driver bwdbwd <cfg.json> <n_in> <B> <input.f32> <table.f16> <dL_dy.f16 [B][padded]> <v.f32 [B][n_in]> <outdir>
+//       second order of the stand-alone encoding (encodings/grid.h:902-1026): forward with input gradients, backward,
+//       backward_backward_input; dumps dL/dx, dL2/d(dL/dy), dL2/dtable, dL2/dx.
 //   ref_driver bench <cfg.json> <n_in> <n_out> <B> <steps> <warmup>
 //       one JSON line: training / inference ms per step (CUDA events), device-resident inputs and
 //       host-buffer (H2D inside the timed region) variants.
@@ -230,6 +233,45 @@ static float time_loop(cudaStream_t stream, uint32_t steps, const std::function<
 	return ms / (float)steps;
 }
 
+static int mode_bwdbwd(int argc, char** argv) {
+	if (argc < 10) { std::cerr << "bwdbwd: bad args\n"; return 2; }
+	json cfg = load_cfg(argv[2]);
+	const uint32_t n_in = std::stoul(argv[3]), B = std::stoul(argv[4]);
+	const std::string out = argv[9];
+	auto in_raw = read_file(argv[5]), tab_raw = read_file(argv[6]), dy_raw = read_file(argv[7]), v_raw = read_file(argv[8]);
+	cudaStream_t stream; CUDA_CHECK_THROW(cudaStreamCreate(&stream));
+	std::unique_ptr<Encoding<precision_t>> enc{create_encoding<precision_t>(n_in, cfg.value("encoding", json::object()))};
+	const size_t P = enc->n_params();
+	const uint32_t W = enc->padded_output_width();
+	if (in_raw.size() != (size_t)B * n_in * 4 || v_raw.size() != in_raw.size() || tab_raw.size() != P * 2 || dy_raw.size() != (size_t)B * W * 2) {
+		std::cerr << "bwdbwd: size mismatch P=" << P << " W=" << W << "\n"; return 2;
+	}
+	GPUMemory<precision_t> table(P), grads(P);
+	CUDA_CHECK_THROW(cudaMemcpy(table.data(), tab_raw.data(), tab_raw.size(), cudaMemcpyHostToDevice));
+	grads.memset(0);
+	enc->set_params(table.data(), table.data(), grads.data());
+
+	GPUMatrix<float> input(n_in, B), v(n_in, B), dL_dx(n_in, B), dL2_dx(n_in, B);
+	CUDA_CHECK_THROW(cudaMemcpy(input.data(), in_raw.data(), in_raw.size(), cudaMemcpyHostToDevice));
+	CUDA_CHECK_THROW(cudaMemcpy(v.data(), v_raw.data(), v_raw.size(), cudaMemcpyHostToDevice));
+	// dL/dy arrives sample-major ([B][W] = column-major W x B = AoS); results are written in the same layout
+	GPUMatrixDynamic<precision_t> dy(W, B, AoS), dd(W, B, AoS), y(W, B, enc->preferred_output_layout());
+	CUDA_CHECK_THROW(cudaMemcpy(dy.data(), dy_raw.data(), dy_raw.size(), cudaMemcpyHostToDevice));
+	dd.memset(0); dL_dx.memset(0); dL2_dx.memset(0);
+
+	auto ctx = enc->forward(stream, input, &y, false, true);
+	enc->backward(stream, *ctx, input, y, dy, &dL_dx, false, GradientMode::Ignore);
+	enc->backward_backward_input(stream, *ctx, input, v, dy, &dd, &dL2_dx, false, GradientMode::Overwrite);
+	CUDA_CHECK_THROW(cudaStreamSynchronize(stream));
+	write_dev(out + "/dL_dx.f32", dL_dx.data(), (size_t)B * n_in);
+	write_dev(out + "/dL2_ddLdy.f16", (const uint16_t*)dd.data(), (size_t)B * W);
+	write_dev(out + "/dL2_dtable.f16", (const uint16_t*)grads.data(), P);
+	write_dev(out + "/dL2_dx.f32", dL2_dx.data(), (size_t)B * n_in);
+	std::ofstream(out + "/meta.json") << json{{"n_params", P}, {"padded_output_width", W}, {"output_width", enc->output_width()}, {"B", B}, {"n_in", n_in}}.dump(1);
+	std::cout << "bwdbwd ok P=" << P << " W=" << W << std::endl;
+	return 0;
+}
+
 static int mode_bench(int argc, char** argv) {
 	if (argc < 8) { std::cerr << "bench: bad args\n"; return 2; }
 	json cfg = load_cfg(argv[2]);
@@ -283,6 +325,7 @@ int main(int argc, char** argv) {
 		if (mode == "dump") return mode_dump(argc, argv);
 		if (mode == "curve") return mode_curve(argc, argv);
 		if (mode == "bench") return mode_bench(argc, argv);
+		if (mode == "bwdbwd") return mode_bwdbwd(argc, argv);
 		std::cerr << "unknown mode " << mode << "\n";
 		return 2;
 	} catch (const std::exception& e) {

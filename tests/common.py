@@ -126,3 +126,22 @@ def oracle_encode(cfg, g, m, x, table16):
     enc = np.zeros((x.shape[0], m.n_input), np.float16)
     enc[:, : g.n_features] = O.grid_forward(g, x, table16)
     return enc
+
+
+# stand-alone grid encodings of the second-order tests / goldens: name -> (n_in, encoding config)
+SECOND_ORDER_ENCODINGS = {
+    "hash2d_linear": (2, {"otype": "HashGrid", "n_levels": 6, "n_features_per_level": 2, "log2_hashmap_size": 10, "base_resolution": 4, "per_level_scale": 1.6}),
+    "hash3d_smooth": (3, {"otype": "HashGrid", "n_levels": 4, "n_features_per_level": 4, "log2_hashmap_size": 9, "base_resolution": 4, "per_level_scale": 1.5, "interpolation": "Smoothstep"}),
+    "tiled2d_smooth": (2, {"otype": "TiledGrid", "n_levels": 4, "n_features_per_level": 2, "base_resolution": 8, "per_level_scale": 1.5, "interpolation": "Smoothstep"}),
+}
+
+
+def second_order_inputs(n_in, n_table, n_features, padded_width, B=256, seed=5):
+    """Seeded inputs of one second-order case: positions, fp16 table, fp16 dL/dy [B][padded] (padding zero), v = dL2/d(dL/dx)."""
+    rng = np.random.default_rng(seed)
+    x = rng.random((B, n_in), dtype=np.float32)
+    table = rng.uniform(-1, 1, n_table).astype(np.float16)
+    dy = np.zeros((B, padded_width), np.float16)
+    dy[:, :n_features] = rng.standard_normal((B, n_features)).astype(np.float16)
+    v = rng.standard_normal((B, n_in)).astype(np.float32)
+    return x, table, dy, v

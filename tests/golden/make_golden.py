@@ -68,11 +68,41 @@ def curves(outdir):
             print(name, "saved", os.path.getsize(os.path.join(outdir, name + ".npz")), "bytes", flush=True)
 
 
+def second_order(outdir):
+    """`ref_driver bwdbwd`: the reference's GridEncoding forward / backward / backward_backward_input on seeded inputs."""
+    for name, (n_in, enc) in common.SECOND_ORDER_ENCODINGS.items():
+        with tempfile.TemporaryDirectory() as d:
+            with open(os.path.join(d, "cfg.json"), "w") as f:
+                json.dump({"encoding": enc}, f)
+            g = common.oracle_configs({"encoding": enc, "network": {"n_neurons": 64, "n_hidden_layers": 1}}, n_in, 1)[0]
+            W = (g.n_features + 7) // 8 * 8
+            B = 256
+            x, table, dy, v = common.second_order_inputs(n_in, g.n_params, g.n_features, W, B)
+            for fn, a in (("x.f32", x), ("table.f16", table), ("dy.f16", dy), ("v.f32", v)):
+                a.tofile(os.path.join(d, fn))
+            r = subprocess.run([REF, "bwdbwd", os.path.join(d, "cfg.json"), str(n_in), str(B)] + [os.path.join(d, fn) for fn in ("x.f32", "table.f16", "dy.f16", "v.f32")] + [d],
+                               capture_output=True, text=True, timeout=600)
+            print(name, r.returncode, r.stdout.strip(), r.stderr.strip()[-400:], flush=True)
+            if r.returncode != 0:
+                continue
+            meta = json.load(open(os.path.join(d, "meta.json")))
+            assert meta["padded_output_width"] == W and meta["n_params"] == g.n_params, meta
+            rd = lambda fn, dt: np.fromfile(os.path.join(d, fn), dtype=dt)  # noqa: E731
+            np.savez_compressed(
+                os.path.join(outdir, "bwdbwd_" + name + ".npz"), encoding=json.dumps(enc), n_in=n_in, B=B, seed=5,
+                dL_dx=rd("dL_dx.f32", np.float32).reshape(B, n_in), dL2_ddLdy=rd("dL2_ddLdy.f16", np.float16).reshape(B, W),
+                dL2_dtable=rd("dL2_dtable.f16", np.float16), dL2_dx=rd("dL2_dx.f32", np.float32).reshape(B, n_in))
+            print(name, "saved", os.path.getsize(os.path.join(outdir, "bwdbwd_" + name + ".npz")), "bytes", flush=True)
+
+
 def main(outdir):
     os.makedirs(outdir, exist_ok=True)
+    if os.environ.get("GOLDEN_SECOND_ORDER_ONLY"):
+        return second_order(outdir)
     only = [n for n in os.environ.get("GOLDEN_ONLY", "").split(",") if n]  # restrict to these case names (no curves)
     if not only:
         curves(outdir)
+        second_order(outdir)
     if os.environ.get("GOLDEN_CURVES_ONLY"):
         return
     for name, cfg, n_in, n_out, B in CASES:

@@ -10,11 +10,7 @@ pytestmark = pytest.mark.gpu
 from oracle import tcnn_oracle as O  # noqa: E402
 from tests import common  # noqa: E402
 
-ENCODINGS = {
-    "hash2d_linear": (2, {"otype": "HashGrid", "n_levels": 6, "n_features_per_level": 2, "log2_hashmap_size": 10, "base_resolution": 4, "per_level_scale": 1.6}),
-    "hash3d_smooth": (3, {"otype": "HashGrid", "n_levels": 4, "n_features_per_level": 4, "log2_hashmap_size": 9, "base_resolution": 4, "per_level_scale": 1.5, "interpolation": "Smoothstep"}),
-    "tiled2d_smooth": (2, {"otype": "TiledGrid", "n_levels": 4, "n_features_per_level": 2, "base_resolution": 8, "per_level_scale": 1.5, "interpolation": "Smoothstep"}),
-}
+ENCODINGS = common.SECOND_ORDER_ENCODINGS
 
 
 @pytest.fixture(scope="module")
@@ -84,3 +80,22 @@ def test_encoding_double_backward_matches_oracle(dev, name):
     assert common.rel_l2(g_c.float().cpu().numpy(), O.grid_bwd_bwd_dLddLdy(g, x_np, table_np, v_np)) < 3e-3
     assert common.rel_l2(g_params.float().cpu().numpy().astype(np.float64), O.grid_bwd_bwd_grid(g, x_np, c_np, v_np)) < 2e-2
     assert common.rel_l2(g_x.cpu().numpy(), O.grid_bwd_bwd_input(g, x_np, table_np, c_np, v_np)) < 2e-3
+
+
+@pytest.mark.parametrize("name", sorted(ENCODINGS))
+def test_c_abi_vs_reference_dump(dev, name):
+    """The same seeded inputs the reference's GridEncoding was run on (tests/golden/bwdbwd_*.npz, `ref_driver bwdbwd`)."""
+    import tinycudann as tcnn
+    from tests.test_oracle_second_order import load_second_order_case
+    D, enc = ENCODINGS[name]
+    g, z, (x_np, table_np, dy_np, v_np) = load_second_order_case(name)
+    native = tcnn.NativeModule(D, 0, {"encoding": enc})
+    W = native.info.encoded_width
+    dy_pad = np.zeros((x_np.shape[0], W), np.float16)
+    dy_pad[:, : g.n_features] = dy_np[:, : g.n_features]
+    x, table, dy, v = (torch.from_numpy(a).to(dev) for a in (x_np, table_np, dy_pad, v_np))
+    dd, gp, dx = native.bwd_bwd_input(x, table, v, dy)
+    F = g.n_features
+    assert common.rel_l2(dd.cpu().numpy()[:, :F], z["dL2_ddLdy"][:, :F]) < 1e-3
+    assert common.rel_l2(gp.cpu().numpy(), z["dL2_dtable"]) < 5e-3  # fp16 atomics on both sides
+    assert common.rel_l2(dx.cpu().numpy(), z["dL2_dx"]) < 1e-5

@@ -61,3 +61,31 @@ def test_second_order_restatement_matches_autograd(D, interp, gtype):
     got_x = O.grid_bwd_bwd_input(cfg, x_np, table_np, dy_np, v_np).astype(np.float64)
     ref_x = np.zeros_like(got_x) if g_x is None else g_x.numpy()
     assert np.linalg.norm(got_x - ref_x) <= 2e-4 * max(np.linalg.norm(ref_x), 1.0)
+
+
+# --- pinned to the reference: dumps of its own GridEncoding::backward_backward_input (ref_driver bwdbwd, make_golden.py) ---
+import os  # noqa: E402
+
+from tests import common  # noqa: E402
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def load_second_order_case(name):
+    n_in, enc = common.SECOND_ORDER_ENCODINGS[name]
+    z = np.load(os.path.join(GOLDEN, f"bwdbwd_{name}.npz"))
+    g = common.oracle_configs({"encoding": enc, "network": {"n_neurons": 64, "n_hidden_layers": 1}}, n_in, 1)[0]
+    W = (g.n_features + 7) // 8 * 8
+    assert z["dL2_ddLdy"].shape == (256, W) and z["dL2_dtable"].size == g.n_params
+    return g, z, common.second_order_inputs(n_in, g.n_params, g.n_features, W, int(z["B"]), int(z["seed"]))
+
+
+@pytest.mark.parametrize("name", sorted(common.SECOND_ORDER_ENCODINGS))
+def test_oracle_second_order_vs_reference_dump(name):
+    g, z, (x, table, dy, v) = load_second_order_case(name)
+    F = g.n_features
+    assert common.rel_l2(O.grid_backward_input(g, x, table, dy[:, :F]), z["dL_dx"]) < 1e-5
+    assert common.rel_l2(O.grid_bwd_bwd_dLddLdy(g, x, table, v), z["dL2_ddLdy"][:, :F]) < 5e-5  # fp16 result
+    assert not z["dL2_ddLdy"][:, F:].any()
+    assert common.rel_l2(O.grid_bwd_bwd_grid(g, x, dy[:, :F], v).reshape(-1), z["dL2_dtable"]) < 3e-3  # fp16 atomics in the reference
+    assert common.rel_l2(O.grid_bwd_bwd_input(g, x, table, dy[:, :F], v), z["dL2_dx"]) < 1e-5
