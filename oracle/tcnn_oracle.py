@@ -177,7 +177,7 @@ class GridConfig:
     # optional per-level (scale, resolution) table dumped from the device (CUDA exp2f vs libm)
     scales: np.ndarray | None = None
     grid_type: str = "Hash"           # Hash | Dense | Tiled (grid.h:702-712; DenseGrid / TiledGrid otypes, grid.h:1180-1208)
-    interpolation: str = "Linear"     # Linear | Smoothstep (common_device.h:801-807)
+    interpolation: str = "Linear"     # Nearest | Linear | Smoothstep (common_device.h:801-807; Nearest: grid.h:121-139)
     offsets: np.ndarray = field(init=False)
     resolutions: np.ndarray = field(init=False)
 
@@ -224,6 +224,10 @@ class GridConfig:
     @property
     def smooth(self) -> bool:
         return self.interpolation.lower() == "smoothstep"
+
+    @property
+    def nearest(self) -> bool:
+        return self.interpolation.lower() == "nearest"
 
 
 def smoothstep(v: np.ndarray) -> np.ndarray:
@@ -276,6 +280,9 @@ def grid_corners(cfg: GridConfig, x: np.ndarray, level: int):
     multiplied in dim order starting from 1.0f.   x: fp32 [B, D] -> (uint32 [B, 2^D], fp32 [B, 2^D])."""
     D = cfg.n_dims
     frac, cell = pos_fract(x, cfg.scales[level])
+    if cfg.nearest:  # grid.h:121-139 / 279-282: the entry at pos_grid alone, weight 1 (no interpolation)
+        hs, res = cfg.level_size(level), int(cfg.resolutions[level])
+        return grid_index(cell, hs, res, cfg.hashed)[:, None], np.ones((x.shape[0], 1), dtype=np.float32)
     if cfg.smooth:
         frac = smoothstep(frac)
     B = x.shape[0]
@@ -308,6 +315,9 @@ def grid_forward(cfg: GridConfig, x: np.ndarray, table: np.ndarray) -> np.ndarra
     for l in range(cfg.n_levels):
         idx, w = grid_corners(cfg, x, l)
         base = int(cfg.offsets[l])
+        if cfg.nearest:  # the entry itself, no arithmetic (grid.h:121-129) - keeps -0.0
+            out[:, l * F:(l + 1) * F] = t[base + idx[:, 0].astype(np.int64)]
+            continue
         res = np.zeros((B, F), dtype=np.float16)
         for c in range(idx.shape[1]):
             val = t[base + idx[:, c].astype(np.int64)]
@@ -358,6 +368,8 @@ def grid_backward_input(cfg: GridConfig, x: np.ndarray, table: np.ndarray, dy: n
     F = cfg.n_features_per_level
     t = table.astype(np.float16).reshape(-1, F)
     result = np.zeros((B, D), np.float32)
+    if cfg.nearest:  # "Gradient is zero when there's no interpolation" (grid.h:131-137)
+        return result
     for l in range(cfg.n_levels):
         scale, res = F32(cfg.scales[l]), int(cfg.resolutions[l])
         frac, cell = pos_fract(x, F32(scale))

@@ -34,6 +34,12 @@ CONFIG_TILED_SMOOTH = {  # TiledGrid + Smoothstep interpolation (grid.h:702-712,
     "encoding": {"otype": "TiledGrid", "n_levels": 8, "n_features_per_level": 2, "base_resolution": 16, "per_level_scale": 1.5, "interpolation": "Smoothstep"},
     "network": {"otype": "FullyFusedMLP", "activation": "ReLU", "output_activation": "None", "n_neurons": 64, "n_hidden_layers": 2},
 }
+CONFIG_NEAREST = {  # Nearest "interpolation" (grid.h:121-139, 279-282): hashed and dense levels, 3-D
+    "loss": {"otype": "L2"},
+    "optimizer": {"otype": "Adam", "learning_rate": 1e-3},
+    "encoding": {"otype": "HashGrid", "n_levels": 8, "n_features_per_level": 2, "log2_hashmap_size": 12, "base_resolution": 4, "per_level_scale": 1.6, "interpolation": "Nearest"},
+    "network": {"otype": "FullyFusedMLP", "activation": "ReLU", "output_activation": "None", "n_neurons": 64, "n_hidden_layers": 2},
+}
 CONFIG_DENSE = {  # DenseGrid, Linear, 3-D, F = 4
     "loss": {"otype": "L2"},
     "optimizer": {"otype": "Adam", "learning_rate": 1e-3},

@@ -34,6 +34,7 @@ CASES = [  # name, config, n_in, n_out, B
     # other grid types / interpolation
     ("tiled_smooth_2d", common.CONFIG_TILED_SMOOTH, 2, 3, 512),
     ("dense_3d_f4", common.CONFIG_DENSE, 3, 3, 512),
+    ("nearest_3d_T12", common.CONFIG_NEAREST, 3, 3, 512),
     # hidden / output activations
     ("act_a_sigmoid_exp_64", common.CONFIG_ACT_A, 2, 3, 512),
     ("act_b_tanh_sigmoid_128", common.CONFIG_ACT_B, 2, 3, 512),

@@ -22,6 +22,7 @@ GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
 CASES = {
     "tiled_smooth_2d": (common.CONFIG_TILED_SMOOTH, 2, 3),
     "dense_3d_f4": (common.CONFIG_DENSE, 3, 3),
+    "nearest_3d_T12": (common.CONFIG_NEAREST, 3, 3),
     "wide_dp_3d_T15": (common.CONFIG_WIDE_DP, 3, 3),
     "wide_f4_3d_T14": (common.CONFIG_WIDE_F4, 3, 4),
     "oneblob_2d_128x5": (common.CONFIG_ONEBLOB, 2, 3),

@@ -44,6 +44,7 @@ struct GridParams {
 	uint32_t rep_entries;    // entries per replica (sum of the replicated levels' sizes)
 	uint32_t image_subs;     // 0: encoded rows [B][padded_width]; n > 0: tile images with n sub-tiles per tile (wide_image_chunk)
 	uint32_t smoothstep;     // interpolation: 0 = Linear, 1 = Smoothstep (weights w -> w^2 (3 - 2 w), common_device.h:801-807)
+	uint32_t nearest;        // interpolation Nearest (grid.h:121-139): own kernels below, never reaches the interpolating ones
 	GridLevel level[MAX_LEVELS];
 };
 
@@ -423,6 +424,60 @@ __global__ void __launch_bounds__(256) grid_backward_input_kernel(const __grid_c
 #pragma unroll
 	for (int d = 0; d < D; ++d) dL_dx[(size_t)i * D + d] = result[d];
 }
+
+// ---- Nearest "interpolation" (grid.h:121-139, 279-282): the entry of the cell the shifted position falls into, weight 1 ----
+// Same launch shapes as grid_forward_kernel / grid_backward_kernel (thread = one sample's 16-byte chunk of the encoded row).
+template <int D, int F>
+__global__ void __launch_bounds__(256) grid_nearest_forward_kernel(const __grid_constant__ GridParams gp, uint32_t B,
+	const float* __restrict__ x, const __half* __restrict__ grid, __half* __restrict__ encoded) {
+	constexpr int LEVELS_PER_CHUNK = 8 / F;
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= B) return;
+	const uint32_t chunk = blockIdx.y;
+	float p[D];
+	load_position<D>(x, i, p);
+	union { uint4 v; typename FeatVec<F>::type f[LEVELS_PER_CHUNK]; } out;
+	out.v = make_uint4(0, 0, 0, 0);
+#pragma unroll
+	for (int s = 0; s < LEVELS_PER_CHUNK; ++s) {
+		const uint32_t level = chunk * LEVELS_PER_CHUNK + s;
+		if (level >= gp.n_levels) break;
+		const GridLevel& lv = gp.level[level];
+		float frac; uint32_t cell[D];
+#pragma unroll
+		for (int d = 0; d < D; ++d) pos_fract_dev(p[d], lv.scale, frac, cell[d]);
+		const uint32_t idx = grid_index_dev<D>(lv, cell);
+		out.f[s] = __ldg(reinterpret_cast<const typename FeatVec<F>::type*>(grid + ((size_t)lv.offset + idx) * F));
+	}
+	const size_t off = gp.image_subs ? wide_image_chunk(i, chunk, gp.image_subs) : ((size_t)i * gp.padded_width + chunk * 8) * 2;
+	*reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(encoded) + off) = out.v;
+}
+
+template <int D, int F>
+__global__ void __launch_bounds__(256) grid_nearest_backward_kernel(const __grid_constant__ GridParams gp, uint32_t B,
+	const float* __restrict__ x, const __half* __restrict__ dL_denc, __half* __restrict__ grid_grad, uint32_t chunk_begin) {
+	constexpr int LEVELS_PER_CHUNK = 8 / F;
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= B) return;
+	const uint32_t chunk = chunk_begin + blockIdx.y;
+	float p[D];
+	load_position<D>(x, i, p);
+	union { uint4 v; __half2 h2[4]; } g;
+	g.v = __ldg(reinterpret_cast<const uint4*>(dL_denc + (size_t)i * gp.padded_width + chunk * 8));
+#pragma unroll
+	for (int s = 0; s < LEVELS_PER_CHUNK; ++s) {
+		const uint32_t level = chunk * LEVELS_PER_CHUNK + s;
+		if (level >= gp.n_levels) break;
+		const GridLevel& lv = gp.level[level];
+		float frac; uint32_t cell[D];
+#pragma unroll
+		for (int d = 0; d < D; ++d) pos_fract_dev(p[d], lv.scale, frac, cell[d]);
+		__half* entry = grid_grad + ((size_t)lv.offset + grid_index_dev<D>(lv, cell)) * F;
+#pragma unroll
+		for (int f = 0; f < F / 2; ++f) red_add_h2(entry + 2 * f, g.h2[s * (F / 2) + f]); // (half)1.0f * grad = grad
+	}
+}
+
 
 // ---- second order (encodings/grid.h:351-650) --------------------------------------------------------------------
 // The backward pass of dL/dx = sum_k dL/dy_k * dy_k/dx (grid_backward_input_kernel): given dL_ddLdx = d(loss)/d(dL/dx), the

@@ -32,6 +32,11 @@ struct AdamArgs {
 	float* m;
 	float* v;
 	uint32_t* steps;
+	// single-GPU fused step: the gradient replicas of the coarse grid levels (tcnn_b200_api.cu backward_params) are summed here
+	// instead of by grid_replica_reduce_kernel - one launch less on the critical path.  Parameters [rep_begin, rep_end) are the
+	// replicated levels (a prefix of the grid table); replica r holds their gradients at replicas + r * (rep_end - rep_begin).
+	const __half* replicas;
+	uint32_t rep_begin, rep_end, n_replicas;
 };
 
 __device__ __forceinline__ bool adam_one(const AdamArgs& a, uint32_t i, float g_half, float& w, float& m, float& v, uint32_t& step) {
@@ -64,6 +69,23 @@ __global__ void __launch_bounds__(256) adam_kernel(const __grid_constant__ AdamA
 	if (i0 + 4 <= a.n) {
 		union { uint2 u; __half h[4]; } g;
 		g.u = *reinterpret_cast<const uint2*>(a.grads + i0);
+		if (i0 >= a.rep_begin && i0 < a.rep_end) { // same arithmetic as grid_replica_reduce_kernel: fp32 sum, one rounding
+			float acc[4] = {0.f, 0.f, 0.f, 0.f};
+			const size_t rep_halfs = a.rep_end - a.rep_begin;
+			const __half* src = a.replicas + (i0 - a.rep_begin);
+			for (uint32_t r0 = 0; r0 < a.n_replicas; r0 += 8) {
+				union { uint2 u; __half2 h2[2]; } v[8];
+#pragma unroll
+				for (uint32_t k = 0; k < 8; ++k) v[k].u = *reinterpret_cast<const uint2*>(src + (size_t)(r0 + k) * rep_halfs);
+#pragma unroll
+				for (uint32_t k = 0; k < 8; ++k) {
+					const float2 lo = __half22float2(v[k].h2[0]), hi = __half22float2(v[k].h2[1]);
+					acc[0] += lo.x; acc[1] += lo.y; acc[2] += hi.x; acc[3] += hi.y;
+				}
+			}
+#pragma unroll
+			for (int k = 0; k < 4; ++k) g.h[k] = __float2half_rn(__half2float(g.h[k]) + acc[k]);
+		}
 		const bool any_nonzero = ((g.u.x | g.u.y) & 0x7FFF7FFFu) != 0;
 		if (i0 >= a.n_matrix && !any_nonzero) return; // nothing to do for four untouched grid entries
 		float4 w = *reinterpret_cast<float4*>(a.master + i0);

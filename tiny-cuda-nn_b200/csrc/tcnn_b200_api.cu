@@ -233,8 +233,9 @@ extern "C" int tcnn_b200_plan_create(const char* json_utf8, uint32_t n_input_dim
 	else FAIL("GridEncoding: invalid grid type '" + gtype + "'");
 	CHECK(jsonmini::lower(enc.string("hash", "CoherentPrime")) == "coherentprime", "only hash 'CoherentPrime' is implemented");
 	const std::string interp = jsonmini::lower(enc.string("interpolation", "Linear"));
-	CHECK(interp == "linear" || interp == "smoothstep", "interpolation '" + interp + "' is not implemented (Linear, Smoothstep)");
+	CHECK(interp == "nearest" || interp == "linear" || interp == "smoothstep", "interpolation '" + interp + "' does not exist (Nearest, Linear, Smoothstep)");
 	p->grid.smoothstep = interp == "smoothstep" ? 1u : 0u;
+	p->grid.nearest = interp == "nearest" ? 1u : 0u;
 	CHECK(!enc.boolean("stochastic_interpolation", false), "stochastic_interpolation is not implemented");
 	in.n_features_per_level = (uint32_t)enc.number("n_features_per_level", 2);
 	CHECK(in.n_features_per_level == 2 || in.n_features_per_level == 4 || in.n_features_per_level == 8,
@@ -518,6 +519,12 @@ static void encode_forward(const tcnn_b200_plan* plan, cudaStream_t stream, uint
 	const uint32_t nz16 = (uint32_t)(zero_bytes / 16);
 	GridParams gp = plan->grid;
 	gp.image_subs = image ? image_subs(plan) : 0u;
+	if (gp.nearest) {
+		if (z16) CUDA_OK(cudaMemsetAsync(z16, 0, zero_bytes, stream));
+		GRID_DISPATCH(grid_nearest_forward_kernel, plan, g, stream, gp, B, x, grid, encoded);
+		launch_check("grid_nearest_forward_kernel");
+		return;
+	}
 	GRID_DISPATCH(grid_forward_kernel, plan, g, stream, gp, B, x, grid, encoded, z16, nz16);
 	launch_check("grid_forward_kernel");
 }
@@ -535,6 +542,11 @@ static void backward_scatter(const tcnn_b200_plan* plan, cudaStream_t stream, co
 	chunk_end = std::min(chunk_end, n_grad_chunks(plan));
 	if (chunk_begin >= chunk_end) return;
 	const dim3 g((B + 255) / 256, chunk_end - chunk_begin, 1);
+	if (gp.nearest) { // one RED per level and sample straight into the gradient buffer; the (zeroed) replicas stay zero
+		GRID_DISPATCH(grid_nearest_backward_kernel, plan, g, stream, gp, B, x, dL_denc, grid_grads, chunk_begin);
+		launch_check("grid_nearest_backward_kernel");
+		return;
+	}
 	GRID_DISPATCH(grid_backward_kernel, plan, g, stream, gp, B, x, dL_denc, grid_grads, replicas, chunk_begin);
 	launch_check("grid_backward_kernel");
 }
@@ -688,7 +700,7 @@ static void launch_mlp(const tcnn_b200_plan* plan, cudaStream_t stream, const Ml
 // Training kernel with the hash-table gradient scatter fused into its last stage; instantiated for the common shapes.
 static bool fused_scatter_available(const tcnn_b200_plan* plan) {
 	const uint32_t D = plan->info.n_input_dims, F = plan->info.n_features_per_level;
-	return !is_wide(plan) && plan->enc_kind == ENC_GRID && !plan->grid.smoothstep && plan->activation == ACT_RELU && plan->info.n_hidden_layers <= 4
+	return !is_wide(plan) && plan->enc_kind == ENC_GRID && !plan->grid.smoothstep && !plan->grid.nearest && plan->activation == ACT_RELU && plan->info.n_hidden_layers <= 4
 		&& plan->info.encoded_width <= 64 && (D == 2 || D == 3) && (F == 2 || F == 4);
 }
 template <int H>
@@ -793,6 +805,10 @@ extern "C" int tcnn_b200_mlp_backward(const tcnn_b200_plan* plan, void* stream_,
 static void encode_backward_input(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t B, const float* x, const __half* grid, const __half* dL_denc, float* dL_dx) {
 	ProfileScope prof(plan, stream, PK_GRID_BWD);
 	const dim3 g((B + 255) / 256, 1, 1);
+	if (plan->grid.nearest) { // "Gradient is zero when there's no interpolation" (grid.h:131-137)
+		CUDA_OK(cudaMemsetAsync(dL_dx, 0, (size_t)B * plan->info.n_input_dims * sizeof(float), stream));
+		return;
+	}
 	GRID_DISPATCH(grid_backward_input_kernel, plan, g, stream, plan->grid, B, x, grid, dL_denc, dL_dx);
 	launch_check("grid_backward_input_kernel");
 }
@@ -890,6 +906,12 @@ extern "C" int tcnn_b200_backward_backward_input(const tcnn_b200_plan* plan, voi
 	(void)workspace;
 	cudaStream_t stream = (cudaStream_t)stream_;
 	const dim3 g((B + 255) / 256, 1, 1);
+	if (plan->grid.nearest) { // dy/dx == 0 everywhere (grid.h:420-423, 522-525 return before touching anything)
+		if (dL_ddLdoutput) CUDA_OK(cudaMemsetAsync(dL_ddLdoutput, 0, (size_t)B * plan->info.encoded_width * 2, stream));
+		if (dL_dinput) CUDA_OK(cudaMemsetAsync(dL_dinput, 0, (size_t)B * plan->info.n_input_dims * sizeof(float), stream));
+		if (dL_dparams) CUDA_OK(cudaMemsetAsync(dL_dparams, 0, plan->info.n_params_grid * 2, stream));
+		return 0;
+	}
 	if (dL_ddLdoutput || dL_dinput) {
 		ProfileScope prof(plan, stream, PK_GRID_BWD);
 		GRID_DISPATCH(grid_backward_backward_input_kernel, plan, g, stream, plan->grid, B, x, (const __half*)params, (const __half*)dL_doutput, dL_ddLdinput,
@@ -983,9 +1005,25 @@ static AdamArgs adam_args(const tcnn_b200_plan* plan, float grad_divisor, uint32
 	a.master = b.master; a.params = b.params; a.grads = b.grads; a.m = b.m; a.v = b.v; a.steps = b.steps;
 	return a;
 }
+// true if the replicated levels of gp are a prefix of the grid table laid out like the table itself (rep_offset == offset):
+// then adam_kernel can sum the replicas while it reads the gradients (AdamArgs::replicas)
+static bool replicas_are_table_prefix(const GridParams& gp) {
+	bool ended = false;
+	for (uint32_t l = 0; l < gp.n_levels; ++l) {
+		const GridLevel& lv = gp.level[l];
+		if (!lv.replicated) { ended = true; continue; }
+		if (ended || lv.rep_offset != lv.offset) return false;
+	}
+	return true;
+}
 static void adam_launch(const tcnn_b200_plan* plan, cudaStream_t stream, float grad_divisor, uint32_t adam_step_count, const AdamBuffers& b,
-	int zero_grid_grads, uint32_t begin, uint32_t end) {
-	const AdamArgs a = adam_args(plan, grad_divisor, adam_step_count, b, zero_grid_grads, begin, end);
+	int zero_grid_grads, uint32_t begin, uint32_t end, const GridParams* reduce_replicas_of = nullptr, const __half* replicas = nullptr) {
+	AdamArgs a = adam_args(plan, grad_divisor, adam_step_count, b, zero_grid_grads, begin, end);
+	if (reduce_replicas_of && reduce_replicas_of->rep_entries) {
+		a.replicas = replicas; a.n_replicas = reduce_replicas_of->n_replicas;
+		a.rep_begin = (uint32_t)plan->info.n_params_mlp;
+		a.rep_end = a.rep_begin + reduce_replicas_of->rep_entries * plan->info.n_features_per_level;
+	}
 	if (a.begin >= a.n) return;
 	ProfileScope prof(plan, stream, PK_ADAM);
 	const uint32_t n_threads = (a.n - a.begin + 3) / 4;
@@ -1060,8 +1098,12 @@ extern "C" int tcnn_b200_training_step(const tcnn_b200_plan* plan, void* stream_
 			launch_check("mlp_finalize_adam_kernel");
 		}
 		CUDA_OK(cudaEventRecord(ev[1], aux));
-		backward_finish(plan, main, gp, gg, w.replicas);
-		adam_launch(plan, main, loss_scale, adam_step_count, ab, 1, (uint32_t)in.n_params_mlp, (uint32_t)in.n_params);
+		if (replicas_are_table_prefix(gp) && in.n_params_mlp % 4 == 0) { // replica sums inside the optimizer kernel
+			adam_launch(plan, main, loss_scale, adam_step_count, ab, 1, (uint32_t)in.n_params_mlp, (uint32_t)in.n_params, &gp, w.replicas);
+		} else {
+			backward_finish(plan, main, gp, gg, w.replicas);
+			adam_launch(plan, main, loss_scale, adam_step_count, ab, 1, (uint32_t)in.n_params_mlp, (uint32_t)in.n_params);
+		}
 		CUDA_OK(cudaStreamWaitEvent(main, ev[1], 0)); // join
 		return 0;
 	}
