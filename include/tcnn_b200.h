@@ -61,7 +61,10 @@ uint32_t tcnn_b200_batch_size_granularity(void);
  * With "network" alone the plan is create_network (Identity encoding + network, src/cpp_api.cu:151-153); with "encoding"
  * alone it is create_encoding (src/cpp_api.cu:156-165): inference/forward then write the encoded batch, fp16
  * [B][next multiple of 8 of n_levels * n_features_per_level], and backward takes dL/d(encoded) of that shape.  The training
- * entry points need both objects. */
+ * entry points need both objects.
+ * A stand-alone grid encoding may carry "precision": "fp32" at the top level (create_encoding(n, encoding, Precision::Fp32),
+ * cpp_api.h:71-75,115): parameters, encoded output, dL/d(encoded) and the parameter gradient of tcnn_b200_inference /
+ * _forward / _backward are then fp32 (same shapes; the `*_fp16` argument names of those calls then carry fp32 buffers). */
 int tcnn_b200_plan_create(const char* json_utf8, uint32_t n_input_dims, uint32_t n_output_dims, tcnn_b200_plan** plan);
 void tcnn_b200_plan_destroy(tcnn_b200_plan* plan);
 int tcnn_b200_plan_info(const tcnn_b200_plan* plan, tcnn_b200_info* info);

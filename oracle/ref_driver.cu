@@ -13,6 +13,9 @@
 //   ref_driver bwdbwd <cfg.json> <n_in> <B> <input.f32> <table.f16> <dL_dy.f16 [B][padded]> <v.f32 [B][n_in]> <outdir>
 //       second order of the stand-alone encoding (encodings/grid.h:902-1026): forward with input gradients, backward,
 //       backward_backward_input; dumps dL/dx, dL2/d(dL/dy), dL2/dtable, dL2/dx.
+//   ref_driver enc32 <cfg.json> <n_in> <B> <input.f32> <table.f32> <dL_dy.f32 [B][padded]> <outdir>
+//       the stand-alone encoding in fp32 precision (create_encoding<float>, what cpp_api.cu:156-165 builds for
+//       Precision::Fp32): forward, backward (table gradient, dL/dx).
 //   ref_driver bench <cfg.json> <n_in> <n_out> <B> <steps> <warmup>
 //       one JSON line: training / inference ms per step (CUDA events), device-resident inputs and
 //       host-buffer (H2D inside the timed region) variants.
@@ -272,6 +275,39 @@ static int mode_bwdbwd(int argc, char** argv) {
 	return 0;
 }
 
+static int mode_enc32(int argc, char** argv) {
+	if (argc < 9) { std::cerr << "enc32: bad args\n"; return 2; }
+	json cfg = load_cfg(argv[2]);
+	const uint32_t n_in = std::stoul(argv[3]), B = std::stoul(argv[4]);
+	const std::string out = argv[8];
+	auto in_raw = read_file(argv[5]), tab_raw = read_file(argv[6]), dy_raw = read_file(argv[7]);
+	cudaStream_t stream; CUDA_CHECK_THROW(cudaStreamCreate(&stream));
+	std::unique_ptr<Encoding<float>> enc{create_encoding<float>(n_in, cfg.value("encoding", json::object()))};
+	const size_t P = enc->n_params();
+	const uint32_t W = enc->padded_output_width();
+	if (in_raw.size() != (size_t)B * n_in * 4 || tab_raw.size() != P * 4 || dy_raw.size() != (size_t)B * W * 4) {
+		std::cerr << "enc32: size mismatch P=" << P << " W=" << W << "\n"; return 2;
+	}
+	GPUMemory<float> table(P), grads(P);
+	CUDA_CHECK_THROW(cudaMemcpy(table.data(), tab_raw.data(), tab_raw.size(), cudaMemcpyHostToDevice));
+	grads.memset(0);
+	enc->set_params(table.data(), table.data(), grads.data());
+	GPUMatrix<float> input(n_in, B), dL_dx(n_in, B);
+	CUDA_CHECK_THROW(cudaMemcpy(input.data(), in_raw.data(), in_raw.size(), cudaMemcpyHostToDevice));
+	GPUMatrixDynamic<float> dy(W, B, AoS), y(W, B, AoS); // sample-major ([B][W]) on both sides
+	CUDA_CHECK_THROW(cudaMemcpy(dy.data(), dy_raw.data(), dy_raw.size(), cudaMemcpyHostToDevice));
+	dL_dx.memset(0);
+	auto ctx = enc->forward(stream, input, &y, false, true);
+	enc->backward(stream, *ctx, input, y, dy, &dL_dx, false, GradientMode::Overwrite);
+	CUDA_CHECK_THROW(cudaStreamSynchronize(stream));
+	write_dev(out + "/encoded.f32", y.data(), (size_t)B * W);
+	write_dev(out + "/dL_dx.f32", dL_dx.data(), (size_t)B * n_in);
+	write_dev(out + "/dL_dtable.f32", grads.data(), P);
+	std::ofstream(out + "/meta.json") << json{{"n_params", P}, {"padded_output_width", W}, {"output_width", enc->output_width()}, {"B", B}, {"n_in", n_in}}.dump(1);
+	std::cout << "enc32 ok P=" << P << " W=" << W << std::endl;
+	return 0;
+}
+
 static int mode_bench(int argc, char** argv) {
 	if (argc < 8) { std::cerr << "bench: bad args\n"; return 2; }
 	json cfg = load_cfg(argv[2]);
@@ -326,6 +362,7 @@ int main(int argc, char** argv) {
 		if (mode == "curve") return mode_curve(argc, argv);
 		if (mode == "bench") return mode_bench(argc, argv);
 		if (mode == "bwdbwd") return mode_bwdbwd(argc, argv);
+		if (mode == "enc32") return mode_enc32(argc, argv);
 		std::cerr << "unknown mode " << mode << "\n";
 		return 2;
 	} catch (const std::exception& e) {

@@ -359,14 +359,49 @@ def grid_backward(cfg: GridConfig, x: np.ndarray, dy: np.ndarray, sequential_fp1
     return g.reshape(-1)
 
 
-def grid_backward_input(cfg: GridConfig, x: np.ndarray, table: np.ndarray, dy: np.ndarray) -> np.ndarray:
+def grid_forward_f32(cfg: GridConfig, x: np.ndarray, table: np.ndarray) -> np.ndarray:
+    """kernel_grid with T = float (an encoding created with Precision::Fp32, cpp_api.cu:156-165): fp32 table, result =
+    fmaf(weight, value, result) per corner in corner order (grid.h:146-163).  Returns fp32 [B, L*F]."""
+    B, F = x.shape[0], cfg.n_features_per_level
+    out = np.zeros((B, cfg.n_features), dtype=np.float32)
+    t = table.astype(np.float32).reshape(-1, F)
+    for l in range(cfg.n_levels):
+        idx, w = grid_corners(cfg, x, l)
+        base = int(cfg.offsets[l])
+        if cfg.nearest:
+            out[:, l * F:(l + 1) * F] = t[base + idx[:, 0].astype(np.int64)]
+            continue
+        res = np.zeros((B, F), dtype=np.float32)
+        for c in range(idx.shape[1]):
+            val = t[base + idx[:, c].astype(np.int64)]
+            res = (w[:, c].astype(np.float64)[:, None] * val.astype(np.float64) + res.astype(np.float64)).astype(np.float32)
+        out[:, l * F:(l + 1) * F] = res
+    return out
+
+
+def grid_backward_f32(cfg: GridConfig, x: np.ndarray, dy: np.ndarray) -> np.ndarray:
+    """kernel_grid_backward with T = float: atomicAdd of the fp32 products weight * grad (grid.h:248-252), summed here in
+    float64 (the atomics' order is arbitrary).  dy fp32 [B, >= L*F] -> float64 [n_params]."""
+    F = cfg.n_features_per_level
+    g = np.zeros((int(cfg.offsets[-1]), F), dtype=np.float64)
+    for l in range(cfg.n_levels):
+        idx, w = grid_corners(cfg, x, l)
+        base = int(cfg.offsets[l])
+        gl = dy[:, l * F:(l + 1) * F].astype(np.float32)
+        for c in range(idx.shape[1]):
+            prod = (w[:, c].astype(np.float32)[:, None] * gl).astype(np.float32)
+            np.add.at(g, base + idx[:, c].astype(np.int64), prod.astype(np.float64))
+    return g.reshape(-1)
+
+
+def grid_backward_input(cfg: GridConfig, x: np.ndarray, table: np.ndarray, dy: np.ndarray, fp32: bool = False) -> np.ndarray:
     """dL/dx of the grid encoding: dy/dx as kernel_grid computes it when asked (grid.h:171-211: per level and feature,
     sum over the 2^(D-1) corner pairs along the gradient dim of scale * prod(other weights) * (val_right - val_left), fp32)
     contracted with dL/dy as kernel_grid_backward_input does (grid.h:322-349: k ascending).  x fp32 [B, D], table fp16,
     dy fp16 [B, >= L*F] -> fp32 [B, D]."""
     B, D = x.shape
     F = cfg.n_features_per_level
-    t = table.astype(np.float16).reshape(-1, F)
+    t = table.astype(np.float32 if fp32 else np.float16).reshape(-1, F)  # fp32: create_encoding<float> (cpp_api.cu:156-165)
     result = np.zeros((B, D), np.float32)
     if cfg.nearest:  # "Gradient is zero when there's no interpolation" (grid.h:131-137)
         return result

@@ -151,3 +151,16 @@ def second_order_inputs(n_in, n_table, n_features, padded_width, B=256, seed=5):
     dy[:, :n_features] = rng.standard_normal((B, n_features)).astype(np.float16)
     v = rng.standard_normal((B, n_in)).astype(np.float32)
     return x, table, dy, v
+
+
+# stand-alone grid encodings in fp32 precision (tcnn.Encoding(dtype=torch.float32)): goldens enc32_*.npz
+FP32_ENCODINGS = dict(SECOND_ORDER_ENCODINGS, nearest3d=(3, CONFIG_NEAREST["encoding"]))
+
+
+def fp32_inputs(n_in, n_table, n_features, padded_width, B=256, seed=6):
+    rng = np.random.default_rng(seed)
+    x = rng.random((B, n_in), dtype=np.float32)
+    table = rng.uniform(-1, 1, n_table).astype(np.float32)
+    dy = np.zeros((B, padded_width), np.float32)
+    dy[:, :n_features] = rng.standard_normal((B, n_features)).astype(np.float32)
+    return x, table, dy

@@ -96,14 +96,43 @@ def second_order(outdir):
             print(name, "saved", os.path.getsize(os.path.join(outdir, "bwdbwd_" + name + ".npz")), "bytes", flush=True)
 
 
+def encoding_fp32(outdir):
+    """`ref_driver enc32`: the reference's GridEncoding<float> (tcnn.Encoding(dtype=torch.float32)) forward / backward."""
+    for name, (n_in, enc) in common.FP32_ENCODINGS.items():
+        with tempfile.TemporaryDirectory() as d:
+            with open(os.path.join(d, "cfg.json"), "w") as f:
+                json.dump({"encoding": enc}, f)
+            g = common.oracle_configs({"encoding": enc, "network": {"n_neurons": 64, "n_hidden_layers": 1}}, n_in, 1)[0]
+            W = (g.n_features + 7) // 8 * 8
+            B = 256
+            x, table, dy = common.fp32_inputs(n_in, g.n_params, g.n_features, W, B)
+            for fn, a in (("x.f32", x), ("table.f32", table), ("dy.f32", dy)):
+                a.tofile(os.path.join(d, fn))
+            r = subprocess.run([REF, "enc32", os.path.join(d, "cfg.json"), str(n_in), str(B)] + [os.path.join(d, fn) for fn in ("x.f32", "table.f32", "dy.f32")] + [d],
+                               capture_output=True, text=True, timeout=600)
+            print(name, r.returncode, r.stdout.strip(), r.stderr.strip()[-400:], flush=True)
+            if r.returncode != 0:
+                continue
+            meta = json.load(open(os.path.join(d, "meta.json")))
+            assert meta["padded_output_width"] == W and meta["n_params"] == g.n_params, meta
+            rd = lambda fn: np.fromfile(os.path.join(d, fn), dtype=np.float32)  # noqa: E731
+            np.savez_compressed(
+                os.path.join(outdir, "enc32_" + name + ".npz"), encoding=json.dumps(enc), n_in=n_in, B=B, seed=6,
+                encoded=rd("encoded.f32").reshape(B, W), dL_dx=rd("dL_dx.f32").reshape(B, n_in), dL_dtable=rd("dL_dtable.f32"))
+            print(name, "saved", os.path.getsize(os.path.join(outdir, "enc32_" + name + ".npz")), "bytes", flush=True)
+
+
 def main(outdir):
     os.makedirs(outdir, exist_ok=True)
     if os.environ.get("GOLDEN_SECOND_ORDER_ONLY"):
         return second_order(outdir)
+    if os.environ.get("GOLDEN_FP32_ONLY"):
+        return encoding_fp32(outdir)
     only = [n for n in os.environ.get("GOLDEN_ONLY", "").split(",") if n]  # restrict to these case names (no curves)
     if not only:
         curves(outdir)
         second_order(outdir)
+        encoding_fp32(outdir)
     if os.environ.get("GOLDEN_CURVES_ONLY"):
         return
     for name, cfg, n_in, n_out, B in CASES:

@@ -368,9 +368,12 @@ __global__ void grid_replica_reduce_kernel(const __grid_constant__ GridParams gp
 // summation order: per level and feature, dy/dx[d] = sum over the 2^(D-1) corner pairs along d of
 // scale * prod_{other dims} w * (val_right - val_left); dL/dx[d] = sum_k dL/dy_k * dy_k/dx[d], k ascending.
 // Thread = sample.
-template <int D, int F>
+__device__ __forceinline__ float to_f32(__half v) { return __half2float(v); }
+__device__ __forceinline__ float to_f32(float v) { return v; }
+// T = __half, or float for a stand-alone encoding created with fp32 precision (cpp_api.cu:156-165)
+template <int D, int F, typename T = __half>
 __global__ void __launch_bounds__(256) grid_backward_input_kernel(const __grid_constant__ GridParams gp, uint32_t B, const float* __restrict__ x,
-	const __half* __restrict__ grid, const __half* __restrict__ dL_denc, float* __restrict__ dL_dx) {
+	const T* __restrict__ grid, const T* __restrict__ dL_denc, float* __restrict__ dL_dx) {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= B) return;
 	float p[D];
@@ -380,7 +383,7 @@ __global__ void __launch_bounds__(256) grid_backward_input_kernel(const __grid_c
 	for (int d = 0; d < D; ++d) result[d] = 0.f;
 	for (uint32_t level = 0; level < gp.n_levels; ++level) {
 		const GridLevel& lv = gp.level[level];
-		const __half* table = grid + (size_t)lv.offset * F;
+		const T* table = grid + (size_t)lv.offset * F;
 		float frac[D]; uint32_t cell[D];
 #pragma unroll
 		for (int d = 0; d < D; ++d) pos_fract_dev(p[d], lv.scale, frac[d], cell[d]);
@@ -389,7 +392,7 @@ __global__ void __launch_bounds__(256) grid_backward_input_kernel(const __grid_c
 		for (int d = 0; d < D; ++d) { dfrac[d] = gp.smoothstep ? smoothstep_derivative_dev(frac[d]) : 1.0f; if (gp.smoothstep) frac[d] = smoothstep_dev(frac[d]); }
 		float dl[F];
 #pragma unroll
-		for (int f = 0; f < F; ++f) dl[f] = __half2float(dL_denc[(size_t)i * gp.padded_width + level * F + f]);
+		for (int f = 0; f < F; ++f) dl[f] = to_f32(dL_denc[(size_t)i * gp.padded_width + level * F + f]);
 		float grads[F][D];
 #pragma unroll
 		for (int f = 0; f < F; ++f)
@@ -413,7 +416,7 @@ __global__ void __launch_bounds__(256) grid_backward_input_kernel(const __grid_c
 				const uint32_t ir = grid_index_dev<D>(lv, pg);
 #pragma unroll
 				for (int f = 0; f < F; ++f)
-					grads[f][gd] += weight * (__half2float(table[(size_t)ir * F + f]) - __half2float(table[(size_t)il * F + f])) * dfrac[gd];
+					grads[f][gd] += weight * (to_f32(table[(size_t)ir * F + f]) - to_f32(table[(size_t)il * F + f])) * dfrac[gd];
 			}
 		}
 #pragma unroll
@@ -423,6 +426,93 @@ __global__ void __launch_bounds__(256) grid_backward_input_kernel(const __grid_c
 	}
 #pragma unroll
 	for (int d = 0; d < D; ++d) dL_dx[(size_t)i * D + d] = result[d];
+}
+
+// ---- fp32 precision (tcnn.Encoding(dtype=torch.float32); create_encoding<float>, cpp_api.cu:156-165) ------------------------
+// The same kernel_grid / kernel_grid_backward arithmetic with T = float: fp32 table, fmaf interpolation in corner order,
+// fp32 atomicAdd of weight * grad (grid.h:146-163, 248-252).  Thread = (sample, level); not a hot path of the trainer.
+template <int D>
+__device__ __forceinline__ void level_corner(const GridLevel& lv, const float (&frac)[D], const uint32_t (&cell)[D], int c, float& weight, uint32_t& idx) {
+	weight = 1.0f;
+	uint32_t pg[D];
+#pragma unroll
+	for (int d = 0; d < D; ++d) {
+		if ((c >> d) & 1) { weight *= frac[d]; pg[d] = cell[d] + 1u; }
+		else { weight *= 1.0f - frac[d]; pg[d] = cell[d]; }
+	}
+	idx = grid_index_dev<D>(lv, pg);
+}
+template <int D, int F>
+__global__ void __launch_bounds__(256) grid_forward_f32_kernel(const __grid_constant__ GridParams gp, uint32_t B,
+	const float* __restrict__ x, const float* __restrict__ grid, float* __restrict__ encoded) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= B) return;
+	const uint32_t level = blockIdx.y;
+	float* out = encoded + (size_t)i * gp.padded_width;
+	if (level == 0) for (uint32_t k = gp.n_features; k < gp.padded_width; ++k) out[k] = 0.0f; // padding (grid.h:749-759)
+	const GridLevel& lv = gp.level[level];
+	const float* table = grid + (size_t)lv.offset * F;
+	float p[D];
+	load_position<D>(x, i, p);
+	float frac[D]; uint32_t cell[D];
+#pragma unroll
+	for (int d = 0; d < D; ++d) pos_fract_dev(p[d], lv.scale, frac[d], cell[d]);
+	float result[F];
+	if (gp.nearest) {
+		const uint32_t idx = grid_index_dev<D>(lv, cell);
+#pragma unroll
+		for (int f = 0; f < F; ++f) result[f] = table[(size_t)idx * F + f];
+	} else {
+		if (gp.smoothstep) {
+#pragma unroll
+			for (int d = 0; d < D; ++d) frac[d] = smoothstep_dev(frac[d]);
+		}
+#pragma unroll
+		for (int f = 0; f < F; ++f) result[f] = 0.0f;
+#pragma unroll
+		for (int c = 0; c < (1 << D); ++c) {
+			float weight; uint32_t idx;
+			level_corner<D>(lv, frac, cell, c, weight, idx);
+#pragma unroll
+			for (int f = 0; f < F; ++f) result[f] = fmaf(weight, table[(size_t)idx * F + f], result[f]);
+		}
+	}
+#pragma unroll
+	for (int f = 0; f < F; ++f) out[level * F + f] = result[f];
+}
+template <int D, int F>
+__global__ void __launch_bounds__(256) grid_backward_f32_kernel(const __grid_constant__ GridParams gp, uint32_t B,
+	const float* __restrict__ x, const float* __restrict__ dL_denc, float* __restrict__ grid_grad) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= B) return;
+	const uint32_t level = blockIdx.y;
+	const GridLevel& lv = gp.level[level];
+	float* gtable = grid_grad + (size_t)lv.offset * F;
+	float p[D];
+	load_position<D>(x, i, p);
+	float frac[D]; uint32_t cell[D];
+#pragma unroll
+	for (int d = 0; d < D; ++d) pos_fract_dev(p[d], lv.scale, frac[d], cell[d]);
+	float g[F];
+#pragma unroll
+	for (int f = 0; f < F; ++f) g[f] = dL_denc[(size_t)i * gp.padded_width + level * F + f];
+	if (gp.nearest) {
+		const uint32_t idx = grid_index_dev<D>(lv, cell);
+#pragma unroll
+		for (int f = 0; f < F; ++f) atomicAdd(gtable + (size_t)idx * F + f, g[f]);
+		return;
+	}
+	if (gp.smoothstep) {
+#pragma unroll
+		for (int d = 0; d < D; ++d) frac[d] = smoothstep_dev(frac[d]);
+	}
+#pragma unroll
+	for (int c = 0; c < (1 << D); ++c) {
+		float weight; uint32_t idx;
+		level_corner<D>(lv, frac, cell, c, weight, idx);
+#pragma unroll
+		for (int f = 0; f < F; ++f) atomicAdd(gtable + (size_t)idx * F + f, weight * g[f]);
+	}
 }
 
 // ---- Nearest "interpolation" (grid.h:121-139, 279-282): the entry of the cell the shifted position falls into, weight 1 ----

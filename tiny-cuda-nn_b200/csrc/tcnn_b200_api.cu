@@ -49,6 +49,7 @@ struct tcnn_b200_plan {
 	int grid_type = 0;              // GRID_HASH / GRID_DENSE / GRID_TILED (GridType, grid_interface.h)
 	int enc_kind = 0;               // ENC_GRID / ENC_IDENTITY / ENC_ONEBLOB
 	uint32_t oneblob_log2_bins = 0;
+	bool f32 = false;               // stand-alone encoding with fp32 parameters / output ("precision": "fp32"; Precision::Fp32 of cpp_api.h)
 	int kind = 0;                   // PLAN_FULL: encoding + network; PLAN_NETWORK: Identity encoding + network; PLAN_ENCODING: grid encoding alone
 	bool no_warp_specialization = getenv("TCNN_B200_NO_WS") != nullptr; // development switch: fused kernel without the scatter warpgroup
 	// optional per-kernel timing (tcnn_b200_profile_*): CUDA events recorded around every launch on the launch stream
@@ -205,6 +206,11 @@ extern "C" int tcnn_b200_plan_create(const char* json_utf8, uint32_t n_input_dim
 	const bool has_encoding = cfg.contains("encoding"), has_network = cfg.contains("network");
 	CHECK(has_encoding || has_network, "config needs an \"encoding\" and/or a \"network\" object");
 	p->kind = has_encoding ? (has_network ? PLAN_FULL : PLAN_ENCODING) : PLAN_NETWORK;
+	// create_encoding(n_input_dims, encoding, Precision) of cpp_api.h:71-75,115: a stand-alone encoding may be asked for in fp32
+	const std::string precision = jsonmini::lower(cfg.string("precision", "fp16"));
+	CHECK(precision == "fp16" || precision == "fp32", "precision must be \"fp16\" or \"fp32\"");
+	p->f32 = precision == "fp32";
+	CHECK(!p->f32 || p->kind == PLAN_ENCODING, "fp32 precision exists for a stand-alone encoding only (networks are fp16, TCNN_HALF_PRECISION)");
 	uint32_t n_features = 0;
 	if (has_encoding) {
 	// --- encoding: create_grid_encoding (encodings/grid.h:1143-1208) ---
@@ -511,6 +517,20 @@ extern "C" int tcnn_b200_cast_params(void* stream_, uint64_t n, const float* par
 		else FAIL("unsupported (n_input_dims, n_features_per_level)");                                            \
 	} while (0)
 
+#define GRID_DISPATCH_T(KERNEL, TT, plan, grid_dim, stream, ...)                                                  \
+	do {                                                                                                          \
+		const uint32_t D_ = (plan)->info.n_input_dims, F_ = (plan)->info.n_features_per_level;                   \
+		if (D_ == 2 && F_ == 2) KERNEL<2, 2, TT><<<grid_dim, 256, 0, stream>>>(__VA_ARGS__);                     \
+		else if (D_ == 2 && F_ == 4) KERNEL<2, 4, TT><<<grid_dim, 256, 0, stream>>>(__VA_ARGS__);                \
+		else if (D_ == 2 && F_ == 8) KERNEL<2, 8, TT><<<grid_dim, 256, 0, stream>>>(__VA_ARGS__);                \
+		else if (D_ == 3 && F_ == 2) KERNEL<3, 2, TT><<<grid_dim, 256, 0, stream>>>(__VA_ARGS__);                \
+		else if (D_ == 3 && F_ == 4) KERNEL<3, 4, TT><<<grid_dim, 256, 0, stream>>>(__VA_ARGS__);                \
+		else if (D_ == 3 && F_ == 8) KERNEL<3, 8, TT><<<grid_dim, 256, 0, stream>>>(__VA_ARGS__);                \
+		else if (D_ == 4 && F_ == 2) KERNEL<4, 2, TT><<<grid_dim, 256, 0, stream>>>(__VA_ARGS__);                \
+		else if (D_ == 4 && F_ == 4) KERNEL<4, 4, TT><<<grid_dim, 256, 0, stream>>>(__VA_ARGS__);                \
+		else FAIL("unsupported (n_input_dims, n_features_per_level)");                                            \
+	} while (0)
+
 static void encode_forward(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t B, const float* x, const __half* grid, __half* encoded,
 	void* zero_on_the_side = nullptr, size_t zero_bytes = 0, bool image = false) {
 	ProfileScope prof(plan, stream, PK_GRID_FWD);
@@ -581,6 +601,7 @@ extern "C" int tcnn_b200_encode_forward(const tcnn_b200_plan* plan, void* stream
 	API_BEGIN
 	require_device(plan); check_batch(B);
 	CHECK(x && encoded && (grid_params || plan->enc_kind != ENC_GRID), "null argument");
+	CHECK(!plan->f32, "fp16 entry point: an fp32-precision encoding goes through tcnn_b200_forward / _inference / _backward");
 	encode_any(plan, (cudaStream_t)stream, B, x, (const __half*)grid_params, (__half*)encoded, /*image=*/false); // OneBlob / Identity: grid_params unused
 	API_END
 }
@@ -588,6 +609,7 @@ extern "C" int tcnn_b200_encode_backward(const tcnn_b200_plan* plan, void* strea
 	API_BEGIN
 	require_device(plan); check_batch(B);
 	CHECK(x && dL_denc && grid_grads, "null argument");
+	CHECK(!plan->f32, "fp16 entry point: an fp32-precision encoding goes through tcnn_b200_forward / _inference / _backward");
 	encode_backward(plan, (cudaStream_t)stream, B, x, (const __half*)dL_denc, (__half*)grid_grads, zero_first, workspace ? carve(plan, B, workspace).replicas : nullptr);
 	API_END
 }
@@ -840,6 +862,15 @@ extern "C" int tcnn_b200_inference(const tcnn_b200_plan* plan, void* stream_, ui
 	cudaStream_t stream = (cudaStream_t)stream_;
 	const Workspace w = carve(plan, B, workspace);
 	const __half* p = (const __half*)params;
+	if (plan->kind == PLAN_ENCODING && plan->f32) { // fp32 table -> fp32 [B][encoded_width] (either output pointer)
+		CHECK(plan->enc_kind == ENC_GRID, "fp32 precision is implemented for grid encodings");
+		float* out = output_fp32 ? output_fp32 : (float*)output_fp16;
+		ProfileScope prof(plan, stream, PK_GRID_FWD);
+		const dim3 g((B + 255) / 256, plan->info.n_levels, 1);
+		GRID_DISPATCH(grid_forward_f32_kernel, plan, g, stream, plan->grid, B, x, (const float*)params, out);
+		launch_check("grid_forward_f32_kernel");
+		return 0;
+	}
 	if (plan->kind == PLAN_ENCODING) { // tcnn.Encoding: output = the encoded batch, fp16 [B][encoded_width]
 		CHECK(output_fp16 && !output_fp32, "a stand-alone encoding writes fp16 [B][encoded_width]");
 		encode_forward(plan, stream, B, x, p, (__half*)output_fp16);
@@ -864,6 +895,24 @@ extern "C" int tcnn_b200_backward(const tcnn_b200_plan* plan, void* stream_, uin
 	const Workspace w = carve(plan, B, workspace);
 	const __half* p = (const __half*)params;
 	__half* g = (__half*)dL_dparams;
+	if (plan->kind == PLAN_ENCODING && plan->f32) { // everything fp32: dL/d(encoded) [B][encoded_width], table gradient (GradientMode::Overwrite)
+		ProfileScope prof(plan, stream, PK_GRID_BWD);
+		if (dL_dparams) {
+			CUDA_OK(cudaMemsetAsync(dL_dparams, 0, plan->info.n_params_grid * sizeof(float), stream));
+			const dim3 gl((B + 255) / 256, plan->info.n_levels, 1);
+			GRID_DISPATCH(grid_backward_f32_kernel, plan, gl, stream, plan->grid, B, x, (const float*)dL_doutput, (float*)dL_dparams);
+			launch_check("grid_backward_f32_kernel");
+		}
+		if (dL_dinput) {
+			if (plan->grid.nearest) CUDA_OK(cudaMemsetAsync(dL_dinput, 0, (size_t)B * plan->info.n_input_dims * sizeof(float), stream));
+			else {
+				const dim3 gs((B + 255) / 256, 1, 1);
+				GRID_DISPATCH_T(grid_backward_input_kernel, float, plan, gs, stream, plan->grid, B, x, (const float*)params, (const float*)dL_doutput, dL_dinput);
+				launch_check("grid_backward_input_kernel<float>");
+			}
+		}
+		return 0;
+	}
 	if (plan->kind == PLAN_ENCODING) { // dL_doutput is dL/d(encoded), fp16 [B][encoded_width]
 		if (g) encode_backward(plan, stream, B, x, (const __half*)dL_doutput, g, /*zero_first=*/1, w.replicas);
 		if (dL_dinput) encode_backward_input(plan, stream, B, x, p, (const __half*)dL_doutput, dL_dinput);
@@ -900,6 +949,7 @@ extern "C" int tcnn_b200_backward_backward_input(const tcnn_b200_plan* plan, voi
 	const float* dL_ddLdinput, const void* dL_doutput, void* dL_ddLdoutput, void* dL_dparams, float* dL_dinput, void* workspace) {
 	API_BEGIN
 	require_device(plan); check_batch(B);
+	CHECK(!plan->f32, "second-order gradients are implemented for fp16 precision");
 	CHECK(plan->kind == PLAN_ENCODING && plan->enc_kind == ENC_GRID,
 		"second-order gradients exist for the stand-alone grid encoding only (FullyFusedMLP has no backward_backward_input in the reference either)");
 	CHECK(x && params && dL_ddLdinput && dL_doutput, "null argument");

@@ -27,6 +27,8 @@ class NativeModule:
         handle = _lib.C.c_void_p()
         check(self.lib.tcnn_b200_plan_create(json.dumps(config).encode(), n_input_dims, n_output_dims, _lib.C.byref(handle)))
         self.handle = handle
+        # Precision of parameters and output (cpp_api.h:71-75): fp32 for a stand-alone encoding created with "precision": "fp32"
+        self.param_dtype = torch.float32 if str(config.get("precision", "fp16")).lower() == "fp32" else torch.half
         self.info = _lib.Info()
         check(self.lib.tcnn_b200_plan_info(self.handle, _lib.C.byref(self.info)))
         self._ws = {}
@@ -69,7 +71,7 @@ class NativeModule:
     # --- compute ---
     def fwd(self, x: torch.Tensor, params: torch.Tensor, need_ctx: bool):
         B = x.shape[0]
-        out = torch.empty(B, self.n_output_dims(), dtype=torch.half, device=x.device)
+        out = torch.empty(B, self.n_output_dims(), dtype=self.param_dtype, device=x.device)
         if need_ctx:
             ws = self.workspace(B, x.device, fresh=True)  # owned by the autograd context, like the reference's Context
             check(self.lib.tcnn_b200_forward(self.handle, _stream_ptr(), B, ptr(x), ptr(params), ptr(out), ptr(ws)))
@@ -79,9 +81,9 @@ class NativeModule:
         return None, out
 
     def bwd(self, ws, x, params, doutput, want_params_grad: bool, want_input_grad: bool = False):
-        """-> (dL_dinput fp32 [B, n_input_dims] or None, dL_dparams fp16 [n_params] or None)"""
+        """-> (dL_dinput fp32 [B, n_input_dims] or None, dL_dparams [n_params] in the parameter precision or None)"""
         B = x.shape[0]
-        g = torch.empty(self.n_params(), dtype=torch.half, device=x.device) if want_params_grad else None
+        g = torch.empty(self.n_params(), dtype=self.param_dtype, device=x.device) if want_params_grad else None
         dx = torch.empty(B, int(self.info.n_input_dims), dtype=torch.float32, device=x.device) if want_input_grad else None
         if g is not None or dx is not None:
             check(self.lib.tcnn_b200_backward(self.handle, _stream_ptr(), B, ptr(x), ptr(params), ptr(doutput), ptr(g), ptr(dx), ptr(ws)))
@@ -135,7 +137,7 @@ class _module_function_backward(torch.autograd.Function):
         ctx.fwd = fwd
         ctx.save_for_backward(x, params, doutput)
         with torch.no_grad():
-            scaled = (doutput.to(torch.float) * fwd.loss_scale).to(torch.half).contiguous()
+            scaled = (doutput.to(torch.float) * fwd.loss_scale).to(fwd.native.param_dtype).contiguous()
             dx, g = fwd.native.bwd(fwd.ws, x, params, scaled, fwd.needs_input_grad[2], fwd.needs_input_grad[1])
             dx = _empty_like(x) if dx is None else dx / fwd.loss_scale
             g = _empty_like(params) if g is None else g / fwd.loss_scale
@@ -161,11 +163,11 @@ class Module(torch.nn.Module):
     def __init__(self, seed=1337):
         super().__init__()
         self.native_tcnn_module = self._native_tcnn_module()
-        self.dtype = torch.half
+        self.dtype = self.native_tcnn_module.param_dtype
         self.seed = seed
         initial_params = self.native_tcnn_module.initial_params(seed)
         self.params = torch.nn.Parameter(initial_params, requires_grad=True)
-        self.loss_scale = 128.0  # default_loss_scale(Fp16), cpp_api.h / common.h:229-233
+        self.loss_scale = 128.0 if self.dtype == torch.half else 1.0  # default_loss_scale(precision), cpp_api.h:76 / common.h:229-233
 
     def forward(self, x):
         if not x.is_cuda:
@@ -178,7 +180,7 @@ class Module(torch.nn.Module):
         output = _module_function.apply(
             self.native_tcnn_module,
             x_padded.to(torch.float).contiguous(),
-            self.params.to(torch.half).contiguous(),
+            self.params.to(self.dtype).contiguous(),
             self.loss_scale,
             torch.is_grad_enabled() and (self.params.requires_grad or x.requires_grad),  # grad mode is off inside Function.forward
         )
@@ -229,20 +231,19 @@ class Network(Module):
 
 class Encoding(Module):
     """Input encoding (modules.py:285-329 of the reference; src/cpp_api.cu:156-165: no padding of the output).  Supported
-    here: HashGrid, fp16 output and parameters (dtype None or torch.half)."""
+    here: grid encodings; dtype None / torch.half (fp16 parameters and output) or torch.float32 (fp32 throughout; first order)."""
 
     def __init__(self, n_input_dims, encoding_config, seed=1337, dtype=None):
         self.n_input_dims = n_input_dims
         self.encoding_config = encoding_config
-        if dtype not in (None, torch.float16):
-            if dtype == torch.float32:
-                raise ValueError("tcnn_b200: Encoding is implemented for fp16 precision only")
+        if dtype not in (None, torch.float16, torch.float32):
             raise ValueError(f"Encoding only supports fp32 or fp16 precision, but got {dtype}")
+        self.precision = "fp32" if dtype == torch.float32 else "fp16"
         super().__init__(seed=seed)
         self.n_output_dims = int(self.native_tcnn_module.info.n_output_dims)
 
     def _native_tcnn_module(self):
-        return NativeModule(self.n_input_dims, 0, {"encoding": self.encoding_config})
+        return NativeModule(self.n_input_dims, 0, {"encoding": self.encoding_config, "precision": self.precision})
 
 
 def free_temporary_memory():
