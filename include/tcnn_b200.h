@@ -68,6 +68,10 @@ uint32_t tcnn_b200_batch_size_granularity(void);
 int tcnn_b200_plan_create(const char* json_utf8, uint32_t n_input_dims, uint32_t n_output_dims, tcnn_b200_plan** plan);
 void tcnn_b200_plan_destroy(tcnn_b200_plan* plan);
 int tcnn_b200_plan_info(const tcnn_b200_plan* plan, tcnn_b200_info* info);
+/* GridEncoding::set_max_level (encodings/grid_interface.h:101-107; default 1000 = all levels): levels with
+ * level >= max_level * n_levels + 1e-3 encode to zero and receive no gradient (grid.h:69-82, 236-243).  Takes effect for
+ * every later call on this plan.  The per-sample variant (set_max_level_gpu) is not implemented. */
+int tcnn_b200_plan_set_max_level(tcnn_b200_plan* plan, float max_level);
 /* Trainer::update_hyperparams (trainer.h:213-216): JSON object with optimizer keys (learning_rate, beta1, ...). */
 int tcnn_b200_plan_update_optimizer(tcnn_b200_plan* plan, const char* json_utf8);
 

@@ -21,6 +21,7 @@
 //       host-buffer (H2D inside the timed region) variants.
 #include <tiny-cuda-nn/common_device.h>
 #include <tiny-cuda-nn/config.h>
+#include <tiny-cuda-nn/encodings/grid_interface.h>
 #include <tiny-cuda-nn/random.h>
 
 #include <cctype>
@@ -137,6 +138,11 @@ static int mode_dump(int argc, char** argv) {
 		model.trainer->set_params_full_precision((const float*)p.data(), P, false);
 	}
 	write_dev(out + "/params_used.f16", (const uint16_t*)model.trainer->params(), P);
+	if (const char* ml = getenv("REF_MAX_LEVEL")) { // GridEncoding::set_max_level (grid_interface.h:105-107)
+		auto* ge = dynamic_cast<GridEncoding<precision_t>*>(model.network->encoding().get());
+		if (!ge) { std::cerr << "dump: REF_MAX_LEVEL needs a grid encoding\n"; return 2; }
+		ge->set_max_level(std::stof(ml));
+	}
 
 	GPUMatrix<float> input(n_in, B), target(n_out, B);
 	CUDA_CHECK_THROW(cudaMemcpy(input.data(), in_raw.data(), in_raw.size(), cudaMemcpyHostToDevice));

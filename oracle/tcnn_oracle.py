@@ -177,6 +177,7 @@ class GridConfig:
     # optional per-level (scale, resolution) table dumped from the device (CUDA exp2f vs libm)
     scales: np.ndarray | None = None
     grid_type: str = "Hash"           # Hash | Dense | Tiled (grid.h:702-712; DenseGrid / TiledGrid otypes, grid.h:1180-1208)
+    max_level: float = 1000.0         # GridEncoding::m_max_level (grid_interface.h:120)
     interpolation: str = "Linear"     # Nearest | Linear | Smoothstep (common_device.h:801-807; Nearest: grid.h:121-139)
     offsets: np.ndarray = field(init=False)
     resolutions: np.ndarray = field(init=False)
@@ -224,6 +225,14 @@ class GridConfig:
     @property
     def smooth(self) -> bool:
         return self.interpolation.lower() == "smoothstep"
+
+    @property
+    def active_levels(self) -> int:
+        """GridEncoding::set_max_level (grid_interface.h:101-107): levels with level >= max_level * n_levels + 1e-3 (fp32,
+        grid.h:69-75) encode to zero and receive no gradient (grid.h:236-243).  Default 1000 = all levels."""
+        F = F32(self.n_features_per_level)
+        scaled = F32(F32(F32(self.max_level) * F32(self.n_levels * self.n_features_per_level)) / F)
+        return sum(1 for l in range(self.n_levels) if not (F32(l) >= F32(scaled + F32(1e-3))))
 
     @property
     def nearest(self) -> bool:
@@ -312,7 +321,7 @@ def grid_forward(cfg: GridConfig, x: np.ndarray, table: np.ndarray) -> np.ndarra
     B, F = x.shape[0], cfg.n_features_per_level
     out = np.zeros((B, cfg.n_features), dtype=np.float16)
     t = table.astype(np.float16).reshape(-1, F)
-    for l in range(cfg.n_levels):
+    for l in range(cfg.active_levels):
         idx, w = grid_corners(cfg, x, l)
         base = int(cfg.offsets[l])
         if cfg.nearest:  # the entry itself, no arithmetic (grid.h:121-129) - keeps -0.0
@@ -333,7 +342,7 @@ def grid_backward(cfg: GridConfig, x: np.ndarray, dy: np.ndarray, sequential_fp1
     comparisons are tolerance-based)."""
     F = cfg.n_features_per_level
     g = np.zeros((int(cfg.offsets[-1]), F), dtype=np.float64)
-    for l in range(cfg.n_levels):
+    for l in range(cfg.active_levels):
         idx, w = grid_corners(cfg, x, l)
         base = int(cfg.offsets[l])
         gl = dy[:, l * F:(l + 1) * F].astype(np.float16)
@@ -365,7 +374,7 @@ def grid_forward_f32(cfg: GridConfig, x: np.ndarray, table: np.ndarray) -> np.nd
     B, F = x.shape[0], cfg.n_features_per_level
     out = np.zeros((B, cfg.n_features), dtype=np.float32)
     t = table.astype(np.float32).reshape(-1, F)
-    for l in range(cfg.n_levels):
+    for l in range(cfg.active_levels):
         idx, w = grid_corners(cfg, x, l)
         base = int(cfg.offsets[l])
         if cfg.nearest:
@@ -384,7 +393,7 @@ def grid_backward_f32(cfg: GridConfig, x: np.ndarray, dy: np.ndarray) -> np.ndar
     float64 (the atomics' order is arbitrary).  dy fp32 [B, >= L*F] -> float64 [n_params]."""
     F = cfg.n_features_per_level
     g = np.zeros((int(cfg.offsets[-1]), F), dtype=np.float64)
-    for l in range(cfg.n_levels):
+    for l in range(cfg.active_levels):
         idx, w = grid_corners(cfg, x, l)
         base = int(cfg.offsets[l])
         gl = dy[:, l * F:(l + 1) * F].astype(np.float32)
@@ -405,7 +414,7 @@ def grid_backward_input(cfg: GridConfig, x: np.ndarray, table: np.ndarray, dy: n
     result = np.zeros((B, D), np.float32)
     if cfg.nearest:  # "Gradient is zero when there's no interpolation" (grid.h:131-137)
         return result
-    for l in range(cfg.n_levels):
+    for l in range(cfg.active_levels):
         scale, res = F32(cfg.scales[l]), int(cfg.resolutions[l])
         frac, cell = pos_fract(x, F32(scale))
         dfrac = smoothstep_derivative(frac) if cfg.smooth else np.ones_like(frac)  # pos_derivative (grid.h:100-113)
@@ -780,7 +789,7 @@ def grid_dy_dx(cfg: GridConfig, x: np.ndarray, table: np.ndarray) -> np.ndarray:
     F = cfg.n_features_per_level
     t = table.astype(np.float16).reshape(-1, F)
     out = np.zeros((B, cfg.n_features, D), np.float32)
-    for l in range(cfg.n_levels):
+    for l in range(cfg.active_levels):
         scale, res = F32(cfg.scales[l]), int(cfg.resolutions[l])
         w, dw, _, cell = _level_frac(cfg, x, l)
         size, base = cfg.level_size(l), int(cfg.offsets[l])
@@ -814,7 +823,7 @@ def grid_bwd_bwd_grid(cfg: GridConfig, x: np.ndarray, dy: np.ndarray, dL_ddLdx: 
     B, D = x.shape
     F = cfg.n_features_per_level
     g = np.zeros((int(cfg.offsets[-1]), F), np.float64)
-    for l in range(cfg.n_levels):
+    for l in range(cfg.active_levels):
         scale, res = F32(cfg.scales[l]), int(cfg.resolutions[l])
         w, dw, _, cell = _level_frac(cfg, x, l)
         size, base = cfg.level_size(l), int(cfg.offsets[l])
@@ -846,7 +855,7 @@ def grid_bwd_bwd_input(cfg: GridConfig, x: np.ndarray, table: np.ndarray, dy: np
     t = table.astype(np.float16).reshape(-1, F).astype(np.float32)
     out = np.zeros((B, D), np.float32)
     v = dL_ddLdx.astype(np.float32)
-    for l in range(cfg.n_levels):
+    for l in range(cfg.active_levels):
         scale, res = F32(cfg.scales[l]), int(cfg.resolutions[l])
         w, dw, d2w, cell = _level_frac(cfg, x, l)
         size, base = cfg.level_size(l), int(cfg.offsets[l])

@@ -164,3 +164,7 @@ def fp32_inputs(n_in, n_table, n_features, padded_width, B=256, seed=6):
     dy = np.zeros((B, padded_width), np.float32)
     dy[:, :n_features] = rng.standard_normal((B, n_features)).astype(np.float32)
     return x, table, dy
+
+
+# goldens dumped with GridEncoding::set_max_level(value) (REF_MAX_LEVEL of `ref_driver dump`): name -> max_level
+MAX_LEVEL_CASES = {"maxlevel_f4_3d_T14": 0.5}

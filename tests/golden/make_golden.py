@@ -35,6 +35,8 @@ CASES = [  # name, config, n_in, n_out, B
     ("tiled_smooth_2d", common.CONFIG_TILED_SMOOTH, 2, 3, 512),
     ("dense_3d_f4", common.CONFIG_DENSE, 3, 3, 512),
     ("nearest_3d_T12", common.CONFIG_NEAREST, 3, 3, 512),
+    # GridEncoding::set_max_level(0.5): the upper half of the levels encodes to zero (REF_MAX_LEVEL of ref_driver dump)
+    ("maxlevel_f4_3d_T14", common.CONFIG_F4, 3, 3, 512),
     # hidden / output activations
     ("act_a_sigmoid_exp_64", common.CONFIG_ACT_A, 2, 3, 512),
     ("act_b_tanh_sigmoid_128", common.CONFIG_ACT_B, 2, 3, 512),
@@ -143,8 +145,9 @@ def main(outdir):
             x.tofile(os.path.join(d, "x.f32")); t.tofile(os.path.join(d, "t.f32"))
             with open(os.path.join(d, "cfg.json"), "w") as f:
                 json.dump(cfg, f)
+            env = dict(os.environ, REF_MAX_LEVEL=str(common.MAX_LEVEL_CASES[name])) if name in common.MAX_LEVEL_CASES else None
             r = subprocess.run([REF, "dump", os.path.join(d, "cfg.json"), str(n_in), str(n_out), str(B), os.path.join(d, "x.f32"),
-                                os.path.join(d, "t.f32"), d], capture_output=True, text=True, timeout=600)
+                                os.path.join(d, "t.f32"), d], capture_output=True, text=True, timeout=600, env=env)
             print(name, r.returncode, r.stdout.strip(), r.stderr.strip()[-400:], flush=True)
             if r.returncode != 0:
                 continue

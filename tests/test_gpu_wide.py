@@ -23,6 +23,7 @@ CASES = {
     "tiled_smooth_2d": (common.CONFIG_TILED_SMOOTH, 2, 3),
     "dense_3d_f4": (common.CONFIG_DENSE, 3, 3),
     "nearest_3d_T12": (common.CONFIG_NEAREST, 3, 3),
+    "maxlevel_f4_3d_T14": (common.CONFIG_F4, 3, 3),  # GridEncoding::set_max_level(0.5), common.MAX_LEVEL_CASES
     "wide_dp_3d_T15": (common.CONFIG_WIDE_DP, 3, 3),
     "wide_f4_3d_T14": (common.CONFIG_WIDE_F4, 3, 4),
     "oneblob_2d_128x5": (common.CONFIG_ONEBLOB, 2, 3),
@@ -57,6 +58,9 @@ class Ctx:
         self.info, self.lib = self.native.info, self.native.lib
         L = self.info.n_levels
         self.g, self.m = common.oracle_configs(self.cfg, self.n_in, self.n_out, scales=np.array(self.info.level_scale[:L], dtype=np.float32) if L else None)
+        if name in common.MAX_LEVEL_CASES:
+            self.native.set_max_level(common.MAX_LEVEL_CASES[name])
+            self.g.max_level = common.MAX_LEVEL_CASES[name]
         self.golden = np.load(os.path.join(GOLDEN, name + ".npz"))
         self.dev = dev
 
@@ -139,6 +143,8 @@ def test_grid_input_gradient_vs_oracle(ctx):
     B = 512
     rng = np.random.default_rng(21)
     enc_mod = tcnn.NativeModule(ctx.n_in, 0, {"encoding": ctx.cfg["encoding"]})
+    if ctx.name in common.MAX_LEVEL_CASES:
+        enc_mod.set_max_level(common.MAX_LEVEL_CASES[ctx.name])
     x_np, _ = common.synth_inputs(B, ctx.n_in, ctx.n_out, seed=8)
     table_np = rng.uniform(-0.5, 0.5, ctx.g.n_params).astype(np.float16)
     W = enc_mod.info.encoded_width
@@ -250,6 +256,8 @@ def test_trainer_converges_and_matches_unfused_step(ctx):
     a = tcnn.create_from_config(ctx.n_in, ctx.n_out, ctx.cfg, device=ctx.dev)
     b = tcnn.create_from_config(ctx.n_in, ctx.n_out, ctx.cfg, device=ctx.dev)
     b.trainer.use_fused_step = False
+    if ctx.name in common.MAX_LEVEL_CASES:  # the fused kernel and the separate kernels both stop at the active levels
+        a.trainer.native.set_max_level(common.MAX_LEVEL_CASES[ctx.name]); b.trainer.native.set_max_level(common.MAX_LEVEL_CASES[ctx.name])
     la = []
     for i in range(40):
         x_np, t_np = common.synth_inputs(B, ctx.n_in, ctx.n_out, seed=50 + i)
@@ -261,6 +269,10 @@ def test_trainer_converges_and_matches_unfused_step(ctx):
     n = ctx.m.n_params
     # fp16 atomics of the grid scatter make two runs differ in the last bits, and 40 Adam steps (sign-like updates early on) amplify that
     assert common.rel_l2(pa[:n], pb[:n]) < (2e-2 if ctx.g is not None else 2e-3)
+    if ctx.name in common.MAX_LEVEL_CASES:  # levels above max_level never receive a gradient: their entries keep the initial values
+        first_dead = ctx.m.n_params + int(ctx.g.offsets[ctx.g.active_levels]) * ctx.g.n_features_per_level
+        p0 = a.trainer.native.initial_params(1337, ctx.dev, trainer_seeding=True).cpu().numpy()
+        assert np.array_equal(pa[first_dead:], p0[first_dead:]) and not np.array_equal(pa[ctx.m.n_params:first_dead], p0[ctx.m.n_params:first_dead])
     assert abs(a.trainer.loss() - b.trainer.loss()) < 5e-2 * abs(b.trainer.loss())
 
 

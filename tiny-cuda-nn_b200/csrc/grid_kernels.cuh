@@ -449,7 +449,8 @@ __global__ void __launch_bounds__(256) grid_forward_f32_kernel(const __grid_cons
 	if (i >= B) return;
 	const uint32_t level = blockIdx.y;
 	float* out = encoded + (size_t)i * gp.padded_width;
-	if (level == 0) for (uint32_t k = gp.n_features; k < gp.padded_width; ++k) out[k] = 0.0f; // padding (grid.h:749-759)
+	if (level == 0) for (uint32_t k = gp.n_features; k < gp.padded_width; ++k) out[k] = 0.0f; // padding (grid.h:749-759) and levels above max_level
+	if (level >= gp.n_levels) return;
 	const GridLevel& lv = gp.level[level];
 	const float* table = grid + (size_t)lv.offset * F;
 	float p[D];
@@ -486,6 +487,7 @@ __global__ void __launch_bounds__(256) grid_backward_f32_kernel(const __grid_con
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= B) return;
 	const uint32_t level = blockIdx.y;
+	if (level >= gp.n_levels) return; // set_max_level(<= 0): no active level, the launch still has one row of blocks
 	const GridLevel& lv = gp.level[level];
 	float* gtable = grid_grad + (size_t)lv.offset * F;
 	float p[D];
@@ -695,6 +697,7 @@ __global__ void __launch_bounds__(256) grid_backward_backward_grid_kernel(const 
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= B) return;
 	const uint32_t level = blockIdx.y;
+	if (level >= gp.n_levels) return; // set_max_level(<= 0): no active level, the launch still has one row of blocks
 	const GridLevel& lv = gp.level[level];
 	float p[D];
 	load_position<D>(x, i, p);
@@ -758,6 +761,7 @@ __global__ void grid_indices_kernel(const __grid_constant__ GridParams gp, uint3
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= B) return;
 	const uint32_t level = blockIdx.y;
+	// (a diagnostic of the index function: every level of the table, whatever max_level says)
 	const GridLevel& lv = gp.level[level];
 	float p[D];
 	load_position<D>(x, i, p);

@@ -9,6 +9,8 @@
 #include <cmath>
 #include <cstring>
 #include <limits>
+#include <map>
+#include <mutex>
 #include <memory>
 #include <random>
 #include <string>
@@ -119,7 +121,7 @@ static GridParams backward_params(const tcnn_b200_plan* p, uint32_t B, bool have
 }
 static size_t replica_bytes(const tcnn_b200_plan* p) {
 	size_t entries = 0;
-	for (uint32_t l = 0; l < p->grid.n_levels; ++l) if (p->grid.level[l].size <= REPLICATE_MAX_ENTRIES) entries += p->grid.level[l].size;
+	for (uint32_t l = 0; l < p->info.n_levels; ++l) if (p->grid.level[l].size <= REPLICATE_MAX_ENTRIES) entries += p->grid.level[l].size; // all levels, whatever max_level says
 	return entries * p->info.n_features_per_level * 2 * N_REPLICAS;
 }
 
@@ -357,6 +359,22 @@ static void ensure_aux(const tcnn_b200_plan* plan_) {
 	CUDA_OK(cudaStreamCreateWithFlags(&p->aux, cudaStreamNonBlocking));
 	for (auto& e : p->ev) CUDA_OK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
 	p->aux_ready = true;
+}
+
+// GridEncoding::set_max_level (grid_interface.h:101-107).  Levels with level >= max_level * n_levels + 1e-3 (fp32, exactly the
+// comparison of grid.h:69-75) encode to zero and get no gradient (grid.h:236-243).  The kernels stop at GridParams::n_levels
+// and leave the columns behind it zero, so the setter only moves that bound; parameter layout and counts do not change.
+extern "C" int tcnn_b200_plan_set_max_level(tcnn_b200_plan* plan, float max_level) {
+	API_BEGIN
+	CHECK(plan, "null argument");
+	CHECK(plan->enc_kind == ENC_GRID && plan->info.n_levels > 0, "max_level belongs to grid encodings");
+	const uint32_t L = plan->info.n_levels, F = plan->info.n_features_per_level;
+	const float scaled = (max_level * (float)(L * F)) / (float)F;
+	uint32_t active = 0;
+	for (uint32_t l = 0; l < L; ++l) if (!((float)l >= scaled + 1e-3f)) active = l + 1;
+	plan->grid.n_levels = active;
+	plan->grid.n_features = active * F;
+	API_END
 }
 
 extern "C" int tcnn_b200_plan_info(const tcnn_b200_plan* plan, tcnn_b200_info* info) {
@@ -630,16 +648,40 @@ extern "C" int tcnn_b200_grid_indices(const tcnn_b200_plan* plan, void* stream, 
 #ifndef TCNN_B200_SCATTER_WARPGROUPS
 #define TCNN_B200_SCATTER_WARPGROUPS 2
 #endif
+// cudaFuncAttributeMaxDynamicSharedMemorySize of a kernel, only ever raised, one record per kernel for the whole process:
+// the attribute belongs to the function, not to the calling thread - a thread-local cache let torch's autograd thread lower
+// the value another thread had set for a wider input (the same instantiation serves several input widths).
+template <typename K>
+static uint32_t ensure_dynamic_smem(K kernel, uint32_t smem) {
+	static std::mutex mutex;
+	static std::map<std::pair<int, const void*>, uint32_t> configured; // per device: one process may drive several GPUs
+	int device = 0;
+	CUDA_OK(cudaGetDevice(&device));
+	std::lock_guard<std::mutex> lock(mutex);
+	uint32_t& have = configured[std::make_pair(device, (const void*)kernel)];
+	if (have < smem) {
+		CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		have = smem;
+	}
+	return have;
+}
 template <int MODE, int H, int FD = 0, int FF = 2, int NSG = 0, bool GEN = false, bool WIN = false>
 static void launch_mlp_k(const tcnn_b200_plan* plan, cudaStream_t stream, const MlpArgs& a, uint32_t grid, const GridParams& gp, uint32_t smem) {
-	static thread_local uint32_t configured = 0;
-	if (configured < smem) {
-		CUDA_OK(cudaFuncSetAttribute(mlp_kernel<MODE, H, FD, FF, NSG, GEN, WIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-		configured = smem;
-	}
+	const uint32_t configured = ensure_dynamic_smem(mlp_kernel<MODE, H, FD, FF, NSG, GEN, WIN>, smem);
 	ProfileScope prof(plan, stream, PK_MLP);
 	mlp_kernel<MODE, H, FD, FF, NSG, GEN, WIN><<<grid, 128 + 128 * NSG, smem, stream>>>(a, gp);
-	launch_check("mlp_kernel");
+	{
+		const cudaError_t e = cudaGetLastError();
+		if (e != cudaSuccess) {
+			cudaFuncAttributes fa{};
+			const cudaError_t qe = cudaFuncGetAttributes(&fa, mlp_kernel<MODE, H, FD, FF, NSG, GEN, WIN>);
+			int dev = -1; cudaGetDevice(&dev);
+			FAIL(std::string("mlp_kernel launch failed: ") + cudaGetErrorString(e) + " (mode " + std::to_string(MODE) + ", hidden " + std::to_string(H) +
+				", grid " + std::to_string(grid) + ", threads " + std::to_string(128 + 128 * NSG) + ", smem " + std::to_string(smem) + ", configured " + std::to_string(configured) +
+				", attr query " + cudaGetErrorString(qe) + ", maxDynamicSharedSizeBytes " + std::to_string(fa.maxDynamicSharedSizeBytes) + ", static smem " + std::to_string(fa.sharedSizeBytes) +
+				", regs " + std::to_string(fa.numRegs) + ", device " + std::to_string(dev) + ", stream " + std::to_string((uintptr_t)stream) + ")");
+		}
+	}
 }
 template <int MODE, int H, int FD = 0, int FF = 2>
 static void launch_mlp_h(const tcnn_b200_plan* plan, cudaStream_t stream, const MlpArgs& a, uint32_t grid, const GridParams& gp) {
@@ -663,9 +705,7 @@ static void launch_mlp_h(const tcnn_b200_plan* plan, cudaStream_t stream, const 
 }
 // ---- 128 neurons: forward (+ loss) -> dgrad chain -> split-K weight gradients (mlp_wide_kernels.cuh) ----
 template <typename K>
-static void wide_set_smem(K kernel, uint32_t smem) {
-	CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-}
+static void wide_set_smem(K kernel, uint32_t smem) { ensure_dynamic_smem(kernel, smem); }
 template <int MODE>
 static void launch_mlp_wide(const tcnn_b200_plan* plan, cudaStream_t stream, const MlpArgs& a, uint32_t n_splits) {
 	constexpr bool train = MODE != MODE_INFER;
@@ -866,7 +906,7 @@ extern "C" int tcnn_b200_inference(const tcnn_b200_plan* plan, void* stream_, ui
 		CHECK(plan->enc_kind == ENC_GRID, "fp32 precision is implemented for grid encodings");
 		float* out = output_fp32 ? output_fp32 : (float*)output_fp16;
 		ProfileScope prof(plan, stream, PK_GRID_FWD);
-		const dim3 g((B + 255) / 256, plan->info.n_levels, 1);
+		const dim3 g((B + 255) / 256, std::max(plan->grid.n_levels, 1u), 1);
 		GRID_DISPATCH(grid_forward_f32_kernel, plan, g, stream, plan->grid, B, x, (const float*)params, out);
 		launch_check("grid_forward_f32_kernel");
 		return 0;
@@ -899,7 +939,7 @@ extern "C" int tcnn_b200_backward(const tcnn_b200_plan* plan, void* stream_, uin
 		ProfileScope prof(plan, stream, PK_GRID_BWD);
 		if (dL_dparams) {
 			CUDA_OK(cudaMemsetAsync(dL_dparams, 0, plan->info.n_params_grid * sizeof(float), stream));
-			const dim3 gl((B + 255) / 256, plan->info.n_levels, 1);
+			const dim3 gl((B + 255) / 256, std::max(plan->grid.n_levels, 1u), 1);
 			GRID_DISPATCH(grid_backward_f32_kernel, plan, gl, stream, plan->grid, B, x, (const float*)dL_doutput, (float*)dL_dparams);
 			launch_check("grid_backward_f32_kernel");
 		}
@@ -971,7 +1011,7 @@ extern "C" int tcnn_b200_backward_backward_input(const tcnn_b200_plan* plan, voi
 	if (dL_dparams) { // GradientMode::Overwrite
 		ProfileScope prof(plan, stream, PK_GRID_BWD);
 		CUDA_OK(cudaMemsetAsync(dL_dparams, 0, plan->info.n_params_grid * 2, stream));
-		const dim3 gl((B + 255) / 256, plan->info.n_levels, 1);
+		const dim3 gl((B + 255) / 256, std::max(plan->grid.n_levels, 1u), 1);
 		GRID_DISPATCH(grid_backward_backward_grid_kernel, plan, gl, stream, plan->grid, B, x, (const __half*)dL_doutput, dL_ddLdinput, (__half*)dL_dparams);
 		launch_check("grid_backward_backward_grid_kernel");
 	}

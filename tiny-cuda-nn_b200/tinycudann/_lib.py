@@ -62,6 +62,7 @@ _SIGNATURES = {
     "tcnn_b200_plan_create": (C.c_int, [C.c_char_p, C.c_uint32, C.c_uint32, C.POINTER(_P)]),
     "tcnn_b200_plan_destroy": (None, [_P]),
     "tcnn_b200_plan_info": (C.c_int, [_P, C.POINTER(Info)]),
+    "tcnn_b200_plan_set_max_level": (C.c_int, [_P, C.c_float]),
     "tcnn_b200_plan_update_optimizer": (C.c_int, [_P, C.c_char_p]),
     "tcnn_b200_workspace_bytes": (C.c_size_t, [_P, C.c_uint32]),
     "tcnn_b200_init_params": (C.c_int, [_P, _P, C.c_uint64, C.c_int, _P]),

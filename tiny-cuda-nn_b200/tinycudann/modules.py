@@ -41,6 +41,10 @@ class NativeModule:
         except Exception:
             pass
 
+    def set_max_level(self, max_level: float):
+        """GridEncoding::set_max_level (grid_interface.h:101-107): levels >= max_level * n_levels encode to zero."""
+        check(self.lib.tcnn_b200_plan_set_max_level(self.handle, float(max_level)))
+
     def refresh_info(self):
         check(self.lib.tcnn_b200_plan_info(self.handle, _lib.C.byref(self.info)))
 
