@@ -178,6 +178,7 @@ class GridConfig:
     scales: np.ndarray | None = None
     grid_type: str = "Hash"           # Hash | Dense | Tiled (grid.h:702-712; DenseGrid / TiledGrid otypes, grid.h:1180-1208)
     max_level: float = 1000.0         # GridEncoding::m_max_level (grid_interface.h:120)
+    stochastic: bool = False          # "stochastic_interpolation" (grid.h:284-303): backward pass only
     interpolation: str = "Linear"     # Nearest | Linear | Smoothstep (common_device.h:801-807; Nearest: grid.h:121-139)
     offsets: np.ndarray = field(init=False)
     resolutions: np.ndarray = field(init=False)
@@ -343,6 +344,22 @@ def grid_backward(cfg: GridConfig, x: np.ndarray, dy: np.ndarray, sequential_fp1
     F = cfg.n_features_per_level
     g = np.zeros((int(cfg.offsets[-1]), F), dtype=np.float64)
     for l in range(cfg.active_levels):
+        if cfg.stochastic and not cfg.nearest:
+            # grid.h:284-303: sample = random_val(1337, i + level * B) = pcg32{1337} advanced by that (uint32) index; the same
+            # draw picks cell or cell + 1 in every dimension; the whole gradient goes to that corner (weight 1)
+            B = x.shape[0]
+            frac, cell = pos_fract(x, cfg.scales[l])
+            if cfg.smooth:
+                frac = smoothstep(frac)
+            sample = np.empty(B, np.float32)
+            for i in range(B):
+                r = Pcg32(1337)
+                r.advance((i + l * B) & 0xFFFFFFFF)
+                sample[i] = _uint_to_float01(np.array([r.next_uint()], dtype=np.uint32))[0]
+            pg = np.where(sample[:, None] >= frac, cell, cell + U32(1)).astype(np.uint32)
+            ids = grid_index(pg, cfg.level_size(l), int(cfg.resolutions[l]), cfg.hashed).astype(np.int64)
+            np.add.at(g, int(cfg.offsets[l]) + ids, dy[:, l * F:(l + 1) * F].astype(np.float16).astype(np.float64))
+            continue
         idx, w = grid_corners(cfg, x, l)
         base = int(cfg.offsets[l])
         gl = dy[:, l * F:(l + 1) * F].astype(np.float16)

@@ -40,6 +40,13 @@ CONFIG_NEAREST = {  # Nearest "interpolation" (grid.h:121-139, 279-282): hashed 
     "encoding": {"otype": "HashGrid", "n_levels": 8, "n_features_per_level": 2, "log2_hashmap_size": 12, "base_resolution": 4, "per_level_scale": 1.6, "interpolation": "Nearest"},
     "network": {"otype": "FullyFusedMLP", "activation": "ReLU", "output_activation": "None", "n_neurons": 64, "n_hidden_layers": 2},
 }
+CONFIG_STOCHASTIC = {  # stochastic_interpolation (grid.h:284-303), Smoothstep weights, 2-D
+    "loss": {"otype": "L2"},
+    "optimizer": {"otype": "Adam", "learning_rate": 1e-3},
+    "encoding": {"otype": "HashGrid", "n_levels": 8, "n_features_per_level": 2, "log2_hashmap_size": 12, "base_resolution": 8, "per_level_scale": 1.5,
+                 "interpolation": "Smoothstep", "stochastic_interpolation": True},
+    "network": {"otype": "FullyFusedMLP", "activation": "ReLU", "output_activation": "None", "n_neurons": 64, "n_hidden_layers": 2},
+}
 CONFIG_DENSE = {  # DenseGrid, Linear, 3-D, F = 4
     "loss": {"otype": "L2"},
     "optimizer": {"otype": "Adam", "learning_rate": 1e-3},
@@ -104,7 +111,7 @@ def oracle_configs(cfg, n_in, n_out, scales=None):
     gtype = "Dense" if otype == "densegrid" else "Tiled" if otype == "tiledgrid" else e.get("type", "Hash")
     g = O.GridConfig(n_in, e.get("n_levels", 16), e.get("n_features_per_level", 2), e.get("log2_hashmap_size", 19),
                      e.get("base_resolution", 16), e.get("per_level_scale", 2.0), scales=scales, grid_type=gtype,
-                     interpolation=e.get("interpolation", "Linear"))
+                     interpolation=e.get("interpolation", "Linear"), stochastic=bool(e.get("stochastic_interpolation", False)))
     n = cfg["network"]
     m = O.MlpConfig(O.next_multiple(g.n_features, 16), n_out, n.get("n_neurons", 128), n.get("n_hidden_layers", 5),
                     n.get("activation", "ReLU"), n.get("output_activation", "None"))

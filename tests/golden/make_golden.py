@@ -35,6 +35,7 @@ CASES = [  # name, config, n_in, n_out, B
     ("tiled_smooth_2d", common.CONFIG_TILED_SMOOTH, 2, 3, 512),
     ("dense_3d_f4", common.CONFIG_DENSE, 3, 3, 512),
     ("nearest_3d_T12", common.CONFIG_NEAREST, 3, 3, 512),
+    ("stochastic_2d_T12", common.CONFIG_STOCHASTIC, 2, 3, 512),
     # GridEncoding::set_max_level(0.5): the upper half of the levels encodes to zero (REF_MAX_LEVEL of ref_driver dump)
     ("maxlevel_f4_3d_T14", common.CONFIG_F4, 3, 3, 512),
     # hidden / output activations

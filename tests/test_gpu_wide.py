@@ -23,6 +23,7 @@ CASES = {
     "tiled_smooth_2d": (common.CONFIG_TILED_SMOOTH, 2, 3),
     "dense_3d_f4": (common.CONFIG_DENSE, 3, 3),
     "nearest_3d_T12": (common.CONFIG_NEAREST, 3, 3),
+    "stochastic_2d_T12": (common.CONFIG_STOCHASTIC, 2, 3),
     "maxlevel_f4_3d_T14": (common.CONFIG_F4, 3, 3),  # GridEncoding::set_max_level(0.5), common.MAX_LEVEL_CASES
     "wide_dp_3d_T15": (common.CONFIG_WIDE_DP, 3, 3),
     "wide_f4_3d_T14": (common.CONFIG_WIDE_F4, 3, 4),

@@ -44,6 +44,8 @@ struct GridParams {
 	uint32_t rep_entries;    // entries per replica (sum of the replicated levels' sizes)
 	uint32_t image_subs;     // 0: encoded rows [B][padded_width]; n > 0: tile images with n sub-tiles per tile (wide_image_chunk)
 	uint32_t smoothstep;     // interpolation: 0 = Linear, 1 = Smoothstep (weights w -> w^2 (3 - 2 w), common_device.h:801-807)
+	uint32_t stochastic;     // stochastic_interpolation (grid.h:284-303): the backward pass adds the whole gradient to ONE random corner
+	uint64_t rng_state, rng_inc; // pcg32{1337} after seeding (random_val, common_device.h:333-337), filled by plan_create
 	uint32_t nearest;        // interpolation Nearest (grid.h:121-139): own kernels below, never reaches the interpolating ones
 	GridLevel level[MAX_LEVELS];
 };
@@ -567,6 +569,55 @@ __global__ void __launch_bounds__(256) grid_nearest_backward_kernel(const __grid
 		__half* entry = grid_grad + ((size_t)lv.offset + grid_index_dev<D>(lv, cell)) * F;
 #pragma unroll
 		for (int f = 0; f < F / 2; ++f) red_add_h2(entry + 2 * f, g.h2[s * (F / 2) + f]); // (half)1.0f * grad = grad
+	}
+}
+
+
+// stochastic_interpolation (grid.h:284-303): one draw per (sample, level) - random_val(1337, i + level * B), i.e. pcg32{1337}
+// advanced by that index - picks cell or cell + 1 in EVERY dimension by comparing the same draw with the (interpolated)
+// fraction; the whole gradient goes to that corner with weight 1.  The forward pass interpolates as usual.
+__device__ __forceinline__ float pcg32_float_at(uint64_t state, uint64_t inc, uint64_t delta) {
+	uint64_t cur_mult = 0x5851f42d4c957f2dULL, cur_plus = inc, acc_mult = 1u, acc_plus = 0u;
+	while (delta > 0) {
+		if (delta & 1) { acc_mult *= cur_mult; acc_plus = acc_plus * cur_mult + cur_plus; }
+		cur_plus = (cur_mult + 1) * cur_plus;
+		cur_mult *= cur_mult;
+		delta >>= 1;
+	}
+	const uint64_t old = acc_mult * state + acc_plus;
+	const uint32_t xorshifted = (uint32_t)(((old >> 18u) ^ old) >> 27u);
+	const uint32_t rot = (uint32_t)(old >> 59u);
+	const uint32_t u = (xorshifted >> rot) | (xorshifted << ((~rot + 1u) & 31));
+	return __uint_as_float((u >> 9) | 0x3f800000u) - 1.0f;
+}
+template <int D, int F>
+__global__ void __launch_bounds__(256) grid_stochastic_backward_kernel(const __grid_constant__ GridParams gp, uint32_t B,
+	const float* __restrict__ x, const __half* __restrict__ dL_denc, __half* __restrict__ grid_grad, uint32_t chunk_begin) {
+	constexpr int LEVELS_PER_CHUNK = 8 / F;
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= B) return;
+	const uint32_t chunk = chunk_begin + blockIdx.y;
+	float p[D];
+	load_position<D>(x, i, p);
+	union { uint4 v; __half2 h2[4]; } g;
+	g.v = __ldg(reinterpret_cast<const uint4*>(dL_denc + (size_t)i * gp.padded_width + chunk * 8));
+#pragma unroll
+	for (int s = 0; s < LEVELS_PER_CHUNK; ++s) {
+		const uint32_t level = chunk * LEVELS_PER_CHUNK + s;
+		if (level >= gp.n_levels) break;
+		const GridLevel& lv = gp.level[level];
+		const float sample = pcg32_float_at(gp.rng_state, gp.rng_inc, (uint64_t)(uint32_t)(i + level * B));
+		uint32_t cell[D];
+#pragma unroll
+		for (int d = 0; d < D; ++d) {
+			float frac;
+			pos_fract_dev(p[d], lv.scale, frac, cell[d]);
+			if (gp.smoothstep) frac = smoothstep_dev(frac);
+			if (!(sample >= frac)) cell[d] += 1u;
+		}
+		__half* entry = grid_grad + ((size_t)lv.offset + grid_index_dev<D>(lv, cell)) * F;
+#pragma unroll
+		for (int f = 0; f < F / 2; ++f) red_add_h2(entry + 2 * f, g.h2[s * (F / 2) + f]);
 	}
 }
 

@@ -244,7 +244,16 @@ extern "C" int tcnn_b200_plan_create(const char* json_utf8, uint32_t n_input_dim
 	CHECK(interp == "nearest" || interp == "linear" || interp == "smoothstep", "interpolation '" + interp + "' does not exist (Nearest, Linear, Smoothstep)");
 	p->grid.smoothstep = interp == "smoothstep" ? 1u : 0u;
 	p->grid.nearest = interp == "nearest" ? 1u : 0u;
-	CHECK(!enc.boolean("stochastic_interpolation", false), "stochastic_interpolation is not implemented");
+	p->grid.stochastic = enc.boolean("stochastic_interpolation", false) ? 1u : 0u;
+	CHECK(!(p->f32 && p->grid.stochastic), "stochastic_interpolation is implemented for fp16 precision");
+	{ // pcg32{1337} (pcg32.h:54-60 seed(initstate, initseq = 1)): the generator random_val() of the scatter starts from
+		const uint64_t mult = 0x5851f42d4c957f2dULL, inc = 3u;
+		uint64_t state = 0u;
+		state = state * mult + inc;
+		state += 1337u;
+		state = state * mult + inc;
+		p->grid.rng_state = state; p->grid.rng_inc = inc;
+	}
 	in.n_features_per_level = (uint32_t)enc.number("n_features_per_level", 2);
 	CHECK(in.n_features_per_level == 2 || in.n_features_per_level == 4 || in.n_features_per_level == 8,
 		"GridEncoding: n_features_per_level must be 2, 4 or 8 on this path (1 needs the fp32 gradient variant)");
@@ -580,6 +589,11 @@ static void backward_scatter(const tcnn_b200_plan* plan, cudaStream_t stream, co
 	chunk_end = std::min(chunk_end, n_grad_chunks(plan));
 	if (chunk_begin >= chunk_end) return;
 	const dim3 g((B + 255) / 256, chunk_end - chunk_begin, 1);
+	if (gp.stochastic && !gp.nearest) { // one random corner per level and sample (grid.h:284-303); Nearest returns before it there too
+		GRID_DISPATCH(grid_stochastic_backward_kernel, plan, g, stream, gp, B, x, dL_denc, grid_grads, chunk_begin);
+		launch_check("grid_stochastic_backward_kernel");
+		return;
+	}
 	if (gp.nearest) { // one RED per level and sample straight into the gradient buffer; the (zeroed) replicas stay zero
 		GRID_DISPATCH(grid_nearest_backward_kernel, plan, g, stream, gp, B, x, dL_denc, grid_grads, chunk_begin);
 		launch_check("grid_nearest_backward_kernel");
@@ -762,7 +776,7 @@ static void launch_mlp(const tcnn_b200_plan* plan, cudaStream_t stream, const Ml
 // Training kernel with the hash-table gradient scatter fused into its last stage; instantiated for the common shapes.
 static bool fused_scatter_available(const tcnn_b200_plan* plan) {
 	const uint32_t D = plan->info.n_input_dims, F = plan->info.n_features_per_level;
-	return !is_wide(plan) && plan->enc_kind == ENC_GRID && !plan->grid.smoothstep && !plan->grid.nearest && plan->activation == ACT_RELU && plan->info.n_hidden_layers <= 4
+	return !is_wide(plan) && plan->enc_kind == ENC_GRID && !plan->grid.smoothstep && !plan->grid.nearest && !plan->grid.stochastic && plan->activation == ACT_RELU && plan->info.n_hidden_layers <= 4
 		&& plan->info.encoded_width <= 64 && (D == 2 || D == 3) && (F == 2 || F == 4);
 }
 template <int H>
