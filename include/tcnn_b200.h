@@ -90,6 +90,17 @@ int tcnn_b200_encode_forward(const tcnn_b200_plan* plan, void* stream, uint32_t 
  * clears it first (the reference's cudaMemsetAsync, grid.h:857-859).  workspace may be NULL (then the coarse levels
  * are scattered without the contention-avoiding private copies). */
 int tcnn_b200_encode_backward(const tcnn_b200_plan* plan, void* stream, uint32_t batch_size, const float* x, const void* dL_dencoded_fp16, void* grid_grads_fp16, int zero_first, void* workspace);
+/* tcnn_b200_encode_backward without a workspace and without any device allocation.  This entry point has no counterpart
+ * in the reference; it was added for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it).  The scratch of the scatter (the private gradient
+ * copies of the coarse levels, used for batches >= 2^14) lives in a file-scope device array of
+ * TCNN_B200_NOALLOC_SCRATCH_BYTES inside the library, which every GPU that loads the library holds until exit.  The call
+ * itself calls no cudaMalloc / cudaFree / allocating routine; a grid whose coarse levels need more scratch than the array
+ * holds is rejected with an error (use tcnn_b200_encode_backward), as is a plan created without a CUDA device or with
+ * profiling enabled.  All calls share the one array: each call clears the part it uses on its stream first, and calls
+ * that overlap on the GPU (different streams, different host threads) race on it - serialise them.  fp16 grid encodings. */
+#define TCNN_B200_NOALLOC_SCRATCH_BYTES (2u << 20)
+int tcnn_b200_encode_backward_noalloc(const tcnn_b200_plan* plan, void* stream, uint32_t batch_size, const float* x, const void* dL_dencoded_fp16, void* grid_grads_fp16, int zero_first);
 /* Parity probe: entry index of every interpolation corner, uint32 [n_levels][B][2^D], computed by the same device
  * functions as the two kernels above (grid_index, common_device.h:690-707). */
 int tcnn_b200_grid_indices(const tcnn_b200_plan* plan, void* stream, uint32_t batch_size, const float* x, uint32_t* indices);

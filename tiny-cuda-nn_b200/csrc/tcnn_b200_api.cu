@@ -645,6 +645,52 @@ extern "C" int tcnn_b200_encode_backward(const tcnn_b200_plan* plan, void* strea
 	encode_backward(plan, (cudaStream_t)stream, B, x, (const __half*)dL_denc, (__half*)grid_grads, zero_first, workspace ? carve(plan, B, workspace).replicas : nullptr);
 	API_END
 }
+// ---- allocation-free variant of tcnn_b200_encode_backward ---------------------------------------------------------
+// For callers that cannot allocate device memory (CUDA graph capture, tight serving loops, harnesses that forbid
+// cudaMalloc): the scratch of the scatter (the private gradient copies of the coarse levels) is a file-scope device array
+// instead of a slice of the caller's workspace.  Every GPU that loads the library holds these bytes until exit.
+// In host code `g_noalloc_scratch` is only a stand-in for the symbol; its device address comes from cudaGetSymbolAddress,
+// once per device with that device current.  The array is shared by all calls and keeps the last call's contents: the
+// part a call uses is cleared on the call's stream first, and calls that overlap on the GPU race on it.
+constexpr size_t NOALLOC_SCRATCH_BYTES = TCNN_B200_NOALLOC_SCRATCH_BYTES; // 2 MiB (include/tcnn_b200.h)
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_SCRATCH_BYTES];
+
+static __half* noalloc_scratch_address() {
+	constexpr int MAX_DEVICES = 64;
+	static std::mutex mutex;
+	static void* address[MAX_DEVICES] = {};
+	int device = 0;
+	CUDA_OK(cudaGetDevice(&device));
+	CHECK(device >= 0 && device < MAX_DEVICES, "device ordinal out of range");
+	std::lock_guard<std::mutex> lock(mutex);
+	if (!address[device]) {
+		void* p = nullptr;
+		CUDA_OK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+		CHECK(p != nullptr, "cudaGetSymbolAddress returned a null address");
+		address[device] = p;
+	}
+	return (__half*)address[device];
+}
+
+extern "C" int tcnn_b200_encode_backward_noalloc(const tcnn_b200_plan* plan, void* stream, uint32_t B, const float* x, const void* dL_denc, void* grid_grads, int zero_first) {
+	API_BEGIN
+	CHECK(plan, "null plan");
+	// require_device() would evaluate the level scales on first use and allocate for it; a plan created with a device present has them
+	CHECK(plan->device_scales, "allocation-free entry point: the plan must have been created with a CUDA device present");
+	CHECK(!plan->profiling, "allocation-free entry point: per-kernel profiling creates CUDA events, disable it");
+	check_batch(B);
+	CHECK(x && dL_denc && grid_grads, "null argument");
+	CHECK(plan->enc_kind == ENC_GRID && !plan->f32, "allocation-free entry point: fp16 grid encodings only");
+	const GridParams gp = backward_params(plan, B, true);
+	const size_t need = replica_bytes_of(plan, gp);
+	CHECK(need <= NOALLOC_SCRATCH_BYTES, "allocation-free entry point: this grid needs " + std::to_string(need) + " bytes of scatter scratch, the built-in array holds " +
+		std::to_string(NOALLOC_SCRATCH_BYTES) + " (use tcnn_b200_encode_backward with a workspace)");
+	__half* scratch = noalloc_scratch_address();
+	// backward_prepare clears the `need` bytes of the array this call accumulates into (cudaMemsetAsync on `stream`)
+	encode_backward(plan, (cudaStream_t)stream, B, x, (const __half*)dL_denc, (__half*)grid_grads, zero_first, scratch);
+	API_END
+}
+
 extern "C" int tcnn_b200_grid_indices(const tcnn_b200_plan* plan, void* stream, uint32_t B, const float* x, uint32_t* indices) {
 	API_BEGIN
 	require_device(plan);

@@ -69,6 +69,7 @@ _SIGNATURES = {
     "tcnn_b200_cast_params": (C.c_int, [_P, C.c_uint64, _P, _P]),
     "tcnn_b200_encode_forward": (C.c_int, [_P, _P, C.c_uint32, _P, _P, _P]),
     "tcnn_b200_encode_backward": (C.c_int, [_P, _P, C.c_uint32, _P, _P, _P, C.c_int, _P]),
+    "tcnn_b200_encode_backward_noalloc": (C.c_int, [_P, _P, C.c_uint32, _P, _P, _P, C.c_int]),
     "tcnn_b200_grid_indices": (C.c_int, [_P, _P, C.c_uint32, _P, _P]),
     "tcnn_b200_mlp_forward": (C.c_int, [_P, _P, C.c_uint32, _P, _P, _P]),
     "tcnn_b200_mlp_backward": (C.c_int, [_P, _P, C.c_uint32, _P, _P, _P, _P, _P, _P]),
