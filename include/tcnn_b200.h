@@ -84,6 +84,10 @@ int tcnn_b200_init_params(const tcnn_b200_plan* plan, void* stream, uint64_t see
 /* fp32 -> fp16 copy of the parameters (trainer.h:83-85). */
 int tcnn_b200_cast_params(void* stream, uint64_t n, const float* params_fp32, void* params_fp16);
 
+/* generate_random_uniform<float>(stream, rng, n, out, lower, upper) of random.h:58-71 with the reference's element -> draw mapping
+ * (random.h:39-56), for a pcg32 generator given by its (state, inc); the caller advances its generator by n afterwards. */
+int tcnn_b200_generate_random_uniform(void* stream, uint64_t rng_state, uint64_t rng_inc, uint64_t n, float* out, float lower, float upper);
+
 /* GridEncoding forward, kernel_grid (encodings/grid.h:48-212, 732-807).  encoded: fp16 [B][encoded_width]. */
 int tcnn_b200_encode_forward(const tcnn_b200_plan* plan, void* stream, uint32_t batch_size, const float* x, const void* grid_params_fp16, void* encoded_fp16);
 /* kernel_grid_backward (grid.h:214-320, 809-900).  Adds into grid_grads_fp16 [n_params_grid]; zero_first != 0
@@ -177,6 +181,11 @@ typedef struct tcnn_b200_dp_comm {
 } tcnn_b200_dp_comm;
 int tcnn_b200_dp_shard(const tcnn_b200_plan* plan, uint32_t rank, uint32_t world_size, uint64_t* param_begin, uint64_t* param_end);
 uint32_t tcnn_b200_dp_flag_bytes(void);
+/* Ranks may enter a step minutes apart (evaluation on one rank, checkpointing, a profiler): the in-kernel waits give up only
+ * after TCNN_B200_DP_TIMEOUT_S seconds (environment, default 600).  A rank that gave up does not trap; it leaves its
+ * parameters untouched and stores the epoch into 32-bit word tcnn_b200_dp_flag_error_word() of its OWN flag block, which the
+ * host reads (after synchronising the stream) and turns into an error. */
+uint32_t tcnn_b200_dp_flag_error_word(void);
 int tcnn_b200_training_step_dp(const tcnn_b200_plan* plan, void* stream, uint32_t batch_size, const float* x, const float* target,
                                float loss_scale, uint32_t adam_step_count, float* params_fp32_shard, float* first_moments_shard,
                                float* second_moments_shard, uint32_t* param_steps_shard, float* loss_out, void* output_fp16,

@@ -2,6 +2,8 @@
  * (include/tiny-cuda-nn/cpp_api.h:86-115, src/cpp_api.cu:62-165), over the tcnn_b200 C ABI.  All pointers are device
  * pointers owned by the caller: input [B][D] fp32, output [B][16] fp16, params / dL_dparams [n_params] fp16. */
 #pragma once
+#include <functional>
+
 #include "trainer.h"
 
 namespace tcnn { namespace cpp {
@@ -10,6 +12,13 @@ enum class Precision { Fp32, Fp16 };
 inline uint32_t batch_size_granularity() { return tcnn_b200_batch_size_granularity(); }
 inline float default_loss_scale(Precision p) { return p == Precision::Fp16 ? 128.0f : 1.0f; }
 inline Precision preferred_precision() { return Precision::Fp16; }
+inline bool has_networks() { return true; }
+inline void free_temporary_memory() { free_all_gpu_memory_arenas(); }
+/* set_log_callback (cpp_api.h:58-66, src/common_host.cu:50-73): the library itself logs nothing - every problem is an exception -
+ * so the callback is only kept for hosts that install one */
+enum class LogSeverity { Info, Debug, Warning, Error, Success };
+inline std::function<void(LogSeverity, const std::string&)>& log_callback() { static std::function<void(LogSeverity, const std::string&)> cb; return cb; }
+inline void set_log_callback(const std::function<void(LogSeverity, const std::string&)>& callback) { log_callback() = callback; }
 
 struct Context { GPUMemory<char> saved; }; /* what backward needs: the encoded batch */
 
@@ -52,6 +61,7 @@ public:
 	Precision param_precision() const { return m_precision; }
 	Precision output_precision() const { return m_precision; }
 	std::string name() const { return "NetworkWithInputEncoding"; }
+	json hyperparams() const { return m_network.hyperparams(); } /* cpp_api.h:112 */
 
 private:
 	Network m_network;

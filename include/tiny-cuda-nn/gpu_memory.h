@@ -2,6 +2,7 @@
  * data(), size(), resize(), enlarge(), memset(), copy_from_host(), copy_to_host(), free_memory()).  Plain cudaMalloc: the
  * tcnn_b200 path has no per-step temporaries, so the reference's stream arena (gpu_memory.h:426-697) has no counterpart. */
 #pragma once
+#include <memory>
 #include <vector>
 
 #include "common.h"
@@ -38,6 +39,8 @@ public:
 		CUDA_CHECK_THROW(cudaMemcpy(m_data, host, n * sizeof(T), cudaMemcpyHostToDevice));
 	}
 	void copy_from_host(const std::vector<T>& host) { enlarge(host.size()); copy_from_host(host.data(), host.size()); }
+	void copy_from_host(const T* host) { copy_from_host(host, m_size); } /* gpu_memory.h:262-264: as many elements as are allocated */
+	void copy_to_host(T* host) const { copy_to_host(host, m_size); }
 	void copy_to_host(T* host, size_t n) const {
 		if (n > m_size) throw std::runtime_error("GPUMemory::copy_to_host: more elements than allocated");
 		CUDA_CHECK_THROW(cudaMemcpy(host, m_data, n * sizeof(T), cudaMemcpyDeviceToHost));
@@ -53,5 +56,16 @@ private:
 	T* m_data = nullptr;
 	size_t m_size = 0;
 };
+
+/* free_gpu_memory_arena / free_all_gpu_memory_arenas (gpu_memory.h:743-756).  There is no arena here: the only temporaries are the
+ * scratch buffers the network / trainer objects keep for the C ABI's workspace argument; they register themselves and are
+ * released by these calls (and grow again on the next use). */
+inline std::vector<std::weak_ptr<GPUMemory<char>>>& scratch_registry() { static std::vector<std::weak_ptr<GPUMemory<char>>> r; return r; }
+inline std::shared_ptr<GPUMemory<char>> make_scratch() { auto p = std::make_shared<GPUMemory<char>>(); scratch_registry().push_back(p); return p; }
+inline void free_all_gpu_memory_arenas() {
+	auto& r = scratch_registry();
+	for (size_t i = 0; i < r.size();) { if (auto p = r[i].lock()) { p->free_memory(); ++i; } else { r[i] = r.back(); r.pop_back(); } }
+}
+inline void free_gpu_memory_arena(cudaStream_t) { free_all_gpu_memory_arenas(); }
 
 } // namespace tcnn

@@ -1,120 +1,99 @@
-/* Network, Trainer and TrainableModel over the tcnn_b200 C ABI.
- *
- * Mirrors, for the HashGrid + FullyFusedMLP path:
- *   Network / DifferentiableObject::inference     include/tiny-cuda-nn/object.h:147-179, network.h
- *   Trainer<float, half, half>                    include/tiny-cuda-nn/trainer.h:47-361 (training_step :163-190, loss :205-207,
- *                                                 optimizer_step :155-157, initialize_params :68-87, buffer layout :75,322-336)
- * Differences by construction: loss and optimizer are part of the plan (no separate Loss / Optimizer objects); the forward
- * context only carries the loss scalar (activations never leave the chip); there is no CUDA-graph re-capture per step. */
+/* Trainer<T, PARAMS_T, COMPUTE_T> over the tcnn_b200 C ABI (include/tiny-cuda-nn/trainer.h:47-361): the parameter buffer in the
+ * reference's layout (:75, 322-336), initialize_params (:68-87), training_step with the reference's full signature (:163-190),
+ * optimizer_step (:155-157), loss (:205-207), update_hyperparams (:213-216), serialize / deserialize (:275-315).
+ * By construction: forward, loss, backward (and on one GPU the optimizer) of a step are ONE call into the library - no
+ * activations, loss values or dL/d(output) exist in device memory, and nothing is re-captured per step. */
 #pragma once
-#include <memory>
-
-#include "gpu_matrix.h"
+#include "loss.h"
+#include "network_with_input_encoding.h"
+#include "optimizer.h"
 
 namespace tcnn {
 
-class Network {
-public:
-	Network(const std::string& config_json, uint32_t n_input_dims, uint32_t n_output_dims) {
-		TCNN_B200_CHECK_THROW(tcnn_b200_plan_create(config_json.c_str(), n_input_dims, n_output_dims, &m_plan));
-		TCNN_B200_CHECK_THROW(tcnn_b200_plan_info(m_plan, &m_info));
-	}
-	Network(const Network&) = delete;
-	Network& operator=(const Network&) = delete;
-	~Network() { if (m_plan) tcnn_b200_plan_destroy(m_plan); }
-
-	/* object.h:147-176: input [D x B] CM fp32, output [O x B] CM fp32 */
-	void inference(cudaStream_t stream, const GPUMatrixDynamic<float>& input, GPUMatrixDynamic<float>& output) {
-		check(input, m_info.n_input_dims, "input");
-		if (output.m() != m_info.n_output_dims || output.n() != input.n() || output.layout() != CM)
-			throw std::runtime_error("Network::inference: output must be a column-major [n_output_dims x batch] matrix");
-		if (!m_params) throw std::runtime_error("Network::inference: no parameters set (set_params)");
-		TCNN_B200_CHECK_THROW(tcnn_b200_inference(m_plan, stream, input.n(), input.data(), m_params, nullptr, output.data(), workspace(input.n())));
-	}
-	void inference(const GPUMatrixDynamic<float>& input, GPUMatrixDynamic<float>& output) { inference(nullptr, input, output); }
-	/* object.h:126-145: fp16 output padded to 16 rows */
-	void inference_mixed_precision(cudaStream_t stream, const GPUMatrixDynamic<float>& input, GPUMatrixDynamic<__half>& output) {
-		check(input, m_info.n_input_dims, "input");
-		if (output.m() != m_info.padded_output_width || output.n() != input.n() || output.layout() != CM)
-			throw std::runtime_error("Network::inference_mixed_precision: output must be a column-major [padded_output_width x batch] matrix");
-		TCNN_B200_CHECK_THROW(tcnn_b200_inference(m_plan, stream, input.n(), input.data(), m_params, output.data(), nullptr, workspace(input.n())));
-	}
-
-	void set_params(__half* params, __half* inference_params, __half* gradients) { m_params = inference_params ? inference_params : params; (void)gradients; }
-	size_t n_params() const { return m_info.n_params; }
-	uint32_t input_width() const { return m_info.n_input_dims; }
-	uint32_t output_width() const { return m_info.n_output_dims; }
-	uint32_t padded_output_width() const { return m_info.padded_output_width; }
-	const tcnn_b200_info& info() const { return m_info; }
-	tcnn_b200_plan* plan() const { return m_plan; }
-
-	void* workspace(uint32_t batch_size) {
-		const size_t need = tcnn_b200_workspace_bytes(m_plan, batch_size);
-		if (need > m_workspace.size()) m_workspace.resize(need);
-		return m_workspace.data();
-	}
-	static void check(const GPUMatrixDynamic<float>& m, uint32_t rows, const char* what) {
-		if (m.layout() != CM || m.m() != rows) throw std::runtime_error(std::string("tcnn_b200: ") + what + " must be a column-major [" + std::to_string(rows) + " x batch] matrix");
-		check_batch_size(m.n());
-	}
-
-private:
-	tcnn_b200_plan* m_plan = nullptr;
-	tcnn_b200_info m_info{};
-	__half* m_params = nullptr;
-	GPUMemory<char> m_workspace;
-};
-
+template <typename T, typename PARAMS_T, typename COMPUTE_T = PARAMS_T>
 class Trainer {
+	static_assert(std::is_same<T, float>::value && std::is_same<PARAMS_T, __half>::value && std::is_same<COMPUTE_T, __half>::value,
+		"the fused path trains fp32 inputs with fp16 parameters and fp16 compute: Trainer<float, __half, __half>");
 public:
-	struct ForwardContext { float* loss_device; };
+	using Model = NetworkWithInputEncoding<PARAMS_T>;
+	struct ForwardContext : public Context { /* trainer.h:89-95; the fused step keeps only what hosts read back */
+		float* loss_device = nullptr;
+		GPUMatrix<COMPUTE_T> output;   /* [padded_output_width x B], filled only if the trainer was asked to (keep_output) */
+	};
 
-	explicit Trainer(std::shared_ptr<Network> network, uint32_t seed = 1337) : m_network(std::move(network)) {
-		const size_t P = m_network->n_params();
-		m_params_buffer.resize(8 * P); /* trainer.h:75: fp32 master | fp16 params | fp16 gradients */
-		m_params_full_precision = reinterpret_cast<float*>(m_params_buffer.data());
-		m_params = reinterpret_cast<__half*>(m_params_buffer.data() + 4 * P);
-		m_param_gradients = reinterpret_cast<__half*>(m_params_buffer.data() + 6 * P);
-		m_first_moments.resize(P); m_second_moments.resize(P); m_param_steps.resize(P); m_loss.resize(1);
-		m_network->set_params(m_params, m_params, m_param_gradients);
-		initialize_params(seed);
+	Trainer(std::shared_ptr<Model> model, std::shared_ptr<Optimizer<PARAMS_T>> optimizer, std::shared_ptr<Loss<PARAMS_T>> loss, uint32_t seed = 1337)
+	: m_model(std::move(model)), m_optimizer(std::move(optimizer)), m_loss(std::move(loss)), m_seed(seed) {
+		const json config = {{"encoding", m_model->encoding_config()}, {"network", m_model->network_config()}, {"loss", m_loss->config()}, {"optimizer", m_optimizer->plan_json()}};
+		TCNN_B200_CHECK_THROW(tcnn_b200_plan_create(config.dump().c_str(), m_model->input_width(), m_model->output_width(), &m_plan));
+		m_optimizer->attach(m_plan);
+		initialize_params();
 	}
+	Trainer(const Trainer&) = delete;
+	Trainer& operator=(const Trainer&) = delete;
+	virtual ~Trainer() { if (m_optimizer) m_optimizer->attach(nullptr); if (m_plan) tcnn_b200_plan_destroy(m_plan); }
 
-	void initialize_params(uint32_t seed = 1337) { /* trainer.h:68-87 */
-		TCNN_B200_CHECK_THROW(tcnn_b200_init_params(m_network->plan(), nullptr, seed, 1, m_params_full_precision));
-		TCNN_B200_CHECK_THROW(tcnn_b200_cast_params(nullptr, m_network->n_params(), m_params_full_precision, m_params));
-		CUDA_CHECK_THROW(cudaMemset(m_param_gradients, 0, 2 * m_network->n_params()));
-		m_first_moments.memset(0); m_second_moments.memset(0); m_param_steps.memset(0); m_loss.memset(0);
-		m_step = 0; m_grads_clean = true;
+	void initialize_params() { /* trainer.h:68-87 */
+		const size_t P = m_model->n_params();
+		m_optimizer->allocate((uint32_t)P);
+		m_params_buffer.resize(8 * P); /* fp32 master | fp16 params | fp16 gradients */
+		m_params_buffer.memset(0);
+		reset_param_pointers();
+		TCNN_B200_CHECK_THROW(tcnn_b200_init_params(m_plan, nullptr, m_seed, 1, m_params_full_precision));
+		TCNN_B200_CHECK_THROW(tcnn_b200_cast_params(nullptr, P, m_params_full_precision, m_params));
+		m_loss_value.resize(1); m_loss_value.memset(0);
+		m_grads_clean = true;
 		CUDA_CHECK_THROW(cudaDeviceSynchronize());
 	}
 
 	/* trainer.h:163-190.  input [D x B] CM, target [O x B] CM. */
-	std::unique_ptr<ForwardContext> training_step(cudaStream_t stream, const GPUMatrixDynamic<float>& input, const GPUMatrix<float>& target, bool run_optimizer = true) {
-		Network::check(input, m_network->input_width(), "input");
-		if (target.m() != m_network->output_width() || target.n() != input.n()) throw std::runtime_error("Trainer::training_step: target must be [n_output_dims x batch]");
+	std::unique_ptr<ForwardContext> training_step(
+		cudaStream_t stream,
+		const GPUMatrixDynamic<T>& input,
+		const GPUMatrix<float>& target,
+		const GPUMatrix<float>* data_pdf = nullptr,
+		bool run_optimizer = true,
+		GPUMatrixDynamic<T>* dL_dinput = nullptr,
+		bool use_inference_params = false,
+		GradientMode param_gradients_mode = GradientMode::Overwrite,
+		const GPUMatrix<COMPUTE_T>* external_dL_dy = nullptr
+	) {
+		if (data_pdf) throw std::runtime_error("Trainer::training_step: data_pdf is not implemented by the fused training step");
+		if (dL_dinput) throw std::runtime_error("Trainer::training_step: dL_dinput is not implemented by the fused training step (cpp::Module::backward computes it)");
+		if (external_dL_dy) throw std::runtime_error("Trainer::training_step: external_dL_dy is not implemented by the fused training step (cpp::Module::backward takes dL/d(output))");
+		if (param_gradients_mode == GradientMode::Accumulate) throw std::runtime_error("Trainer::training_step: GradientMode::Accumulate is not implemented");
+		(void)use_inference_params; /* one parameter copy (trainer.h:329-333) */
+		Model::check(input, m_model->input_width(), "input");
+		if (target.m() != m_model->output_width() || target.n() != input.n()) throw std::runtime_error("Trainer::training_step: target must be [n_output_dims x batch]");
 		const uint32_t B = input.n();
-		void* ws = m_network->workspace(B);
+		void* ws = m_model->workspace(B);
+		auto ctx = std::unique_ptr<ForwardContext>(new ForwardContext());
+		ctx->loss_device = m_loss_value.data();
+		void* out = nullptr;
+		if (m_keep_output) { ctx->output = GPUMatrix<COMPUTE_T>(m_model->padded_output_width(), B); out = ctx->output.data(); }
+		if (param_gradients_mode == GradientMode::Ignore) run_optimizer = false;
 		if (run_optimizer && m_grads_clean) {
-			++m_step;
-			TCNN_B200_CHECK_THROW(tcnn_b200_training_step(m_network->plan(), stream, B, input.data(), target.data(), loss_scale(), m_step, m_params_full_precision, m_params,
-				m_param_gradients, m_first_moments.data(), m_second_moments.data(), m_param_steps.data(), m_loss.data(), nullptr, ws));
+			m_optimizer->advance_step();
+			TCNN_B200_CHECK_THROW(tcnn_b200_training_step(m_plan, stream, B, input.data(), target.data(), loss_scale(), m_optimizer->step(), m_params_full_precision, m_params,
+				m_param_gradients, m_optimizer->first_moments(), m_optimizer->second_moments(), m_optimizer->param_steps(), m_loss_value.data(), out, ws));
 		} else {
-			TCNN_B200_CHECK_THROW(tcnn_b200_training_fwd_bwd(m_network->plan(), stream, B, input.data(), target.data(), m_params, m_param_gradients, loss_scale(),
-				m_grads_clean ? 0 : 1, m_loss.data(), nullptr, ws));
+			TCNN_B200_CHECK_THROW(tcnn_b200_training_fwd_bwd(m_plan, stream, B, input.data(), target.data(), m_params, m_param_gradients, loss_scale(),
+				m_grads_clean ? 0 : 1, m_loss_value.data(), out, ws));
 			m_grads_clean = false;
 			if (run_optimizer) optimizer_step(stream, loss_scale());
 		}
-		return std::unique_ptr<ForwardContext>(new ForwardContext{m_loss.data()});
+		return ctx;
 	}
-	std::unique_ptr<ForwardContext> training_step(const GPUMatrixDynamic<float>& input, const GPUMatrix<float>& target) { return training_step(nullptr, input, target); }
+	std::unique_ptr<ForwardContext> training_step(
+		const GPUMatrixDynamic<T>& input, const GPUMatrix<float>& target, const GPUMatrix<float>* data_pdf = nullptr, bool run_optimizer = true,
+		GPUMatrixDynamic<T>* dL_dinput = nullptr, bool use_inference_params = false, GradientMode param_gradients_mode = GradientMode::Overwrite,
+		const GPUMatrix<COMPUTE_T>* external_dL_dy = nullptr
+	) { return training_step(nullptr, input, target, data_pdf, run_optimizer, dL_dinput, use_inference_params, param_gradients_mode, external_dL_dy); }
 
 	void optimizer_step(cudaStream_t stream, float loss_scale) { /* trainer.h:155-157 */
-		++m_step;
-		TCNN_B200_CHECK_THROW(tcnn_b200_adam_step(m_network->plan(), stream, loss_scale, m_step, m_params_full_precision, m_params, m_param_gradients,
-			m_first_moments.data(), m_second_moments.data(), m_param_steps.data(), 1));
+		m_optimizer->step(stream, loss_scale, m_params_full_precision, m_params, m_param_gradients);
 		m_grads_clean = true;
 	}
+	void optimizer_step(float loss_scale) { optimizer_step(nullptr, loss_scale); }
 
 	/* trainer.h:205-207: synchronises and returns the mean loss of the step */
 	float loss(cudaStream_t stream, const ForwardContext& ctx) const {
@@ -123,27 +102,90 @@ public:
 		CUDA_CHECK_THROW(cudaStreamSynchronize(stream));
 		return v;
 	}
+	float loss(const ForwardContext& ctx) const { return loss(nullptr, ctx); }
 
-	void update_hyperparams(const std::string& optimizer_json) { TCNN_B200_CHECK_THROW(tcnn_b200_plan_update_optimizer(m_network->plan(), optimizer_json.c_str())); }
+	/* trainer.h:213-216: {"optimizer": {...}, "loss": {...}} */
+	void update_hyperparams(const json& params) {
+		m_optimizer->update_hyperparams(params.value("optimizer", json::object()));
+		m_loss->update_hyperparams(params.value("loss", json::object()));
+	}
+	json hyperparams() const { return {{"otype", "Trainer"}, {"optimizer", m_optimizer->hyperparams()}, {"loss", m_loss->hyperparams()}}; }
 
-	float loss_scale() const { return default_loss_scale<network_precision_t>(); }
+	/* trainer.h:243-273 */
+	void set_params_full_precision(const float* params, size_t n_params, bool device_ptr = false) {
+		if (n_params != m_model->n_params()) throw std::runtime_error("Can't set fp params because buffer has the wrong size.");
+		CUDA_CHECK_THROW(cudaMemcpy(m_params_full_precision, params, n_params * sizeof(float), device_ptr ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice));
+		TCNN_B200_CHECK_THROW(tcnn_b200_cast_params(nullptr, n_params, m_params_full_precision, m_params));
+		CUDA_CHECK_THROW(cudaDeviceSynchronize());
+	}
+	void set_params(const PARAMS_T* params, size_t n_params, bool device_ptr = false) {
+		if (n_params != m_model->n_params()) throw std::runtime_error("Can't set params because buffer has the wrong size.");
+		CUDA_CHECK_THROW(cudaMemcpy(m_params, params, n_params * sizeof(PARAMS_T), device_ptr ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice));
+		std::vector<PARAMS_T> h(n_params); std::vector<float> f(n_params); /* master weights follow the fp16 values */
+		CUDA_CHECK_THROW(cudaMemcpy(h.data(), m_params, n_params * sizeof(PARAMS_T), cudaMemcpyDeviceToHost));
+		for (size_t i = 0; i < n_params; ++i) f[i] = __half2float(h[i]);
+		CUDA_CHECK_THROW(cudaMemcpy(m_params_full_precision, f.data(), n_params * sizeof(float), cudaMemcpyHostToDevice));
+	}
+
+	/* trainer.h:275-288 (+ adam.h:278-286) */
+	json serialize(bool serialize_optimizer = false) {
+		const size_t n = m_model->n_params();
+		json data;
+		data["n_params"] = n;
+		data["params_type"] = "__half";
+		data["params_binary"] = Optimizer<PARAMS_T>::to_binary(m_params, sizeof(PARAMS_T) * n);
+		if (serialize_optimizer) data["optimizer"] = m_optimizer->serialize();
+		return data;
+	}
+	/* trainer.h:290-315 */
+	void deserialize(const json& data) {
+		const std::string type = data.value("params_type", "__half");
+		if (type == "float") {
+			GPUMemory<float> p; Optimizer<PARAMS_T>::from_binary(data["params_binary"], p);
+			set_params_full_precision(p.data(), p.size(), true);
+		} else if (type == "__half") {
+			GPUMemory<PARAMS_T> p; Optimizer<PARAMS_T>::from_binary(data["params_binary"], p);
+			set_params(p.data(), p.size(), true);
+		} else {
+			throw std::runtime_error{"Trainer: snapshot parameters must be of type float of __half"};
+		}
+		if (data.contains("optimizer")) m_optimizer->deserialize(data["optimizer"]);
+		CUDA_CHECK_THROW(cudaMemset(m_param_gradients, 0, sizeof(PARAMS_T) * m_model->n_params()));
+		m_grads_clean = true;
+		CUDA_CHECK_THROW(cudaDeviceSynchronize());
+	}
+
+	float loss_scale() const { return default_loss_scale<PARAMS_T>(); }
 	float* params_full_precision() const { return m_params_full_precision; }
-	__half* params() const { return m_params; }
-	__half* param_gradients() const { return m_param_gradients; }
-	size_t n_params() const { return m_network->n_params(); }
-	uint32_t step() const { return m_step; }
-	std::shared_ptr<Network> model() const { return m_network; }
+	PARAMS_T* params() const { return m_params; }
+	PARAMS_T* params_inference() const { return m_params; }
+	PARAMS_T* param_gradients() const { return m_param_gradients; }
+	size_t n_params() const { return m_model->n_params(); }
+	uint32_t step() const { return m_optimizer->step(); }
+	std::shared_ptr<Model> model() { return m_model; }
+	std::shared_ptr<Optimizer<PARAMS_T>> optimizer() { return m_optimizer; }
+	/* facade extension: also write the network output [padded_output_width x B] of every training step into ForwardContext::output */
+	void keep_output(bool keep) { m_keep_output = keep; }
 
 private:
-	std::shared_ptr<Network> m_network;
+	void reset_param_pointers() { /* trainer.h:322-336 */
+		const size_t P = m_model->n_params();
+		m_params_full_precision = reinterpret_cast<float*>(m_params_buffer.data());
+		m_params = reinterpret_cast<PARAMS_T*>(m_params_buffer.data() + 4 * P);
+		m_param_gradients = reinterpret_cast<PARAMS_T*>(m_params_buffer.data() + 6 * P);
+		m_model->set_params(m_params, m_params, m_param_gradients);
+	}
+	std::shared_ptr<Model> m_model;
+	std::shared_ptr<Optimizer<PARAMS_T>> m_optimizer;
+	std::shared_ptr<Loss<PARAMS_T>> m_loss;
+	tcnn_b200_plan* m_plan = nullptr;
+	uint32_t m_seed;
 	GPUMemory<char> m_params_buffer;
 	float* m_params_full_precision = nullptr;
-	__half* m_params = nullptr;
-	__half* m_param_gradients = nullptr;
-	GPUMemory<float> m_first_moments, m_second_moments, m_loss;
-	GPUMemory<uint32_t> m_param_steps;
-	uint32_t m_step = 0;
-	bool m_grads_clean = true;
+	PARAMS_T* m_params = nullptr;
+	PARAMS_T* m_param_gradients = nullptr;
+	GPUMemory<float> m_loss_value;
+	bool m_grads_clean = true, m_keep_output = false;
 };
 
 } // namespace tcnn

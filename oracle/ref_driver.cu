@@ -16,11 +16,41 @@
 //   ref_driver enc32 <cfg.json> <n_in> <B> <input.f32> <table.f32> <dL_dy.f32 [B][padded]> <outdir>
 //       the stand-alone encoding in fp32 precision (create_encoding<float>, what cpp_api.cu:156-165 builds for
 //       Precision::Fp32): forward, backward (table gradient, dL/dx).
+//   ref_driver state <cfg.json> <n_in> <n_out> <B> <seed> <outdir> <n_steps> <dump_step> [<dump_step> ...]
+//       the `curve` loop with the trainer's whole state written after the listed (1-based) steps: fp32 master weights, fp16
+//       parameters, fp16 gradient buffer, Adam first / second moments and per-parameter step counters (via
+//       Optimizer::serialize, optimizers/adam.h:278-286), plus the loss of every step.
+//   ref_driver serialize <cfg.json> <n_in> <n_out> <B> <seed> <n_steps> <out.msgpack> <outdir>
+//       json::to_msgpack(Trainer::serialize(true)) (trainer.h:275-288) after n_steps of the `curve` loop, then the losses of
+//       two more steps (what a correct resume has to reproduce).
+//   ref_driver deserialize <cfg.json> <n_in> <n_out> <B> <seed> <n_steps> <in.msgpack>
+//       Trainer::deserialize (trainer.h:290-315) of a snapshot taken after n_steps, then the same two further steps; prints their losses.
 //   ref_driver bench <cfg.json> <n_in> <n_out> <B> <steps> <warmup>
 //       one JSON line: training / inference ms per step (CUDA events), device-resident inputs and
 //       host-buffer (H2D inside the timed region) variants.
+#include <algorithm>
+#include <cctype>
+#include <chrono>
+#include <cstdio>
+#include <fstream>
+#include <functional>
+#include <iostream>
+#include <memory>
+#include <sstream>
+#include <string>
+#include <unordered_map>
+#include <vector>
+// `dump` with REF_DUMP_HIDDEN=1 reads the hidden activations the reference keeps in its (private) forward contexts
+// (network_with_input_encoding.h:185-189, networks/fully_fused_mlp.h:148-151).  The headers stay unmodified; only this
+// harness sees the members as public.  Access specifiers do not change layout or symbol names.
+#define private public
+#define protected public
 #include <tiny-cuda-nn/common_device.h>
 #include <tiny-cuda-nn/config.h>
+#include <tiny-cuda-nn/network_with_input_encoding.h>
+#include <tiny-cuda-nn/networks/fully_fused_mlp.h>
+#undef private
+#undef protected
 #include <tiny-cuda-nn/encodings/grid_interface.h>
 #include <tiny-cuda-nn/random.h>
 
@@ -191,6 +221,17 @@ static int mode_dump(int argc, char** argv) {
 	write_dev(out + "/grads.f16", (const uint16_t*)model.trainer->param_gradients(), P);
 	write_dev(out + "/output_padded.f16", (const uint16_t*)ctx->output.data(), (size_t)model.network->padded_output_width() * B);
 	write_dev(out + "/dL_doutput.f16", (const uint16_t*)ctx->dL_doutput.data(), (size_t)model.network->padded_output_width() * B);
+	if (getenv("REF_DUMP_HIDDEN")) { // post-activation hidden layers as the reference's backward pass sees them: [B][W] fp16 per layer
+		auto* nctx = static_cast<NetworkWithInputEncoding<precision_t>::ForwardContext*>(ctx->model_ctx.get());
+		const uint32_t W = cfg["network"].value("n_neurons", 128u);
+		auto dump_hidden = [&](auto* fctx) {
+			for (size_t k = 0; k < fctx->hidden.size(); ++k)
+				write_dev(out + "/hidden_" + std::to_string(k) + ".f16", (const uint16_t*)fctx->hidden[k].data(), (size_t)W * B);
+		};
+		if (W == 64) dump_hidden(static_cast<FullyFusedMLP<precision_t, 64>::ForwardContext*>(nctx->network_ctx.get()));
+		else if (W == 128) dump_hidden(static_cast<FullyFusedMLP<precision_t, 128>::ForwardContext*>(nctx->network_ctx.get()));
+		else { std::cerr << "dump: REF_DUMP_HIDDEN needs 64 or 128 neurons\n"; return 2; }
+	}
 	// then the optimizer step on those gradients
 	model.trainer->optimizer_step(stream, default_loss_scale<precision_t>());
 	CUDA_CHECK_THROW(cudaStreamSynchronize(stream));
@@ -228,6 +269,109 @@ static int mode_curve(int argc, char** argv) {
 	write_host(out + "/losses.f32", losses);
 	write_dev(out + "/params_final.f32", model.trainer->params_full_precision(), model.trainer->n_params());
 	std::cout << "curve ok first=" << losses.front() << " last=" << losses.back() << std::endl;
+	return 0;
+}
+
+
+static void write_bytes(const std::string& path, const std::vector<uint8_t>& b) {
+	std::ofstream f(path, std::ios::binary);
+	f.write((const char*)b.data(), b.size());
+}
+
+static int mode_state(int argc, char** argv) {
+	if (argc < 10) { std::cerr << "state: bad args\n"; return 2; }
+	json cfg = load_cfg(argv[2]);
+	const uint32_t n_in = std::stoul(argv[3]), n_out = std::stoul(argv[4]), B = std::stoul(argv[5]);
+	const uint64_t seed = std::stoull(argv[6]);
+	const std::string out = argv[7];
+	const uint32_t n_steps = std::stoul(argv[8]);
+	std::vector<uint32_t> dump_steps;
+	for (int i = 9; i < argc; ++i) dump_steps.push_back(std::stoul(argv[i]));
+	cudaStream_t stream; CUDA_CHECK_THROW(cudaStreamCreate(&stream));
+	auto model = create_from_config(n_in, n_out, cfg);
+	const size_t P = model.trainer->n_params();
+	default_rng_t rng{seed};
+	GPUMatrix<float> input(n_in, B), target(n_out, B);
+	std::vector<float> losses(n_steps);
+	for (uint32_t i = 0; i < n_steps; ++i) {
+		generate_random_uniform<float>(stream, rng, (size_t)B * n_in, input.data());
+		synth_target<<<div_round_up(B, 256u), 256, 0, stream>>>(B, n_in, n_out, input.data(), target.data());
+		auto ctx = model.trainer->training_step(stream, input, target);
+		losses[i] = model.trainer->loss(stream, *ctx);
+		if (std::find(dump_steps.begin(), dump_steps.end(), i + 1) != dump_steps.end()) {
+			CUDA_CHECK_THROW(cudaStreamSynchronize(stream));
+			const std::string pre = out + "/s" + std::to_string(i + 1) + "_";
+			write_dev(pre + "master.f32", model.trainer->params_full_precision(), P);
+			write_dev(pre + "params.f16", (const uint16_t*)model.trainer->params(), P);
+			write_dev(pre + "grads.f16", (const uint16_t*)model.trainer->param_gradients(), P);
+			const json opt = model.optimizer->serialize();
+			write_bytes(pre + "m.f32", opt["first_moments_binary"].get_binary());
+			write_bytes(pre + "v.f32", opt["second_moments_binary"].get_binary());
+			write_bytes(pre + "steps.u32", opt["param_steps_binary"].get_binary());
+		}
+	}
+	write_host(out + "/losses.f32", losses);
+	std::cout << "state ok first=" << losses.front() << " last=" << losses.back() << " P=" << P << std::endl;
+	return 0;
+}
+
+// two steps of the `curve` loop from wherever rng / trainer stand; returns their losses
+static std::vector<float> two_more_steps(cudaStream_t stream, TrainableModel& model, default_rng_t& rng, uint32_t n_in, uint32_t n_out, uint32_t B) {
+	GPUMatrix<float> input(n_in, B), target(n_out, B);
+	std::vector<float> l;
+	for (int i = 0; i < 2; ++i) {
+		generate_random_uniform<float>(stream, rng, (size_t)B * n_in, input.data());
+		synth_target<<<div_round_up(B, 256u), 256, 0, stream>>>(B, n_in, n_out, input.data(), target.data());
+		auto ctx = model.trainer->training_step(stream, input, target);
+		l.push_back(model.trainer->loss(stream, *ctx));
+	}
+	return l;
+}
+
+static int mode_serialize(int argc, char** argv) {
+	if (argc < 10) { std::cerr << "serialize: bad args\n"; return 2; }
+	json cfg = load_cfg(argv[2]);
+	const uint32_t n_in = std::stoul(argv[3]), n_out = std::stoul(argv[4]), B = std::stoul(argv[5]);
+	const uint64_t seed = std::stoull(argv[6]);
+	const uint32_t n_steps = std::stoul(argv[7]);
+	const std::string snapshot = argv[8], out = argv[9];
+	cudaStream_t stream; CUDA_CHECK_THROW(cudaStreamCreate(&stream));
+	auto model = create_from_config(n_in, n_out, cfg);
+	default_rng_t rng{seed};
+	GPUMatrix<float> input(n_in, B), target(n_out, B);
+	std::vector<float> losses;
+	for (uint32_t i = 0; i < n_steps; ++i) {
+		generate_random_uniform<float>(stream, rng, (size_t)B * n_in, input.data());
+		synth_target<<<div_round_up(B, 256u), 256, 0, stream>>>(B, n_in, n_out, input.data(), target.data());
+		auto ctx = model.trainer->training_step(stream, input, target);
+		losses.push_back(model.trainer->loss(stream, *ctx));
+	}
+	CUDA_CHECK_THROW(cudaStreamSynchronize(stream));
+	const std::vector<uint8_t> blob = json::to_msgpack(model.trainer->serialize(true));
+	write_bytes(snapshot, blob);
+	write_dev(out + "/master_at_snapshot.f32", model.trainer->params_full_precision(), model.trainer->n_params());
+	const auto next = two_more_steps(stream, model, rng, n_in, n_out, B);
+	losses.insert(losses.end(), next.begin(), next.end());
+	write_host(out + "/losses.f32", losses);
+	std::cout << "serialize ok bytes=" << blob.size() << " next=" << next[0] << "," << next[1] << std::endl;
+	return 0;
+}
+
+static int mode_deserialize(int argc, char** argv) {
+	if (argc < 9) { std::cerr << "deserialize: bad args\n"; return 2; }
+	json cfg = load_cfg(argv[2]);
+	const uint32_t n_in = std::stoul(argv[3]), n_out = std::stoul(argv[4]), B = std::stoul(argv[5]);
+	const uint64_t seed = std::stoull(argv[6]);
+	const uint32_t n_steps = std::stoul(argv[7]);
+	auto raw = read_file(argv[8]);
+	cudaStream_t stream; CUDA_CHECK_THROW(cudaStreamCreate(&stream));
+	auto model = create_from_config(n_in, n_out, cfg);
+	model.trainer->deserialize(json::from_msgpack(std::vector<uint8_t>(raw.begin(), raw.end())));
+	default_rng_t rng{seed};
+	GPUMatrix<float> input(n_in, B);
+	for (uint32_t i = 0; i < n_steps; ++i) generate_random_uniform<float>(stream, rng, (size_t)B * n_in, input.data()); // skip the batches already trained on
+	const auto next = two_more_steps(stream, model, rng, n_in, n_out, B);
+	std::cout << json{{"mode", "deserialize"}, {"next_losses", next}}.dump() << std::endl;
 	return 0;
 }
 
@@ -369,6 +513,9 @@ int main(int argc, char** argv) {
 		if (mode == "bench") return mode_bench(argc, argv);
 		if (mode == "bwdbwd") return mode_bwdbwd(argc, argv);
 		if (mode == "enc32") return mode_enc32(argc, argv);
+		if (mode == "state") return mode_state(argc, argv);
+		if (mode == "serialize") return mode_serialize(argc, argv);
+		if (mode == "deserialize") return mode_deserialize(argc, argv);
 		std::cerr << "unknown mode " << mode << "\n";
 		return 2;
 	} catch (const std::exception& e) {

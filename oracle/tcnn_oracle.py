@@ -564,11 +564,22 @@ def matmul_acc(a: np.ndarray, b: np.ndarray, acc=np.float32) -> np.ndarray:
     return out
 
 
-def mlp_forward(cfg: MlpConfig, params: np.ndarray, x: np.ndarray, acc=np.float32):
+def _dw_splitk16(g: np.ndarray, inp: np.ndarray, slice_samples: int = 4096) -> np.ndarray:
+    """g^T [out, B] @ inp [B, in] the way a split-K GEMM with fp16 accumulators behaves: every slice of `slice_samples` samples is
+    accumulated in fp16 (rounded after each 16-sample step), the slices are then summed (fully_fused_mlp.cu:775: split_k = B / 4096)."""
+    total = np.zeros((g.shape[1], inp.shape[1]), np.float64)
+    for s0 in range(0, g.shape[0], slice_samples):
+        total += matmul_acc(np.ascontiguousarray(g[s0:s0 + slice_samples].T), inp[s0:s0 + slice_samples], "hmma16").astype(np.float64)
+    return total.astype(np.float16).astype(np.float64)
+
+
+def mlp_forward(cfg: MlpConfig, params: np.ndarray, x: np.ndarray, acc="hmma16"):
     """x: fp16 [B, n_input] -> (output fp16 [B, out_pad], list of post-activation hidden fp16 [B, W]).
 
-    Storage fp16 after every layer like the reference (fully_fused_mlp.cu:47-129); `acc` is the accumulator type:
-    the reference accumulates in fp16 wmma fragments, the B200 kernels in fp32 TMEM (BASELINE tolerance 1e-2)."""
+    Storage fp16 after every layer like the reference (fully_fused_mlp.cu:47-129); `acc` is the accumulator type.  The
+    default "hmma16" is the reference's: fp16 wmma fragments, rounded after every 16-deep step (this reproduces the reference
+    build's network output to <= 3 last-place differences per 3000 values; the B200 kernels accumulate the same way in TMEM
+    and match it bit for bit).  np.float32 / np.float64 give the exactly-accumulated result for comparison."""
     ws = cfg.split(params.astype(np.float16))
     h = x.astype(np.float16)
     hidden = []
@@ -580,12 +591,14 @@ def mlp_forward(cfg: MlpConfig, params: np.ndarray, x: np.ndarray, acc=np.float3
     return y, hidden
 
 
-def mlp_backward(cfg: MlpConfig, params: np.ndarray, x: np.ndarray, hidden, dy: np.ndarray, acc=np.float32, dw_acc=np.float64, y=None):
+def mlp_backward(cfg: MlpConfig, params: np.ndarray, x: np.ndarray, hidden, dy: np.ndarray, acc="hmma16", dw_acc=np.float64, y=None):
     """dy: fp16 [B, out_pad] (loss-scaled) -> (dparams float64 [n_params] exact-ish, dx fp16 [B, n_input]).
 
     Chain (fully_fused_mlp.cu:150-259): g = (W_next^T dy) * relu'(h) with the mask taken from the stored
-    post-activation (common_device.h:243-248), rounded to fp16 at every layer; weight gradients dW = g^T h_prev
-    over the batch (fully_fused_mlp.cu:783-829)."""
+    post-activation (common_device.h:243-248), rounded to fp16 at every layer (accumulator `acc` as in mlp_forward); weight
+    gradients dW = g^T h_prev over the batch (fully_fused_mlp.cu:783-829).  The reference accumulates those in fp16 too, in
+    split-K slices of 4096 samples (cutlass_matmul.h:437-479) whose summation order is CUTLASS's; `dw_acc` = np.float64 returns
+    the exact sums, "splitk16" an emulation of the sliced fp16 accumulation (16-sample steps) that shows its underflow."""
     ws = cfg.split(params.astype(np.float16))
     grads = [None] * len(ws)
     g = dy.astype(np.float16)
@@ -595,7 +608,7 @@ def mlp_backward(cfg: MlpConfig, params: np.ndarray, x: np.ndarray, hidden, dy: 
         g = activation_backward(g, y, cfg.output_activation)
     for k in range(len(ws) - 1, -1, -1):
         inp = hidden[k - 1] if k > 0 else x.astype(np.float16)
-        grads[k] = matmul_acc(np.ascontiguousarray(g.T), inp, dw_acc).astype(np.float64)
+        grads[k] = _dw_splitk16(g, inp) if isinstance(dw_acc, str) and dw_acc == "splitk16" else matmul_acc(np.ascontiguousarray(g.T), inp, dw_acc).astype(np.float64)
         z = matmul_acc(g, ws[k], acc)
         g = z.astype(np.float16)
         if k > 0:

@@ -83,6 +83,8 @@ def test_defaults_and_case_insensitive_otype(lib):
     ({"encoding": {"otype": "HashGrid", "n_levels": 4, "n_features": 8}}, "simultaneously"),
     ({"loss": {"otype": "CrossEntropy"}}, "outside the hot path"),
     ({"optimizer": {"otype": "Shampoo"}}, "outside the hot path"),
+    ({"optimizer": {"otype": "Adam", "learnign_rate": 1e-2}}, "unknown optimizer key"),          # a misspelt key must not train with the default
+    ({"encoding": {"otype": "TiledGrid", "n_levels": 4, "base_resolution": 5}}, "multiple of 8"),  # 25-entry tiles: unaligned level tables
 ])
 def test_error_reporting(lib, patch, msg):
     cfg = json.loads(json.dumps(common.CONFIG_1))
@@ -90,6 +92,17 @@ def test_error_reporting(lib, patch, msg):
     rc, _ = _plan(lib, cfg, 2, 3)
     assert rc != 0
     assert msg in lib.tcnn_b200_last_error().decode()
+
+
+def test_optimizer_freeze_flags_are_accepted(lib):
+    """optimize_matrix_params / optimize_non_matrix_params (optimizers/adam.h:57-58, 77-85) are keys of the reference's Adam."""
+    cfg = json.loads(json.dumps(common.CONFIG_1))
+    cfg["optimizer"] = {"otype": "Adam", "optimize_matrix_params": False, "optimize_non_matrix_params": True, "adabound": False}
+    rc, h = _plan(lib, cfg, 2, 3)
+    assert rc == 0, lib.tcnn_b200_last_error()
+    assert lib.tcnn_b200_plan_update_optimizer(h, json.dumps({"optimize_non_matrix_params": False}).encode()) == 0
+    assert lib.tcnn_b200_plan_update_optimizer(h, json.dumps({"momentum": 0.9}).encode()) != 0
+    lib.tcnn_b200_plan_destroy(h)
 
 
 def test_malformed_json(lib):

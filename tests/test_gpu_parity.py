@@ -2,9 +2,9 @@
 inputs, and against the golden dumps of the reference's own CUDA build (tests/golden/*.npz).
 
 Tolerances (BASELINE.json north_star): grid/hash indices bit-exact; encoded features <= 1e-3 relative; MLP outputs
-and parameter gradients <= 1e-2 relative L2 (the reference accumulates in fp16, we in fp32).  Grid-table gradients are
-compared at 8e-2 against the reference because a handful of ReLU-mask flips between fp16- and fp32-accumulated
-activations dominate their difference (DESIGN.md "Parity"); against the oracle (same accumulation) they match to 2e-3."""
+and parameter gradients <= 1e-2 relative L2; loss after 1000 steps within 2 %.  The kernels accumulate in fp16 in TMEM like the
+reference's wmma fragments, so the network output is compared BIT FOR BIT with the reference dump and every gradient tensor
+(the grid tables included) at the 1e-2 bar (DESIGN.md "Parity")."""
 import json
 import os
 
@@ -192,26 +192,30 @@ def test_training_step_and_adam_vs_reference_golden(ctx):
     x_np, t_np = common.synth_inputs(B, ctx.n_in, ctx.n_out, seed=1)
     x, t = torch.from_numpy(x_np).to(ctx.dev), torch.from_numpy(t_np).to(ctx.dev)
     pred = tr.inference(x).cpu().numpy()
-    assert common.rel_l2(pred, z["output"]) < 1e-2
+    assert np.array_equal(pred, z["output"])  # same fp16 values cast to fp32
     out = torch.empty(B, 16, dtype=torch.half, device=ctx.dev)
     tr.training_step(x, t, run_optimizer=False, output=out)
-    assert abs(tr.loss() - float(z["loss"])) <= 2e-3 * abs(float(z["loss"]))
-    assert common.rel_l2(out.cpu().numpy(), z["output_padded"]) < 1e-2
+    assert abs(tr.loss() - float(z["loss"])) <= 1e-5 * abs(float(z["loss"]))
+    # fp16 accumulation in TMEM = the reference's wmma arithmetic: all 16 (padded) output columns bit for bit (+0 == -0)
+    assert np.array_equal(out.cpu().numpy().astype(np.float32), z["output_padded"].astype(np.float32))
     n_mlp = int(z["n_params_mlp"])
     grads = tr.param_gradients.cpu().numpy()
     assert common.rel_l2(grads[:n_mlp], z["grads_mlp"]) < 1e-2
     nz = z["grads_grid_nz_idx"].astype(np.int64)
     gg = grads[n_mlp:]
-    assert common.rel_l2(gg[nz], z["grads_grid_nz_val"]) < 8e-2
+    assert common.rel_l2(gg[nz], z["grads_grid_nz_val"]) < 1e-2  # north-star bar (6e-4 .. 1.1e-3 measured): no ReLU mask differs
     ours_nz = np.flatnonzero(gg.view(np.uint16) & 0x7FFF)
     assert len(np.setxor1d(ours_nz, nz)) <= 2e-3 * len(nz) + 4  # same set of touched entries (up to fp16 underflow)
     before = tr.params_full_precision.cpu().numpy()
     tr.optimizer_step()
     after = tr.params_full_precision.cpu().numpy()
-    # first Adam step moves every touched parameter by ~lr * sign(g): compare the update vectors
-    assert common.rel_l2(after[:n_mlp] - before[:n_mlp], z["params_after_mlp"] - z["params_init_mlp"]) < 0.15  # first step ~ lr*sign(g)
+    # The first Adam step moves a parameter by lr * g / (|g| + eps): +-lr unless |g| is within a few eps of 0.  The grid tables follow the
+    # reference to 1e-2; the MLP weights of this freshly initialised network have gradients in the fp16 subnormal range where the
+    # reference's split-K GEMM underflows in its own summation order (test_adam_state_trajectory_vs_reference follows them over 100 steps)
+    assert common.rel_l2(after[:n_mlp] - before[:n_mlp], z["params_after_mlp"] - z["params_init_mlp"]) < 0.15
     mi = z["params_after_moved_idx"].astype(np.int64)
-    assert common.rel_l2(after[mi] - before[mi], z["params_after_moved_val"] - before[mi]) < 0.2  # first step ~ lr*sign(g): tiny-gradient sign flips
+    gi = mi[mi >= n_mlp]
+    assert common.rel_l2(after[gi] - before[gi], z["params_after_moved_val"][mi >= n_mlp] - before[gi]) < 1e-2
     moved = np.count_nonzero(after != before)
     assert abs(moved - int(z["n_moved"])) <= 2e-3 * int(z["n_moved"]) + 4
 
@@ -469,15 +473,15 @@ def test_loss_curve_vs_reference(dev, name):
     assert np.array_equal(x_np[-len(g["x_last"]):], g["x_last"])
     ours = losses.cpu().numpy().astype(np.float64)
     assert abs(ours[0] - ref[0]) <= 1e-3 * ref[0], (ours[0], ref[0])          # same parameters, same batch
+    wide = name == "curve_nerf_3d_T19"  # the reference's own run-to-run spread on this config is 3.5 % (atomics order), on cfg1 0.1 %
     for lo, hi in ((0, 10), (10, 50), (50, 100), (100, 200), (200, 500), (500, 950)):
         a, b = ours[lo:hi].mean(), ref[lo:hi].mean()
-        assert abs(a - b) <= 0.10 * b, f"steps {lo}-{hi}: {a} vs reference {b}"    # trajectory stays on the reference's curve
+        assert abs(a - b) <= (0.10 if wide else 0.03) * b, f"steps {lo}-{hi}: {a} vs reference {b}"    # trajectory stays on the reference's curve
     a, b = ours[-50:].mean(), ref[-50:].mean()
     print(f"{name}: final loss (mean of last 50 steps) {a:.4e}, reference {b:.4e}, ratio {a / b:.4f}")
-    # north_star asks for 2 %.  Measured (tests/dev/curve_spread.py, 4 runs each): cfg1 ours/reference = 1.042 +- 0.002 with a
-    # reference run-to-run spread of 0.1 % (systematic); nerf 1.00 +- 0.03 with a reference spread of
-    # 3.5 %.  The bar here is what is reproducibly met; the 2 % figure is reported, not asserted.
-    assert abs(a - b) <= 0.06 * b, f"loss after {steps} steps {a} vs reference {b}"
+    # north_star: within 2 %.  Measured: cfg1 ours / reference = 1.000 .. 1.003 (it was 1.042 while the kernels accumulated in fp32: the
+    # reference's fp16-accumulated weight gradients make the difference); nerf 1.00 +- 0.03 = the reference's own spread.
+    assert abs(a - b) <= (0.06 if wide else 0.02) * b, f"loss after {steps} steps {a} vs reference {b}"
 
 
 def test_cpp_facade_host_trains(dev):
@@ -556,3 +560,94 @@ def test_full_size_properties(dev):
     grads2 = torch.zeros_like(grads)
     check(lib.tcnn_b200_encode_backward(native.handle, S(), B, ptr(x), ptr((dy.float() * 2).half()), ptr(grads2), 1, ptr(ws)))
     assert abs(grads2.float().sum().item() - 2 * grads.float().sum().item()) < 1e-3 * grads.float().abs().sum().item()
+
+
+def test_adam_freeze_flags(dev):
+    """optimize_matrix_params / optimize_non_matrix_params = false (optimizers/adam.h:77-85): that parameter class and its Adam
+    state stay untouched while the other trains."""
+    import copy
+    import tinycudann as tcnn
+    x_np, t_np = common.synth_inputs(2048, 2, 3, seed=4)
+    x, t = torch.from_numpy(x_np).to(dev), torch.from_numpy(t_np).to(dev)
+    for key, frozen_is_mlp in (("optimize_matrix_params", True), ("optimize_non_matrix_params", False)):
+        cfg = copy.deepcopy(common.CONFIG_SHIPPED)
+        cfg["optimizer"][key] = False
+        tr = tcnn.create_from_config(2, 3, cfg, seed=1337, device=dev).trainer
+        n_mlp = int(tr.info.n_params_mlp)
+        before = tr.params_full_precision.clone()
+        for _ in range(3):
+            tr.training_step(x, t)
+        after = tr.params_full_precision
+        frozen = slice(0, n_mlp) if frozen_is_mlp else slice(n_mlp, None)
+        moving = slice(n_mlp, None) if frozen_is_mlp else slice(0, n_mlp)
+        assert torch.equal(after[frozen], before[frozen]) and not tr.param_steps[frozen].any().item()
+        assert not torch.equal(after[moving], before[moving]) and tr.param_steps[moving].any().item()
+
+
+def test_workspace_is_grow_only_and_released(dev):
+    """One scratch buffer per module and stream, re-used across batch sizes (the reference's per-stream arena,
+    gpu_memory.h:699-720), dropped by tcnn.free_temporary_memory()."""
+    import tinycudann as tcnn
+    native = tcnn.NativeModule(2, 3, common.CONFIG_SHIPPED)
+    big = native.workspace(4096, dev)
+    small = native.workspace(1024, dev)
+    assert small.data_ptr() == big.data_ptr() and len(native._ws) == 1
+    bigger = native.workspace(8192, dev)
+    assert bigger.numel() > big.numel() and len(native._ws) == 1
+    tcnn.free_temporary_memory()
+    assert len(native._ws) == 0
+
+
+def test_adam_state_trajectory_vs_reference(dev):
+    """Trainer state along the first 100 steps of the loss-curve run against dumps of the reference's own state (`ref_driver state`:
+    fp32 master weights, Adam first / second moments, per-parameter step counters, gradient buffer; every MLP weight and every 997th
+    grid parameter, tests/golden/state_cfg1_2d_T19.npz).  Same initial parameters, same pcg32 batches.  Pins the zero-gradient skip
+    (step counters, number of non-zero gradient entries per level), the moments and the parameter trajectory - not only the sign of
+    one step.  Bars are 2-3 x what two runs of different atomics order measure (tests/dev/parity_probe.py state)."""
+    import tinycudann as tcnn
+    g = np.load(os.path.join(GOLDEN, "state_cfg1_2d_T19.npz"))
+    cfg = json.loads(str(g["config"]))
+    B, n_in, n_out, seed, n_mlp = (int(g[k]) for k in ("B", "n_in", "n_out", "seed", "n_params_mlp"))
+    idx = g["index"].astype(np.int64)
+    is_mlp = idx < n_mlp
+    tr = tcnn.create_from_config(n_in, n_out, cfg, seed=1337, device=dev).trainer
+    info = tr.info
+    init = tr.params_full_precision.cpu().numpy()[idx]
+    level_of = np.searchsorted(np.array(info.level_offset[1: info.n_levels + 1], dtype=np.int64) * info.n_features_per_level + n_mlp, idx, side="right")
+    coarse = ~is_mlp & (level_of <= 4)
+    fine = ~is_mlp & (level_of > 4)
+    #            MLP weights   levels 0-4    levels 5-15      (relative L2 of the displacement from the initial parameters)
+    bars = {1: (0.60, 0.01, 0.01), 2: (0.40, 0.06, 0.12), 3: (0.30, 0.06, 0.20), 10: (0.12, 0.06, 0.30), 30: (0.10, 0.04, 0.15), 100: (0.10, 0.04, 0.08)}
+    rng = O.Pcg32(seed)
+    steps_done = 0
+    for s in [int(v) for v in g["golden_steps"]]:
+        while steps_done < s:
+            x_np = O.random_uniform(rng, B * n_in).reshape(B, n_in)
+            x, t = torch.from_numpy(x_np).to(dev), torch.from_numpy(O.synth_target(x_np, n_out)).to(dev)
+            last = steps_done + 1 == s
+            tr.training_step(x, t, run_optimizer=not last)
+            if last:
+                grads = tr.param_gradients.cpu().numpy()
+                loss = tr.loss()
+                tr.optimizer_step()
+            steps_done += 1
+        assert abs(loss - float(g["losses"][s - 1])) <= 5e-3 * float(g["losses"][s - 1]), f"step {s}: loss {loss} vs {g['losses'][s - 1]}"
+        master, m1, v1 = (a.cpu().numpy()[idx] for a in (tr.params_full_precision, tr.first_moments, tr.second_moments))
+        st = tr.param_steps.cpu().numpy().view(np.uint32)
+        # zero-gradient skip: per level the number of touched entries and the sum of the step counters agree to 0.2 %
+        for l in range(info.n_levels):
+            a, b = n_mlp + 2 * info.level_offset[l], n_mlp + 2 * info.level_offset[l + 1]
+            nz_ref, sum_ref = int(g[f"s{s}_nz_L{l}"]), int(g[f"s{s}_stepsum_L{l}"])
+            assert abs(np.count_nonzero(grads[a:b]) - nz_ref) <= 2e-3 * nz_ref + 2, f"step {s} level {l}: touched entries"
+            assert abs(int(st[a:b].astype(np.int64).sum()) - sum_ref) <= 2e-3 * sum_ref + 2, f"step {s} level {l}: step counters"
+        assert np.mean(st[idx] != g[f"s{s}_steps"]) <= (2e-3 if s == 1 else 0.02 + 2e-3 * s), f"step {s}: per-parameter step counters"
+        assert np.array_equal(st[idx][is_mlp], g[f"s{s}_steps"][is_mlp])  # matrix weights are never skipped
+        for which, sel, bar in (("mlp", is_mlp, bars[s][0]), ("levels 0-4", coarse, bars[s][1]), ("levels 5-15", fine, bars[s][2])):
+            e = common.rel_l2(master[sel] - init[sel], g[f"s{s}_master"][sel] - init[sel])
+            assert e < bar, f"step {s} {which}: parameter displacement differs by {e}"
+        # second moments integrate g^2 over the trajectory: their sums agree to a few per cent, the first step exactly follows the gradient
+        for which, sel in (("levels 0-4", coarse), ("levels 5-15", fine)):
+            r = float(v1[sel].astype(np.float64).sum() / g[f"s{s}_v"][sel].astype(np.float64).sum())
+            assert abs(r - 1) < 0.06, f"step {s} {which}: sum of second moments ratio {r}"
+        if s == 1:
+            assert common.rel_l2(m1[~is_mlp], g["s1_m"][~is_mlp]) < 1e-2 and common.rel_l2(v1[~is_mlp], g["s1_v"][~is_mlp]) < 2e-2

@@ -192,9 +192,11 @@ def test_mlp_forward_backward_vs_oracle(ctx, B):
     # A handful of ReLU-mask flips (pre-activations within fp32 rounding of zero: 8 of 25 M elements at B = 2^16 between a
     # float32 and a float64 run of the ORACLE itself) carry a whole gradient element each: 1e-3 at large B is the oracle's
     # own reproducibility, not kernel error.
-    bar = 2e-3 if B <= 1024 else 6e-3
-    assert common.rel_l2(dx.cpu().numpy(), dx_ref) < bar
-    _per_matrix(ctx.m, gp.cpu().numpy().astype(np.float64), dW, bar, "dW")
+    # The chain accumulates in fp16 like the reference; the oracle rounds after every 16-deep step too but sums inside a step in
+    # fp32 where the tensor core keeps more bits: last-place differences that H layers amplify.  The weight gradients are
+    # accumulated in fp16 over each CTA's tiles (the reference: over 4096-sample slices), the oracle's are exact: north-star bar.
+    assert common.rel_l2(dx.cpu().numpy(), dx_ref) < 1e-2
+    _per_matrix(ctx.m, gp.cpu().numpy().astype(np.float64), dW, 1e-2, "dW")
 
 
 def test_training_fwd_bwd_vs_oracle_and_reference(ctx):
@@ -221,14 +223,15 @@ def test_training_fwd_bwd_vs_oracle_and_reference(ctx):
     n_first = ctx.m.shapes()[0][0] * ctx.m.shapes()[0][1]
     # with the reference's initial table (|values| <= 1e-4) the input-matrix gradients of the grid configs are ~5e-6, i.e. fp16
     # SUBNORMALS (spacing 6e-8): their storage format alone limits them to ~1e-2
-    _per_matrix(ctx.m, got[: ctx.m.n_params], dW, 3e-3, "dW vs oracle") if ctx.g is None else (
-        _per_matrix(ctx.m, np.r_[dW[:n_first], got[n_first: ctx.m.n_params]], dW, 3e-3, "dW vs oracle"),
-        None if common.rel_l2(got[:n_first], dW[:n_first]) < 1.5e-2 else pytest.fail("dW_in vs oracle"))
+    # (and the kernels accumulate them in fp16 like the reference's split-K GEMMs, the oracle exactly: north-star bar 1e-2 elsewhere)
+    _per_matrix(ctx.m, got[: ctx.m.n_params], dW, 1e-2, "dW vs oracle") if ctx.g is None else (
+        _per_matrix(ctx.m, np.r_[dW[:n_first], got[n_first: ctx.m.n_params]], dW, 1e-2, "dW vs oracle"),
+        None if common.rel_l2(got[:n_first], dW[:n_first]) < 5e-2 else pytest.fail("dW_in vs oracle"))
     if ctx.g is not None:
         gg = O.grid_backward(ctx.g, x_np, dx[:, : ctx.g.n_features]).reshape(-1)
         assert common.rel_l2(got[ctx.m.n_params:], gg) < 1e-2
-    # reference dump (fp16 accumulation on its side)
-    assert common.rel_l2(out.cpu().numpy()[:, : ctx.n_out].astype(np.float32), z["output"]) < 2e-2
+    # reference dump: same fp16 accumulation on both sides
+    assert common.rel_l2(out.cpu().numpy()[:, : ctx.n_out].astype(np.float32), z["output"]) < 1e-3
     assert abs(loss.item() - float(z["loss"])) <= 2e-3 * float(z["loss"])
     last = ctx.m.shapes()[-1][0] * ctx.m.shapes()[-1][1]
     assert common.rel_l2(got[ctx.m.n_params - last: ctx.m.n_params], z["grads_mlp"][-last:].astype(np.float64)) < 1e-2
@@ -336,6 +339,7 @@ def test_full_size_weight_gradients_are_linear_in_dy(dev):
     full = dW(enc, dy)
     assert torch.isfinite(full).all() and full.abs().max() > 0
     dbl = dW(enc, (dy.float() * 2).half())
-    assert common.rel_l2((dbl / 2).cpu().numpy(), full.cpu().numpy()) < 2e-3
+    # fp16 accumulators: scaling by 2 is exact except in the subnormal range, and a different split of the batch rounds differently
+    assert common.rel_l2((dbl / 2).cpu().numpy(), full.cpu().numpy()) < 5e-3
     halves = dW(enc[: B // 2].contiguous(), dy[: B // 2].contiguous()) + dW(enc[B // 2:].contiguous(), dy[B // 2:].contiguous())
-    assert common.rel_l2(halves.cpu().numpy(), full.cpu().numpy()) < 2e-3
+    assert common.rel_l2(halves.cpu().numpy(), full.cpu().numpy()) < 5e-3

@@ -60,9 +60,12 @@ def test_mlp_loss_gradients_within_tolerance(case):
     enc = np.zeros((B, m.n_input), np.float16)
     enc[:, : g.n_features] = O.grid_forward(g, case["x"], p16[m.n_params:])
     y, hidden = O.mlp_forward(m, p16[: m.n_params], enc)
-    assert common.rel_l2(y, z["output_padded"]) < 1e-2  # reference accumulates in fp16
-    # max_level case: half of the (1e-4-sized) features are zero, the outputs are ~1e-5 - fp16 subnormals with 0.6 % spacing
-    assert common.rel_l2(y[:, :n_out].astype(np.float32), z["output"]) < (1.5e-2 if g.max_level < 1 else 1e-2)
+    # the oracle accumulates like the reference (fp16, rounded every 16-deep step): a handful of last-place differences remain
+    assert common.rel_l2(y, z["output_padded"]) < 1e-3
+    assert np.count_nonzero(y.astype(np.float32) != z["output_padded"].astype(np.float32)) <= 2e-3 * y.size
+    assert common.rel_l2(y[:, :n_out].astype(np.float32), z["output"]) < 1e-3
+    y32, _ = O.mlp_forward(m, p16[: m.n_params], enc, acc=np.float32)  # exact accumulation: the north-star tolerance
+    assert common.rel_l2(y32[:, :n_out].astype(np.float32), z["output"]) < (1.5e-2 if g.max_level < 1 else 1e-2)
     relative = case["cfg"]["loss"]["otype"] == "RelativeL2"
     # loss + gradient restatement checked on the reference's own prediction: must agree to fp32 rounding
     lv, dy = O.loss_l2(z["output_padded"], case["t"], n_out, relative=relative)
@@ -72,7 +75,7 @@ def test_mlp_loss_gradients_within_tolerance(case):
     assert common.rel_l2(dW, z["grads_mlp"]) < 1e-2
     gg = O.grid_backward(g, case["x"], dx[:, : g.n_features])
     nz = z["grads_grid_nz_idx"].astype(np.int64)
-    assert common.rel_l2(gg[nz], z["grads_grid_nz_val"]) < 8e-2  # ReLU-mask flips (fp16 vs fp32 accumulate), see DESIGN.md
+    assert common.rel_l2(gg[nz], z["grads_grid_nz_val"]) < 1e-2  # north-star bar; 5-9e-4 measured (no ReLU mask differs any more)
     assert abs(np.count_nonzero(gg) - len(nz)) <= 2e-3 * len(nz) + 4
 
 
@@ -182,27 +185,28 @@ def test_wide_encoding_matches_reference(wide_case):
 
 
 def test_wide_mlp_vs_reference(wide_case):
-    """fp32-accumulating oracle (= what the B200 kernels compute) within the north-star tolerance of the reference for the
-    outputs; with the reference's arithmetic emulated (accumulator rounded to fp16 every 16-deep MMA step) the oracle
-    reproduces the reference's output to 2e-3, which shows the remaining gap is the reference's own fp16 accumulation."""
+    """With the reference's arithmetic (accumulator rounded to fp16 every 16-deep MMA step, the oracle's default and what the
+    B200 kernels do in TMEM) the oracle reproduces the reference's output to 1e-3; exact (fp32) accumulation stays within
+    the north-star tolerance only - the gap is the reference's own fp16 accumulation."""
     z, cfg, m, n_out = wide_case["z"], wide_case["cfg"], wide_case["m"], wide_case["n_out"]
     p16 = wide_case["p"].astype(np.float16)
     enc = np.ascontiguousarray(z["encoded_soa"].T)  # the reference's own encoding output
     y, hidden = O.mlp_forward(m, p16[: m.n_params], enc)
-    assert common.rel_l2(y[:, :n_out].astype(np.float32), z["output"]) < 2e-2
-    y16, _ = O.mlp_forward(m, p16[: m.n_params], enc, acc="hmma16")
-    assert common.rel_l2(y16[:, :n_out].astype(np.float32), z["output"]) < 2e-3
+    assert common.rel_l2(y[:, :n_out].astype(np.float32), z["output"]) < 1e-3
+    y32, _ = O.mlp_forward(m, p16[: m.n_params], enc, acc=np.float32)
+    assert common.rel_l2(y32[:, :n_out].astype(np.float32), z["output"]) < 2e-2
     relative = cfg["loss"]["otype"] == "RelativeL2"
     lv, dy = O.loss_l2(z["output_padded"], wide_case["t"], n_out, relative=relative)
     assert abs(lv - float(z["loss"])) < 1e-5 * abs(lv)
     assert common.rel_l2(dy, z["dL_doutput"]) < 1e-6
     dW, _ = O.mlp_backward(m, p16[: m.n_params], enc, hidden, O.loss_l2(y, wide_case["t"], n_out, relative=relative)[1], y=y)
-    # last matrices first: the closer to the input, the more fp16-accumulated layers of the reference lie in between
+    assert common.rel_l2(dW, z["grads_mlp"].astype(np.float64)) < 1e-2  # north-star bar for parameter gradients
     pos = m.n_params
-    bars = [5e-3, 1.5e-2, 3e-2, 5e-2, 5e-2, 5e-2]
-    for k, (r, c) in enumerate(reversed(m.shapes())):
+    for k, (r, c) in enumerate(reversed(m.shapes())):  # per matrix: the reference's own fp16 split-K accumulation is the residual
         pos -= r * c
-        bar = 1e-1 if (k == len(m.shapes()) - 1 and wide_case["g"] is not None) else bars[min(k, len(bars) - 1)]
+        # input matrix behind a freshly initialised grid: features ~1e-4, so its gradient entries are fp16 subnormals (~4e-6, spacing
+        # 6e-8) and the reference's fp16-accumulating split-K GEMM underflows on top of that
+        bar = 1e-1 if (k == len(m.shapes()) - 1 and wide_case["g"] is not None) else 3e-2
         assert common.rel_l2(dW[pos:pos + r * c], z["grads_mlp"][pos:pos + r * c].astype(np.float64)) < bar, f"dW {r}x{c}"
 
 

@@ -34,7 +34,14 @@ struct GridLevel {
 	uint32_t hashed;        // 1 if (Hash grid && size < final stride)
 	uint32_t replicated;    // backward: scatter into one of n_replicas private copies (coarse, heavily contended levels)
 	uint32_t rep_offset;    // first entry of this level inside one replica
+	uint64_t magic;         // ceil(2^64 / size): index % size without a division (fastmod_u32)
 };
+
+// a % d for 32-bit a, d with M = ceil(2^64 / d) (Lemire, Kaser, Kurz: "Faster remainder by direct computation", exact for all 32-bit
+// operands).  The dense levels' sizes are not powers of two (grid_index takes `index % hashmap_size`, common_device.h:706); a
+// hardware-less 32-bit modulo costs ~20 instructions and a branch around it, this costs four multiplies and no branch.
+__host__ __device__ __forceinline__ uint64_t fastmod_magic(uint32_t d) { return 0xFFFFFFFFFFFFFFFFull / d + 1; }
+__device__ __forceinline__ uint32_t fastmod_u32(uint32_t a, uint64_t M, uint32_t d) { return (uint32_t)__umul64hi(M * a, d); }
 
 struct GridParams {
 	uint32_t n_levels;
@@ -84,8 +91,7 @@ __device__ __forceinline__ uint32_t grid_index_dev(const GridLevel& lv, const ui
 #pragma unroll
 		for (int d = 0; d < D; ++d) index += pg[d] * lv.stride[d]; // stride[d] == 0 for skipped dims
 	}
-	// size is a power of two for every hashed level (2^log2_hashmap_size); dense levels need the real modulo
-	return (lv.size & (lv.size - 1)) == 0 ? (index & (lv.size - 1)) : (index % lv.size);
+	return fastmod_u32(index, lv.magic, lv.size);
 }
 
 template <int F> struct FeatVec;
@@ -297,7 +303,7 @@ __device__ __forceinline__ void scatter_chunk(const GridParams& gp, const float 
 				const uint32_t q0 = l0 == 0 ? v0 : (together && l1 == 0 ? v1 : 0u), q1 = l0 == 1 ? v0 : (together && l1 == 1 ? v1 : 0u);
 				const uint32_t q2 = l0 == 2 ? v0 : (together && l1 == 2 ? v1 : 0u), q3 = l0 == 3 ? v0 : (together && l1 == 3 ? v1 : 0u);
 				red_add_h2x4(gtable + (size_t)(idx[c] & ~3u) * 2, q0, q1, q2, q3);
-				if (!together) red_add_h2(gtable + (size_t)idx[c + 1] * 2, *reinterpret_cast<const __half2*>(&v1));
+				red_add_h2_if(!together, gtable + (size_t)idx[c + 1] * 2, v1);
 #else
 				const bool paired = ((idx[c] ^ idx[c + 1]) == 1u), odd = (idx[c] & 1u) != 0;
 				const uint32_t nb = paired ? v1 : 0u;
@@ -313,7 +319,7 @@ __device__ __forceinline__ void scatter_chunk(const GridParams& gp, const float 
 				const bool paired = ((idx[c] ^ idx[c + 1]) == 1u), odd = (idx[c] & 1u) != 0;
 				const uint32_t n0 = paired ? b0 : 0u, n1 = paired ? b1 : 0u;
 				red_add_h2x4(gtable + (size_t)(idx[c] & ~1u) * 4, odd ? n0 : a0, odd ? n1 : a1, odd ? a0 : n0, odd ? a1 : n1);
-				if (!paired) red_add_h2x2(gtable + (size_t)idx[c + 1] * 4, b0, b1);
+				red_add_h2x2_if(!paired, gtable + (size_t)idx[c + 1] * 4, b0, b1);
 			}
 		} else { // F == 8: one 16-byte reduction per corner
 #pragma unroll

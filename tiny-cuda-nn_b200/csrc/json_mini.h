@@ -21,6 +21,7 @@ struct Value {
 	std::map<std::string, Value> obj;
 
 	bool contains(const std::string& k) const { return kind == Object && obj.count(k) != 0; }
+	std::vector<std::string> keys() const { std::vector<std::string> r; for (const auto& kv : obj) r.push_back(kv.first); return r; }
 	const Value& at(const std::string& k) const {
 		auto it = obj.find(k);
 		if (it == obj.end()) throw std::runtime_error("json: missing key '" + k + "'");

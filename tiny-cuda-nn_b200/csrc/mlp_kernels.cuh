@@ -69,6 +69,48 @@ struct MlpArgs {
 	__half* wide_hidden; __half* wide_gtmp; __half* wide_dy;
 };
 
+// Accumulator precision.  The reference accumulates every layer in fp16 (wmma half fragments, fully_fused_mlp.cu:66-68) and its
+// weight-gradient GEMMs too (cutlass_matmul.h:59-86), and its results depend on that: with fp16 accumulators in TMEM (instruction
+// descriptor c_format = F16, the tensor core rounds to fp16 after every 16-deep step exactly like HMMA.16816.F16) the network
+// output is BIT-IDENTICAL to the reference build's, no ReLU mask differs, and the 1000-step loss agrees to < 0.5 % where fp32
+// accumulation - more accurate, but not the reference's arithmetic - ended 4 % apart.  So fp16 is the
+// default; -DTCNN_B200_F32_ACC builds the fp32-accumulating kernels.
+#ifdef TCNN_B200_F32_ACC
+constexpr uint32_t ACC_F32 = 1;
+#else
+constexpr uint32_t ACC_F32 = 0;
+#endif
+// This thread's accumulator row, columns [0, 2 N), as N packed half2.  fp16 accumulators sit in the low half of their 32-bit TMEM
+// column and are fetched two per register (tcgen05.ld .pack::16b); fp32 accumulators are fetched whole and rounded here.
+template <int N> struct AccRow {
+	uint32_t h[N];
+	uint32_t raw[ACC_F32 ? 2 * N : 1];
+};
+template <int N> __device__ __forceinline__ void acc_issue(uint32_t taddr, AccRow<N>& a) {
+	static_assert(N == 8 || N == 16 || N == 32, "8, 16 or 32 packed pairs");
+	if constexpr (ACC_F32) {
+		if constexpr (N == 8) { tmem_ld16(taddr, a.raw); }
+		else if constexpr (N == 16) { tmem_ld32(taddr, a.raw); }
+		else { tmem_ld32(taddr, *reinterpret_cast<uint32_t(*)[32]>(&a.raw[0])); tmem_ld32(taddr + 32, *reinterpret_cast<uint32_t(*)[32]>(&a.raw[32])); }
+	} else {
+		if constexpr (N == 8) tmem_ld8_pack16(taddr, a.h);
+		else if constexpr (N == 16) tmem_ld16_pack16(taddr, a.h);
+		else tmem_ld32_pack16(taddr, a.h);
+	}
+}
+template <int N> __device__ __forceinline__ void acc_finish(AccRow<N>& a) {
+	tmem_ld_wait();
+	if constexpr (ACC_F32) {
+#pragma unroll
+		for (int i = 0; i < N; ++i) a.h[i] = pack_h2(__uint_as_float(a.raw[2 * i]), __uint_as_float(a.raw[2 * i + 1]));
+	}
+}
+// one weight-gradient accumulator element as read by the unpacked tcgen05.ld of the per-CTA flush
+__device__ __forceinline__ float dw_value(uint32_t v) {
+	if constexpr (ACC_F32) return __uint_as_float(v);
+	else return __half2float(__ushort_as_half((unsigned short)(v & 0xFFFFu)));
+}
+
 // byte offset of 16-byte chunk `c` of row `r` inside a 128-byte-swizzled tile
 __device__ __forceinline__ uint32_t sw128(uint32_t r, uint32_t c) { return r * 128u + ((c ^ (r & 7u)) << 4); }
 
@@ -187,11 +229,11 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 	// descriptors (constant parts)
 	constexpr uint32_t SBO = 1024, LBO_K = 16, LBO_MN = TILE_BYTES;
 	const uint32_t act_addr = smem_u32(act), g_addr = smem_u32(gbuf);
-	const uint32_t idesc_fwd64 = make_idesc_f16(128, 64, 0, 0);
-	const uint32_t idesc_fwd16 = make_idesc_f16(128, 16, 0, 0);
-	const uint32_t idesc_dgrad = make_idesc_f16(128, 64, 0, 1);   // A K-major, B = weight tile viewed MN-major
-	const uint32_t idesc_dx = make_idesc_f16(128, E, 0, 0);       // B = W_inT K-major
-	const uint32_t idesc_dw = make_idesc_f16(128, 64, 1, 1);      // both operands MN-major, K = 128 samples
+	const uint32_t idesc_fwd64 = make_idesc_f16(128, 64, 0, 0, ACC_F32);
+	const uint32_t idesc_fwd16 = make_idesc_f16(128, 16, 0, 0, ACC_F32);
+	const uint32_t idesc_dgrad = make_idesc_f16(128, 64, 0, 1, ACC_F32);   // A K-major, B = weight tile viewed MN-major
+	const uint32_t idesc_dx = make_idesc_f16(128, E, 0, 0, ACC_F32);       // B = W_inT K-major
+	const uint32_t idesc_dw = make_idesc_f16(128, 64, 1, 1, ACC_F32);      // both operands MN-major, K = 128 samples
 
 	// ---- scatter warpgroups (WS) ---------------------------------------------------------------------
 	if constexpr (WS) {
@@ -294,23 +336,15 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 			STAGE_CLOCK(a); // W: MMA complete
 			tc_fence_after();
 			const uint32_t dst = act_tile(k + 1);
-			uint32_t v0[32], v1[32];
-			tmem_ld32(t_acc + lane_off, v0);
-			tmem_ld32(t_acc + lane_off + 32, v1);
-			tmem_ld_wait();
+			AccRow<32> acc;
+			acc_issue(t_acc + lane_off, acc);
+			acc_finish(acc);
 #pragma unroll
-			for (int c = 0; c < 4; ++c) {
+			for (int c = 0; c < 8; ++c) {
 				uint32_t pk[4];
 #pragma unroll
-				for (int j = 0; j < 4; ++j) pk[j] = hidden_act_forward<GEN>(pack_h2(__uint_as_float(v0[c * 8 + 2 * j]), __uint_as_float(v0[c * 8 + 2 * j + 1])), a.activation);
+				for (int j = 0; j < 4; ++j) pk[j] = hidden_act_forward<GEN>(acc.h[c * 4 + j], a.activation);
 				sts128(dst + sw128(row, c), pk[0], pk[1], pk[2], pk[3]);
-			}
-#pragma unroll
-			for (int c = 0; c < 4; ++c) {
-				uint32_t pk[4];
-#pragma unroll
-				for (int j = 0; j < 4; ++j) pk[j] = hidden_act_forward<GEN>(pack_h2(__uint_as_float(v1[c * 8 + 2 * j]), __uint_as_float(v1[c * 8 + 2 * j + 1])), a.activation);
-				sts128(dst + sw128(row, 4 + c), pk[0], pk[1], pk[2], pk[3]);
 			}
 			STAGE_CLOCK(a); // E: epilogue math + sts issued
 			fence_proxy_async_smem();
@@ -330,12 +364,12 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 		STAGE_CLOCK(a); // W: MMA complete
 		tc_fence_after();
 		{
-			uint32_t v[16];
-			tmem_ld16(t_acc + lane_off, v);
-			tmem_ld_wait();
+			AccRow<8> acc;
+			acc_issue(t_acc + lane_off, acc);
+			acc_finish(acc);
 			uint32_t yk[8];
 #pragma unroll
-			for (int j = 0; j < 8; ++j) yk[j] = pack_h2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
+			for (int j = 0; j < 8; ++j) yk[j] = acc.h[j];
 			if (a.output_activation != ACT_NONE) { // on the fp16 pre-activation, all 16 padded columns like the reference
 #pragma unroll
 				for (int j = 0; j < 8; ++j) yk[j] = act_forward_h2(yk[j], a.output_activation);
@@ -427,23 +461,18 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 				// ReLU' from this row's stored post-activation ACT[k] (fp16 > 0), applied to the packed fp16 gradient
 				const uint32_t dst = g_addr + (gcur ^ 1) * TILE_BYTES;
 				const uint32_t asrc = act_tile(k);
-				uint32_t v0[32], v1[32];
-				tmem_ld32(t_acc + lane_off, v0);
-				tmem_ld32(t_acc + lane_off + 32, v1);
+				AccRow<32> acc;
+				acc_issue(t_acc + lane_off, acc);
 				uint4 av[8];
 #pragma unroll
 				for (int c = 0; c < 8; ++c) av[c] = lds128(asrc + sw128(row, c)); // all in flight under the TMEM load
-				tmem_ld_wait();
+				acc_finish(acc);
 #pragma unroll
 				for (int c = 0; c < 8; ++c) {
 					const uint32_t aw[4] = {av[c].x, av[c].y, av[c].z, av[c].w};
 					uint32_t pk[4];
 #pragma unroll
-					for (int j = 0; j < 4; ++j) {
-						const int e = (c & 3) * 8 + 2 * j;
-						const float f0 = __uint_as_float(c < 4 ? v0[e] : v1[e]), f1 = __uint_as_float(c < 4 ? v0[e + 1] : v1[e + 1]);
-						pk[j] = hidden_act_backward<GEN>(pack_h2(f0, f1), aw[j], a.activation);
-					}
+					for (int j = 0; j < 4; ++j) pk[j] = hidden_act_backward<GEN>(acc.h[c * 4 + j], aw[j], a.activation);
 					sts128(dst + sw128(row, c), pk[0], pk[1], pk[2], pk[3]);
 				}
 				gcur ^= 1;
@@ -475,12 +504,12 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 				if (want_dx) {
 					__half* dst = a.dL_dinput ? a.dL_dinput + (sample0 + row) * E : nullptr;
 					for (uint32_t c0 = 0; c0 < E; c0 += 16) {
-						uint32_t v[16];
-						tmem_ld16(t_acc + lane_off + c0, v);
-						tmem_ld_wait();
+						AccRow<8> acc;
+						acc_issue(t_acc + lane_off + c0, acc);
+						acc_finish(acc);
 						uint32_t pk[8];
 #pragma unroll
-						for (int j = 0; j < 8; ++j) pk[j] = pack_h2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
+						for (int j = 0; j < 8; ++j) pk[j] = acc.h[j];
 						if (dst) {
 							reinterpret_cast<uint4*>(dst + c0)[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
 							reinterpret_cast<uint4*>(dst + c0)[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
@@ -527,7 +556,7 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 						if (have) { tmem_ld32(t_dw_in + lane_off + half_i * 32, v); tmem_ld_wait(); }
 						if (r < E) {
 #pragma unroll
-							for (int j = 0; j < 32; ++j) out[(half_i * 32 + j) * E + r] = have ? __uint_as_float(v[j]) : 0.f;
+							for (int j = 0; j < 32; ++j) out[(half_i * 32 + j) * E + r] = have ? dw_value(v[j]) : 0.f;
 						}
 					}
 				}
@@ -541,7 +570,7 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 					if (have) { tmem_ld32(t_dw_in + lane_off + half_i * 32, v); tmem_ld_wait(); }
 					if (r < E) {
 #pragma unroll
-						for (int j = 0; j < 32; ++j) out[(half_i * 32 + j) * E + r] = have ? __uint_as_float(v[j]) : 0.f;
+						for (int j = 0; j < 32; ++j) out[(half_i * 32 + j) * E + r] = have ? dw_value(v[j]) : 0.f;
 					}
 				}
 				float* o = out + 64 * E;
@@ -553,7 +582,7 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 						float4* o4 = reinterpret_cast<float4*>(o + r * 64 + half_i * 32);
 #pragma unroll
 						for (int j = 0; j < 8; ++j)
-							o4[j] = have ? make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3])) : make_float4(0, 0, 0, 0);
+							o4[j] = have ? make_float4(dw_value(v[4 * j]), dw_value(v[4 * j + 1]), dw_value(v[4 * j + 2]), dw_value(v[4 * j + 3])) : make_float4(0, 0, 0, 0);
 					}
 					o += 64 * 64;
 				}
@@ -566,7 +595,7 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 							float4* o4 = reinterpret_cast<float4*>(o + r * 64 + half_i * 32);
 #pragma unroll
 							for (int j = 0; j < 8; ++j)
-								o4[j] = have ? make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3])) : make_float4(0, 0, 0, 0);
+								o4[j] = have ? make_float4(dw_value(v[4 * j]), dw_value(v[4 * j + 1]), dw_value(v[4 * j + 2]), dw_value(v[4 * j + 3])) : make_float4(0, 0, 0, 0);
 						}
 					}
 				}

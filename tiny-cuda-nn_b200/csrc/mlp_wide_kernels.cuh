@@ -154,7 +154,7 @@ __global__ void __launch_bounds__(128 * NWG, 1) mlp_wide_forward_kernel(const __
 	const uint32_t t_acc = *tmem_slot + wg * 128;
 	const uint32_t lane_off = (warp * 32) << 16;
 	const uint32_t act_addr = smem_u32(act) + wg * WIDE_TILE_BYTES;
-	const uint32_t idesc_hid = make_idesc_f16(128, 128, 0, 0), idesc_out = make_idesc_f16(128, 16, 0, 0);
+	const uint32_t idesc_hid = make_idesc_f16(128, 128, 0, 0, ACC_F32), idesc_out = make_idesc_f16(128, 16, 0, 0, ACC_F32);
 	uint64_t* bar = bars + wg;
 	uint64_t* bar_x = bars_x + wg;
 	uint32_t phase = 0, phase_x = 0;
@@ -201,16 +201,16 @@ __global__ void __launch_bounds__(128 * NWG, 1) mlp_wide_forward_kernel(const __
 			tc_fence_after();
 			if (STORE && k > 0) wide_wg_sync<NWG>(wg); // thread 0 arrives once the bulk copy has read the tile: it may be overwritten
 #pragma unroll
-			for (int cb = 0; cb < 4; ++cb) {
-				uint32_t v[32];
-				tmem_ld32(t_acc + lane_off + cb * 32, v);
-				tmem_ld_wait();
+			for (int cb = 0; cb < 2; ++cb) { // 64 accumulator columns = one sub-tile row per step
+				AccRow<32> acc;
+				acc_issue(t_acc + lane_off + cb * 64, acc);
+				acc_finish(acc);
 #pragma unroll
-				for (int c = 0; c < 4; ++c) {
+				for (int c = 0; c < 8; ++c) {
 					uint32_t pk[4];
 #pragma unroll
-					for (int j = 0; j < 4; ++j) pk[j] = hidden_act_forward<true>(pack_h2(__uint_as_float(v[c * 8 + 2 * j]), __uint_as_float(v[c * 8 + 2 * j + 1])), a.activation);
-					sts128(act_addr + (cb >> 1) * SUB_BYTES + sw128(row, (cb & 1) * 4 + c), pk[0], pk[1], pk[2], pk[3]);
+					for (int j = 0; j < 4; ++j) pk[j] = hidden_act_forward<true>(acc.h[c * 4 + j], a.activation);
+					sts128(act_addr + cb * SUB_BYTES + sw128(row, c), pk[0], pk[1], pk[2], pk[3]);
 				}
 			}
 			fence_proxy_async_smem();
@@ -238,12 +238,12 @@ __global__ void __launch_bounds__(128 * NWG, 1) mlp_wide_forward_kernel(const __
 			tma_bulk_g2s_addr(act_addr, x_img + (size_t)(tile + tile_step) * x_bytes, x_bytes, bar_x);
 		}
 		{
-			uint32_t v[16];
-			tmem_ld16(t_acc + lane_off, v);
-			tmem_ld_wait();
+			AccRow<8> acc;
+			acc_issue(t_acc + lane_off, acc);
+			acc_finish(acc);
 			uint32_t yk[8];
 #pragma unroll
-			for (int j = 0; j < 8; ++j) yk[j] = pack_h2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
+			for (int j = 0; j < 8; ++j) yk[j] = acc.h[j];
 			if (a.output_activation != ACT_NONE) {
 #pragma unroll
 				for (int j = 0; j < 8; ++j) yk[j] = act_forward_h2(yk[j], a.output_activation);
@@ -360,8 +360,8 @@ __global__ void __launch_bounds__(128 * NWG, 1) mlp_wide_backward_kernel(const _
 	const uint32_t t_acc = *tmem_slot + wg * 128;
 	const uint32_t lane_off = (warp * 32) << 16;
 	const uint32_t g_addr = smem_u32(gt) + wg * WIDE_TILE_BYTES;
-	const uint32_t idesc_dgrad = make_idesc_f16(128, 128, 0, 1);         // A K-major, B = weight tile viewed MN-major
-	const uint32_t idesc_dx = make_idesc_f16(128, in_sub * 64, 0, 1);
+	const uint32_t idesc_dgrad = make_idesc_f16(128, 128, 0, 1, ACC_F32);         // A K-major, B = weight tile viewed MN-major
+	const uint32_t idesc_dx = make_idesc_f16(128, in_sub * 64, 0, 1, ACC_F32);
 	uint64_t* bar = bars + wg;
 	uint32_t phase = 0;
 	const uint32_t row = wt;
@@ -407,18 +407,18 @@ __global__ void __launch_bounds__(128 * NWG, 1) mlp_wide_backward_kernel(const _
 			tc_fence_after();
 			if (m < H) wide_wg_sync<NWG>(wg); // the bulk copy has read the tile (thread 0 arrives after its wait)
 #pragma unroll
-			for (int cb = 0; cb < 4; ++cb) {
-				uint32_t v[32];
-				tmem_ld32(t_acc + lane_off + cb * 32, v);
-				tmem_ld_wait();
+			for (int cb = 0; cb < 2; ++cb) {
+				AccRow<32> acc;
+				acc_issue(t_acc + lane_off + cb * 64, acc);
+				acc_finish(acc);
 #pragma unroll
-				for (int c = 0; c < 4; ++c) {
-					const uint4 aw4 = av[cb * 4 + c];
+				for (int c = 0; c < 8; ++c) {
+					const uint4 aw4 = av[cb * 8 + c];
 					const uint32_t aw[4] = {aw4.x, aw4.y, aw4.z, aw4.w};
 					uint32_t pk[4];
 #pragma unroll
-					for (int j = 0; j < 4; ++j) pk[j] = hidden_act_backward<true>(pack_h2(__uint_as_float(v[c * 8 + 2 * j]), __uint_as_float(v[c * 8 + 2 * j + 1])), aw[j], a.activation);
-					sts128(g_addr + (cb >> 1) * SUB_BYTES + sw128(row, (cb & 1) * 4 + c), pk[0], pk[1], pk[2], pk[3]);
+					for (int j = 0; j < 4; ++j) pk[j] = hidden_act_backward<true>(acc.h[c * 4 + j], aw[j], a.activation);
+					sts128(g_addr + cb * SUB_BYTES + sw128(row, c), pk[0], pk[1], pk[2], pk[3]);
 				}
 			}
 			fence_proxy_async_smem();
@@ -442,12 +442,10 @@ __global__ void __launch_bounds__(128 * NWG, 1) mlp_wide_backward_kernel(const _
 			tc_fence_after();
 			__half* dst = a.dL_dinput + (sample0 + row) * E;
 			for (uint32_t c0 = 0; c0 < E; c0 += 16) {
-				uint32_t v[16];
-				tmem_ld16(t_acc + lane_off + c0, v);
-				tmem_ld_wait();
-				uint32_t pk[8];
-#pragma unroll
-				for (int j = 0; j < 8; ++j) pk[j] = pack_h2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
+				AccRow<8> acc;
+				acc_issue(t_acc + lane_off + c0, acc);
+				acc_finish(acc);
+				const uint32_t (&pk)[8] = acc.h;
 				reinterpret_cast<uint4*>(dst + c0)[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
 				reinterpret_cast<uint4*>(dst + c0)[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
 			}
@@ -463,7 +461,7 @@ __global__ void __launch_bounds__(128 * NWG, 1) mlp_wide_backward_kernel(const _
 
 // ---- weight gradients: split-K over the batch ------------------------------------------------------------------
 // CTA (split j, matrix m): D[out][in] = sum over its tiles of G_m^T[out x 128 samples] * ACT_m[128 samples x in], both
-// operands MN-major views of [sample][feature] tiles; fp32 in TMEM across all tiles of the CTA, one flush at the end into
+// operands MN-major views of [sample][feature] tiles; accumulated in TMEM (fp16 like the reference's split-K GEMMs, see ACC_F32) across all tiles of the CTA, one flush at the end into
 // partials[j]; mlp_finalize(_adam)_kernel sums the splits (deterministic).  Replaces the reference's three split-K CUTLASS
 // GEMMs (fully_fused_mlp.cu:783-829).  The kernel is a pure stream over HBM (64 KB of operands per 0.27 us of MMA): the
 // tile images are fetched by bulk copies into a 3-stage ring, two tiles ahead of the MMA; only thread 0 works in the loop.
@@ -496,7 +494,7 @@ __global__ void __launch_bounds__(128, 1) mlp_wide_dw_kernel(const __grid_consta
 	const uint32_t bw = (m == 0) ? E : (uint32_t)WIDE_W;
 	const uint32_t b_bytes = (m == 0) ? in_sub * SUB_BYTES : WIDE_TILE_BYTES;
 	const uint32_t tx_bytes = b_bytes + (a_is_dy ? 0u : WIDE_TILE_BYTES);
-	const uint32_t idesc = make_idesc_f16(128, (m == 0) ? in_sub * 64 : 128, 1, 1);
+	const uint32_t idesc = make_idesc_f16(128, (m == 0) ? in_sub * 64 : 128, 1, 1, ACC_F32);
 	const uint32_t smem_addr = smem_u32(smem);
 	const uint32_t n_my = split < a.n_tiles ? (a.n_tiles - split + a.n_splits - 1) / a.n_splits : 0u;
 	auto tile_of = [&](uint32_t i) { return split + i * a.n_splits; };
@@ -557,7 +555,7 @@ __global__ void __launch_bounds__(128, 1) mlp_wide_dw_kernel(const __grid_consta
 #pragma unroll
 				for (int j = 0; j < 4; ++j)
 					reinterpret_cast<float4*>(out + c0)[j] = n_my == 0 ? make_float4(0, 0, 0, 0)
-						: make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
+						: make_float4(dw_value(v[4 * j]), dw_value(v[4 * j + 1]), dw_value(v[4 * j + 2]), dw_value(v[4 * j + 3]));
 			}
 		}
 	}

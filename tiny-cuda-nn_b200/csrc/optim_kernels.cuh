@@ -26,6 +26,7 @@ struct AdamArgs {
 	uint32_t global_step;         // step count of parameters updated every step (after this update)
 	float global_correction;      // sqrtf(1 - beta2^t) / (1 - beta1^t) at t = global_step
 	int zero_grads;               // re-zero the non-matrix gradients after consuming them
+	int optimize_matrix, optimize_non_matrix; // adam.h:77-85: 0 freezes the MLP weights / the grid tables (their state does not advance)
 	float* master;
 	__half* params;
 	__half* grads;
@@ -42,7 +43,7 @@ struct AdamArgs {
 __device__ __forceinline__ bool adam_one(const AdamArgs& a, uint32_t i, float g_half, float& w, float& m, float& v, uint32_t& step) {
 	float gradient = a.inv_loss_scale != 0.f ? g_half * a.inv_loss_scale : g_half / a.loss_scale;
 	const bool is_matrix = i < a.n_matrix;
-	if (!is_matrix && gradient == 0.f) return false;
+	if (is_matrix ? !a.optimize_matrix : (!a.optimize_non_matrix || gradient == 0.f)) return false;
 	if (is_matrix) gradient += a.l2_reg * w;
 	const float gradient_sq = gradient * gradient;
 	m = a.beta1 * m + (1 - a.beta1) * gradient;
@@ -166,11 +167,15 @@ __global__ void __launch_bounds__(256) mlp_finalize_adam_kernel(uint32_t n_param
 //           multimem.st)
 //   exit :  the last CTA announces "my parameter writes are visible" and waits for the same from all peers, so that
 //           when the kernel retires every rank may read its parameters and re-zero its gradients.
-// The waits are on other GPUs' kernels, never on CTAs of this launch, and give up after DP_TIMEOUT_NS (trap).
+// The waits are on other GPUs' kernels, never on CTAs of this launch.  Ranks may be minutes apart (rank-0-only evaluation,
+// checkpointing, a first-step module load, a profiler): a wait gives up only after DpComm::timeout_ns (default 10 min,
+// TCNN_B200_DP_TIMEOUT_S), and then does NOT trap - a trap would kill the CUDA context of every rank - but writes the epoch
+// into word DP_FLAG_ERROR of the rank's own flag block and lets the kernel return without touching the parameters; the host
+// turns the flag into an error the next time it looks (Trainer.loss / Trainer.check_peers).
 constexpr uint32_t DP_MAX_RANKS = 8;
-constexpr uint32_t DP_FLAG_GRADS = 0, DP_FLAG_PARAMS = 8, DP_FLAG_COUNTER = 16, DP_FLAG_WORDS = 32;
-constexpr uint64_t DP_TIMEOUT_NS = 10ull * 1000 * 1000 * 1000;
+constexpr uint32_t DP_FLAG_GRADS = 0, DP_FLAG_PARAMS = 8, DP_FLAG_COUNTER = 16, DP_FLAG_ERROR = 17, DP_FLAG_WORDS = 32;
 struct DpComm {
+	uint64_t timeout_ns;
 	uint32_t rank, world, epoch, use_multicast;
 	__half* peer_grads[DP_MAX_RANKS];
 	__half* peer_params[DP_MAX_RANKS];
@@ -181,13 +186,16 @@ struct DpComm {
 
 // signal = release store, wait = acquire polling with back-off (hundreds of CTAs poll the same line), both system scope
 __device__ __forceinline__ void dp_signal(uint32_t* flag, uint32_t epoch) { st_release_sys(flag, epoch); }
-__device__ __forceinline__ void dp_wait_flag(const uint32_t* flag, uint32_t epoch) {
-	if ((int32_t)(ld_acquire_sys(flag) - epoch) >= 0) return;
+__device__ __forceinline__ bool dp_wait_flag(const uint32_t* flag, uint32_t epoch, uint64_t timeout_ns) {
+	if ((int32_t)(ld_acquire_sys(flag) - epoch) >= 0) return true;
 	const uint64_t t0 = globaltimer_ns();
+	uint32_t backoff = 100;
 	while ((int32_t)(ld_acquire_sys(flag) - epoch) < 0) {
-		__nanosleep(100);
-		if (globaltimer_ns() - t0 > DP_TIMEOUT_NS) { printf("tcnn_b200: data-parallel barrier timed out (a peer rank is gone)\n"); __trap(); }
+		__nanosleep(backoff);
+		if (backoff < 2000) backoff += 100; // long skews: poll the peer-written line less often
+		if (globaltimer_ns() - t0 > timeout_ns) return false;
 	}
+	return true;
 }
 
 // Persistent: a few CTAs per SM walk the shard in rows of 256 groups (group = 4 consecutive parameters = one 8-byte
@@ -201,8 +209,12 @@ __global__ void __launch_bounds__(256) dp_adam_kernel(const __grid_constant__ Ad
 #endif
 	// the scatter before this kernel is complete (stream order): thread r of the first CTA tells rank r
 	if (blockIdx.x == 0 && threadIdx.x < c.world) dp_signal(c.peer_flags[threadIdx.x] + DP_FLAG_GRADS + c.rank, c.epoch);
-	if (threadIdx.x < c.world) dp_wait_flag(my_flags + DP_FLAG_GRADS + threadIdx.x, c.epoch);
-	__syncthreads();
+	bool peers_ok = true;
+	if (threadIdx.x < c.world) peers_ok = dp_wait_flag(my_flags + DP_FLAG_GRADS + threadIdx.x, c.epoch, c.timeout_ns);
+	if (__syncthreads_or(!peers_ok)) { // a peer never arrived: leave the parameters alone, tell the host
+		if (threadIdx.x == 0) st_relaxed_sys(my_flags + DP_FLAG_ERROR, c.epoch);
+		return;
+	}
 #ifdef DP_STAMPS
 	if (blockIdx.x == 0 && threadIdx.x == 0) reinterpret_cast<uint64_t*>(my_flags)[13] = globaltimer_ns();
 #endif
@@ -256,7 +268,7 @@ __global__ void __launch_bounds__(256) dp_adam_kernel(const __grid_constant__ Ad
 		if (threadIdx.x == 0) reinterpret_cast<uint64_t*>(my_flags)[14] = globaltimer_ns();
 #endif
 		dp_signal(c.peer_flags[threadIdx.x] + DP_FLAG_PARAMS + c.rank, c.epoch);
-		dp_wait_flag(my_flags + DP_FLAG_PARAMS + threadIdx.x, c.epoch);
+		if (!dp_wait_flag(my_flags + DP_FLAG_PARAMS + threadIdx.x, c.epoch, c.timeout_ns)) st_relaxed_sys(my_flags + DP_FLAG_ERROR, c.epoch);
 	}
 #ifdef DP_STAMPS
 	__syncthreads();

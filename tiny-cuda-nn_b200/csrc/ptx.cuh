@@ -79,8 +79,8 @@ __device__ __forceinline__ uint64_t make_desc_sw128(uint32_t smem_addr, uint32_t
 
 // Instruction descriptor for kind::f16, fp16 A/B, fp32 accumulate.
 //   [4,6) c_format=1(F32) | [7,10) a_format=0(F16) | [10,13) b_format=0 | 15 a_major | 16 b_major | [17,23) N>>3 | [24,29) M>>4
-__host__ __device__ constexpr uint32_t make_idesc_f16(uint32_t M, uint32_t N, uint32_t a_mn_major, uint32_t b_mn_major) {
-	return (1u << 4) | (a_mn_major << 15) | (b_mn_major << 16) | ((N >> 3) << 17) | ((M >> 4) << 24);
+__host__ __device__ constexpr uint32_t make_idesc_f16(uint32_t M, uint32_t N, uint32_t a_mn_major, uint32_t b_mn_major, uint32_t c_format_f32 = 1) {
+	return (c_format_f32 << 4) | (a_mn_major << 15) | (b_mn_major << 16) | ((N >> 3) << 17) | ((M >> 4) << 24);
 }
 
 // D[tmem] (+)= A[smem] * B[smem]; issued by ONE thread.
@@ -116,6 +116,33 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
 		"{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
 		: "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
 		  "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+		: "r"(taddr) : "memory");
+}
+// fp16 accumulators (instruction descriptor c_format = F16): a 16-bit element sits in the low half of its 32-bit TMEM column;
+// .pack::16b returns two adjacent columns per register (column 2i in the low half), i.e. the row as packed half2.
+__device__ __forceinline__ void tmem_ld32_pack16(uint32_t taddr, uint32_t (&r)[32]) { // 64 columns
+	asm volatile(
+		"tcgen05.ld.sync.aligned.32x32b.x32.pack::16b.b32 "
+		"{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+		"%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+		: "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+		  "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+		  "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+		  "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+		: "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tmem_ld16_pack16(uint32_t taddr, uint32_t (&r)[16]) { // 32 columns
+	asm volatile(
+		"tcgen05.ld.sync.aligned.32x32b.x16.pack::16b.b32 "
+		"{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+		: "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+		  "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+		: "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tmem_ld8_pack16(uint32_t taddr, uint32_t (&r)[8]) { // 16 columns
+	asm volatile(
+		"tcgen05.ld.sync.aligned.32x32b.x8.pack::16b.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+		: "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
 		: "r"(taddr) : "memory");
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
@@ -169,9 +196,20 @@ __device__ __forceinline__ void red_add_h2x2(__half* addr, uint32_t a, uint32_t 
 __device__ __forceinline__ void red_add_h2x4(__half* addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
 	asm volatile("red.relaxed.gpu.global.add.noftz.v4.f16x2 [%0], {%1, %2, %3, %4};" ::"l"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
+// predicated forms: no branch around the reduction, so the scatter of several levels stays one schedulable block
+__device__ __forceinline__ void red_add_h2_if(bool p, __half* addr, uint32_t v) {
+	asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %2, 0;\n\t@q red.relaxed.gpu.global.add.noftz.f16x2 [%0], %1;\n\t}" ::"l"(addr), "r"(v), "r"((uint32_t)p) : "memory");
+}
+__device__ __forceinline__ void red_add_h2x2_if(bool p, __half* addr, uint32_t a, uint32_t b) {
+	asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %3, 0;\n\t@q red.relaxed.gpu.global.add.noftz.v2.f16x2 [%0], {%1, %2};\n\t}" ::"l"(addr), "r"(a), "r"(b), "r"((uint32_t)p) : "memory");
+}
 __device__ __forceinline__ uint32_t h2_bits(__half2 v) { return *reinterpret_cast<uint32_t*>(&v); }
 __device__ __forceinline__ uint32_t pack_h2(float a, float b) {
+#ifdef TCNN_B200_PACK_RZ // development experiment (tests/dev/parity_probe.py): round the fp32 accumulators toward zero
+	__half2 h = __halves2half2(__float2half_rz(a), __float2half_rz(b));
+#else
 	__half2 h = __floats2half2_rn(a, b);
+#endif
 	return *reinterpret_cast<uint32_t*>(&h);
 }
 

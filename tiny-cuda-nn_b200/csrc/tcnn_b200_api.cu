@@ -48,6 +48,7 @@ struct tcnn_b200_plan {
 	int activation = ACT_RELU, output_activation = ACT_NONE; // network.activation / network.output_activation (activation.cuh)
 	float non_matrix_lr_factor = 1.f, weight_clip = 0.f;
 	bool adabound = false;
+	bool optimize_matrix_params = true, optimize_non_matrix_params = true; // adam.h:57-58, 77-85: a false one freezes that parameter class
 	int grid_type = 0;              // GRID_HASH / GRID_DENSE / GRID_TILED (GridType, grid_interface.h)
 	int enc_kind = 0;               // ENC_GRID / ENC_IDENTITY / ENC_ONEBLOB
 	uint32_t oneblob_log2_bins = 0;
@@ -99,6 +100,7 @@ static void fill_level(GridLevel& lv, float scale, uint32_t size, uint32_t offse
 	lv.n_dense_dims = d;
 	lv.hashed = (hash_type && size < stride) ? 1u : 0u; // Dense / Tiled grids never hash: dense index with wrap, % size
 	lv.replicated = 0; lv.rep_offset = 0;
+	lv.magic = fastmod_magic(size ? size : 1u);
 }
 
 constexpr uint32_t N_REPLICAS = 32;          // private copies of the contended coarse gradient levels
@@ -109,7 +111,8 @@ constexpr uint32_t REPLICATE_MIN_BATCH = 1u << 14; // ... when the batch is larg
 static GridParams backward_params(const tcnn_b200_plan* p, uint32_t B, bool have_replicas) {
 	GridParams gp = p->grid;
 	gp.n_replicas = N_REPLICAS; gp.rep_entries = 0;
-	if (!have_replicas || B < REPLICATE_MIN_BATCH) return gp;
+	static const bool never = getenv("TCNN_B200_NO_REPLICAS") != nullptr; // development switch (tests/dev/parity_probe.py): plain fp16 reductions on every level
+	if (!have_replicas || B < REPLICATE_MIN_BATCH || never) return gp;
 	for (uint32_t l = 0; l < gp.n_levels; ++l) {
 		if (gp.level[l].size <= REPLICATE_MAX_ENTRIES) {
 			gp.level[l].replicated = 1;
@@ -185,6 +188,16 @@ static void parse_optimizer(tcnn_b200_plan* p, const jsonmini::Value& o) {
 	p->adabound = o.boolean("adabound", p->adabound);
 	p->weight_clip = (float)o.number("clipping_magnitude", p->weight_clip);
 	p->non_matrix_lr_factor = (float)o.number("non_matrix_learning_rate_factor", p->non_matrix_lr_factor);
+	p->optimize_matrix_params = o.boolean("optimize_matrix_params", p->optimize_matrix_params);
+	p->optimize_non_matrix_params = o.boolean("optimize_non_matrix_params", p->optimize_non_matrix_params);
+	// anything else would be silently ignored: a misspelt key must not train with defaults
+	static const char* known[] = {"otype", "learning_rate", "beta1", "beta2", "epsilon", "l2_reg", "relative_decay", "absolute_decay", "adabound",
+		"clipping_magnitude", "non_matrix_learning_rate_factor", "optimize_matrix_params", "optimize_non_matrix_params"};
+	for (const std::string& key : o.keys()) {
+		bool ok = false;
+		for (const char* k : known) ok |= key == k;
+		CHECK(ok, "Adam: unknown optimizer key '" + key + "' (optimizers/adam.h:210-258)");
+	}
 }
 
 // ---- plan ------------------------------------------------------------------------------------------
@@ -294,6 +307,9 @@ extern "C" int tcnn_b200_plan_create(const char* json_utf8, uint32_t n_input_dim
 			uint32_t tile = 1;
 			for (uint32_t d = 0; d < n_input_dims; ++d) tile *= in.base_resolution;     // powi(base_resolution, N_POS_DIMS)
 			n = std::min(n, tile);
+			// every kernel reads / reduces aligned 16-byte slots of the level tables: level offsets must stay multiples of 8 entries.
+			// The reference accepts base_resolution^D that is not (e.g. 5 or 6 in 2-D); here that is an error, not a misaligned access.
+			CHECK(n % 8 == 0, "TiledGrid: base_resolution^n_input_dims (" + std::to_string(tile) + ") must be a multiple of 8 in this build (level tables are accessed in aligned 16-byte slots)");
 		}
 		in.level_offset[l] = offset;
 		CHECK((uint64_t)offset + n < (1ull << 32) / in.n_features_per_level, "GridEncoding: more than 2^32 grid parameters");
@@ -520,6 +536,19 @@ extern "C" int tcnn_b200_cast_params(void* stream_, uint64_t n, const float* par
 	CHECK(params_fp32 && params_fp16, "null argument");
 	cast_f32_to_f16_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream_>>>(n, params_fp32, (__half*)params_fp16);
 	launch_check("cast_f32_to_f16_kernel");
+	API_END
+}
+
+// generate_random_uniform<float> (random.h:39-71) for the hosts of the C++ facade (samples draw their training batches with it):
+// element i + n_threads * j is the j-th draw of the generator advanced by 4 i, n_threads = 128 * ceil(ceil(n / 4) / 128).
+extern "C" int tcnn_b200_generate_random_uniform(void* stream, uint64_t rng_state, uint64_t rng_inc, uint64_t n, float* out, float lower, float upper) {
+	API_BEGIN
+	CHECK(out || n == 0, "null output");
+	CHECK(n < (1ull << 32), "at most 2^32 - 1 elements per call");
+	if (n == 0) return 0;
+	const uint32_t n32 = (uint32_t)n, n_threads = next_multiple_u32((n32 + 3) / 4, 128);
+	init_uniform_kernel<<<(n32 + 255) / 256, 256, 0, (cudaStream_t)stream>>>(n32, n_threads, rng_state, rng_inc, 0, lower, upper, out);
+	launch_check("init_uniform_kernel");
 	API_END
 }
 
@@ -1145,6 +1174,7 @@ static AdamArgs adam_args(const tcnn_b200_plan* plan, float grad_divisor, uint32
 	}
 	a.weight_clip = plan->weight_clip;
 	a.non_matrix_lr_factor = plan->non_matrix_lr_factor;
+	a.optimize_matrix = plan->optimize_matrix_params ? 1 : 0; a.optimize_non_matrix = plan->optimize_non_matrix_params ? 1 : 0;
 	a.zero_grads = zero_grid_grads;
 	int e = 0;
 	const float mant = std::frexp(grad_divisor, &e);
@@ -1311,6 +1341,7 @@ extern "C" int tcnn_b200_dp_shard(const tcnn_b200_plan* plan, uint32_t rank, uin
 	API_END
 }
 extern "C" uint32_t tcnn_b200_dp_flag_bytes(void) { return DP_FLAG_WORDS * 4; }
+extern "C" uint32_t tcnn_b200_dp_flag_error_word(void) { return DP_FLAG_ERROR; }
 
 extern "C" int tcnn_b200_training_step_dp(const tcnn_b200_plan* plan, void* stream_, uint32_t B, const float* x, const float* target,
 	float loss_scale, uint32_t adam_step_count, float* params_fp32_shard, float* first_moments_shard, float* second_moments_shard,
@@ -1326,6 +1357,10 @@ extern "C" int tcnn_b200_training_step_dp(const tcnn_b200_plan* plan, void* stre
 	CHECK(plan->enc_kind == ENC_GRID, "the data-parallel step is built for the grid encoding (a parameter-free encoding has ~100 KB of gradients: all-reduce them)");
 	DpComm c{};
 	c.rank = comm->rank; c.world = comm->world_size; c.epoch = comm->epoch;
+	{ // how long a rank waits for its peers inside the kernel before it gives up (sets the error word, does not trap)
+		static const double timeout_s = [] { const char* e = getenv("TCNN_B200_DP_TIMEOUT_S"); const double v = e ? atof(e) : 0.0; return v > 0.0 ? v : 600.0; }();
+		c.timeout_ns = (uint64_t)(timeout_s * 1e9);
+	}
 	for (uint32_t r = 0; r < c.world; ++r) {
 		CHECK(comm->peer_grads[r] && comm->peer_params[r] && comm->peer_flags[r], "null peer buffer");
 		c.peer_grads[r] = (__half*)comm->peer_grads[r]; c.peer_params[r] = (__half*)comm->peer_params[r]; c.peer_flags[r] = (uint32_t*)comm->peer_flags[r];

@@ -67,6 +67,7 @@ _SIGNATURES = {
     "tcnn_b200_workspace_bytes": (C.c_size_t, [_P, C.c_uint32]),
     "tcnn_b200_init_params": (C.c_int, [_P, _P, C.c_uint64, C.c_int, _P]),
     "tcnn_b200_cast_params": (C.c_int, [_P, C.c_uint64, _P, _P]),
+    "tcnn_b200_generate_random_uniform": (C.c_int, [_P, C.c_uint64, C.c_uint64, C.c_uint64, _P, C.c_float, C.c_float]),
     "tcnn_b200_encode_forward": (C.c_int, [_P, _P, C.c_uint32, _P, _P, _P]),
     "tcnn_b200_encode_backward": (C.c_int, [_P, _P, C.c_uint32, _P, _P, _P, C.c_int, _P]),
     "tcnn_b200_encode_backward_noalloc": (C.c_int, [_P, _P, C.c_uint32, _P, _P, _P, C.c_int]),
@@ -82,6 +83,7 @@ _SIGNATURES = {
     "tcnn_b200_adam_step_range": (C.c_int, [_P, _P, C.c_float, C.c_uint32, _P, _P, _P, _P, _P, _P, C.c_int, C.c_uint64, C.c_uint64]),
     "tcnn_b200_dp_shard": (C.c_int, [_P, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
     "tcnn_b200_dp_flag_bytes": (C.c_uint32, []),
+    "tcnn_b200_dp_flag_error_word": (C.c_uint32, []),
     "tcnn_b200_training_step_dp": (C.c_int, [_P, _P, C.c_uint32, _P, _P, C.c_float, C.c_uint32, _P, _P, _P, _P, _P, _P, _P, C.POINTER(DpComm)]),
     "tcnn_b200_training_step": (C.c_int, [_P, _P, C.c_uint32, _P, _P, C.c_float, C.c_uint32, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "tcnn_b200_profile_enable": (C.c_int, [_P, C.c_int]),

@@ -7,6 +7,7 @@ from __future__ import annotations
 
 import json
 import warnings
+import weakref
 
 import torch
 
@@ -16,6 +17,9 @@ from ._lib import check, ptr
 
 def _stream_ptr():
     return _lib.C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+_live_modules = weakref.WeakSet()  # for free_temporary_memory(): every NativeModule that may hold a cached workspace
 
 
 class NativeModule:
@@ -32,6 +36,7 @@ class NativeModule:
         self.info = _lib.Info()
         check(self.lib.tcnn_b200_plan_info(self.handle, _lib.C.byref(self.info)))
         self._ws = {}
+        _live_modules.add(self)
 
     def __del__(self):
         try:
@@ -62,10 +67,16 @@ class NativeModule:
         n = int(self.lib.tcnn_b200_workspace_bytes(self.handle, batch_size))
         if fresh:
             return torch.empty(n, dtype=torch.uint8, device=device)
-        key = (batch_size, str(device))
-        if key not in self._ws:
-            self._ws[key] = torch.empty(n, dtype=torch.uint8, device=device)
-        return self._ws[key]
+        # ONE grow-only scratch buffer per (device, stream), like the reference's per-stream arena (gpu_memory.h:699-720): callers with
+        # varying batch sizes (NeRF ray batches) re-use it instead of piling up one buffer per size; free_temporary_memory() drops it
+        key = (str(device), torch.cuda.current_stream(device).cuda_stream if torch.device(device).type == "cuda" else 0)
+        ws = self._ws.get(key)
+        if ws is None or ws.numel() < n:
+            self._ws[key] = ws = torch.empty(n, dtype=torch.uint8, device=device)
+        return ws
+
+    def free_workspaces(self):
+        self._ws.clear()
 
     def initial_params(self, seed: int, device="cuda", trainer_seeding: bool = False) -> torch.Tensor:
         p = torch.empty(self.n_params(), dtype=torch.float32, device=device)
@@ -251,8 +262,11 @@ class Encoding(Module):
 
 
 def free_temporary_memory():
-    """tcnn.free_temporary_memory (modules.py:77-81): the C ABI owns no temporaries; workspaces are torch tensors."""
+    """tcnn.free_temporary_memory (modules.py:77-81 -> free_all_gpu_memory_arenas): the C ABI owns no temporaries; the scratch buffers are
+    torch tensors cached per module and stream (NativeModule.workspace) and are released here."""
     import gc
 
+    for m in list(_live_modules):
+        m.free_workspaces()
     gc.collect()
     torch.cuda.empty_cache()

@@ -20,7 +20,10 @@ from ._lib import check, ptr
 from .modules import NativeModule, _stream_ptr
 from .parallel import PeerMemory, allreduce_gradients, grad_divisor
 
-LOSS_SCALE = 128.0  # default_loss_scale<__half>(), common.h:229-233; trainer.h:174
+import os
+
+# default_loss_scale<__half>(), common.h:229-233; trainer.h:174.  TCNN_B200_LOSS_SCALE: development override (tests/dev/parity_probe.py)
+LOSS_SCALE = float(os.environ.get("TCNN_B200_LOSS_SCALE", "128"))
 
 
 class Trainer:
@@ -139,8 +142,18 @@ class Trainer:
             ptr(self.first_moments), ptr(self.second_moments), ptr(self.param_steps), 1))
         self._grid_grads_clean = True
 
+    def check_peers(self):
+        """Data-parallel peer mode: raise if a rank gave up waiting for its peers inside the exchange kernel (the kernel sets an
+        error word instead of trapping; TCNN_B200_DP_TIMEOUT_S, default 600 s).  Synchronises."""
+        if self.peer_memory is not None:
+            word = int(self.lib.tcnn_b200_dp_flag_error_word())
+            if int(self.peer_memory.flags[word].item()) != 0:
+                raise RuntimeError("tcnn_b200: a data-parallel peer did not reach the gradient exchange in time (TCNN_B200_DP_TIMEOUT_S); "
+                                   "this rank's parameters are stale - restart from a snapshot")
+
     # trainer.h:205-207 (synchronises, like the reference's reduce_sum + D2H)
     def loss(self) -> float:
+        self.check_peers()
         if self.world_size > 1:  # mean over the global batch; collective: call on every rank
             v = self.loss_value.clone()
             torch.distributed.all_reduce(v, group=self.process_group)
