@@ -138,7 +138,7 @@ def run_reference(args, cfg):
     ref = os.path.join(ROOT, "oracle", "_ref", "ref_driver")
     line = {"impl": "reference", "metric": METRIC, "unit": "samples/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "note": "reference is single-GPU; value is its 1-GPU number for every --gpus"}}
+            "config": config_dict(args.gpus), "reference_note": "the reference is single-GPU: its 1-GPU number is reported for every --gpus"}
     cpu = cpu_baseline_port(cfg)
     have_gpu = False
     try:
@@ -169,12 +169,66 @@ def run_reference(args, cfg):
     print(json.dumps(line), flush=True)
 
 
+def config_dict(world, dp_mode="peer"):
+    """The `config` object of the JSON line: identical in both arms (ours and --impl reference) for the same --gpus."""
+    return {"workload": WORKLOAD, "batch_per_gpu": BATCH, "global_batch": BATCH * world, "parallelism": f"dp{world}",
+            "l2": "no flush: one step streams ~0.45 GB of parameter/optimizer state (> 126 MB L2) and cycles 4 distinct resident batches"}
+
+
 DP_NOTE = {
     "peer": "one fused kernel per step: sum of this rank's gradient shard over all ranks (NVSwitch multimem.ld_reduce; plain peer loads at 2 GPUs) -> Adam on the shard -> new fp16 parameters to all ranks (multimem.st / peer stores), both barriers in-kernel",
     "peer-mc": "one fused kernel per step: NVSwitch multimem.ld_reduce of this rank's gradient shard -> Adam on the shard -> multimem.st of the new fp16 parameters to all ranks, both barriers in-kernel",
     "peer-p2p": "one fused kernel per step: peer loads of this rank's gradient shard from all ranks -> Adam on the shard -> peer stores of the new fp16 parameters, both barriers in-kernel",
     "allreduce": "fp16 NCCL all-reduce of the 22.4 MB gradient buffer per step, replicated Adam",
 }
+
+
+def run_dp_check(cfg, dev, rank, world, dp_mode):
+    """Correctness of the multi-rank step, printed with the bench line: (1) after 50 data-parallel steps on a fixed global batch
+    sequence every rank holds bit-identical fp16 parameters; (2) the loss of those steps equals what ONE rank gets on the same
+    global batches (run live on rank 0 with a one-rank trainer), up to the summation order of fp16 gradients."""
+    import hashlib
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    import tinycudann as tcnn
+    from tests import common
+    from tinycudann import parallel
+
+    steps, gb = 50, 1 << 16
+    solo_group = dist.new_group([0])  # collective: every rank creates it, rank 0 trains alone in it
+    kw = {"dp_mode": dp_mode.split("-")[0], "use_multicast": {"peer": None, "peer-p2p": False, "peer-mc": True}.get(dp_mode)}
+    tr = tcnn.create_from_config(N_IN, N_OUT, cfg, seed=1337, device=dev, **kw).trainer
+    lo, hi = parallel.shard_bounds(gb, rank, world)
+    losses = []
+    for s in range(steps):
+        x_np, t_np = common.synth_inputs(gb, N_IN, N_OUT, seed=500 + s)
+        tr.training_step(torch.from_numpy(x_np[lo:hi]).to(dev), torch.from_numpy(t_np[lo:hi]).to(dev))
+        if s >= steps - 5:
+            losses.append(tr.loss())  # mean over ranks = loss of the global batch
+    torch.cuda.synchronize()
+    digest = hashlib.sha256(tr.params.cpu().numpy().tobytes()).digest()[:8]
+    mine = torch.tensor(list(digest), dtype=torch.int32, device=dev)
+    every = [torch.zeros_like(mine) for _ in range(world)]
+    dist.all_gather(every, mine)
+    identical = all(torch.equal(e, every[0]) for e in every)
+    out = None
+    if rank == 0:
+        one = tcnn.create_from_config(N_IN, N_OUT, cfg, seed=1337, device=dev, process_group=solo_group, dp_mode="allreduce").trainer
+        ref = []
+        for s in range(steps):
+            x_np, t_np = common.synth_inputs(gb, N_IN, N_OUT, seed=500 + s)
+            one.training_step(torch.from_numpy(x_np).to(dev), torch.from_numpy(t_np).to(dev))
+            if s >= steps - 5:
+                ref.append(float(one.loss_value.item()))
+        a, b = float(np.mean(losses)), float(np.mean(ref))
+        out = {"params_identical": bool(identical), "params_sha256_64": digest.hex(), "steps": steps, "global_batch": gb,
+               "loss": a, "loss_1rank": b, "rel": abs(a - b) / b,
+               "what": "mean training loss of steps 46-50 on a fixed global batch sequence: N ranks (sharded) vs one rank (whole batch), same seed"}
+    dist.barrier()
+    return out
 
 
 def main():
@@ -272,7 +326,9 @@ def main():
     ev_loss = [torch.cuda.Event() for _ in range(2)]
     ev_loss_copied = [torch.cuda.Event() for _ in range(2)]
 
-    def train_e2e(i):
+    E2E_WARMUP = 6  # untimed iterations of the same loop in front: the first, un-overlapped H2D copy is not part of a 20-step measurement
+
+    def train_e2e(i, last=False):
         k = i % 2
         if i == 0:
             enqueue_copy(0)
@@ -288,7 +344,7 @@ def main():
             d2h_stream.wait_event(ev_loss[k])
             hlosses[i % 4096: i % 4096 + 1].copy_(loss_bufs[k], non_blocking=True)
             ev_loss_copied[k].record(d2h_stream)
-        if i == e2e_steps - 1:
+        if last:
             main.wait_event(ev_loss_copied[k])  # the last read-back ends inside the timed region
 
     for i in range(args.warmup):
@@ -309,7 +365,10 @@ def main():
     for ev in ev_free:
         ev.record(torch.cuda.current_stream())
     e2e_steps = min(args.e2e_steps, args.steps)
-    e2e_ms = timed(e2e_steps, train_e2e) / e2e_steps
+    for i in range(E2E_WARMUP):
+        train_e2e(i)
+    e2e_ms = timed(e2e_steps, lambda i: train_e2e(E2E_WARMUP + i, last=(i == e2e_steps - 1))) / e2e_steps
+    h2d_gbs = BATCH * 4 * (N_IN + N_OUT) / (e2e_ms * 1e-3) / 1e9  # what the copy stream must sustain per rank to keep up with the step
     tr.loss_value = loss_bufs[0]
     e2e_value = BATCH * world / (e2e_ms * 1e-3)
 
@@ -336,17 +395,19 @@ def main():
     except Exception:  # noqa: BLE001
         pass
 
+    dp_check = None
+    if world > 1:
+        dp_check = run_dp_check(cfg, dev, rank, world, args.dp_mode)
+
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16",
             "data": "synthetic",
-            "config": {"workload": WORKLOAD, "batch_per_gpu": BATCH, "global_batch": BATCH * world, "parallelism": f"dp{world}",
-                       "l2": "no flush: one step streams ~0.45 GB of parameter/optimizer state (> 126 MB L2) and cycles 4 distinct resident batches",
-                       "gradient_exchange": DP_NOTE.get(args.dp_mode, args.dp_mode) if world > 1 else "none"},
+            "config": config_dict(world), "gradient_exchange": DP_NOTE.get(args.dp_mode, args.dp_mode) if world > 1 else "none",
             "clocks": clk.summary(),
             "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": BATCH * 4 * (N_IN + N_OUT), "d2h_bytes_per_step": 4,
-                    "ms_per_step": e2e_ms, "steps": e2e_steps, "how": "pinned host batch -> H2D on a copy stream (double-buffered, overlaps the previous step) -> training_step -> async 4-byte loss D2H on its own stream (two loss buffers); one host sync at the end"},
+                    "ms_per_step": e2e_ms, "steps": e2e_steps, "warmup": E2E_WARMUP, "h2d_gb_per_s_per_rank": h2d_gbs, "how": "pinned host batch -> H2D on a copy stream (double-buffered, overlaps the previous step) -> training_step -> async 4-byte loss D2H on its own stream (two loss buffers); one host sync at the end"},
             "gpu_launches": int(sum(launches_per_step.values()) * args.steps),
             "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
                          "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": per_kernel_bytes[dominant],
@@ -356,6 +417,8 @@ def main():
             "inference": {"value": BATCH * world / (inf_ms * 1e-3), "unit": "samples/s", "ms_per_batch": inf_ms,
                           "what": "Network::inference, fp32 output, inputs resident, batch 2^18 per GPU"},
         }
+        if dp_check is not None:
+            line["dp_check"] = dp_check
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_port(cfg)
         print(json.dumps(line), flush=True)

@@ -35,13 +35,23 @@ struct GridLevel {
 	uint32_t replicated;    // backward: scatter into one of n_replicas private copies (coarse, heavily contended levels)
 	uint32_t rep_offset;    // first entry of this level inside one replica
 	uint64_t magic;         // ceil(2^64 / size): index % size without a division (fastmod_u32)
+	uint32_t mode;          // LEVEL_HASH / LEVEL_DENSE_POW2 / LEVEL_DENSE_MOD: which of the three index computations applies (uniform per level)
+	uint32_t reserved;
 };
+enum LevelMode : uint32_t { LEVEL_HASH = 0, LEVEL_DENSE_POW2 = 1, LEVEL_DENSE_MOD = 2 };
 
 // a % d for 32-bit a, d with M = ceil(2^64 / d) (Lemire, Kaser, Kurz: "Faster remainder by direct computation", exact for all 32-bit
 // operands).  The dense levels' sizes are not powers of two (grid_index takes `index % hashmap_size`, common_device.h:706); a
 // hardware-less 32-bit modulo costs ~20 instructions and a branch around it, this costs four multiplies and no branch.
 __host__ __device__ __forceinline__ uint64_t fastmod_magic(uint32_t d) { return 0xFFFFFFFFFFFFFFFFull / d + 1; }
-__device__ __forceinline__ uint32_t fastmod_u32(uint32_t a, uint64_t M, uint32_t d) { return (uint32_t)__umul64hi(M * a, d); }
+__device__ __forceinline__ uint32_t fastmod_u32(uint32_t a, uint64_t M, uint32_t d) {
+	// low 64 bits of M * a, then the high 32 bits of (that * d) >> 32: four 32-bit multiplies
+	const uint32_t mlo = (uint32_t)M, mhi = (uint32_t)(M >> 32);
+	const uint64_t t = (uint64_t)mlo * a;
+	const uint32_t l_lo = (uint32_t)t, l_hi = (uint32_t)(t >> 32) + mhi * a;
+	const uint64_t p = (uint64_t)l_lo * d;
+	return (uint32_t)(((uint64_t)l_hi * d + (p >> 32)) >> 32);
+}
 
 struct GridParams {
 	uint32_t n_levels;
@@ -94,6 +104,28 @@ __device__ __forceinline__ uint32_t grid_index_dev(const GridLevel& lv, const ui
 	return fastmod_u32(index, lv.magic, lv.size);
 }
 
+// Entry indices of all 2^D corners of a cell (corner c: bit d of c selects cell[d] + 1), for a level whose index rule is known at
+// compile time.  Same results as grid_index_dev per corner (uint32 wrap included), with the shared terms computed once:
+// hash: (cell[d] + 1) * prime[d] = cell[d] * prime[d] + prime[d] (mod 2^32); dense: one base index plus stride sums.
+template <int D, uint32_t MODE>
+__device__ __forceinline__ void corner_indices(const GridLevel& lv, const uint32_t (&cell)[D], uint32_t (&idx)[1 << D]) {
+	constexpr uint32_t primes[7] = {1u, 2654435761u, 805459861u, 3674653429u, 2097192037u, 1434869437u, 2165219737u};
+	uint32_t term[D][2];
+#pragma unroll
+	for (int d = 0; d < D; ++d) {
+		const uint32_t m = MODE == LEVEL_HASH ? primes[d] : lv.stride[d]; // stride[d] == 0 for dims the reference's loop never reaches
+		term[d][0] = cell[d] * m;
+		term[d][1] = term[d][0] + m;
+	}
+#pragma unroll
+	for (int c = 0; c < (1 << D); ++c) {
+		uint32_t v = term[0][c & 1];
+#pragma unroll
+		for (int d = 1; d < D; ++d) v = MODE == LEVEL_HASH ? (v ^ term[d][(c >> d) & 1]) : (v + term[d][(c >> d) & 1]);
+		idx[c] = MODE == LEVEL_DENSE_MOD ? fastmod_u32(v, lv.magic, lv.size) : (v & (lv.size - 1));
+	}
+}
+
 template <int F> struct FeatVec;
 template <> struct FeatVec<1> { using type = __half; };
 template <> struct FeatVec<2> { using type = __half2; };
@@ -117,11 +149,100 @@ __device__ __forceinline__ void load_position(const float* __restrict__ x, size_
 #ifndef TCNN_B200_GATHER_QUAD
 #define TCNN_B200_GATHER_QUAD 1
 #endif
+// One level of encode_chunk for a level whose index rule is a template parameter (uniform over the warp, see scatter_level).
+// Writes the level's F interpolated halfs to out[0 .. F/2).
+template <int D, int F, uint32_t MODE>
+__device__ __forceinline__ void encode_level(const GridParams& gp, const GridLevel& lv, const __half* __restrict__ grid, const float (&x)[D], __half2* out) {
+	constexpr int NC = 1 << D;
+	float frac[D]; uint32_t cell[D];
+#pragma unroll
+	for (int d = 0; d < D; ++d) pos_fract_dev(x[d], lv.scale, frac[d], cell[d]);
+	if (gp.smoothstep) {
+#pragma unroll
+		for (int d = 0; d < D; ++d) frac[d] = smoothstep_dev(frac[d]);
+	}
+	const uint8_t* table = reinterpret_cast<const uint8_t*>(grid + (size_t)lv.offset * F);
+	// issue every gather of the level before the fp16 fma chain (grid.h:146-163 order: corner 0..2^D-1)
+	uint32_t idx[NC]; float w[NC];
+	corner_indices<D, MODE>(lv, cell, idx);
+#pragma unroll
+	for (int c = 0; c < NC; ++c) {
+		float weight = 1.0f;
+#pragma unroll
+		for (int d = 0; d < D; ++d) weight *= (c & (1 << d)) == 0 ? 1.0f - frac[d] : frac[d];
+		w[c] = weight;
+	}
+	if constexpr (F == 2) {
+		// Corners c and c+1 differ in dim 0 only.  For even cells their entries are the two halves of one aligned 8-byte
+		// slot on every level (dense: index and index+1; coherent-prime hash: prime[0] = 1 so the indices differ in bit
+		// 0 only), so one 8-byte load serves both; otherwise the second corner gets its own (predicated) load.
+		__half2 val[NC];
+#pragma unroll
+		for (int c = 0; c < NC; c += 2) {
+#if TCNN_B200_GATHER_QUAD
+			// the gather is bound by L1 tag lookups (one per lane and load): a 16-byte load of the aligned slot
+			// {idx & ~3 .. idx | 3} also brings the dim-0 neighbour unless idx % 4 == 3 -> 1.25 lookups per corner pair
+			const uint32_t l0 = idx[c] & 3u, l1 = idx[c + 1] & 3u;
+			const bool together = ((idx[c] ^ idx[c + 1]) & ~3u) == 0u;
+			const uint4 a = __ldg(reinterpret_cast<const uint4*>(table + ((idx[c] >> 2) << 4)));
+			const uint32_t own = l0 == 0 ? a.x : l0 == 1 ? a.y : l0 == 2 ? a.z : a.w;
+			uint32_t other = l1 == 0 ? a.x : l1 == 1 ? a.y : l1 == 2 ? a.z : a.w;
+			if (!together) other = __ldg(reinterpret_cast<const uint32_t*>(table + (idx[c + 1] << 2)));
+#else
+			const bool paired = ((idx[c] ^ idx[c + 1]) == 1u);
+			const uint2 a = __ldg(reinterpret_cast<const uint2*>(table + ((idx[c] >> 1) << 3)));
+			uint32_t own = (idx[c] & 1u) ? a.y : a.x, other = (idx[c] & 1u) ? a.x : a.y;
+			if (!paired) other = __ldg(reinterpret_cast<const uint32_t*>(table + (idx[c + 1] << 2)));
+#endif
+			val[c] = *reinterpret_cast<const __half2*>(&own);
+			val[c + 1] = *reinterpret_cast<const __half2*>(&other);
+		}
+		__half2 r = __floats2half2_rn(0.f, 0.f);
+#pragma unroll
+		for (int c = 0; c < NC; ++c) r = __hfma2(__half2half2(__float2half(w[c])), val[c], r);
+		out[0] = r;
+	} else if constexpr (F == 4) {
+		uint2 val[NC];
+#pragma unroll
+		for (int c = 0; c < NC; c += 2) { // same pairing with 16-byte slots
+			const bool paired = ((idx[c] ^ idx[c + 1]) == 1u);
+			const uint4 a = __ldg(reinterpret_cast<const uint4*>(table + ((idx[c] >> 1) << 4)));
+			val[c] = (idx[c] & 1u) ? make_uint2(a.z, a.w) : make_uint2(a.x, a.y);
+			val[c + 1] = (idx[c] & 1u) ? make_uint2(a.x, a.y) : make_uint2(a.z, a.w);
+			if (!paired) val[c + 1] = __ldg(reinterpret_cast<const uint2*>(table + (idx[c + 1] << 3)));
+		}
+		__half2 r0 = __floats2half2_rn(0.f, 0.f), r1 = r0;
+#pragma unroll
+		for (int c = 0; c < NC; ++c) {
+			const __half2 wh = __half2half2(__float2half(w[c]));
+			r0 = __hfma2(wh, *reinterpret_cast<__half2*>(&val[c].x), r0);
+			r1 = __hfma2(wh, *reinterpret_cast<__half2*>(&val[c].y), r1);
+		}
+		out[0] = r0; out[1] = r1;
+	} else if constexpr (F == 8) {
+		uint4 val[NC];
+#pragma unroll
+		for (int c = 0; c < NC; ++c) val[c] = __ldg(reinterpret_cast<const uint4*>(table + (idx[c] << 4)));
+		__half2 r[4];
+#pragma unroll
+		for (int k = 0; k < 4; ++k) r[k] = __floats2half2_rn(0.f, 0.f);
+#pragma unroll
+		for (int c = 0; c < NC; ++c) {
+			const __half2 wh = __half2half2(__float2half(w[c]));
+			const __half2* v = reinterpret_cast<const __half2*>(&val[c]);
+#pragma unroll
+			for (int k = 0; k < 4; ++k) r[k] = __hfma2(wh, v[k], r[k]);
+		}
+#pragma unroll
+		for (int k = 0; k < 4; ++k) out[k] = r[k];
+	}
+}
+
 // Encode the levels of one 16-byte chunk for one sample.  Returns 8 halfs packed in a uint4.
 template <int D, int F>
 __device__ __forceinline__ uint4 encode_chunk(const GridParams& gp, const __half* __restrict__ grid, const float (&x)[D], uint32_t chunk) {
+	static_assert(F == 2 || F == 4 || F == 8, "packed half2 features");
 	constexpr int LEVELS_PER_CHUNK = 8 / F;
-	constexpr int NC = 1 << D;
 	union { uint4 v; __half2 h2[4]; } out;
 	out.v = make_uint4(0, 0, 0, 0);
 #pragma unroll
@@ -129,96 +250,10 @@ __device__ __forceinline__ uint4 encode_chunk(const GridParams& gp, const __half
 		const uint32_t level = chunk * LEVELS_PER_CHUNK + s;
 		if (level >= gp.n_levels) break; // padding columns stay zero (grid.h:749-759 pads with zeros too)
 		const GridLevel& lv = gp.level[level];
-		float frac[D]; uint32_t cell[D];
-#pragma unroll
-		for (int d = 0; d < D; ++d) pos_fract_dev(x[d], lv.scale, frac[d], cell[d]);
-		if (gp.smoothstep) {
-#pragma unroll
-			for (int d = 0; d < D; ++d) frac[d] = smoothstep_dev(frac[d]);
-		}
-		const __half* table = grid + (size_t)lv.offset * F;
-		// issue every gather of the level before the fp16 fma chain (grid.h:146-163 order: corner 0..2^D-1)
-		uint32_t idx[NC]; float w[NC];
-#pragma unroll
-		for (int c = 0; c < NC; ++c) {
-			float weight = 1.0f; uint32_t pg[D];
-#pragma unroll
-			for (int d = 0; d < D; ++d) {
-				if ((c & (1 << d)) == 0) { weight *= 1.0f - frac[d]; pg[d] = cell[d]; }
-				else { weight *= frac[d]; pg[d] = cell[d] + 1u; }
-			}
-			idx[c] = grid_index_dev<D>(lv, pg);
-			w[c] = weight;
-		}
-		if constexpr (F == 2) {
-			// Corners c and c+1 differ in dim 0 only.  For even cells their entries are the two halves of one aligned 8-byte
-			// slot on every level (dense: index and index+1; coherent-prime hash: prime[0] = 1 so the indices differ in bit
-			// 0 only), so one 8-byte load serves both; otherwise the second corner gets its own (predicated) load.
-			__half2 val[NC];
-#pragma unroll
-			for (int c = 0; c < NC; c += 2) {
-#if TCNN_B200_GATHER_QUAD
-				// the gather is bound by L1 tag lookups (one per lane and load): a 16-byte load of the aligned slot
-				// {idx & ~3 .. idx | 3} also brings the dim-0 neighbour unless idx % 4 == 3 -> 1.25 lookups per corner pair
-				const uint32_t l0 = idx[c] & 3u, l1 = idx[c + 1] & 3u;
-				const bool together = ((idx[c] ^ idx[c + 1]) & ~3u) == 0u;
-				const uint4 a = __ldg(reinterpret_cast<const uint4*>(table) + (idx[c] >> 2));
-				const uint32_t own = l0 == 0 ? a.x : l0 == 1 ? a.y : l0 == 2 ? a.z : a.w;
-				uint32_t other = l1 == 0 ? a.x : l1 == 1 ? a.y : l1 == 2 ? a.z : a.w;
-				if (!together) other = __ldg(reinterpret_cast<const uint32_t*>(table) + idx[c + 1]);
-#else
-				const bool paired = ((idx[c] ^ idx[c + 1]) == 1u);
-				const uint2 a = __ldg(reinterpret_cast<const uint2*>(table) + (idx[c] >> 1));
-				uint32_t own = (idx[c] & 1u) ? a.y : a.x, other = (idx[c] & 1u) ? a.x : a.y;
-				if (!paired) other = __ldg(reinterpret_cast<const uint32_t*>(table) + idx[c + 1]);
-#endif
-				val[c] = *reinterpret_cast<const __half2*>(&own);
-				val[c + 1] = *reinterpret_cast<const __half2*>(&other);
-			}
-			__half2 r = __floats2half2_rn(0.f, 0.f);
-#pragma unroll
-			for (int c = 0; c < NC; ++c) r = __hfma2(__half2half2(__float2half(w[c])), val[c], r);
-			out.h2[s] = r;
-		} else if constexpr (F == 4) {
-			uint2 val[NC];
-#pragma unroll
-			for (int c = 0; c < NC; c += 2) { // same pairing with 16-byte slots
-				const bool paired = ((idx[c] ^ idx[c + 1]) == 1u);
-				const uint4 a = __ldg(reinterpret_cast<const uint4*>(table) + (idx[c] >> 1));
-				val[c] = (idx[c] & 1u) ? make_uint2(a.z, a.w) : make_uint2(a.x, a.y);
-				val[c + 1] = (idx[c] & 1u) ? make_uint2(a.x, a.y) : make_uint2(a.z, a.w);
-				if (!paired) val[c + 1] = __ldg(reinterpret_cast<const uint2*>(table) + idx[c + 1]);
-			}
-			__half2 r0 = __floats2half2_rn(0.f, 0.f), r1 = r0;
-#pragma unroll
-			for (int c = 0; c < NC; ++c) {
-				const __half2 wh = __half2half2(__float2half(w[c]));
-				r0 = __hfma2(wh, *reinterpret_cast<__half2*>(&val[c].x), r0);
-				r1 = __hfma2(wh, *reinterpret_cast<__half2*>(&val[c].y), r1);
-			}
-			out.h2[2 * s] = r0; out.h2[2 * s + 1] = r1;
-		} else if constexpr (F == 8) {
-			uint4 val[NC];
-#pragma unroll
-			for (int c = 0; c < NC; ++c) val[c] = __ldg(reinterpret_cast<const uint4*>(table) + idx[c]);
-			__half2 r[4];
-#pragma unroll
-			for (int k = 0; k < 4; ++k) r[k] = __floats2half2_rn(0.f, 0.f);
-#pragma unroll
-			for (int c = 0; c < NC; ++c) {
-				const __half2 wh = __half2half2(__float2half(w[c]));
-				const __half2* v = reinterpret_cast<const __half2*>(&val[c]);
-#pragma unroll
-				for (int k = 0; k < 4; ++k) r[k] = __hfma2(wh, v[k], r[k]);
-			}
-#pragma unroll
-			for (int k = 0; k < 4; ++k) out.h2[k] = r[k];
-		} else { // F == 1: scalar __hfma (vec.h:210-212)
-			__half r = __float2half(0.f);
-#pragma unroll
-			for (int c = 0; c < NC; ++c) r = __hfma(__float2half(w[c]), table[idx[c]], r);
-			reinterpret_cast<__half*>(&out.v)[s] = r;
-		}
+		__half2* o = &out.h2[s * (F / 2)];
+		if (lv.mode == LEVEL_HASH) encode_level<D, F, LEVEL_HASH>(gp, lv, grid, x, o);
+		else if (lv.mode == LEVEL_DENSE_POW2) encode_level<D, F, LEVEL_DENSE_POW2>(gp, lv, grid, x, o);
+		else encode_level<D, F, LEVEL_DENSE_MOD>(gp, lv, grid, x, o);
 	}
 	return out.v;
 }
@@ -249,84 +284,104 @@ __global__ void __launch_bounds__(256) grid_forward_kernel(const __grid_constant
 #ifndef TCNN_B200_SCATTER_QUAD
 #define TCNN_B200_SCATTER_QUAD 1
 #endif
+// One level of scatter_chunk, for a level whose index rule (LevelMode) is a template parameter: the rule is uniform over the
+// warp, so scatter_chunk branches once per level and the body carries one index computation instead of a predicated mix of all.
+// g0 / g1: this level's F gradient halfs (g1 only for F >= 4, packed pairs 2, 3 in gx for F == 8).
+template <int D, int F, uint32_t MODE, bool SMOOTH>
+__device__ __forceinline__ void scatter_level(const GridParams& gp, const GridLevel& lv, const float (&p)[D], const __half2 (&g)[F / 2],
+	__half* __restrict__ grid_grad, __half* __restrict__ replicas, uint32_t replica_id) {
+	constexpr int NC = 1 << D;
+	float frac[D]; uint32_t cell[D];
+#pragma unroll
+	for (int d = 0; d < D; ++d) pos_fract_dev(p[d], lv.scale, frac[d], cell[d]);
+	if constexpr (SMOOTH) {
+		if (gp.smoothstep) {
+#pragma unroll
+			for (int d = 0; d < D; ++d) frac[d] = smoothstep_dev(frac[d]);
+		}
+	}
+	// Same-address f16x2 reductions serialise in L2 (~80 ns each, measured: 2-D level 0 alone took 244 us at B = 2^18);
+	// coarse levels therefore scatter into one of n_replicas copies chosen per block and are summed afterwards.
+	uint8_t* gtable = reinterpret_cast<uint8_t*>(lv.replicated
+		? replicas + ((size_t)replica_id * gp.rep_entries + lv.rep_offset) * F
+		: grid_grad + (size_t)lv.offset * F);
+	uint32_t idx[NC]; __half2 wh[NC];
+	corner_indices<D, MODE>(lv, cell, idx);
+#pragma unroll
+	for (int c = 0; c < NC; ++c) {
+		float weight = 1.0f;
+#pragma unroll
+		for (int d = 0; d < D; ++d) weight *= (c & (1 << d)) == 0 ? 1.0f - frac[d] : frac[d];
+		wh[c] = __half2half2(__float2half(weight));
+	}
+	// byte offset of entry i inside the level: a level holds at most 2^28 entries of at most 16 bytes (checked by plan_create), so
+	// 32-bit offsets + one widening add per reduction
+	auto at = [&](uint32_t byte_off) { return reinterpret_cast<__half*>(gtable + byte_off); };
+	// One vector reduction covers an aligned slot (see the forward kernel): for even cells it carries both dim-0 neighbours, for
+	// odd cells the other lanes add +0 and the neighbour gets its own (predicated) reduction: fewer L2 reduction operations per
+	// corner pair (the scatter is bound by the L2's reduction rate).
+	if constexpr (F == 2) {
+#pragma unroll
+		for (int c = 0; c < NC; c += 2) {
+			const uint32_t v0 = h2_bits(__hmul2(wh[c], g[0])), v1 = h2_bits(__hmul2(wh[c + 1], g[0]));
+#if TCNN_B200_SCATTER_QUAD
+			// 16-byte slot {idx & ~3 .. idx | 3}: holds the dim-0 neighbour unless idx % 4 == 3 -> 1.25 reductions per pair
+			const uint32_t l0 = idx[c] & 3u, l1 = idx[c + 1] & 3u;
+			const bool together = ((idx[c] ^ idx[c + 1]) & ~3u) == 0u && l0 != l1;
+			const uint32_t t1 = together ? l1 : 4u;
+			const uint32_t q0 = l0 == 0 ? v0 : (t1 == 0 ? v1 : 0u), q1 = l0 == 1 ? v0 : (t1 == 1 ? v1 : 0u);
+			const uint32_t q2 = l0 == 2 ? v0 : (t1 == 2 ? v1 : 0u), q3 = l0 == 3 ? v0 : (t1 == 3 ? v1 : 0u);
+			red_add_h2x4(at((idx[c] >> 2) << 4), q0, q1, q2, q3);
+			red_add_h2_if(!together, at(idx[c + 1] << 2), v1);
+#else
+			const bool paired = ((idx[c] ^ idx[c + 1]) == 1u), odd = (idx[c] & 1u) != 0;
+			const uint32_t nb = paired ? v1 : 0u;
+			red_add_h2x2(at((idx[c] >> 1) << 3), odd ? nb : v0, odd ? v0 : nb);
+			red_add_h2_if(!paired, at(idx[c + 1] << 2), v1);
+#endif
+		}
+	} else if constexpr (F == 4) {
+#pragma unroll
+		for (int c = 0; c < NC; c += 2) {
+			const uint32_t a0 = h2_bits(__hmul2(wh[c], g[0])), a1 = h2_bits(__hmul2(wh[c], g[1]));
+			const uint32_t b0 = h2_bits(__hmul2(wh[c + 1], g[0])), b1 = h2_bits(__hmul2(wh[c + 1], g[1]));
+			const bool paired = ((idx[c] ^ idx[c + 1]) == 1u), odd = (idx[c] & 1u) != 0;
+			const uint32_t n0 = paired ? b0 : 0u, n1 = paired ? b1 : 0u;
+			red_add_h2x4(at((idx[c] >> 1) << 4), odd ? n0 : a0, odd ? n1 : a1, odd ? a0 : n0, odd ? a1 : n1);
+			red_add_h2x2_if(!paired, at(idx[c + 1] << 3), b0, b1);
+		}
+	} else { // F == 8: one 16-byte reduction per corner
+#pragma unroll
+		for (int c = 0; c < NC; ++c)
+			red_add_h2x4(at(idx[c] << 4), h2_bits(__hmul2(wh[c], g[0])), h2_bits(__hmul2(wh[c], g[1])),
+				h2_bits(__hmul2(wh[c], g[2])), h2_bits(__hmul2(wh[c], g[3])));
+	}
+}
+
 // SMOOTH = false compiles the Smoothstep branch out: the fused MLP kernel (Linear only) keeps its register budget.
 template <int D, int F, bool SMOOTH = false>
 __device__ __forceinline__ void scatter_chunk(const GridParams& gp, const float (&p)[D], uint4 gv, uint32_t chunk,
 	__half* __restrict__ grid_grad, __half* __restrict__ replicas, uint32_t replica_id) {
 	static_assert(F == 2 || F == 4 || F == 8, "fp16 gradient scatter needs F >= 2 (grid.h:655-666)");
 	constexpr int LEVELS_PER_CHUNK = 8 / F;
-	constexpr int NC = 1 << D;
 	union { uint4 v; __half2 h2[4]; } g;
 	g.v = gv;
-#pragma unroll
+	// Rolled on purpose: the three index-rule variants of a level are ~120 instructions each; unrolled over the levels of a chunk the
+	// scatter was 5 000 instructions of the fused kernel and ran out of the instruction cache.  The chunk's gradient halfs rotate
+	// through the low words instead of being indexed by the loop counter.
+#pragma unroll 1
 	for (int s = 0; s < LEVELS_PER_CHUNK; ++s) {
 		const uint32_t level = chunk * LEVELS_PER_CHUNK + s;
 		if (level >= gp.n_levels) break;
 		const GridLevel& lv = gp.level[level];
-		float frac[D]; uint32_t cell[D];
+		__half2 gl[F / 2];
 #pragma unroll
-		for (int d = 0; d < D; ++d) pos_fract_dev(p[d], lv.scale, frac[d], cell[d]);
-		if constexpr (SMOOTH) {
-			if (gp.smoothstep) {
-#pragma unroll
-				for (int d = 0; d < D; ++d) frac[d] = smoothstep_dev(frac[d]);
-			}
-		}
-		// Same-address f16x2 reductions serialise in L2 (~80 ns each, measured: 2-D level 0 alone took 244 us at B = 2^18);
-		// coarse levels therefore scatter into one of n_replicas copies chosen per block and are summed afterwards.
-		__half* gtable = lv.replicated
-			? replicas + ((size_t)replica_id * gp.rep_entries + lv.rep_offset) * F
-			: grid_grad + (size_t)lv.offset * F;
-		uint32_t idx[NC]; __half2 wh[NC];
-#pragma unroll
-		for (int c = 0; c < NC; ++c) {
-			float weight = 1.0f; uint32_t pg[D];
-#pragma unroll
-			for (int d = 0; d < D; ++d) {
-				if ((c & (1 << d)) == 0) { weight *= 1.0f - frac[d]; pg[d] = cell[d]; }
-				else { weight *= frac[d]; pg[d] = cell[d] + 1u; }
-			}
-			idx[c] = grid_index_dev<D>(lv, pg);
-			wh[c] = __half2half2(__float2half(weight));
-		}
-		// One vector reduction covers the aligned slot {idx & ~1, idx | 1} (see the forward kernel): for even cells it carries
-		// both dim-0 neighbours, for odd cells the other half adds +0 and the neighbour gets its own (predicated) reduction.
-		// 1.5 L2 reduction ops per corner pair instead of 2 (the scatter is bound by L2 atomic throughput).
-		if constexpr (F == 2) {
-#pragma unroll
-			for (int c = 0; c < NC; c += 2) {
-				const uint32_t v0 = h2_bits(__hmul2(wh[c], g.h2[s])), v1 = h2_bits(__hmul2(wh[c + 1], g.h2[s]));
-#if TCNN_B200_SCATTER_QUAD
-				// 16-byte slot {idx & ~3 .. idx | 3}: holds the dim-0 neighbour unless idx % 4 == 3 -> 1.25 reductions per pair
-				const uint32_t l0 = idx[c] & 3u, l1 = idx[c + 1] & 3u;
-				const bool together = ((idx[c] ^ idx[c + 1]) & ~3u) == 0u && l0 != l1;
-				const uint32_t q0 = l0 == 0 ? v0 : (together && l1 == 0 ? v1 : 0u), q1 = l0 == 1 ? v0 : (together && l1 == 1 ? v1 : 0u);
-				const uint32_t q2 = l0 == 2 ? v0 : (together && l1 == 2 ? v1 : 0u), q3 = l0 == 3 ? v0 : (together && l1 == 3 ? v1 : 0u);
-				red_add_h2x4(gtable + (size_t)(idx[c] & ~3u) * 2, q0, q1, q2, q3);
-				red_add_h2_if(!together, gtable + (size_t)idx[c + 1] * 2, v1);
-#else
-				const bool paired = ((idx[c] ^ idx[c + 1]) == 1u), odd = (idx[c] & 1u) != 0;
-				const uint32_t nb = paired ? v1 : 0u;
-				red_add_h2x2(gtable + (size_t)(idx[c] & ~1u) * 2, odd ? nb : v0, odd ? v0 : nb);
-				if (!paired) red_add_h2(gtable + (size_t)idx[c + 1] * 2, *reinterpret_cast<const __half2*>(&v1));
-#endif
-			}
-		} else if constexpr (F == 4) {
-#pragma unroll
-			for (int c = 0; c < NC; c += 2) {
-				const uint32_t a0 = h2_bits(__hmul2(wh[c], g.h2[2 * s])), a1 = h2_bits(__hmul2(wh[c], g.h2[2 * s + 1]));
-				const uint32_t b0 = h2_bits(__hmul2(wh[c + 1], g.h2[2 * s])), b1 = h2_bits(__hmul2(wh[c + 1], g.h2[2 * s + 1]));
-				const bool paired = ((idx[c] ^ idx[c + 1]) == 1u), odd = (idx[c] & 1u) != 0;
-				const uint32_t n0 = paired ? b0 : 0u, n1 = paired ? b1 : 0u;
-				red_add_h2x4(gtable + (size_t)(idx[c] & ~1u) * 4, odd ? n0 : a0, odd ? n1 : a1, odd ? a0 : n0, odd ? a1 : n1);
-				red_add_h2x2_if(!paired, gtable + (size_t)idx[c + 1] * 4, b0, b1);
-			}
-		} else { // F == 8: one 16-byte reduction per corner
-#pragma unroll
-			for (int c = 0; c < NC; ++c)
-				red_add_h2x4(gtable + (size_t)idx[c] * 8, h2_bits(__hmul2(wh[c], g.h2[0])), h2_bits(__hmul2(wh[c], g.h2[1])),
-					h2_bits(__hmul2(wh[c], g.h2[2])), h2_bits(__hmul2(wh[c], g.h2[3])));
-		}
+		for (int k = 0; k < F / 2; ++k) gl[k] = g.h2[k];
+		if (lv.mode == LEVEL_HASH) scatter_level<D, F, LEVEL_HASH, SMOOTH>(gp, lv, p, gl, grid_grad, replicas, replica_id);
+		else if (lv.mode == LEVEL_DENSE_POW2) scatter_level<D, F, LEVEL_DENSE_POW2, SMOOTH>(gp, lv, p, gl, grid_grad, replicas, replica_id);
+		else scatter_level<D, F, LEVEL_DENSE_MOD, SMOOTH>(gp, lv, p, gl, grid_grad, replicas, replica_id);
+		if constexpr (F == 2) g.v = make_uint4(g.v.y, g.v.z, g.v.w, g.v.x);
+		else if constexpr (F == 4) g.v = make_uint4(g.v.z, g.v.w, g.v.x, g.v.y);
 	}
 }
 

@@ -101,6 +101,9 @@ static void fill_level(GridLevel& lv, float scale, uint32_t size, uint32_t offse
 	lv.hashed = (hash_type && size < stride) ? 1u : 0u; // Dense / Tiled grids never hash: dense index with wrap, % size
 	lv.replicated = 0; lv.rep_offset = 0;
 	lv.magic = fastmod_magic(size ? size : 1u);
+	const bool pow2 = size && (size & (size - 1)) == 0;
+	lv.mode = lv.hashed ? LEVEL_HASH : pow2 ? LEVEL_DENSE_POW2 : LEVEL_DENSE_MOD; // hashed levels have size 2^log2_hashmap_size
+	lv.reserved = 0;
 }
 
 constexpr uint32_t N_REPLICAS = 32;          // private copies of the contended coarse gradient levels
@@ -313,6 +316,7 @@ extern "C" int tcnn_b200_plan_create(const char* json_utf8, uint32_t n_input_dim
 		}
 		in.level_offset[l] = offset;
 		CHECK((uint64_t)offset + n < (1ull << 32) / in.n_features_per_level, "GridEncoding: more than 2^32 grid parameters");
+		CHECK((uint64_t)n * in.n_features_per_level * 4 <= 0xFFFFFFFFull, "GridEncoding: a single level of more than 4 GiB (fp32) is not supported (the kernels address entries inside a level with 32-bit byte offsets)");
 		offset += n;
 	}
 	in.level_offset[in.n_levels] = offset;

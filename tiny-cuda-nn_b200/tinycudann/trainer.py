@@ -44,18 +44,21 @@ class Trainer:
             dp_mode = "peer" if (self.world_size > 1 and self.device.type == "cuda" and torch.distributed.get_backend(process_group) == "nccl") else "allreduce"
         if dp_mode == "peer":
             # fp16 parameters and gradients live in symmetric memory that every rank maps (parallel.PeerMemory)
+            # fp32 master weights and Adam state exist for this rank's shard [b, e) only (ZeRO-1 in memory as well as in traffic)
             self.peer_memory = PeerMemory(native, self.device, process_group, use_multicast=use_multicast)
-            self.params_full_precision = torch.zeros(P, dtype=torch.float32, device=self.device)
+            b, e = self.peer_memory.shard
+            self.params_full_precision = torch.zeros(e - b, dtype=torch.float32, device=self.device)
             self.params, self.param_gradients = self.peer_memory.params, self.peer_memory.grads
         else:
             self.params_buffer = torch.zeros(8 * P, dtype=torch.uint8, device=self.device)
             self.params_full_precision = self.params_buffer[: 4 * P].view(torch.float32)
             self.params = self.params_buffer[4 * P : 6 * P].view(torch.half)
             self.param_gradients = self.params_buffer[6 * P : 8 * P].view(torch.half)
-        # AdamOptimizer::allocate (adam.h:128-148)
-        self.first_moments = torch.zeros(P, dtype=torch.float32, device=self.device)
-        self.second_moments = torch.zeros(P, dtype=torch.float32, device=self.device)
-        self.param_steps = torch.zeros(P, dtype=torch.int32, device=self.device)
+        # AdamOptimizer::allocate (adam.h:128-148); peer mode: the shard's state only
+        n_state = self.params_full_precision.numel()
+        self.first_moments = torch.zeros(n_state, dtype=torch.float32, device=self.device)
+        self.second_moments = torch.zeros(n_state, dtype=torch.float32, device=self.device)
+        self.param_steps = torch.zeros(n_state, dtype=torch.int32, device=self.device)
         self.current_step = 0
         self.loss_value = torch.zeros(1, dtype=torch.float32, device=self.device)
         self._grid_grads_clean = True  # grid gradient region is all zero (after init / after an optimizer step)
@@ -65,8 +68,13 @@ class Trainer:
     # trainer.h:68-87
     def initialize_params(self, seed: int = 1337):
         with torch.cuda.device(self.device):
-            check(self.lib.tcnn_b200_init_params(self.native.handle, _stream_ptr(), seed, 1, ptr(self.params_full_precision)))
-            check(self.lib.tcnn_b200_cast_params(_stream_ptr(), self.n_params, ptr(self.params_full_precision), ptr(self.params)))
+            full = self.params_full_precision if self.peer_memory is None else torch.empty(self.n_params, dtype=torch.float32, device=self.device)
+            check(self.lib.tcnn_b200_init_params(self.native.handle, _stream_ptr(), seed, 1, ptr(full)))
+            check(self.lib.tcnn_b200_cast_params(_stream_ptr(), self.n_params, ptr(full), ptr(self.params)))
+            if self.peer_memory is not None:
+                b, e = self.peer_memory.shard
+                self.params_full_precision.copy_(full[b:e])
+                del full
             self.param_gradients.zero_()
             self.first_moments.zero_(); self.second_moments.zero_(); self.param_steps.zero_()
             self.current_step = 0
@@ -74,8 +82,13 @@ class Trainer:
             torch.cuda.synchronize(self.device)
 
     def set_params_full_precision(self, params_fp32: torch.Tensor):
-        self.params_full_precision.copy_(params_fp32.to(self.device, torch.float32))
-        check(self.lib.tcnn_b200_cast_params(_stream_ptr(), self.n_params, ptr(self.params_full_precision), ptr(self.params)))
+        full = params_fp32.to(self.device, torch.float32).contiguous()
+        if self.peer_memory is None:
+            self.params_full_precision.copy_(full)
+        else:
+            b, e = self.peer_memory.shard
+            self.params_full_precision.copy_(full[b:e])
+        check(self.lib.tcnn_b200_cast_params(_stream_ptr(), self.n_params, ptr(full), ptr(self.params)))
 
     # trainer.h:163-190.  input [B, D] fp32, target [B, O] fp32 (== GPUMatrix CM [D x B] / [O x B]).
     def training_step(self, input: torch.Tensor, target: torch.Tensor, run_optimizer: bool = True, output: torch.Tensor | None = None):
@@ -116,15 +129,17 @@ class Trainer:
         b, e = pm.shard
         check(self.lib.tcnn_b200_training_step_dp(
             self.native.handle, _stream_ptr(), B, ptr(input), ptr(target), LOSS_SCALE, self.current_step,
-            ptr(self.params_full_precision[b:e]), ptr(self.first_moments[b:e]), ptr(self.second_moments[b:e]),
-            ptr(self.param_steps[b:e]), ptr(self.loss_value), ptr(output), ptr(ws), _lib.C.byref(pm.comm)))
+            ptr(self.params_full_precision), ptr(self.first_moments), ptr(self.second_moments),
+            ptr(self.param_steps), ptr(self.loss_value), ptr(output), ptr(ws), _lib.C.byref(pm.comm)))
         return self
 
     def gather_params_full_precision(self) -> torch.Tensor:
         """fp32 master weights of all shards (collective; in peer-memory mode each rank only updates its own shard)."""
         if self.peer_memory is None:
             return self.params_full_precision.clone()
-        full = self.params_full_precision.clone()
+        full = torch.zeros(self.n_params, dtype=torch.float32, device=self.device)
+        b, e = self.peer_memory.shard
+        full[b:e] = self.params_full_precision
         for r in range(self.world_size):
             b, e = self.peer_memory.shard_of(r)
             if e > b:
