@@ -60,6 +60,10 @@ def _net(n, h, act, out_act):
 _GRID_SMALL_2D = {"otype": "HashGrid", "n_levels": 8, "n_features_per_level": 2, "log2_hashmap_size": 12, "base_resolution": 8, "per_level_scale": 1.5}
 _GRID_SMALL_3D = {"otype": "HashGrid", "n_levels": 8, "n_features_per_level": 4, "log2_hashmap_size": 12, "base_resolution": 8, "per_level_scale": 1.5}
 # hidden / output activations other than ReLU / None (common_device.h:100-304), on both MLP widths
+CONFIG_SNAPSHOT = {  # small enough that a full Trainer::serialize(true) snapshot of the reference is a 250 KB fixture
+    "loss": {"otype": "L2"}, "optimizer": {"otype": "Adam", "learning_rate": 1e-2, "beta1": 0.9, "beta2": 0.99, "epsilon": 1e-15, "l2_reg": 1e-6},
+    "encoding": {"otype": "HashGrid", "n_levels": 8, "n_features_per_level": 2, "log2_hashmap_size": 10, "base_resolution": 8, "per_level_scale": 1.5},
+    "network": _net(64, 2, "ReLU", "None")}
 CONFIG_ACT_A = {"loss": {"otype": "L2"}, "optimizer": {"otype": "Adam"}, "encoding": _GRID_SMALL_2D, "network": _net(64, 3, "Sigmoid", "Exponential")}
 CONFIG_ACT_B = {"loss": {"otype": "RelativeL2"}, "optimizer": {"otype": "Adam"}, "encoding": {"otype": "OneBlob", "n_bins": 16}, "network": _net(128, 2, "Tanh", "Sigmoid")}
 CONFIG_ACT_C = {"loss": {"otype": "L2"}, "optimizer": {"otype": "Adam"}, "encoding": {"otype": "OneBlob", "n_bins": 16}, "network": _net(64, 2, "Squareplus", "Softplus")}

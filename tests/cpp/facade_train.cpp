@@ -7,6 +7,8 @@
 
 #include <cmath>
 #include <cstdio>
+#include <fstream>
+#include <iterator>
 #include <random>
 #include <vector>
 
@@ -22,6 +24,16 @@ static const char* kConfig = R"({
 int main(int argc, char** argv) {
 	const bool compile_only = argc > 1 && std::string(argv[1]) == "--no-gpu";
 	try {
+		if (argc > 2 && std::string(argv[1]) == "--msgpack") { // no device: a snapshot written by the reference goes through json.h unchanged
+			std::ifstream f(argv[2], std::ios::binary);
+			const std::vector<uint8_t> raw((std::istreambuf_iterator<char>(f)), std::istreambuf_iterator<char>());
+			const json snap = json::from_msgpack(raw);
+			const bool same = json::to_msgpack(snap) == raw;
+			std::printf("n_params=%zu params_type=%s params_bytes=%zu current_step=%u moments_bytes=%zu rewritten_identically=%d\n", (size_t)snap["n_params"],
+				snap["params_type"].get<std::string>().c_str(), snap["params_binary"].get_binary().size(), (uint32_t)snap["optimizer"]["current_step"],
+				snap["optimizer"]["first_moments_binary"].get_binary().size(), (int)same);
+			return same ? 0 : 1;
+		}
 		const uint32_t n_in = 2, n_out = 3, B = 1 << 14, steps = 300;
 		if (compile_only) { // no device here: the plan (JSON, level table, sizes) can still be built; compute calls must throw
 			Network net(kConfig, n_in, n_out);

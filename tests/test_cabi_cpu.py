@@ -173,3 +173,37 @@ def test_snapshot_format_roundtrip_through_msgpack():
     import pytest
     with pytest.raises(RuntimeError, match="float of __half"):
         checkpoint.unpack({"params_type": "double", "params_binary": b""})
+
+
+def test_snapshot_written_by_the_reference_is_read():
+    """tests/golden/snapshot_small_2d.msgpack = json::to_msgpack(Trainer::serialize(true)) of the REFERENCE build after 20 training
+    steps on common.CONFIG_SNAPSHOT (`ref_driver serialize`, tests/dev/n2_pin.py).  checkpoint.unpack reads it; its sizes are
+    the plan's; the C++ json type of include/tiny-cuda-nn/json.h re-emits the file byte for byte."""
+    import json as js
+    import subprocess
+    import msgpack
+    import numpy as np
+    import __graft_entry__ as ge
+    from tinycudann import checkpoint
+    from tinycudann import _lib
+    golden = os.path.join(ROOT, "tests", "golden")
+    meta = js.load(open(os.path.join(golden, "snapshot_small_2d.json")))
+    raw = open(os.path.join(golden, "snapshot_small_2d.msgpack"), "rb").read()
+    params, opt = checkpoint.unpack(msgpack.unpackb(raw, raw=False))
+    lib = _lib.lib()
+    rc, h = _plan(lib, meta["config"], meta["n_in"], meta["n_out"])
+    assert rc == 0, lib.tcnn_b200_last_error()
+    info = _lib.Info()
+    assert lib.tcnn_b200_plan_info(h, C.byref(info)) == 0
+    P = int(info.n_params_grid + info.n_params_mlp)
+    lib.tcnn_b200_plan_destroy(h)
+    assert params.dtype == np.float16 and params.size == P
+    assert opt["current_step"] == meta["n_steps"] and abs(opt["base_learning_rate"] - 1e-2) < 1e-9
+    assert opt["first_moments"].size == P and opt["second_moments"].size == P and opt["param_steps"].size == P
+    assert opt["param_steps"].max() == meta["n_steps"] and (opt["second_moments"] >= 0).all()
+    # our writer -> the same object again
+    again = msgpack.unpackb(msgpack.packb(checkpoint.pack(params, opt), use_bin_type=True), raw=False)
+    p2, o2 = checkpoint.unpack(again)
+    assert np.array_equal(p2, params) and all(np.array_equal(o2[k], opt[k]) for k in ("first_moments", "second_moments", "param_steps"))
+    r = subprocess.run([ge.build_cpp_facade_sample(), "--msgpack", os.path.join(golden, "snapshot_small_2d.msgpack")], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 0 and f"n_params={P} params_type=__half" in r.stdout and "rewritten_identically=1" in r.stdout, r.stdout + r.stderr

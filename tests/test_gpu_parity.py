@@ -495,6 +495,89 @@ def test_cpp_facade_host_trains(dev):
     assert "inference mse" in r.stdout
 
 
+def test_reference_sample_training_loop_compiles_and_trains(dev):
+    """tests/cpp/sample_training_loop.cu: the loop of the reference's samples/mlp_learning_an_image.cu:185-296 (create_loss,
+    create_optimizer, NetworkWithInputEncoding<precision_t>, Trainer<float, precision_t, precision_t>, generate_random_uniform,
+    linear_kernel, training_step / loss / inference) compiled by nvcc against include/tiny-cuda-nn/ and run; then a C++
+    serialize -> msgpack -> deserialize resume, update_hyperparams, and an unsupported argument that has to throw."""
+    import subprocess
+    import __graft_entry__ as ge
+    exe = ge.build_reference_sample_loop()
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "resumed: loss" in r.stdout
+
+
+def _snapshot_golden():
+    meta = json.load(open(os.path.join(GOLDEN, "snapshot_small_2d.json")))
+    return meta, os.path.join(GOLDEN, "snapshot_small_2d.msgpack")
+
+
+def _snapshot_batches(meta, dev, skip, n):
+    rng = O.Pcg32(meta["seed"])
+    for i in range(skip + n):
+        x = O.random_uniform(rng, meta["B"] * meta["n_in"]).reshape(meta["B"], meta["n_in"])
+        if i >= skip:
+            yield torch.from_numpy(x).to(dev), torch.from_numpy(O.synth_target(x, meta["n_out"])).to(dev)
+
+
+def test_snapshot_of_the_reference_resumes_on_its_curve(dev):
+    """N2 pin: tests/golden/snapshot_small_2d.msgpack was written by the reference (json::to_msgpack(Trainer::serialize(true)) after 20
+    steps, trainer.h:275-288, adam.h:278-286); the reference then ran two more steps (losses[20:22] of the golden).  Our
+    Trainer.deserialize of the file followed by the same two batches reproduces those losses (python and C++ facade)."""
+    import msgpack
+    import subprocess
+    import tinycudann as tcnn
+    import __graft_entry__ as ge
+    meta, path = _snapshot_golden()
+    N, ref = meta["n_steps"], np.array(meta["losses"])
+    tr = tcnn.create_from_config(meta["n_in"], meta["n_out"], meta["config"], seed=5, device=dev).trainer
+    tr.deserialize(msgpack.unpackb(open(path, "rb").read(), raw=False))
+    assert tr.current_step == N
+    ours = []
+    for x, t in _snapshot_batches(meta, dev, N, 2):
+        tr.training_step(x, t); ours.append(tr.loss())
+    # measured: step 21 identical to the last digit, step 22 within 7e-5 (the fp32 master weights restart from the fp16 copy on both sides)
+    assert np.allclose(ours, ref[N:], rtol=1e-3, atol=0), (ours, ref[N:])
+    cfg_path = os.path.join(os.environ.get("TMPDIR", "/tmp"), "snapshot_cfg.json")
+    json.dump(meta["config"], open(cfg_path, "w"))
+    r = subprocess.run([ge.build_reference_sample_loop(), "--resume", cfg_path, path, str(meta["B"]), str(meta["seed"]), str(N)], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stdout + r.stderr
+    got = [float(v) for v in r.stdout.split("resume losses")[1].split()[:2]]
+    assert np.allclose(got, ref[N:], rtol=1e-3, atol=0), (got, ref[N:])
+
+
+def test_our_snapshot_is_read_by_the_reference(dev):
+    """N2 pin, other direction: our Trainer.serialize(True) -> msgpack -> `ref_driver deserialize` (the reference's
+    Trainer::deserialize, trainer.h:290-315) -> two more steps there; our own two steps give the same losses."""
+    import msgpack
+    import subprocess
+    import tempfile
+    import tinycudann as tcnn
+    ref_driver = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "ref_driver")
+    if not os.path.exists(ref_driver):
+        pytest.skip("oracle/_ref/ref_driver not built")
+    meta, _ = _snapshot_golden()
+    N = meta["n_steps"]
+    tr = tcnn.create_from_config(meta["n_in"], meta["n_out"], meta["config"], seed=1337, device=dev).trainer
+    first = []
+    for x, t in _snapshot_batches(meta, dev, 0, N):
+        tr.training_step(x, t); first.append(tr.loss())
+    assert np.allclose(first, meta["losses"][:N], rtol=2e-2)     # same init, same batches: on the reference's curve before the snapshot
+    with tempfile.TemporaryDirectory() as d:
+        cfg_path, snap = os.path.join(d, "cfg.json"), os.path.join(d, "ours.msgpack")
+        json.dump(meta["config"], open(cfg_path, "w"))
+        open(snap, "wb").write(msgpack.packb(tr.serialize(serialize_optimizer=True), use_bin_type=True))
+        r = subprocess.run([ref_driver, "deserialize", cfg_path, str(meta["n_in"]), str(meta["n_out"]), str(meta["B"]), str(meta["seed"]), str(N), snap],
+                           capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    theirs = json.loads(r.stdout.strip().splitlines()[-1])["next_losses"]
+    ours = []
+    for x, t in _snapshot_batches(meta, dev, N, 2):
+        tr.training_step(x, t); ours.append(tr.loss())
+    assert np.allclose(ours, theirs, rtol=1e-3, atol=0), (ours, theirs)
+
+
 def test_trainer_snapshot_resumes_identically(dev):
     """Trainer.serialize(serialize_optimizer=True) -> msgpack -> Trainer.deserialize on a fresh trainer: same parameters and
     optimizer state, and the next step gives the same loss as the uninterrupted run (trainer.h:275-315)."""
