@@ -26,6 +26,36 @@ BATCH = 1 << 18
 N_IN, N_OUT = 2, 3
 METRIC = "training samples/sec HashGrid+FullyFusedMLP64 @ batch 2^18, 1/2/4/8 B200"
 WORKLOAD = "cfg1: 2D HashGrid 16x2 T=2^19 base16 scale2.0 + FullyFusedMLP 64x2 ReLU, L2, Adam, batch 2^18 per GPU (README.md:19-42 config of the reference)"
+CONFIG_NAME = "cfg1"
+
+
+def select_workload(name):
+    """--config: cfg1 is the metric's configuration (the default, the only one the driver runs); the others are BASELINE.json's
+    secondary configurations, same JSON line, `metric` saying which."""
+    global BATCH, N_IN, N_OUT, METRIC, WORKLOAD, CONFIG_NAME
+    from tests import common
+    CONFIG_NAME = name
+    if name == "cfg1":
+        return common.CONFIG_1
+    if name == "cfg2":  # BASELINE.json configs[1]: benchmarks/image/bench_ours.cu with data/config_oneblob.json at 128 neurons
+        BATCH, N_IN, N_OUT = 1 << 18, 2, 3
+        METRIC = "training samples/sec OneBlob+FullyFusedMLP128x5 @ batch 2^18 (bench_ours.cu)"
+        WORKLOAD = "cfg2: OneBlob 64 bins (2-D -> 128 features) + FullyFusedMLP 128x5 ReLU, RelativeL2, Adam, batch 2^18 per GPU (data/config_oneblob.json)"
+        return common.CONFIG_ONEBLOB
+    if name == "cfg3":  # configs[2]
+        BATCH, N_IN, N_OUT = 1 << 20, 3, 4
+        METRIC = "training samples/sec NeRF-style 3D HashGrid+FullyFusedMLP64 @ batch 2^20"
+        WORKLOAD = "cfg3: 3D HashGrid 16x2 T=2^19 scale1.38 + FullyFusedMLP 64x2, L2, Adam, batch 2^20 per GPU"
+        return common.CONFIG_NERF
+    if name in ("cfg4", "cfg5"):
+        base, log2_T, b = (common.CONFIG_WIDE_F4, 24, 20) if name == "cfg4" else (common.CONFIG_WIDE_DP, 22, 19)
+        c = json.loads(json.dumps(base)); c["encoding"]["log2_hashmap_size"] = log2_T
+        BATCH, N_IN, N_OUT = 1 << b, 3, (4 if name == "cfg4" else 3)
+        METRIC = f"training samples/sec 3D HashGrid T=2^{log2_T}+FullyFusedMLP128 @ batch 2^{b}"
+        WORKLOAD = (f"{name}: 3D HashGrid 16x{c['encoding']['n_features_per_level']} T=2^{log2_T} + FullyFusedMLP 128x{c['network']['n_hidden_layers']}, "
+                    f"L2, Adam, batch 2^{b} per GPU")
+        return c
+    raise SystemExit(f"unknown --config {name}")
 
 
 def load_peaks():
@@ -34,6 +64,34 @@ def load_peaks():
             return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
     except Exception:  # noqa: BLE001
         return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def load_l2_peaks():
+    """profiles/l2_peaks.json: random-address reduction / load rates of one B200's L2, measured by tests/dev/l2_peaks.cu."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "l2_peaks.json")) as f:
+            d = json.load(f)
+        return {"red": float(d["red_gops_per_s"]["table_32MiB_16B"]), "ld": float(d["ld_gops_per_s"]["table_32MiB_16B"])}
+    except Exception:  # noqa: BLE001
+        return None
+
+
+def l2_rooflines(info, B, kernel_ms):
+    """The two L2-bound kernels against the L2's own ceilings.  Operations per launch: a corner pair (the two
+    dim-0 neighbours) costs one 16-byte slot access plus a second access when the pair straddles a slot (1 time in 4), i.e.
+    1.25 x 2^(D-1) per sample and level - loads in the gather, red.global.add.f16x2 in the scatter of the fused kernel."""
+    peaks = load_l2_peaks()
+    if not peaks or not info.n_levels or info.n_features_per_level != 2:
+        return None
+    ops = B * int(info.n_levels) * (1 << (int(info.n_input_dims) - 1)) * 1.25
+    out = {"source": "profiles/l2_peaks.json (tests/dev/l2_peaks.cu on a B200)", "unit": "Gop/s"}
+    for kernel, kind in (("mlp_fused", "red"), ("grid_forward", "ld")):
+        ms = kernel_ms.get(kernel, 0.0)
+        if ms > 0:
+            ach = ops / (ms * 1e-3) / 1e9
+            out[kernel] = {"op": {"red": "red.global.add.noftz.f16x2 (v1/v4)", "ld": "ld.global.nc 4/16 B"}[kind], "ops_per_launch": ops,
+                           "achieved": ach, "peak": peaks[kind], "frac": ach / peaks[kind]}
+    return out
 
 
 class ClockSampler:
@@ -139,7 +197,10 @@ def run_reference(args, cfg):
     line = {"impl": "reference", "metric": METRIC, "unit": "samples/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16", "data": "synthetic",
             "config": config_dict(args.gpus), "reference_note": "the reference is single-GPU: its 1-GPU number is reported for every --gpus"}
-    cpu = cpu_baseline_port(cfg)
+    try:
+        cpu = cpu_baseline_port(cfg)
+    except Exception as e:  # noqa: BLE001
+        cpu = {"unavailable": str(e)[:200], "value": None}
     have_gpu = False
     try:
         import torch
@@ -171,8 +232,9 @@ def run_reference(args, cfg):
 
 def config_dict(world, dp_mode="peer"):
     """The `config` object of the JSON line: identical in both arms (ours and --impl reference) for the same --gpus."""
-    return {"workload": WORKLOAD, "batch_per_gpu": BATCH, "global_batch": BATCH * world, "parallelism": f"dp{world}",
-            "l2": "no flush: one step streams ~0.45 GB of parameter/optimizer state (> 126 MB L2) and cycles 4 distinct resident batches"}
+    l2 = ("no flush: one step streams ~0.45 GB of parameter/optimizer state (> 126 MB L2) and cycles 4 distinct resident batches" if CONFIG_NAME == "cfg1" else
+          "no flush: 4 distinct resident batches are cycled; parameters + optimizer state + the per-batch activations of one step exceed the 126 MB L2")
+    return {"workload": WORKLOAD, "batch_per_gpu": BATCH, "global_batch": BATCH * world, "parallelism": f"dp{world}", "l2": l2}
 
 
 DP_NOTE = {
@@ -237,6 +299,7 @@ def main():
     ap.add_argument("--steps", type=int, default=2000)
     ap.add_argument("--warmup", type=int, default=50)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="cfg1", choices=["cfg1", "cfg2", "cfg3", "cfg4", "cfg5"], help="cfg1 = the metric's configuration (default); cfg2..5 = BASELINE.json's secondary configurations")
     ap.add_argument("--e2e-steps", type=int, default=300)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--force-dp", action="store_true", help="N = 1: run the data-parallel step on a one-rank group")
@@ -246,7 +309,7 @@ def main():
     args.warmup = max(args.warmup, 3)
 
     from tests import common
-    cfg = common.CONFIG_1
+    cfg = select_workload(args.config)
     if args.impl == "reference":
         return run_reference(args, cfg)
 
@@ -303,49 +366,15 @@ def main():
         x, t = batches[i % n_batches]
         tr.training_step(x, t)
 
-    # End-to-end: every step's inputs come from pinned host memory (H2D inside the timed region) and its loss goes back
-    # to the host.  Double-buffered: the copy of step i+1 runs on a copy stream under the compute of step i, the loss
-    # read-back is asynchronous (one 4-byte D2H per step), the host synchronises once at the end of the timed region.
-    copy_stream = torch.cuda.Stream(device=dev)
-    bufs = [(torch.empty_like(batches[0][0]), torch.empty_like(batches[0][1])) for _ in range(2)]
-    ev_ready = [torch.cuda.Event() for _ in range(2)]
-    ev_free = [torch.cuda.Event() for _ in range(2)]
+    # End-to-end: every step's inputs come from pinned host memory (H2D inside the timed region) and its loss goes back to the host,
+    # through the public call for host-resident batches: Trainer.training_step_host = tcnn_b200_host_batch_begin -> training_step ->
+    # tcnn_b200_host_batch_end.  The library copies the NEXT batch on its copy stream under this step's compute and reads the
+    # 4-byte loss back on a third stream; the host synchronises once at the end of the timed region.
     hlosses = torch.zeros(4096, dtype=torch.float32).pin_memory()
-
-    def enqueue_copy(k):
-        with torch.cuda.stream(copy_stream):
-            copy_stream.wait_event(ev_free[k])
-            bufs[k][0].copy_(hx, non_blocking=True)
-            bufs[k][1].copy_(ht, non_blocking=True)
-            ev_ready[k].record(copy_stream)
-
-    # The 4-byte loss read-back runs on its own stream (a D2H on the compute stream holds the next gather back by the copy
-    # engine's latency); two loss buffers alternate so that step i+1 never overwrites a loss that is still being copied.
-    d2h_stream = torch.cuda.Stream(device=dev)
-    loss_bufs = [tr.loss_value, torch.zeros_like(tr.loss_value)]
-    ev_loss = [torch.cuda.Event() for _ in range(2)]
-    ev_loss_copied = [torch.cuda.Event() for _ in range(2)]
-
     E2E_WARMUP = 6  # untimed iterations of the same loop in front: the first, un-overlapped H2D copy is not part of a 20-step measurement
 
     def train_e2e(i, last=False):
-        k = i % 2
-        if i == 0:
-            enqueue_copy(0)
-        enqueue_copy(1 - k)  # prefetch the next step's batch
-        main = torch.cuda.current_stream()
-        main.wait_event(ev_ready[k])
-        main.wait_event(ev_loss_copied[k])  # loss of step i-2 has left buffer k (long done)
-        tr.loss_value = loss_bufs[k]
-        tr.training_step(bufs[k][0], bufs[k][1])
-        ev_free[k].record(main)
-        ev_loss[k].record(main)
-        with torch.cuda.stream(d2h_stream):
-            d2h_stream.wait_event(ev_loss[k])
-            hlosses[i % 4096: i % 4096 + 1].copy_(loss_bufs[k], non_blocking=True)
-            ev_loss_copied[k].record(d2h_stream)
-        if last:
-            main.wait_event(ev_loss_copied[k])  # the last read-back ends inside the timed region
+        tr.training_step_host(hx, ht, next_batch=None if last else (hx, ht), host_loss=hlosses[i % 4096: i % 4096 + 1], join=last)
 
     for i in range(args.warmup):
         train(i)
@@ -362,14 +391,11 @@ def main():
     inf_steps = min(args.steps, 500)
     inf_ms = timed(inf_steps, lambda i: tr.inference(batches[i % n_batches][0], inf_out)) / inf_steps
 
-    for ev in ev_free:
-        ev.record(torch.cuda.current_stream())
     e2e_steps = min(args.e2e_steps, args.steps)
     for i in range(E2E_WARMUP):
         train_e2e(i)
     e2e_ms = timed(e2e_steps, lambda i: train_e2e(E2E_WARMUP + i, last=(i == e2e_steps - 1))) / e2e_steps
     h2d_gbs = BATCH * 4 * (N_IN + N_OUT) / (e2e_ms * 1e-3) / 1e9  # what the copy stream must sustain per rank to keep up with the step
-    tr.loss_value = loss_bufs[0]
     e2e_value = BATCH * world / (e2e_ms * 1e-3)
 
     # per-kernel device time over a further stretch of the same loop (CUDA events on the launch stream)
@@ -404,23 +430,28 @@ def main():
             "metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16",
             "data": "synthetic",
-            "config": config_dict(world), "gradient_exchange": DP_NOTE.get(args.dp_mode, args.dp_mode) if world > 1 else "none",
+            "config": config_dict(world), "launch": "one static CUDA graph per (batch, buffers): %d kernel nodes, Adam scalars patched per step" % int(sum(launches_per_step.values())) if world == 1 and tr.graph_stats()[1] else "stream launches", "gradient_exchange": DP_NOTE.get(args.dp_mode, args.dp_mode) if world > 1 else "none",
             "clocks": clk.summary(),
             "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": BATCH * 4 * (N_IN + N_OUT), "d2h_bytes_per_step": 4,
-                    "ms_per_step": e2e_ms, "steps": e2e_steps, "warmup": E2E_WARMUP, "h2d_gb_per_s_per_rank": h2d_gbs, "how": "pinned host batch -> H2D on a copy stream (double-buffered, overlaps the previous step) -> training_step -> async 4-byte loss D2H on its own stream (two loss buffers); one host sync at the end"},
+                    "ms_per_step": e2e_ms, "steps": e2e_steps, "warmup": E2E_WARMUP, "h2d_gb_per_s_per_rank": h2d_gbs, "last_loss_on_host": float(hlosses[(E2E_WARMUP + e2e_steps - 1) % 4096]),
+                    "how": "Trainer.training_step_host: pinned host batch -> H2D on the library's copy stream (two staging slots, next batch copied under this step) -> training_step (static graph) -> 4-byte loss D2H on a third stream into pinned memory; one host sync at the end"},
             "gpu_launches": int(sum(launches_per_step.values()) * args.steps),
             "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
                          "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": per_kernel_bytes[dominant],
                          "kernel_ms_per_step_serial": kernel_ms, "launches_per_step": launches_per_step, "kernel_share": {k: v / max(sum(kernel_ms.values()), 1e-9) for k, v in kernel_ms.items()},
+                         "l2": l2_rooflines(info, BATCH, kernel_ms),
                          "step": {"algorithmic_bytes": a_train, "achieved": a_train / (ms_per_step * 1e-3) / 1e9, "frac": a_train / (ms_per_step * 1e-3) / 1e9 / hbm_peak}},
             "final_loss": final_loss,
             "inference": {"value": BATCH * world / (inf_ms * 1e-3), "unit": "samples/s", "ms_per_batch": inf_ms,
-                          "what": "Network::inference, fp32 output, inputs resident, batch 2^18 per GPU"},
+                          "what": f"Network::inference, fp32 output, inputs resident, batch {BATCH} per GPU"},
         }
         if dp_check is not None:
             line["dp_check"] = dp_check
         if world == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"] = cpu_baseline_port(cfg)
+            try:
+                line["cpu_baseline"] = cpu_baseline_port(cfg)
+            except Exception as e:  # noqa: BLE001 - the CPU port covers grid encodings (the metric's configuration)
+                line["cpu_baseline"] = {"unavailable": str(e)[:200]}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()

@@ -201,6 +201,33 @@ int tcnn_b200_training_step(const tcnn_b200_plan* plan, void* stream, uint32_t b
                             float* first_moments, float* second_moments, uint32_t* param_steps, float* loss_out, void* output_fp16,
                             void* workspace);
 
+/* Static CUDA graphs behind tcnn_b200_training_step (what include/tiny-cuda-nn/cuda_graph.h:65-153 does for the reference's
+ * Trainer::training_step).  The launches of one step are captured once per (batch size, buffer addresses, loss scale, plan
+ * settings) and replayed with one cudaGraphLaunch on the caller's stream; the per-step Adam scalars are patched into the
+ * optimizer kernel nodes before each replay.  Up to 8 buffer sets are cached per plan; a caller that passes new buffers on
+ * every call is no longer captured after 32 misses in a row.  A step issued while the CALLER's stream is being captured is
+ * launched plainly so that it lands in the caller's graph.  mode: 1 = graphs, 0 = plain launches, -1 = environment
+ * TCNN_B200_GRAPH ("0" disables; default graphs).  Changing the mode drops the cached graphs. */
+int tcnn_b200_plan_set_graph_mode(tcnn_b200_plan* plan, int mode);
+int tcnn_b200_plan_graph_stats(const tcnn_b200_plan* plan, uint32_t* captures, uint32_t* replays);
+
+
+/* Batches that live in host memory (no reference counterpart: the reference's hosts create their batches on the device, e.g.
+ * samples/mlp_learning_an_image.cu:240-243).  begin/end bracket ONE call of any step entry point above:
+ *   begin  stages this step's batch in one of two device slots inside `staging` (skipped when an earlier begin prefetched the
+ *          same host pointers as its `next_*`), starts the copy of the next batch into the other slot on an internal copy
+ *          stream, makes `stream` wait for this step's data and returns device pointers for x, target and a loss word;
+ *   end    marks the slot reusable once the work enqueued on `stream` so far is done and, if host_loss_out is not NULL, copies
+ *          the loss word to it on a third stream (join != 0: `stream` also waits for that copy).
+ * Host buffers should be pinned (cudaHostAlloc / torch pin_memory) or the copies serialise with the host.  host_loss_out is
+ * valid after the caller synchronises (device, or `stream` after an end with join).  Nothing is allocated: staging is caller
+ * memory of tcnn_b200_host_staging_bytes(plan, batch_size) bytes. */
+size_t tcnn_b200_host_staging_bytes(const tcnn_b200_plan* plan, uint32_t batch_size);
+int tcnn_b200_host_batch_begin(tcnn_b200_plan* plan, void* stream, uint32_t batch_size, const float* host_x, const float* host_target,
+                               const float* next_host_x, const float* next_host_target, void* staging,
+                               float** device_x, float** device_target, float** device_loss);
+int tcnn_b200_host_batch_end(tcnn_b200_plan* plan, void* stream, float* host_loss_out, int join);
+
 /* Per-kernel device timing for bench.py's roofline line (no reference counterpart): when enabled, every kernel launch
  * of this plan is bracketed by CUDA events on its launch stream.  profile_read synchronises them and returns the summed
  * milliseconds and launch counts for kind 0..4 = grid forward, MLP, MLP finalize, grid backward (+memset), Adam. */

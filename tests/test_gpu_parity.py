@@ -508,6 +508,82 @@ def test_reference_sample_training_loop_compiles_and_trains(dev):
     assert "resumed: loss" in r.stdout
 
 
+def test_training_step_graph_replay_matches_plain_launches(dev):
+    """a17: tcnn_b200_training_step replays one static CUDA graph per (batch size, buffers) with the Adam step scalars patched into
+    the optimizer nodes (cuda_graph.h:65-153 is what the reference wraps around Trainer::training_step).  Same seed, same batches:
+    the graph trainer follows the plain-launch trainer step by step, across a hyper-parameter change (new capture) and an
+    AdaBound-style per-step bound; and the captures / replays counters say the graph path really ran."""
+    import tinycudann as tcnn
+    cfg = json.loads(json.dumps(common.CONFIG_SHIPPED))
+    cfg["optimizer"]["adabound"] = True
+    a = tcnn.create_from_config(2, 3, cfg, seed=1337, device=dev).trainer
+    b = tcnn.create_from_config(2, 3, cfg, seed=1337, device=dev).trainer
+    a.set_graph_mode(1); b.set_graph_mode(0)
+    B = 1 << 12
+    batches = [tuple(torch.from_numpy(v).to(dev) for v in common.synth_inputs(B, 2, 3, seed=80 + i)) for i in range(2)]
+    la, lb = [], []
+    for i in range(40):
+        if i == 20:
+            a.update_hyperparams({"learning_rate": 3e-3}); b.update_hyperparams({"learning_rate": 3e-3})
+        x, t = batches[i % 2]
+        a.training_step(x, t); b.training_step(x, t)
+        la.append(a.loss()); lb.append(b.loss())
+    assert np.allclose(la, lb, rtol=5e-3), (la, lb)          # atomics order differs between two runs: not bit-identical
+    assert la[-1] < 0.5 * la[0]
+    # measured 1.8e-3 after 40 steps: the order of the fp16 reductions differs between any two runs and Adam's early steps amplify it
+    assert common.rel_l2(a.params_full_precision.cpu().numpy(), b.params_full_precision.cpu().numpy()) < 1e-2
+    assert torch.equal(a.param_steps[: a.info.n_params_mlp], b.param_steps[: b.info.n_params_mlp])
+    assert a.graph_stats() == (4, 40), a.graph_stats()       # 2 buffer sets x 2 plan versions captured, every step replayed
+    assert b.graph_stats() == (0, 0)
+    # a caller that captures the step into a graph of its own gets plain launches inside its capture (no nested capture)
+    x, t = batches[0]
+    s = torch.cuda.Stream(device=dev)
+    s.wait_stream(torch.cuda.current_stream(dev))
+    with torch.cuda.stream(s):
+        a.training_step(x, t)          # warm-up on the side stream: workspace and streams exist before the capture
+    torch.cuda.current_stream(dev).wait_stream(s)
+    torch.cuda.synchronize(dev)
+    before = a.graph_stats()
+    step0 = a.current_step
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, stream=s):
+        a.training_step(x, t)
+    assert a.graph_stats() == before   # nothing captured or replayed by the library while the caller captures
+    g.replay(); torch.cuda.synchronize(dev)
+    assert np.isfinite(a.loss()) and a.current_step == step0 + 1
+
+
+def test_host_batch_pipeline_matches_resident_batches(dev):
+    """tcnn_b200_host_batch_begin / _end (Trainer.training_step_host): batches in pinned host memory, next batch prefetched under the
+    running step, loss word copied back asynchronously.  Same seed and batches as a trainer fed resident tensors: same losses."""
+    import tinycudann as tcnn
+    a = tcnn.create_from_config(2, 3, common.CONFIG_SHIPPED, seed=1337, device=dev).trainer
+    b = tcnn.create_from_config(2, 3, common.CONFIG_SHIPPED, seed=1337, device=dev).trainer
+    B, n = 1 << 12, 9
+    host = [tuple(torch.from_numpy(v).pin_memory() for v in common.synth_inputs(B, 2, 3, seed=90 + i)) for i in range(3)]
+    hl = torch.zeros(n, dtype=torch.float32).pin_memory()
+    lb = []
+    for i in range(n):
+        cur = host[i % 3]
+        nxt = host[(i + 1) % 3] if (i + 1 < n and i != 4) else None       # step 5 arrives un-prefetched: staged by its own begin
+        a.training_step_host(cur[0], cur[1], next_batch=nxt, host_loss=hl[i: i + 1], join=(i + 1 == n))
+        b.training_step(cur[0].to(dev), cur[1].to(dev)); lb.append(b.loss())
+    torch.cuda.current_stream(dev).synchronize()
+    assert np.allclose(hl.numpy(), lb, rtol=5e-3), (hl, lb)
+    assert hl[-1] < hl[0]
+    # the same pinned buffer refilled by the host between steps (one buffer, no prefetch): the data of the call is what counts
+    x, t = host[0]
+    ref = b
+    for i in range(3):
+        x.copy_(host[(i + 1) % 3][0]); t.copy_(host[(i + 1) % 3][1])
+        a.training_step_host(x, t, host_loss=hl[0:1], join=True)
+        torch.cuda.current_stream(dev).synchronize()              # the host may only rewrite the buffer after the copy has run
+        ref.training_step(x.to(dev), t.to(dev))
+        assert abs(float(hl[0]) - ref.loss()) <= 5e-3 * ref.loss()
+    with pytest.raises(RuntimeError, match="fp32 host tensors"):
+        a.training_step_host(x.to(dev), t)
+
+
 def _snapshot_golden():
     meta = json.load(open(os.path.join(GOLDEN, "snapshot_small_2d.json")))
     return meta, os.path.join(GOLDEN, "snapshot_small_2d.msgpack")

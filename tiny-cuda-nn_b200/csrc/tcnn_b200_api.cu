@@ -63,6 +63,26 @@ struct tcnn_b200_plan {
 	bool profiling = false;
 	struct Span { int kind; cudaEvent_t e0, e1; };
 	std::vector<Span> spans;
+	// static graphs of tcnn_b200_training_step, one per (batch size, buffers) - see StepGraph below
+	uint64_t version = 0;           // bumped by every setter that changes what a captured step would do
+	int graph_mode = -1;            // -1: environment TCNN_B200_GRAPH (default on), 0: off, 1: on
+	cudaStream_t capture_stream = nullptr;
+	std::vector<struct StepGraph*> step_graphs;
+	uint64_t graph_clock = 0;
+	uint32_t graph_captures = 0, graph_replays = 0, graph_misses_in_a_row = 0;
+	bool graph_broken = false;      // capture failed or the Adam nodes were not found: direct launches from then on
+	// host-batch pipeline (tcnn_b200_host_batch_begin / _end): two staging slots, copy engines on their own streams
+	struct HostPipe {
+		bool ready = false;
+		cudaStream_t h2d = nullptr, d2h = nullptr;
+		cudaEvent_t filled[2] = {}, consumed[2] = {}, loss_written[2] = {}, loss_copied[2] = {};
+		const void* holds_x[2] = {nullptr, nullptr};   // host batch a slot was filled from (or is being filled from)
+		const void* holds_t[2] = {nullptr, nullptr};
+		uint32_t holds_B[2] = {0, 0};
+		void* staging[2] = {nullptr, nullptr};
+		uint32_t slot = 0;          // slot of the step between begin and end
+		bool open = false;
+	} pipe;
 };
 
 enum PlanKind { PLAN_FULL = 0, PLAN_NETWORK = 1, PLAN_ENCODING = 2 };
@@ -375,7 +395,17 @@ extern "C" int tcnn_b200_plan_create(const char* json_utf8, uint32_t n_input_dim
 	API_END
 }
 
+struct StepGraph;
+static void drop_step_graphs(tcnn_b200_plan* p);
 extern "C" void tcnn_b200_plan_destroy(tcnn_b200_plan* plan) {
+	if (plan) {
+		drop_step_graphs(plan);
+		if (plan->capture_stream) cudaStreamDestroy(plan->capture_stream);
+		if (plan->pipe.ready) {
+			cudaStreamDestroy(plan->pipe.h2d); cudaStreamDestroy(plan->pipe.d2h);
+			for (int k = 0; k < 2; ++k) { cudaEventDestroy(plan->pipe.filled[k]); cudaEventDestroy(plan->pipe.consumed[k]); cudaEventDestroy(plan->pipe.loss_written[k]); cudaEventDestroy(plan->pipe.loss_copied[k]); }
+		}
+	}
 	if (plan && plan->aux_ready) {
 		cudaStreamDestroy(plan->aux);
 		for (auto& e : plan->ev) cudaEventDestroy(e);
@@ -403,6 +433,7 @@ extern "C" int tcnn_b200_plan_set_max_level(tcnn_b200_plan* plan, float max_leve
 	for (uint32_t l = 0; l < L; ++l) if (!((float)l >= scaled + 1e-3f)) active = l + 1;
 	plan->grid.n_levels = active;
 	plan->grid.n_features = active * F;
+	++plan->version;
 	API_END
 }
 
@@ -417,6 +448,7 @@ extern "C" int tcnn_b200_plan_update_optimizer(tcnn_b200_plan* plan, const char*
 	API_BEGIN
 	CHECK(plan && json_utf8, "null argument");
 	parse_optimizer(plan, jsonmini::parse(json_utf8));
+	++plan->version;
 	API_END
 }
 
@@ -1161,6 +1193,17 @@ extern "C" int tcnn_b200_training_fwd_bwd(const tcnn_b200_plan* plan, void* stre
 
 // ---- optimizer --------------------------------------------------------------------------------------------
 struct AdamBuffers { float* master; __half* params; __half* grads; float* m; float* v; uint32_t* steps; };
+// the members of AdamArgs that change from one optimizer step to the next (everything else is fixed per plan and buffers)
+static void set_adam_step(const tcnn_b200_plan* plan, AdamArgs& a, uint32_t adam_step_count) {
+	const tcnn_b200_info& in = plan->info;
+	a.lower_lr_bound = 0.f; a.upper_lr_bound = std::numeric_limits<float>::max();
+	if (plan->adabound) { // optimizers/adam.h:156-160
+		a.lower_lr_bound = 0.1f - 0.1f / ((1 - in.beta2) * (float)adam_step_count + 1);
+		a.upper_lr_bound = 0.1f + 0.1f / ((1 - in.beta2) * (float)adam_step_count);
+	}
+	a.global_step = adam_step_count;
+	a.global_correction = std::sqrt(1 - std::pow(in.beta2, (float)adam_step_count)) / (1 - std::pow(in.beta1, (float)adam_step_count));
+}
 static AdamArgs adam_args(const tcnn_b200_plan* plan, float grad_divisor, uint32_t adam_step_count, const AdamBuffers& b,
 	int zero_grid_grads, uint32_t begin, uint32_t end) {
 	const tcnn_b200_info& in = plan->info;
@@ -1171,11 +1214,7 @@ static AdamArgs adam_args(const tcnn_b200_plan* plan, float grad_divisor, uint32
 	a.loss_scale = grad_divisor;
 	a.learning_rate = in.learning_rate; a.beta1 = in.beta1; a.beta2 = in.beta2; a.epsilon = in.epsilon; a.l2_reg = in.l2_reg;
 	a.relative_decay = in.relative_decay; a.absolute_decay = in.absolute_decay;
-	a.lower_lr_bound = 0.f; a.upper_lr_bound = std::numeric_limits<float>::max();
-	if (plan->adabound) { // optimizers/adam.h:156-160
-		a.lower_lr_bound = 0.1f - 0.1f / ((1 - in.beta2) * (float)adam_step_count + 1);
-		a.upper_lr_bound = 0.1f + 0.1f / ((1 - in.beta2) * (float)adam_step_count);
-	}
+	set_adam_step(plan, a, adam_step_count);
 	a.weight_clip = plan->weight_clip;
 	a.non_matrix_lr_factor = plan->non_matrix_lr_factor;
 	a.optimize_matrix = plan->optimize_matrix_params ? 1 : 0; a.optimize_non_matrix = plan->optimize_non_matrix_params ? 1 : 0;
@@ -1184,8 +1223,6 @@ static AdamArgs adam_args(const tcnn_b200_plan* plan, float grad_divisor, uint32
 	const float mant = std::frexp(grad_divisor, &e);
 	a.inv_loss_scale = (mant == 0.5f) ? 1.0f / grad_divisor : 0.f; // exact only for powers of two
 	a.log2_beta1 = std::log2(in.beta1); a.log2_beta2 = std::log2(in.beta2);
-	a.global_step = adam_step_count;
-	a.global_correction = std::sqrt(1 - std::pow(in.beta2, (float)adam_step_count)) / (1 - std::pow(in.beta1, (float)adam_step_count));
 	a.master = b.master; a.params = b.params; a.grads = b.grads; a.m = b.m; a.v = b.v; a.steps = b.steps;
 	return a;
 }
@@ -1242,15 +1279,10 @@ extern "C" int tcnn_b200_adam_step_range(const tcnn_b200_plan* plan, void* strea
 // complete its Adam update starts on a second stream.  The scatter is bound by L2 atomic throughput (ncu r01b: lts 68 %,
 // DRAM 5 %), Adam by HBM (DRAM 63 %), so the two overlap almost perfectly.  Requires zeroed grid gradients on entry
 // (tcnn_b200_adam_step / this function leave them zeroed).
-extern "C" int tcnn_b200_training_step(const tcnn_b200_plan* plan, void* stream_, uint32_t B, const float* x, const float* target,
+static void training_step_launches(const tcnn_b200_plan* plan, cudaStream_t main, uint32_t B, const float* x, const float* target,
 	float loss_scale, uint32_t adam_step_count, float* params_fp32, void* params_fp16, void* grads_fp16, float* first_moments, float* second_moments,
 	uint32_t* param_steps, float* loss_out, void* output_fp16, void* workspace) {
-	API_BEGIN
-	require_device(plan); check_batch(B);
-	CHECK(plan->kind == PLAN_FULL, "training entry points need an encoding and a network");
-	CHECK(x && target && params_fp32 && params_fp16 && grads_fp16 && first_moments && second_moments && param_steps && workspace, "null argument");
-	ensure_aux(plan);
-	cudaStream_t main = (cudaStream_t)stream_, aux = plan->aux;
+	cudaStream_t aux = plan->aux;
 	const cudaEvent_t* ev = plan->ev;
 	const Workspace w = carve(plan, B, workspace);
 	const tcnn_b200_info& in = plan->info;
@@ -1272,16 +1304,19 @@ extern "C" int tcnn_b200_training_step(const tcnn_b200_plan* plan, void* stream_
 		encode_forward(plan, main, B, x, p + in.n_params_mlp, w.encoded, w.replicas, replica_bytes_of(plan, gp));
 		a.dL_dinput = nullptr; a.positions = x; a.grid_grad = gg; a.replicas = w.replicas;
 		launch_mlp_train_fused(plan, main, a, mlp_grid, gp);
+		// while the per-kernel timer is on, the small kernel runs in line: on the second stream its event pair would measure how long
+		// it waits for SMs next to the table-wide Adam kernel, not its own duration
+		cudaStream_t side = plan->profiling ? main : aux;
 		CUDA_OK(cudaEventRecord(ev[0], main));
-		CUDA_OK(cudaStreamWaitEvent(aux, ev[0], 0));
+		CUDA_OK(cudaStreamWaitEvent(side, ev[0], 0));
 		{
-			ProfileScope prof(plan, aux, PK_FINALIZE);
+			ProfileScope prof(plan, side, PK_FINALIZE);
 			const AdamArgs am = adam_args(plan, loss_scale, adam_step_count, ab, 1, 0u, (uint32_t)in.n_params_mlp);
-			mlp_finalize_adam_kernel<<<((uint32_t)in.n_params_mlp + 31) / 32, 256, 0, aux>>>((uint32_t)in.n_params_mlp, mlp_grid, w.dw_partials,
+			mlp_finalize_adam_kernel<<<((uint32_t)in.n_params_mlp + 31) / 32, 256, 0, side>>>((uint32_t)in.n_params_mlp, mlp_grid, w.dw_partials,
 				loss_out ? w.loss_partials : nullptr, loss_out, am, mlp_grid);
 			launch_check("mlp_finalize_adam_kernel");
 		}
-		CUDA_OK(cudaEventRecord(ev[1], aux));
+		CUDA_OK(cudaEventRecord(ev[1], side));
 		if (replicas_are_table_prefix(gp) && in.n_params_mlp % 4 == 0) { // replica sums inside the optimizer kernel
 			adam_launch(plan, main, loss_scale, adam_step_count, ab, 1, (uint32_t)in.n_params_mlp, (uint32_t)in.n_params, &gp, w.replicas);
 		} else {
@@ -1289,7 +1324,7 @@ extern "C" int tcnn_b200_training_step(const tcnn_b200_plan* plan, void* stream_
 			adam_launch(plan, main, loss_scale, adam_step_count, ab, 1, (uint32_t)in.n_params_mlp, (uint32_t)in.n_params);
 		}
 		CUDA_OK(cudaStreamWaitEvent(main, ev[1], 0)); // join
-		return 0;
+		return;
 	}
 	if (plan->enc_kind != ENC_GRID) { // parameter-free encoding: encode -> MLP forward/backward -> weight-gradient reduction + Adam in one kernel
 		encode_any(plan, main, B, x, nullptr, w.encoded, is_wide(plan));
@@ -1300,7 +1335,7 @@ extern "C" int tcnn_b200_training_step(const tcnn_b200_plan* plan, void* stream_
 		mlp_finalize_adam_kernel<<<((uint32_t)in.n_params_mlp + 31) / 32, 256, 0, main>>>((uint32_t)in.n_params_mlp, mlp_grid, w.dw_partials,
 			loss_out ? w.loss_partials : nullptr, loss_out, am, mlp_loss_parts(plan, B / MLP_TILE, mlp_grid));
 		launch_check("mlp_finalize_adam_kernel");
-		return 0;
+		return;
 	}
 	backward_prepare(plan, main, gp, gg, /*zero_first=*/0, w.replicas);
 	encode_forward(plan, main, B, x, p + in.n_params_mlp, w.encoded, nullptr, 0, is_wide(plan));
@@ -1328,6 +1363,253 @@ extern "C" int tcnn_b200_training_step(const tcnn_b200_plan* plan, void* stream_
 	}
 	CUDA_OK(cudaEventRecord(ev[6], aux));
 	CUDA_OK(cudaStreamWaitEvent(main, ev[6], 0)); // join
+}
+
+// ---- static graph of the training step (replaces cuda_graph.h:65-153 of the reference, which captures Trainer::training_step) ----
+// One instantiated graph per (batch size, buffer addresses, loss scale, plan version): captured on an internal stream (the caller's
+// may be the legacy default stream, which cannot be captured), launched on the caller's.  The only values that change from step
+// to step are the four Adam scalars of set_adam_step; they are patched into the graph's optimizer kernel nodes before every launch
+// (cudaGraphExecKernelNodeSetParams).  Pointer sets are cached least-recently-used; a caller that passes new buffers every step
+// stops being captured after GRAPH_MAX_MISSES misses in a row.
+struct StepKey {
+	uint32_t B; float loss_scale; uint64_t version;
+	const void* ptr[11];
+	bool operator==(const StepKey& o) const { return B == o.B && loss_scale == o.loss_scale && version == o.version && !memcmp(ptr, o.ptr, sizeof(ptr)); }
+};
+struct StepGraph {
+	StepKey key{};
+	cudaGraph_t graph = nullptr;
+	cudaGraphExec_t exec = nullptr;
+	uint64_t last_use = 0;
+	struct OptimizerNode {
+		cudaGraphNode_t node; cudaKernelNodeParams params;
+		std::vector<std::vector<unsigned char>> args; std::vector<void*> arg_ptrs; size_t adam_arg;
+	};
+	std::vector<OptimizerNode> optimizer_nodes;
+	~StepGraph() { if (exec) cudaGraphExecDestroy(exec); if (graph) cudaGraphDestroy(graph); }
+};
+static constexpr size_t GRAPH_CACHE = 8;
+static constexpr uint32_t GRAPH_MAX_MISSES = 32;
+
+static bool graphs_enabled(const tcnn_b200_plan* plan) {
+	if (plan->graph_broken || plan->profiling) return false;
+	if (plan->graph_mode >= 0) return plan->graph_mode != 0;
+	static const bool env_on = [] { const char* e = getenv("TCNN_B200_GRAPH"); return !(e && e[0] == '0'); }();
+	return env_on;
+}
+
+static void drop_step_graphs(tcnn_b200_plan* p) {
+	for (StepGraph* g : p->step_graphs) delete g;
+	p->step_graphs.clear();
+}
+
+// copies the arguments of the optimizer kernels out of a captured graph so that they can be re-issued with new Adam scalars
+static void collect_optimizer_nodes(StepGraph& sg) {
+	size_t n = 0;
+	CUDA_OK(cudaGraphGetNodes(sg.graph, nullptr, &n));
+	std::vector<cudaGraphNode_t> nodes(n);
+	CUDA_OK(cudaGraphGetNodes(sg.graph, nodes.data(), &n));
+	for (cudaGraphNode_t node : nodes) {
+		cudaGraphNodeType type;
+		CUDA_OK(cudaGraphNodeGetType(node, &type));
+		if (type != cudaGraphNodeTypeKernel) continue;
+		cudaKernelNodeParams kp{};
+		CUDA_OK(cudaGraphKernelNodeGetParams(node, &kp));
+		std::vector<size_t> sizes; size_t adam_arg;
+		if (kp.func == (void*)adam_kernel) { sizes = {sizeof(AdamArgs)}; adam_arg = 0; }
+		else if (kp.func == (void*)mlp_finalize_adam_kernel) { sizes = {4, 4, sizeof(void*), sizeof(void*), sizeof(void*), sizeof(AdamArgs), 4}; adam_arg = 5; }
+		else continue;
+		CHECK(kp.kernelParams != nullptr, "graph kernel node without a parameter array");
+		sg.optimizer_nodes.emplace_back();
+		StepGraph::OptimizerNode& on = sg.optimizer_nodes.back();
+		on.node = node; on.params = kp; on.adam_arg = adam_arg;
+		for (size_t k = 0; k < sizes.size(); ++k) {
+			const unsigned char* src = (const unsigned char*)kp.kernelParams[k];
+			on.args.emplace_back(src, src + sizes[k]);
+		}
+		for (auto& a : on.args) on.arg_ptrs.push_back(a.data());
+		on.params.kernelParams = on.arg_ptrs.data();
+		on.params.extra = nullptr;
+	}
+}
+
+extern "C" int tcnn_b200_training_step(const tcnn_b200_plan* plan, void* stream_, uint32_t B, const float* x, const float* target,
+	float loss_scale, uint32_t adam_step_count, float* params_fp32, void* params_fp16, void* grads_fp16, float* first_moments, float* second_moments,
+	uint32_t* param_steps, float* loss_out, void* output_fp16, void* workspace) {
+	API_BEGIN
+	require_device(plan); check_batch(B);
+	CHECK(plan->kind == PLAN_FULL, "training entry points need an encoding and a network");
+	CHECK(x && target && params_fp32 && params_fp16 && grads_fp16 && first_moments && second_moments && param_steps && workspace, "null argument");
+	ensure_aux(plan);
+	cudaStream_t main = (cudaStream_t)stream_;
+	tcnn_b200_plan* mp = const_cast<tcnn_b200_plan*>(plan);
+	auto direct = [&] {
+		training_step_launches(plan, main, B, x, target, loss_scale, adam_step_count, params_fp32, params_fp16, grads_fp16, first_moments, second_moments,
+			param_steps, loss_out, output_fp16, workspace);
+	};
+	cudaStreamCaptureStatus capturing = cudaStreamCaptureStatusNone;
+	if (main != nullptr && main != cudaStreamLegacy) CUDA_OK(cudaStreamIsCapturing(main, &capturing));
+	if (!graphs_enabled(plan) || capturing != cudaStreamCaptureStatusNone) { direct(); return 0; } // a caller capturing us gets the plain launches
+
+	StepKey key{};
+	key.B = B; key.loss_scale = loss_scale; key.version = plan->version;
+	const void* ptrs[11] = {x, target, params_fp32, params_fp16, grads_fp16, first_moments, second_moments, param_steps, loss_out, output_fp16, workspace};
+	memcpy(key.ptr, ptrs, sizeof(ptrs));
+	StepGraph* sg = nullptr;
+	for (StepGraph* g : mp->step_graphs) if (g->key == key) { sg = g; break; }
+	if (!sg) {
+		if (++mp->graph_misses_in_a_row > GRAPH_MAX_MISSES) { // new buffers every step: capturing costs more than it saves
+			mp->graph_broken = true; drop_step_graphs(mp);
+			direct(); return 0;
+		}
+		if (mp->step_graphs.size() >= GRAPH_CACHE) {
+			size_t oldest = 0;
+			for (size_t k = 1; k < mp->step_graphs.size(); ++k) if (mp->step_graphs[k]->last_use < mp->step_graphs[oldest]->last_use) oldest = k;
+			delete mp->step_graphs[oldest];
+			mp->step_graphs.erase(mp->step_graphs.begin() + oldest);
+		}
+		if (!mp->capture_stream) CUDA_OK(cudaStreamCreateWithFlags(&mp->capture_stream, cudaStreamNonBlocking));
+		std::unique_ptr<StepGraph> fresh(new StepGraph);
+		fresh->key = key;
+		bool ok = true; std::string why;
+		CUDA_OK(cudaStreamBeginCapture(mp->capture_stream, cudaStreamCaptureModeRelaxed));
+		try {
+			training_step_launches(plan, mp->capture_stream, B, x, target, loss_scale, adam_step_count, params_fp32, params_fp16, grads_fp16, first_moments,
+				second_moments, param_steps, loss_out, output_fp16, workspace);
+		} catch (const std::exception& e) { ok = false; why = e.what(); }
+		const cudaError_t end = cudaStreamEndCapture(mp->capture_stream, &fresh->graph);
+		if (ok && end != cudaSuccess) { ok = false; why = std::string("cudaStreamEndCapture: ") + cudaGetErrorString(end); }
+		if (ok) {
+			const cudaError_t inst = cudaGraphInstantiate(&fresh->exec, fresh->graph, 0);
+			if (inst != cudaSuccess) { ok = false; why = std::string("cudaGraphInstantiate: ") + cudaGetErrorString(inst); }
+		}
+		if (ok) {
+			collect_optimizer_nodes(*fresh);
+			if (fresh->optimizer_nodes.empty()) { ok = false; why = "no optimizer kernel node found in the captured step"; }
+		}
+		if (!ok) { // never silently wrong: forget graphs for this plan and say why once
+			cudaGetLastError();
+			mp->graph_broken = true; drop_step_graphs(mp);
+			fprintf(stderr, "tcnn_b200: training-step graph disabled (%s)\n", why.c_str());
+			direct(); return 0;
+		}
+		sg = fresh.release();
+		mp->step_graphs.push_back(sg);
+		++mp->graph_captures;
+	} else {
+		mp->graph_misses_in_a_row = 0;
+	}
+	for (StepGraph::OptimizerNode& on : sg->optimizer_nodes) {
+		AdamArgs a;
+		memcpy(&a, on.args[on.adam_arg].data(), sizeof(AdamArgs));
+		set_adam_step(plan, a, adam_step_count);
+		memcpy(on.args[on.adam_arg].data(), &a, sizeof(AdamArgs));
+		CUDA_OK(cudaGraphExecKernelNodeSetParams(sg->exec, on.node, &on.params));
+	}
+	sg->last_use = ++mp->graph_clock;
+	CUDA_OK(cudaGraphLaunch(sg->exec, main));
+	++mp->graph_replays;
+	API_END
+}
+
+// mode: 0 = plain launches, 1 = static graphs, -1 = environment TCNN_B200_GRAPH (default: graphs)
+extern "C" int tcnn_b200_plan_set_graph_mode(tcnn_b200_plan* plan, int mode) {
+	API_BEGIN
+	CHECK(plan && mode >= -1 && mode <= 1, "bad argument");
+	plan->graph_mode = mode;
+	plan->graph_broken = false; plan->graph_misses_in_a_row = 0;
+	drop_step_graphs(plan);
+	API_END
+}
+extern "C" int tcnn_b200_plan_graph_stats(const tcnn_b200_plan* plan, uint32_t* captures, uint32_t* replays) {
+	API_BEGIN
+	CHECK(plan && captures && replays, "null argument");
+	*captures = plan->graph_captures; *replays = plan->graph_replays;
+	API_END
+}
+
+
+// ---- batches that live in host memory ------------------------------------------------------------------------------------
+// The reference's hosts generate or load their batches on the device; a host that holds them in (pinned) host memory needs the
+// copy of step i+1 under the compute of step i and the loss back without a device-wide sync.  begin/end wrap ANY of the step
+// entry points: begin stages this step's batch (unless an earlier begin already prefetched it), starts the copy of the next one
+// into the other slot, makes `stream` wait for the data and hands out device pointers; end releases the slot and sends the
+// 4-byte loss to the host on a third stream.  Nothing is allocated: the caller passes `staging` (tcnn_b200_host_staging_bytes).
+static size_t host_slot_bytes(const tcnn_b200_plan* plan, uint32_t B) {
+	return align256((size_t)B * plan->info.n_input_dims * 4) + align256((size_t)B * plan->info.n_output_dims * 4) + 256;
+}
+extern "C" size_t tcnn_b200_host_staging_bytes(const tcnn_b200_plan* plan, uint32_t B) { return plan ? 2 * host_slot_bytes(plan, B) : 0; }
+
+static void ensure_pipe(tcnn_b200_plan* p) {
+	if (p->pipe.ready) return;
+	CUDA_OK(cudaStreamCreateWithFlags(&p->pipe.h2d, cudaStreamNonBlocking));
+	CUDA_OK(cudaStreamCreateWithFlags(&p->pipe.d2h, cudaStreamNonBlocking));
+	for (int k = 0; k < 2; ++k) {
+		CUDA_OK(cudaEventCreateWithFlags(&p->pipe.filled[k], cudaEventDisableTiming));
+		CUDA_OK(cudaEventCreateWithFlags(&p->pipe.consumed[k], cudaEventDisableTiming));
+		CUDA_OK(cudaEventCreateWithFlags(&p->pipe.loss_written[k], cudaEventDisableTiming));
+		CUDA_OK(cudaEventCreateWithFlags(&p->pipe.loss_copied[k], cudaEventDisableTiming));
+	}
+	p->pipe.ready = true;
+}
+static void pipe_fill(tcnn_b200_plan* p, int k, uint32_t B, const float* hx, const float* ht) {
+	auto& q = p->pipe;
+	const size_t xb = (size_t)B * p->info.n_input_dims * 4, tb = (size_t)B * p->info.n_output_dims * 4;
+	char* slot = (char*)q.staging[k];
+	CUDA_OK(cudaStreamWaitEvent(q.h2d, q.consumed[k], 0));        // the step that last read this slot has finished
+	CUDA_OK(cudaMemcpyAsync(slot, hx, xb, cudaMemcpyHostToDevice, q.h2d));
+	CUDA_OK(cudaMemcpyAsync(slot + align256(xb), ht, tb, cudaMemcpyHostToDevice, q.h2d));
+	CUDA_OK(cudaEventRecord(q.filled[k], q.h2d));
+	q.holds_x[k] = hx; q.holds_t[k] = ht; q.holds_B[k] = B;
+}
+
+extern "C" int tcnn_b200_host_batch_begin(tcnn_b200_plan* plan, void* stream_, uint32_t B, const float* host_x, const float* host_target,
+	const float* next_host_x, const float* next_host_target, void* staging, float** device_x, float** device_target, float** device_loss) {
+	API_BEGIN
+	CHECK(plan && host_x && host_target && staging && device_x && device_target && device_loss, "null argument");
+	require_device(plan); check_batch(B);
+	CHECK(!plan->pipe.open, "tcnn_b200_host_batch_begin called twice without tcnn_b200_host_batch_end");
+	CHECK((next_host_x == nullptr) == (next_host_target == nullptr), "next batch needs both pointers");
+	ensure_pipe(plan);
+	auto& q = plan->pipe;
+	cudaStream_t main = (cudaStream_t)stream_;
+	const size_t slot_bytes = host_slot_bytes(plan, B);
+	if (q.staging[0] != staging || q.staging[1] != (char*)staging + slot_bytes) { // new staging buffer (or batch size): nothing is prefetched
+		q.staging[0] = staging; q.staging[1] = (char*)staging + slot_bytes;
+		q.holds_x[0] = q.holds_x[1] = nullptr;
+	}
+	// the slot that already holds this batch (prefetched by the previous begin), else the one not used by the previous step
+	int k = -1;
+	for (int c = 0; c < 2; ++c) if (q.holds_x[c] == host_x && q.holds_t[c] == host_target && q.holds_B[c] == B) k = c;
+	if (k < 0) { k = (int)(q.slot ^ 1u); pipe_fill(plan, k, B, host_x, host_target); }
+	if (next_host_x) pipe_fill(plan, k ^ 1, B, next_host_x, next_host_target);
+	const size_t xb = (size_t)B * plan->info.n_input_dims * 4, tb = (size_t)B * plan->info.n_output_dims * 4;
+	char* slot = (char*)q.staging[k];
+	CUDA_OK(cudaStreamWaitEvent(main, q.filled[k], 0));
+	CUDA_OK(cudaStreamWaitEvent(main, q.loss_copied[k], 0));        // the loss word of this slot (two steps ago) has left the device
+	*device_x = (float*)slot; *device_target = (float*)(slot + align256(xb)); *device_loss = (float*)(slot + align256(xb) + align256(tb));
+	q.slot = (uint32_t)k; q.open = true;
+	q.holds_x[k] = nullptr;                                          // consumed by this step: a later begin with the same host pointer copies again
+	API_END
+}
+
+extern "C" int tcnn_b200_host_batch_end(tcnn_b200_plan* plan, void* stream_, float* host_loss_out, int join) {
+	API_BEGIN
+	CHECK(plan && plan->pipe.open, "tcnn_b200_host_batch_end without tcnn_b200_host_batch_begin");
+	auto& q = plan->pipe;
+	cudaStream_t main = (cudaStream_t)stream_;
+	const int k = (int)q.slot;
+	q.open = false;
+	CUDA_OK(cudaEventRecord(q.consumed[k], main));
+	if (host_loss_out) {
+		const size_t xb = (size_t)q.holds_B[k] * plan->info.n_input_dims * 4, tb = (size_t)q.holds_B[k] * plan->info.n_output_dims * 4;
+		const float* dev_loss = (const float*)((char*)q.staging[k] + align256(xb) + align256(tb));
+		CUDA_OK(cudaEventRecord(q.loss_written[k], main));
+		CUDA_OK(cudaStreamWaitEvent(q.d2h, q.loss_written[k], 0));
+		CUDA_OK(cudaMemcpyAsync(host_loss_out, dev_loss, 4, cudaMemcpyDeviceToHost, q.d2h));
+		CUDA_OK(cudaEventRecord(q.loss_copied[k], q.d2h));
+		if (join) CUDA_OK(cudaStreamWaitEvent(main, q.loss_copied[k], 0)); // the read-back ends before anything the caller enqueues next
+	}
 	API_END
 }
 

@@ -206,6 +206,53 @@ class Trainer:
         self._grid_grads_clean = True
         torch.cuda.synchronize(self.device)
 
+    # Batches in pinned host memory: H2D of the next batch under this step, loss back on its own stream (tcnn_b200_host_batch_begin/_end).
+    def training_step_host(self, host_input: torch.Tensor, host_target: torch.Tensor, next_batch=None, host_loss: torch.Tensor | None = None,
+                           join: bool = False, **step_kwargs):
+        """One training step on a batch held in (pinned) host memory.  `next_batch` = (host_input, host_target) of the following
+        call: its copy runs under this step's compute.  `host_loss` = pinned fp32 tensor of one element that receives this step's
+        loss asynchronously (valid after a synchronize; `join=True` makes the current stream wait for it)."""
+        import ctypes as C
+        B = host_input.shape[0]
+        if host_input.is_cuda or host_target.is_cuda or host_input.dtype != torch.float32 or host_target.dtype != torch.float32:
+            raise RuntimeError("training_step_host takes fp32 host tensors")
+        need = int(self.lib.tcnn_b200_host_staging_bytes(self.native.handle, B))
+        st = getattr(self, "_host_staging", None)
+        if st is None or st.numel() < need:
+            st = self._host_staging = torch.empty(need, dtype=torch.uint8, device=self.device)
+            self._host_views = {}
+        dx, dt, dl = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        nx, nt = (next_batch if next_batch is not None else (None, None))
+        check(self.lib.tcnn_b200_host_batch_begin(self.native.handle, _stream_ptr(), B, host_input.data_ptr(), host_target.data_ptr(),
+                                                  nx.data_ptr() if nx is not None else None, nt.data_ptr() if nt is not None else None,
+                                                  st.data_ptr(), C.byref(dx), C.byref(dt), C.byref(dl)))
+        key = (dx.value, B)
+        views = self._host_views.get(key)
+        if views is None:
+            base = st.data_ptr()
+            def view(p, n, shape):
+                return st[p - base: p - base + 4 * n].view(torch.float32).view(shape)
+            views = self._host_views[key] = (view(dx.value, B * host_input.shape[1], (B, host_input.shape[1])),
+                                             view(dt.value, B * host_target.shape[1], (B, host_target.shape[1])), view(dl.value, 1, (1,)))
+        keep = self.loss_value
+        self.loss_value = views[2]
+        try:
+            self.training_step(views[0], views[1], **step_kwargs)
+        finally:
+            self.loss_value = keep
+            check(self.lib.tcnn_b200_host_batch_end(self.native.handle, _stream_ptr(), host_loss.data_ptr() if host_loss is not None else None, 1 if join else 0))
+        return self
+
+    # static CUDA graphs behind the fused step (cuda_graph.h:65-153 of the reference): 1 on, 0 off, -1 environment TCNN_B200_GRAPH
+    def set_graph_mode(self, mode: int):
+        check(self.lib.tcnn_b200_plan_set_graph_mode(self.native.handle, int(mode)))
+
+    def graph_stats(self) -> tuple[int, int]:
+        import ctypes as C
+        captures, replays = C.c_uint32(0), C.c_uint32(0)
+        check(self.lib.tcnn_b200_plan_graph_stats(self.native.handle, C.byref(captures), C.byref(replays)))
+        return captures.value, replays.value
+
     def update_hyperparams(self, params: dict):
         check(self.lib.tcnn_b200_plan_update_optimizer(self.native.handle, json.dumps(params).encode()))
         self.native.refresh_info()
