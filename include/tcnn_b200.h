@@ -72,6 +72,12 @@ int tcnn_b200_plan_info(const tcnn_b200_plan* plan, tcnn_b200_info* info);
  * level >= max_level * n_levels + 1e-3 encode to zero and receive no gradient (grid.h:69-82, 236-243).  Takes effect for
  * every later call on this plan.  The per-sample variant (set_max_level_gpu) is not implemented. */
 int tcnn_b200_plan_set_max_level(tcnn_b200_plan* plan, float max_level);
+/* GridEncoding::set_max_level_gpu (encodings/grid_interface.h:113-115): `max_level_per_sample` is a device array with one value
+ * per sample of every batch passed from now on (sample i sees the levels l < max_level[i] * n_levels + 1e-3, grid.h:69-75); NULL
+ * switches it off.  The pointer is kept, not copied.  Plans with a per-sample max level, with a hash other than CoherentPrime
+ * ("hash": Prime / ReversedPrime / Rng, common_device.h:631-688) or with n_features_per_level = 1 (gradients accumulated in fp32
+ * and cast, grid.h:655-666, 877-885) run general one-thread-per-(sample, level) kernels instead of the specialised ones. */
+int tcnn_b200_plan_set_max_level_gpu(tcnn_b200_plan* plan, const float* max_level_per_sample);
 /* Trainer::update_hyperparams (trainer.h:213-216): JSON object with optimizer keys (learning_rate, beta1, ...). */
 int tcnn_b200_plan_update_optimizer(tcnn_b200_plan* plan, const char* json_utf8);
 
@@ -130,6 +136,11 @@ int tcnn_b200_forward(const tcnn_b200_plan* plan, void* stream, uint32_t batch_s
  * kernel_grid_backward_input (grid.h:322-349) with dy/dx (grid.h:171-211) recomputed on the fly instead of stored. */
 int tcnn_b200_backward(const tcnn_b200_plan* plan, void* stream, uint32_t batch_size, const float* x, const void* params_fp16,
                        const void* dL_doutput_fp16, void* dL_dparams_fp16, float* dL_dinput, void* workspace);
+/* The same with an explicit GradientMode (object.h:115-119): 0 = Ignore (no parameter gradients), 1 = Overwrite, 2 = Accumulate:
+ * the weight gradients are added to what dL_dparams holds (the reference's GEMMs with beta = 1, src/fully_fused_mlp.cu:769) and
+ * the grid gradients are scattered without the memset in front (grid.h:857-859). */
+int tcnn_b200_backward_mode(const tcnn_b200_plan* plan, void* stream, uint32_t batch_size, const float* x, const void* params_fp16,
+                            const void* dL_doutput_fp16, void* dL_dparams_fp16, float* dL_dinput, void* workspace, int gradient_mode);
 
 /* DifferentiableObject::backward_backward_input (object.h:208-240) for the stand-alone grid encoding
  * (encodings/grid.h:351-650, 902-1026): the backward pass of dL/dx = sum_k dL/dy_k * dy_k/dx.  Given dL_ddLdinput

@@ -95,7 +95,7 @@ __global__ void synth_target(uint32_t n, uint32_t n_in, uint32_t n_out, const fl
 }
 
 // Indices as the reference's own device functions compute them (common_device.h:690-718, 825-868).
-template <uint32_t D>
+template <uint32_t D, HashType HASH = HashType::CoherentPrime>
 __global__ void dump_indices(uint32_t n, uint32_t n_levels, const uint32_t* __restrict__ hashmap_sizes, uint32_t base_resolution,
 	float log2_per_level_scale, const float* __restrict__ x, uint32_t* __restrict__ idx_out, float* __restrict__ scale_out, uint32_t* __restrict__ res_out, GridType grid_type) {
 	const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
@@ -110,7 +110,7 @@ __global__ void dump_indices(uint32_t n, uint32_t n_levels, const uint32_t* __re
 	for (uint32_t c = 0; c < (1u << D); ++c) {
 		uvec<D> p;
 		for (uint32_t d = 0; d < D; ++d) p[d] = pos_grid[d] + ((c >> d) & 1u);
-		idx_out[((size_t)level * n + i) * (1u << D) + c] = grid_index<D, HashType::CoherentPrime>(grid_type, hashmap_sizes[level], resolution, p);
+		idx_out[((size_t)level * n + i) * (1u << D) + c] = grid_index<D, HASH>(grid_type, hashmap_sizes[level], resolution, p);
 	}
 }
 
@@ -173,6 +173,16 @@ static int mode_dump(int argc, char** argv) {
 		if (!ge) { std::cerr << "dump: REF_MAX_LEVEL needs a grid encoding\n"; return 2; }
 		ge->set_max_level(std::stof(ml));
 	}
+	GPUMemory<float> max_level_per_sample;
+	if (getenv("REF_MAX_LEVEL_GPU")) { // GridEncoding::set_max_level_gpu (grid_interface.h:109-111): sample i keeps the fraction 0.25 * (1 + i % 4) of the levels
+		auto* ge = dynamic_cast<GridEncoding<precision_t>*>(model.network->encoding().get());
+		if (!ge) { std::cerr << "dump: REF_MAX_LEVEL_GPU needs a grid encoding\n"; return 2; }
+		std::vector<float> ml(B);
+		for (uint32_t i = 0; i < B; ++i) ml[i] = 0.25f * (float)(1 + i % 4);
+		max_level_per_sample.resize(B);
+		max_level_per_sample.copy_from_host(ml);
+		ge->set_max_level_gpu(max_level_per_sample.data());
+	}
 
 	GPUMatrix<float> input(n_in, B), target(n_out, B);
 	CUDA_CHECK_THROW(cudaMemcpy(input.data(), in_raw.data(), in_raw.size(), cudaMemcpyHostToDevice));
@@ -193,8 +203,13 @@ static int mode_dump(int argc, char** argv) {
 		const dim3 blocks{div_round_up(B, 256u), L, 1};
 		const float l2s = std::log2(enc.value("per_level_scale", 2.0f));
 		const uint32_t base = enc.value("base_resolution", 16u);
-		if (n_in == 2) dump_indices<2><<<blocks, 256, 0, stream>>>(B, L, d_sizes.data(), base, l2s, input.data(), d_idx.data(), d_scale.data(), d_res.data(), grid_type_of(enc));
-		else if (n_in == 3) dump_indices<3><<<blocks, 256, 0, stream>>>(B, L, d_sizes.data(), base, l2s, input.data(), d_idx.data(), d_scale.data(), d_res.data(), grid_type_of(enc));
+		std::string hash = enc.value("hash", std::string("CoherentPrime"));
+		for (auto& c : hash) c = (char)std::tolower(c);
+#define DUMP_IDX(DD, HH) dump_indices<DD, HH><<<blocks, 256, 0, stream>>>(B, L, d_sizes.data(), base, l2s, input.data(), d_idx.data(), d_scale.data(), d_res.data(), grid_type_of(enc))
+#define DUMP_IDX_D(DD) do { if (hash == "prime") DUMP_IDX(DD, HashType::Prime); else if (hash == "reversedprime") DUMP_IDX(DD, HashType::ReversedPrime); \
+		else if (hash == "rng") DUMP_IDX(DD, HashType::Rng); else DUMP_IDX(DD, HashType::CoherentPrime); } while (0)
+		if (n_in == 2) DUMP_IDX_D(2);
+		else if (n_in == 3) DUMP_IDX_D(3);
 		else { std::cerr << "dump: n_in must be 2 or 3\n"; return 2; }
 		CUDA_CHECK_THROW(cudaStreamSynchronize(stream));
 		write_dev(out + "/indices.u32", d_idx.data(), d_idx.size());
@@ -221,6 +236,11 @@ static int mode_dump(int argc, char** argv) {
 	write_dev(out + "/grads.f16", (const uint16_t*)model.trainer->param_gradients(), P);
 	write_dev(out + "/output_padded.f16", (const uint16_t*)ctx->output.data(), (size_t)model.network->padded_output_width() * B);
 	write_dev(out + "/dL_doutput.f16", (const uint16_t*)ctx->dL_doutput.data(), (size_t)model.network->padded_output_width() * B);
+	if (getenv("REF_ACCUMULATE")) { // the same backward pass once more with GradientMode::Accumulate (object.h:115-119): gradients double
+		model.network->backward(stream, *ctx->model_ctx, input, ctx->output, ctx->dL_doutput, nullptr, false, GradientMode::Accumulate);
+		CUDA_CHECK_THROW(cudaStreamSynchronize(stream));
+		write_dev(out + "/grads_accumulated.f16", (const uint16_t*)model.trainer->param_gradients(), P);
+	}
 	if (getenv("REF_DUMP_HIDDEN")) { // post-activation hidden layers as the reference's backward pass sees them: [B][W] fp16 per layer
 		auto* nctx = static_cast<NetworkWithInputEncoding<precision_t>::ForwardContext*>(ctx->model_ctx.get());
 		const uint32_t W = cfg["network"].value("n_neurons", 128u);

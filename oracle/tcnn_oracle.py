@@ -180,6 +180,8 @@ class GridConfig:
     max_level: float = 1000.0         # GridEncoding::m_max_level (grid_interface.h:120)
     stochastic: bool = False          # "stochastic_interpolation" (grid.h:284-303): backward pass only
     interpolation: str = "Linear"     # Nearest | Linear | Smoothstep (common_device.h:801-807; Nearest: grid.h:121-139)
+    hash: str = "CoherentPrime"       # Prime | CoherentPrime | ReversedPrime | Rng (common_device.h:631-688, grid.h:1151)
+    max_level_gpu: np.ndarray | None = None   # per-sample max level (GridEncoding::set_max_level_gpu, grid.h:69-75): fp32 [B]
     offsets: np.ndarray = field(init=False)
     resolutions: np.ndarray = field(init=False)
 
@@ -240,6 +242,17 @@ class GridConfig:
         return self.interpolation.lower() == "nearest"
 
 
+def sample_level_mask(cfg: GridConfig, B: int, level: int, backward: bool = False) -> np.ndarray:
+    """Which samples see `level` when a per-sample max level is set (grid.h:69-75 forward: zero if level >= m + 1e-3;
+    grid.h:236-243 backward: skipped if level > m + 1e-3; m = max_level_gpu[i] * (L * F) / F in fp32)."""
+    if cfg.max_level_gpu is None:
+        return np.ones(B, dtype=bool)
+    F = F32(cfg.n_features_per_level)
+    m = ((cfg.max_level_gpu[:B].astype(np.float32) * F32(cfg.n_levels * cfg.n_features_per_level)).astype(np.float32) / F).astype(np.float32)
+    lim = (m + F32(1e-3)).astype(np.float32)
+    return ~(F32(level) > lim) if backward else ~(F32(level) >= lim)
+
+
 def smoothstep(v: np.ndarray) -> np.ndarray:
     """common_device.h:801-803, fp32."""
     v = v.astype(np.float32)
@@ -263,8 +276,39 @@ def pos_fract(x: np.ndarray, scale: np.float32):
     return frac, cell
 
 
-def grid_index(pos_grid: np.ndarray, hashmap_size: int, resolution: int, hashed: bool = True) -> np.ndarray:
-    """common_device.h:690-707 for GridType::Hash + CoherentPrime, including the uint32 stride wrap (SURVEY F6).
+HASH_FACTORS = {  # common_device.h:643-659
+    "prime": [1958374283, 2654435761, 805459861, 3674653429, 2097192037, 1434869437, 2165219737],
+    "coherentprime": [1, 2654435761, 805459861, 3674653429, 2097192037, 1434869437, 2165219737],
+    "reversedprime": [2165219737, 1434869437, 2097192037, 3674653429, 805459861, 2654435761, 1958374283],
+}
+
+
+def grid_hash(pos_grid: np.ndarray, hash_type: str = "CoherentPrime") -> np.ndarray:
+    """grid_hash, common_device.h:631-688: xor of pos[d] * factor[d] (uint32 wrap) for the three prime hashes; Rng: pcg32{1337} advanced
+    by xor_d(pos[d] << d * (64 / D)) (a 64-bit step), next_uint()."""
+    D = pos_grid.shape[-1]
+    name = hash_type.lower()
+    if name == "rng":
+        bits = 64 // D
+        step = np.zeros(pos_grid.shape[:-1], dtype=np.uint64)
+        for d in range(D):
+            step ^= (pos_grid[..., d].astype(np.uint64) << np.uint64(d * bits)) if d * bits < 64 else np.uint64(0)
+        flat = step.reshape(-1)
+        out = np.empty(flat.shape, dtype=np.uint32)
+        for k, st in enumerate(flat):
+            r = Pcg32(1337)
+            r.advance(int(st) - (1 << 64) if int(st) >= (1 << 63) else int(st))  # (int64_t)step
+            out[k] = r.next_uint()
+        return out.reshape(step.shape).astype(np.uint64)
+    f = HASH_FACTORS[name]
+    h = np.zeros(pos_grid.shape[:-1], dtype=np.uint64)
+    for d in range(D):
+        h ^= (pos_grid[..., d].astype(np.uint64) * np.uint64(f[d])) & np.uint64(0xFFFFFFFF)
+    return h
+
+
+def grid_index(pos_grid: np.ndarray, hashmap_size: int, resolution: int, hashed: bool = True, hash_type: str = "CoherentPrime") -> np.ndarray:
+    """common_device.h:690-707 for GridType::Hash, including the uint32 stride wrap (SURVEY F6).
 
     pos_grid: uint32 [..., D] -> uint32 [...]."""
     D = pos_grid.shape[-1]
@@ -276,10 +320,7 @@ def grid_index(pos_grid: np.ndarray, hashmap_size: int, resolution: int, hashed:
         index = (index + pos_grid[..., d].astype(np.uint64) * np.uint64(stride)) & np.uint64(0xFFFFFFFF)
         stride = (stride * resolution) & 0xFFFFFFFF
     if hashed and hashmap_size < stride:
-        h = np.zeros(pos_grid.shape[:-1], dtype=np.uint64)
-        for d in range(D):
-            h ^= (pos_grid[..., d].astype(np.uint64) * COHERENT_PRIMES[d]) & np.uint64(0xFFFFFFFF)
-        index = h
+        index = grid_hash(pos_grid, hash_type)
     return (index % np.uint64(hashmap_size)).astype(np.uint32)
 
 
@@ -292,7 +333,7 @@ def grid_corners(cfg: GridConfig, x: np.ndarray, level: int):
     frac, cell = pos_fract(x, cfg.scales[level])
     if cfg.nearest:  # grid.h:121-139 / 279-282: the entry at pos_grid alone, weight 1 (no interpolation)
         hs, res = cfg.level_size(level), int(cfg.resolutions[level])
-        return grid_index(cell, hs, res, cfg.hashed)[:, None], np.ones((x.shape[0], 1), dtype=np.float32)
+        return grid_index(cell, hs, res, cfg.hashed, cfg.hash)[:, None], np.ones((x.shape[0], 1), dtype=np.float32)
     if cfg.smooth:
         frac = smoothstep(frac)
     B = x.shape[0]
@@ -309,7 +350,7 @@ def grid_corners(cfg: GridConfig, x: np.ndarray, level: int):
             else:
                 weight = (weight * (F32(1) - frac[:, d])).astype(np.float32)
                 pg[:, d] = cell[:, d]
-        idx[:, c] = grid_index(pg, hs, res, cfg.hashed)
+        idx[:, c] = grid_index(pg, hs, res, cfg.hashed, cfg.hash)
         w[:, c] = weight
     return idx, w
 
@@ -325,15 +366,16 @@ def grid_forward(cfg: GridConfig, x: np.ndarray, table: np.ndarray) -> np.ndarra
     for l in range(cfg.active_levels):
         idx, w = grid_corners(cfg, x, l)
         base = int(cfg.offsets[l])
+        keep = sample_level_mask(cfg, B, l)
         if cfg.nearest:  # the entry itself, no arithmetic (grid.h:121-129) - keeps -0.0
-            out[:, l * F:(l + 1) * F] = t[base + idx[:, 0].astype(np.int64)]
+            out[:, l * F:(l + 1) * F] = np.where(keep[:, None], t[base + idx[:, 0].astype(np.int64)], np.float16(0))
             continue
         res = np.zeros((B, F), dtype=np.float16)
         for c in range(idx.shape[1]):
             val = t[base + idx[:, c].astype(np.int64)]
             wh = w[:, c].astype(np.float16)
             res = (wh.astype(np.float64)[:, None] * val.astype(np.float64) + res.astype(np.float64)).astype(np.float16)
-        out[:, l * F:(l + 1) * F] = res
+        out[:, l * F:(l + 1) * F] = np.where(keep[:, None], res, np.float16(0))
     return out
 
 
@@ -344,6 +386,7 @@ def grid_backward(cfg: GridConfig, x: np.ndarray, dy: np.ndarray, sequential_fp1
     F = cfg.n_features_per_level
     g = np.zeros((int(cfg.offsets[-1]), F), dtype=np.float64)
     for l in range(cfg.active_levels):
+        keep = sample_level_mask(cfg, x.shape[0], l, backward=True)
         if cfg.stochastic and not cfg.nearest:
             # grid.h:284-303: sample = random_val(1337, i + level * B) = pcg32{1337} advanced by that (uint32) index; the same
             # draw picks cell or cell + 1 in every dimension; the whole gradient goes to that corner (weight 1)
@@ -357,8 +400,8 @@ def grid_backward(cfg: GridConfig, x: np.ndarray, dy: np.ndarray, sequential_fp1
                 r.advance((i + l * B) & 0xFFFFFFFF)
                 sample[i] = _uint_to_float01(np.array([r.next_uint()], dtype=np.uint32))[0]
             pg = np.where(sample[:, None] >= frac, cell, cell + U32(1)).astype(np.uint32)
-            ids = grid_index(pg, cfg.level_size(l), int(cfg.resolutions[l]), cfg.hashed).astype(np.int64)
-            np.add.at(g, int(cfg.offsets[l]) + ids, dy[:, l * F:(l + 1) * F].astype(np.float16).astype(np.float64))
+            ids = grid_index(pg, cfg.level_size(l), int(cfg.resolutions[l]), cfg.hashed, cfg.hash).astype(np.int64)
+            np.add.at(g, int(cfg.offsets[l]) + ids[keep], dy[keep, l * F:(l + 1) * F].astype(np.float16).astype(np.float64))
             continue
         idx, w = grid_corners(cfg, x, l)
         base = int(cfg.offsets[l])
@@ -367,8 +410,10 @@ def grid_backward(cfg: GridConfig, x: np.ndarray, dy: np.ndarray, sequential_fp1
         for c in range(idx.shape[1]):
             wh = w[:, c].astype(np.float16)
             prod = (wh.astype(np.float32)[:, None] * gl.astype(np.float32)).astype(np.float16)  # __hmul2, one rounding
+            if F == 1:  # grad_t = float (grid.h:655-666): (float)weight * grad in fp32, fp32 atomics, one cast to fp16 at the end (grid.h:877-885)
+                prod = (w[:, c].astype(np.float32)[:, None] * gl.astype(np.float32)).astype(np.float32)
             if not sequential_fp16:
-                np.add.at(g, base + idx[:, c].astype(np.int64), prod.astype(np.float64))
+                np.add.at(g, base + idx[keep, c].astype(np.int64), prod[keep].astype(np.float64))
             else:
                 contrib.append((idx[:, c].astype(np.int64), prod))
         if sequential_fp16:
@@ -450,10 +495,11 @@ def grid_backward_input(cfg: GridConfig, x: np.ndarray, table: np.ndarray, dy: n
                     else:
                         weight = (weight * frac[:, dim]).astype(np.float32); pg[:, dim] = cell[:, dim] + np.uint32(1)
                 pg[:, gd] = cell[:, gd]
-                vl = t[base + grid_index(pg, size, res, cfg.hashed).astype(np.int64)].astype(np.float32)
+                vl = t[base + grid_index(pg, size, res, cfg.hashed, cfg.hash).astype(np.int64)].astype(np.float32)
                 pg[:, gd] = cell[:, gd] + np.uint32(1)
-                vr = t[base + grid_index(pg, size, res, cfg.hashed).astype(np.int64)].astype(np.float32)
+                vr = t[base + grid_index(pg, size, res, cfg.hashed, cfg.hash).astype(np.int64)].astype(np.float32)
                 grads[:, :, gd] = (grads[:, :, gd] + (weight[:, None] * (vr - vl)).astype(np.float32) * dfrac[:, gd, None]).astype(np.float32)
+        grads[~sample_level_mask(cfg, B, l)] = 0  # dy/dx of a level the sample does not see is zero (grid.h:78-89)
         for f in range(F):
             dl = dy[:, l * F + f].astype(np.float32)
             result = (result + dl[:, None] * grads[:, f, :]).astype(np.float32)
@@ -834,9 +880,9 @@ def grid_dy_dx(cfg: GridConfig, x: np.ndarray, table: np.ndarray) -> np.ndarray:
                     else:
                         weight = (weight * w[:, dim]).astype(np.float32); pg[:, dim] = cell[:, dim] + np.uint32(1)
                 pg[:, gd] = cell[:, gd]
-                vl = t[base + grid_index(pg, size, res, cfg.hashed).astype(np.int64)].astype(np.float32)
+                vl = t[base + grid_index(pg, size, res, cfg.hashed, cfg.hash).astype(np.int64)].astype(np.float32)
                 pg[:, gd] = cell[:, gd] + np.uint32(1)
-                vr = t[base + grid_index(pg, size, res, cfg.hashed).astype(np.int64)].astype(np.float32)
+                vr = t[base + grid_index(pg, size, res, cfg.hashed, cfg.hash).astype(np.int64)].astype(np.float32)
                 out[:, l * F:(l + 1) * F, gd] += (weight[:, None] * (vr - vl)).astype(np.float32) * dw[:, gd, None]
     return out
 
@@ -873,7 +919,7 @@ def grid_bwd_bwd_grid(cfg: GridConfig, x: np.ndarray, dy: np.ndarray, dL_ddLdx: 
                     pg[:, gd] = cell[:, gd] + np.uint32(side)
                     wh = (F32(sign) * weight).astype(np.float16).astype(np.float32)
                     prod = (wh[:, None] * gl).astype(np.float16)  # (GRAD_T)weight * grad: half multiply
-                    np.add.at(g, base + grid_index(pg, size, res, cfg.hashed).astype(np.int64), prod.astype(np.float64))
+                    np.add.at(g, base + grid_index(pg, size, res, cfg.hashed, cfg.hash).astype(np.int64), prod.astype(np.float64))
     return g.reshape(-1)
 
 
@@ -892,7 +938,7 @@ def grid_bwd_bwd_input(cfg: GridConfig, x: np.ndarray, table: np.ndarray, dy: np
         gl = dy[:, l * F:(l + 1) * F].astype(np.float16).astype(np.float32)
 
         def calc(pg, weight):
-            vals = t[base + grid_index(pg, size, res, cfg.hashed).astype(np.int64)]
+            vals = t[base + grid_index(pg, size, res, cfg.hashed, cfg.hash).astype(np.int64)]
             return ((vals * gl).sum(axis=1) * weight).astype(np.float32)
 
         diag = (scale * scale * v * d2w).astype(np.float32)

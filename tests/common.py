@@ -60,6 +60,18 @@ def _net(n, h, act, out_act):
 _GRID_SMALL_2D = {"otype": "HashGrid", "n_levels": 8, "n_features_per_level": 2, "log2_hashmap_size": 12, "base_resolution": 8, "per_level_scale": 1.5}
 _GRID_SMALL_3D = {"otype": "HashGrid", "n_levels": 8, "n_features_per_level": 4, "log2_hashmap_size": 12, "base_resolution": 8, "per_level_scale": 1.5}
 # hidden / output activations other than ReLU / None (common_device.h:100-304), on both MLP widths
+# the options the general (one thread per sample and level) grid kernels exist for: F = 1 (fp32 gradient accumulation, grid.h:655-666),
+# the hashes other than CoherentPrime (common_device.h:631-688), the per-sample max level (grid.h:69-75)
+CONFIG_F1 = {"loss": {"otype": "L2"}, "optimizer": {"otype": "Adam"}, "network": _net(64, 2, "ReLU", "None"),
+             "encoding": {"otype": "HashGrid", "n_levels": 16, "n_features_per_level": 1, "log2_hashmap_size": 12, "base_resolution": 8, "per_level_scale": 1.5}}
+CONFIG_HASH_PRIME = {"loss": {"otype": "L2"}, "optimizer": {"otype": "Adam"}, "network": _net(64, 2, "ReLU", "None"),
+                     "encoding": dict(_GRID_SMALL_3D, hash="Prime")}
+CONFIG_HASH_REVERSED = {"loss": {"otype": "L2"}, "optimizer": {"otype": "Adam"}, "network": _net(64, 2, "ReLU", "None"),
+                        "encoding": dict(_GRID_SMALL_2D, hash="ReversedPrime", interpolation="Smoothstep")}
+CONFIG_HASH_RNG = {"loss": {"otype": "L2"}, "optimizer": {"otype": "Adam"}, "network": _net(64, 2, "ReLU", "None"),
+                   "encoding": dict(_GRID_SMALL_3D, hash="Rng", n_features_per_level=2)}
+CONFIG_SMALL_2D = {"loss": {"otype": "L2"}, "optimizer": {"otype": "Adam"}, "network": _net(64, 2, "ReLU", "None"), "encoding": _GRID_SMALL_2D}
+
 CONFIG_SNAPSHOT = {  # small enough that a full Trainer::serialize(true) snapshot of the reference is a 250 KB fixture
     "loss": {"otype": "L2"}, "optimizer": {"otype": "Adam", "learning_rate": 1e-2, "beta1": 0.9, "beta2": 0.99, "epsilon": 1e-15, "l2_reg": 1e-6},
     "encoding": {"otype": "HashGrid", "n_levels": 8, "n_features_per_level": 2, "log2_hashmap_size": 10, "base_resolution": 8, "per_level_scale": 1.5},
@@ -115,7 +127,8 @@ def oracle_configs(cfg, n_in, n_out, scales=None):
     gtype = "Dense" if otype == "densegrid" else "Tiled" if otype == "tiledgrid" else e.get("type", "Hash")
     g = O.GridConfig(n_in, e.get("n_levels", 16), e.get("n_features_per_level", 2), e.get("log2_hashmap_size", 19),
                      e.get("base_resolution", 16), e.get("per_level_scale", 2.0), scales=scales, grid_type=gtype,
-                     interpolation=e.get("interpolation", "Linear"), stochastic=bool(e.get("stochastic_interpolation", False)))
+                     interpolation=e.get("interpolation", "Linear"), stochastic=bool(e.get("stochastic_interpolation", False)),
+                     hash=e.get("hash", "CoherentPrime"))
     n = cfg["network"]
     m = O.MlpConfig(O.next_multiple(g.n_features, 16), n_out, n.get("n_neurons", 128), n.get("n_hidden_layers", 5),
                     n.get("activation", "ReLU"), n.get("output_activation", "None"))
@@ -179,3 +192,11 @@ def fp32_inputs(n_in, n_table, n_features, padded_width, B=256, seed=6):
 
 # goldens dumped with GridEncoding::set_max_level(value) (REF_MAX_LEVEL of `ref_driver dump`): name -> max_level
 MAX_LEVEL_CASES = {"maxlevel_f4_3d_T14": 0.5}
+# goldens dumped with GridEncoding::set_max_level_gpu (REF_MAX_LEVEL_GPU): sample i keeps the fraction 0.25 * (1 + i % 4) of the levels
+MAX_LEVEL_GPU_CASES = {"maxlevelgpu_f4_3d_T14"}
+# goldens with a second backward pass in GradientMode::Accumulate on top of the first (REF_ACCUMULATE): `grads_accumulated_*`
+ACCUMULATE_CASES = {"accumulate_2d_T12"}
+
+
+def max_level_per_sample(B):
+    return (0.25 * (1 + np.arange(B) % 4)).astype(np.float32)

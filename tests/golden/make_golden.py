@@ -38,6 +38,13 @@ CASES = [  # name, config, n_in, n_out, B
     ("stochastic_2d_T12", common.CONFIG_STOCHASTIC, 2, 3, 512),
     # GridEncoding::set_max_level(0.5): the upper half of the levels encodes to zero (REF_MAX_LEVEL of ref_driver dump)
     ("maxlevel_f4_3d_T14", common.CONFIG_F4, 3, 3, 512),
+    # F = 1, the other hashes, the per-sample max level, GradientMode::Accumulate (the general grid kernels)
+    ("f1_2d_T12", common.CONFIG_F1, 2, 3, 512),
+    ("hash_prime_3d_T12", common.CONFIG_HASH_PRIME, 3, 3, 512),
+    ("hash_reversed_2d_T12", common.CONFIG_HASH_REVERSED, 2, 3, 512),
+    ("hash_rng_3d_T12", common.CONFIG_HASH_RNG, 3, 3, 256),
+    ("maxlevelgpu_f4_3d_T14", common.CONFIG_F4, 3, 3, 512),
+    ("accumulate_2d_T12", common.CONFIG_SMALL_2D, 2, 3, 512),
     # hidden / output activations
     ("act_a_sigmoid_exp_64", common.CONFIG_ACT_A, 2, 3, 512),
     ("act_b_tanh_sigmoid_128", common.CONFIG_ACT_B, 2, 3, 512),
@@ -147,6 +154,10 @@ def main(outdir):
             with open(os.path.join(d, "cfg.json"), "w") as f:
                 json.dump(cfg, f)
             env = dict(os.environ, REF_MAX_LEVEL=str(common.MAX_LEVEL_CASES[name])) if name in common.MAX_LEVEL_CASES else None
+            if name in common.MAX_LEVEL_GPU_CASES:
+                env = dict(os.environ, REF_MAX_LEVEL_GPU="1")
+            if name in common.ACCUMULATE_CASES:
+                env = dict(os.environ, REF_ACCUMULATE="1")
             r = subprocess.run([REF, "dump", os.path.join(d, "cfg.json"), str(n_in), str(n_out), str(B), os.path.join(d, "x.f32"),
                                 os.path.join(d, "t.f32"), d], capture_output=True, text=True, timeout=600, env=env)
             print(name, r.returncode, r.stdout.strip(), r.stderr.strip()[-400:], flush=True)
@@ -168,6 +179,9 @@ def main(outdir):
             enc_raw = rd("encoded_soa.f16", np.float16)
             extra = dict(level_scale=rd("level_scale.f32", np.float32), level_res=rd("level_res.u32", np.uint32), level_size=rd("level_size.u32", np.uint32),
                          indices=rd("indices.u32", np.uint32).reshape(L, B, 1 << n_in)) if grid else {}
+            if name in common.ACCUMULATE_CASES:
+                acc = rd("grads_accumulated.f16", np.float16)
+                extra.update(grads_accumulated_mlp=acc[:P_mlp], grads_accumulated_grid_nz_val=acc[P_mlp:][nz])
             # SoA dumps are [E x B]; an AoS encoding (OneBlob) is stored transposed so that `encoded_soa` always reads [E x B]
             encoded_soa = enc_raw.reshape(E, B) if meta.get("encoded_layout", "SoA") == "SoA" else np.ascontiguousarray(enc_raw.reshape(B, E).T)
             np.savez_compressed(

@@ -25,6 +25,13 @@ CASES = {
     "nearest_3d_T12": (common.CONFIG_NEAREST, 3, 3),
     "stochastic_2d_T12": (common.CONFIG_STOCHASTIC, 2, 3),
     "maxlevel_f4_3d_T14": (common.CONFIG_F4, 3, 3),  # GridEncoding::set_max_level(0.5), common.MAX_LEVEL_CASES
+    # the general grid kernels: F = 1, the hashes other than CoherentPrime, the per-sample max level
+    "f1_2d_T12": (common.CONFIG_F1, 2, 3),
+    "hash_prime_3d_T12": (common.CONFIG_HASH_PRIME, 3, 3),
+    "hash_reversed_2d_T12": (common.CONFIG_HASH_REVERSED, 2, 3),
+    "hash_rng_3d_T12": (common.CONFIG_HASH_RNG, 3, 3),
+    "maxlevelgpu_f4_3d_T14": (common.CONFIG_F4, 3, 3),  # GridEncoding::set_max_level_gpu, common.MAX_LEVEL_GPU_CASES
+    "accumulate_2d_T12": (common.CONFIG_SMALL_2D, 2, 3),
     "wide_dp_3d_T15": (common.CONFIG_WIDE_DP, 3, 3),
     "wide_f4_3d_T14": (common.CONFIG_WIDE_F4, 3, 4),
     "oneblob_2d_128x5": (common.CONFIG_ONEBLOB, 2, 3),
@@ -59,11 +66,23 @@ class Ctx:
         self.info, self.lib = self.native.info, self.native.lib
         L = self.info.n_levels
         self.g, self.m = common.oracle_configs(self.cfg, self.n_in, self.n_out, scales=np.array(self.info.level_scale[:L], dtype=np.float32) if L else None)
-        if name in common.MAX_LEVEL_CASES:
-            self.native.set_max_level(common.MAX_LEVEL_CASES[name])
-            self.g.max_level = common.MAX_LEVEL_CASES[name]
-        self.golden = np.load(os.path.join(GOLDEN, name + ".npz"))
         self.dev = dev
+        self.max_level_gpu = None
+        if name in common.MAX_LEVEL_CASES:
+            self.g.max_level = common.MAX_LEVEL_CASES[name]
+        if name in common.MAX_LEVEL_GPU_CASES:  # one value per sample of any batch the tests pass (the longest is 2^15)
+            self.g.max_level_gpu = common.max_level_per_sample(1 << 16)
+            self.max_level_gpu = torch.from_numpy(self.g.max_level_gpu).to(dev)
+        self.options(self.native)
+        self.golden = np.load(os.path.join(GOLDEN, name + ".npz"))
+
+    def options(self, native):
+        """the per-object settings of this case (set_max_level / set_max_level_gpu) on any module built from its config"""
+        if self.name in common.MAX_LEVEL_CASES:
+            native.set_max_level(common.MAX_LEVEL_CASES[self.name])
+        if self.max_level_gpu is not None:
+            native.set_max_level_gpu(self.max_level_gpu)
+        return native
 
     def params16(self, rng=None):
         p = O.init_params(self.m, self.g, 1337, True)
@@ -143,9 +162,7 @@ def test_grid_input_gradient_vs_oracle(ctx):
     from tinycudann._lib import check, ptr
     B = 512
     rng = np.random.default_rng(21)
-    enc_mod = tcnn.NativeModule(ctx.n_in, 0, {"encoding": ctx.cfg["encoding"]})
-    if ctx.name in common.MAX_LEVEL_CASES:
-        enc_mod.set_max_level(common.MAX_LEVEL_CASES[ctx.name])
+    enc_mod = ctx.options(tcnn.NativeModule(ctx.n_in, 0, {"encoding": ctx.cfg["encoding"]}))
     x_np, _ = common.synth_inputs(B, ctx.n_in, ctx.n_out, seed=8)
     table_np = rng.uniform(-0.5, 0.5, ctx.g.n_params).astype(np.float16)
     W = enc_mod.info.encoded_width
@@ -237,6 +254,38 @@ def test_training_fwd_bwd_vs_oracle_and_reference(ctx):
     assert common.rel_l2(got[ctx.m.n_params - last: ctx.m.n_params], z["grads_mlp"][-last:].astype(np.float64)) < 1e-2
 
 
+def test_backward_accumulate_vs_reference(ctx):
+    """GradientMode::Accumulate (object.h:115-119): tcnn_b200_backward_mode(..., 2) adds to the gradient buffer (the reference's
+    weight-gradient GEMMs with beta = 1, fully_fused_mlp.cu:769; grid.h:857-859 skips the memset); golden = the reference after an
+    Overwrite pass followed by an Accumulate pass of the same batch.  Mode 0 (Ignore) leaves the buffer alone."""
+    if ctx.name not in common.ACCUMULATE_CASES:
+        pytest.skip("golden without an Accumulate pass")
+    from tinycudann._lib import check, ptr
+    z = ctx.golden
+    B = int(z["B"])
+    x_np, _ = common.synth_inputs(B, ctx.n_in, ctx.n_out, seed=1)
+    p16_np = ctx.params16()
+    x, p16 = torch.from_numpy(x_np).to(ctx.dev), torch.from_numpy(p16_np).to(ctx.dev)
+    dy = torch.from_numpy(z["dL_doutput"]).to(ctx.dev)
+    ws = ctx.native.workspace(B, ctx.dev)
+    out = torch.zeros(B, 16, dtype=torch.half, device=ctx.dev)
+    check(ctx.lib.tcnn_b200_forward(ctx.native.handle, S(), B, ptr(x), ptr(p16), ptr(out), ptr(ws)))
+    g = torch.full((ctx.info.n_params,), 7.0, dtype=torch.half, device=ctx.dev)
+    check(ctx.lib.tcnn_b200_backward_mode(ctx.native.handle, S(), B, ptr(x), ptr(p16), ptr(dy), ptr(g), None, ptr(ws), 1))   # Overwrite
+    first = g.cpu().numpy().astype(np.float64)
+    n, nz = ctx.m.n_params, z["grads_grid_nz_idx"].astype(np.int64)
+    assert common.rel_l2(first[n:][nz], z["grads_grid_nz_val"].astype(np.float64)) < 1e-2
+    check(ctx.lib.tcnn_b200_backward_mode(ctx.native.handle, S(), B, ptr(x), ptr(p16), ptr(dy), ptr(g), None, ptr(ws), 2))   # Accumulate
+    both = g.cpu().numpy().astype(np.float64)
+    last = ctx.m.shapes()[-1][0] * ctx.m.shapes()[-1][1]
+    assert common.rel_l2(both[n - last: n], z["grads_accumulated_mlp"][-last:].astype(np.float64)) < 1e-2
+    assert common.rel_l2(both[:n], 2 * first[:n]) < 2e-3 and common.rel_l2(both[n:], 2 * first[n:]) < 2e-3
+    assert common.rel_l2(both[n:][nz], z["grads_accumulated_grid_nz_val"].astype(np.float64)) < 1e-2
+    check(ctx.lib.tcnn_b200_backward_mode(ctx.native.handle, S(), B, ptr(x), ptr(p16), ptr(dy), ptr(g), None, ptr(ws), 0))   # Ignore
+    assert np.array_equal(g.cpu().numpy().astype(np.float64), both)
+    assert ctx.lib.tcnn_b200_backward_mode(ctx.native.handle, S(), B, ptr(x), ptr(p16), ptr(dy), ptr(g), None, ptr(ws), 3) != 0
+
+
 def test_inference_fp32_output(ctx):
     from tinycudann._lib import check, ptr
     B = 512
@@ -260,8 +309,7 @@ def test_trainer_converges_and_matches_unfused_step(ctx):
     a = tcnn.create_from_config(ctx.n_in, ctx.n_out, ctx.cfg, device=ctx.dev)
     b = tcnn.create_from_config(ctx.n_in, ctx.n_out, ctx.cfg, device=ctx.dev)
     b.trainer.use_fused_step = False
-    if ctx.name in common.MAX_LEVEL_CASES:  # the fused kernel and the separate kernels both stop at the active levels
-        a.trainer.native.set_max_level(common.MAX_LEVEL_CASES[ctx.name]); b.trainer.native.set_max_level(common.MAX_LEVEL_CASES[ctx.name])
+    ctx.options(a.trainer.native); ctx.options(b.trainer.native)  # the fused kernel and the separate kernels both stop at the active levels
     la = []
     for i in range(40):
         x_np, t_np = common.synth_inputs(B, ctx.n_in, ctx.n_out, seed=50 + i)
@@ -285,6 +333,7 @@ def test_module_autograd_surface(ctx):
     import tinycudann as tcnn
     B = 512
     net = tcnn.NetworkWithInputEncoding(ctx.n_in, ctx.n_out, ctx.cfg["encoding"], ctx.cfg["network"]).to(ctx.dev)
+    ctx.options(net.native_tcnn_module)
     x_np, t_np = common.synth_inputs(B, ctx.n_in, ctx.n_out, seed=3)
     x = torch.from_numpy(x_np).to(ctx.dev).requires_grad_(True)
     y = net(x)

@@ -10,7 +10,8 @@ from oracle import tcnn_oracle as O
 from tests import common
 
 GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
-NAMES = ["cfg1_2d_T19", "shipped_2d_T15", "nerf_3d_T19", "f4_3d_T14", "tiled_smooth_2d", "dense_3d_f4", "nearest_3d_T12", "maxlevel_f4_3d_T14", "stochastic_2d_T12"]
+NAMES = ["cfg1_2d_T19", "shipped_2d_T15", "nerf_3d_T19", "f4_3d_T14", "tiled_smooth_2d", "dense_3d_f4", "nearest_3d_T12", "maxlevel_f4_3d_T14", "stochastic_2d_T12",
+         "f1_2d_T12", "hash_prime_3d_T12", "hash_reversed_2d_T12", "hash_rng_3d_T12", "maxlevelgpu_f4_3d_T14", "accumulate_2d_T12"]
 
 
 @pytest.fixture(scope="module", params=NAMES)
@@ -20,9 +21,11 @@ def case(request):
     n_in, n_out, B = int(z["n_in"]), int(z["n_out"]), int(z["B"])
     g, m = common.oracle_configs(cfg, n_in, n_out, scales=z["level_scale"])
     g.max_level = common.MAX_LEVEL_CASES.get(request.param, g.max_level)  # GridEncoding::set_max_level of that dump
+    if request.param in common.MAX_LEVEL_GPU_CASES:                       # GridEncoding::set_max_level_gpu of that dump
+        g.max_level_gpu = common.max_level_per_sample(B)
     x, t = common.synth_inputs(B, n_in, n_out, seed=int(z["seed"]))
     p = O.init_params(m, g, 1337, True)
-    return dict(z=z, cfg=cfg, g=g, m=m, x=x, t=t, p=p, n_out=n_out, B=B)
+    return dict(z=z, cfg=cfg, g=g, m=m, x=x, t=t, p=p, n_out=n_out, B=B, name=request.param)
 
 
 def test_level_table(case):
@@ -77,6 +80,11 @@ def test_mlp_loss_gradients_within_tolerance(case):
     nz = z["grads_grid_nz_idx"].astype(np.int64)
     assert common.rel_l2(gg[nz], z["grads_grid_nz_val"]) < 1e-2  # north-star bar; 5-9e-4 measured (no ReLU mask differs any more)
     assert abs(np.count_nonzero(gg) - len(nz)) <= 2e-3 * len(nz) + 4
+    if case["name"] in common.ACCUMULATE_CASES:
+        # a second backward pass in GradientMode::Accumulate adds the same gradients once more (object.h:115-119; fully_fused_mlp.cu:769
+        # beta = 1, grid.h:857-859 no memset): twice the first pass up to the fp16 rounding of the sum and the order of the atomics
+        assert common.rel_l2(z["grads_accumulated_mlp"].astype(np.float64), 2 * z["grads_mlp"].astype(np.float64)) < 2e-3
+        assert common.rel_l2(z["grads_accumulated_grid_nz_val"].astype(np.float64), 2 * z["grads_grid_nz_val"].astype(np.float64)) < 2e-3
 
 
 def test_adam_first_step(case):
@@ -86,7 +94,8 @@ def test_adam_first_step(case):
     n = m.n_params
     master = case["p"][:n].copy()
     mm, vv, ss = np.zeros(n, np.float32), np.zeros(n, np.float32), np.zeros(n, np.uint32)
-    O.adam_step(ac, n, master, z["grads_mlp"], mm, vv, ss)  # the reference's own gradients -> its own update
+    # the reference's own gradients -> its own update (the Accumulate dump stepped on the gradients of both passes)
+    O.adam_step(ac, n, master, z["grads_accumulated_mlp"] if case["name"] in common.ACCUMULATE_CASES else z["grads_mlp"], mm, vv, ss)
     assert np.max(np.abs(master - z["params_after_mlp"])) < 2e-7 + 1e-5 * ac.learning_rate
 
 

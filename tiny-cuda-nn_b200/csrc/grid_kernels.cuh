@@ -36,8 +36,9 @@ struct GridLevel {
 	uint32_t rep_offset;    // first entry of this level inside one replica
 	uint64_t magic;         // ceil(2^64 / size): index % size without a division (fastmod_u32)
 	uint32_t mode;          // LEVEL_HASH / LEVEL_DENSE_POW2 / LEVEL_DENSE_MOD: which of the three index computations applies (uniform per level)
-	uint32_t reserved;
+	uint32_t hash_type;     // HASH_COHERENT_PRIME (the specialised kernels) / HASH_PRIME / HASH_REVERSED_PRIME / HASH_RNG (grid_index_dev only)
 };
+enum HashKind : uint32_t { HASH_COHERENT_PRIME = 0, HASH_PRIME = 1, HASH_REVERSED_PRIME = 2, HASH_RNG = 3 };
 enum LevelMode : uint32_t { LEVEL_HASH = 0, LEVEL_DENSE_POW2 = 1, LEVEL_DENSE_MOD = 2 };
 
 // a % d for 32-bit a, d with M = ceil(2^64 / d) (Lemire, Kaser, Kurz: "Faster remainder by direct computation", exact for all 32-bit
@@ -64,6 +65,8 @@ struct GridParams {
 	uint32_t stochastic;     // stochastic_interpolation (grid.h:284-303): the backward pass adds the whole gradient to ONE random corner
 	uint64_t rng_state, rng_inc; // pcg32{1337} after seeding (random_val, common_device.h:333-337), filled by plan_create
 	uint32_t nearest;        // interpolation Nearest (grid.h:121-139): own kernels below, never reaches the interpolating ones
+	uint32_t n_levels_total; // levels of the encoding (n_levels above is the active prefix after set_max_level)
+	const float* max_level_gpu; // per-sample max level (GridEncoding::set_max_level_gpu) or nullptr; read by the general kernels only
 	GridLevel level[MAX_LEVELS];
 };
 
@@ -87,15 +90,59 @@ __device__ __forceinline__ void pos_fract_dev(float x, float scale, float& frac,
 __device__ __forceinline__ float smoothstep_dev(float v) { return v * v * (3.0f - 2.0f * v); }
 __device__ __forceinline__ float smoothstep_derivative_dev(float v) { return 6 * v * (1.0f - v); }
 
+// pcg32 (pcg32.h:54-69, 145-168): the generator after `delta` steps from (state, inc), and its 32-bit output function
+__device__ __forceinline__ uint64_t pcg32_state_at(uint64_t state, uint64_t inc, uint64_t delta) {
+	uint64_t cur_mult = 0x5851f42d4c957f2dULL, cur_plus = inc, acc_mult = 1u, acc_plus = 0u;
+	while (delta > 0) {
+		if (delta & 1) { acc_mult *= cur_mult; acc_plus = acc_plus * cur_mult + cur_plus; }
+		cur_plus = (cur_mult + 1) * cur_plus;
+		cur_mult *= cur_mult;
+		delta >>= 1;
+	}
+	return acc_mult * state + acc_plus;
+}
+__device__ __forceinline__ uint32_t pcg32_output(uint64_t old) {
+	const uint32_t xorshifted = (uint32_t)(((old >> 18u) ^ old) >> 27u);
+	const uint32_t rot = (uint32_t)(old >> 59u);
+	return (xorshifted >> rot) | (xorshifted << ((~rot + 1u) & 31));
+}
+
+// grid_hash (common_device.h:631-688).  The three prime hashes differ in their factor tables; Rng draws the next output of
+// pcg32{1337} advanced by xor_d(pos[d] << d * (64 / D)).
+template <int D>
+__device__ __forceinline__ uint32_t grid_hash_dev(uint32_t hash_type, const uint32_t (&pg)[D]) {
+	constexpr uint32_t coherent[7] = {1u, 2654435761u, 805459861u, 3674653429u, 2097192037u, 1434869437u, 2165219737u};
+	uint32_t h = 0;
+	if (hash_type == HASH_COHERENT_PRIME) {
+#pragma unroll
+		for (int d = 0; d < D; ++d) h ^= pg[d] * coherent[d];
+	} else if (hash_type == HASH_PRIME) {
+		constexpr uint32_t f[7] = {1958374283u, 2654435761u, 805459861u, 3674653429u, 2097192037u, 1434869437u, 2165219737u};
+#pragma unroll
+		for (int d = 0; d < D; ++d) h ^= pg[d] * f[d];
+	} else if (hash_type == HASH_REVERSED_PRIME) {
+		constexpr uint32_t f[7] = {2165219737u, 1434869437u, 2097192037u, 3674653429u, 805459861u, 2654435761u, 1958374283u};
+#pragma unroll
+		for (int d = 0; d < D; ++d) h ^= pg[d] * f[d];
+	} else {
+		constexpr uint32_t bits = 64 / D;
+		uint64_t step = 0;
+#pragma unroll
+		for (int d = 0; d < D; ++d) step ^= (uint64_t)pg[d] << (d * bits);
+		// pcg32{1337}: seed(1337, 1) = state 0, inc 3, one step, += 1337, one step (pcg32.h:54-60)
+		const uint64_t mult = 0x5851f42d4c957f2dULL, inc = 3u;
+		uint64_t state = (0u * mult + inc + 1337u) * mult + inc;
+		h = pcg32_output(pcg32_state_at(state, inc, step));
+	}
+	return h;
+}
+
 // common_device.h:690-707 with the level-constant part hoisted (strides, hashed flag); primes :650-654.
 template <int D>
 __device__ __forceinline__ uint32_t grid_index_dev(const GridLevel& lv, const uint32_t (&pg)[D]) {
-	constexpr uint32_t primes[7] = {1u, 2654435761u, 805459861u, 3674653429u, 2097192037u, 1434869437u, 2165219737u};
 	uint32_t index;
 	if (lv.hashed) {
-		index = 0;
-#pragma unroll
-		for (int d = 0; d < D; ++d) index ^= pg[d] * primes[d];
+		index = grid_hash_dev<D>(lv.hash_type, pg);
 	} else {
 		index = 0;
 #pragma unroll
@@ -444,7 +491,12 @@ __global__ void __launch_bounds__(256) grid_backward_input_kernel(const __grid_c
 	float result[D];
 #pragma unroll
 	for (int d = 0; d < D; ++d) result[d] = 0.f;
-	for (uint32_t level = 0; level < gp.n_levels; ++level) {
+	uint32_t n_levels = gp.n_levels;
+	if (gp.max_level_gpu) { // dy/dx of the levels a sample does not see is zero (grid.h:69-92)
+		const float max_level = (__ldg(gp.max_level_gpu + i) * (float)(gp.n_levels_total * F)) / (float)F;
+		while (n_levels > 0 && (float)(n_levels - 1) >= max_level + 1e-3f) --n_levels;
+	}
+	for (uint32_t level = 0; level < n_levels; ++level) {
 		const GridLevel& lv = gp.level[level];
 		const T* table = grid + (size_t)lv.offset * F;
 		float frac[D]; uint32_t cell[D];
@@ -638,17 +690,7 @@ __global__ void __launch_bounds__(256) grid_nearest_backward_kernel(const __grid
 // advanced by that index - picks cell or cell + 1 in EVERY dimension by comparing the same draw with the (interpolated)
 // fraction; the whole gradient goes to that corner with weight 1.  The forward pass interpolates as usual.
 __device__ __forceinline__ float pcg32_float_at(uint64_t state, uint64_t inc, uint64_t delta) {
-	uint64_t cur_mult = 0x5851f42d4c957f2dULL, cur_plus = inc, acc_mult = 1u, acc_plus = 0u;
-	while (delta > 0) {
-		if (delta & 1) { acc_mult *= cur_mult; acc_plus = acc_plus * cur_mult + cur_plus; }
-		cur_plus = (cur_mult + 1) * cur_plus;
-		cur_mult *= cur_mult;
-		delta >>= 1;
-	}
-	const uint64_t old = acc_mult * state + acc_plus;
-	const uint32_t xorshifted = (uint32_t)(((old >> 18u) ^ old) >> 27u);
-	const uint32_t rot = (uint32_t)(old >> 59u);
-	const uint32_t u = (xorshifted >> rot) | (xorshifted << ((~rot + 1u) & 31));
+	const uint32_t u = pcg32_output(pcg32_state_at(state, inc, delta));
 	return __uint_as_float((u >> 9) | 0x3f800000u) - 1.0f;
 }
 template <int D, int F>
@@ -682,6 +724,125 @@ __global__ void __launch_bounds__(256) grid_stochastic_backward_kernel(const __g
 	}
 }
 
+
+// ---- general kernels: everything the specialised ones above leave out ---------------------------------------------
+// One thread per (sample, level) like the reference's kernel_grid / kernel_grid_backward (grid.h:48-320), with every option as a
+// run-time switch: any hash (grid_index_dev), Nearest / Linear / Smoothstep, stochastic_interpolation, the per-sample max level
+// (grid.h:69-75, 236-243) and F = 1, whose gradients the reference accumulates in fp32 and casts afterwards (grad_t = float,
+// grid.h:655-666, 877-885).  Chosen by the host for plans with a non-default hash, F = 1 or a per-sample max level.
+template <int D, int F>
+__global__ void __launch_bounds__(256) grid_general_forward_kernel(const __grid_constant__ GridParams gp, uint32_t B,
+	const float* __restrict__ x, const __half* __restrict__ grid, __half* __restrict__ encoded) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= B) return;
+	const uint32_t level = blockIdx.y;                       // blockIdx.y runs over padded_width / F: the tail writes the zero padding
+	__half result[F];
+#pragma unroll
+	for (int f = 0; f < F; ++f) result[f] = __float2half(0.f);
+	bool active = level < gp.n_levels;
+	if (active && gp.max_level_gpu) {
+		const float max_level = (__ldg(gp.max_level_gpu + i) * (float)(gp.n_levels_total * F)) / (float)F;
+		active = !((float)level >= max_level + 1e-3f);
+	}
+	if (active) {
+		const GridLevel& lv = gp.level[level];
+		float p[D], frac[D]; uint32_t cell[D];
+		load_position<D>(x, i, p);
+#pragma unroll
+		for (int d = 0; d < D; ++d) pos_fract_dev(p[d], lv.scale, frac[d], cell[d]);
+		const __half* table = grid + (size_t)lv.offset * F;
+		if (gp.nearest) {
+			const uint32_t idx = grid_index_dev<D>(lv, cell);
+#pragma unroll
+			for (int f = 0; f < F; ++f) result[f] = __ldg(table + (size_t)idx * F + f);
+		} else {
+			if (gp.smoothstep) {
+#pragma unroll
+				for (int d = 0; d < D; ++d) frac[d] = smoothstep_dev(frac[d]);
+			}
+#pragma unroll
+			for (int c = 0; c < (1 << D); ++c) {
+				float weight = 1.0f; uint32_t pg[D];
+#pragma unroll
+				for (int d = 0; d < D; ++d) {
+					weight *= (c & (1 << d)) == 0 ? 1.0f - frac[d] : frac[d];
+					pg[d] = cell[d] + ((c >> d) & 1);
+				}
+				const uint32_t idx = grid_index_dev<D>(lv, pg);
+				const __half wh = __float2half(weight);
+#pragma unroll
+				for (int f = 0; f < F; ++f) result[f] = __hfma(wh, __ldg(table + (size_t)idx * F + f), result[f]); // one rounding per corner, as __hfma2 per lane
+			}
+		}
+	}
+	const uint32_t col = level * F;
+	const size_t off = gp.image_subs ? wide_image_chunk(i, col >> 3, gp.image_subs) + (col & 7u) * 2 : ((size_t)i * gp.padded_width + col) * 2;
+	__half* dst = reinterpret_cast<__half*>(reinterpret_cast<uint8_t*>(encoded) + off);
+#pragma unroll
+	for (int f = 0; f < F; ++f) dst[f] = result[f];
+}
+
+// grad_f32 != nullptr (F = 1): fp32 atomics into a zeroed fp32 copy of the table gradient, cast by grid_cast_gradient_kernel.
+template <int D, int F>
+__global__ void __launch_bounds__(256) grid_general_backward_kernel(const __grid_constant__ GridParams gp, uint32_t B,
+	const float* __restrict__ x, const __half* __restrict__ dL_denc, __half* __restrict__ grid_grad, float* __restrict__ grad_f32) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= B) return;
+	const uint32_t level = blockIdx.y;
+	if (level >= gp.n_levels) return;
+	if (gp.max_level_gpu) {
+		const float max_level = (__ldg(gp.max_level_gpu + i) * (float)(gp.n_levels_total * F)) / (float)F;
+		if ((float)level > max_level + 1e-3f) return;
+	}
+	const GridLevel& lv = gp.level[level];
+	float p[D], frac[D]; uint32_t cell[D];
+	load_position<D>(x, i, p);
+#pragma unroll
+	for (int d = 0; d < D; ++d) pos_fract_dev(p[d], lv.scale, frac[d], cell[d]);
+	if (gp.smoothstep && !gp.nearest) {
+#pragma unroll
+		for (int d = 0; d < D; ++d) frac[d] = smoothstep_dev(frac[d]);
+	}
+	__half g[F];
+#pragma unroll
+	for (int f = 0; f < F; ++f) g[f] = __ldg(dL_denc + (size_t)i * gp.padded_width + level * F + f);
+	auto add = [&](const uint32_t (&pg)[D], float weight) {
+		const size_t entry = ((size_t)lv.offset + grid_index_dev<D>(lv, pg)) * F;
+		if constexpr (F == 1) {
+			atomicAdd(grad_f32 + entry, weight * __half2float(g[0]));
+		} else {
+			const __half2 wh = __half2half2(__float2half(weight));
+#pragma unroll
+			for (int f = 0; f < F; f += 2) red_add_h2(grid_grad + entry + f, __hmul2(wh, __halves2half2(g[f], g[f + 1])));
+		}
+	};
+	if (gp.nearest) { add(cell, 1.0f); return; }
+	if (gp.stochastic) {
+		const float sample = pcg32_float_at(gp.rng_state, gp.rng_inc, (uint64_t)(uint32_t)(i + level * B));
+		uint32_t pg[D];
+#pragma unroll
+		for (int d = 0; d < D; ++d) pg[d] = sample >= frac[d] ? cell[d] : cell[d] + 1u;
+		add(pg, 1.0f);
+		return;
+	}
+#pragma unroll
+	for (int c = 0; c < (1 << D); ++c) {
+		float weight = 1.0f; uint32_t pg[D];
+#pragma unroll
+		for (int d = 0; d < D; ++d) {
+			weight *= (c & (1 << d)) == 0 ? 1.0f - frac[d] : frac[d];
+			pg[d] = cell[d] + ((c >> d) & 1);
+		}
+		add(pg, weight);
+	}
+}
+
+// grad[i] = (half)tmp[i] (grid.h:877-885); accumulate: added to what grad holds (GradientMode::Accumulate)
+__global__ void grid_cast_gradient_kernel(uint32_t n, const float* __restrict__ tmp, __half* __restrict__ grad, int accumulate) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	grad[i] = __float2half(accumulate ? __half2float(grad[i]) + tmp[i] : tmp[i]);
+}
 
 // ---- second order (encodings/grid.h:351-650) --------------------------------------------------------------------
 // The backward pass of dL/dx = sum_k dL/dy_k * dy_k/dx (grid_backward_input_kernel): given dL_ddLdx = d(loss)/d(dL/dx), the

@@ -618,7 +618,7 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 // Sum the per-CTA fp32 partials -> fp16 weight gradients (layout of the reference's gradient matrices) and the loss.
 // Block = 32 parameters x 8 slices of the partial list (coalesced 128-byte rows), tree-reduced in shared memory.
 __global__ void __launch_bounds__(256) mlp_finalize_kernel(uint32_t n_params, uint32_t n_parts, const float* __restrict__ partials, __half* __restrict__ grads,
-	const float* __restrict__ loss_partials, float* __restrict__ loss_out, uint32_t n_loss_parts) {
+	const float* __restrict__ loss_partials, float* __restrict__ loss_out, uint32_t n_loss_parts, int accumulate) {
 	__shared__ float sh[8][33];
 	const uint32_t px = threadIdx.x & 31, sl = threadIdx.x >> 5;
 	const uint32_t i = blockIdx.x * 32 + px;
@@ -632,6 +632,7 @@ __global__ void __launch_bounds__(256) mlp_finalize_kernel(uint32_t n_params, ui
 		float t = 0.f;
 #pragma unroll
 		for (int k = 0; k < 8; ++k) t += sh[k][px];
+		if (accumulate) t += __half2float(grads[i]); // GradientMode::Accumulate: D = A B + C in one rounding, like the reference's GEMM epilogue with beta = 1
 		grads[i] = __float2half(t);
 	}
 	if (blockIdx.x == 0 && loss_partials && loss_out) {

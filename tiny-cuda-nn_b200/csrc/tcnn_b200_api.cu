@@ -50,6 +50,7 @@ struct tcnn_b200_plan {
 	bool adabound = false;
 	bool optimize_matrix_params = true, optimize_non_matrix_params = true; // adam.h:57-58, 77-85: a false one freezes that parameter class
 	int grid_type = 0;              // GRID_HASH / GRID_DENSE / GRID_TILED (GridType, grid_interface.h)
+	uint32_t hash_type = 0;         // HashKind (grid_kernels.cuh): "hash" of the encoding config (grid.h:1151), default CoherentPrime
 	int enc_kind = 0;               // ENC_GRID / ENC_IDENTITY / ENC_ONEBLOB
 	uint32_t oneblob_log2_bins = 0;
 	bool f32 = false;               // stand-alone encoding with fp32 parameters / output ("precision": "fp32"; Precision::Fp32 of cpp_api.h)
@@ -106,7 +107,7 @@ struct ProfileScope {
 static uint32_t next_multiple_u32(uint32_t v, uint32_t m) { return (v + m - 1) / m * m; }
 
 // Per-level constants of grid_index (common_device.h:690-707) for a given (scale, size): strides with uint32 wrap.
-static void fill_level(GridLevel& lv, float scale, uint32_t size, uint32_t offset, uint32_t n_dims, bool hash_type) {
+static void fill_level(GridLevel& lv, float scale, uint32_t size, uint32_t offset, uint32_t n_dims, bool hash_type, uint32_t hash_kind) {
 	lv.scale = scale;
 	lv.resolution = (uint32_t)std::ceil(scale) + 1; // grid_resolution, common_device.h:716-718
 	lv.size = size;
@@ -123,19 +124,24 @@ static void fill_level(GridLevel& lv, float scale, uint32_t size, uint32_t offse
 	lv.magic = fastmod_magic(size ? size : 1u);
 	const bool pow2 = size && (size & (size - 1)) == 0;
 	lv.mode = lv.hashed ? LEVEL_HASH : pow2 ? LEVEL_DENSE_POW2 : LEVEL_DENSE_MOD; // hashed levels have size 2^log2_hashmap_size
-	lv.reserved = 0;
+	lv.hash_type = hash_kind;
 }
 
 constexpr uint32_t N_REPLICAS = 32;          // private copies of the contended coarse gradient levels
 constexpr uint32_t REPLICATE_MAX_ENTRIES = 8192; // levels up to this many entries are replicated ...
 constexpr uint32_t REPLICATE_MIN_BATCH = 1u << 14; // ... when the batch is large enough for contention to matter
 
+// Plans the specialised gather / scatter kernels do not cover (a hash other than CoherentPrime, F = 1, a per-sample max level) run the
+// general per-(sample, level) kernels: no replicas, no fusion into the MLP kernel.
+static bool general_grid(const tcnn_b200_plan* p) {
+	return p->enc_kind == 0 /* ENC_GRID */ && p->info.n_levels > 0 && (p->hash_type != HASH_COHERENT_PRIME || p->info.n_features_per_level == 1 || p->grid.max_level_gpu != nullptr);
+}
 // GridParams for the backward launch: marks the replicated levels (if a replica buffer is available).
 static GridParams backward_params(const tcnn_b200_plan* p, uint32_t B, bool have_replicas) {
 	GridParams gp = p->grid;
 	gp.n_replicas = N_REPLICAS; gp.rep_entries = 0;
 	static const bool never = getenv("TCNN_B200_NO_REPLICAS") != nullptr; // development switch (tests/dev/parity_probe.py): plain fp16 reductions on every level
-	if (!have_replicas || B < REPLICATE_MIN_BATCH || never) return gp;
+	if (!have_replicas || B < REPLICATE_MIN_BATCH || never || general_grid(p)) return gp;
 	for (uint32_t l = 0; l < gp.n_levels; ++l) {
 		if (gp.level[l].size <= REPLICATE_MAX_ENTRIES) {
 			gp.level[l].replicated = 1;
@@ -146,6 +152,7 @@ static GridParams backward_params(const tcnn_b200_plan* p, uint32_t B, bool have
 	return gp;
 }
 static size_t replica_bytes(const tcnn_b200_plan* p) {
+	if (p->info.n_features_per_level == 1) return (size_t)p->info.n_params_grid * 4; // F = 1: this region holds the fp32 copy of the table gradient instead
 	size_t entries = 0;
 	for (uint32_t l = 0; l < p->info.n_levels; ++l) if (p->grid.level[l].size <= REPLICATE_MAX_ENTRIES) entries += p->grid.level[l].size; // all levels, whatever max_level says
 	return entries * p->info.n_features_per_level * 2 * N_REPLICAS;
@@ -154,7 +161,7 @@ static size_t replica_bytes(const tcnn_b200_plan* p) {
 static void build_levels(tcnn_b200_plan* p, const float* scales) {
 	const tcnn_b200_info& in = p->info;
 	for (uint32_t l = 0; l < in.n_levels; ++l) {
-		fill_level(p->grid.level[l], scales[l], in.level_offset[l + 1] - in.level_offset[l], in.level_offset[l], in.n_input_dims, p->grid_type == GRID_HASH);
+		fill_level(p->grid.level[l], scales[l], in.level_offset[l + 1] - in.level_offset[l], in.level_offset[l], in.n_input_dims, p->grid_type == GRID_HASH, p->hash_type);
 		p->info.level_scale[l] = scales[l];
 		p->info.level_resolution[l] = p->grid.level[l].resolution;
 	}
@@ -275,7 +282,14 @@ extern "C" int tcnn_b200_plan_create(const char* json_utf8, uint32_t n_input_dim
 	else if (gtype == "dense") p->grid_type = GRID_DENSE;
 	else if (gtype == "tiled") p->grid_type = GRID_TILED;
 	else FAIL("GridEncoding: invalid grid type '" + gtype + "'");
-	CHECK(jsonmini::lower(enc.string("hash", "CoherentPrime")) == "coherentprime", "only hash 'CoherentPrime' is implemented");
+	{ // string_to_hash_type (grid.h:1106-1119)
+		const std::string h = jsonmini::lower(enc.string("hash", "CoherentPrime"));
+		if (h == "coherentprime") p->hash_type = HASH_COHERENT_PRIME;
+		else if (h == "prime") p->hash_type = HASH_PRIME;
+		else if (h == "reversedprime") p->hash_type = HASH_REVERSED_PRIME;
+		else if (h == "rng") p->hash_type = HASH_RNG;
+		else FAIL("Invalid hash type: " + h);
+	}
 	const std::string interp = jsonmini::lower(enc.string("interpolation", "Linear"));
 	CHECK(interp == "nearest" || interp == "linear" || interp == "smoothstep", "interpolation '" + interp + "' does not exist (Nearest, Linear, Smoothstep)");
 	p->grid.smoothstep = interp == "smoothstep" ? 1u : 0u;
@@ -291,8 +305,9 @@ extern "C" int tcnn_b200_plan_create(const char* json_utf8, uint32_t n_input_dim
 		p->grid.rng_state = state; p->grid.rng_inc = inc;
 	}
 	in.n_features_per_level = (uint32_t)enc.number("n_features_per_level", 2);
-	CHECK(in.n_features_per_level == 2 || in.n_features_per_level == 4 || in.n_features_per_level == 8,
-		"GridEncoding: n_features_per_level must be 2, 4 or 8 on this path (1 needs the fp32 gradient variant)");
+	CHECK(in.n_features_per_level == 1 || in.n_features_per_level == 2 || in.n_features_per_level == 4 || in.n_features_per_level == 8,
+		"GridEncoding: n_features_per_level must be 1, 2, 4 or 8");
+	CHECK(!(in.n_features_per_level == 1 && p->f32), "n_features_per_level = 1 is implemented for fp16 precision");
 	if (enc.contains("n_features") || enc.contains("n_grid_features")) {
 		CHECK(!enc.contains("n_levels"), "GridEncoding: may not specify n_features and n_levels simultaneously (one determines the other)");
 		n_features = (uint32_t)enc.number(enc.contains("n_features") ? "n_features" : "n_grid_features", 0);
@@ -342,6 +357,7 @@ extern "C" int tcnn_b200_plan_create(const char* json_utf8, uint32_t n_input_dim
 	in.level_offset[in.n_levels] = offset;
 	in.n_params_grid = (uint64_t)offset * in.n_features_per_level;
 	p->grid.n_levels = in.n_levels;
+	p->grid.n_levels_total = in.n_levels;
 	p->grid.n_features = n_features;
 	p->grid.padded_width = in.encoded_width;
 	build_levels(p.get(), host_scales);
@@ -433,6 +449,18 @@ extern "C" int tcnn_b200_plan_set_max_level(tcnn_b200_plan* plan, float max_leve
 	for (uint32_t l = 0; l < L; ++l) if (!((float)l >= scaled + 1e-3f)) active = l + 1;
 	plan->grid.n_levels = active;
 	plan->grid.n_features = active * F;
+	++plan->version;
+	API_END
+}
+
+// GridEncoding::set_max_level_gpu (grid_interface.h:113-115): a device array of one max level per sample of the batches to come
+// (nullptr switches it off).  The plan then runs the general grid kernels (grid_general_forward_kernel ...).
+extern "C" int tcnn_b200_plan_set_max_level_gpu(tcnn_b200_plan* plan, const float* max_level_per_sample) {
+	API_BEGIN
+	CHECK(plan, "null argument");
+	CHECK(plan->enc_kind == ENC_GRID && plan->info.n_levels > 0, "max_level belongs to grid encodings");
+	CHECK(!plan->f32 || !max_level_per_sample, "the per-sample max level is implemented for fp16 precision");
+	plan->grid.max_level_gpu = max_level_per_sample;
 	++plan->version;
 	API_END
 }
@@ -609,6 +637,16 @@ extern "C" int tcnn_b200_generate_random_uniform(void* stream, uint64_t rng_stat
 		else FAIL("unsupported (n_input_dims, n_features_per_level)");                                            \
 	} while (0)
 
+#define GRID_DISPATCH_F1(KERNEL, plan, grid_dim, stream, ...)                                                     \
+	do {                                                                                                          \
+		const uint32_t D1_ = (plan)->info.n_input_dims;                                                           \
+		if ((plan)->info.n_features_per_level != 1) GRID_DISPATCH(KERNEL, plan, grid_dim, stream, __VA_ARGS__);   \
+		else if (D1_ == 2) GRID_LAUNCH(KERNEL, 2, 1, grid_dim, stream, __VA_ARGS__);                        \
+		else if (D1_ == 3) GRID_LAUNCH(KERNEL, 3, 1, grid_dim, stream, __VA_ARGS__);                        \
+		else if (D1_ == 4) GRID_LAUNCH(KERNEL, 4, 1, grid_dim, stream, __VA_ARGS__);                        \
+		else FAIL("unsupported n_input_dims");                                                                    \
+	} while (0)
+
 #define GRID_DISPATCH_T(KERNEL, TT, plan, grid_dim, stream, ...)                                                  \
 	do {                                                                                                          \
 		const uint32_t D_ = (plan)->info.n_input_dims, F_ = (plan)->info.n_features_per_level;                   \
@@ -631,6 +669,13 @@ static void encode_forward(const tcnn_b200_plan* plan, cudaStream_t stream, uint
 	const uint32_t nz16 = (uint32_t)(zero_bytes / 16);
 	GridParams gp = plan->grid;
 	gp.image_subs = image ? image_subs(plan) : 0u;
+	if (general_grid(plan)) {
+		if (z16) CUDA_OK(cudaMemsetAsync(z16, 0, zero_bytes, stream));
+		const dim3 gl((B + 255) / 256, plan->info.encoded_width / plan->info.n_features_per_level, 1);
+		GRID_DISPATCH_F1(grid_general_forward_kernel, plan, gl, stream, gp, B, x, grid, encoded);
+		launch_check("grid_general_forward_kernel");
+		return;
+	}
 	if (gp.nearest) {
 		if (z16) CUDA_OK(cudaMemsetAsync(z16, 0, zero_bytes, stream));
 		GRID_DISPATCH(grid_nearest_forward_kernel, plan, g, stream, gp, B, x, grid, encoded);
@@ -645,6 +690,10 @@ static size_t replica_bytes_of(const tcnn_b200_plan* plan, const GridParams& gp)
 static void backward_prepare(const tcnn_b200_plan* plan, cudaStream_t stream, const GridParams& gp, __half* grid_grads, int zero_first, __half* replicas) {
 	ProfileScope prof(plan, stream, PK_GRID_BWD);
 	if (zero_first) CUDA_OK(cudaMemsetAsync(grid_grads, 0, plan->info.n_params_grid * 2, stream));
+	if (plan->info.n_features_per_level == 1) { // fp32 copy of the table gradient (grid.h:846-859)
+		CHECK(replicas != nullptr, "n_features_per_level = 1 accumulates its gradients in fp32: a workspace is required");
+		CUDA_OK(cudaMemsetAsync(replicas, 0, plan->info.n_params_grid * 4, stream));
+	}
 	if (gp.rep_entries) CUDA_OK(cudaMemsetAsync(replicas, 0, (size_t)gp.rep_entries * plan->info.n_features_per_level * 2 * gp.n_replicas, stream));
 }
 static uint32_t n_grad_chunks(const tcnn_b200_plan* plan) { return (plan->grid.n_features + 7) / 8; } // padding chunks carry no gradient
@@ -654,6 +703,13 @@ static void backward_scatter(const tcnn_b200_plan* plan, cudaStream_t stream, co
 	chunk_end = std::min(chunk_end, n_grad_chunks(plan));
 	if (chunk_begin >= chunk_end) return;
 	const dim3 g((B + 255) / 256, chunk_end - chunk_begin, 1);
+	if (general_grid(plan)) { // all levels in one launch, with the first chunk group
+		if (chunk_begin != 0) return;
+		const dim3 gl((B + 255) / 256, std::max(gp.n_levels, 1u), 1);
+		GRID_DISPATCH_F1(grid_general_backward_kernel, plan, gl, stream, gp, B, x, dL_denc, grid_grads, (float*)replicas);
+		launch_check("grid_general_backward_kernel");
+		return;
+	}
 	if (gp.stochastic && !gp.nearest) { // one random corner per level and sample (grid.h:284-303); Nearest returns before it there too
 		GRID_DISPATCH(grid_stochastic_backward_kernel, plan, g, stream, gp, B, x, dL_denc, grid_grads, chunk_begin);
 		launch_check("grid_stochastic_backward_kernel");
@@ -670,6 +726,13 @@ static void backward_scatter(const tcnn_b200_plan* plan, cudaStream_t stream, co
 // Adds the replica sums of the replicated levels among the encoding chunks [chunk_begin, chunk_end) to the gradient buffer.
 static void backward_finish(const tcnn_b200_plan* plan, cudaStream_t stream, const GridParams& gp, __half* grid_grads, __half* replicas,
 	uint32_t chunk_begin = 0, uint32_t chunk_end = 0xFFFFFFFFu) {
+	if (plan->info.n_features_per_level == 1) { // cast of the fp32 copy, added to what the gradient buffer holds (zero after an Overwrite prepare)
+		if (chunk_begin != 0) return;
+		const uint32_t n = (uint32_t)plan->info.n_params_grid;
+		grid_cast_gradient_kernel<<<(n + 255) / 256, 256, 0, stream>>>(n, (const float*)replicas, grid_grads, 1);
+		launch_check("grid_cast_gradient_kernel");
+		return;
+	}
 	if (!gp.rep_entries) return;
 	const uint32_t F = plan->info.n_features_per_level, lpc = 8 / F;
 	const uint32_t level_begin = std::min(chunk_begin * lpc, gp.n_levels);
@@ -747,7 +810,7 @@ extern "C" int tcnn_b200_encode_backward_noalloc(const tcnn_b200_plan* plan, voi
 	CHECK(x && dL_denc && grid_grads, "null argument");
 	CHECK(plan->enc_kind == ENC_GRID && !plan->f32, "allocation-free entry point: fp16 grid encodings only");
 	const GridParams gp = backward_params(plan, B, true);
-	const size_t need = replica_bytes_of(plan, gp);
+	const size_t need = plan->info.n_features_per_level == 1 ? (size_t)plan->info.n_params_grid * 4 : replica_bytes_of(plan, gp);
 	CHECK(need <= NOALLOC_SCRATCH_BYTES, "allocation-free entry point: this grid needs " + std::to_string(need) + " bytes of scatter scratch, the built-in array holds " +
 		std::to_string(NOALLOC_SCRATCH_BYTES) + " (use tcnn_b200_encode_backward with a workspace)");
 	__half* scratch = noalloc_scratch_address();
@@ -887,7 +950,7 @@ static void launch_mlp(const tcnn_b200_plan* plan, cudaStream_t stream, const Ml
 // Training kernel with the hash-table gradient scatter fused into its last stage; instantiated for the common shapes.
 static bool fused_scatter_available(const tcnn_b200_plan* plan) {
 	const uint32_t D = plan->info.n_input_dims, F = plan->info.n_features_per_level;
-	return !is_wide(plan) && plan->enc_kind == ENC_GRID && !plan->grid.smoothstep && !plan->grid.nearest && !plan->grid.stochastic && plan->activation == ACT_RELU && plan->info.n_hidden_layers <= 4
+	return !is_wide(plan) && plan->enc_kind == ENC_GRID && !general_grid(plan) && !plan->grid.smoothstep && !plan->grid.nearest && !plan->grid.stochastic && plan->activation == ACT_RELU && plan->info.n_hidden_layers <= 4
 		&& plan->info.encoded_width <= 64 && (D == 2 || D == 3) && (F == 2 || F == 4);
 }
 template <int H>
@@ -933,11 +996,12 @@ static void mlp_infer(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t 
 	launch_mlp<MODE_INFER>(plan, stream, a, mlp_grid_size(plan, a.n_tiles, false));
 }
 
-static void mlp_finalize(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t n_parts, const Workspace& w, __half* grads, float* loss_out, bool with_loss, uint32_t n_tiles = 0) {
+static void mlp_finalize(const tcnn_b200_plan* plan, cudaStream_t stream, uint32_t n_parts, const Workspace& w, __half* grads, float* loss_out, bool with_loss, uint32_t n_tiles = 0,
+	bool accumulate = false) {
 	ProfileScope prof(plan, stream, PK_FINALIZE);
 	const uint32_t n = (uint32_t)plan->info.n_params_mlp;
 	mlp_finalize_kernel<<<(n + 31) / 32, 256, 0, stream>>>(n, n_parts, w.dw_partials, grads, with_loss ? w.loss_partials : nullptr, loss_out,
-		mlp_loss_parts(plan, n_tiles, n_parts));
+		mlp_loss_parts(plan, n_tiles, n_parts), accumulate ? 1 : 0);
 	launch_check("mlp_finalize_kernel");
 }
 
@@ -996,7 +1060,7 @@ static void encode_backward_input(const tcnn_b200_plan* plan, cudaStream_t strea
 		CUDA_OK(cudaMemsetAsync(dL_dx, 0, (size_t)B * plan->info.n_input_dims * sizeof(float), stream));
 		return;
 	}
-	GRID_DISPATCH(grid_backward_input_kernel, plan, g, stream, plan->grid, B, x, grid, dL_denc, dL_dx);
+	GRID_DISPATCH_F1(grid_backward_input_kernel, plan, g, stream, plan->grid, B, x, grid, dL_denc, dL_dx);
 	launch_check("grid_backward_input_kernel");
 }
 
@@ -1050,11 +1114,16 @@ extern "C" int tcnn_b200_forward(const tcnn_b200_plan* plan, void* stream, uint3
 	return tcnn_b200_inference(plan, stream, B, x, params, output_fp16, nullptr, workspace);
 }
 
-extern "C" int tcnn_b200_backward(const tcnn_b200_plan* plan, void* stream_, uint32_t B, const float* x, const void* params,
-	const void* dL_doutput, void* dL_dparams, float* dL_dinput, void* workspace) {
+// GradientMode (object.h:115-119)
+enum GradientModeKind { GRADIENT_IGNORE = 0, GRADIENT_OVERWRITE = 1, GRADIENT_ACCUMULATE = 2 };
+extern "C" int tcnn_b200_backward_mode(const tcnn_b200_plan* plan, void* stream_, uint32_t B, const float* x, const void* params,
+	const void* dL_doutput, void* dL_dparams, float* dL_dinput, void* workspace, int gradient_mode) {
 	API_BEGIN
 	require_device(plan); check_batch(B);
 	CHECK(x && params && dL_doutput && workspace, "null argument");
+	CHECK(gradient_mode >= GRADIENT_IGNORE && gradient_mode <= GRADIENT_ACCUMULATE, "gradient_mode must be 0 (Ignore), 1 (Overwrite) or 2 (Accumulate)");
+	if (gradient_mode == GRADIENT_IGNORE) dL_dparams = nullptr;
+	const bool accumulate = gradient_mode == GRADIENT_ACCUMULATE;
 	if (!dL_dparams && !dL_dinput) return 0;
 	cudaStream_t stream = (cudaStream_t)stream_;
 	const Workspace w = carve(plan, B, workspace);
@@ -1063,7 +1132,7 @@ extern "C" int tcnn_b200_backward(const tcnn_b200_plan* plan, void* stream_, uin
 	if (plan->kind == PLAN_ENCODING && plan->f32) { // everything fp32: dL/d(encoded) [B][encoded_width], table gradient (GradientMode::Overwrite)
 		ProfileScope prof(plan, stream, PK_GRID_BWD);
 		if (dL_dparams) {
-			CUDA_OK(cudaMemsetAsync(dL_dparams, 0, plan->info.n_params_grid * sizeof(float), stream));
+			if (!accumulate) CUDA_OK(cudaMemsetAsync(dL_dparams, 0, plan->info.n_params_grid * sizeof(float), stream)); // grid.h:857-859
 			const dim3 gl((B + 255) / 256, std::max(plan->grid.n_levels, 1u), 1);
 			GRID_DISPATCH(grid_backward_f32_kernel, plan, gl, stream, plan->grid, B, x, (const float*)dL_doutput, (float*)dL_dparams);
 			launch_check("grid_backward_f32_kernel");
@@ -1079,7 +1148,7 @@ extern "C" int tcnn_b200_backward(const tcnn_b200_plan* plan, void* stream_, uin
 		return 0;
 	}
 	if (plan->kind == PLAN_ENCODING) { // dL_doutput is dL/d(encoded), fp16 [B][encoded_width]
-		if (g) encode_backward(plan, stream, B, x, (const __half*)dL_doutput, g, /*zero_first=*/1, w.replicas);
+		if (g) encode_backward(plan, stream, B, x, (const __half*)dL_doutput, g, /*zero_first=*/accumulate ? 0 : 1, w.replicas);
 		if (dL_dinput) encode_backward_input(plan, stream, B, x, p, (const __half*)dL_doutput, dL_dinput);
 		return 0;
 	}
@@ -1089,7 +1158,7 @@ extern "C" int tcnn_b200_backward(const tcnn_b200_plan* plan, void* stream_, uin
 	a.dW_partials = g ? w.dw_partials : nullptr;
 	const uint32_t grid = mlp_grid_size(plan, a.n_tiles, true);
 	launch_mlp<MODE_BACKWARD>(plan, stream, a, grid);
-	if (g) mlp_finalize(plan, stream, grid, w, g, nullptr, false);
+	if (g) mlp_finalize(plan, stream, grid, w, g, nullptr, false, 0, accumulate); // beta = 1 of the weight-gradient GEMMs (fully_fused_mlp.cu:769)
 	if (plan->enc_kind == ENC_IDENTITY) {
 		if (dL_dinput) {
 			const uint32_t n = B * plan->info.n_input_dims;
@@ -1103,10 +1172,14 @@ extern "C" int tcnn_b200_backward(const tcnn_b200_plan* plan, void* stream_, uin
 			launch_check("oneblob_backward_input_kernel");
 		}
 	} else {
-		if (g) encode_backward(plan, stream, B, x, w.dL_denc, g + plan->info.n_params_mlp, /*zero_first=*/1, w.replicas);
+		if (g) encode_backward(plan, stream, B, x, w.dL_denc, g + plan->info.n_params_mlp, /*zero_first=*/accumulate ? 0 : 1, w.replicas);
 		if (dL_dinput) encode_backward_input(plan, stream, B, x, p + plan->info.n_params_mlp, w.dL_denc, dL_dinput);
 	}
 	API_END
+}
+extern "C" int tcnn_b200_backward(const tcnn_b200_plan* plan, void* stream, uint32_t B, const float* x, const void* params,
+	const void* dL_doutput, void* dL_dparams, float* dL_dinput, void* workspace) {
+	return tcnn_b200_backward_mode(plan, stream, B, x, params, dL_doutput, dL_dparams, dL_dinput, workspace, GRADIENT_OVERWRITE);
 }
 
 // DifferentiableObject::backward_backward_input (object.h:208-240) of the grid encoding (grid.h:902-1026).
@@ -1115,6 +1188,7 @@ extern "C" int tcnn_b200_backward_backward_input(const tcnn_b200_plan* plan, voi
 	API_BEGIN
 	require_device(plan); check_batch(B);
 	CHECK(!plan->f32, "second-order gradients are implemented for fp16 precision");
+	CHECK(plan->info.n_features_per_level != 1 && !plan->grid.max_level_gpu, "second-order gradients are implemented for n_features_per_level 2, 4, 8 without a per-sample max level");
 	CHECK(plan->kind == PLAN_ENCODING && plan->enc_kind == ENC_GRID,
 		"second-order gradients exist for the stand-alone grid encoding only (FullyFusedMLP has no backward_backward_input in the reference either)");
 	CHECK(x && params && dL_ddLdinput && dL_doutput, "null argument");
@@ -1346,7 +1420,7 @@ static void training_step_launches(const tcnn_b200_plan* plan, cudaStream_t main
 
 	// level groups: up to 4, finest first
 	const uint32_t n_chunks = n_grad_chunks(plan);
-	const uint32_t n_groups = std::min(4u, n_chunks);
+	const uint32_t n_groups = general_grid(plan) ? 1u : std::min(4u, n_chunks); // the general scatter covers all levels in one launch
 	uint32_t group_end = n_chunks;
 	for (uint32_t gi = 0; gi < n_groups; ++gi) {
 		const uint32_t remaining_groups = n_groups - gi;

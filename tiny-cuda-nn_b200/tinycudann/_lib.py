@@ -91,6 +91,8 @@ _SIGNATURES = {
     "tcnn_b200_host_staging_bytes": (C.c_size_t, [_P, C.c_uint32]),
     "tcnn_b200_host_batch_begin": (C.c_int, [_P, _P, C.c_uint32, _P, _P, _P, _P, _P, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]),
     "tcnn_b200_host_batch_end": (C.c_int, [_P, _P, _P, C.c_int]),
+    "tcnn_b200_backward_mode": (C.c_int, [_P, _P, C.c_uint32, _P, _P, _P, _P, _P, _P, C.c_int]),
+    "tcnn_b200_plan_set_max_level_gpu": (C.c_int, [_P, _P]),
     "tcnn_b200_profile_enable": (C.c_int, [_P, C.c_int]),
     "tcnn_b200_profile_read": (C.c_int, [_P, C.POINTER(C.c_float), C.POINTER(C.c_uint32), C.c_uint32]),
 }

@@ -50,6 +50,14 @@ class NativeModule:
         """GridEncoding::set_max_level (grid_interface.h:101-107): levels >= max_level * n_levels encode to zero."""
         check(self.lib.tcnn_b200_plan_set_max_level(self.handle, float(max_level)))
 
+    def set_max_level_gpu(self, max_level_per_sample: torch.Tensor | None):
+        """GridEncoding::set_max_level_gpu (grid_interface.h:113-115): one fp32 max level per sample of the batches to come, on the
+        device; the tensor is kept alive here because the library keeps the pointer."""
+        if max_level_per_sample is not None and (not max_level_per_sample.is_cuda or max_level_per_sample.dtype != torch.float32):
+            raise RuntimeError("set_max_level_gpu takes a float32 CUDA tensor")
+        self._max_level_gpu = max_level_per_sample
+        check(self.lib.tcnn_b200_plan_set_max_level_gpu(self.handle, ptr(max_level_per_sample)))
+
     def refresh_info(self):
         check(self.lib.tcnn_b200_plan_info(self.handle, _lib.C.byref(self.info)))
 
