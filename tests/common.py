@@ -200,3 +200,13 @@ ACCUMULATE_CASES = {"accumulate_2d_T12"}
 
 def max_level_per_sample(B):
     return (0.25 * (1 + np.arange(B) % 4)).astype(np.float32)
+
+
+def big_case_params(cfg, n_in, n_out, seed=77):
+    """Parameters of the full-size golden (tests/golden/cfg1_2d_T19_b18.npz): the reference's initial MLP weights with a table of
+    uniform(-0.5, 0.5) values instead of the initial +-1e-4 - hidden activations of order one, so that gradients at batch 2^18 sit
+    well above fp16 underflow (from the initial table the reference's own fp16 split-K weight gradients are 94 % zeros)."""
+    g, m = oracle_configs(cfg, n_in, n_out)
+    p = O.init_params(m, g, 1337, True)
+    p[m.n_params:] = np.random.default_rng(seed).uniform(-0.5, 0.5, g.n_params).astype(np.float32)
+    return p

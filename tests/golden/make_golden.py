@@ -132,8 +132,72 @@ def encoding_fp32(outdir):
             print(name, "saved", os.path.getsize(os.path.join(outdir, "enc32_" + name + ".npz")), "bytes", flush=True)
 
 
+BIG_CASES = [  # name, config, n_in, n_out, B: the benchmark shape itself; too large to store, so samples + exact checksums
+    ("cfg1_2d_T19_b18", common.CONFIG_1, 2, 3, 1 << 18),
+]
+
+
+def bits_sum(a16):
+    """sum of the 16-bit patterns of an fp16 array as uint64: equal sums over 4 M values = bit-identical arrays, for all practical purposes"""
+    return np.uint64(a16.view(np.uint16).astype(np.uint64).sum())
+
+
+def big(outdir):
+    """`ref_driver dump` at the benchmark batch size: the whole encoded batch and the whole network output enter as exact checksums
+    (sum of bit patterns, float64 column sums) plus every 64th row; the table gradients as per-level sums / norms plus every 997th entry."""
+    for name, cfg, n_in, n_out, B in BIG_CASES:
+        x, t = common.synth_inputs(B, n_in, n_out, seed=1)
+        with tempfile.TemporaryDirectory() as d:
+            x.tofile(os.path.join(d, "x.f32")); t.tofile(os.path.join(d, "t.f32"))
+            json.dump(cfg, open(os.path.join(d, "cfg.json"), "w"))
+            common.big_case_params(cfg, n_in, n_out).tofile(os.path.join(d, "params.f32"))
+            r = subprocess.run([REF, "dump", os.path.join(d, "cfg.json"), str(n_in), str(n_out), str(B), os.path.join(d, "x.f32"),
+                                os.path.join(d, "t.f32"), d, os.path.join(d, "params.f32")], capture_output=True, text=True, timeout=900)
+            print(name, r.returncode, r.stdout.strip(), r.stderr.strip()[-400:], flush=True)
+            if r.returncode != 0:
+                continue
+            meta = json.load(open(os.path.join(d, "meta.json")))
+            rd = lambda fn, dt: np.fromfile(os.path.join(d, fn), dtype=dt)  # noqa: E731
+            P, E, O = meta["n_params"], meta["encoded_width"], meta["padded_output_width"]
+            P_mlp = P - meta["n_params_encoding"]
+            grads = rd("grads.f16", np.float16)
+            gg = grads[P_mlp:].astype(np.float64)
+            enc = rd("encoded_soa.f16", np.float16).reshape(E, B)
+            out = rd("output_padded.f16", np.float16).reshape(B, O)
+            sizes = rd("level_size.u32", np.uint32).astype(np.int64)
+            F = cfg["encoding"]["n_features_per_level"]
+            bounds = np.r_[0, np.cumsum(sizes * F)]
+            # The exact table gradient next to the reference's: 4.2 M sequential fp16 atomics into the 296 entries of level 0 stagnate
+            # (the reference's level-0 norm comes out 7 % low, level 1 0.6 %), so the coarse levels are compared with the oracle's sum.
+            from oracle import tcnn_oracle as O
+            g_cfg, m_cfg = common.oracle_configs(cfg, n_in, n_out, scales=rd("level_scale.f32", np.float32))
+            p16 = common.big_case_params(cfg, n_in, n_out).astype(np.float16)
+            enc_o = O.grid_forward(g_cfg, x, p16[m_cfg.n_params:])
+            y_o, hid_o = O.mlp_forward(m_cfg, p16[: m_cfg.n_params], enc_o)
+            _, dy_o = O.loss_l2(y_o, t, n_out, relative=cfg["loss"]["otype"] == "RelativeL2")
+            _, dx_o = O.mlp_backward(m_cfg, p16[: m_cfg.n_params], enc_o, hid_o, dy_o, y=y_o)
+            gg_o = O.grid_backward(g_cfg, x, dx_o[:, : g_cfg.n_features])
+            np.savez_compressed(
+                os.path.join(outdir, name + ".npz"), config=json.dumps(cfg), n_in=n_in, n_out=n_out, B=B, seed=1, loss=np.float32(meta["loss"]),
+                n_params=P, n_params_mlp=P_mlp,
+                oracle_level_sum=np.array([gg_o[bounds[l]:bounds[l + 1]].sum() for l in range(len(sizes))]),
+                oracle_level_sumsq=np.array([(gg_o[bounds[l]:bounds[l + 1]] ** 2).sum() for l in range(len(sizes))]),
+                encoded_bits_sum=bits_sum(enc), encoded_row_sum=enc.astype(np.float64).sum(axis=1),
+                output_bits_sum=bits_sum(out), output_col_sum=out.astype(np.float64).sum(axis=0), output_rows_sample=out[::64],
+                dL_doutput_bits_sum=bits_sum(rd("dL_doutput.f16", np.float16)),
+                grads_mlp=grads[:P_mlp],
+                grid_sample_val=grads[P_mlp:][::SAMPLE_STRIDE],
+                grid_level_sum=np.array([gg[bounds[l]:bounds[l + 1]].sum() for l in range(len(sizes))]),
+                grid_level_sumsq=np.array([(gg[bounds[l]:bounds[l + 1]] ** 2).sum() for l in range(len(sizes))]),
+                grid_level_nonzero=np.array([np.count_nonzero(gg[bounds[l]:bounds[l + 1]]) for l in range(len(sizes))]),
+            )
+            print(name, "saved", os.path.getsize(os.path.join(outdir, name + ".npz")), "bytes", flush=True)
+
+
 def main(outdir):
     os.makedirs(outdir, exist_ok=True)
+    if os.environ.get("GOLDEN_BIG_ONLY"):
+        return big(outdir)
     if os.environ.get("GOLDEN_SECOND_ORDER_ONLY"):
         return second_order(outdir)
     if os.environ.get("GOLDEN_FP32_ONLY"):
