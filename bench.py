@@ -235,6 +235,37 @@ def run_reference(args, cfg):
     print(json.dumps(line), flush=True)
 
 
+def bind_to_gpu_numa_node(local_rank):
+    """Run this rank's host threads on the CPUs next to its GPU before any pinned buffer is allocated (first touch places the pages on
+    that NUMA node): at N >= 4 every rank pulls 5.2 MB per step over PCIe and a buffer on the far socket halves that rate.
+    -> description of what was done, for the JSON line."""
+    try:
+        import torch
+        pr = torch.cuda.get_device_properties(local_rank)
+        if all(hasattr(pr, k) for k in ("pci_domain_id", "pci_bus_id", "pci_device_id")):
+            bdf = f"{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+        else:
+            import pynvml
+            pynvml.nvmlInit()
+            bdf = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(local_rank)).busId
+            bdf = (bdf.decode() if isinstance(bdf, bytes) else bdf).lower()
+            if len(bdf.split(":")[0]) == 8:  # nvml prints an 8-digit PCI domain, sysfs uses 4
+                bdf = bdf[4:]
+        path = f"/sys/bus/pci/devices/{bdf}/local_cpulist"
+        cpus = set()
+        for part in open(path).read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return "no local CPU of the GPU in this process's affinity mask"
+        os.sched_setaffinity(0, cpus)
+        node = open(f"/sys/bus/pci/devices/{bdf}/numa_node").read().strip()
+        return f"host threads bound to the {len(cpus)} CPUs local to GPU {bdf} (NUMA node {node}) before the pinned allocations"
+    except Exception as e:  # noqa: BLE001 - containers without sysfs PCI topology: run unbound
+        return f"unbound ({type(e).__name__}: {str(e)[:80]})"
+
+
 def config_dict(world, dp_mode="peer"):
     """The `config` object of the JSON line: identical in both arms (ours and --impl reference) for the same --gpus."""
     l2 = ("no flush: one step streams ~0.45 GB of parameter/optimizer state (> 126 MB L2) and cycles 4 distinct resident batches" if CONFIG_NAME == "cfg1" else
@@ -330,6 +361,7 @@ def main():
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
     dev = torch.device("cuda", local_rank)
     torch.cuda.set_device(dev)
+    numa = bind_to_gpu_numa_node(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     elif args.force_dp:  # development aid: the data-parallel step on a one-rank group (ncu can profile it)
@@ -440,7 +472,7 @@ def main():
             "config": config_dict(world), "launch": "one static CUDA graph per (batch, buffers): %d kernel nodes, Adam scalars patched per step" % int(sum(launches_per_step.values())) if world == 1 and tr.graph_stats()[1] else "stream launches", "gradient_exchange": DP_NOTE.get(args.dp_mode, args.dp_mode) if world > 1 else "none",
             "clocks": clk.summary(),
             "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": BATCH * 4 * (N_IN + N_OUT), "d2h_bytes_per_step": 4,
-                    "ms_per_step": e2e_ms, "steps": e2e_steps, "warmup": E2E_WARMUP, "h2d_gb_per_s_per_rank": h2d_gbs, "last_loss_on_host": float(hlosses[(E2E_WARMUP + e2e_steps - 1) % 4096]),
+                    "ms_per_step": e2e_ms, "steps": e2e_steps, "warmup": E2E_WARMUP, "h2d_gb_per_s_per_rank": h2d_gbs, "host_placement": numa, "last_loss_on_host": float(hlosses[(E2E_WARMUP + e2e_steps - 1) % 4096]),
                     "how": "Trainer.training_step_host: pinned host batch -> H2D on the library's copy stream (two staging slots, next batch copied under this step) -> training_step (static graph) -> 4-byte loss D2H on a third stream into pinned memory; one host sync at the end"},
             "gpu_launches": int(sum(launches_per_step.values()) * args.steps),
             "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
