@@ -40,6 +40,21 @@ struct AdamArgs {
 	uint32_t rep_begin, rep_end, n_replicas;
 };
 
+// Square root, reciprocal and 2^x of the optimizer: the SFU approximations (<= 2 ulp) unless built with -DTCNN_B200_ADAM_IEEE.
+// adam_kernel was issue-bound as much as HBM-bound (ncu r02b: issue slots 62 % busy, DRAM 62 %): the IEEE division and square root
+// expand to ~20 instructions per parameter and the per-parameter bias correction (every entry whose step counter lags the
+// optimizer's, i.e. most of the fine levels) to ~40.  A 2-ulp error of the step size changes an update by 3e-7 of ITS size - four
+// orders of magnitude below one fp32 ulp of the weight it is added to; test_adam_vs_oracle / the state-trajectory golden hold.
+#ifdef TCNN_B200_ADAM_IEEE
+__device__ __forceinline__ float adam_sqrt(float x) { return sqrtf(x); }
+__device__ __forceinline__ float adam_div(float x, float y) { return x / y; }
+__device__ __forceinline__ float adam_exp2(float x) { return exp2f(x); }
+#else
+__device__ __forceinline__ float adam_sqrt(float x) { float r; asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float adam_div(float x, float y) { return __fdividef(x, y); }
+__device__ __forceinline__ float adam_exp2(float x) { float r; asm("ex2.approx.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+#endif
+
 __device__ __forceinline__ bool adam_one(const AdamArgs& a, uint32_t i, float g_half, float& w, float& m, float& v, uint32_t& step) {
 	float gradient = a.inv_loss_scale != 0.f ? g_half * a.inv_loss_scale : g_half / a.loss_scale;
 	const bool is_matrix = i < a.n_matrix;
@@ -54,8 +69,8 @@ __device__ __forceinline__ bool adam_one(const AdamArgs& a, uint32_t i, float g_
 	// adam.h:103-105: lr *= sqrtf(1 - powf(beta2, t)) / (1 - powf(beta1, t)).  Two powf per parameter made this kernel
 	// SM-bound (ncu r01a: 85 % SM, 39 % DRAM); parameters in step with the optimizer use the host-evaluated factor.
 	if (step == a.global_step) lr *= a.global_correction;
-	else lr *= sqrtf(1 - exp2f((float)step * a.log2_beta2)) / (1 - exp2f((float)step * a.log2_beta1));
-	const float eff = fminf(fmaxf(lr / (sqrtf(v) + a.epsilon), a.lower_lr_bound), a.upper_lr_bound);
+	else lr *= adam_div(adam_sqrt(1 - adam_exp2((float)step * a.log2_beta2)), 1 - adam_exp2((float)step * a.log2_beta1));
+	const float eff = fminf(fmaxf(adam_div(lr, adam_sqrt(v) + a.epsilon), a.lower_lr_bound), a.upper_lr_bound);
 	// weight_decay(relative * lr, absolute * lr, w)   (common_device.h:870-873)
 	const float decayed = (1 - a.relative_decay * lr) * w - copysignf(a.absolute_decay * lr, w);
 	float nw = decayed - eff * m;
