@@ -1,5 +1,5 @@
 """Bring-up diagnostic (run on the GPU box, not a pytest): each kernel against the oracle, verbose numbers.
-usage: python tests/diag_gpu.py [config_name] [B]"""
+usage: python tests/dev/diag_gpu.py [config_name] [B]"""
 import os
 import sys
 import time
