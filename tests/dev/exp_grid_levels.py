@@ -1,6 +1,6 @@
 """Experiment (GPU box): time grid forward / backward per group of levels to locate scatter contention."""
 import os, sys, copy
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tiny-cuda-nn_b200"))
 import torch
 import tinycudann as tcnn
