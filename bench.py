@@ -222,7 +222,9 @@ def run_reference(args, cfg):
         if r.returncode == 0:
             j = json.loads(r.stdout.strip().splitlines()[-1])
             line.update({"value": j["train_samples_per_s"], "ms_per_step": j["train_ms_per_step"], "steps": steps,
-                         "e2e": {"value": j["train_e2e_samples_per_s"], "unit": "samples/s", "h2d_bytes_per_step": BATCH * 4 * (N_IN + N_OUT), "d2h_bytes_per_step": 4},
+                         "e2e": {"value": j["train_e2e_samples_per_s"], "unit": "samples/s", "h2d_bytes_per_step": BATCH * 4 * (N_IN + N_OUT), "d2h_bytes_per_step": 4,
+                                 "ms_per_step": j["train_e2e_ms_per_step"],
+                                 "how": "pinned host batch -> H2D on a second stream into the other of two device buffers under the previous step -> Trainer::training_step -> Trainer::loss (the reference's blocking loss read-back) every step"},
                          "reference_kind": "reference CUDA build (nvcc -gencode arch=compute_100,code=sm_100 of /root/reference/src), 1 B200",
                          "inference_samples_per_s": j["inference_samples_per_s"], "cpu_baseline": cpu, "gpu_launches": None})
             print(json.dumps(line), flush=True)

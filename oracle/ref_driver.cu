@@ -503,11 +503,28 @@ static int mode_bench(int argc, char** argv) {
 
 	uint32_t it = 0;
 	auto train = [&]() { model.trainer->training_step(stream, inputs[it % n_batches], targets[it % n_batches]); ++it; };
+	// End to end from pinned host batches, as well as the reference's API allows: the batch of step i + 1 is copied on a second stream
+	// into the other of two device buffers while step i computes (what the product's host-batch pipeline does too); the loss comes back
+	// through Trainer::loss, which is the reference's only way to read it and blocks the host (reduce_sum + synchronous 4-byte copy).
+	cudaStream_t copy_stream; CUDA_CHECK_THROW(cudaStreamCreateWithFlags(&copy_stream, cudaStreamNonBlocking));
+	cudaEvent_t filled[2], consumed[2];
+	for (int k = 0; k < 2; ++k) { CUDA_CHECK_THROW(cudaEventCreateWithFlags(&filled[k], cudaEventDisableTiming)); CUDA_CHECK_THROW(cudaEventCreateWithFlags(&consumed[k], cudaEventDisableTiming)); }
+	auto stage = [&](uint32_t k) {
+		CUDA_CHECK_THROW(cudaStreamWaitEvent(copy_stream, consumed[k], 0));
+		CUDA_CHECK_THROW(cudaMemcpyAsync(inputs[k].data(), h_in, (size_t)B * n_in * 4, cudaMemcpyHostToDevice, copy_stream));
+		CUDA_CHECK_THROW(cudaMemcpyAsync(targets[k].data(), h_tg, (size_t)B * n_out * 4, cudaMemcpyHostToDevice, copy_stream));
+		CUDA_CHECK_THROW(cudaEventRecord(filled[k], copy_stream));
+	};
+	uint32_t e2e_it = 0;
 	auto train_e2e = [&]() {
-		CUDA_CHECK_THROW(cudaMemcpyAsync(inputs[0].data(), h_in, (size_t)B * n_in * 4, cudaMemcpyHostToDevice, stream));
-		CUDA_CHECK_THROW(cudaMemcpyAsync(targets[0].data(), h_tg, (size_t)B * n_out * 4, cudaMemcpyHostToDevice, stream));
-		auto ctx = model.trainer->training_step(stream, inputs[0], targets[0]);
+		const uint32_t k = e2e_it & 1u;
+		if (e2e_it == 0) stage(0);
+		stage(k ^ 1u); // next step's batch, under this step's compute
+		CUDA_CHECK_THROW(cudaStreamWaitEvent(stream, filled[k], 0));
+		auto ctx = model.trainer->training_step(stream, inputs[k], targets[k]);
+		CUDA_CHECK_THROW(cudaEventRecord(consumed[k], stream));
 		*h_loss = model.trainer->loss(stream, *ctx);
+		++e2e_it;
 	};
 	auto infer = [&]() { model.network->inference(stream, inputs[it % n_batches], prediction); ++it; };
 	for (uint32_t i = 0; i < warmup; ++i) train();
