@@ -382,7 +382,9 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 			}
 			if (MODE == MODE_INFER && a.output_f32) {
 				const __half* yh = reinterpret_cast<const __half*>(yk);
-				for (uint32_t j = 0; j < a.n_out; ++j) a.output_f32[s * a.n_out + j] = __half2float(yh[j]);
+#pragma unroll
+				for (uint32_t j = 0; j < (uint32_t)MLP_OUT; ++j) // unrolled with a predicate: a run-time loop bound would index yk[] dynamically (local memory)
+					if (j < a.n_out) a.output_f32[s * a.n_out + j] = __half2float(yh[j]);
 			}
 			if (MODE == MODE_TRAIN) {
 				// loss on the fp16 prediction (the reference's network output is fp16), gradients as fp16 * loss_scale.
