@@ -72,6 +72,10 @@ CONFIG_HASH_RNG = {"loss": {"otype": "L2"}, "optimizer": {"otype": "Adam"}, "net
                    "encoding": dict(_GRID_SMALL_3D, hash="Rng", n_features_per_level=2)}
 CONFIG_SMALL_2D = {"loss": {"otype": "L2"}, "optimizer": {"otype": "Adam"}, "network": _net(64, 2, "ReLU", "None"), "encoding": _GRID_SMALL_2D}
 
+# the reference's 16- and 32-neuron FullyFusedMLP (fully_fused_mlp.cu:862-870): zero-padded inside the 64-wide kernel here
+CONFIG_NARROW32 = {"loss": {"otype": "L2"}, "optimizer": {"otype": "Adam"}, "network": _net(32, 3, "ReLU", "None"), "encoding": _GRID_SMALL_2D}
+CONFIG_NARROW16 = {"loss": {"otype": "RelativeL2"}, "optimizer": {"otype": "Adam"}, "network": _net(16, 2, "Sigmoid", "None"), "encoding": _GRID_SMALL_3D}
+
 CONFIG_SNAPSHOT = {  # small enough that a full Trainer::serialize(true) snapshot of the reference is a 250 KB fixture
     "loss": {"otype": "L2"}, "optimizer": {"otype": "Adam", "learning_rate": 1e-2, "beta1": 0.9, "beta2": 0.99, "epsilon": 1e-15, "l2_reg": 1e-6},
     "encoding": {"otype": "HashGrid", "n_levels": 8, "n_features_per_level": 2, "log2_hashmap_size": 10, "base_resolution": 8, "per_level_scale": 1.5},

@@ -45,6 +45,9 @@ CASES = [  # name, config, n_in, n_out, B
     ("hash_rng_3d_T12", common.CONFIG_HASH_RNG, 3, 3, 256),
     ("maxlevelgpu_f4_3d_T14", common.CONFIG_F4, 3, 3, 512),
     ("accumulate_2d_T12", common.CONFIG_SMALL_2D, 2, 3, 512),
+    # 16 and 32 neurons
+    ("narrow32_2d_T12", common.CONFIG_NARROW32, 2, 3, 512),
+    ("narrow16_3d_T12", common.CONFIG_NARROW16, 3, 3, 512),
     # hidden / output activations
     ("act_a_sigmoid_exp_64", common.CONFIG_ACT_A, 2, 3, 512),
     ("act_b_tanh_sigmoid_128", common.CONFIG_ACT_B, 2, 3, 512),

@@ -207,3 +207,18 @@ def test_snapshot_written_by_the_reference_is_read():
     assert np.array_equal(p2, params) and all(np.array_equal(o2[k], opt[k]) for k in ("first_moments", "second_moments", "param_steps"))
     r = subprocess.run([ge.build_cpp_facade_sample(), "--msgpack", os.path.join(golden, "snapshot_small_2d.msgpack")], capture_output=True, text=True, timeout=60)
     assert r.returncode == 0 and f"n_params={P} params_type=__half" in r.stdout and "rewritten_identically=1" in r.stdout, r.stdout + r.stderr
+
+
+def test_network_widths(lib):
+    """FullyFusedMLP widths of the reference (fully_fused_mlp.cu:862-870): 16, 32, 64, 128 - parameter counts W*E + (H-1)*W*W + 16*W."""
+    from tinycudann import _lib
+    for W, H in ((16, 2), (32, 3), (64, 2), (128, 3)):
+        cfg = dict(common.CONFIG_1, network=dict(common.CONFIG_1["network"], n_neurons=W, n_hidden_layers=H))
+        rc, h = _plan(lib, cfg, 2, 3)
+        assert rc == 0, lib.tcnn_b200_last_error()
+        info = _lib.Info()
+        assert lib.tcnn_b200_plan_info(h, C.byref(info)) == 0
+        assert info.n_params_mlp == W * 32 + (H - 1) * W * W + 16 * W
+        lib.tcnn_b200_plan_destroy(h)
+    rc, _ = _plan(lib, dict(common.CONFIG_1, network=dict(common.CONFIG_1["network"], n_neurons=48)), 2, 3)
+    assert rc != 0 and b"16, 32, 64, and 128" in lib.tcnn_b200_last_error()

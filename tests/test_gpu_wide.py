@@ -32,6 +32,8 @@ CASES = {
     "hash_rng_3d_T12": (common.CONFIG_HASH_RNG, 3, 3),
     "maxlevelgpu_f4_3d_T14": (common.CONFIG_F4, 3, 3),  # GridEncoding::set_max_level_gpu, common.MAX_LEVEL_GPU_CASES
     "accumulate_2d_T12": (common.CONFIG_SMALL_2D, 2, 3),
+    "narrow32_2d_T12": (common.CONFIG_NARROW32, 2, 3),   # 32 and 16 neurons: zero-padded inside the 64-wide kernel
+    "narrow16_3d_T12": (common.CONFIG_NARROW16, 3, 3),
     "wide_dp_3d_T15": (common.CONFIG_WIDE_DP, 3, 3),
     "wide_f4_3d_T14": (common.CONFIG_WIDE_F4, 3, 4),
     "oneblob_2d_128x5": (common.CONFIG_ONEBLOB, 2, 3),

@@ -11,7 +11,8 @@ from tests import common
 
 GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
 NAMES = ["cfg1_2d_T19", "shipped_2d_T15", "nerf_3d_T19", "f4_3d_T14", "tiled_smooth_2d", "dense_3d_f4", "nearest_3d_T12", "maxlevel_f4_3d_T14", "stochastic_2d_T12",
-         "f1_2d_T12", "hash_prime_3d_T12", "hash_reversed_2d_T12", "hash_rng_3d_T12", "maxlevelgpu_f4_3d_T14", "accumulate_2d_T12"]
+         "f1_2d_T12", "hash_prime_3d_T12", "hash_reversed_2d_T12", "hash_rng_3d_T12", "maxlevelgpu_f4_3d_T14", "accumulate_2d_T12",
+         "narrow32_2d_T12", "narrow16_3d_T12"]
 
 
 @pytest.fixture(scope="module", params=NAMES)

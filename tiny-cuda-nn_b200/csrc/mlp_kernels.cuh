@@ -44,8 +44,9 @@ struct MlpArgs {
 	uint32_t in_width;             // E_pad: 16, 32, 48 or 64
 	uint32_t n_hidden;             // hidden layers H >= 1 (hidden matmuls = H-1)
 	uint32_t n_out;                // real output dims (<= 16)
+	uint32_t n_neurons;            // 64; 16 or 32 in the GEN instantiations (the narrow network sits zero-padded inside the 64-wide tiles)
 	const __half* input;           // [B][in_width]
-	const __half* params;          // [64 x in], (H-1) x [64 x 64], [16 x 64]   row-major (fully_fused_mlp.cu:654-671)
+	const __half* params;          // [W x in], (H-1) x [W x W], [16 x W]   row-major (fully_fused_mlp.cu:654-671), W = n_neurons
 	__half* output;                // [B][16]  (nullable in TRAIN)
 	float* output_f32;             // [B][n_out] (INFER only, nullable): fused trim_and_cast (object.h:174-175)
 	const float* target;           // [B][n_out] fp32 (TRAIN)
@@ -190,29 +191,38 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 	if (warp == 0) tmem_alloc(tmem_slot, tmem_cols);
 	if (tid == 32) { mbar_init(bar, 1); mbar_init(bar2, 1); mbar_fence_init(); }
 
+	// Network width: 64 compiled in, except in the GEN instantiations, which also run the reference's 16- and 32-neuron networks
+	// (fully_fused_mlp.cu:862-870): their matrices sit zero-padded inside the 64-wide tiles, so every MMA keeps its shape; a padded
+	// neuron has zero weights on both sides, contributes nothing forward and receives a zero gradient.
+	const uint32_t W = GEN ? a.n_neurons : 64u;
 	// weights: global row-major -> swizzled tiles (16-byte chunks, coalesced reads)
 	{
 		const __half* p = a.params;
 		const uint32_t cpr_in = E / 8; // chunks per row of W_in
-		for (uint32_t q = tid; q < 64 * cpr_in; q += NT) {
+		const uint32_t cpr_w = W / 8;  // chunks per row of a hidden / output matrix
+		if constexpr (GEN) {
+			if (W < 64) for (uint8_t* z = w_in + tid * 16; z < w_out + 2048; z += NT * 16) *reinterpret_cast<uint4*>(z) = make_uint4(0, 0, 0, 0);
+			__syncthreads();
+		}
+		for (uint32_t q = tid; q < W * cpr_in; q += NT) {
 			const uint32_t r = q / cpr_in, c = q % cpr_in;
 			*reinterpret_cast<uint4*>(w_in + (c >> 3) * 8192 + sw128(r, c & 7)) = __ldg(reinterpret_cast<const uint4*>(p + r * E) + c);
 		}
-		for (uint32_t q = tid; q < 64 * E; q += NT) { // transposed copy, element-wise (once per CTA)
+		for (uint32_t q = tid; q < W * E; q += NT) { // transposed copy, element-wise (once per CTA)
 			const uint32_t o = q / E, i = q % E;
 			*reinterpret_cast<__half*>(w_inT + sw128(i, o >> 3) + (o & 7) * 2) = p[o * E + i];
 		}
-		p += 64 * E;
+		p += W * E;
 		for (uint32_t l = 0; l + 1 < H; ++l) {
-			for (uint32_t q = tid; q < 64 * 8; q += NT) {
-				const uint32_t r = q >> 3, c = q & 7;
-				*reinterpret_cast<uint4*>(w_hid + l * 8192 + sw128(r, c)) = __ldg(reinterpret_cast<const uint4*>(p + r * 64) + c);
+			for (uint32_t q = tid; q < W * cpr_w; q += NT) {
+				const uint32_t r = q / cpr_w, c = q % cpr_w;
+				*reinterpret_cast<uint4*>(w_hid + l * 8192 + sw128(r, c)) = __ldg(reinterpret_cast<const uint4*>(p + r * W) + c);
 			}
-			p += 64 * 64;
+			p += W * W;
 		}
-		for (uint32_t q = tid; q < 16 * 8; q += NT) {
-			const uint32_t r = q >> 3, c = q & 7;
-			*reinterpret_cast<uint4*>(w_out + sw128(r, c)) = __ldg(reinterpret_cast<const uint4*>(p + r * 64) + c);
+		for (uint32_t q = tid; q < 16 * cpr_w; q += NT) {
+			const uint32_t r = q / cpr_w, c = q % cpr_w;
+			*reinterpret_cast<uint4*>(w_out + sw128(r, c)) = __ldg(reinterpret_cast<const uint4*>(p + r * W) + c);
 		}
 	}
 	fence_proxy_async_smem();
@@ -558,7 +568,7 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 						if (have) { tmem_ld32(t_dw_in + lane_off + half_i * 32, v); tmem_ld_wait(); }
 						if (r < E) {
 #pragma unroll
-							for (int j = 0; j < 32; ++j) out[(half_i * 32 + j) * E + r] = have ? dw_value(v[j]) : 0.f;
+							for (int j = 0; j < 32; ++j) if (!GEN || half_i * 32 + j < (int)W) out[(half_i * 32 + j) * E + r] = have ? dw_value(v[j]) : 0.f;
 						}
 					}
 				}
@@ -572,21 +582,28 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 					if (have) { tmem_ld32(t_dw_in + lane_off + half_i * 32, v); tmem_ld_wait(); }
 					if (r < E) {
 #pragma unroll
-						for (int j = 0; j < 32; ++j) out[(half_i * 32 + j) * E + r] = have ? dw_value(v[j]) : 0.f;
+						for (int j = 0; j < 32; ++j) if (!GEN || half_i * 32 + j < (int)W) out[(half_i * 32 + j) * E + r] = have ? dw_value(v[j]) : 0.f;
 					}
 				}
-				float* o = out + 64 * E;
+				float* o = out + W * E;
 				for (uint32_t l = 0; l + 1 < H; ++l) {
 #pragma unroll
 					for (int half_i = 0; half_i < 2; ++half_i) {
 						uint32_t v[32];
 						if (have) { tmem_ld32(t_dw_hid + l * 64 + lane_off + half_i * 32, v); tmem_ld_wait(); }
-						float4* o4 = reinterpret_cast<float4*>(o + r * 64 + half_i * 32);
+						if constexpr (GEN) { // run-time width: the valid W x W corner of the 64 x 64 accumulator, rows of W floats
+							if (r < W) {
 #pragma unroll
-						for (int j = 0; j < 8; ++j)
-							o4[j] = have ? make_float4(dw_value(v[4 * j]), dw_value(v[4 * j + 1]), dw_value(v[4 * j + 2]), dw_value(v[4 * j + 3])) : make_float4(0, 0, 0, 0);
+								for (int j = 0; j < 32; ++j) if (half_i * 32 + j < (int)W) o[r * W + half_i * 32 + j] = have ? dw_value(v[j]) : 0.f;
+							}
+						} else {
+							float4* o4 = reinterpret_cast<float4*>(o + r * 64 + half_i * 32);
+#pragma unroll
+							for (int j = 0; j < 8; ++j)
+								o4[j] = have ? make_float4(dw_value(v[4 * j]), dw_value(v[4 * j + 1]), dw_value(v[4 * j + 2]), dw_value(v[4 * j + 3])) : make_float4(0, 0, 0, 0);
+						}
 					}
-					o += 64 * 64;
+					o += W * W;
 				}
 				if (warp == 0) {
 #pragma unroll
@@ -594,10 +611,15 @@ __global__ void __launch_bounds__(128 + 128 * NSG, NSG ? 2 : 1) mlp_kernel(const
 						uint32_t v[32];
 						if (have) { tmem_ld32(t_dw_out + lane_off + half_i * 32, v); tmem_ld_wait(); }
 						if (r < 16) {
-							float4* o4 = reinterpret_cast<float4*>(o + r * 64 + half_i * 32);
+							if constexpr (GEN) {
 #pragma unroll
-							for (int j = 0; j < 8; ++j)
-								o4[j] = have ? make_float4(dw_value(v[4 * j]), dw_value(v[4 * j + 1]), dw_value(v[4 * j + 2]), dw_value(v[4 * j + 3])) : make_float4(0, 0, 0, 0);
+								for (int j = 0; j < 32; ++j) if (half_i * 32 + j < (int)W) o[r * W + half_i * 32 + j] = have ? dw_value(v[j]) : 0.f;
+							} else {
+								float4* o4 = reinterpret_cast<float4*>(o + r * 64 + half_i * 32);
+#pragma unroll
+								for (int j = 0; j < 8; ++j)
+									o4[j] = have ? make_float4(dw_value(v[4 * j]), dw_value(v[4 * j + 1]), dw_value(v[4 * j + 2]), dw_value(v[4 * j + 3])) : make_float4(0, 0, 0, 0);
+							}
 						}
 					}
 				}

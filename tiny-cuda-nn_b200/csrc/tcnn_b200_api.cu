@@ -377,8 +377,8 @@ extern "C" int tcnn_b200_plan_create(const char* json_utf8, uint32_t n_input_dim
 	CHECK(ntype == "fullyfusedmlp" || ntype == "megakernelmlp", "network otype '" + ntype + "' is outside the hot path (FullyFusedMLP only)");
 	in.n_neurons = (uint32_t)net.number("n_neurons", 128);
 	in.n_hidden_layers = (uint32_t)net.number("n_hidden_layers", 5);
-	CHECK(in.n_neurons == 64 || in.n_neurons == 128, "FullyFusedMLP: this build implements n_neurons = 64 and 128 (16/32 are out of scope, DESIGN.md)");
-	if (in.n_neurons == 64) CHECK(in.n_hidden_layers >= 1 && in.n_hidden_layers <= (uint32_t)MLP_MAX_HIDDEN, "FullyFusedMLP: n_hidden_layers must be in [1, 5] at 64 neurons");
+	CHECK(in.n_neurons == 16 || in.n_neurons == 32 || in.n_neurons == 64 || in.n_neurons == 128, "FullyFusedMLP only supports 16, 32, 64, and 128 neurons, but got " + std::to_string(in.n_neurons)); // fully_fused_mlp.cu:862-870
+	if (in.n_neurons <= 64) CHECK(in.n_hidden_layers >= 1 && in.n_hidden_layers <= (uint32_t)MLP_MAX_HIDDEN, "FullyFusedMLP: n_hidden_layers must be in [1, 5] at up to 64 neurons");
 	else CHECK(in.n_hidden_layers >= 1 && in.n_hidden_layers <= (uint32_t)WIDE_MAX_HIDDEN, "FullyFusedMLP: n_hidden_layers must be in [1, 8] at 128 neurons");
 	p->activation = parse_activation(net.string("activation", "ReLU"));               // defaults: src/network.cu:107-113
 	p->output_activation = parse_activation(net.string("output_activation", "None"));
@@ -887,7 +887,7 @@ static void launch_mlp_h(const tcnn_b200_plan* plan, cudaStream_t stream, const 
 		// hidden activation other than ReLU: the kernel variant that reads it at run time (never the fused-scatter kernels)
 		// inputs wider than the network (64 < E <= 128): the variant with a two-sub-tile input (activation read at run time)
 		if (a.in_width > 64) { launch_mlp_k<MODE, H, 0, 2, 0, true, true>(plan, stream, a, grid, gp, smem); return; }
-		if (a.activation != ACT_RELU) { launch_mlp_k<MODE, H, 0, 2, 0, true>(plan, stream, a, grid, gp, smem); return; }
+		if (a.activation != ACT_RELU || a.n_neurons < 64) { launch_mlp_k<MODE, H, 0, 2, 0, true>(plan, stream, a, grid, gp, smem); return; }
 	}
 	launch_mlp_k<MODE, H, FD, FF, 0>(plan, stream, a, grid, gp, smem);
 }
@@ -950,7 +950,7 @@ static void launch_mlp(const tcnn_b200_plan* plan, cudaStream_t stream, const Ml
 // Training kernel with the hash-table gradient scatter fused into its last stage; instantiated for the common shapes.
 static bool fused_scatter_available(const tcnn_b200_plan* plan) {
 	const uint32_t D = plan->info.n_input_dims, F = plan->info.n_features_per_level;
-	return !is_wide(plan) && plan->enc_kind == ENC_GRID && !general_grid(plan) && !plan->grid.smoothstep && !plan->grid.nearest && !plan->grid.stochastic && plan->activation == ACT_RELU && plan->info.n_hidden_layers <= 4
+	return plan->info.n_neurons == 64 && plan->enc_kind == ENC_GRID && !general_grid(plan) && !plan->grid.smoothstep && !plan->grid.nearest && !plan->grid.stochastic && plan->activation == ACT_RELU && plan->info.n_hidden_layers <= 4
 		&& plan->info.encoded_width <= 64 && (D == 2 || D == 3) && (F == 2 || F == 4);
 }
 template <int H>
@@ -979,6 +979,7 @@ static MlpArgs base_mlp_args(const tcnn_b200_plan* plan, uint32_t B, const __hal
 	a.in_width = plan->info.encoded_width;
 	a.n_hidden = plan->info.n_hidden_layers;
 	a.n_out = plan->info.n_output_dims;
+	a.n_neurons = plan->info.n_neurons;
 	a.input = input;
 	a.params = params;
 	a.n_mlp_params = (uint32_t)plan->info.n_params_mlp;
