@@ -32,6 +32,9 @@ CASES = {  # name: (config, n_in, n_out, B)
     "cfg4_T24_128x4_b20": (big(common.CONFIG_WIDE_F4, 24), 3, 4, 1 << 20),
     "cfg5_T22_128x3_b19": (big(common.CONFIG_WIDE_DP, 22), 3, 3, 1 << 19),
     "cfg3_nerf_b20": (common.CONFIG_NERF, 3, 4, 1 << 20),
+    # cfg #1 with the reference's narrow network widths
+    "cfg1_32x2_b18": (dict(common.CONFIG_1, network=dict(common.CONFIG_1["network"], n_neurons=32)), 2, 3, 1 << 18),
+    "cfg1_16x2_b18": (dict(common.CONFIG_1, network=dict(common.CONFIG_1["network"], n_neurons=16)), 2, 3, 1 << 18),
 }
 
 
